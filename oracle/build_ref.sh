@@ -1,0 +1,47 @@
+#!/bin/bash
+# TEST INFRASTRUCTURE ONLY -- builds the *unmodified* reference (sfiligoi/omp-bowtie2-prime)
+# from the sources where they lie under /root/reference into oracle/_ref/.
+# No reference source is copied into this repo; outputs (binaries) go only to oracle/_ref/
+# (git-ignored, travels to the GPU box with the gpurun snapshot).
+#
+# Flags = the reference Makefile's (Makefile:39,75-84,208-233,294-302) minus the nvc++-only
+# -DASM_PREFETCH (bt2_idx.h:63-68), compiled with g++ directly (the reference's build system
+# is NOT run).  bowtie2-build-l is linked by hand (its Makefile rule has an empty SHARED_CPPS).
+set -e
+REF=${REF:-/root/reference}
+HERE="$(cd "$(dirname "$0")" && pwd)"
+OUT="$HERE/_ref"
+if [ ! -d "$REF" ]; then
+  echo "build_ref.sh: $REF absent (GPU box?) -- using prebuilt files in $OUT" >&2
+  exit 0
+fi
+mkdir -p "$OUT"
+GCCLIB=$(dirname "$(g++ -print-libgcc-file-name)")
+COMMON="-std=c++17 -DFORCE_ALL_OMP -fopenmp -B$GCCLIB -L$GCCLIB -DPOPCNT_CAPABILITY -DNO_SPINLOCK \
+ -DWITH_QUEUELOCK=1 -w -fno-strict-aliasing -DBOWTIE2_VERSION=\"2.5.4\" -DBUILD_HOST=\"graft\" \
+ -DBUILD_TIME=\"na\" -DCOMPILER_VERSION=\"gcc\" -DCOMPILER_OPTIONS=\"-O3\" -D_LARGEFILE_SOURCE \
+ -D_FILE_OFFSET_BITS=64 -D_GNU_SOURCE -DBOWTIE_MM -DBOWTIE2 -DBOWTIE_64BIT_INDEX -DNDEBUG \
+ -I$REF -I$REF/third_party"
+
+build_align() { # name extra-flags
+  local name=$1; shift
+  if [ "$OUT/$name" -nt "$REF/bt2_search.cpp" ] && [ -z "$FORCE" ]; then return; fi
+  echo "[build_ref] $name" >&2
+  g++ -O3 -msse2 $COMMON "$@" -o "$OUT/$name" "$REF/bowtie2-align.cpp" -lpthread -lz
+}
+
+build_build() {
+  if [ "$OUT/bowtie2-build-l" -nt "$REF/bt2_build.cpp" ] && [ -z "$FORCE" ]; then return; fi
+  echo "[build_ref] bowtie2-build-l" >&2
+  printf '#include <utility>\n#include <string>\n#include <iostream>\nusing namespace std;\n' > "$OUT/pre.h"
+  local S=""
+  for f in bt2_build bowtie_build_main diff_sample ccnt_lut ref_read alphabet shmem edit bt2_idx bt2_io \
+           bt2_locks bt2_util reference ds multikey_qsort limit random_source; do S="$S $REF/$f.cpp"; done
+  g++ -include "$OUT/pre.h" -O2 -msse2 $COMMON -o "$OUT/bowtie2-build-l" $S -lpthread -lz
+}
+
+build_align bowtie2-align-l &
+build_build &
+wait
+if [ -n "$WITH_I16" ]; then build_align bowtie2-align-l-i16 -DENABLE_I16; fi
+ls -la "$OUT" >&2
