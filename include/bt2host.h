@@ -1,0 +1,85 @@
+/*
+ * bt2host.h -- C-ABI of libbt2host.so: the host-side pieces that sit either
+ * side of the GPU hot path when it is used WITHOUT the reference's own host
+ * code (bench.py, the tests, the bt2gpu-align CLI).  They mirror, for the
+ * unpaired end-to-end mode the reference supports:
+ *
+ *   index files    Ebwt::readIntoMemory            bt2_io.cpp:39-633
+ *                  BitPairReference ctor           reference.cpp:31-181
+ *   options        parseOption / presets           bt2_search.cpp:1137-1578, presets.cpp:28-66
+ *                  SeedAlignmentPolicy::parseString aligner_seed_policy.cpp
+ *                  SimpleFunc::f                   simple_func.h:89-110
+ *   read input     FastqPatternSource::parse       pat.cpp:1124-1235, genRandSeed pat.cpp:45-83
+ *   per-read P0    minsc / nceil / interval        bt2_search.cpp:2484-2558
+ *   sink           AlnSinkWrap::finishRead         aln_sink.cpp:643-1384
+ *                  AlnSinkWrap::selectByScore      aln_sink.cpp:1477-1627
+ *                  BowtieMapq2::mapq               unique.h:170-330
+ *                  AlnSinkSam::appendMate          aln_sink.cpp:1889-2124
+ *                  SamConfig::printAlignedOptFlags sam.cpp:121-470
+ *                  StackedAln (CIGAR / MD:Z)       aligner_result.cpp
+ *
+ * In a real drop-in these stay the reference's own C++; this
+ * library exists so that the GPU path can be driven and checked end to end
+ * (FASTQ in, SAM out) on a box that has no reference sources.
+ */
+#ifndef BT2HOST_H_
+#define BT2HOST_H_
+
+#include "bt2gpu.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bt2host_job   bt2host_job;
+typedef struct bt2host_batch bt2host_batch;
+
+/* Load <base>.{1,2,3,4}.bt2l and parse a bowtie2-style option string
+ * (e.g. "--sensitive --dpad 12 -k 3"). Returns NULL and fills err on failure. */
+bt2host_job *bt2host_job_create(const char *index_base, const char *options,
+                                char *err, size_t errlen);
+void bt2host_job_destroy(bt2host_job *job);
+
+const bt2gpu_index  *bt2host_job_index(const bt2host_job *job);
+const bt2gpu_ref    *bt2host_job_ref(const bt2host_job *job);
+const bt2gpu_params *bt2host_job_params(const bt2host_job *job);
+/* Number of reference sequences and their names (as printed in @SQ / RNAME). */
+uint64_t    bt2host_job_nrefs(const bt2host_job *job);
+const char *bt2host_job_refname(const bt2host_job *job, uint64_t i);
+
+/* Parse up to max_reads FASTQ records starting at record `skip` (0-based) of
+ * `path`; fills the per-read scalars of phase P0.  max_reads==0 means all. */
+bt2host_batch *bt2host_batch_from_fastq(const bt2host_job *job, const char *path,
+                                        uint64_t skip, uint64_t max_reads,
+                                        char *err, size_t errlen);
+/* Build a batch from in-memory reads (names may be NULL -> "0","1",...). seq is
+ * ASCII (ACGTN), qual Phred+33 ASCII. */
+bt2host_batch *bt2host_batch_from_arrays(const bt2host_job *job, uint32_t n,
+                                         const uint32_t *off, const char *seq,
+                                         const char *qual, const char *const *names,
+                                         char *err, size_t errlen);
+void bt2host_batch_destroy(bt2host_batch *b);
+const bt2gpu_reads *bt2host_batch_reads(const bt2host_batch *b);
+const char *bt2host_batch_name(const bt2host_batch *b, uint32_t i);
+
+/* SAM header (@HD, @SQ..., @PG) into a malloc'd string the caller frees with
+ * bt2host_free. */
+char *bt2host_sam_header(const bt2host_job *job);
+/* Run the sink over a batch's results: returns a malloc'd buffer holding one
+ * SAM record per read, in read order.  *len receives its length.
+ * mode: 0 = well-formed CIGAR/MD from each alignment's own edits (what the
+ *           reference prints once its DList shallow-copy bug is fixed, SURVEY F14, oracle E)
+ *       1 = byte parity with the unmodified reference: edits are read through
+ *           the per-read aliased scratch (oracle A). */
+char *bt2host_sam_records(const bt2host_job *job, const bt2host_batch *b,
+                          const bt2gpu_results *res, int mode, size_t *len);
+void bt2host_free(void *p);
+
+/* Summary counters of the last bt2host_sam_records call sequence on this job
+ * (ReportingMetrics, aln_sink.h:44-233): [0]=reads [1]=unaligned [2]=aligned once [3]=aligned >1 */
+void bt2host_job_metrics(const bt2host_job *job, uint64_t out[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BT2HOST_H_ */

@@ -1,0 +1,75 @@
+// C-ABI of libbt2host.so (include/bt2host.h).
+#include "host_internal.hpp"
+#include <cstdio>
+#include <cstdlib>
+
+namespace bt2host {
+void sam_for_read(Job& job, const Batch& b, const bt2gpu_results& res, uint32_t ri, int mode, std::string& o);
+std::string sam_header(const Job& job);
+}
+
+static void set_err(char* err, size_t errlen, const std::string& msg) {
+	if(err && errlen) { snprintf(err, errlen, "%s", msg.c_str()); }
+}
+
+extern "C" {
+
+bt2host_job* bt2host_job_create(const char* index_base, const char* options, char* err, size_t errlen) {
+	bt2host_job* job = new bt2host_job();
+	std::string e;
+	if(!bt2host::parse_options(job->j.opt, options ? options : "", e) ||
+	   !bt2host::load_index(job->j, index_base ? index_base : "", e)) {
+		set_err(err, errlen, e);
+		delete job;
+		return nullptr;
+	}
+	return job;
+}
+void bt2host_job_destroy(bt2host_job* job) { delete job; }
+const bt2gpu_index*  bt2host_job_index(const bt2host_job* job)  { return &job->j.ix; }
+const bt2gpu_ref*    bt2host_job_ref(const bt2host_job* job)    { return &job->j.rf; }
+const bt2gpu_params* bt2host_job_params(const bt2host_job* job) { return &job->j.opt.p; }
+uint64_t bt2host_job_nrefs(const bt2host_job* job) { return job->j.refnames.size(); }
+const char* bt2host_job_refname(const bt2host_job* job, uint64_t i) {
+	return i < job->j.refnames.size() ? job->j.refnames[i].c_str() : nullptr;
+}
+
+bt2host_batch* bt2host_batch_from_fastq(const bt2host_job* job, const char* path, uint64_t skip, uint64_t max_reads,
+                                        char* err, size_t errlen) {
+	bt2host_batch* b = new bt2host_batch();
+	std::string e;
+	if(!bt2host::batch_from_fastq(job->j, b->b, path, skip, max_reads, e)) { set_err(err, errlen, e); delete b; return nullptr; }
+	return b;
+}
+bt2host_batch* bt2host_batch_from_arrays(const bt2host_job* job, uint32_t n, const uint32_t* off, const char* seq,
+                                         const char* qual, const char* const* names, char* err, size_t errlen) {
+	bt2host_batch* b = new bt2host_batch();
+	if(!bt2host::batch_from_arrays(job->j, b->b, n, off, seq, qual, names)) { set_err(err, errlen, "bad arrays"); delete b; return nullptr; }
+	return b;
+}
+void bt2host_batch_destroy(bt2host_batch* b) { delete b; }
+const bt2gpu_reads* bt2host_batch_reads(const bt2host_batch* b) { return &b->b.view; }
+const char* bt2host_batch_name(const bt2host_batch* b, uint32_t i) {
+	return i < b->b.names.size() ? b->b.names[i].c_str() : nullptr;
+}
+
+static char* dup_out(const std::string& s, size_t* len) {
+	char* p = (char*)malloc(s.size() + 1);
+	if(!p) return nullptr;
+	memcpy(p, s.data(), s.size()); p[s.size()] = 0;
+	if(len) *len = s.size();
+	return p;
+}
+char* bt2host_sam_header(const bt2host_job* job) { return dup_out(bt2host::sam_header(job->j), nullptr); }
+char* bt2host_sam_records(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, size_t* len) {
+	std::string o;
+	const uint32_t n = res->n;
+	o.reserve((size_t)n * 400);
+	bt2host::Job& j = const_cast<bt2host_job*>(job)->j;
+	for(uint32_t i = 0; i < n; i++) bt2host::sam_for_read(j, b->b, *res, i, mode, o);
+	return dup_out(o, len);
+}
+void bt2host_free(void* p) { free(p); }
+void bt2host_job_metrics(const bt2host_job* job, uint64_t out[4]) { for(int i = 0; i < 4; i++) out[i] = job->j.met[i]; }
+
+} // extern "C"

@@ -1,0 +1,84 @@
+// Internal structures of libbt2host.so (see include/bt2host.h for what each
+// piece mirrors in the reference).
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <cmath>
+#include <limits>
+#include "bt2host.h"
+
+namespace bt2host {
+
+// SimpleFunc (simple_func.h:60-110): f(x) = max(I, min(X, C + L*g(x))), cast by truncation.
+struct SimpleFunc {
+	int type = 0; // 1 const, 2 linear, 3 sqrt, 4 log  (SIMPLE_FUNC_*)
+	double I = -std::numeric_limits<double>::max();
+	double X = std::numeric_limits<double>::max();
+	double C = 0.0, L = 0.0;
+	void init(int t, double c, double l) { type = t; C = c; L = l;
+		I = -std::numeric_limits<double>::max(); X = std::numeric_limits<double>::max(); }
+	void init(int t, double i, double x, double c, double l) { type = t; I = i; X = x; C = c; L = l; }
+	template<typename T> T f(double x) const {
+		double g;
+		if(type == 1) g = 0.0; else if(type == 2) g = x;
+		else if(type == 3) g = std::sqrt(x); else g = std::log(x);
+		double ret = std::max(I, std::min(X, C + L * g));
+		if(ret == std::numeric_limits<double>::max()) return std::numeric_limits<T>::max();
+		if(ret == std::numeric_limits<double>::min()) return std::numeric_limits<T>::min();
+		return (T)ret;
+	}
+	// "S,1,1.15" style (bt2_search.cpp:1436-1474, simple_func.cpp parse)
+	bool parse(const std::string& s, double defC, double defL, double defI, double defX);
+};
+
+struct Options {
+	bt2gpu_params p;
+	SimpleFunc scoreMin, nCeil, msIval;
+	uint32_t seed = 0;       // --seed
+	int trim5 = 0, trim3 = 0;
+	bool phred64 = false;
+	int mapqv = 2;
+	bool yfQuirk = true;     // print YF:Z:LN on every record like the reference does in practice
+	bool noUnal = false;
+	std::string cmdline;
+};
+
+struct Job {
+	// index arrays (owned)
+	std::vector<uint64_t> plen, rstarts, fchr, ftab, eftab, offs;
+	std::vector<uint8_t> ebwt;
+	std::vector<uint64_t> rec_off, rec_len;
+	std::vector<uint8_t> rec_first, refbuf;
+	std::vector<std::string> refnames;
+	std::vector<uint64_t> reflens; // full reference lengths incl. Ns (for @SQ LN)
+	bt2gpu_index ix;
+	bt2gpu_ref rf;
+	Options opt;
+	uint64_t met[4] = {0, 0, 0, 0};
+};
+
+struct Batch {
+	std::vector<uint32_t> off;
+	std::vector<uint8_t> seq, qual;
+	std::vector<uint32_t> seed;
+	std::vector<int32_t> minsc, nceil, interval;
+	std::vector<std::string> names;
+	bt2gpu_reads view;
+	void finalize();
+};
+
+bool load_index(Job& job, const std::string& base, std::string& err);
+bool parse_options(Options& o, const std::string& args, std::string& err);
+uint32_t gen_rand_seed(const uint8_t* seq, const uint8_t* qual, size_t len,
+                       const std::string& name, uint32_t seed);
+void fill_p0(const Job& job, Batch& b); // minsc / nceil / interval per read
+bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_t skip, uint64_t maxn, std::string& err);
+bool batch_from_arrays(const Job& job, Batch& b, uint32_t n, const uint32_t* off, const char* seq,
+                       const char* qual, const char* const* names);
+
+} // namespace bt2host
+
+struct bt2host_job   { bt2host::Job j; };
+struct bt2host_batch { bt2host::Batch b; };

@@ -1,0 +1,236 @@
+// Option parsing, FASTQ input and the per-read scalars of phase P0.
+#include "host_internal.hpp"
+#include <cstdio>
+#include <cstdlib>
+#include <sstream>
+#include <algorithm>
+
+namespace bt2host {
+
+// ---------------------------------------------------------------- options
+static int func_type(const std::string& s) { // SimpleFunc::parseType
+	if(s == "C") return 1; if(s == "L") return 2; if(s == "S") return 3; if(s == "G") return 4;
+	return 0;
+}
+
+// PARSE_FUNC (aligner_seed_policy.cpp:47-75): type, const, coeff, min, (5th token also sets min)
+static bool parse_func(SimpleFunc& f, const std::string& arg) {
+	std::vector<std::string> t; std::string cur; std::istringstream ss(arg);
+	while(std::getline(ss, cur, ',')) t.push_back(cur);
+	if(t.empty() || t.size() > 5) return false;
+	int ty = func_type(t[0]); if(!ty) return false;
+	f.type = ty;
+	if(t.size() >= 2) f.C = atof(t[1].c_str());
+	if(t.size() >= 3) f.L = atof(t[2].c_str());
+	if(t.size() >= 4) f.I = atof(t[3].c_str());
+	if(t.size() >= 5) f.I = atof(t[4].c_str());
+	return true;
+}
+
+// Scoring::initPens (scoring.h:43-66)
+static void init_pens(int32_t* pens, int type, int consMin, int consMax) {
+	for(int i = 0; i < 256; i++) {
+		if(type == 2) { // COST_MODEL_QUAL
+			int ii = std::min(i, 40);
+			float frac = (float)ii / 40.0f;
+			pens[i] = consMin + (int)(frac * (consMax - consMin));
+		} else { // COST_MODEL_CONSTANT
+			pens[i] = consMax;
+		}
+	}
+}
+
+bool parse_options(Options& o, const std::string& args, std::string& err) {
+	const double DMAX = std::numeric_limits<double>::max();
+	bt2gpu_params& p = o.p;
+	memset(&p, 0, sizeof(p));
+	p.abi_version = BT2GPU_ABI_VERSION;
+	// resetOptions (bt2_search.cpp:265-444) + preset "sensitive" (presets.cpp:47-53)
+	p.seedLen = 22; p.seedMms = 0; p.nSeedRounds = 2; p.seedBoostThresh = 300;
+	p.maxhalf = 15; p.doExtend = 1; p.enable8 = 1; p.tighten = 3;
+	p.khits = 1; p.mhits = 50; p.msample = 1; p.nofw = 0; p.norc = 0; p.gapbar = 4;
+	p.rdGapConst = 5; p.rdGapLinear = 3; p.rfGapConst = 5; p.rfGapLinear = 3; p.matchBonus = 0;
+	int maxIters = 400, maxUg = 300, maxDp = 300, maxDpStreak = 15;
+	const int maxItersIncr = 20, maxStreakIncr = 10;
+	int mmType = 2, mmMax = 6, mmMin = 2, nType = 3, penN = 1;
+	bool ignoreQuals = false, sawK = false;
+	o.scoreMin.init(2, -0.6f, -0.6f);
+	o.nCeil.init(2, 0.0, DMAX, 0.0f, 0.15f);
+	o.msIval.init(3, 1.0, DMAX, 1.0f, 1.15f);
+	o.cmdline = args;
+	std::vector<std::string> tok; { std::istringstream ss(args); std::string t; while(ss >> t) tok.push_back(t); }
+	auto need = [&](size_t& i) -> const std::string* {
+		if(i + 1 >= tok.size()) { err = "option " + tok[i] + " needs an argument"; return nullptr; }
+		return &tok[++i];
+	};
+	for(size_t i = 0; i < tok.size(); i++) {
+		const std::string& t = tok[i];
+		const std::string* a;
+		if(t == "--very-fast")           { maxDpStreak = 5;  p.nSeedRounds = 1; p.seedLen = 22; o.msIval.init(3, 1.0, DMAX, 0.0, 2.50); }
+		else if(t == "--fast")           { maxDpStreak = 10; p.nSeedRounds = 2; p.seedLen = 22; o.msIval.init(3, 1.0, DMAX, 0.0, 2.50); }
+		else if(t == "--sensitive")      { maxDpStreak = 15; p.nSeedRounds = 2; p.seedLen = 22; o.msIval.init(3, 1.0, DMAX, 1.0, 1.15); }
+		else if(t == "--very-sensitive") { maxDpStreak = 20; p.nSeedRounds = 3; p.seedLen = 20; o.msIval.init(3, 1.0, DMAX, 1.0, 0.50); }
+		else if(t == "--end-to-end") { }
+		else if(t == "-D") { if(!(a = need(i))) return false; maxDpStreak = atoi(a->c_str()); }
+		else if(t == "-R") { if(!(a = need(i))) return false; p.nSeedRounds = atoi(a->c_str()); }
+		else if(t == "-L") { if(!(a = need(i))) return false; p.seedLen = atoi(a->c_str());
+			if(p.seedLen < 1 || p.seedLen > 32) { err = "-L must be within [1,32]"; return false; } }
+		else if(t == "-N") { if(!(a = need(i))) return false; p.seedMms = atoi(a->c_str()); }
+		else if(t == "-i") { if(!(a = need(i))) return false; if(!parse_func(o.msIval, *a)) { err = "bad -i"; return false; } }
+		else if(t == "--score-min" || t == "--min-score") { if(!(a = need(i))) return false; if(!parse_func(o.scoreMin, *a)) { err = "bad --score-min"; return false; } }
+		else if(t == "--n-ceil") { if(!(a = need(i))) return false; if(!parse_func(o.nCeil, *a)) { err = "bad --n-ceil"; return false; } }
+		else if(t == "--dpad") { if(!(a = need(i))) return false; p.maxhalf = atoi(a->c_str()); }
+		else if(t == "--gbar") { if(!(a = need(i))) return false; p.gapbar = std::max(1, atoi(a->c_str())); }
+		else if(t == "-k") { if(!(a = need(i))) return false; p.khits = std::max(1, atoi(a->c_str())); sawK = true; }
+		else if(t == "--mp") { if(!(a = need(i))) return false; // "MX,MN" (bt2_search.cpp ARG "mp")
+			int mx = 6, mn = 2; if(sscanf(a->c_str(), "%d,%d", &mx, &mn) < 2) mn = std::min(mn, mx); mmMax = mx; mmMin = std::min(mn, mx); }
+		else if(t == "--np") { if(!(a = need(i))) return false; penN = atoi(a->c_str()); }
+		else if(t == "--rdg") { if(!(a = need(i))) return false; sscanf(a->c_str(), "%d,%d", &p.rdGapConst, &p.rdGapLinear); }
+		else if(t == "--rfg") { if(!(a = need(i))) return false; sscanf(a->c_str(), "%d,%d", &p.rfGapConst, &p.rfGapLinear); }
+		else if(t == "--ignore-quals") ignoreQuals = true;
+		else if(t == "--nofw") p.nofw = 1;
+		else if(t == "--norc") p.norc = 1;
+		else if(t == "--seed") { if(!(a = need(i))) return false; o.seed = (uint32_t)strtoul(a->c_str(), nullptr, 10); }
+		else if(t == "--trim5" || t == "-5") { if(!(a = need(i))) return false; o.trim5 = atoi(a->c_str()); }
+		else if(t == "--trim3" || t == "-3") { if(!(a = need(i))) return false; o.trim3 = atoi(a->c_str()); }
+		else if(t == "--phred64") o.phred64 = true;
+		else if(t == "--phred33" || t == "-q" || t == "--reorder" || t == "-t") { }
+		else if(t == "--no-unal") o.noUnal = true;
+		else if(t == "--no-yf-quirk") o.yfQuirk = false;
+		else if(t == "--i16") p.i16 = 1;
+		else if(t == "-p" || t == "--threads") { if(!(a = need(i))) return false; } // batch multiplier in the reference (F8); no meaning here
+		else { err = "unsupported option: " + t; return false; }
+	}
+	if(ignoreQuals) mmType = 3;
+	init_pens(p.mmpens, mmType, mmMin, mmMax);
+	init_pens(p.npens, nType, penN, penN);
+	if(sawK) { p.msample = 0; p.mhits = 0; } // bt2_search.cpp:1681-1687
+	const int mul = (p.khits > 1) ? (p.khits - 1) : 0; // msWorkerConsts, bt2_search.cpp:2207-2211
+	p.streak = maxDpStreak + mul * maxStreakIncr;
+	p.mxDp = maxDp + mul * maxItersIncr;
+	p.mxUg = maxUg + mul * maxItersIncr;
+	p.mxIter = maxIters + mul * maxItersIncr;
+	if(p.mxIter > BT2GPU_MAX_ITER) { err = "FATAL: mxIter too big"; return false; } // bt2_search.cpp:2213
+	return true;
+}
+
+// ---------------------------------------------------------------- reads
+// genRandSeed (pat.cpp:45-83)
+uint32_t gen_rand_seed(const uint8_t* seq, const uint8_t* qual, size_t len,
+                       const std::string& name, uint32_t seed) {
+	uint32_t rseed = (seed + 101) * 59 * 61 * 67 * 71 * 73 * 79 * 83;
+	for(size_t i = 0; i < len; i++) {
+		int p = (int)seq[i];
+		size_t off = ((i & 15) << 1);
+		rseed ^= ((uint32_t)p << off);
+	}
+	for(size_t i = 0; i < len; i++) {
+		int p = (int)qual[i];
+		size_t off = ((i & 3) << 3);
+		rseed ^= (p << off);
+	}
+	for(size_t i = 0; i < name.size(); i++) {
+		int p = (int)name[i];
+		if(p == '/') break;
+		size_t off = ((i & 3) << 3);
+		rseed ^= (p << off);
+	}
+	return rseed;
+}
+
+static inline uint8_t asc2dna(int c) { // alphabet.cpp:142
+	switch(c) { case 'A': case 'a': return 0; case 'C': case 'c': return 1;
+	            case 'G': case 'g': return 2; case 'T': case 't': return 3; default: return 4; }
+}
+
+void Batch::finalize() {
+	view.n = (uint32_t)(off.size() - 1);
+	view.seq_off = off.data(); view.seq = seq.data(); view.qual = qual.data();
+	view.rng_seed = seed.data(); view.minsc = minsc.data(); view.nceil = nceil.data();
+	view.interval = interval.data();
+}
+
+// bt2_search.cpp:2484-2493, 2551-2555; aligner_sw.cpp:44
+void fill_p0(const Job& job, Batch& b) {
+	const size_t n = b.off.size() - 1;
+	b.minsc.resize(n); b.nceil.resize(n); b.interval.resize(n);
+	for(size_t i = 0; i < n; i++) {
+		const size_t rdlen = b.off[i + 1] - b.off[i];
+		int64_t ms = job.opt.scoreMin.f<int64_t>((double)rdlen);
+		if(ms > 0) ms = 0;
+		else if(!job.opt.p.i16 && ms < -254) ms = -254;
+		b.minsc[i] = (int32_t)ms;
+		b.nceil[i] = job.opt.nCeil.f<int>((double)rdlen);
+		b.interval[i] = std::max((int)job.opt.msIval.f<int>((double)rdlen), 1);
+	}
+}
+
+static void add_read(const Job& job, Batch& b, std::string name, const std::string& s, const std::string& q) {
+	// trimming as FastqPatternSource::parse (pat.cpp:1148-1213)
+	size_t t5 = std::min<size_t>((size_t)job.opt.trim5, s.size());
+	size_t rem = s.size() - t5;
+	size_t t3 = std::min<size_t>((size_t)job.opt.trim3, rem);
+	size_t len = rem - t3;
+	if(name.empty()) name = std::to_string(b.names.size());
+	const size_t base = b.seq.size();
+	for(size_t i = 0; i < len; i++) {
+		int c = s[t5 + i]; if(c == '.') c = 'N';
+		b.seq.push_back(asc2dna(c));
+		int qc = (t5 + i < q.size()) ? (unsigned char)q[t5 + i] : 'I';
+		if(job.opt.phred64) qc -= 31;
+		b.qual.push_back((uint8_t)qc);
+	}
+	b.off.push_back((uint32_t)b.seq.size());
+	b.seed.push_back(gen_rand_seed(b.seq.data() + base, b.qual.data() + base, len, name, job.opt.seed));
+	b.names.push_back(std::move(name));
+}
+
+static bool getline_trim(FILE* f, std::string& line) {
+	line.clear();
+	int c;
+	bool any = false;
+	while((c = fgetc(f)) != EOF) {
+		any = true;
+		if(c == '\n') break;
+		if(c != '\r') line.push_back((char)c);
+	}
+	return any;
+}
+
+bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_t skip, uint64_t maxn, std::string& err) {
+	FILE* f = fopen(path.c_str(), "rb");
+	if(!f) { err = "cannot open " + path; return false; }
+	b.off.assign(1, 0);
+	std::string h, s, plus, q;
+	uint64_t rec = 0;
+	while(true) {
+		if(!getline_trim(f, h)) break;
+		if(h.empty()) continue;
+		if(h[0] != '@') { err = "FASTQ record does not start with @ in " + path; fclose(f); return false; }
+		if(!getline_trim(f, s) || !getline_trim(f, plus) || !getline_trim(f, q)) break;
+		// sequence keeps alphabetic characters only (pat.cpp:1151-1163)
+		std::string s2; for(char c : s) { if(c == '.') c = 'N'; if(isalpha((unsigned char)c)) s2.push_back(c); }
+		if(rec >= skip) add_read(job, b, h.substr(1), s2, q);
+		rec++;
+		if(maxn && rec >= skip + maxn) break;
+	}
+	fclose(f);
+	fill_p0(job, b);
+	b.finalize();
+	return true;
+}
+
+bool batch_from_arrays(const Job& job, Batch& b, uint32_t n, const uint32_t* off, const char* seq,
+                       const char* qual, const char* const* names) {
+	b.off.assign(1, 0);
+	for(uint32_t i = 0; i < n; i++) {
+		std::string s(seq + off[i], seq + off[i + 1]);
+		std::string q(qual + off[i], qual + off[i + 1]);
+		add_read(job, b, names ? std::string(names[i]) : std::string(), s, q);
+	}
+	fill_p0(job, b);
+	b.finalize();
+	return true;
+}
+
+} // namespace bt2host
