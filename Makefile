@@ -1,0 +1,31 @@
+# Builds the product libraries in-tree (they travel to the GPU box with the gpurun snapshot):
+#   omp-bowtie2-prime_b200/libbt2gpu.so   CUDA kernels + C-ABI (sm_100a only)
+#   omp-bowtie2-prime_b200/libbt2host.so  host-side index loader / FASTQ reader / SAM sink used by tests, bench and the CLI
+# and the test-only oracle (oracle/liboracle.so, oracle/oracle_align, oracle/_ref/*).
+PKG   := omp-bowtie2-prime_b200
+GPU   := $(PKG)/csrc/gpu
+HOST  := $(PKG)/csrc/host
+NVCC  ?= nvcc
+NVFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=false -Xcompiler -fPIC -shared -Iinclude
+GCCLIB := $(dir $(shell g++ -print-libgcc-file-name))
+CXXFLAGS := -O2 -std=c++17 -fPIC -fopenmp -B$(GCCLIB) -L$(GCCLIB) -Iinclude -w
+
+all: $(PKG)/libbt2gpu.so $(PKG)/libbt2host.so oracle
+
+$(PKG)/libbt2gpu.so: $(wildcard $(GPU)/*.cu $(GPU)/*.cuh) include/bt2gpu.h
+	$(NVCC) $(NVFLAGS) -o $@ $(GPU)/bt2gpu.cu
+
+$(PKG)/libbt2host.so: $(wildcard $(HOST)/*.cpp $(HOST)/*.hpp) include/bt2gpu.h include/bt2host.h
+	g++ $(CXXFLAGS) -shared -o $@ $(HOST)/host_index.cpp $(HOST)/host_reads.cpp $(HOST)/host_sink.cpp $(HOST)/host_api.cpp
+
+oracle:
+	$(MAKE) -C oracle all
+
+emu: tests/emu/emu_pipeline
+tests/emu/emu_pipeline: tests/emu/emu_pipeline.cpp $(wildcard $(GPU)/*.cuh oracle/*.hpp $(HOST)/*.cpp)
+	g++ $(CXXFLAGS) -Ioracle -o $@ tests/emu/emu_pipeline.cpp $(HOST)/host_index.cpp $(HOST)/host_reads.cpp $(HOST)/host_sink.cpp $(HOST)/host_api.cpp
+
+clean:
+	rm -f $(PKG)/*.so oracle/liboracle.so oracle/oracle_align tests/emu/emu_pipeline
+
+.PHONY: all oracle emu clean

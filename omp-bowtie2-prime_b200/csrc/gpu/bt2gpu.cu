@@ -1,0 +1,489 @@
+// libbt2gpu.so -- C-ABI (include/bt2gpu.h) and the host-side orchestration of the
+// sm_100a kernels.  One context = one CUDA device, one stream; index + reference are
+// copied to HBM at create time and stay resident.
+//
+// Per batch the host drives a short loop of phases (the device analogue of the
+// reference's "one omp parallel for + barrier per phase", bt2_search.cpp:2591-2860):
+//   begin -> [round select -> K_seed -> glue -> { step -> K_fill -> backtrace }* -> round end]* -> gather
+// The host only reads back list lengths (a few words) between phases.
+#include <cuda_runtime.h>
+#include <cub/cub.cuh>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <algorithm>
+#include "bt2gpu.h"
+#include "dev_common.cuh"
+#include "k_seed.cuh"
+#include "k_fill.cuh"
+#include "k_scalar.cuh"
+
+using namespace bt2;
+
+#define CK(call) do { cudaError_t e_ = (call); if(e_ != cudaSuccess) { \
+	char b_[512]; snprintf(b_, sizeof(b_), "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+	throw std::string(b_); } } while(0)
+
+enum { PH_SEED = 0, PH_GLUE, PH_RESOLVE, PH_FILL, PH_BT, PH_H2D, PH_D2H, PH_N };
+enum { C_CAND0 = 0, C_CAND1, C_ACTIVE, C_EXT0, C_EXT1, C_ROUNDEND, C_SAMP, C_SEEDTASK, C_N = 16 };
+
+struct DBuf { // growable device buffer
+	void* p = nullptr; size_t cap = 0;
+	void ensure(size_t bytes) {
+		if(bytes <= cap) return;
+		if(p) CK(cudaFree(p));
+		p = nullptr; cap = 0;
+		const size_t want = bytes + bytes / 8 + 256;
+		CK(cudaMalloc(&p, want)); cap = want;
+	}
+	void release() { if(p) cudaFree(p); p = nullptr; cap = 0; }
+	template<typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+struct HBuf { // growable pinned host buffer
+	void* p = nullptr; size_t cap = 0;
+	void ensure(size_t bytes) {
+		if(bytes <= cap) return;
+		if(p) CK(cudaFreeHost(p));
+		p = nullptr; cap = 0;
+		const size_t want = bytes + bytes / 8 + 256;
+		CK(cudaMallocHost(&p, want)); cap = want;
+	}
+	void release() { if(p) cudaFreeHost(p); p = nullptr; cap = 0; }
+	template<typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct bt2gpu_ctx {
+	int device = 0;
+	cudaStream_t stream = nullptr;
+	std::string err;
+	bt2gpu_params hp;
+	DevParams P; DevParams* dP = nullptr;
+	DevIndex ix; DevRef rf;
+	std::vector<void*> resident;      // index / reference allocations
+	uint32_t nslots = 0, sampSlots = 0, maxBatch = 0;
+	// problem-slot arrays
+	DBuf probs, hef, masks, stacks;
+	// per-batch arrays
+	DBuf seq, qual, seq_off, rng_seed, minsc, nceil, interval;
+	DBuf states, scratch, hits, lists[7], counters, stats;
+	DBuf p_sav, p_sorted, p_rank, p_sp2, p_exr, p_exrfw, p_nsp, p_nsmall, p_nexr, p_nelt, p_nadd;
+	DBuf s_ovr, s_ovp, s_ovv, s_sr, s_sv, s_cv, s_rn, s_rcur, s_rth, s_rfl, s_rco, s_rcn, s_rns, s_mass, s_elim;
+	DBuf chunks, sats, alnp, editp, pooltops, poolerr;
+	DBuf nal, ned, albase, edbase, cubtmp;
+	DBuf o_rr, o_alns, o_edits;
+	HBuf h_counters, h_rr, h_alns, h_edits, h_in;
+	// multi sub-batch accumulation
+	std::vector<bt2gpu_read_result> acc_rr; std::vector<bt2gpu_aln> acc_alns; std::vector<bt2gpu_edit> acc_edits;
+	// state of the current resident batch
+	uint32_t n = 0, W = 0, maxOffs = 0; uint64_t nbases = 0;
+	uint64_t out_alns = 0, out_edits = 0;
+	Pools pools;
+	bt2gpu_counters ctr;
+	std::vector<cudaEvent_t> evpool; size_t evused = 0;
+	struct Span { int ph; cudaEvent_t a, b; }; std::vector<Span> spans;
+};
+
+namespace {
+
+template<typename T> T* upload(bt2gpu_ctx* c, const T* src, size_t n) {
+	T* d = nullptr;
+	CK(cudaMalloc((void**)&d, std::max<size_t>(n, 1) * sizeof(T) + 16));
+	if(n) CK(cudaMemcpy(d, src, n * sizeof(T), cudaMemcpyHostToDevice));
+	c->resident.push_back(d);
+	return d;
+}
+
+cudaEvent_t get_event(bt2gpu_ctx* c) {
+	if(c->evused == c->evpool.size()) { cudaEvent_t e; CK(cudaEventCreate(&e)); c->evpool.push_back(e); }
+	return c->evpool[c->evused++];
+}
+struct Phase {
+	bt2gpu_ctx* c; size_t idx;
+	Phase(bt2gpu_ctx* c_, int ph) : c(c_) {
+		bt2gpu_ctx::Span s; s.ph = ph; s.a = get_event(c); s.b = get_event(c);
+		CK(cudaEventRecord(s.a, c->stream)); c->spans.push_back(s); idx = c->spans.size() - 1;
+	}
+	~Phase() { cudaEventRecord(c->spans[idx].b, c->stream); }
+};
+void flush_spans(bt2gpu_ctx* c) {
+	double* acc[PH_N] = { &c->ctr.ms_seed, &c->ctr.ms_glue, &c->ctr.ms_resolve, &c->ctr.ms_extend, &c->ctr.ms_extend, &c->ctr.ms_h2d, &c->ctr.ms_d2h };
+	for(auto& s : c->spans) { float ms = 0; if(cudaEventElapsedTime(&ms, s.a, s.b) == cudaSuccess) *acc[s.ph] += ms; }
+	c->spans.clear(); c->evused = 0;
+}
+
+inline uint32_t nblk(uint64_t n, uint32_t t) { return (uint32_t)((n + t - 1) / t); }
+
+// copy the device counters to the host and wait
+const uint32_t* read_counters(bt2gpu_ctx* c) {
+	CK(cudaMemcpyAsync(c->h_counters.p, c->counters.p, C_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+	CK(cudaStreamSynchronize(c->stream));
+	return c->h_counters.as<uint32_t>();
+}
+void zero_counter(bt2gpu_ctx* c, int which) {
+	CK(cudaMemsetAsync(c->counters.as<uint32_t>() + which, 0, sizeof(uint32_t), c->stream));
+}
+
+void setup_params(bt2gpu_ctx* c, const bt2gpu_params* p) {
+	DevParams& P = c->P; memset(&P, 0, sizeof(P));
+	P.seedLen = p->seedLen; P.seedMms = p->seedMms; P.nSeedRounds = p->nSeedRounds; P.seedBoostThresh = p->seedBoostThresh;
+	P.maxhalf = p->maxhalf; P.mxIter = p->mxIter; P.mxUg = p->mxUg; P.mxDp = p->mxDp; P.streak = p->streak; P.doExtend = p->doExtend;
+	P.enable8 = p->enable8; P.tighten = p->tighten; P.khits = p->khits; P.mhits = p->mhits; P.msample = p->msample;
+	P.nofw = p->nofw; P.norc = p->norc; P.gapbar = p->gapbar;
+	P.rdGapOpen = p->rdGapConst + p->rdGapLinear; P.rdGapExt = p->rdGapLinear;
+	P.rfGapOpen = p->rfGapConst + p->rfGapLinear; P.rfGapExt = p->rfGapLinear;
+	P.matchBonus = p->matchBonus; P.i16 = p->i16;
+	for(int i = 0; i < 256; i++) {
+		P.mmpens[i] = (uint8_t)std::min(255, std::max(0, p->mmpens[i]));
+		P.npens[i] = (uint8_t)std::min(255, std::max(0, p->npens[i]));
+	}
+}
+
+void ensure_batch(bt2gpu_ctx* c, uint32_t n, uint64_t nbases, uint32_t maxOffs) {
+	const uint32_t W = 2 * maxOffs;
+	const size_t nn = (size_t)n + 1;
+	c->seq.ensure(nbases + 16); c->qual.ensure(nbases + 16);
+	c->seq_off.ensure(nn * 4); c->rng_seed.ensure(nn * 4); c->minsc.ensure(nn * 4); c->nceil.ensure(nn * 4); c->interval.ensure(nn * 4);
+	c->states.ensure(nn * sizeof(ReadState));
+	c->scratch.ensure(nn * BT2_SCRATCH_EDITS * 4);
+	c->hits.ensure(nn * W * sizeof(SeedHit));
+	for(int i = 0; i < 7; i++) c->lists[i].ensure(nn * 4);
+	c->p_sav.ensure(nn * W * 2); c->p_sorted.ensure(nn * W); c->p_rank.ensure(nn * W * 2); c->p_sp2.ensure(nn * W * 2);
+	c->p_exr.ensure(nn * W * sizeof(ExRange16)); c->p_exrfw.ensure(nn * W);
+	c->p_nsp.ensure(nn * 4); c->p_nsmall.ensure(nn * 4); c->p_nexr.ensure(nn * 4); c->p_nelt.ensure(nn * 8); c->p_nadd.ensure(nn * 4);
+	const size_t S = c->sampSlots, MI = BT2_SAMPLE_MI;
+	c->s_ovr.ensure(S * 2 * MI * 2); c->s_ovp.ensure(S * 2 * MI * 2); c->s_ovv.ensure(S * 2 * MI * 2);
+	c->s_sr.ensure(S * MI * 2); c->s_sv.ensure(S * MI * 2); c->s_cv.ensure(S * MI * 2);
+	c->s_rn.ensure(S * W * 2); c->s_rcur.ensure(S * W * 2); c->s_rth.ensure(S * W * 2); c->s_rfl.ensure(S * W);
+	c->s_rco.ensure(S * W * 4); c->s_rcn.ensure(S * W * 2); c->s_rns.ensure(S * W * 2); c->s_mass.ensure(S * W * 8); c->s_elim.ensure(S * W);
+	// pools
+	Pools& p = c->pools;
+	p.chunk_cap = (uint32_t)std::min<size_t>(nn * 6 + 4096, 0x7fffffff);
+	p.sat_cap   = (uint32_t)std::min<size_t>(nn * 48 + 65536, 0x7fffffff);
+	p.aln_cap   = (uint32_t)std::min<size_t>(nn * 6 + 4096, 0x7fffffff);
+	p.edit_cap  = (uint32_t)std::min<size_t>(nn * 96 + 65536, 0x7fffffff);
+	c->chunks.ensure((size_t)p.chunk_cap * sizeof(Chunk)); c->sats.ensure((size_t)p.sat_cap * sizeof(SatEntry));
+	c->alnp.ensure((size_t)p.aln_cap * sizeof(AlnRec)); c->editp.ensure((size_t)p.edit_cap * 4);
+	p.chunks = c->chunks.as<Chunk>(); p.sats = c->sats.as<SatEntry>(); p.alns = c->alnp.as<AlnRec>(); p.edits = c->editp.as<uint32_t>();
+	uint32_t* tops = c->pooltops.as<uint32_t>();
+	p.chunk_top = tops + 0; p.sat_top = tops + 1; p.aln_top = tops + 2; p.edit_top = tops + 3;
+	p.error = c->poolerr.as<uint32_t>();
+	c->nal.ensure(nn * 4); c->ned.ensure(nn * 4); c->albase.ensure(nn * 4); c->edbase.ensure(nn * 4);
+	size_t tmp = 0; cub::DeviceScan::ExclusiveSum(nullptr, tmp, (uint32_t*)nullptr, (uint32_t*)nullptr, (int)nn);
+	c->cubtmp.ensure(tmp + 256);
+	c->o_rr.ensure(nn * sizeof(bt2gpu_read_result));
+	c->h_rr.ensure(nn * sizeof(bt2gpu_read_result));
+}
+
+uint32_t max_offs_of(const bt2gpu_ctx* c, const bt2gpu_reads* in, uint32_t lo, uint32_t hi) {
+	uint32_t m = 1;
+	for(uint32_t i = lo; i < hi; i++) {
+		const uint32_t L = in->seq_off[i + 1] - in->seq_off[i];
+		const uint32_t iv = (uint32_t)std::max(1, in->interval[i]);
+		uint32_t k = 1;
+		if((int)L > c->P.seedLen) k += (L - (uint32_t)c->P.seedLen) / iv;
+		m = std::max(m, k);
+	}
+	return m;
+}
+
+void do_upload(bt2gpu_ctx* c, const bt2gpu_reads* in, uint32_t lo, uint32_t hi) {
+	const uint32_t n = hi - lo;
+	const uint32_t b0 = in->seq_off[lo], b1 = in->seq_off[hi];
+	const uint64_t nb = b1 - b0;
+	for(uint32_t i = lo; i < hi; i++) {
+		if(in->interval[i] < 1) throw std::string("bt2gpu: interval must be >= 1");
+		if(in->seq_off[i + 1] < in->seq_off[i]) throw std::string("bt2gpu: seq_off must be non-decreasing");
+	}
+	const uint32_t maxOffs = max_offs_of(c, in, lo, hi);
+	if(2 * maxOffs > 65535u) throw std::string("bt2gpu: too many seeds per read");
+	ensure_batch(c, n, nb, maxOffs);
+	c->n = n; c->nbases = nb; c->maxOffs = maxOffs; c->W = 2 * maxOffs;
+	Phase ph(c, PH_H2D);
+	// offsets are rebased to the sub-batch
+	c->h_in.ensure(((size_t)n + 1) * 4);
+	uint32_t* ho = c->h_in.as<uint32_t>();
+	for(uint32_t i = 0; i <= n; i++) ho[i] = in->seq_off[lo + i] - b0;
+	CK(cudaMemcpyAsync(c->seq_off.p, ho, ((size_t)n + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+	if(nb) {
+		CK(cudaMemcpyAsync(c->seq.p, in->seq + b0, nb, cudaMemcpyHostToDevice, c->stream));
+		CK(cudaMemcpyAsync(c->qual.p, in->qual + b0, nb, cudaMemcpyHostToDevice, c->stream));
+	}
+	if(n) {
+		CK(cudaMemcpyAsync(c->rng_seed.p, in->rng_seed + lo, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+		CK(cudaMemcpyAsync(c->minsc.p, in->minsc + lo, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+		CK(cudaMemcpyAsync(c->nceil.p, in->nceil + lo, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+		CK(cudaMemcpyAsync(c->interval.p, in->interval + lo, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+	}
+	CK(cudaStreamSynchronize(c->stream)); // h_in is reused by the next upload
+}
+
+#define LAUNCH(c) (c)->ctr.launches++
+
+void do_run(bt2gpu_ctx* c) {
+	const uint32_t n = c->n, W = c->W, maxOffs = c->maxOffs;
+	cudaStream_t st = c->stream;
+	c->out_alns = c->out_edits = 0;
+	if(n == 0) return;
+	CK(cudaMemsetAsync(c->counters.p, 0, C_N * 4, st));
+	CK(cudaMemsetAsync(c->pooltops.p, 0, 16, st));
+	CK(cudaMemsetAsync(c->poolerr.p, 0, 4, st));
+	CK(cudaMemsetAsync(c->stats.p, 0, 32 * 8, st));
+	CK(cudaMemsetAsync(c->scratch.p, 0, (size_t)n * BT2_SCRATCH_EDITS * 4, st));
+	uint32_t* cnt = c->counters.as<uint32_t>();
+	unsigned long long* stats = c->stats.as<unsigned long long>();
+	ReadState* states = c->states.as<ReadState>();
+	uint32_t* L[7]; for(int i = 0; i < 7; i++) L[i] = c->lists[i].as<uint32_t>();
+	// L0/L1 round candidates, L2 active, L3/L4 extension ping-pong, L5 round end, L6 sampling
+	BatchArrays ba; ba.n = n; ba.seq_off = c->seq_off.as<uint32_t>(); ba.seq = c->seq.as<uint8_t>(); ba.qual = c->qual.as<uint8_t>();
+	ba.rng_seed = c->rng_seed.as<uint32_t>(); ba.minsc = c->minsc.as<int32_t>(); ba.nceil = c->nceil.as<int32_t>(); ba.interval = c->interval.as<int32_t>();
+	PrioArrays pa; pa.sav = c->p_sav.as<uint16_t>(); pa.sorted = c->p_sorted.as<uint8_t>(); pa.rank = c->p_rank.as<uint16_t>(); pa.sp2 = c->p_sp2.as<uint16_t>();
+	pa.exr = c->p_exr.as<ExRange16>(); pa.exrfw = c->p_exrfw.as<uint8_t>(); pa.nsp = c->p_nsp.as<uint32_t>(); pa.nsmall = c->p_nsmall.as<uint32_t>();
+	pa.nexr = c->p_nexr.as<uint32_t>(); pa.nelt = c->p_nelt.as<uint64_t>(); pa.nelt_added = c->p_nadd.as<uint32_t>();
+	SampleArrays sa; sa.ov_rng = c->s_ovr.as<uint16_t>(); sa.ov_pos = c->s_ovp.as<uint16_t>(); sa.ov_val = c->s_ovv.as<uint16_t>();
+	sa.seen_rng = c->s_sr.as<uint16_t>(); sa.seen_val = c->s_sv.as<uint16_t>(); sa.conv_val = c->s_cv.as<uint16_t>();
+	sa.r_n = c->s_rn.as<uint16_t>(); sa.r_cur = c->s_rcur.as<uint16_t>(); sa.r_thresh = c->s_rth.as<uint16_t>(); sa.r_flags = c->s_rfl.as<uint8_t>();
+	sa.r_conv_off = c->s_rco.as<uint32_t>(); sa.r_conv_n = c->s_rcn.as<uint16_t>(); sa.r_nseen = c->s_rns.as<uint16_t>();
+	sa.mass = c->s_mass.as<double>(); sa.elim = c->s_elim.as<uint8_t>();
+	BtArrays bta; bta.hef = c->hef.as<uint32_t>(); bta.masks = c->masks.as<uint16_t>(); bta.stacks = c->stacks.as<BtFrame>();
+	bta.scratch = c->scratch.as<uint32_t>(); bta.seq = ba.seq; bta.qual = ba.qual;
+	Problem* probs = c->probs.as<Problem>();
+	const Pools pools = c->pools;
+	int seedBlocks = 0; { int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device); seedBlocks = nsm * 8; }
+
+	k_begin<<<nblk(n, 256), 256, 0, st>>>(ba, states, L[0], cnt + C_CAND0); LAUNCH(c);
+	uint32_t ncand = read_counters(c)[C_CAND0];
+	int cand = 0;
+	for(uint32_t round = 0; ncand > 0; round++) {
+		zero_counter(c, C_ACTIVE); zero_counter(c, C_EXT0); zero_counter(c, C_EXT1); zero_counter(c, C_ROUNDEND);
+		zero_counter(c, C_SAMP); zero_counter(c, C_SEEDTASK); zero_counter(c, cand ? C_CAND0 : C_CAND1);
+		k_round_select<<<nblk(ncand, 256), 256, 0, st>>>(c->dP, states, L[cand], ncand, round, L[2], cnt + C_ACTIVE); LAUNCH(c);
+		const uint32_t nactive = read_counters(c)[C_ACTIVE];
+		if(nactive == 0) break;
+		{
+			Phase ph(c, PH_SEED);
+			SeedKernelArgs sk; sk.active = L[2]; sk.nactive = nactive; sk.W = W; sk.maxOffs = maxOffs; sk.states = states; sk.seq = ba.seq;
+			sk.hits = c->hits.as<SeedHit>(); sk.counter = cnt + C_SEEDTASK; sk.stats = stats;
+			const uint64_t ntasks = (uint64_t)nactive * W;
+			const uint32_t blocks = (uint32_t)std::min<uint64_t>((uint64_t)seedBlocks, (ntasks + 31) / 32);
+			k_seed<0><<<blocks, 256, 0, st>>>(c->ix, c->dP, sk); LAUNCH(c);
+		}
+		uint32_t ncur, nsamp;
+		{
+			Phase ph(c, PH_GLUE);
+			k_prio1<<<nblk(nactive, 128), 128, 0, st>>>(c->dP, pools, states, L[2], nactive, c->hits.as<SeedHit>(), W, maxOffs, pa,
+			                                            L[3], cnt + C_EXT0, L[6], cnt + C_SAMP); LAUNCH(c);
+			const uint32_t* hc = read_counters(c);
+			ncur = hc[C_EXT0]; nsamp = hc[C_SAMP];
+			for(uint32_t b = 0; b < nsamp; b += c->sampSlots) {
+				const uint32_t k = std::min(c->sampSlots, nsamp - b);
+				k_prio2<<<nblk(k, 64), 64, 0, st>>>(c->dP, pools, states, L[2], c->hits.as<SeedHit>(), W, maxOffs, pa, sa, L[6], b, k); LAUNCH(c);
+			}
+		}
+		int cur = 0; // L[3+cur] is the current extension list
+		while(ncur > 0) {
+			const int nxt = cur ^ 1;
+			zero_counter(c, nxt ? C_EXT1 : C_EXT0);
+			for(uint32_t b = 0; b < ncur; b += c->nslots) {
+				const uint32_t k = std::min(c->nslots, ncur - b);
+				{ Phase ph(c, PH_RESOLVE);
+				  k_step<<<nblk(k, 128), 128, 0, st>>>(c->dP, c->ix, c->rf, pools, states, L[3 + cur], b, k, probs, L[5], cnt + C_ROUNDEND); LAUNCH(c); }
+				{ Phase ph(c, PH_FILL);
+				  FillArgs fa; fa.probs = probs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.hef = c->hef.as<uint32_t>(); fa.stats = stats + 8;
+				  k_fill<<<nblk(k, BT2_FILL_WARPS), BT2_FILL_WARPS * 32, 0, st>>>(c->dP, fa); LAUNCH(c); }
+				{ Phase ph(c, PH_BT);
+				  k_bt<<<nblk(k, 128), 128, 0, st>>>(c->dP, pools, states, probs, k, bta, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); }
+			}
+			ncur = read_counters(c)[nxt ? C_EXT1 : C_EXT0];
+			cur = nxt;
+		}
+		const uint32_t nend = read_counters(c)[C_ROUNDEND];
+		const int ncandIdx = cand ^ 1;
+		if(nend) { k_round_end<<<nblk(nend, 256), 256, 0, st>>>(c->dP, states, L[5], nend, L[ncandIdx], cnt + (ncandIdx ? C_CAND1 : C_CAND0)); LAUNCH(c); }
+		ncand = read_counters(c)[ncandIdx ? C_CAND1 : C_CAND0];
+		cand = ncandIdx;
+	}
+	// ---- pack results
+	{
+		Phase ph(c, PH_GLUE);
+		k_count<<<nblk(n, 256), 256, 0, st>>>(states, pools, n, c->nal.as<uint32_t>(), c->ned.as<uint32_t>(), stats + 16); LAUNCH(c);
+		size_t tmp = c->cubtmp.cap;
+		CK(cub::DeviceScan::ExclusiveSum(c->cubtmp.p, tmp, c->nal.as<uint32_t>(), c->albase.as<uint32_t>(), (int)n, st)); LAUNCH(c);
+		tmp = c->cubtmp.cap;
+		CK(cub::DeviceScan::ExclusiveSum(c->cubtmp.p, tmp, c->ned.as<uint32_t>(), c->edbase.as<uint32_t>(), (int)n, st)); LAUNCH(c);
+		uint32_t last[4];
+		CK(cudaMemcpyAsync(&last[0], c->albase.as<uint32_t>() + (n - 1), 4, cudaMemcpyDeviceToHost, st));
+		CK(cudaMemcpyAsync(&last[1], c->nal.as<uint32_t>() + (n - 1), 4, cudaMemcpyDeviceToHost, st));
+		CK(cudaMemcpyAsync(&last[2], c->edbase.as<uint32_t>() + (n - 1), 4, cudaMemcpyDeviceToHost, st));
+		CK(cudaMemcpyAsync(&last[3], c->ned.as<uint32_t>() + (n - 1), 4, cudaMemcpyDeviceToHost, st));
+		uint32_t perr = 0;
+		CK(cudaMemcpyAsync(&perr, c->poolerr.p, 4, cudaMemcpyDeviceToHost, st));
+		CK(cudaStreamSynchronize(st));
+		if(perr) { char b[128]; snprintf(b, sizeof(b), "bt2gpu: device pool exhausted (mask %u); use smaller batches", perr); throw std::string(b); }
+		c->out_alns = (uint64_t)last[0] + last[1]; c->out_edits = (uint64_t)last[2] + last[3];
+		c->o_alns.ensure((c->out_alns + 1) * sizeof(bt2gpu_aln)); c->o_edits.ensure((c->out_edits + 1) * sizeof(bt2gpu_edit));
+		k_gather<<<nblk(n, 128), 128, 0, st>>>(states, pools, c->scratch.as<uint32_t>(), n, c->albase.as<uint32_t>(), c->edbase.as<uint32_t>(),
+		                                       c->o_rr.as<bt2gpu_read_result>(), c->o_alns.as<bt2gpu_aln>(), c->o_edits.as<bt2gpu_edit>()); LAUNCH(c);
+	}
+	// ---- counters
+	unsigned long long hs[32];
+	CK(cudaMemcpyAsync(hs, c->stats.p, sizeof(hs), cudaMemcpyDeviceToHost, st));
+	CK(cudaStreamSynchronize(st));
+	CK(cudaGetLastError());
+	c->ctr.reads += n; c->ctr.seeds_searched += hs[0]; c->ctr.lf_steps_search += hs[1]; c->ctr.lf_steps_extend += hs[2]; c->ctr.lf_sides_touched += hs[3];
+	c->ctr.dp_problems += hs[8]; c->ctr.dp_cells += hs[9];
+	c->ctr.sa_rows_resolved += hs[16]; c->ctr.lf_steps_resolve += hs[17]; c->ctr.bt_attempts += hs[18]; c->ctr.bt_steps += hs[19]; c->ctr.alns_reported += hs[20];
+	flush_spans(c);
+}
+
+void do_fetch(bt2gpu_ctx* c, bt2gpu_results* out) {
+	const uint32_t n = c->n;
+	c->h_alns.ensure((c->out_alns + 1) * sizeof(bt2gpu_aln)); c->h_edits.ensure((c->out_edits + 1) * sizeof(bt2gpu_edit));
+	{
+		Phase ph(c, PH_D2H);
+		if(n) CK(cudaMemcpyAsync(c->h_rr.p, c->o_rr.p, (size_t)n * sizeof(bt2gpu_read_result), cudaMemcpyDeviceToHost, c->stream));
+		if(c->out_alns) CK(cudaMemcpyAsync(c->h_alns.p, c->o_alns.p, c->out_alns * sizeof(bt2gpu_aln), cudaMemcpyDeviceToHost, c->stream));
+		if(c->out_edits) CK(cudaMemcpyAsync(c->h_edits.p, c->o_edits.p, c->out_edits * sizeof(bt2gpu_edit), cudaMemcpyDeviceToHost, c->stream));
+	}
+	CK(cudaStreamSynchronize(c->stream));
+	flush_spans(c);
+	out->n = n; out->reads = c->h_rr.as<bt2gpu_read_result>(); out->alns = c->h_alns.as<bt2gpu_aln>(); out->n_alns = c->out_alns;
+	out->edits = c->h_edits.as<bt2gpu_edit>(); out->n_edits = c->out_edits;
+}
+
+} // namespace
+
+extern "C" {
+
+int bt2gpu_abi_version(void) { return BT2GPU_ABI_VERSION; }
+
+bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const bt2gpu_params* p, int device, char* err, size_t errlen) {
+	bt2gpu_ctx* c = nullptr;
+	try {
+		if(!hix || !hrf || !p) throw std::string("bt2gpu_create: null argument");
+		if(p->abi_version != BT2GPU_ABI_VERSION) throw std::string("bt2gpu_create: ABI version mismatch");
+		if(hix->lineRate != 7) throw std::string("bt2gpu_create: only 128-byte sides (.bt2l, lineRate 7) are supported");
+		if(p->matchBonus != 0) throw std::string("bt2gpu_create: end-to-end mode only (matchBonus must be 0)");
+		if(p->i16) throw std::string("bt2gpu_create: the -DENABLE_I16 protocol is not implemented in this build");
+		if(p->seedLen < 1 || p->seedLen > 32) throw std::string("bt2gpu_create: seedLen must be within [1,32]");
+		if(p->mxIter > BT2GPU_MAX_ITER) throw std::string("bt2gpu_create: mxIter too big");
+		int ndev = 0;
+		if(cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) throw std::string("bt2gpu_create: no CUDA device (this library has no CPU path)");
+		if(device < 0 || device >= ndev) throw std::string("bt2gpu_create: bad device ordinal");
+		CK(cudaSetDevice(device));
+		c = new bt2gpu_ctx();
+		c->device = device; c->hp = *p;
+		memset(&c->ctr, 0, sizeof(c->ctr));
+		CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+		setup_params(c, p);
+		CK(cudaMalloc((void**)&c->dP, sizeof(DevParams)));
+		CK(cudaMemcpy(c->dP, &c->P, sizeof(DevParams), cudaMemcpyHostToDevice));
+		// ---- index
+		DevIndex& ix = c->ix;
+		ix.ebwt = upload(c, hix->ebwt, hix->ebwtTotLen);
+		ix.ftab = upload(c, hix->ftab, hix->ftabLen); ix.eftab = upload(c, hix->eftab, hix->eftabLen);
+		ix.offs = upload(c, hix->offs, hix->offsLen); ix.rstarts = upload(c, hix->rstarts, hix->nFrag * 3); ix.plen = upload(c, hix->plen, hix->nPat);
+		for(int i = 0; i < 5; i++) ix.fchr[i] = hix->fchr[i];
+		ix.len = hix->len; ix.zOff = hix->zOff; ix.nFrag = hix->nFrag; ix.nPat = hix->nPat; ix.offRate = hix->offRate; ix.ftabChars = hix->ftabChars;
+		// ---- reference
+		std::vector<uint64_t> tstart(hrf->nrecs), cum(hrf->nrecs), rec0;
+		{ uint64_t cu = 0, pos = 0;
+		  for(uint64_t r = 0; r < hrf->nrecs; r++) {
+			if(hrf->rec_first[r]) { rec0.push_back(r); pos = 0; }
+			tstart[r] = pos; cum[r] = cu; pos += hrf->rec_off[r] + hrf->rec_len[r]; cu += hrf->rec_len[r];
+		  }
+		  rec0.push_back(hrf->nrecs);
+		  if(rec0.size() != hix->nPat + 1) throw std::string("bt2gpu_create: reference records do not match the index (nPat)");
+		}
+		DevRef& rf = c->rf;
+		rf.buf = upload(c, hrf->buf, (hrf->bufBases + 3) / 4);
+		rf.rec_off = upload(c, hrf->rec_off, hrf->nrecs); rf.rec_len = upload(c, hrf->rec_len, hrf->nrecs);
+		rf.rec_tstart = upload(c, tstart.data(), tstart.size()); rf.rec_cum = upload(c, cum.data(), cum.size());
+		rf.ref_rec0 = upload(c, rec0.data(), rec0.size()); rf.nrecs = hrf->nrecs;
+		// ---- problem slots
+		const char* es = getenv("BT2GPU_SLOTS"); const char* eb = getenv("BT2GPU_BATCH");
+		size_t freeB = 0, totB = 0; CK(cudaMemGetInfo(&freeB, &totB));
+		const size_t perSlot = sizeof(Problem) + (size_t)BT2_HEF_WORDS * 4 + (size_t)BT2_MASK_WORDS * 2 + (size_t)BT2_BT_STACK * sizeof(BtFrame);
+		uint32_t slots = es ? (uint32_t)atoi(es) : 131072u;
+		const size_t budget = freeB / 3;
+		if((size_t)slots * perSlot > budget) slots = (uint32_t)(budget / perSlot);
+		if(slots < 64) throw std::string("bt2gpu_create: not enough device memory for the DP problem slots");
+		c->nslots = slots; c->sampSlots = 2048;
+		c->maxBatch = eb ? (uint32_t)atoi(eb) : (1u << 20);
+		if(c->maxBatch < 1) c->maxBatch = 1;
+		c->probs.ensure((size_t)slots * sizeof(Problem)); c->hef.ensure((size_t)slots * BT2_HEF_WORDS * 4);
+		c->masks.ensure((size_t)slots * BT2_MASK_WORDS * 2); c->stacks.ensure((size_t)slots * BT2_BT_STACK * sizeof(BtFrame));
+		c->counters.ensure(C_N * 4); c->stats.ensure(32 * 8); c->pooltops.ensure(16); c->poolerr.ensure(4);
+		c->h_counters.ensure(C_N * 4);
+		CK(cudaDeviceSynchronize());
+	} catch(const std::string& e) {
+		if(err && errlen) snprintf(err, errlen, "%s", e.c_str());
+		if(c) bt2gpu_destroy(c);
+		return nullptr;
+	}
+	return c;
+}
+
+#define API_GUARD(...) \
+	if(!ctx) return -1; \
+	try { cudaSetDevice(ctx->device); __VA_ARGS__; } catch(const std::string& e) { ctx->err = e; ctx->spans.clear(); ctx->evused = 0; return -2; } \
+	return 0;
+
+int bt2gpu_upload(bt2gpu_ctx* ctx, const bt2gpu_reads* in) {
+	API_GUARD({
+		if(!in) throw std::string("bt2gpu_upload: null batch");
+		if(in->n > ctx->maxBatch) throw std::string("bt2gpu_upload: batch larger than BT2GPU_BATCH; use bt2gpu_align_batch");
+		do_upload(ctx, in, 0, in->n);
+		flush_spans(ctx);
+	})
+}
+int bt2gpu_run_resident(bt2gpu_ctx* ctx) { API_GUARD({ do_run(ctx); }) }
+int bt2gpu_fetch(bt2gpu_ctx* ctx, bt2gpu_results* out) { API_GUARD({ if(!out) throw std::string("bt2gpu_fetch: null out"); do_fetch(ctx, out); }) }
+
+int bt2gpu_align_batch(bt2gpu_ctx* ctx, const bt2gpu_reads* in, bt2gpu_results* out) {
+	API_GUARD({
+		if(!in || !out) throw std::string("bt2gpu_align_batch: null argument");
+		if(in->n <= ctx->maxBatch) {
+			do_upload(ctx, in, 0, in->n); do_run(ctx); do_fetch(ctx, out);
+		} else {
+			ctx->acc_rr.clear(); ctx->acc_alns.clear(); ctx->acc_edits.clear();
+			for(uint32_t lo = 0; lo < in->n; lo += ctx->maxBatch) {
+				const uint32_t hi = std::min(in->n, lo + ctx->maxBatch);
+				bt2gpu_results r;
+				do_upload(ctx, in, lo, hi); do_run(ctx); do_fetch(ctx, &r);
+				const uint32_t ab = (uint32_t)ctx->acc_alns.size(), eb2 = (uint32_t)ctx->acc_edits.size();
+				for(uint32_t i = 0; i < r.n; i++) { bt2gpu_read_result x = r.reads[i]; x.aln_off += ab; x.scratch_off += eb2; ctx->acc_rr.push_back(x); }
+				for(uint64_t i = 0; i < r.n_alns; i++) { bt2gpu_aln x = r.alns[i]; x.edit_off += eb2; ctx->acc_alns.push_back(x); }
+				ctx->acc_edits.insert(ctx->acc_edits.end(), r.edits, r.edits + r.n_edits);
+			}
+			out->n = in->n; out->reads = ctx->acc_rr.data(); out->alns = ctx->acc_alns.data(); out->n_alns = ctx->acc_alns.size();
+			out->edits = ctx->acc_edits.data(); out->n_edits = ctx->acc_edits.size();
+		}
+	})
+}
+
+int bt2gpu_get_counters(bt2gpu_ctx* ctx, bt2gpu_counters* c) { if(!ctx || !c) return -1; *c = ctx->ctr; return 0; }
+int bt2gpu_reset_counters(bt2gpu_ctx* ctx) { if(!ctx) return -1; memset(&ctx->ctr, 0, sizeof(ctx->ctr)); return 0; }
+const char* bt2gpu_last_error(const bt2gpu_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+void bt2gpu_destroy(bt2gpu_ctx* c) {
+	if(!c) return;
+	cudaSetDevice(c->device);
+	cudaDeviceSynchronize();
+	for(void* p : c->resident) cudaFree(p);
+	if(c->dP) cudaFree(c->dP);
+	DBuf* all[] = { &c->probs, &c->hef, &c->masks, &c->stacks, &c->seq, &c->qual, &c->seq_off, &c->rng_seed, &c->minsc, &c->nceil, &c->interval,
+		&c->states, &c->scratch, &c->hits, &c->lists[0], &c->lists[1], &c->lists[2], &c->lists[3], &c->lists[4], &c->lists[5], &c->lists[6], &c->counters, &c->stats,
+		&c->p_sav, &c->p_sorted, &c->p_rank, &c->p_sp2, &c->p_exr, &c->p_exrfw, &c->p_nsp, &c->p_nsmall, &c->p_nexr, &c->p_nelt, &c->p_nadd,
+		&c->s_ovr, &c->s_ovp, &c->s_ovv, &c->s_sr, &c->s_sv, &c->s_cv, &c->s_rn, &c->s_rcur, &c->s_rth, &c->s_rfl, &c->s_rco, &c->s_rcn, &c->s_rns, &c->s_mass, &c->s_elim,
+		&c->chunks, &c->sats, &c->alnp, &c->editp, &c->pooltops, &c->poolerr, &c->nal, &c->ned, &c->albase, &c->edbase, &c->cubtmp, &c->o_rr, &c->o_alns, &c->o_edits };
+	for(DBuf* b : all) b->release();
+	HBuf* hall[] = { &c->h_counters, &c->h_rr, &c->h_alns, &c->h_edits, &c->h_in };
+	for(HBuf* b : hall) b->release();
+	for(cudaEvent_t e : c->evpool) cudaEventDestroy(e);
+	if(c->stream) cudaStreamDestroy(c->stream);
+	delete c;
+}
+
+} // extern "C"

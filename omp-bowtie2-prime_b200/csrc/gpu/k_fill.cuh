@@ -1,0 +1,173 @@
+// K_fill: the end-to-end affine-gap DP fill of one read-window problem per warp.
+//   SwAligner::alignEnd2EndSseU8 / EEU8_alignNucleotides / EEU8_alignOne / EEU8_lazyF
+//       aligner_swsse_ee_u8.cpp:250-671   (recurrence, unsigned saturating 8-bit, start 0xff)
+//   SwAligner::buildQueryProfileEnd2EndSseU8   aligner_swsse_ee_u8.cpp:71-134
+//   candidate gathering + DpBtCandidate order  aligner_swsse_ee_u8.cpp:600-671, aligner_sw_nuc.h
+//
+// The reference computes the full rdlen x rflen rectangle in a Farrar-striped SSE2
+// layout; results do not depend on the evaluation order, so here the rectangle is
+// swept as a wavefront: the rows are cut into 64 strips of R = ceil(rdlen/64) rows,
+// strip v works on column t-v at step t.  Two strips share a 32-bit register as two
+// signed 16-bit lanes (strip L in the low half, strip 32+L in the high half of lane L),
+// because on sm_100a the 16x2 DPX instructions (VIADDMNMX.S16x2, VIMNMX3.S16x2) are
+// native while the 8x4 video intrinsics (__vmaxu4/__vsubus4) are emulated with 4-5
+// LOP3/PRMT each (SASS evidence).  u8 saturation is exact in 16 bits:
+// subs_u8(a,b) == max(a-b,0) for 0<=a,b<=255, which is one VIADDMNMX.
+// Strip boundaries travel down with __shfl_up_sync.  Every cell is stored as one
+// 32-bit word H | E<<8 | F<<16 in a skewed layout [(col+strip)*R+k][strip] so that
+// each store instruction writes one contiguous 128-byte line.
+#pragma once
+#include "dev_common.cuh"
+
+namespace bt2 {
+
+struct FillArgs {
+	Problem*         probs;     // [nslots]
+	uint32_t         nprob;
+	const ReadState* states;
+	const uint8_t*   seq;
+	const uint8_t*   qual;
+	uint32_t*        hef;       // [nslots * BT2_HEF_WORDS]
+	unsigned long long* stats;  // [0] problems [1] cells
+};
+
+#define BT2_FILL_WARPS 4
+struct FillShared {
+	uint32_t tab[3 * 5 * 64];          // negated penalties, pre-positioned per half
+	uint8_t  refc[BT2GPU_MAX_COLS + 8]; // reference code 0..4 per column
+	uint8_t  hlast[BT2GPU_MAX_COLS + 8];
+	uint16_t ckey[BT2GPU_MAX_COLS + 8];
+};
+
+__device__ __forceinline__ uint32_t pack2(int lo, int hi) { return ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16); }
+
+template<int R>
+__device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillShared& sh, uint32_t* __restrict__ hef, uint32_t lane) {
+	const int rows = pb.rows, cols = pb.cols;
+	const int nv = (rows + R - 1) / R;                 // active strips
+	const uint32_t neg_rdgo = pack2(-P.rdGapOpen, -P.rdGapOpen), neg_rdge = pack2(-P.rdGapExt, -P.rdGapExt);
+	const uint32_t neg_rfgo = pack2(-P.rfGapOpen, -P.rfGapOpen), neg_rfge = pack2(-P.rfGapExt, -P.rfGapExt);
+	// gap barrier masks per row of the two strips (aligner_swsse_ee_u8.cpp:101-115: first/last gapbar rows)
+	uint32_t gbm[R];
+	#pragma unroll
+	for(int k = 0; k < R; k++) {
+		const int rlo = (int)lane * R + k, rhi = (32 + (int)lane) * R + k;
+		const bool alo = !(rlo < P.gapbar || rows - 1 - rlo < P.gapbar), ahi = !(rhi < P.gapbar || rows - 1 - rhi < P.gapbar);
+		gbm[k] = (alo ? 0xffffu : 0u) | (ahi ? 0xffff0000u : 0u);
+	}
+	const bool strip_lo = (int)lane < nv, strip_hi = 32 + (int)lane < nv;
+	// which (lane, half, k) owns the last row
+	const int vstar = (rows - 1) / R, kstar = (rows - 1) - vstar * R;
+	const bool own_lo = vstar == (int)lane, own_hi = vstar == 32 + (int)lane;
+	uint32_t Hp[R], Ep[R];
+	#pragma unroll
+	for(int k = 0; k < R; k++) { Hp[k] = 0; Ep[k] = 0; }
+	uint32_t sendH = 0, sendF = 0, prevRecvH = (lane == 0) ? 0x000000ffu : 0u;
+	const int nsteps = cols + nv - 1;
+	for(int t = 0; t < nsteps; t++) {
+		const int c_lo = t - (int)lane, c_hi = c_lo - 32;
+		const bool act_lo = strip_lo && c_lo >= 0 && c_lo < cols, act_hi = strip_hi && c_hi >= 0 && c_hi < cols;
+		const uint32_t am = (act_lo ? 0xffffu : 0u) | (act_hi ? 0xffff0000u : 0u);
+		// values produced by the strip above in the previous step
+		uint32_t recvH = __shfl_up_sync(0xffffffffu, sendH, 1), recvF = __shfl_up_sync(0xffffffffu, sendF, 1);
+		const uint32_t wrapH = __shfl_sync(0xffffffffu, sendH, 31), wrapF = __shfl_sync(0xffffffffu, sendF, 31);
+		if(lane == 0) { recvH = 0x00ffu | (wrapH << 16); recvF = (wrapF << 16); } // row 0: H(-1,*) = 0xff, F = 0
+		const uint32_t x_lo = act_lo ? sh.refc[c_lo] : 4u, x_hi = act_hi ? sh.refc[c_hi] : 4u;
+		uint32_t diag = prevRecvH, f = recvF;
+		uint32_t* outp = hef + (((uint32_t)t * R) << 6) + lane;
+		#pragma unroll
+		for(int k = 0; k < R; k++) {
+			const uint32_t s = sh.tab[(k * 5 + x_lo) * 64 + lane] | sh.tab[(k * 5 + x_hi) * 64 + 32 + lane];
+			const uint32_t hd = diag; diag = Hp[k];
+			f &= gbm[k];
+			uint32_t h = __viaddmax_s16x2(hd, s, 0u);
+			const uint32_t e = Ep[k];
+			h = __vimax3_s16x2(h, e, f);
+			// one word per cell: H | E<<8 | F<<16
+			if(act_lo) outp[(k << 6)]      = __byte_perm(__byte_perm(h, e, 0x0040), f, 0x5410);
+			if(act_hi) outp[(k << 6) + 32] = __byte_perm(__byte_perm(h, e, 0x0062), f, 0x7610);
+			if(k == kstar) {
+				if(own_lo && act_lo) sh.hlast[c_lo] = (uint8_t)(h & 0xffu);
+				if(own_hi && act_hi) sh.hlast[c_hi] = (uint8_t)((h >> 16) & 0xffu);
+			}
+			const uint32_t t1 = __viaddmax_s16x2(h, neg_rdgo, 0u) & gbm[k];
+			const uint32_t en = __viaddmax_s16x2(e, neg_rdge, t1);
+			const uint32_t t2 = __viaddmax_s16x2(h, neg_rfgo, 0u);
+			f = __viaddmax_s16x2(f, neg_rfge, t2);
+			Hp[k] = h & am; Ep[k] = en & am;
+		}
+		sendH = Hp[R - 1]; sendF = f & am;
+		prevRecvH = (lane == 0) ? (0x00ffu | (recvH & 0xffff0000u)) : recvH;
+	}
+}
+
+__global__ void __launch_bounds__(BT2_FILL_WARPS * 32) k_fill(const DevParams* __restrict__ Pp, const FillArgs a) {
+	__shared__ FillShared shs[BT2_FILL_WARPS];
+	const DevParams& P = *Pp;
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint32_t slot = blockIdx.x * BT2_FILL_WARPS + warp;
+	if(slot >= a.nprob) return;
+	Problem& pb = a.probs[slot];
+	if(pb.read == BT2_NIL) return;
+	FillShared& sh = shs[warp];
+	const ReadState& rs = a.states[pb.read];
+	const int rows = pb.rows, cols = pb.cols, R = pb.R;
+	const bool fw = pb.fw != 0;
+	const uint8_t* rseq = a.seq + rs.seq_off; const uint8_t* rqual = a.qual + rs.seq_off;
+	// query profile: tab[(k*5+x)*64 + v] = -(penalty of row v*R+k against reference code x), positioned in its half
+	for(int idx = (int)lane; idx < R * 64; idx += 32) {
+		const int k = idx / 64, v = idx - k * 64;
+		const int r = v * R + k;
+		int rdc = 4, q = 0;
+		if(r < rows) {
+			if(fw) { rdc = rseq[r]; q = rqual[r]; }
+			else { const int c0 = rseq[rows - 1 - r]; rdc = c0 > 3 ? 4 : 3 - c0; q = rqual[rows - 1 - r]; }
+			q -= 33; if(q < 0) q = 0; if(q > 255) q = 255;
+		}
+		#pragma unroll
+		for(int x = 0; x < 5; x++) {
+			int pen = 0;
+			if(r < rows) pen = (x == 4 || rdc > 3) ? (int)P.npens[q] : (x == rdc ? 0 : (int)P.mmpens[q]);
+			const uint32_t neg = (uint32_t)(-pen) & 0xffffu;
+			sh.tab[(k * 5 + x) * 64 + v] = v < 32 ? neg : (neg << 16);
+		}
+	}
+	for(int c = (int)lane; c < cols; c += 32) {
+		const uint32_t m = pb.rf[c];
+		sh.refc[c] = (uint8_t)(m > 15 ? 4 : (31 - __clz(m)));
+		sh.hlast[c] = 0;
+	}
+	__syncwarp();
+	uint32_t* hef = a.hef + (size_t)slot * BT2_HEF_WORDS;
+	if(R == 1) fill_body<1>(P, pb, sh, hef, lane);
+	else if(R == 2) fill_body<2>(P, pb, sh, hef, lane);
+	else fill_body<3>(P, pb, sh, hef, lane);
+	__syncwarp();
+	// ---- last-row candidates: H-0xff >= minsc, sorted by (score desc, col desc)
+	const int minsc = pb.minsc;
+	int lrmax = 0; uint32_t ncand = 0;
+	for(int c0 = 0; c0 < cols; c0 += 32) {
+		const int c = c0 + (int)lane;
+		const int hv = c < cols ? (int)sh.hlast[c] : 0;
+		lrmax = max(lrmax, hv);
+		const bool isc = c < cols && (hv - 255) >= minsc;
+		const uint32_t bal = __ballot_sync(0xffffffffu, isc);
+		if(isc) sh.ckey[ncand + __popc(bal & ((1u << lane) - 1))] = (uint16_t)((hv << 8) | c);
+		ncand += __popc(bal);
+	}
+	#pragma unroll
+	for(int o = 16; o > 0; o >>= 1) lrmax = max(lrmax, __shfl_xor_sync(0xffffffffu, lrmax, o));
+	__syncwarp();
+	for(uint32_t j = lane; j < ncand; j += 32) {
+		const uint32_t key = sh.ckey[j];
+		uint32_t rank = 0;
+		for(uint32_t i = 0; i < ncand; i++) rank += (sh.ckey[i] > key) ? 1u : 0u;
+		pb.cand[rank] = (uint16_t)key;
+	}
+	if(lane == 0) {
+		pb.lrmax = lrmax; pb.ncand = ncand;
+		atomicAdd(&a.stats[0], 1ull); atomicAdd(&a.stats[1], (unsigned long long)rows * cols);
+	}
+}
+
+} // namespace bt2

@@ -1,0 +1,189 @@
+// Thread-per-read / thread-per-problem kernels around the two warp-cooperative ones:
+// batch setup, round selection, the glue (dev_prio.cuh), the extension step
+// (dev_step.cuh), the post-fill stage (dev_bt.cuh) and result packing (dev_gather.cuh).
+// Work lists are compact arrays of read ids appended to with one atomic per entry.
+#pragma once
+#include "dev_common.cuh"
+#include "dev_prio.cuh"
+#include "dev_step.cuh"
+#include "dev_bt.cuh"
+#include "dev_gather.cuh"
+
+namespace bt2 {
+
+struct BatchArrays {
+	uint32_t n;
+	const uint32_t* seq_off; const uint8_t* seq; const uint8_t* qual;
+	const uint32_t* rng_seed; const int32_t* minsc; const int32_t* nceil; const int32_t* interval;
+};
+
+__device__ __forceinline__ void list_append(uint32_t* list, uint32_t* cnt, uint32_t v) { list[atomicAdd(cnt, 1u)] = v; }
+
+__global__ void k_begin(const BatchArrays b, ReadState* states, uint32_t* list, uint32_t* cnt) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= b.n) return;
+	ReadState rs;
+	const uint32_t so = b.seq_off[i];
+	read_begin(rs, so, b.seq_off[i + 1] - so, b.rng_seed[i], b.minsc[i], b.nceil[i], b.interval[i]);
+	states[i] = rs;
+	if(rs.phase != RS_FINISHED) list_append(list, cnt, i);
+}
+
+// reads that want seed round `round` go to `out`; the others are finished
+__global__ void k_round_select(const DevParams* __restrict__ Pp, ReadState* states, const uint32_t* in, uint32_t nin,
+                               uint32_t round, uint32_t* out, uint32_t* cnt) {
+	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+	if(j >= nin) return;
+	ReadState& rs = states[in[j]];
+	uint32_t off;
+	if(!round_wanted(*Pp, rs, round, off)) { rs.phase = RS_FINISHED; return; }
+	rs.round = (uint8_t)round; rs.roundsRun++;
+	rs.phase = RS_EXTEND;
+	rs.nDpFail = 0; rs.passStarted = 0; rs.cur_i = 0; rs.first = 1; rs.sat_n = 0; rs.neltLeft = 0; // extendSeeds entry (:310-312)
+	list_append(out, cnt, in[j]);
+}
+
+struct PrioArrays { // per active read, W entries each
+	uint16_t* sav; uint8_t* sorted; uint16_t* rank; uint16_t* sp2; ExRange16* exr; uint8_t* exrfw;
+	uint32_t* nsp; uint32_t* nsmall; uint32_t* nexr; uint64_t* nelt; uint32_t* nelt_added; // [nactive]
+};
+
+__device__ __forceinline__ void prio_work(const PrioArrays& pa, uint32_t ai, uint32_t W, PrioWork& w) {
+	const size_t o = (size_t)ai * W;
+	w.sav = pa.sav + o; w.sorted = pa.sorted + o; w.rank = pa.rank + o; w.sp2 = pa.sp2 + o; w.exr = pa.exr + o; w.exrfw = pa.exrfw + o;
+}
+
+__global__ void k_prio1(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const uint32_t* active, uint32_t nactive,
+                        const SeedHit* hits, uint32_t W, uint32_t maxOffs, const PrioArrays pa,
+                        uint32_t* ext_list, uint32_t* ext_cnt, uint32_t* samp_list, uint32_t* samp_cnt) {
+	const uint32_t ai = blockIdx.x * blockDim.x + threadIdx.x;
+	if(ai >= nactive) return;
+	const DevParams& P = *Pp;
+	const uint32_t read = active[ai];
+	ReadState rs = states[read];
+	uint32_t offset = 0; round_wanted(P, rs, rs.round, offset);
+	const SeedGeom g = seed_geom(P, rs.rdlen, offset, (uint32_t)rs.interval, maxOffs);
+	PrioWork w; prio_work(pa, ai, W, w);
+	const bool sample = prio_stage1(P, pools, rs, hits + (size_t)ai * W, g, w);
+	if(rs.numRanges == 0 || rs.nonzTot == 0) {
+		rs.flags |= BT2GPU_RF_NO_SEED_HITS; rs.phase = RS_FINISHED;
+	} else {
+		pa.nsp[ai] = w.nsp; pa.nsmall[ai] = w.nsmall; pa.nexr[ai] = w.nexr; pa.nelt[ai] = w.nelt; pa.nelt_added[ai] = w.nelt_added;
+		if(sample) list_append(samp_list, samp_cnt, ai);
+		list_append(ext_list, ext_cnt, read);
+	}
+	states[read] = rs;
+}
+
+struct SampleArrays { // per sampling slot
+	uint16_t* ov_rng; uint16_t* ov_pos; uint16_t* ov_val; uint16_t* seen_rng; uint16_t* seen_val; uint16_t* conv_val; // [slots * (2*MI | MI)]
+	uint16_t* r_n; uint16_t* r_cur; uint16_t* r_thresh; uint8_t* r_flags; uint32_t* r_conv_off; uint16_t* r_conv_n; uint16_t* r_nseen;
+	double* mass; uint8_t* elim; // [slots * W]
+};
+#define BT2_SAMPLE_MI (BT2GPU_MAX_ITER + 8)
+
+__global__ void k_prio2(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const uint32_t* active,
+                        const SeedHit* hits, uint32_t W, uint32_t maxOffs, const PrioArrays pa, const SampleArrays sa,
+                        const uint32_t* samp_list, uint32_t base, uint32_t count) {
+	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+	if(j >= count) return;
+	const DevParams& P = *Pp;
+	const uint32_t ai = samp_list[base + j];
+	const uint32_t read = active[ai];
+	ReadState rs = states[read];
+	uint32_t offset = 0; round_wanted(P, rs, rs.round, offset);
+	const SeedGeom g = seed_geom(P, rs.rdlen, offset, (uint32_t)rs.interval, maxOffs);
+	PrioWork w; prio_work(pa, ai, W, w);
+	w.nsp = pa.nsp[ai]; w.nsmall = pa.nsmall[ai]; w.nexr = pa.nexr[ai]; w.nelt = pa.nelt[ai]; w.nelt_added = pa.nelt_added[ai];
+	SampleWork s;
+	const size_t o2 = (size_t)j * 2 * BT2_SAMPLE_MI, o1 = (size_t)j * BT2_SAMPLE_MI, ow = (size_t)j * W;
+	s.ov_rng = sa.ov_rng + o2; s.ov_pos = sa.ov_pos + o2; s.ov_val = sa.ov_val + o2;
+	s.seen_rng = sa.seen_rng + o1; s.seen_val = sa.seen_val + o1; s.conv_val = sa.conv_val + o1;
+	s.r_n = sa.r_n + ow; s.r_cur = sa.r_cur + ow; s.r_thresh = sa.r_thresh + ow; s.r_flags = sa.r_flags + ow;
+	s.r_conv_off = sa.r_conv_off + ow; s.r_conv_n = sa.r_conv_n + ow; s.r_nseen = sa.r_nseen + ow; s.mass = sa.mass + ow; s.elim = sa.elim + ow;
+	prio_stage2(P, pools, rs, hits + (size_t)ai * W, g, w, s);
+	states[read] = rs;
+}
+
+// one extension step per read of the chunk; problem slot = position in the chunk
+__global__ void k_step(const DevParams* __restrict__ Pp, const DevIndex ix, const DevRef rf, const Pools pools, ReadState* states,
+                       const uint32_t* list, uint32_t base, uint32_t count, Problem* probs,
+                       uint32_t* roundend_list, uint32_t* roundend_cnt) {
+	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+	if(j >= count) return;
+	const uint32_t read = list[base + j];
+	ReadState rs = states[read];
+	Problem& pb = probs[j];
+	pb.read = read;
+	if(advance(*Pp, ix, rf, pools, rs, pb) == ADV_ROUND_END) {
+		pb.read = BT2_NIL;
+		rs.phase = RS_ROUND_DONE;
+		list_append(roundend_list, roundend_cnt, read);
+	}
+	states[read] = rs;
+}
+
+struct BtArrays { const uint32_t* hef; uint16_t* masks; BtFrame* stacks; uint32_t* scratch; const uint8_t* seq; const uint8_t* qual; };
+
+__global__ void k_bt(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const Problem* probs, uint32_t count,
+                     const BtArrays ba, uint32_t* next_list, uint32_t* next_cnt, uint32_t* roundend_list, uint32_t* roundend_cnt) {
+	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+	if(j >= count) return;
+	const Problem& pb = probs[j];
+	if(pb.read == BT2_NIL) return;
+	const uint32_t read = pb.read;
+	ReadState rs = states[read];
+	BtCtx cx;
+	cx.P = Pp; cx.prob = &pb;
+	cx.hef = ba.hef + (size_t)j * BT2_HEF_WORDS;
+	cx.masks = ba.masks + (size_t)j * BT2_MASK_WORDS;
+	cx.stack = ba.stacks + (size_t)j * BT2_BT_STACK;
+	cx.scratch = ba.scratch + (size_t)read * BT2_SCRATCH_EDITS;
+	cx.rv.seq = ba.seq + rs.seq_off; cx.rv.qual = ba.qual + rs.seq_off; cx.rv.rdlen = rs.rdlen; cx.rv.fw = pb.fw != 0;
+	if(after_fill(cx, pools, rs) == BT_ROUND_END) {
+		rs.phase = RS_ROUND_DONE;
+		list_append(roundend_list, roundend_cnt, read);
+	} else {
+		list_append(next_list, next_cnt, read);
+	}
+	states[read] = rs;
+}
+
+// reads whose round is over: another seed round, or finished
+__global__ void k_round_end(const DevParams* __restrict__ Pp, ReadState* states, const uint32_t* in, uint32_t nin,
+                            uint32_t* out, uint32_t* cnt) {
+	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+	if(j >= nin) return;
+	ReadState& rs = states[in[j]];
+	if(next_round_wanted(*Pp, rs)) list_append(out, cnt, in[j]);
+	else rs.phase = RS_FINISHED;
+}
+
+__global__ void k_count(const ReadState* states, const Pools pools, uint32_t n, uint32_t* nal, uint32_t* ned, unsigned long long* wstats) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	unsigned long long v[6] = { 0, 0, 0, 0, 0, 0 };
+	if(i < n) {
+		const ReadState& rs = states[i];
+		nal[i] = rs.n_alns; ned[i] = read_edit_count(rs, pools);
+		v[0] = rs.saRows; v[1] = rs.lfResolve; v[2] = rs.btAttempts; v[3] = rs.btSteps; v[4] = rs.n_alns; v[5] = rs.nExDps;
+	}
+	// work counters for the roofline arithmetic (warp-aggregated)
+	#pragma unroll
+	for(int k = 0; k < 6; k++) {
+		unsigned long long x = v[k];
+		for(int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+		if((threadIdx.x & 31) == 0 && x) atomicAdd(&wstats[k], x);
+	}
+}
+
+__global__ void k_gather(const ReadState* states, const Pools pools, const uint32_t* scratch, uint32_t n,
+                         const uint32_t* aln_base, const uint32_t* edit_base,
+                         bt2gpu_read_result* rr, bt2gpu_aln* alns, bt2gpu_edit* edits) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= n) return;
+	bt2gpu_read_result r;
+	gather_read(states[i], pools, scratch + (size_t)i * BT2_SCRATCH_EDITS, aln_base[i], edit_base[i], r, alns, edits);
+	rr[i] = r;
+}
+
+} // namespace bt2

@@ -1,0 +1,151 @@
+"""Shared helpers of the test-suite: case table, index cache, oracle binding.
+The oracle (oracle/liboracle.so) is TEST INFRASTRUCTURE: it is only ever loaded from here,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs."""
+import ctypes as C
+import importlib
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+WORK = os.path.join(ROOT, "tests", "_work")
+REFBIN = os.path.join(ROOT, "oracle", "_ref")
+sys.path.insert(0, ROOT)
+pkg = importlib.import_module("omp-bowtie2-prime_b200")
+
+# name -> (reference fasta maker, reads maker, options, golden file)
+CASES = {
+    "lambda_default": ("lambda", "lambda_reads_1k", "", "lambda_default.sam"),
+    "lambda_k3_vs": ("lambda", "lambda_reads_1k", "-k 3 --very-sensitive", "lambda_k3_vs.sam"),
+    "syn150_sensitive_dpad12": ("syn", "syn150", "--sensitive --dpad 12", "syn150_sensitive_dpad12.sam"),
+    "syn100_default": ("syn", "syn100", "", "syn100_default.sam"),
+    "syn100_k5": ("syn", "syn100", "-k 5", "syn100_k5.sam"),
+}
+
+
+def _run(cmd):
+    subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+
+
+def have_builder():
+    return os.access(os.path.join(REFBIN, "bowtie2-build-l"), os.X_OK)
+
+
+def gen(args):
+    _run([sys.executable, os.path.join(ROOT, "tools", "gen_data.py")] + [str(a) for a in args])
+
+
+def index_base(name):
+    """Build (once) the .bt2l index of a named reference with the reference's own builder."""
+    os.makedirs(WORK, exist_ok=True)
+    base = os.path.join(WORK, name)
+    if os.path.exists(base + ".4.bt2l") and os.path.exists(base + ".1.bt2l"):
+        return base
+    if name == "lambda":
+        fa = os.path.join(GOLD, "lambda_virus.fa")
+    elif name == "syn":
+        fa = base + ".fa"
+        gen(["ref", fa, 300000, "--seed", 4242, "--repeats", 0.2, "--nseq", 3])
+    elif name.startswith("iid"):  # iid<len>
+        fa = base + ".fa"
+        gen(["ref", fa, int(name[3:]), "--seed", 12345])
+    else:
+        raise KeyError(name)
+    _run([os.path.join(REFBIN, "bowtie2-build-l"), "--threads", "4", fa, base])
+    return base
+
+
+def reads_path(name):
+    os.makedirs(WORK, exist_ok=True)
+    if name == "lambda_reads_1k":
+        return os.path.join(GOLD, "lambda_reads_1k.fq")
+    p = os.path.join(WORK, name + ".fq")
+    if os.path.exists(p):
+        return p
+    index_base("syn")
+    fa = os.path.join(WORK, "syn.fa")
+    if name == "syn150":
+        gen(["reads", fa, p, 1500, 150, "--seed", 7, "--randqual", "--nfrac", 0.002])
+    elif name == "syn100":
+        gen(["reads", fa, p, 1500, 100, "--seed", 8, "--subst", 0.03])
+    else:
+        raise KeyError(name)
+    return p
+
+
+def sorted_records(sam_text):
+    recs = [l for l in sam_text.split("\n") if l and not l.startswith("@")]
+    return sorted(recs, key=lambda s: s.encode("latin-1"))
+
+
+def golden_records(fname):
+    with open(os.path.join(GOLD, fname), encoding="latin-1") as f:
+        return [l.rstrip("\n") for l in f if l.strip()]
+
+
+class Oracle:
+    """ctypes view of oracle/liboracle.so (oracle_capi.cpp)."""
+
+    def __init__(self, job):
+        p = os.path.join(ROOT, "oracle", "liboracle.so")
+        self.lib = C.CDLL(p)
+        self.lib.oracle_create.restype = C.c_void_p
+        self.lib.oracle_create.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self.lib.oracle_align_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        self.lib.oracle_destroy.argtypes = [C.c_void_p]
+        self.lib.oracle_counters.argtypes = [C.c_void_p, C.POINTER(C.c_uint64 * 10)]
+        self.ptr = self.lib.oracle_create(C.cast(job.index, C.c_void_p), C.cast(job.ref, C.c_void_p), C.cast(job.params, C.c_void_p))
+        self.job = job
+
+    def align(self, batch, nthreads=0):
+        r = pkg.bt2gpu_results()
+        self.lib.oracle_align_batch(self.ptr, C.cast(batch.reads, C.c_void_p), C.cast(C.byref(r), C.c_void_p), nthreads)
+        return pkg.Results(r)
+
+    def counters(self):
+        a = (C.c_uint64 * 10)()
+        self.lib.oracle_counters(self.ptr, C.byref(a))
+        names = ["seeds", "lfSearch", "lfExtend", "saRows", "lfResolve", "dps", "cells", "btAttempts", "btSteps", "alns"]
+        return dict(zip(names, list(a)))
+
+    def close(self):
+        if self.ptr:
+            self.lib.oracle_destroy(self.ptr)
+            self.ptr = None
+
+
+def compare_results(a, b, check_counters=True):
+    """Field-for-field comparison of two Results (oracle vs CUDA). Returns a list of differences."""
+    import numpy as np
+    diffs = []
+    if len(a.reads) != len(b.reads):
+        return ["n reads %d vs %d" % (len(a.reads), len(b.reads))]
+    fields = ["n_alns", "rng_last", "rng_lastOff", "minsc", "status", "flags", "rounds", "done_policy"]
+    if check_counters:
+        fields += ["nExIters", "nExDps", "nExDpSuccs", "nExDpFails", "nDpFail", "nDpFailStreak", "nDpLastSucc", "nRedundants",
+                   "bestLtMinsc", "nonzTot", "numElts", "numRanges", "nSeedsTried", "n_scratch"]
+    for f in fields:
+        bad = np.nonzero(a.reads[f] != b.reads[f])[0]
+        if len(bad):
+            diffs.append("reads.%s differs for %d reads, first %d: %s vs %s" % (f, len(bad), bad[0], a.reads[f][bad[0]], b.reads[f][bad[0]]))
+    if diffs:
+        return diffs
+    for i in range(len(a.reads)):
+        ra, rb = a.reads[i], b.reads[i]
+        for k in range(int(ra["n_alns"])):
+            x, y = a.alns[ra["aln_off"] + k], b.alns[rb["aln_off"] + k]
+            for f in ("refoff", "tidx", "score", "minsc", "ns", "gaps", "edits", "basesAligned", "refns", "n_edits", "fw"):
+                if x[f] != y[f]:
+                    diffs.append("read %d aln %d %s: %s vs %s" % (i, k, f, x[f], y[f]))
+            ea = a.edits[x["edit_off"]:x["edit_off"] + x["n_edits"]]
+            eb = b.edits[y["edit_off"]:y["edit_off"] + y["n_edits"]]
+            if len(ea) != len(eb) or (ea != eb).any():
+                diffs.append("read %d aln %d edits differ" % (i, k))
+        sa = a.edits[ra["scratch_off"]:ra["scratch_off"] + ra["n_scratch"]]
+        sb = b.edits[rb["scratch_off"]:rb["scratch_off"] + rb["n_scratch"]]
+        if len(sa) != len(sb) or (sa != sb).any():
+            diffs.append("read %d scratch differs" % i)
+        if len(diffs) > 20:
+            break
+    return diffs

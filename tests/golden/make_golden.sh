@@ -1,0 +1,29 @@
+#!/bin/bash
+# Regenerates the golden vectors of this directory by running the UNMODIFIED reference
+# (oracle/_ref/bowtie2-align-l, built by oracle/build_ref.sh from /root/reference) here.
+# Inputs: the reference's shipped example (example/reference/lambda_virus.fa, first 1000
+# records of example/reads/reads_1.fq -- BASELINE config 1) and seeded synthetic sets
+# from tools/gen_data.py.  Output order depends on the thread schedule, so records are
+# stored sorted.  Needs /root/reference; not run on the GPU box.
+set -e
+HERE="$(cd "$(dirname "$0")" && pwd)"; ROOT="$HERE/../.."; REF=${REF:-/root/reference}
+B="$ROOT/oracle/_ref"; T=$(mktemp -d)
+cp "$REF/example/reference/lambda_virus.fa" "$HERE/lambda_virus.fa"
+head -4000 "$REF/example/reads/reads_1.fq" > "$HERE/lambda_reads_1k.fq"
+run() { # name index reads opts
+  OMP_NUM_THREADS=4 "$B/bowtie2-align-l" -x "$2" -U "$3" -S "$T/o.sam" -p 8 $4 2>/dev/null
+  grep -v '^@' "$T/o.sam" | LC_ALL=C sort > "$HERE/$1.sam"
+}
+"$B/bowtie2-build-l" "$HERE/lambda_virus.fa" "$T/lambda" >/dev/null 2>&1
+run lambda_default "$T/lambda" "$HERE/lambda_reads_1k.fq" ""
+run lambda_k3_vs   "$T/lambda" "$HERE/lambda_reads_1k.fq" "-k 3 --very-sensitive"
+# synthetic: 300 kbp i.i.d. reference, 3 sequences, 20% repeat families
+python "$ROOT/tools/gen_data.py" ref "$T/syn.fa" 300000 --seed 4242 --repeats 0.2 --nseq 3
+"$B/bowtie2-build-l" "$T/syn.fa" "$T/syn" >/dev/null 2>&1
+python "$ROOT/tools/gen_data.py" reads "$T/syn.fa" "$T/syn150.fq" 1500 150 --seed 7 --randqual --nfrac 0.002
+python "$ROOT/tools/gen_data.py" reads "$T/syn.fa" "$T/syn100.fq" 1500 100 --seed 8 --subst 0.03
+run syn150_sensitive_dpad12 "$T/syn" "$T/syn150.fq" "--sensitive --dpad 12"
+run syn100_default          "$T/syn" "$T/syn100.fq" ""
+run syn100_k5               "$T/syn" "$T/syn100.fq" "-k 5"
+rm -rf "$T"
+ls -la "$HERE"

@@ -1,0 +1,62 @@
+"""CPU: the C-ABI libraries load and export every symbol the headers declare."""
+import ctypes
+import os
+import re
+import common
+from common import pkg
+
+
+def _declared(header):
+    txt = open(os.path.join(common.ROOT, "include", header)).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(bt2(?:gpu|host)_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_bt2gpu_exports():
+    p = pkg.lib_paths()["gpu"]
+    assert os.path.exists(p), "libbt2gpu.so not built (run make / __graft_entry__.build())"
+    lib = ctypes.CDLL(p)
+    names = _declared("bt2gpu.h")
+    assert len(names) >= 10
+    for n in names:
+        assert hasattr(lib, n), n
+    lib.bt2gpu_abi_version.restype = ctypes.c_int
+    assert lib.bt2gpu_abi_version() == 1
+
+
+def test_bt2host_exports():
+    lib = ctypes.CDLL(pkg.lib_paths()["host"])
+    for n in _declared("bt2host.h"):
+        assert hasattr(lib, n), n
+
+
+def test_struct_sizes_match_header():
+    # the ctypes mirrors must have the C layout (checked against sizes compiled from the header)
+    import subprocess, tempfile, textwrap
+    src = textwrap.dedent('''
+        #include <stdio.h>
+        #include "bt2gpu.h"
+        int main(){ printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(bt2gpu_index), sizeof(bt2gpu_ref), sizeof(bt2gpu_params),
+          sizeof(bt2gpu_reads), sizeof(bt2gpu_edit), sizeof(bt2gpu_aln), sizeof(bt2gpu_read_result), sizeof(bt2gpu_counters)); return 0; }''')
+    with tempfile.TemporaryDirectory() as d:
+        open(os.path.join(d, "s.c"), "w").write(src)
+        subprocess.run(["gcc", "-I", os.path.join(common.ROOT, "include"), "-o", os.path.join(d, "s"), os.path.join(d, "s.c")], check=True)
+        out = subprocess.run([os.path.join(d, "s")], capture_output=True, text=True, check=True).stdout.split()
+    got = [ctypes.sizeof(x) for x in (pkg.bt2gpu_index, pkg.bt2gpu_ref, pkg.bt2gpu_params, pkg.bt2gpu_reads, pkg.bt2gpu_edit,
+                                      pkg.bt2gpu_aln, pkg.bt2gpu_read_result, pkg.bt2gpu_counters)]
+    assert got == [int(x) for x in out]
+
+
+def test_no_gpu_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        return
+    if not common.have_builder():
+        return
+    job = pkg.Job(common.index_base("lambda"), "")
+    try:
+        pkg.GpuAligner(job)
+    except RuntimeError as e:
+        assert "no CUDA device" in str(e)
+    else:
+        raise AssertionError("GpuAligner must not work without a GPU")

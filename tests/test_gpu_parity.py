@@ -1,0 +1,94 @@
+"""GPU: the CUDA path, called through the C-ABI (libbt2gpu.so), equals the oracle
+struct-for-struct (alignments, edits, RNG state, counters, F14 scratch) and reproduces
+the reference's golden SAM byte for byte."""
+import numpy as np
+import pytest
+import common
+from common import pkg
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu(job):
+    return pkg.GpuAligner(job, 0)
+
+
+@pytest.mark.parametrize("name", sorted(common.CASES))
+def test_gpu_matches_oracle_and_golden(name):
+    ref, reads, opts, gold = common.CASES[name]
+    job = pkg.Job(common.index_base(ref), opts)
+    batch = job.fastq(common.reads_path(reads))
+    orc = common.Oracle(job)
+    want = orc.align(batch)
+    gpu = _gpu(job)
+    got = gpu.align(batch)
+    diffs = common.compare_results(want, got)
+    assert not diffs, "\n".join(diffs[:10])
+    sam = common.sorted_records(job.sam(batch, got, mode=1))
+    assert sam == common.golden_records(gold)
+    c = gpu.counters()
+    oc = orc.counters()
+    assert c["dp_problems"] == oc["dps"] and c["dp_cells"] == oc["cells"]
+    assert c["lf_steps_search"] == oc["lfSearch"] and c["lf_steps_extend"] == oc["lfExtend"]
+    assert c["bt_steps"] == oc["btSteps"] and c["sa_rows_resolved"] == oc["saRows"]
+    assert c["launches"] > 0
+    gpu.close(); orc.close()
+
+
+def test_gpu_edge_cases():
+    """empty read, read shorter than the seed, all-N read, read > 160 bp (dropped like the reference), Ns inside seeds"""
+    job = pkg.Job(common.index_base("syn"), "")
+    fa = open(common.index_base("syn") + ".fa").read().split("\n")
+    s = "".join(l for l in fa[1:200] if not l.startswith(">"))
+    seqs = ["", s[100:110], "N" * 50, s[1000:1170], s[2000:2100], s[3000:3050] + "N" + s[3051:3100],
+            s[4000:4022], s[5000:5023], "ACGT" * 30, s[6000:6160]]
+    quals = ["I" * len(x) for x in seqs]
+    batch = job.arrays(seqs, quals)
+    orc = common.Oracle(job)
+    want = orc.align(batch)
+    gpu = _gpu(job)
+    got = gpu.align(batch)
+    diffs = common.compare_results(want, got)
+    assert not diffs, "\n".join(diffs[:10])
+    assert job.sam(batch, got, 1) == job.sam(batch, want, 1)
+    gpu.close(); orc.close()
+
+
+def test_gpu_batch_split_and_determinism(monkeypatch):
+    """results do not depend on the internal batch size or the number of DP slots (SURVEY 8b determinism contract)"""
+    job = pkg.Job(common.index_base("syn"), "-k 2")
+    batch = job.fastq(common.reads_path("syn100"), 0, 700)
+    g1 = _gpu(job)
+    a = g1.align(batch)
+    sam_a = job.sam(batch, a, 1)
+    g1.close()
+    monkeypatch.setenv("BT2GPU_BATCH", "256")
+    monkeypatch.setenv("BT2GPU_SLOTS", "100")
+    g2 = _gpu(job)
+    b = g2.align(batch)
+    assert job.sam(batch, b, 1) == sam_a
+    # split API == align_batch
+    monkeypatch.setenv("BT2GPU_BATCH", "4096")
+    g3 = _gpu(job)
+    g3.upload(batch); g3.run_resident(); c = g3.fetch()
+    assert job.sam(batch, c, 1) == sam_a
+    g2.close(); g3.close()
+
+
+def test_gpu_larger_iid_vs_oracle():
+    """5 Mbp i.i.d. reference, 150 bp reads, --sensitive --dpad 12 (BASELINE config 2 at reduced read count)"""
+    base = common.index_base("iid5000000")
+    import os
+    fq = os.path.join(common.WORK, "iid150.fq")
+    if not os.path.exists(fq):
+        common.gen(["reads", base + ".fa", fq, 20000, 150, "--seed", 2])
+    job = pkg.Job(base, "--sensitive --dpad 12")
+    batch = job.fastq(fq)
+    orc = common.Oracle(job)
+    want = orc.align(batch)
+    gpu = _gpu(job)
+    got = gpu.align(batch)
+    diffs = common.compare_results(want, got)
+    assert not diffs, "\n".join(diffs[:10])
+    assert job.sam(batch, got, 1) == job.sam(batch, want, 1)
+    gpu.close(); orc.close()

@@ -1,0 +1,34 @@
+"""CPU: the oracle restatement + host sink reproduce, byte for byte, the SAM records the
+unmodified reference printed for the committed fixtures (tests/golden/make_golden.sh),
+including the reference's aliased-edit CIGAR/MD artefact and YF quirk (F11)."""
+import pytest
+import common
+from common import pkg
+
+
+@pytest.mark.parametrize("name", sorted(common.CASES))
+def test_oracle_matches_reference_golden(name):
+    if not common.have_builder():
+        pytest.skip("oracle/_ref/bowtie2-build-l not built")
+    ref, reads, opts, gold = common.CASES[name]
+    job = pkg.Job(common.index_base(ref), opts)
+    batch = job.fastq(common.reads_path(reads))
+    orc = common.Oracle(job)
+    res = orc.align(batch)
+    got = common.sorted_records(job.sam(batch, res, mode=1))
+    want = common.golden_records(gold)
+    assert len(got) == len(want)
+    bad = [(g, w) for g, w in zip(got, want) if g != w]
+    assert not bad, "first differing record:\n%s\n%s" % bad[0]
+    orc.close(); batch.close(); job.close()
+
+
+def test_oracle_thread_count_independent():
+    if not common.have_builder():
+        pytest.skip("no builder")
+    job = pkg.Job(common.index_base("syn"), "")
+    batch = job.fastq(common.reads_path("syn100"), 0, 300)
+    orc = common.Oracle(job)
+    a = job.sam(batch, orc.align(batch, 1), 1)
+    b = job.sam(batch, orc.align(batch, 4), 1)
+    assert a == b
