@@ -463,6 +463,47 @@ int bt2gpu_align_batch(bt2gpu_ctx* ctx, const bt2gpu_reads* in, bt2gpu_results* 
 	})
 }
 
+int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, const uint8_t* seq, const uint8_t* qual,
+                     const uint16_t* rows, const uint16_t* cols, const uint32_t* rf_off, const uint8_t* rf, const int32_t* minsc,
+                     const uint64_t* hef_off, uint8_t* H, uint8_t* E, uint8_t* F, uint16_t* cand, uint32_t* ncand, int32_t* lrmax) {
+	API_GUARD({
+		if(nprob > ctx->nslots) throw std::string("bt2gpu_test_fill: more problems than DP slots");
+		std::vector<ReadState> hs(nprob); std::vector<Problem> hp(nprob);
+		uint64_t nb = 0;
+		for(uint32_t i = 0; i < nprob; i++) {
+			if(rows[i] < 1 || rows[i] > BT2GPU_MAX_ROWS || cols[i] < 1 || cols[i] >= BT2GPU_MAX_COLS) throw std::string("bt2gpu_test_fill: bad problem size");
+			memset(&hs[i], 0, sizeof(ReadState)); hs[i].seq_off = seq_off[i]; hs[i].rdlen = rows[i];
+			memset(&hp[i], 0, sizeof(Problem));
+			hp[i].read = i; hp[i].rows = rows[i]; hp[i].cols = cols[i]; hp[i].fw = 1; hp[i].R = (uint8_t)((rows[i] + 63) / 64); hp[i].minsc = minsc[i];
+			memcpy(hp[i].rf, rf + rf_off[i], (size_t)cols[i] + 1);
+			nb = std::max<uint64_t>(nb, (uint64_t)seq_off[i] + rows[i]);
+		}
+		ctx->seq.ensure(nb + 16); ctx->qual.ensure(nb + 16); ctx->states.ensure((size_t)nprob * sizeof(ReadState));
+		cudaStream_t st = ctx->stream;
+		CK(cudaMemcpyAsync(ctx->seq.p, seq, nb, cudaMemcpyHostToDevice, st)); CK(cudaMemcpyAsync(ctx->qual.p, qual, nb, cudaMemcpyHostToDevice, st));
+		CK(cudaMemcpyAsync(ctx->states.p, hs.data(), (size_t)nprob * sizeof(ReadState), cudaMemcpyHostToDevice, st));
+		CK(cudaMemcpyAsync(ctx->probs.p, hp.data(), (size_t)nprob * sizeof(Problem), cudaMemcpyHostToDevice, st));
+		CK(cudaMemsetAsync(ctx->stats.p, 0, 32 * 8, st));
+		FillArgs fa; fa.probs = ctx->probs.as<Problem>(); fa.nprob = nprob; fa.states = ctx->states.as<ReadState>(); fa.seq = ctx->seq.as<uint8_t>();
+		fa.qual = ctx->qual.as<uint8_t>(); fa.hef = ctx->hef.as<uint32_t>(); fa.stats = ctx->stats.as<unsigned long long>() + 8;
+		k_fill<<<nblk(nprob, BT2_FILL_WARPS), BT2_FILL_WARPS * 32, 0, st>>>(ctx->dP, fa);
+		CK(cudaMemcpyAsync(hp.data(), ctx->probs.p, (size_t)nprob * sizeof(Problem), cudaMemcpyDeviceToHost, st));
+		std::vector<uint32_t> w(BT2_HEF_WORDS);
+		for(uint32_t i = 0; i < nprob; i++) {
+			CK(cudaMemcpyAsync(w.data(), ctx->hef.as<uint32_t>() + (size_t)i * BT2_HEF_WORDS, (size_t)BT2_HEF_WORDS * 4, cudaMemcpyDeviceToHost, st));
+			CK(cudaStreamSynchronize(st));
+			for(uint32_t r = 0; r < rows[i]; r++) for(uint32_t cc = 0; cc < cols[i]; cc++) {
+				const uint32_t x = w[hef_index(r, cc, hp[i].R)];
+				const uint64_t o = hef_off[i] + (uint64_t)r * cols[i] + cc;
+				H[o] = (uint8_t)x; E[o] = (uint8_t)(x >> 8); F[o] = (uint8_t)(x >> 16);
+			}
+			ncand[i] = hp[i].ncand; lrmax[i] = hp[i].lrmax;
+			for(uint32_t k = 0; k < hp[i].ncand && k < 256; k++) cand[256 * (size_t)i + k] = hp[i].cand[k];
+		}
+		CK(cudaGetLastError());
+	})
+}
+
 int bt2gpu_get_counters(bt2gpu_ctx* ctx, bt2gpu_counters* c) { if(!ctx || !c) return -1; *c = ctx->ctr; return 0; }
 int bt2gpu_reset_counters(bt2gpu_ctx* ctx) { if(!ctx) return -1; memset(&ctx->ctr, 0, sizeof(ctx->ctr)); return 0; }
 const char* bt2gpu_last_error(const bt2gpu_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }

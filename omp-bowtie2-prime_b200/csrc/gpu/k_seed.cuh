@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(256) k_seed(const DevIndex ix, const DevParams
 	uint64_t task = 0, task_end = 0;
 	// per-seed state (uniform within the group)
 	bool busy = false, extending = false;
-	uint64_t top = 0, bot = 0;
+	uint64_t top = 0, bot = 0, seed_top = 0, seed_len = 0; // (seed_top, seed_len): the range reported, i.e. before the left extension
 	int pos = 0;            // next strand-buffer position to consume (descending)
 	int seed_lo = 0;        // strand-buffer offset of the seed's first base
 	uint32_t nlex = 0;
@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(256) k_seed(const DevIndex ix, const DevParams
 			}
 			busy = true; extending = false; nlex = 0;
 			if(pos < seed_lo) { // whole seed consumed by the ftab jump
-				extending = true;
+				extending = true; seed_top = top; seed_len = bot - top;
 				if(!P.doExtend || pos < 0) { if(l8 == 0) { out->top = top; out->len = bot - top; out->key = key; out->nlex = 0; out->valid = 1; } busy = false; }
 			}
 			continue;
@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(256) k_seed(const DevIndex ix, const DevParams
 				if(!failed && b == t) failed = true;
 				if(!failed) {
 					top = t; bot = b; pos--;
-					if(pos < seed_lo) { extending = true; if(!P.doExtend || pos < 0) finished = true; }
+					if(pos < seed_lo) { extending = true; seed_top = top; seed_len = bot - top; if(!P.doExtend || pos < 0) finished = true; }
 				}
 			} else {
 				st_extend++;
@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(256) k_seed(const DevIndex ix, const DevParams
 			if(l8 == 0) { out->top = 0; out->len = 0; out->key = key; out->nlex = 0; out->valid = 0; }
 			busy = false;
 		} else if(finished) {
-			if(l8 == 0) { out->top = top; out->len = bot - top; out->key = key; out->nlex = nlex; out->valid = 1; }
+			if(l8 == 0) { out->top = seed_top; out->len = seed_len; out->key = key; out->nlex = nlex; out->valid = 1; }
 			busy = false;
 		}
 	}

@@ -93,3 +93,21 @@ void oracle_counters(oracle_ctx* c, uint64_t out[10]) {
 }
 
 } // extern "C"
+
+// Stage oracle for the DP fill: one SwAligner problem (strand buffer rd/qu already oriented),
+// returns the raw u8 H/E/F matrices [rows*cols] and the sorted candidate list (rawH<<8|col).
+extern "C" int oracle_fill(const bt2gpu_params* P, const uint8_t* rd, const uint8_t* qu, int rows,
+                           const uint8_t* rfmasks, int cols, int minsc, uint8_t* H, uint8_t* E, uint8_t* F,
+                           uint16_t* cand, int* ncand, int* lrmax) {
+	orc::SwProblem sw; sw.P = P; sw.sc.P = P; sw.i16 = false; sw.fw = true; sw.rd = rd; sw.qu = qu; sw.rdlen = rows; sw.nceil = rows;
+	sw.rf.assign(rfmasks, rfmasks + cols + 1); sw.rflen = cols; sw.minsc = minsc;
+	int64_t best = 0; orc::WorkCounters wc;
+	sw.align(best, wc);
+	for(size_t i = 0; i < (size_t)rows * cols; i++) { H[i] = (uint8_t)(sw.H[i] + 255); E[i] = (uint8_t)(sw.E[i] + 255); F[i] = (uint8_t)(sw.F[i] + 255); }
+	*ncand = (int)sw.cands.size();
+	int mx = 0;
+	for(int c = 0; c < cols; c++) mx = std::max(mx, (int)H[(size_t)(rows - 1) * cols + c]);
+	*lrmax = mx;
+	for(size_t i = 0; i < sw.cands.size(); i++) cand[i] = (uint16_t)((sw.cands[i].score << 8) | sw.cands[i].col);
+	return 0;
+}
