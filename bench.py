@@ -1,0 +1,320 @@
+#!/usr/bin/env python
+"""Headline benchmark of the seed-and-extend hot path (BASELINE.json: aligned reads/sec,
+150 bp, --sensitive end-to-end; DP GCUPS beside it).
+
+  python bench.py --gpus N --steps K --warmup W          CUDA path (libbt2gpu.so through the C-ABI)
+  python bench.py --impl reference ...                   the reference's own OpenMP CPU path (oracle/_ref)
+
+Workload = BASELINE configs[1]: synthetic 5 Mbp i.i.d. reference, 1 M simulated 150 bp reads
+(1 % substitutions, one 1-bp indel in 10 % of reads), unpaired, `--sensitive --dpad 12`
+(the reference's 200-column DP buffer cannot hold a 150 bp read at the default --dpad 15,
+SURVEY F13).  One step = one pass of the whole hot path over one batch of reads; every
+rank aligns its own batch against its own replica of the index (weak scaling, no collective
+on the data path).  `value` times bt2gpu_run_resident (inputs resident in HBM) with CUDA
+events recorded on the library's stream; `e2e` times bt2gpu_align_batch from host buffers
+(H2D + kernels + D2H of the results).
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+WORK = os.path.join(ROOT, "bench_work")
+REFBIN = os.path.join(ROOT, "oracle", "_ref")
+OPTS = "--sensitive --dpad 12"
+REF_LEN = 5_000_000
+READ_LEN = 150
+METRIC = "aligned_reads_per_sec_150bp_sensitive_e2e"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def make_reference():
+    """5 Mbp i.i.d. reference (seed 12345) + its .bt2l index, built once with the reference's own builder."""
+    os.makedirs(WORK, exist_ok=True)
+    base = os.path.join(WORK, "iid5m")
+    fa = base + ".fa"
+    rng = np.random.default_rng(12345)
+    codes = rng.integers(0, 4, size=REF_LEN, dtype=np.uint8)
+    if not os.path.exists(base + ".4.bt2l"):
+        seq = np.frombuffer(b"ACGT", dtype=np.uint8)[codes]
+        with open(fa, "wb") as f:
+            f.write(b">seq0\n")
+            for i in range(0, REF_LEN, 60):
+                f.write(seq[i:i + 60].tobytes() + b"\n")
+        builder = os.path.join(REFBIN, "bowtie2-build-l")
+        if not os.access(builder, os.X_OK):
+            raise RuntimeError("oracle/_ref/bowtie2-build-l missing: run oracle/build_ref.sh where /root/reference exists")
+        subprocess.run([builder, "--threads", str(min(16, os.cpu_count() or 1)), fa, base], check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return base, codes
+
+
+def simulate_reads(codes, n, seed):
+    """n reads of READ_LEN bp: uniform start, 1 % substitutions, a 1-bp indel in 10 % of the reads, random strand, Q40."""
+    if n > 100000:  # bound the temporaries
+        parts = [simulate_reads(codes, min(100000, n - i), seed * 7919 + i) for i in range(0, n, 100000)]
+        return np.concatenate(parts, axis=0)
+    rng = np.random.default_rng(seed)
+    L = READ_LEN
+    st = rng.integers(0, REF_LEN - L - 2, size=n)
+    win = codes[st[:, None] + np.arange(L + 2)[None, :]]
+    sub = rng.random((n, L + 2)) < 0.01
+    win = np.where(sub, (win + rng.integers(1, 4, size=(n, L + 2), dtype=np.uint8)) % 4, win).astype(np.uint8)
+    indel = np.nonzero(rng.random(n) < 0.10)[0]
+    pos = rng.integers(10, L - 10, size=len(indel))
+    ins = rng.random(len(indel)) < 0.5
+    newb = rng.integers(0, 4, size=len(indel), dtype=np.uint8)
+    for k, r in enumerate(indel):
+        p = pos[k]
+        if ins[k]:
+            win[r, p + 1:] = win[r, p:-1].copy(); win[r, p] = newb[k]
+        else:
+            win[r, p:-1] = win[r, p + 1:].copy()
+    rd = win[:, :L]
+    rc = rng.random(n) < 0.5
+    rd = np.where(rc[:, None], 3 - rd[:, ::-1], rd).astype(np.uint8)
+    return np.frombuffer(b"ACGT", dtype=np.uint8)[rd]  # ASCII [n, L]
+
+
+def write_fastq(path, ascii_reads):
+    n, L = ascii_reads.shape
+    q = b"I" * L
+    with open(path, "wb") as f:
+        for i in range(n):
+            f.write(b"@r%d\n" % i + ascii_reads[i].tobytes() + b"\n+\n" + q + b"\n")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+
+    def __init__(self, gpu):
+        super().__init__(daemon=True)
+        self.gpu, self.rows, self.stop_ = gpu, [], threading.Event()
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self.stop_.is_set():
+            try:
+                o = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=5).stdout.strip()
+                if o:
+                    self.rows.append([x.strip() for x in o.split(",")])
+            except Exception:
+                pass
+            self.stop_.wait(0.2)
+
+    def summary(self):
+        self.stop_.set()
+        self.join(timeout=3)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        reasons = []
+        for i, nm in enumerate(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]):
+            if any(len(r) > 3 + i and r[3 + i].lower().startswith("active") for r in self.rows):
+                reasons.append(nm)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]) if self.rows[0][1].replace(".", "").isdigit() else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+def run_reference_binary(base, fq, nreads, threads, pmult):
+    """Wall time of the unmodified reference aligner on a FASTQ sample (index load included; it is ~10 ms for 5 Mbp)."""
+    env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="close", OMP_PLACES="cores")
+    t0 = time.time()
+    r = subprocess.run([os.path.join(REFBIN, "bowtie2-align-l"), "-x", base, "-U", fq, "-S", "/dev/null", "-p", str(pmult)] + OPTS.split(),
+                       env=env, capture_output=True, text=True)
+    dt = time.time() - t0
+    if r.returncode != 0:
+        raise RuntimeError("reference aligner failed: " + r.stderr[-300:])
+    ext = None
+    for ln in r.stderr.split("\n"):
+        if "extendSeeds" in ln:
+            try:
+                ext = float(ln.split()[-2])
+            except Exception:
+                pass
+    return dt, ext
+
+
+def cpu_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def reference_arm(args, rank, world):
+    """--impl reference: the reference's own OpenMP CPU implementation on the host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    base, codes = make_reference()
+    cores = cpu_cores()
+    sample = int(os.environ.get("BT2_BENCH_REF_READS", "100000"))
+    reads = simulate_reads(codes, sample, seed=2)
+    fq = os.path.join(WORK, "ref_sample.fq")
+    write_fastq(fq, reads)
+    pmult = int(os.environ.get("BT2_BENCH_REF_P", "100"))
+    for _ in range(args.warmup):
+        run_reference_binary(base, fq, sample, cores, pmult)
+    t = []
+    for _ in range(args.steps):
+        dt, _ext = run_reference_binary(base, fq, sample, cores, pmult)
+        t.append(dt)
+    tot = sum(t)
+    val = sample * args.steps / tot
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "reads/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1000.0 * tot / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic", "config": {"workload": "configs[1]: 5 Mbp i.i.d. reference, 150 bp simulated reads, unpaired, %s" % OPTS,
+                                             "reads_per_step": sample, "note": "bounded sample of the 1M-read workload; wall time of bowtie2-align-l -S /dev/null incl. index load"},
+            "cpu_baseline": {"value": val, "unit": "reads/s", "cores": cores, "kind": "reference",
+                             "sample": "%d reads/step x %d steps, OMP_NUM_THREADS=%d -p %d" % (sample, args.steps, cores, pmult)},
+            "e2e": {"value": val, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="bt2gpu")
+    ap.add_argument("--reads", type=int, default=int(os.environ.get("BT2_BENCH_READS", "1000000")))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the bt2gpu path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = importlib.import_module("omp-bowtie2-prime_b200")
+
+    if rank == 0:
+        base, codes = make_reference()
+    if world > 1:
+        dist.barrier()
+    if rank != 0:
+        base, codes = make_reference()
+    job = pkg.Job(base, OPTS)
+    n = args.reads
+    t0 = time.time()
+    ascii_reads = simulate_reads(codes, n, seed=2 + 1000 * rank)
+    off = (np.arange(n + 1, dtype=np.uint64) * READ_LEN).astype(np.uint32)
+    seqb = ascii_reads.tobytes(); qualb = b"I" * (n * READ_LEN)
+    err = C.create_string_buffer(512)
+    bp = job._h.bt2host_batch_from_arrays(job.ptr, n, off.ctypes.data, seqb, qualb, None, err, 512)
+    if not bp:
+        raise RuntimeError(err.value.decode())
+    batch = pkg.Batch(job, bp)
+    log("[bench] rank %d: %d reads simulated and packed in %.1fs" % (rank, n, time.time() - t0))
+    gpu = pkg.GpuAligner(job, local)
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- resident timing: inputs already in HBM
+    gpu.upload(batch)
+    for _ in range(args.warmup):
+        gpu.run_resident()
+    gpu.counters(reset=True)
+    sampler = ClockSampler(local); sampler.start()
+    sync_all()
+    w0 = time.time()
+    for _ in range(args.steps):
+        gpu.run_resident()
+    sync_all()
+    wall = time.time() - w0
+    ctr = gpu.counters(reset=True)
+    clocks = sampler.summary()
+    dev_s = ctr["ms_run"] / 1000.0  # CUDA events on the library's stream around every run_resident
+    res = gpu.fetch()
+    aligned = int((res.reads["n_alns"] > 0).sum())
+    # ---- end to end through the C-ABI from host buffers
+    for _ in range(min(args.warmup, 1)):
+        gpu.align(batch)
+    gpu.counters(reset=True)
+    sync_all()
+    e0 = time.time()
+    for _ in range(args.steps):
+        r2 = gpu.align(batch)
+    sync_all()
+    e2e_s = time.time() - e0
+    d2h = n * C.sizeof(pkg.bt2gpu_read_result) + int(r2.raw.n_alns) * C.sizeof(pkg.bt2gpu_aln) + int(r2.raw.n_edits) * C.sizeof(pkg.bt2gpu_edit)
+    h2d = 2 * n * READ_LEN + 4 * (n + 1) + 16 * n
+
+    t_dev = torch.tensor([dev_s, e2e_s, wall], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t_dev, op=dist.ReduceOp.MAX)
+    dev_s, e2e_s, wall = [float(x) for x in t_dev.tolist()]
+    total_reads = n * world * args.steps
+    value = total_reads / dev_s
+    peak, peak_src = peaks()
+    # dominant kernel by device time, algorithmic bytes per launch (DESIGN.md "Kernels")
+    phases = {"k_seed": (ctr["ms_seed"], ctr["n_seed"], 128.0 * ctr["lf_sides_touched"] + 16.0 * ctr["seeds_searched"]),
+              "k_step": (ctr["ms_resolve"], ctr["n_step"], 128.0 * ctr["lf_steps_resolve"] + 8.0 * ctr["sa_rows_resolved"] + 60.0 * ctr["dp_problems"]),
+              "k_fill": (ctr["ms_fill"], ctr["n_fill"], 4.0 * ctr["dp_cells"]),
+              "k_bt": (ctr["ms_bt"], ctr["n_bt"], 12.0 * ctr["bt_steps"])}
+    dom = max(phases, key=lambda k: phases[k][0])
+    ms, nl, byts = phases[dom]
+    achieved = (byts / max(nl, 1)) / ((ms / max(nl, 1)) * 1e-3) / 1e9 if ms > 0 else 0.0
+    line = {"metric": METRIC, "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1000.0 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic",
+            "config": {"workload": "configs[1]: 5 Mbp i.i.d. reference, 1M x 150 bp simulated reads, unpaired, %s" % OPTS,
+                       "reads_per_step_per_gpu": n, "l2": "inputs larger than L2 (300 MB of reads + 160 KB of DP scratch per problem per step)",
+                       "aligned_fraction": aligned / float(n), "parallelism": "reads sharded, index replicated per GPU"},
+            "gcups": ctr["dp_cells"] * world / dev_s / 1e9 if dev_s > 0 else None,
+            "gcups_fill_kernel": ctr["dp_cells"] / (ctr["ms_fill"] * 1e-3) / 1e9 if ctr["ms_fill"] > 0 else None,
+            "phase_ms_per_step": {k: phases[k][0] / args.steps for k in phases} | {"glue": ctr["ms_glue"] / args.steps, "wall": 1000.0 * wall / args.steps},
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src},
+            "e2e": {"value": total_reads / e2e_s, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(ctr["launches"]), "clocks": clocks}
+    if rank == 0:
+        if not args.no_cpu_baseline and world == 1:
+            try:
+                cores = cpu_cores()
+                sample = int(os.environ.get("BT2_BENCH_REF_READS", "100000"))
+                fq = os.path.join(WORK, "ref_sample.fq")
+                write_fastq(fq, ascii_reads[:sample])
+                pm = int(os.environ.get("BT2_BENCH_REF_P", "100"))
+                dt, ext = run_reference_binary(base, fq, sample, cores, pm)
+                line["cpu_baseline"] = {"value": sample / dt, "unit": "reads/s", "cores": cores, "kind": "reference",
+                                        "sample": "first %d reads of the workload, bowtie2-align-l OMP_NUM_THREADS=%d -p %d -S /dev/null, wall %.2fs (extendSeeds phase %s s)" % (sample, cores, pm, dt, ext)}
+            except Exception as e:  # the baseline is reported, never required
+                line["cpu_baseline"] = {"value": None, "unit": "reads/s", "cores": cpu_cores(), "kind": "reference", "sample": "failed: %s" % e}
+        print(json.dumps(line), flush=True)
+    gpu.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -239,8 +239,12 @@ typedef struct bt2gpu_counters {
 	uint64_t bt_attempts;
 	uint64_t bt_steps;
 	uint64_t alns_reported;
-	double   ms_seed, ms_glue, ms_resolve, ms_extend, ms_h2d, ms_d2h; /* CUDA-event totals */
+	/* CUDA-event totals (ms) on the library's stream, per phase: K_seed, glue kernels,
+	 * extension-step kernel (SA resolve + framing + window fetch), K_fill, backtrace kernel,
+	 * H2D, D2H, and whole bt2gpu_run_resident calls */
+	double   ms_seed, ms_glue, ms_resolve, ms_fill, ms_bt, ms_h2d, ms_d2h, ms_run;
 	uint64_t launches;          /* kernels launched by the library                 */
+	uint64_t n_seed, n_step, n_fill, n_bt; /* launches of the four main kernels    */
 } bt2gpu_counters;
 
 typedef struct bt2gpu_ctx bt2gpu_ctx;

@@ -26,7 +26,7 @@ using namespace bt2;
 	char b_[512]; snprintf(b_, sizeof(b_), "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
 	throw std::string(b_); } } while(0)
 
-enum { PH_SEED = 0, PH_GLUE, PH_RESOLVE, PH_FILL, PH_BT, PH_H2D, PH_D2H, PH_N };
+enum { PH_SEED = 0, PH_GLUE, PH_RESOLVE, PH_FILL, PH_BT, PH_H2D, PH_D2H, PH_RUN, PH_N };
 enum { C_CAND0 = 0, C_CAND1, C_ACTIVE, C_EXT0, C_EXT1, C_ROUNDEND, C_SAMP, C_SEEDTASK, C_N = 16 };
 
 struct DBuf { // growable device buffer
@@ -62,7 +62,7 @@ struct bt2gpu_ctx {
 	DevParams P; DevParams* dP = nullptr;
 	DevIndex ix; DevRef rf;
 	std::vector<void*> resident;      // index / reference allocations
-	uint32_t nslots = 0, sampSlots = 0, maxBatch = 0;
+	uint32_t nslots = 0, sampSlots = 0, maxBatch = 0, btgen = 0;
 	// problem-slot arrays
 	DBuf probs, hef, masks, stacks;
 	// per-batch arrays
@@ -108,7 +108,7 @@ struct Phase {
 	~Phase() { cudaEventRecord(c->spans[idx].b, c->stream); }
 };
 void flush_spans(bt2gpu_ctx* c) {
-	double* acc[PH_N] = { &c->ctr.ms_seed, &c->ctr.ms_glue, &c->ctr.ms_resolve, &c->ctr.ms_extend, &c->ctr.ms_extend, &c->ctr.ms_h2d, &c->ctr.ms_d2h };
+	double* acc[PH_N] = { &c->ctr.ms_seed, &c->ctr.ms_glue, &c->ctr.ms_resolve, &c->ctr.ms_fill, &c->ctr.ms_bt, &c->ctr.ms_h2d, &c->ctr.ms_d2h, &c->ctr.ms_run };
 	for(auto& s : c->spans) { float ms = 0; if(cudaEventElapsedTime(&ms, s.a, s.b) == cudaSuccess) *acc[s.ph] += ms; }
 	c->spans.clear(); c->evused = 0;
 }
@@ -226,6 +226,8 @@ void do_run(bt2gpu_ctx* c) {
 	cudaStream_t st = c->stream;
 	c->out_alns = c->out_edits = 0;
 	if(n == 0) return;
+	bt2gpu_ctx::Span runspan; runspan.ph = PH_RUN; runspan.a = get_event(c); runspan.b = get_event(c);
+	CK(cudaEventRecord(runspan.a, st));
 	CK(cudaMemsetAsync(c->counters.p, 0, C_N * 4, st));
 	CK(cudaMemsetAsync(c->pooltops.p, 0, 16, st));
 	CK(cudaMemsetAsync(c->poolerr.p, 0, 4, st));
@@ -246,7 +248,7 @@ void do_run(bt2gpu_ctx* c) {
 	sa.r_n = c->s_rn.as<uint16_t>(); sa.r_cur = c->s_rcur.as<uint16_t>(); sa.r_thresh = c->s_rth.as<uint16_t>(); sa.r_flags = c->s_rfl.as<uint8_t>();
 	sa.r_conv_off = c->s_rco.as<uint32_t>(); sa.r_conv_n = c->s_rcn.as<uint16_t>(); sa.r_nseen = c->s_rns.as<uint16_t>();
 	sa.mass = c->s_mass.as<double>(); sa.elim = c->s_elim.as<uint8_t>();
-	BtArrays bta; bta.hef = c->hef.as<uint32_t>(); bta.masks = c->masks.as<uint16_t>(); bta.stacks = c->stacks.as<BtFrame>();
+	BtArrays bta; bta.hef = c->hef.as<uint32_t>(); bta.masks = c->masks.as<uint32_t>(); bta.gen = 0; bta.stacks = c->stacks.as<BtFrame>();
 	bta.scratch = c->scratch.as<uint32_t>(); bta.seq = ba.seq; bta.qual = ba.qual;
 	Problem* probs = c->probs.as<Problem>();
 	const Pools pools = c->pools;
@@ -267,7 +269,7 @@ void do_run(bt2gpu_ctx* c) {
 			sk.hits = c->hits.as<SeedHit>(); sk.counter = cnt + C_SEEDTASK; sk.stats = stats;
 			const uint64_t ntasks = (uint64_t)nactive * W;
 			const uint32_t blocks = (uint32_t)std::min<uint64_t>((uint64_t)seedBlocks, (ntasks + 31) / 32);
-			k_seed<0><<<blocks, 256, 0, st>>>(c->ix, c->dP, sk); LAUNCH(c);
+			k_seed<0><<<blocks, 256, 0, st>>>(c->ix, c->dP, sk); LAUNCH(c); c->ctr.n_seed++;
 		}
 		uint32_t ncur, nsamp;
 		{
@@ -288,12 +290,14 @@ void do_run(bt2gpu_ctx* c) {
 			for(uint32_t b = 0; b < ncur; b += c->nslots) {
 				const uint32_t k = std::min(c->nslots, ncur - b);
 				{ Phase ph(c, PH_RESOLVE);
-				  k_step<<<nblk(k, 128), 128, 0, st>>>(c->dP, c->ix, c->rf, pools, states, L[3 + cur], b, k, probs, L[5], cnt + C_ROUNDEND); LAUNCH(c); }
+				  k_step<<<nblk(k, 128), 128, 0, st>>>(c->dP, c->ix, c->rf, pools, states, L[3 + cur], b, k, probs, L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_step++; }
 				{ Phase ph(c, PH_FILL);
 				  FillArgs fa; fa.probs = probs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.hef = c->hef.as<uint32_t>(); fa.stats = stats + 8;
-				  k_fill<<<nblk(k, BT2_FILL_WARPS), BT2_FILL_WARPS * 32, 0, st>>>(c->dP, fa); LAUNCH(c); }
+				  k_fill<<<nblk(k, BT2_FILL_WARPS), BT2_FILL_WARPS * 32, 0, st>>>(c->dP, fa); LAUNCH(c); c->ctr.n_fill++; }
 				{ Phase ph(c, PH_BT);
-				  k_bt<<<nblk(k, 128), 128, 0, st>>>(c->dP, pools, states, probs, k, bta, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); }
+				  if(++c->btgen >= (1u << 19)) { CK(cudaMemsetAsync(c->masks.p, 0, (size_t)c->nslots * BT2_MASK_WORDS * 4, st)); c->btgen = 1; }
+				  bta.gen = c->btgen;
+				  k_bt<<<nblk(k, 128), 128, 0, st>>>(c->dP, pools, states, probs, k, bta, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_bt++; }
 			}
 			ncur = read_counters(c)[nxt ? C_EXT1 : C_EXT0];
 			cur = nxt;
@@ -326,6 +330,7 @@ void do_run(bt2gpu_ctx* c) {
 		k_gather<<<nblk(n, 128), 128, 0, st>>>(states, pools, c->scratch.as<uint32_t>(), n, c->albase.as<uint32_t>(), c->edbase.as<uint32_t>(),
 		                                       c->o_rr.as<bt2gpu_read_result>(), c->o_alns.as<bt2gpu_aln>(), c->o_edits.as<bt2gpu_edit>()); LAUNCH(c);
 	}
+	CK(cudaEventRecord(runspan.b, st)); c->spans.push_back(runspan);
 	// ---- counters
 	unsigned long long hs[32];
 	CK(cudaMemcpyAsync(hs, c->stats.p, sizeof(hs), cudaMemcpyDeviceToHost, st));
@@ -404,7 +409,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		// ---- problem slots
 		const char* es = getenv("BT2GPU_SLOTS"); const char* eb = getenv("BT2GPU_BATCH");
 		size_t freeB = 0, totB = 0; CK(cudaMemGetInfo(&freeB, &totB));
-		const size_t perSlot = sizeof(Problem) + (size_t)BT2_HEF_WORDS * 4 + (size_t)BT2_MASK_WORDS * 2 + (size_t)BT2_BT_STACK * sizeof(BtFrame);
+		const size_t perSlot = sizeof(Problem) + (size_t)BT2_HEF_WORDS * 4 + (size_t)BT2_MASK_WORDS * 4 + (size_t)BT2_BT_STACK * sizeof(BtFrame);
 		uint32_t slots = es ? (uint32_t)atoi(es) : 131072u;
 		const size_t budget = freeB / 3;
 		if((size_t)slots * perSlot > budget) slots = (uint32_t)(budget / perSlot);
@@ -413,7 +418,8 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		c->maxBatch = eb ? (uint32_t)atoi(eb) : (1u << 20);
 		if(c->maxBatch < 1) c->maxBatch = 1;
 		c->probs.ensure((size_t)slots * sizeof(Problem)); c->hef.ensure((size_t)slots * BT2_HEF_WORDS * 4);
-		c->masks.ensure((size_t)slots * BT2_MASK_WORDS * 2); c->stacks.ensure((size_t)slots * BT2_BT_STACK * sizeof(BtFrame));
+		c->masks.ensure((size_t)slots * BT2_MASK_WORDS * 4);
+		CK(cudaMemset(c->masks.p, 0, (size_t)slots * BT2_MASK_WORDS * 4)); c->stacks.ensure((size_t)slots * BT2_BT_STACK * sizeof(BtFrame));
 		c->counters.ensure(C_N * 4); c->stats.ensure(32 * 8); c->pooltops.ensure(16); c->poolerr.ensure(4);
 		c->h_counters.ensure(C_N * 4);
 		CK(cudaDeviceSynchronize());

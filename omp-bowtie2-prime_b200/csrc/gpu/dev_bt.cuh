@@ -40,11 +40,12 @@ struct BtCtx {
 	const DevParams* P;
 	const Problem* prob;
 	const uint32_t* hef;   // skewed H|E<<8|F<<16 words of this problem
-	uint16_t* masks;       // [rows][cols] of this problem slot
+	uint32_t* masks;       // [rows][cols] of this problem slot: SSEMatrix::masks_ (low 13 bits) tagged with `gen`
+	uint32_t gen;          // generation of this problem (19 bits); a cell whose tag differs reads as 0, which
+	                       // replaces the reference's lazy per-row memset (resetRow, aligner_swsse.h)
 	BtFrame* stack;        // [BT2_BT_STACK] of this problem slot
 	uint32_t* scratch;     // per-read edit scratch
 	ReadView rv;
-	uint32_t rowReset[(BT2GPU_MAX_ROWS + 31) / 32];
 };
 
 BT2_HD int mask_to_char(int m) { return m > 15 ? 'N' : "?ACMGRSVTWYHKDBN"[m]; }
@@ -80,16 +81,14 @@ BT2_HD bool backtrace(BtCtx& cx, ReadState& rs, AlnRec& out, int row, int col) {
 	#define EV(w) ((int)(((w) >> 8) & 255u) - 255)
 	#define FV(w) ((int)(((w) >> 16) & 255u) - 255)
 	#define MK(r, c) cx.masks[(uint32_t)(r) * (uint32_t)cols + (uint32_t)(c)]
+	const uint32_t gtag = cx.gen << 13;
 	while(row >= 0) {
 		rs.btSteps++;
 		const int readc = cx.rv.rd(row), refm = pb.rf[col], readq = cx.rv.q(row);
 		bool empty = false, canMoveThru = true, branch = false;
 		int cur = MV_DIAG;
-		if(!(cx.rowReset[row >> 5] & (1u << (row & 31)))) {
-			for(int c = 0; c < cols; c++) MK(row, c) = 0;
-			cx.rowReset[row >> 5] |= (1u << (row & 31));
-		}
 		uint32_t m16 = MK(row, col);
+		m16 = ((m16 & ~0x1fffu) == gtag) ? (m16 & 0x1fffu) : 0u;
 		const bool reportedThru = (m16 & 1) != 0;
 		if(reportedThru) {
 			canMoveThru = false;
@@ -153,7 +152,7 @@ BT2_HD bool backtrace(BtCtx& cx, ReadState& rs, AlnRec& out, int row, int col) {
 			}
 		}
 		m16 |= 1;
-		MK(row, col) = (uint16_t)m16;
+		MK(row, col) = gtag | m16;
 		if(!canMoveThru) {
 			if(nstack > 0) {
 				const BtFrame f = cx.stack[--nstack];
@@ -296,7 +295,6 @@ BT2_HD int after_fill(BtCtx& cx, const Pools& pools, ReadState& rs) {
 	rs.nExDpSuccs++; rs.nDpLastSucc = rs.nExDps - 1;
 	if(rs.nDpFail > rs.nDpFailStreak) rs.nDpFailStreak = rs.nDpFail;
 	rs.nDpFail = 0;
-	for(uint32_t i = 0; i < (BT2GPU_MAX_ROWS + 31) / 32; i++) cx.rowReset[i] = 0;
 	uint32_t cural = 0;
 	const uint32_t ncand = pb.ncand;
 	const int lastRow = pb.rows - 1;
@@ -308,7 +306,8 @@ BT2_HD int after_fill(BtCtx& cx, const Pools& pools, ReadState& rs) {
 		AlnRec a; bool got = false;
 		while(cural < ncand) {
 			const int col = pb.cand[cural] & 255;
-			if((cx.rowReset[lastRow >> 5] & (1u << (lastRow & 31))) && (cx.masks[(uint32_t)lastRow * pb.cols + col] & 1)) { cural++; continue; }
+			{ const uint32_t m = cx.masks[(uint32_t)lastRow * pb.cols + col];
+			  if((m & ~0x1fffu) == (cx.gen << 13) && (m & 1u)) { cural++; continue; } } // start cell already reportedThrough
 			const uint32_t reseed = rnd.nextU32() + 1;
 			rnd.init(reseed);
 			got = backtrace(cx, rs, a, lastRow, col);

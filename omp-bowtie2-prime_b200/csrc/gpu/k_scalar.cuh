@@ -123,7 +123,7 @@ __global__ void k_step(const DevParams* __restrict__ Pp, const DevIndex ix, cons
 	states[read] = rs;
 }
 
-struct BtArrays { const uint32_t* hef; uint16_t* masks; BtFrame* stacks; uint32_t* scratch; const uint8_t* seq; const uint8_t* qual; };
+struct BtArrays { const uint32_t* hef; uint32_t* masks; uint32_t gen; BtFrame* stacks; uint32_t* scratch; const uint8_t* seq; const uint8_t* qual; };
 
 __global__ void k_bt(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const Problem* probs, uint32_t count,
                      const BtArrays ba, uint32_t* next_list, uint32_t* next_cnt, uint32_t* roundend_list, uint32_t* roundend_cnt) {
@@ -136,7 +136,7 @@ __global__ void k_bt(const DevParams* __restrict__ Pp, const Pools pools, ReadSt
 	BtCtx cx;
 	cx.P = Pp; cx.prob = &pb;
 	cx.hef = ba.hef + (size_t)j * BT2_HEF_WORDS;
-	cx.masks = ba.masks + (size_t)j * BT2_MASK_WORDS;
+	cx.masks = ba.masks + (size_t)j * BT2_MASK_WORDS; cx.gen = ba.gen;
 	cx.stack = ba.stacks + (size_t)j * BT2_BT_STACK;
 	cx.scratch = ba.scratch + (size_t)read * BT2_SCRATCH_EDITS;
 	cx.rv.seq = ba.seq + rs.seq_off; cx.rv.qual = ba.qual + rs.seq_off; cx.rv.rdlen = rs.rdlen; cx.rv.fw = pb.fw != 0;
