@@ -40,8 +40,8 @@ struct BtCtx {
 	const DevParams* P;
 	const Problem* prob;
 	const uint32_t* hef;   // skewed H|E<<8|F<<16 words of this problem
-	uint32_t* masks;       // [rows][cols] of this problem slot: SSEMatrix::masks_ (low 13 bits) tagged with `gen`
-	uint32_t gen;          // generation of this problem (19 bits); a cell whose tag differs reads as 0, which
+	uint16_t* masks;       // [rows][cols] of this problem slot: SSEMatrix::masks_ (low 13 bits) tagged with `gen`
+	uint32_t gen;          // generation of this problem (1..7, 3 bits); a cell whose tag differs reads as 0, which
 	                       // replaces the reference's lazy per-row memset (resetRow, aligner_swsse.h)
 	BtFrame* stack;        // [BT2_BT_STACK] of this problem slot
 	uint32_t* scratch;     // per-read edit scratch
@@ -152,7 +152,7 @@ BT2_HD bool backtrace(BtCtx& cx, ReadState& rs, AlnRec& out, int row, int col) {
 			}
 		}
 		m16 |= 1;
-		MK(row, col) = gtag | m16;
+		MK(row, col) = (uint16_t)(gtag | m16);
 		if(!canMoveThru) {
 			if(nstack > 0) {
 				const BtFrame f = cx.stack[--nstack];

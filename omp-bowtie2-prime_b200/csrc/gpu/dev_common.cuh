@@ -305,14 +305,19 @@ struct Problem {
 	uint8_t  rf[BT2GPU_MAX_COLS + 8];   // reference masks for columns 0..cols (cols+1 fetched)
 };
 
-// skewed H/E/F store: word index of cell (r,c); each word = H | E<<8 | F<<16 (raw u8 values)
+// skewed H/E/F store: word index of cell (r,c); each word = H | E<<8 | F<<16 (raw u8 values).
+// Layout [col+strip][strip][k] with the R (padded to RP) rows of a strip adjacent: one fill store
+// instruction writes one contiguous run of 32 x RP words, and the backtrace finds (r,c) and (r-1,c)
+// in the same 16-byte chunk two times out of three.
 BT2_HD uint32_t hef_index(uint32_t r, uint32_t c, uint32_t R) {
 	const uint32_t v = (R == 1) ? r : (R == 2 ? (r >> 1) : (r / 3));
 	const uint32_t k = r - v * R;
-	return (((c + v) * R + k) << 6) + v;
+	const uint32_t RP = (R == 3) ? 4u : R;
+	return (((c + v) << 6) + v) * RP + k;
 }
-#define BT2_HEF_WORDS ((BT2GPU_MAX_COLS + 64) * 3 * 64)       // per problem slot
+#define BT2_HEF_WORDS ((BT2GPU_MAX_COLS + 64) * 64 * 4)      // per problem slot
 #define BT2_MASK_WORDS (BT2GPU_MAX_ROWS * BT2GPU_MAX_COLS)    // u16 per cell, per problem slot
+#define BT2_MASK_GENS 7                                       // 3-bit generation tag: memset every 7 launches
 
 // pools shared by the per-read kernels
 struct Pools {

@@ -14,8 +14,8 @@
 // LOP3/PRMT each (SASS evidence).  u8 saturation is exact in 16 bits:
 // subs_u8(a,b) == max(a-b,0) for 0<=a,b<=255, which is one VIADDMNMX.
 // Strip boundaries travel down with __shfl_up_sync.  Every cell is stored as one
-// 32-bit word H | E<<8 | F<<16 in a skewed layout [(col+strip)*R+k][strip] so that
-// each store instruction writes one contiguous 128-byte line.
+// 32-bit word H | E<<8 | F<<16 in a skewed layout [col+strip][strip][k] so that each
+// store instruction writes one contiguous run (16 bytes per lane for R=3).
 #pragma once
 #include "dev_common.cuh"
 
@@ -74,7 +74,7 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 		if(lane == 0) { recvH = 0x00ffu | (wrapH << 16); recvF = (wrapF << 16); } // row 0: H(-1,*) = 0xff, F = 0
 		const uint32_t x_lo = act_lo ? sh.refc[c_lo] : 4u, x_hi = act_hi ? sh.refc[c_hi] : 4u;
 		uint32_t diag = prevRecvH, f = recvF;
-		uint32_t* outp = hef + (((uint32_t)t * R) << 6) + lane;
+		uint32_t wlo[R], whi[R];
 		#pragma unroll
 		for(int k = 0; k < R; k++) {
 			const uint32_t s = sh.tab[(k * 5 + x_lo) * 64 + lane] | sh.tab[(k * 5 + x_hi) * 64 + 32 + lane];
@@ -84,8 +84,8 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 			const uint32_t e = Ep[k];
 			h = __vimax3_s16x2(h, e, f);
 			// one word per cell: H | E<<8 | F<<16
-			if(act_lo) outp[(k << 6)]      = __byte_perm(__byte_perm(h, e, 0x0040), f, 0x5410);
-			if(act_hi) outp[(k << 6) + 32] = __byte_perm(__byte_perm(h, e, 0x0062), f, 0x7610);
+			wlo[k] = __byte_perm(__byte_perm(h, e, 0x0040), f, 0x5410);
+			whi[k] = __byte_perm(__byte_perm(h, e, 0x0062), f, 0x7610);
 			if(k == kstar) {
 				if(own_lo && act_lo) sh.hlast[c_lo] = (uint8_t)(h & 0xffu);
 				if(own_hi && act_hi) sh.hlast[c_hi] = (uint8_t)((h >> 16) & 0xffu);
@@ -95,6 +95,21 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 			const uint32_t t2 = __viaddmax_s16x2(h, neg_rfgo, 0u);
 			f = __viaddmax_s16x2(f, neg_rfge, t2);
 			Hp[k] = h & am; Ep[k] = en & am;
+		}
+		{ // one 4*RP-byte store per strip: [t][strip][k]
+			constexpr int RP = (R == 3) ? 4 : R;
+			uint32_t* olo = hef + (((uint32_t)t << 6) + lane) * RP;
+			uint32_t* ohi = olo + 32 * RP;
+			if(R == 3) {
+				if(act_lo) *reinterpret_cast<uint4*>(olo) = make_uint4(wlo[0], wlo[1 % R], wlo[2 % R], 0u);
+				if(act_hi) *reinterpret_cast<uint4*>(ohi) = make_uint4(whi[0], whi[1 % R], whi[2 % R], 0u);
+			} else if(R == 2) {
+				if(act_lo) *reinterpret_cast<uint2*>(olo) = make_uint2(wlo[0], wlo[1 % R]);
+				if(act_hi) *reinterpret_cast<uint2*>(ohi) = make_uint2(whi[0], whi[1 % R]);
+			} else {
+				if(act_lo) *olo = wlo[0];
+				if(act_hi) *ohi = whi[0];
+			}
 		}
 		sendH = Hp[R - 1]; sendF = f & am;
 		prevRecvH = (lane == 0) ? (0x00ffu | (recvH & 0xffff0000u)) : recvH;

@@ -123,7 +123,7 @@ __global__ void k_step(const DevParams* __restrict__ Pp, const DevIndex ix, cons
 	states[read] = rs;
 }
 
-struct BtArrays { const uint32_t* hef; uint32_t* masks; uint32_t gen; BtFrame* stacks; uint32_t* scratch; const uint8_t* seq; const uint8_t* qual; };
+struct BtArrays { const uint32_t* hef; uint16_t* masks; uint32_t gen; BtFrame* stacks; uint32_t* scratch; const uint8_t* seq; const uint8_t* qual; };
 
 __global__ void k_bt(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const Problem* probs, uint32_t count,
                      const BtArrays ba, uint32_t* next_list, uint32_t* next_cnt, uint32_t* roundend_list, uint32_t* roundend_cnt) {
