@@ -211,7 +211,8 @@ typedef struct bt2gpu_read_result {
 	/* F14: the reference's per-slot edit scratch (SwDriver::resGap_.alres.ned_)
 	 * as the last backtrace attempt of the read left it; the reference's SAM
 	 * writer reads alignment edits through it. */
-	uint32_t scratch_off;  /* index of first scratch edit in bt2gpu_results.edits   */
+	uint32_t scratch_off;  /* index of first scratch edit in bt2gpu_results.edits; the image is
+	                        * cut at the largest n_edits of the read's alignments     */
 	uint32_t n_scratch;
 } bt2gpu_read_result;
 

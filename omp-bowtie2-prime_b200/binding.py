@@ -255,6 +255,12 @@ class GpuAligner:
         self._ck(self._g.bt2gpu_align_batch(self.ptr, batch.reads, C.byref(r)), "bt2gpu_align_batch")
         return Results(r)
 
+    def align_raw(self, reads_struct):
+        """bt2gpu_align_batch on a caller-built bt2gpu_reads (e.g. views over pinned host memory)."""
+        r = bt2gpu_results()
+        self._ck(self._g.bt2gpu_align_batch(self.ptr, C.byref(reads_struct), C.byref(r)), "bt2gpu_align_batch")
+        return Results(r)
+
     def upload(self, batch):
         self._ck(self._g.bt2gpu_upload(self.ptr, batch.reads), "bt2gpu_upload")
 

@@ -27,7 +27,7 @@ using namespace bt2;
 	throw std::string(b_); } } while(0)
 
 enum { PH_SEED = 0, PH_GLUE, PH_RESOLVE, PH_FILL, PH_BT, PH_H2D, PH_D2H, PH_RUN, PH_N };
-enum { C_CAND0 = 0, C_CAND1, C_ACTIVE, C_EXT0, C_EXT1, C_ROUNDEND, C_SAMP, C_SEEDTASK, C_N = 16 };
+enum { C_CAND0 = 0, C_CAND1, C_ACTIVE, C_EXT0, C_EXT1, C_ROUNDEND, C_SAMP, C_SEEDTASK, C_BTTASK, C_N = 16 };
 
 struct DBuf { // growable device buffer
 	void* p = nullptr; size_t cap = 0;
@@ -248,11 +248,11 @@ void do_run(bt2gpu_ctx* c) {
 	sa.r_n = c->s_rn.as<uint16_t>(); sa.r_cur = c->s_rcur.as<uint16_t>(); sa.r_thresh = c->s_rth.as<uint16_t>(); sa.r_flags = c->s_rfl.as<uint8_t>();
 	sa.r_conv_off = c->s_rco.as<uint32_t>(); sa.r_conv_n = c->s_rcn.as<uint16_t>(); sa.r_nseen = c->s_rns.as<uint16_t>();
 	sa.mass = c->s_mass.as<double>(); sa.elim = c->s_elim.as<uint8_t>();
-	BtArrays bta; bta.hef = c->hef.as<uint32_t>(); bta.masks = c->masks.as<uint16_t>(); bta.gen = 0; bta.stacks = c->stacks.as<BtFrame>();
+	BtArrays bta; bta.hef = c->hef.as<uint32_t>(); bta.masks = c->masks.as<uint32_t>(); bta.gen = 0; bta.stacks = c->stacks.as<BtFrame>();
 	bta.scratch = c->scratch.as<uint32_t>(); bta.seq = ba.seq; bta.qual = ba.qual;
 	Problem* probs = c->probs.as<Problem>();
 	const Pools pools = c->pools;
-	int seedBlocks = 0; { int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device); seedBlocks = nsm * 8; }
+	int seedBlocks = 0, btMaxBlocks = 0; { int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device); seedBlocks = nsm * 8; btMaxBlocks = nsm * 8; }
 
 	k_begin<<<nblk(n, 256), 256, 0, st>>>(ba, states, L[0], cnt + C_CAND0); LAUNCH(c);
 	uint32_t ncand = read_counters(c)[C_CAND0];
@@ -295,9 +295,11 @@ void do_run(bt2gpu_ctx* c) {
 				  FillArgs fa; fa.probs = probs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.hef = c->hef.as<uint32_t>(); fa.stats = stats + 8;
 				  k_fill<<<nblk(k, BT2_FILL_WARPS), BT2_FILL_WARPS * 32, 0, st>>>(c->dP, fa); LAUNCH(c); c->ctr.n_fill++; }
 				{ Phase ph(c, PH_BT);
-				  if(++c->btgen > BT2_MASK_GENS) { CK(cudaMemsetAsync(c->masks.p, 0, (size_t)c->nslots * BT2_MASK_WORDS * 2, st)); c->btgen = 1; }
+				  if(++c->btgen > BT2_MASK_GEN_MAX) { CK(cudaMemsetAsync(c->masks.p, 0, (size_t)c->nslots * BT2_MASK_WORDS * 4, st)); c->btgen = 1; }
 				  bta.gen = c->btgen;
-				  k_bt<<<nblk(k, 128), 128, 0, st>>>(c->dP, pools, states, probs, k, bta, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_bt++; }
+				  zero_counter(c, C_BTTASK);
+				  const uint32_t btBlocks = std::min<uint32_t>(nblk(k, 128), (uint32_t)btMaxBlocks);
+				  k_bt<<<btBlocks, 128, 0, st>>>(c->dP, pools, states, probs, k, bta, cnt + C_BTTASK, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_bt++; }
 			}
 			ncur = read_counters(c)[nxt ? C_EXT1 : C_EXT0];
 			cur = nxt;
@@ -409,7 +411,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		// ---- problem slots
 		const char* es = getenv("BT2GPU_SLOTS"); const char* eb = getenv("BT2GPU_BATCH");
 		size_t freeB = 0, totB = 0; CK(cudaMemGetInfo(&freeB, &totB));
-		const size_t perSlot = sizeof(Problem) + (size_t)BT2_HEF_WORDS * 4 + (size_t)BT2_MASK_WORDS * 2 + (size_t)BT2_BT_STACK * sizeof(BtFrame);
+		const size_t perSlot = sizeof(Problem) + (size_t)BT2_HEF_WORDS * 4 + (size_t)BT2_MASK_WORDS * 4 + (size_t)BT2_BT_STACK * sizeof(BtFrame);
 		uint32_t slots = es ? (uint32_t)atoi(es) : 262144u;
 		const size_t budget = (freeB / 20) * 9;
 		if((size_t)slots * perSlot > budget) slots = (uint32_t)(budget / perSlot);
@@ -418,8 +420,8 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		c->maxBatch = eb ? (uint32_t)atoi(eb) : (1u << 20);
 		if(c->maxBatch < 1) c->maxBatch = 1;
 		c->probs.ensure((size_t)slots * sizeof(Problem)); c->hef.ensure((size_t)slots * BT2_HEF_WORDS * 4);
-		c->masks.ensure((size_t)slots * BT2_MASK_WORDS * 2);
-		CK(cudaMemset(c->masks.p, 0, (size_t)slots * BT2_MASK_WORDS * 2)); c->stacks.ensure((size_t)slots * BT2_BT_STACK * sizeof(BtFrame));
+		c->masks.ensure((size_t)slots * BT2_MASK_WORDS * 4);
+		CK(cudaMemset(c->masks.p, 0, (size_t)slots * BT2_MASK_WORDS * 4)); c->stacks.ensure((size_t)slots * BT2_BT_STACK * sizeof(BtFrame));
 		c->counters.ensure(C_N * 4); c->stats.ensure(32 * 8); c->pooltops.ensure(16); c->poolerr.ensure(4);
 		c->h_counters.ensure(C_N * 4);
 		CK(cudaDeviceSynchronize());

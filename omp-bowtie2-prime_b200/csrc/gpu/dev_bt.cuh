@@ -1,4 +1,4 @@
-// What follows a DP fill inside SwDriver::extendSeeds, one thread per problem:
+// What follows a DP fill inside SwDriver::extendSeeds:
 //   result bookkeeping                               aligner_sw_driver.cpp:505-531
 //   SwAligner::nextAlignment                         aligner_sw.cpp:252-375
 //   SwAligner::backtraceNucleotidesEnd2EndSseU8      aligner_swsse_ee_u8.cpp:746-1352
@@ -6,6 +6,10 @@
 //   AlnSinkWrap::report + ReportingState::foundUnpaired  aln_sink.cpp:1395-1453, 107-140
 //   minsc tightening                                 aligner_sw_driver.cpp:588-618
 // The per-read edit scratch reproduces SwDriver::resGap_.alres.ned_.
+//
+// Written as a flat state machine (BtMachine::step does one unit of work: take a
+// candidate, one backtrace cell, or finish an alignment) so that the lanes of a warp,
+// each working on its own problem and pulling a new one when done, stay in one loop.
 #pragma once
 #include "dev_common.cuh"
 
@@ -22,9 +26,16 @@ namespace bt2 {
 enum { BT_CONTINUE = 0, BT_ROUND_END = 1 };
 enum { CT_E = 0, CT_F = 1, CT_H = 2 };
 enum { MV_DIAG, MV_REF_OPEN, MV_READ_OPEN, MV_RFGAP_EXT, MV_RDGAP_EXT };
+enum { BP_CAND = 0, BP_STEP = 1, BP_POST = 2, BP_DONE = 3 };
 
 struct BtFrame { uint32_t a, b, c, d; }; // packed branch-stack frame
 #define BT2_BT_STACK 400
+// backtrace masks: SSEMatrix::masks_ (13 bits) + 19-bit generation tag per cell, stored by
+// diagonal ([col-row+rows-1][row]) so that a run of diagonal moves stays inside one sector;
+// a cell whose tag differs from the problem's generation reads as 0, which replaces the
+// reference's lazy per-row memset (SSEMatrix::resetRow, aligner_swsse.h)
+#define BT2_MASK_GEN_MAX ((1u << 19) - 1)
+#define BT2_MASK_WORDS ((BT2GPU_MAX_ROWS + BT2GPU_MAX_COLS) * BT2GPU_MAX_ROWS)
 
 struct ReadView {
 	const uint8_t* seq; const uint8_t* qual; uint32_t rdlen; bool fw;
@@ -34,18 +45,6 @@ struct ReadView {
 		return c > 3 ? 4 : 3 - c;
 	}
 	BT2_HD int q(uint32_t row) const { return fw ? qual[row] : qual[rdlen - 1 - row]; }
-};
-
-struct BtCtx {
-	const DevParams* P;
-	const Problem* prob;
-	const uint32_t* hef;   // skewed H|E<<8|F<<16 words of this problem
-	uint16_t* masks;       // [rows][cols] of this problem slot: SSEMatrix::masks_ (low 13 bits) tagged with `gen`
-	uint32_t gen;          // generation of this problem (1..7, 3 bits); a cell whose tag differs reads as 0, which
-	                       // replaces the reference's lazy per-row memset (resetRow, aligner_swsse.h)
-	BtFrame* stack;        // [BT2_BT_STACK] of this problem slot
-	uint32_t* scratch;     // per-read edit scratch
-	ReadView rv;
 };
 
 BT2_HD int mask_to_char(int m) { return m > 15 ? 'N' : "?ACMGRSVTWYHKDBN"[m]; }
@@ -58,184 +57,6 @@ BT2_HD int sc_score(const DevParams& P, int rdc, int refm, int q) {
 	if(rdc > 3 || refm > 15) return -(int)P.npens[q];
 	if((refm & (1 << rdc)) != 0) return P.matchBonus;
 	return -(int)P.mmpens[q];
-}
-
-// One backtrace attempt from (row, col).  Edits are appended to the scratch 3'->5' and
-// reversed on success.  Returns true and fills `out` on success.
-BT2_HD bool backtrace(BtCtx& cx, ReadState& rs, AlnRec& out, int row, int col) {
-	const DevParams& P = *cx.P; const Problem& pb = *cx.prob;
-	const int rows = pb.rows, cols = pb.cols; const uint32_t R = pb.R;
-	int score = 0, ns = 0, readGaps = 0, refGaps = 0;
-	const int origCol = col;
-	uint32_t nstack = 0;
-	uint32_t ned = 0; // scratch count
-	uint32_t hw = rs.scr_hw;
-	#define PUSH_EDIT(x) do { if(ned < BT2_SCRATCH_EDITS) { cx.scratch[ned] = (x); } ned++; if(ned > hw) hw = ned; } while(0)
-	bool coreHit = false;
-	const int trimEnd = rows - row - 1;
-	int ct = CT_H;
-	rs.btAttempts++;
-	const int rdgo = P.rdGapOpen, rdge = P.rdGapExt, rfgo = P.rfGapOpen, rfge = P.rfGapExt;
-	#define HEF(r, c) cx.hef[hef_index((uint32_t)(r), (uint32_t)(c), R)]
-	#define HV(w) ((int)((w) & 255u) - 255)
-	#define EV(w) ((int)(((w) >> 8) & 255u) - 255)
-	#define FV(w) ((int)(((w) >> 16) & 255u) - 255)
-	#define MK(r, c) cx.masks[(uint32_t)(r) * (uint32_t)cols + (uint32_t)(c)]
-	const uint32_t gtag = cx.gen << 13;
-	while(row >= 0) {
-		rs.btSteps++;
-		const int readc = cx.rv.rd(row), refm = pb.rf[col], readq = cx.rv.q(row);
-		bool empty = false, canMoveThru = true, branch = false;
-		int cur = MV_DIAG;
-		uint32_t m16 = MK(row, col);
-		m16 = ((m16 & ~0x1fffu) == gtag) ? (m16 & 0x1fffu) : 0u;
-		const bool reportedThru = (m16 & 1) != 0;
-		if(reportedThru) {
-			canMoveThru = false;
-		} else if(row > 0) {
-			const bool gapsAllowed = !(row < P.gapbar || (rows - row - 1) < P.gapbar);
-			if(ct == CT_E) {
-				const uint32_t wc = HEF(row, col), wl = col > 0 ? HEF(row, col - 1) : 0u;
-				const int sc_cur = EV(wc);
-				int mask = 0;
-				if(HV(wl) - rdgo == sc_cur) mask |= 1;
-				if(EV(wl) - rdge == sc_cur) mask |= 2;
-				const int origMask = mask;
-				if(m16 & (1u << 7)) mask = (m16 >> 8) & 3;
-				if(mask == 3)      { cur = MV_READ_OPEN; m16 = (m16 & ~(7u << 7)) | (1u << 7) | (2u << 8); branch = true; }
-				else if(mask == 2) { cur = MV_RDGAP_EXT; m16 = (m16 & ~(7u << 7)) | (1u << 7); }
-				else if(mask == 1) { cur = MV_READ_OPEN; m16 = (m16 & ~(7u << 7)) | (1u << 7); }
-				else { empty = true; canMoveThru = (origMask == 0); }
-			} else if(ct == CT_F) {
-				const uint32_t wc = HEF(row, col), wu = HEF(row - 1, col);
-				const int sc_cur = FV(wc);
-				int mask = 0;
-				if(HV(wu) - rfgo == sc_cur) mask |= 1;
-				if(FV(wu) - rfge == sc_cur) mask |= 2;
-				const int origMask = mask;
-				if(m16 & (1u << 10)) mask = (m16 >> 11) & 3;
-				if(mask == 3)      { cur = MV_REF_OPEN;  m16 = (m16 & ~(7u << 10)) | (1u << 10) | (2u << 11); branch = true; }
-				else if(mask == 2) { cur = MV_RFGAP_EXT; m16 = (m16 & ~(7u << 10)) | (1u << 10); }
-				else if(mask == 1) { cur = MV_REF_OPEN;  m16 = (m16 & ~(7u << 10)) | (1u << 10); }
-				else { empty = true; canMoveThru = (origMask == 0); }
-			} else {
-				const uint32_t wc = HEF(row, col), wu = HEF(row - 1, col);
-				const bool hasLeft = col > 0;
-				const uint32_t wl = hasLeft ? HEF(row, col - 1) : 0xffffffu, wul = hasLeft ? HEF(row - 1, col - 1) : 0xffffffu;
-				const int sc_cur = HV(wc);
-				const int sc_diag = sc_score(P, readc, refm, readq - 33);
-				int mask = 0;
-				if(gapsAllowed) {
-					if(sc_cur == HV(wu) - rfgo) mask |= 1;
-					if(hasLeft && sc_cur == HV(wl) - rdgo) mask |= 2;
-					if(sc_cur == FV(wu) - rfge) mask |= 4;
-					if(hasLeft && sc_cur == EV(wl) - rdge) mask |= 8;
-				}
-				if(hasLeft && sc_cur == HV(wul) + sc_diag) mask |= 16;
-				const int origMask = mask;
-				if(m16 & (1u << 1)) mask = (m16 >> 2) & 31;
-				int select = -1;
-				const int opts = BT2_POPC((unsigned)mask);
-				if(opts == 1) {
-					select = BT2_CTZ((unsigned)mask);
-					m16 = (m16 & ~(31u << 1)) | (1u << 1);
-				} else if(opts > 1) {
-					if(mask & 16) select = 4; else if(mask & 1) select = 0; else if(mask & 4) select = 2;
-					else if(mask & 2) select = 1; else select = 3;
-					mask &= ~(1 << select);
-					m16 = (m16 & ~(31u << 1)) | (1u << 1) | ((uint32_t)mask << 2);
-					branch = true;
-				}
-				if(select != -1) {
-					cur = select == 4 ? MV_DIAG : select == 0 ? MV_REF_OPEN : select == 1 ? MV_READ_OPEN : select == 2 ? MV_RFGAP_EXT : MV_RDGAP_EXT;
-				} else { empty = true; canMoveThru = (origMask == 0); }
-			}
-		}
-		m16 |= 1;
-		MK(row, col) = (uint16_t)(gtag | m16);
-		if(!canMoveThru) {
-			if(nstack > 0) {
-				const BtFrame f = cx.stack[--nstack];
-				ned = f.a & 1023u; row = (int)((f.a >> 10) & 255u); col = (int)((f.a >> 18) & 255u);
-				ct = (int)((f.a >> 26) & 3u); coreHit = ((f.a >> 28) & 1u) != 0;
-				readGaps = (int)(f.b & 1023u); refGaps = (int)((f.b >> 10) & 1023u); ns = (int)((f.b >> 20) & 1023u);
-				score = (int)f.c;
-				continue;
-			}
-			rs.scr_cur = (uint16_t)ned; rs.scr_hw = (uint16_t)hw;
-			return false;
-		}
-		// this cell joins the path: core-diagonal test (aligner_swsse_ee_u8.cpp:1229-1262) folded in
-		const int diag = col - row + pb.triml;
-		const bool cellCore = diag >= 0 && diag >= pb.corel && diag <= pb.corer;
-		if(empty || row == 0) { coreHit = coreHit || cellCore; break; }
-		if(branch) {
-			if(nstack < BT2_BT_STACK) {
-				BtFrame f;
-				f.a = (ned & 1023u) | ((uint32_t)row << 10) | ((uint32_t)col << 18) | ((uint32_t)ct << 26) | ((coreHit ? 1u : 0u) << 28);
-				f.b = ((uint32_t)readGaps & 1023u) | (((uint32_t)refGaps & 1023u) << 10) | (((uint32_t)ns & 1023u) << 20);
-				f.c = (uint32_t)score; f.d = 0;
-				cx.stack[nstack++] = f;
-			}
-		}
-		coreHit = coreHit || cellCore;
-		switch(cur) {
-		case MV_DIAG: {
-			const int m = (readc > 3 || refm > 15) ? -1 : ((refm & (1 << readc)) ? 1 : 0);
-			ct = CT_H;
-			if(m != 1) {
-				PUSH_EDIT(pack_edit((uint32_t)row, (uint32_t)mask_to_char(refm), (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_MM));
-				score -= sc_mm(P, readc, refm, readq - 33);
-			} else score += P.matchBonus;
-			if(m == -1) ns++;
-			row--; col--;
-			break; }
-		case MV_REF_OPEN: case MV_RFGAP_EXT: {
-			PUSH_EDIT(pack_edit((uint32_t)row, '-', (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_REF_GAP));
-			row--;
-			ct = (cur == MV_REF_OPEN) ? CT_H : CT_F;
-			score -= (cur == MV_REF_OPEN) ? rfgo : rfge;
-			refGaps++;
-			break; }
-		default: {
-			PUSH_EDIT(pack_edit((uint32_t)row + 1, (uint32_t)mask_to_char(refm), '-', BT2GPU_EDIT_READ_GAP));
-			col--;
-			ct = (cur == MV_READ_OPEN) ? CT_H : CT_E;
-			score -= (cur == MV_READ_OPEN) ? rdgo : rdge;
-			readGaps++;
-			break; }
-		}
-	}
-	#undef HEF
-	#undef HV
-	#undef EV
-	#undef FV
-	#undef MK
-	rs.scr_hw = (uint16_t)hw;
-	rs.scr_cur = (uint16_t)ned;
-	if(!coreHit) return false;
-	{
-		const int readc = cx.rv.rd(row), refm = pb.rf[col];
-		const int m = (readc > 3 || refm > 15) ? -1 : ((refm & (1 << readc)) ? 1 : 0);
-		if(m != 1) {
-			PUSH_EDIT(pack_edit((uint32_t)row, (uint32_t)mask_to_char(refm), (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_MM));
-			score -= sc_mm(P, readc, refm, cx.rv.q(row) - 33);
-		} else score += P.matchBonus;
-		if(m == -1) ns++;
-		rs.scr_cur = (uint16_t)ned; rs.scr_hw = (uint16_t)hw;
-	}
-	#undef PUSH_EDIT
-	if(ns > rs.nceil) return false;
-	if(ned > BT2_SCRATCH_EDITS) return false; // beyond the reference's own DList<Edit,160> capacity
-	for(uint32_t i = 0; i < ned / 2; i++) { const uint32_t t = cx.scratch[i]; cx.scratch[i] = cx.scratch[ned - 1 - i]; cx.scratch[ned - 1 - i] = t; }
-	out.fw = pb.fw; out.tidx = pb.tidx; out.refoff = (int64_t)col + pb.refl;
-	out.score = score; out.ns = ns; out.gaps = readGaps + refGaps; out.edits = (int32_t)ned;
-	out.basesAligned = rows - trimEnd - (int32_t)ned;
-	int refns = 0;
-	for(int i = col; i <= origCol; i++) if(pb.rf[i] > 15) refns++;
-	out.refns = refns;
-	out.n_edits = (uint16_t)ned;
-	return true;
 }
 
 // left-end-based view of an edit list that may be stored 5'-based for a rc read
@@ -277,88 +98,270 @@ BT2_HD bool alns_overlap(const EditView& a, int64_t arefoff, const EditView& b, 
 	return false;
 }
 
-// Everything extendSeeds does with one filled DP problem.  Returns BT_ROUND_END with
-// rs.status set when the round is over, BT_CONTINUE when the element loop goes on.
-BT2_HD int after_fill(BtCtx& cx, const Pools& pools, ReadState& rs) {
-	const DevParams& P = *cx.P; const Problem& pb = *cx.prob;
-	const int32_t perfect = (int32_t)rs.rdlen * P.matchBonus;
-	rs.dpCells += (uint64_t)pb.rows * pb.cols;
-	const int32_t bestCell = pb.lrmax - 255;
-	const bool found = bestCell >= pb.minsc && pb.ncand > 0;
-	rs.nExDps++;
-	if(!found) {
-		rs.nExDpFails++; rs.nDpFail++;
-		if(rs.nDpFail >= (uint32_t)P.streak) { rs.status = BT2GPU_ST_SOFT_LIMIT; return BT_ROUND_END; }
-		if(bestCell > rs.bestLtMinsc) rs.bestLtMinsc = bestCell;
-		return BT_CONTINUE;
-	}
-	rs.nExDpSuccs++; rs.nDpLastSucc = rs.nExDps - 1;
-	if(rs.nDpFail > rs.nDpFailStreak) rs.nDpFailStreak = rs.nDpFail;
-	rs.nDpFail = 0;
-	uint32_t cural = 0;
-	const uint32_t ncand = pb.ncand;
-	const int lastRow = pb.rows - 1;
-	Rng rnd = rs.rnd;
-	int result = BT_CONTINUE;
-	while(true) {
-		if(cural == ncand) break;
-		// ---- SwAligner::nextAlignment
-		AlnRec a; bool got = false;
-		while(cural < ncand) {
-			const int col = pb.cand[cural] & 255;
-			{ const uint32_t m = cx.masks[(uint32_t)lastRow * pb.cols + col];
-			  if((m & ~0x1fffu) == (cx.gen << 13) && (m & 1u)) { cural++; continue; } } // start cell already reportedThrough
-			const uint32_t reseed = rnd.nextU32() + 1;
-			rnd.init(reseed);
-			got = backtrace(cx, rs, a, lastRow, col);
-			rnd.init(reseed + 1);
-			if(got) break;
-			cural++;
+struct BtMachine {
+	// ---- context of the current problem
+	const DevParams* P; const Pools* pools;
+	const Problem* pb;
+	const uint32_t* hef;   // skewed H|E<<8|F<<16 words of this problem
+	uint32_t* masks;       // diagonal-major tagged masks of this problem slot
+	BtFrame* stack;        // [BT2_BT_STACK]
+	uint32_t* scratch;     // per-read edit scratch
+	ReadView rv;
+	uint32_t gtag;         // generation << 13
+	ReadState rs;          // working copy of the read's state
+	// ---- nextAlignment state
+	int phase, result;
+	uint32_t cural, reseed;
+	// ---- backtrace state (one attempt)
+	int row, col, origCol, ct, score, ns, readGaps, refGaps;
+	uint32_t nstack, ned, hw;
+	bool coreHit;
+
+	BT2_HD uint32_t& MK(int r, int c) { return masks[(uint32_t)(c - r + (int)pb->rows - 1) * (uint32_t)pb->rows + (uint32_t)r]; }
+	BT2_HD uint32_t mask_get(int r, int c) { const uint32_t m = MK(r, c); return ((m & ~0x1fffu) == gtag) ? (m & 0x1fffu) : 0u; }
+	BT2_HD void push_edit(uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scratch[ned] = x; ned++; if(ned > hw) hw = ned; }
+
+	// SwDriver::extendSeeds right after swa.align(): counters, then either the candidate loop or done
+	BT2_HD void begin() {
+		const DevParams& Pr = *P;
+		rs.dpCells += (uint64_t)pb->rows * pb->cols;
+		const int32_t bestCell = pb->lrmax - 255;
+		const bool found = bestCell >= pb->minsc && pb->ncand > 0;
+		rs.nExDps++;
+		result = BT_CONTINUE;
+		if(!found) {
+			rs.nExDpFails++; rs.nDpFail++;
+			if(rs.nDpFail >= (uint32_t)Pr.streak) { rs.status = BT2GPU_ST_SOFT_LIMIT; result = BT_ROUND_END; }
+			else if(bestCell > rs.bestLtMinsc) rs.bestLtMinsc = bestCell;
+			phase = BP_DONE;
+			return;
 		}
-		if(!got) break;
+		rs.nExDpSuccs++; rs.nDpLastSucc = rs.nExDps - 1;
+		if(rs.nDpFail > rs.nDpFailStreak) rs.nDpFailStreak = rs.nDpFail;
+		rs.nDpFail = 0;
+		cural = 0;
+		phase = BP_CAND;
+	}
+
+	// SwAligner::nextAlignment: next candidate whose start cell has not been reported through
+	BT2_HD void cand() {
+		if(cural >= pb->ncand) { phase = BP_DONE; return; }
+		const int lastRow = pb->rows - 1;
+		const int c0 = pb->cand[cural] & 255;
+		if(mask_get(lastRow, c0) & 1u) { cural++; return; }
+		reseed = rs.rnd.nextU32() + 1;
+		rs.rnd.init(reseed);
+		row = lastRow; col = c0; origCol = c0; ct = CT_H;
+		score = 0; ns = 0; readGaps = 0; refGaps = 0; nstack = 0; ned = 0; hw = rs.scr_hw; coreHit = false;
+		rs.btAttempts++;
+		phase = BP_STEP;
+	}
+
+	BT2_HD void attempt_failed() { // backtrace returned false: scratch keeps what was written (res.reset() only drops the count)
+		rs.scr_cur = (uint16_t)ned; rs.scr_hw = (uint16_t)hw;
+		rs.rnd.init(reseed + 1);
 		cural++;
-		const uint32_t ne = a.n_edits;
-		if(!pb.fw) { // AlnRes::invertEdits: scratch becomes 5'-based
-			for(uint32_t i = 0; i < ne / 2; i++) { const uint32_t t = cx.scratch[i]; cx.scratch[i] = cx.scratch[ne - 1 - i]; cx.scratch[ne - 1 - i] = t; }
+		phase = BP_CAND;
+	}
+
+	// one cell of backtraceNucleotidesEnd2EndSseU8
+	BT2_HD void bt_step() {
+		const DevParams& Pr = *P; const Problem& p = *pb;
+		const int rows = p.rows; const uint32_t R = p.R;
+		const int rdgo = Pr.rdGapOpen, rdge = Pr.rdGapExt, rfgo = Pr.rfGapOpen, rfge = Pr.rfGapExt;
+		#define HEF(r, c) hef[hef_index((uint32_t)(r), (uint32_t)(c), R)]
+		#define HV(w) ((int)((w) & 255u) - 255)
+		#define EV(w) ((int)(((w) >> 8) & 255u) - 255)
+		#define FV(w) ((int)(((w) >> 16) & 255u) - 255)
+		rs.btSteps++;
+		const int readc = rv.rd(row), refm = p.rf[col], readq = rv.q(row);
+		bool empty = false, canMoveThru = true, branch = false;
+		int cur = MV_DIAG;
+		uint32_t m16 = mask_get(row, col);
+		if(m16 & 1u) {
+			canMoveThru = false;
+		} else if(row > 0) {
+			const bool gapsAllowed = !(row < Pr.gapbar || (rows - row - 1) < Pr.gapbar);
+			if(ct == CT_E) {
+				const uint32_t wc = HEF(row, col), wl = col > 0 ? HEF(row, col - 1) : 0u;
+				const int sc_cur = EV(wc);
+				int mask = 0;
+				if(HV(wl) - rdgo == sc_cur) mask |= 1;
+				if(EV(wl) - rdge == sc_cur) mask |= 2;
+				const int origMask = mask;
+				if(m16 & (1u << 7)) mask = (m16 >> 8) & 3;
+				if(mask == 3)      { cur = MV_READ_OPEN; m16 = (m16 & ~(7u << 7)) | (1u << 7) | (2u << 8); branch = true; }
+				else if(mask == 2) { cur = MV_RDGAP_EXT; m16 = (m16 & ~(7u << 7)) | (1u << 7); }
+				else if(mask == 1) { cur = MV_READ_OPEN; m16 = (m16 & ~(7u << 7)) | (1u << 7); }
+				else { empty = true; canMoveThru = (origMask == 0); }
+			} else if(ct == CT_F) {
+				const uint32_t wc = HEF(row, col), wu = HEF(row - 1, col);
+				const int sc_cur = FV(wc);
+				int mask = 0;
+				if(HV(wu) - rfgo == sc_cur) mask |= 1;
+				if(FV(wu) - rfge == sc_cur) mask |= 2;
+				const int origMask = mask;
+				if(m16 & (1u << 10)) mask = (m16 >> 11) & 3;
+				if(mask == 3)      { cur = MV_REF_OPEN;  m16 = (m16 & ~(7u << 10)) | (1u << 10) | (2u << 11); branch = true; }
+				else if(mask == 2) { cur = MV_RFGAP_EXT; m16 = (m16 & ~(7u << 10)) | (1u << 10); }
+				else if(mask == 1) { cur = MV_REF_OPEN;  m16 = (m16 & ~(7u << 10)) | (1u << 10); }
+				else { empty = true; canMoveThru = (origMask == 0); }
+			} else {
+				const uint32_t wc = HEF(row, col), wu = HEF(row - 1, col);
+				const bool hasLeft = col > 0;
+				const uint32_t wl = hasLeft ? HEF(row, col - 1) : 0xffffffu, wul = hasLeft ? HEF(row - 1, col - 1) : 0xffffffu;
+				const int sc_cur = HV(wc);
+				const int sc_diag = sc_score(Pr, readc, refm, readq - 33);
+				int mask = 0;
+				if(gapsAllowed) {
+					if(sc_cur == HV(wu) - rfgo) mask |= 1;
+					if(hasLeft && sc_cur == HV(wl) - rdgo) mask |= 2;
+					if(sc_cur == FV(wu) - rfge) mask |= 4;
+					if(hasLeft && sc_cur == EV(wl) - rdge) mask |= 8;
+				}
+				if(hasLeft && sc_cur == HV(wul) + sc_diag) mask |= 16;
+				const int origMask = mask;
+				if(m16 & (1u << 1)) mask = (m16 >> 2) & 31;
+				int select = -1;
+				const int opts = BT2_POPC((unsigned)mask);
+				if(opts == 1) {
+					select = BT2_CTZ((unsigned)mask);
+					m16 = (m16 & ~(31u << 1)) | (1u << 1);   // hMaskSet clears bits 1..5 only (aligner_swsse.h:362)
+				} else if(opts > 1) {
+					if(mask & 16) select = 4; else if(mask & 1) select = 0; else if(mask & 4) select = 2;
+					else if(mask & 2) select = 1; else select = 3;
+					mask &= ~(1 << select);
+					m16 = (m16 & ~(31u << 1)) | (1u << 1) | ((uint32_t)mask << 2);
+					branch = true;
+				}
+				if(select != -1) {
+					cur = select == 4 ? MV_DIAG : select == 0 ? MV_REF_OPEN : select == 1 ? MV_READ_OPEN : select == 2 ? MV_RFGAP_EXT : MV_RDGAP_EXT;
+				} else { empty = true; canMoveThru = (origMask == 0); }
+			}
+		}
+		#undef HEF
+		#undef HV
+		#undef EV
+		#undef FV
+		MK(row, col) = gtag | m16 | 1u;
+		if(!canMoveThru) {
+			if(nstack > 0) {
+				const BtFrame f = stack[--nstack];
+				ned = f.a & 1023u; row = (int)((f.a >> 10) & 255u); col = (int)((f.a >> 18) & 255u);
+				ct = (int)((f.a >> 26) & 3u); coreHit = ((f.a >> 28) & 1u) != 0;
+				readGaps = (int)(f.b & 1023u); refGaps = (int)((f.b >> 10) & 1023u); ns = (int)((f.b >> 20) & 1023u);
+				score = (int)f.c;
+				return; // retry the same cell with its remaining options
+			}
+			attempt_failed();
+			return;
+		}
+		// this cell joins the path: core-diagonal test (aligner_swsse_ee_u8.cpp:1229-1262) folded in
+		const int diag = col - row + p.triml;
+		const bool cellCore = diag >= 0 && diag >= p.corel && diag <= p.corer;
+		if(empty || row == 0) { coreHit = coreHit || cellCore; phase = BP_POST; return; }
+		if(branch && nstack < BT2_BT_STACK) {
+			BtFrame f;
+			f.a = (ned & 1023u) | ((uint32_t)row << 10) | ((uint32_t)col << 18) | ((uint32_t)ct << 26) | ((coreHit ? 1u : 0u) << 28);
+			f.b = ((uint32_t)readGaps & 1023u) | (((uint32_t)refGaps & 1023u) << 10) | (((uint32_t)ns & 1023u) << 20);
+			f.c = (uint32_t)score; f.d = 0;
+			stack[nstack++] = f;
+		}
+		coreHit = coreHit || cellCore;
+		if(cur == MV_DIAG) {
+			const int m = (readc > 3 || refm > 15) ? -1 : ((refm & (1 << readc)) ? 1 : 0);
+			ct = CT_H;
+			if(m != 1) {
+				push_edit(pack_edit((uint32_t)row, (uint32_t)mask_to_char(refm), (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_MM));
+				score -= sc_mm(Pr, readc, refm, readq - 33);
+			} else score += Pr.matchBonus;
+			if(m == -1) ns++;
+			row--; col--;
+		} else if(cur == MV_REF_OPEN || cur == MV_RFGAP_EXT) {
+			push_edit(pack_edit((uint32_t)row, '-', (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_REF_GAP));
+			row--;
+			ct = (cur == MV_REF_OPEN) ? CT_H : CT_F;
+			score -= (cur == MV_REF_OPEN) ? rfgo : rfge;
+			refGaps++;
+		} else {
+			push_edit(pack_edit((uint32_t)row + 1, (uint32_t)mask_to_char(refm), '-', BT2GPU_EDIT_READ_GAP));
+			col--;
+			ct = (cur == MV_READ_OPEN) ? CT_H : CT_E;
+			score -= (cur == MV_READ_OPEN) ? rdgo : rdge;
+			readGaps++;
+		}
+	}
+
+	// end of a backtrace that reached row 0 / an empty cell, then the rest of nextAlignment and of
+	// the extendSeeds body for one alignment: redundancy, report, policy, tighten
+	BT2_HD void post() {
+		const DevParams& Pr = *P; const Problem& p = *pb;
+		if(!coreHit) { attempt_failed(); return; }
+		{
+			const int readc = rv.rd(row), refm = p.rf[col];
+			const int m = (readc > 3 || refm > 15) ? -1 : ((refm & (1 << readc)) ? 1 : 0);
+			if(m != 1) {
+				push_edit(pack_edit((uint32_t)row, (uint32_t)mask_to_char(refm), (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_MM));
+				score -= sc_mm(Pr, readc, refm, rv.q(row) - 33);
+			} else score += Pr.matchBonus;
+			if(m == -1) ns++;
+		}
+		if(ns > rs.nceil || ned > BT2_SCRATCH_EDITS) { attempt_failed(); return; } // (> capacity: beyond the reference's own DList<Edit,160>)
+		const uint32_t ne = ned;
+		for(uint32_t i = 0; i < ne / 2; i++) { const uint32_t t = scratch[i]; scratch[i] = scratch[ne - 1 - i]; scratch[ne - 1 - i] = t; }
+		rs.scr_cur = (uint16_t)ned; rs.scr_hw = (uint16_t)hw;
+		rs.rnd.init(reseed + 1);
+		cural++;
+		phase = BP_CAND;
+		AlnRec a;
+		a.fw = p.fw; a.tidx = p.tidx; a.refoff = (int64_t)col + p.refl;
+		a.score = score; a.ns = ns; a.gaps = readGaps + refGaps; a.edits = (int32_t)ne;
+		a.basesAligned = (int32_t)p.rows - (int32_t)ne;   // trimEnd is 0: candidates come from the last row only
+		int refns = 0;
+		for(int i = col; i <= origCol; i++) if(p.rf[i] > 15) refns++;
+		a.refns = refns; a.n_edits = (uint16_t)ne;
+		if(!p.fw) { // AlnRes::invertEdits: scratch becomes 5'-based
+			for(uint32_t i = 0; i < ne / 2; i++) { const uint32_t t = scratch[i]; scratch[i] = scratch[ne - 1 - i]; scratch[ne - 1 - i] = t; }
 			for(uint32_t i = 0; i < ne; i++) {
-				const uint32_t x = cx.scratch[i];
-				cx.scratch[i] = edit_with_pos(x, (uint32_t)rs.rdlen - edit_pos(x) - (edit_type(x) == BT2GPU_EDIT_READ_GAP ? 0u : 1u));
+				const uint32_t x = scratch[i];
+				scratch[i] = edit_with_pos(x, (uint32_t)rs.rdlen - edit_pos(x) - (edit_type(x) == BT2GPU_EDIT_READ_GAP ? 0u : 1u));
 			}
 		}
 		// ---- RedundantAlns::overlap against every alignment already reported for this read
-		EditView nv; nv.e = cx.scratch; nv.n = ne; nv.inv = !pb.fw; nv.rdlen = rs.rdlen;
+		EditView nv; nv.e = scratch; nv.n = ne; nv.inv = !p.fw; nv.rdlen = rs.rdlen;
 		bool olap = false;
-		for(uint32_t p = rs.aln_tail; p != BT2_NIL && !olap; p = pools.alns[p].prev) {
-			const AlnRec& o = pools.alns[p];
+		for(uint32_t q = rs.aln_tail; q != BT2_NIL && !olap; q = pools->alns[q].prev) {
+			const AlnRec& o = pools->alns[q];
 			if(o.tidx != a.tidx || o.fw != a.fw) continue;
-			EditView ov; ov.e = pools.edits + o.edit_off; ov.n = o.n_edits; ov.inv = !o.fw; ov.rdlen = rs.rdlen;
+			EditView ov; ov.e = pools->edits + o.edit_off; ov.n = o.n_edits; ov.inv = !o.fw; ov.rdlen = rs.rdlen;
 			olap = alns_overlap(nv, a.refoff, ov, o.refoff, rs.rdlen);
 		}
-		if(olap) continue;
+		if(olap) return;
 		// ---- report
-		const uint32_t slot = atomic_bump(pools.aln_top, 1);
-		const uint32_t eoff = ne ? atomic_bump(pools.edit_top, ne) : 0;
-		if(slot >= pools.aln_cap) { set_error(pools, 4); rs.status = BT2GPU_ST_HARD_LIMIT; result = BT_ROUND_END; break; }
-		if(ne && eoff + ne > pools.edit_cap) { set_error(pools, 8); rs.status = BT2GPU_ST_HARD_LIMIT; result = BT_ROUND_END; break; }
-		for(uint32_t i = 0; i < ne; i++) pools.edits[eoff + i] = cx.scratch[i];
+		const uint32_t slot = atomic_bump(pools->aln_top, 1);
+		const uint32_t eoff = ne ? atomic_bump(pools->edit_top, ne) : 0;
+		if(slot >= pools->aln_cap) { set_error(*pools, 4); rs.status = BT2GPU_ST_HARD_LIMIT; result = BT_ROUND_END; phase = BP_DONE; return; }
+		if(ne && eoff + ne > pools->edit_cap) { set_error(*pools, 8); rs.status = BT2GPU_ST_HARD_LIMIT; result = BT_ROUND_END; phase = BP_DONE; return; }
+		for(uint32_t i = 0; i < ne; i++) pools->edits[eoff + i] = scratch[i];
 		a.edit_off = eoff; a.minsc = rs.minsc; a.prev = rs.aln_tail; a.pad = 0; a.pad2 = 0;
-		pools.alns[slot] = a;
+		pools->alns[slot] = a;
 		rs.aln_tail = slot; rs.n_alns++;
 		// ReportingState::foundUnpaired + best / second best
 		rs.nunpair++;
-		const bool mhitsSet = P.mhits != 0;
+		const bool mhitsSet = Pr.mhits != 0;
 		if(!rs.doneUnpair) {
-			if(rs.nunpair >= (uint32_t)P.khits && !mhitsSet) rs.doneUnpair = 1;
-			else if(mhitsSet && rs.nunpair > (uint32_t)P.mhits) rs.doneUnpair = 1;
+			if(rs.nunpair >= (uint32_t)Pr.khits && !mhitsSet) rs.doneUnpair = 1;
+			else if(mhitsSet && rs.nunpair > (uint32_t)Pr.mhits) rs.doneUnpair = 1;
 			if(rs.doneUnpair) rs.donePolicy = 1;
 		}
 		if(a.score > rs.best) { rs.best2 = rs.best; rs.best = a.score; } else if(a.score > rs.best2) rs.best2 = a.score;
-		if(rs.donePolicy) { rs.status = BT2GPU_ST_POLICY_FULFILLED; result = BT_ROUND_END; break; }
-		if(P.tighten > 0 && mhitsSet && rs.best2 != BT2_I32_MIN) {
+		if(rs.donePolicy) { rs.status = BT2GPU_ST_POLICY_FULFILLED; result = BT_ROUND_END; phase = BP_DONE; return; }
+		if(Pr.tighten > 0 && mhitsSet && rs.best2 != BT2_I32_MIN) {
+			const int32_t perfect = (int32_t)rs.rdlen * Pr.matchBonus;
 			const int32_t best = rs.best, sec = rs.best2;
-			if(P.tighten == 1) {
+			if(Pr.tighten == 1) {
 				if(best >= rs.minsc) { rs.minsc = best; if(rs.minsc < perfect && best == sec) rs.minsc++; }
-			} else if(P.tighten == 2) {
+			} else if(Pr.tighten == 2) {
 				if(sec >= rs.minsc) { rs.minsc = sec; if(rs.minsc < perfect) rs.minsc++; }
 			} else {
 				const int32_t diff = best - sec;
@@ -367,8 +370,14 @@ BT2_HD int after_fill(BtCtx& cx, const Pools& pools, ReadState& rs) {
 			}
 		}
 	}
-	rs.rnd = rnd;
-	return result;
-}
+
+	// one unit of work; returns false once the problem is finished (result / rs are final)
+	BT2_HD bool step() {
+		if(phase == BP_STEP) bt_step();
+		else if(phase == BP_CAND) cand();
+		else if(phase == BP_POST) post();
+		return phase != BP_DONE;
+	}
+};
 
 } // namespace bt2

@@ -316,8 +316,6 @@ BT2_HD uint32_t hef_index(uint32_t r, uint32_t c, uint32_t R) {
 	return (((c + v) << 6) + v) * RP + k;
 }
 #define BT2_HEF_WORDS ((BT2GPU_MAX_COLS + 64) * 64 * 4)      // per problem slot
-#define BT2_MASK_WORDS (BT2GPU_MAX_ROWS * BT2GPU_MAX_COLS)    // u16 per cell, per problem slot
-#define BT2_MASK_GENS 7                                       // 3-bit generation tag: memset every 7 launches
 
 // pools shared by the per-read kernels
 struct Pools {

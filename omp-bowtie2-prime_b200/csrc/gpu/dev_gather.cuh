@@ -10,9 +10,16 @@ BT2_HD void unpack_edit(uint32_t e, bt2gpu_edit& o) {
 	o.pos = edit_pos(e); o.chr = (uint8_t)edit_chr(e); o.qchr = (uint8_t)edit_qchr(e); o.type = (uint8_t)edit_type(e); o.pad = 0;
 }
 
+// The host only ever reads the scratch through an alignment's own edit count (the AlnRes copies keep
+// their count by value and alias the buffer), so the image is cut at the largest n_edits.
+BT2_HD uint32_t scratch_count(const ReadState& rs, const Pools& pools) {
+	uint32_t m = 0;
+	for(uint32_t p = rs.aln_tail; p != BT2_NIL; p = pools.alns[p].prev) if(pools.alns[p].n_edits > m) m = pools.alns[p].n_edits;
+	return m < rs.scr_hw ? m : rs.scr_hw;
+}
 // # of bt2gpu_edit entries this read contributes (its alignments' edits + the scratch image)
 BT2_HD uint32_t read_edit_count(const ReadState& rs, const Pools& pools) {
-	uint32_t n = rs.scr_hw;
+	uint32_t n = scratch_count(rs, pools);
 	for(uint32_t p = rs.aln_tail; p != BT2_NIL; p = pools.alns[p].prev) n += pools.alns[p].n_edits;
 	return n;
 }
@@ -45,8 +52,9 @@ BT2_HD void gather_read(const ReadState& rs, const Pools& pools, const uint32_t*
 		for(uint32_t i = 0; i < a.n_edits; i++) unpack_edit(pools.edits[a.edit_off + i], edits[end + i]);
 	}
 	eo = edit_base + tot;
-	rr.scratch_off = eo; rr.n_scratch = rs.scr_hw;
-	for(uint32_t i = 0; i < rs.scr_hw; i++) unpack_edit(scratch[i], edits[eo + i]);
+	const uint32_t ns = scratch_count(rs, pools);
+	rr.scratch_off = eo; rr.n_scratch = ns;
+	for(uint32_t i = 0; i < ns; i++) unpack_edit(scratch[i], edits[eo + i]);
 }
 
 } // namespace bt2

@@ -123,30 +123,40 @@ __global__ void k_step(const DevParams* __restrict__ Pp, const DevIndex ix, cons
 	states[read] = rs;
 }
 
-struct BtArrays { const uint32_t* hef; uint16_t* masks; uint32_t gen; BtFrame* stacks; uint32_t* scratch; const uint8_t* seq; const uint8_t* qual; };
+struct BtArrays { const uint32_t* hef; uint32_t* masks; uint32_t gen; BtFrame* stacks; uint32_t* scratch; const uint8_t* seq; const uint8_t* qual; };
 
-__global__ void k_bt(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const Problem* probs, uint32_t count,
-                     const BtArrays ba, uint32_t* next_list, uint32_t* next_cnt, uint32_t* roundend_list, uint32_t* roundend_cnt) {
-	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-	if(j >= count) return;
-	const Problem& pb = probs[j];
-	if(pb.read == BT2_NIL) return;
-	const uint32_t read = pb.read;
-	ReadState rs = states[read];
-	BtCtx cx;
-	cx.P = Pp; cx.prob = &pb;
-	cx.hef = ba.hef + (size_t)j * BT2_HEF_WORDS;
-	cx.masks = ba.masks + (size_t)j * BT2_MASK_WORDS; cx.gen = ba.gen;
-	cx.stack = ba.stacks + (size_t)j * BT2_BT_STACK;
-	cx.scratch = ba.scratch + (size_t)read * BT2_SCRATCH_EDITS;
-	cx.rv.seq = ba.seq + rs.seq_off; cx.rv.qual = ba.qual + rs.seq_off; cx.rv.rdlen = rs.rdlen; cx.rv.fw = pb.fw != 0;
-	if(after_fill(cx, pools, rs) == BT_ROUND_END) {
-		rs.phase = RS_ROUND_DONE;
-		list_append(roundend_list, roundend_cnt, read);
-	} else {
-		list_append(next_list, next_cnt, read);
+// Persistent threads: every lane runs BtMachine::step in one loop and pulls the next problem
+// from `task` when its own is finished, so a warp is busy until the chunk runs dry.
+__global__ void __launch_bounds__(128) k_bt(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const Problem* probs, uint32_t count,
+                     const BtArrays ba, uint32_t* task, uint32_t* next_list, uint32_t* next_cnt, uint32_t* roundend_list, uint32_t* roundend_cnt) {
+	BtMachine m;
+	m.P = Pp; m.pools = &pools; m.gtag = ba.gen << 13;
+	bool have = false;
+	uint32_t read = 0;
+	while(true) {
+		if(!have) {
+			const uint32_t j = atomicAdd(task, 1u);
+			if(j >= count) break;
+			const Problem& pb = probs[j];
+			if(pb.read == BT2_NIL) continue;
+			read = pb.read;
+			m.rs = states[read];
+			m.pb = &pb;
+			m.hef = ba.hef + (size_t)j * BT2_HEF_WORDS;
+			m.masks = ba.masks + (size_t)j * BT2_MASK_WORDS;
+			m.stack = ba.stacks + (size_t)j * BT2_BT_STACK;
+			m.scratch = ba.scratch + (size_t)read * BT2_SCRATCH_EDITS;
+			m.rv.seq = ba.seq + m.rs.seq_off; m.rv.qual = ba.qual + m.rs.seq_off; m.rv.rdlen = m.rs.rdlen; m.rv.fw = pb.fw != 0;
+			m.begin();
+			have = true;
+		}
+		if(m.phase == BP_DONE || !m.step()) {
+			if(m.result == BT_ROUND_END) { m.rs.phase = RS_ROUND_DONE; list_append(roundend_list, roundend_cnt, read); }
+			else list_append(next_list, next_cnt, read);
+			states[read] = m.rs;
+			have = false;
+		}
 	}
-	states[read] = rs;
 }
 
 // reads whose round is over: another seed round, or finished

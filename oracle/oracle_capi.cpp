@@ -77,8 +77,11 @@ int oracle_align_batch(oracle_ctx* c, const bt2gpu_reads* in, bt2gpu_results* ou
 			for(size_t e = 0; e < a.ned.size(); e++) { bt2gpu_edit pe; pack_edit(a.ned[e], pe); st.edits.push_back(pe); }
 			st.alns.push_back(o);
 		}
-		rr.scratch_off = (uint32_t)st.edits.size(); rr.n_scratch = (uint32_t)r.scratch.hw;
-		for(size_t e = 0; e < r.scratch.hw; e++) { bt2gpu_edit pe; pack_edit(r.scratch.buf[e], pe); st.edits.push_back(pe); }
+		size_t nscr = 0; // the image is cut at the largest edit count any alignment reads it through
+		for(size_t k = 0; k < r.alns.size(); k++) nscr = std::max(nscr, r.alns[k].ned.size());
+		nscr = std::min(nscr, r.scratch.hw);
+		rr.scratch_off = (uint32_t)st.edits.size(); rr.n_scratch = (uint32_t)nscr;
+		for(size_t e = 0; e < nscr; e++) { bt2gpu_edit pe; pack_edit(r.scratch.buf[e], pe); st.edits.push_back(pe); }
 	}
 	out->n = n; out->reads = st.reads.data(); out->alns = st.alns.data(); out->n_alns = st.alns.size();
 	out->edits = st.edits.data(); out->n_edits = st.edits.size();

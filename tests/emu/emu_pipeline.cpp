@@ -94,7 +94,7 @@ int main(int argc, char** argv) {
 	const uint32_t MI = BT2GPU_MAX_ITER + 8;
 	std::vector<uint16_t> ov_rng(2 * MI), ov_pos(2 * MI), ov_val(2 * MI), seen_rng(MI), seen_val(MI), conv_val(MI), r_n(W), r_cur(W), r_thresh(W), r_conv_n(W), r_nseen(W);
 	std::vector<uint8_t> r_flags(W), elim(W); std::vector<uint32_t> r_conv_off(W); std::vector<double> mass(W);
-	std::vector<uint32_t> hef(BT2_HEF_WORDS); std::vector<uint16_t> masks(BT2_MASK_WORDS, 0); uint32_t gen = 0; std::vector<BtFrame> stack(BT2_BT_STACK);
+	std::vector<uint32_t> hef(BT2_HEF_WORDS); std::vector<uint32_t> masks(BT2_MASK_WORDS, 0); uint32_t gen = 0; std::vector<BtFrame> stack(BT2_BT_STACK);
 	orc::WorkCounters wc;
 	for(uint32_t ri = 0; ri < n; ri++) {
 		ReadState& rs = states[ri];
@@ -141,11 +141,16 @@ int main(int argc, char** argv) {
 			while(true) {
 				Problem pb; pb.read = ri;
 				if(advance(P, ix, rf, pools, rs, pb) == ADV_ROUND_END) break;
-				BtCtx cx; cx.P = &P; cx.prob = &pb; cx.hef = hef.data(); cx.masks = masks.data(); cx.stack = stack.data(); if(++gen > BT2_MASK_GENS) { std::fill(masks.begin(), masks.end(), (uint16_t)0); gen = 1; } cx.gen = gen;
-				cx.scratch = scratch.data() + (size_t)ri * BT2_SCRATCH_EDITS;
-				cx.rv.seq = in->seq + so; cx.rv.qual = in->qual + so; cx.rv.rdlen = rdlen; cx.rv.fw = pb.fw != 0;
-				fill_emu(P, pb, cx.rv, hef.data());
-				if(after_fill(cx, pools, rs) == BT_ROUND_END) break;
+				BtMachine m; m.P = &P; m.pools = &pools; m.pb = &pb; m.hef = hef.data(); m.masks = masks.data(); m.stack = stack.data();
+				if(++gen > BT2_MASK_GEN_MAX) { std::fill(masks.begin(), masks.end(), 0u); gen = 1; }
+				m.gtag = gen << 13;
+				m.scratch = scratch.data() + (size_t)ri * BT2_SCRATCH_EDITS;
+				m.rv.seq = in->seq + so; m.rv.qual = in->qual + so; m.rv.rdlen = rdlen; m.rv.fw = pb.fw != 0;
+				fill_emu(P, pb, m.rv, hef.data());
+				m.rs = rs; m.begin();
+				while(m.phase != BP_DONE && m.step()) { }
+				rs = m.rs;
+				if(m.result == BT_ROUND_END) break;
 			}
 			if(!next_round_wanted(P, rs)) break;
 		}
