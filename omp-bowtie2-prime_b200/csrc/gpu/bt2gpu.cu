@@ -27,7 +27,7 @@ using namespace bt2;
 	throw std::string(b_); } } while(0)
 
 enum { PH_SEED = 0, PH_GLUE, PH_RESOLVE, PH_FILL, PH_BT, PH_H2D, PH_D2H, PH_RUN, PH_N };
-enum { C_CAND0 = 0, C_CAND1, C_ACTIVE, C_EXT0, C_EXT1, C_ROUNDEND, C_SAMP, C_SEEDTASK, C_BTTASK, C_N = 16 };
+enum { C_CAND0 = 0, C_CAND1, C_ACTIVE, C_EXT0, C_EXT1, C_ROUNDEND, C_SAMP, C_SEEDTASK, C_BTTASK, C_SEEDNT, C_N = 16 };
 
 struct DBuf { // growable device buffer
 	void* p = nullptr; size_t cap = 0;
@@ -67,7 +67,7 @@ struct bt2gpu_ctx {
 	DBuf probs, hef, masks, stacks;
 	// per-batch arrays
 	DBuf seq, qual, seq_off, rng_seed, minsc, nceil, interval;
-	DBuf states, scratch, hits, lists[7], counters, stats;
+	DBuf states, scratch, hits, seedtasks, lists[7], counters, stats;
 	DBuf p_sav, p_sorted, p_rank, p_sp2, p_exr, p_exrfw, p_nsp, p_nsmall, p_nexr, p_nelt, p_nadd;
 	DBuf s_ovr, s_ovp, s_ovv, s_sr, s_sv, s_cv, s_rn, s_rcur, s_rth, s_rfl, s_rco, s_rcn, s_rns, s_mass, s_elim;
 	DBuf chunks, sats, alnp, editp, pooltops, poolerr;
@@ -147,7 +147,7 @@ void ensure_batch(bt2gpu_ctx* c, uint32_t n, uint64_t nbases, uint32_t maxOffs) 
 	c->seq_off.ensure(nn * 4); c->rng_seed.ensure(nn * 4); c->minsc.ensure(nn * 4); c->nceil.ensure(nn * 4); c->interval.ensure(nn * 4);
 	c->states.ensure(nn * sizeof(ReadState));
 	c->scratch.ensure(nn * BT2_SCRATCH_EDITS * 4);
-	c->hits.ensure(nn * W * sizeof(SeedHit));
+	c->hits.ensure(nn * W * sizeof(SeedHit)); c->seedtasks.ensure(nn * W * sizeof(SeedTask));
 	for(int i = 0; i < 7; i++) c->lists[i].ensure(nn * 4);
 	c->p_sav.ensure(nn * W * 2); c->p_sorted.ensure(nn * W); c->p_rank.ensure(nn * W * 2); c->p_sp2.ensure(nn * W * 2);
 	c->p_exr.ensure(nn * W * sizeof(ExRange16)); c->p_exrfw.ensure(nn * W);
@@ -259,17 +259,20 @@ void do_run(bt2gpu_ctx* c) {
 	int cand = 0;
 	for(uint32_t round = 0; ncand > 0; round++) {
 		zero_counter(c, C_ACTIVE); zero_counter(c, C_EXT0); zero_counter(c, C_EXT1); zero_counter(c, C_ROUNDEND);
-		zero_counter(c, C_SAMP); zero_counter(c, C_SEEDTASK); zero_counter(c, cand ? C_CAND0 : C_CAND1);
+		zero_counter(c, C_SAMP); zero_counter(c, C_SEEDTASK); zero_counter(c, C_SEEDNT); zero_counter(c, cand ? C_CAND0 : C_CAND1);
 		k_round_select<<<nblk(ncand, 256), 256, 0, st>>>(c->dP, states, L[cand], ncand, round, L[2], cnt + C_ACTIVE); LAUNCH(c);
 		const uint32_t nactive = read_counters(c)[C_ACTIVE];
 		if(nactive == 0) break;
 		{
 			Phase ph(c, PH_SEED);
 			SeedKernelArgs sk; sk.active = L[2]; sk.nactive = nactive; sk.W = W; sk.maxOffs = maxOffs; sk.states = states; sk.seq = ba.seq;
-			sk.hits = c->hits.as<SeedHit>(); sk.counter = cnt + C_SEEDTASK; sk.stats = stats;
-			const uint64_t ntasks = (uint64_t)nactive * W;
-			const uint32_t blocks = (uint32_t)std::min<uint64_t>((uint64_t)seedBlocks, (ntasks + 31) / 32);
-			k_seed<0><<<blocks, 256, 0, st>>>(c->ix, c->dP, sk); LAUNCH(c); c->ctr.n_seed++;
+			sk.hits = c->hits.as<SeedHit>(); sk.tasks = c->seedtasks.as<SeedTask>(); sk.ntasks = cnt + C_SEEDNT; sk.counter = cnt + C_SEEDTASK; sk.stats = stats;
+			const uint64_t nslots = (uint64_t)nactive * W;
+			k_seed_init<<<(uint32_t)((nslots + 255) / 256), 256, 0, st>>>(c->ix, c->dP, sk); LAUNCH(c);
+			const uint32_t blocks = (uint32_t)std::min<uint64_t>((uint64_t)seedBlocks, (nslots + 31) / 32);
+			if(c->ix.len < 0xfffffff0ull) k_seed_walk<uint32_t><<<blocks, 256, 0, st>>>(c->ix, c->dP, sk);
+			else k_seed_walk<uint64_t><<<blocks, 256, 0, st>>>(c->ix, c->dP, sk);
+			LAUNCH(c); c->ctr.n_seed++;
 		}
 		uint32_t ncur, nsamp;
 		{
@@ -523,7 +526,7 @@ void bt2gpu_destroy(bt2gpu_ctx* c) {
 	for(void* p : c->resident) cudaFree(p);
 	if(c->dP) cudaFree(c->dP);
 	DBuf* all[] = { &c->probs, &c->hef, &c->masks, &c->stacks, &c->seq, &c->qual, &c->seq_off, &c->rng_seed, &c->minsc, &c->nceil, &c->interval,
-		&c->states, &c->scratch, &c->hits, &c->lists[0], &c->lists[1], &c->lists[2], &c->lists[3], &c->lists[4], &c->lists[5], &c->lists[6], &c->counters, &c->stats,
+		&c->states, &c->scratch, &c->hits, &c->seedtasks, &c->lists[0], &c->lists[1], &c->lists[2], &c->lists[3], &c->lists[4], &c->lists[5], &c->lists[6], &c->counters, &c->stats,
 		&c->p_sav, &c->p_sorted, &c->p_rank, &c->p_sp2, &c->p_exr, &c->p_exrfw, &c->p_nsp, &c->p_nsmall, &c->p_nexr, &c->p_nelt, &c->p_nadd,
 		&c->s_ovr, &c->s_ovp, &c->s_ovv, &c->s_sr, &c->s_sv, &c->s_cv, &c->s_rn, &c->s_rcur, &c->s_rth, &c->s_rfl, &c->s_rco, &c->s_rcn, &c->s_rns, &c->s_mass, &c->s_elim,
 		&c->chunks, &c->sats, &c->alnp, &c->editp, &c->pooltops, &c->poolerr, &c->nal, &c->ned, &c->albase, &c->edbase, &c->cubtmp, &c->o_rr, &c->o_alns, &c->o_edits };
