@@ -276,12 +276,14 @@ int bt2gpu_abi_version(void);
  * seq_off[i] (already oriented: the strand buffer the fill sees), cols[i] reference
  * columns whose masks (1<<base, N=16; cols[i]+1 entries) start at rf + rf_off[i], and
  * minsc[i].  Outputs, per problem: dense raw-u8 H/E/F matrices (row-major rows x cols)
- * at hef_off[i] in H/E/F, the sorted candidate list ((rawH<<8)|col) at cand + 256*i,
- * ncand[i] and lrmax[i]. */
+ * at hef_off[i] in H/E/F (kept by a debug instantiation of the kernel only), the byte of
+ * backtrace comparison flags the production kernel stores per cell in `flags` (same
+ * indexing; bit meanings: DESIGN.md "cell flags"), the sorted candidate list
+ * ((rawH<<8)|col) at cand + 256*i, ncand[i] and lrmax[i].  nprob <= 4096. */
 int bt2gpu_test_fill(bt2gpu_ctx *ctx, uint32_t nprob, const uint32_t *seq_off, const uint8_t *seq,
                      const uint8_t *qual, const uint16_t *rows, const uint16_t *cols,
                      const uint32_t *rf_off, const uint8_t *rf, const int32_t *minsc,
-                     const uint64_t *hef_off, uint8_t *H, uint8_t *E, uint8_t *F,
+                     const uint64_t *hef_off, uint8_t *H, uint8_t *E, uint8_t *F, uint8_t *flags,
                      uint16_t *cand, uint32_t *ncand, int32_t *lrmax);
 
 #ifdef __cplusplus

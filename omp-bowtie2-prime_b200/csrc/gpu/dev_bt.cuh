@@ -102,92 +102,110 @@ struct BtMachine {
 	// ---- context of the current problem
 	const DevParams* P; const Pools* pools;
 	const Problem* pb;
-	const uint32_t* hef;   // skewed H|E<<8|F<<16 words of this problem
+	const uint8_t* cells;  // CF_* flag bytes of this problem (cell_index)
 	uint32_t* masks;       // diagonal-major tagged masks of this problem slot
 	BtFrame* stack;        // [BT2_BT_STACK]
 	uint32_t* scratch;     // per-read edit scratch
-	ReadView rv;
+	const uint8_t* seqbase; const uint8_t* qualbase; // batch arrays
+	ReadState* rs;         // the read's state, updated in place
 	uint32_t gtag;         // generation << 13
-	ReadState rs;          // working copy of the read's state
+	// ---- cached per problem
+	int rows, R, glo, ghi, dlo, dhi; // gaps allowed in rows [glo,ghi); core diagonals: dlo <= col-row <= dhi
 	// ---- nextAlignment state
 	int phase, result;
 	uint32_t cural, reseed;
 	// ---- backtrace state (one attempt)
-	int row, col, origCol, ct, score, ns, readGaps, refGaps;
-	uint32_t nstack, ned, hw;
+	int row, col, origCol, ct, score, ns, readGaps, refGaps, kk; // kk = row % R
+	uint32_t cidx, midx;   // cell_index(row,col), mask index of (row,col)
+	uint32_t nstack, ned, hw, fl, nsteps;
 	bool coreHit;
 
-	BT2_HD uint32_t& MK(int r, int c) { return masks[(uint32_t)(c - r + (int)pb->rows - 1) * (uint32_t)pb->rows + (uint32_t)r]; }
-	BT2_HD uint32_t mask_get(int r, int c) { const uint32_t m = MK(r, c); return ((m & ~0x1fffu) == gtag) ? (m & 0x1fffu) : 0u; }
+	BT2_HD ReadView view() const { ReadView v; v.seq = seqbase + rs->seq_off; v.qual = qualbase + rs->seq_off; v.rdlen = rs->rdlen; v.fw = pb->fw != 0; return v; }
+	BT2_HD uint32_t mask_index(int r, int c) const { return (uint32_t)(c - r + rows - 1) * (uint32_t)rows + (uint32_t)r; }
+	BT2_HD uint32_t mask_at(uint32_t idx) const { const uint32_t m = masks[idx]; return ((m & ~0x1fffu) == gtag) ? (m & 0x1fffu) : 0u; }
+	BT2_HD void locate() { // (row, col) changed arbitrarily: recompute the running indices
+		const uint32_t v = (R == 1) ? (uint32_t)row : (R == 2 ? ((uint32_t)row >> 1) : ((uint32_t)row / 3u));
+		kk = row - (int)v * R;
+		cidx = (uint32_t)col * 256u + v * 260u + (uint32_t)kk;
+		midx = mask_index(row, col);
+	}
+	BT2_HD void row_dec() { row--; midx += (uint32_t)rows - 1u; if(kk > 0) { kk--; cidx--; } else { kk = R - 1; cidx -= 260u - (uint32_t)kk; } }
+	BT2_HD void col_dec() { col--; midx -= (uint32_t)rows; cidx -= 256u; }
 	BT2_HD void push_edit(uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scratch[ned] = x; ned++; if(ned > hw) hw = ned; }
 
 	// SwDriver::extendSeeds right after swa.align(): counters, then either the candidate loop or done
 	BT2_HD void begin() {
 		const DevParams& Pr = *P;
-		rs.dpCells += (uint64_t)pb->rows * pb->cols;
+		rows = pb->rows; R = pb->R;
+		glo = Pr.gapbar; ghi = rows - Pr.gapbar;
+		dlo = (pb->corel > 0 ? pb->corel : 0) - pb->triml; dhi = pb->corer - pb->triml;
+		nsteps = 0;
+		rs->dpCells += (uint64_t)pb->rows * pb->cols;
 		const int32_t bestCell = pb->lrmax - 255;
 		const bool found = bestCell >= pb->minsc && pb->ncand > 0;
-		rs.nExDps++;
+		rs->nExDps++;
 		result = BT_CONTINUE;
 		if(!found) {
-			rs.nExDpFails++; rs.nDpFail++;
-			if(rs.nDpFail >= (uint32_t)Pr.streak) { rs.status = BT2GPU_ST_SOFT_LIMIT; result = BT_ROUND_END; }
-			else if(bestCell > rs.bestLtMinsc) rs.bestLtMinsc = bestCell;
+			rs->nExDpFails++; rs->nDpFail++;
+			if(rs->nDpFail >= (uint32_t)Pr.streak) { rs->status = BT2GPU_ST_SOFT_LIMIT; result = BT_ROUND_END; }
+			else if(bestCell > rs->bestLtMinsc) rs->bestLtMinsc = bestCell;
 			phase = BP_DONE;
 			return;
 		}
-		rs.nExDpSuccs++; rs.nDpLastSucc = rs.nExDps - 1;
-		if(rs.nDpFail > rs.nDpFailStreak) rs.nDpFailStreak = rs.nDpFail;
-		rs.nDpFail = 0;
+		rs->nExDpSuccs++; rs->nDpLastSucc = rs->nExDps - 1;
+		if(rs->nDpFail > rs->nDpFailStreak) rs->nDpFailStreak = rs->nDpFail;
+		rs->nDpFail = 0;
 		cural = 0;
 		phase = BP_CAND;
 	}
+	BT2_HD void finish() { rs->btSteps += nsteps; }
 
 	// SwAligner::nextAlignment: next candidate whose start cell has not been reported through
 	BT2_HD void cand() {
 		if(cural >= pb->ncand) { phase = BP_DONE; return; }
-		const int lastRow = pb->rows - 1;
+		const int lastRow = rows - 1;
 		const int c0 = pb->cand[cural] & 255;
-		if(mask_get(lastRow, c0) & 1u) { cural++; return; }
-		reseed = rs.rnd.nextU32() + 1;
-		rs.rnd.init(reseed);
+		if(mask_at(mask_index(lastRow, c0)) & 1u) { cural++; return; }
+		Rng rnd = rs->rnd;
+		reseed = rnd.nextU32() + 1;
+		rnd.init(reseed);
+		rs->rnd = rnd;
 		row = lastRow; col = c0; origCol = c0; ct = CT_H;
-		score = 0; ns = 0; readGaps = 0; refGaps = 0; nstack = 0; ned = 0; hw = rs.scr_hw; coreHit = false;
-		rs.btAttempts++;
+		locate();
+		score = 0; ns = 0; readGaps = 0; refGaps = 0; nstack = 0; ned = 0; hw = rs->scr_hw; coreHit = false;
+		rs->btAttempts++;
 		phase = BP_STEP;
 	}
 
 	BT2_HD void attempt_failed() { // backtrace returned false: scratch keeps what was written (res.reset() only drops the count)
-		rs.scr_cur = (uint16_t)ned; rs.scr_hw = (uint16_t)hw;
-		rs.rnd.init(reseed + 1);
+		rs->scr_cur = (uint16_t)ned; rs->scr_hw = (uint16_t)hw;
+		rs->rnd.init(reseed + 1);
 		cural++;
 		phase = BP_CAND;
 	}
 
+	// the diagonal move / the last cell of a path: mismatch edit, N count, score
+	BT2_HD void take_cell() {
+		if(fl & CF_MM) return;    // (fl holds the equalities that are TRUE: bit set = match; matchBonus is 0 end-to-end)
+		const ReadView rv = view();
+		const int readc = rv.rd((uint32_t)row), refm = pb->rf[col];
+		push_edit(pack_edit((uint32_t)row, (uint32_t)mask_to_char(refm), (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_MM));
+		score -= sc_mm(*P, readc, refm, rv.q((uint32_t)row) - 33);
+		if(readc > 3 || refm > 15) ns++;
+	}
+
 	// one cell of backtraceNucleotidesEnd2EndSseU8
 	BT2_HD void bt_step() {
-		const DevParams& Pr = *P; const Problem& p = *pb;
-		const int rows = p.rows; const uint32_t R = p.R;
-		const int rdgo = Pr.rdGapOpen, rdge = Pr.rdGapExt, rfgo = Pr.rfGapOpen, rfge = Pr.rfGapExt;
-		#define HEF(r, c) hef[hef_index((uint32_t)(r), (uint32_t)(c), R)]
-		#define HV(w) ((int)((w) & 255u) - 255)
-		#define EV(w) ((int)(((w) >> 8) & 255u) - 255)
-		#define FV(w) ((int)(((w) >> 16) & 255u) - 255)
-		rs.btSteps++;
-		const int readc = rv.rd(row), refm = p.rf[col], readq = rv.q(row);
+		nsteps++;
+		fl = ~(uint32_t)cells[cidx];
 		bool empty = false, canMoveThru = true, branch = false;
 		int cur = MV_DIAG;
-		uint32_t m16 = mask_get(row, col);
+		uint32_t m16 = mask_at(midx);
 		if(m16 & 1u) {
 			canMoveThru = false;
 		} else if(row > 0) {
-			const bool gapsAllowed = !(row < Pr.gapbar || (rows - row - 1) < Pr.gapbar);
 			if(ct == CT_E) {
-				const uint32_t wc = HEF(row, col), wl = col > 0 ? HEF(row, col - 1) : 0u;
-				const int sc_cur = EV(wc);
-				int mask = 0;
-				if(HV(wl) - rdgo == sc_cur) mask |= 1;
-				if(EV(wl) - rdge == sc_cur) mask |= 2;
+				int mask = col > 0 ? (int)((fl >> 3) & 3u) : 0;
 				const int origMask = mask;
 				if(m16 & (1u << 7)) mask = (m16 >> 8) & 3;
 				if(mask == 3)      { cur = MV_READ_OPEN; m16 = (m16 & ~(7u << 7)) | (1u << 7) | (2u << 8); branch = true; }
@@ -195,11 +213,7 @@ struct BtMachine {
 				else if(mask == 1) { cur = MV_READ_OPEN; m16 = (m16 & ~(7u << 7)) | (1u << 7); }
 				else { empty = true; canMoveThru = (origMask == 0); }
 			} else if(ct == CT_F) {
-				const uint32_t wc = HEF(row, col), wu = HEF(row - 1, col);
-				const int sc_cur = FV(wc);
-				int mask = 0;
-				if(HV(wu) - rfgo == sc_cur) mask |= 1;
-				if(FV(wu) - rfge == sc_cur) mask |= 2;
+				int mask = (int)((fl >> 5) & 3u);
 				const int origMask = mask;
 				if(m16 & (1u << 10)) mask = (m16 >> 11) & 3;
 				if(mask == 3)      { cur = MV_REF_OPEN;  m16 = (m16 & ~(7u << 10)) | (1u << 10) | (2u << 11); branch = true; }
@@ -207,19 +221,13 @@ struct BtMachine {
 				else if(mask == 1) { cur = MV_REF_OPEN;  m16 = (m16 & ~(7u << 10)) | (1u << 10); }
 				else { empty = true; canMoveThru = (origMask == 0); }
 			} else {
-				const uint32_t wc = HEF(row, col), wu = HEF(row - 1, col);
 				const bool hasLeft = col > 0;
-				const uint32_t wl = hasLeft ? HEF(row, col - 1) : 0xffffffu, wul = hasLeft ? HEF(row - 1, col - 1) : 0xffffffu;
-				const int sc_cur = HV(wc);
-				const int sc_diag = sc_score(Pr, readc, refm, readq - 33);
 				int mask = 0;
-				if(gapsAllowed) {
-					if(sc_cur == HV(wu) - rfgo) mask |= 1;
-					if(hasLeft && sc_cur == HV(wl) - rdgo) mask |= 2;
-					if(sc_cur == FV(wu) - rfge) mask |= 4;
-					if(hasLeft && sc_cur == EV(wl) - rdge) mask |= 8;
+				if(row >= glo && row < ghi) { // gaps allowed in this row
+					if(fl & CF_HF) mask |= (int)(((fl >> 5) & 1u) | (((fl >> 6) & 1u) << 2));             // H_up - rfgo (1), F_up - rfge (4)
+					if(hasLeft && (fl & CF_HE)) mask |= (int)((((fl >> 3) & 1u) << 1) | (((fl >> 4) & 1u) << 3)); // H_left - rdgo (2), E_left - rdge (8)
 				}
-				if(hasLeft && sc_cur == HV(wul) + sc_diag) mask |= 16;
+				if(hasLeft && (fl & CF_D)) mask |= 16;
 				const int origMask = mask;
 				if(m16 & (1u << 1)) mask = (m16 >> 2) & 31;
 				int select = -1;
@@ -239,11 +247,7 @@ struct BtMachine {
 				} else { empty = true; canMoveThru = (origMask == 0); }
 			}
 		}
-		#undef HEF
-		#undef HV
-		#undef EV
-		#undef FV
-		MK(row, col) = gtag | m16 | 1u;
+		masks[midx] = gtag | m16 | 1u;
 		if(!canMoveThru) {
 			if(nstack > 0) {
 				const BtFrame f = stack[--nstack];
@@ -251,14 +255,15 @@ struct BtMachine {
 				ct = (int)((f.a >> 26) & 3u); coreHit = ((f.a >> 28) & 1u) != 0;
 				readGaps = (int)(f.b & 1023u); refGaps = (int)((f.b >> 10) & 1023u); ns = (int)((f.b >> 20) & 1023u);
 				score = (int)f.c;
+				locate();
 				return; // retry the same cell with its remaining options
 			}
 			attempt_failed();
 			return;
 		}
 		// this cell joins the path: core-diagonal test (aligner_swsse_ee_u8.cpp:1229-1262) folded in
-		const int diag = col - row + p.triml;
-		const bool cellCore = diag >= 0 && diag >= p.corel && diag <= p.corer;
+		const int dg = col - row;
+		const bool cellCore = dg >= dlo && dg <= dhi;
 		if(empty || row == 0) { coreHit = coreHit || cellCore; phase = BP_POST; return; }
 		if(branch && nstack < BT2_BT_STACK) {
 			BtFrame f;
@@ -269,25 +274,22 @@ struct BtMachine {
 		}
 		coreHit = coreHit || cellCore;
 		if(cur == MV_DIAG) {
-			const int m = (readc > 3 || refm > 15) ? -1 : ((refm & (1 << readc)) ? 1 : 0);
 			ct = CT_H;
-			if(m != 1) {
-				push_edit(pack_edit((uint32_t)row, (uint32_t)mask_to_char(refm), (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_MM));
-				score -= sc_mm(Pr, readc, refm, readq - 33);
-			} else score += Pr.matchBonus;
-			if(m == -1) ns++;
-			row--; col--;
+			take_cell();
+			row_dec(); col_dec();
 		} else if(cur == MV_REF_OPEN || cur == MV_RFGAP_EXT) {
+			const int readc = view().rd((uint32_t)row);
 			push_edit(pack_edit((uint32_t)row, '-', (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_REF_GAP));
-			row--;
+			row_dec();
 			ct = (cur == MV_REF_OPEN) ? CT_H : CT_F;
-			score -= (cur == MV_REF_OPEN) ? rfgo : rfge;
+			score -= (cur == MV_REF_OPEN) ? P->rfGapOpen : P->rfGapExt;
 			refGaps++;
 		} else {
+			const int refm = pb->rf[col];
 			push_edit(pack_edit((uint32_t)row + 1, (uint32_t)mask_to_char(refm), '-', BT2GPU_EDIT_READ_GAP));
-			col--;
+			col_dec();
 			ct = (cur == MV_READ_OPEN) ? CT_H : CT_E;
-			score -= (cur == MV_READ_OPEN) ? rdgo : rdge;
+			score -= (cur == MV_READ_OPEN) ? P->rdGapOpen : P->rdGapExt;
 			readGaps++;
 		}
 	}
@@ -297,15 +299,8 @@ struct BtMachine {
 	BT2_HD void post() {
 		const DevParams& Pr = *P; const Problem& p = *pb;
 		if(!coreHit) { attempt_failed(); return; }
-		{
-			const int readc = rv.rd(row), refm = p.rf[col];
-			const int m = (readc > 3 || refm > 15) ? -1 : ((refm & (1 << readc)) ? 1 : 0);
-			if(m != 1) {
-				push_edit(pack_edit((uint32_t)row, (uint32_t)mask_to_char(refm), (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_MM));
-				score -= sc_mm(Pr, readc, refm, rv.q(row) - 33);
-			} else score += Pr.matchBonus;
-			if(m == -1) ns++;
-		}
+		take_cell();
+		ReadState& rs = *this->rs;
 		if(ns > rs.nceil || ned > BT2_SCRATCH_EDITS) { attempt_failed(); return; } // (> capacity: beyond the reference's own DList<Edit,160>)
 		const uint32_t ne = ned;
 		for(uint32_t i = 0; i < ne / 2; i++) { const uint32_t t = scratch[i]; scratch[i] = scratch[ne - 1 - i]; scratch[ne - 1 - i] = t; }

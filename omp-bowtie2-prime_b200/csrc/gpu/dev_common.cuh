@@ -305,17 +305,32 @@ struct Problem {
 	uint8_t  rf[BT2GPU_MAX_COLS + 8];   // reference masks for columns 0..cols (cols+1 fetched)
 };
 
-// skewed H/E/F store: word index of cell (r,c); each word = H | E<<8 | F<<16 (raw u8 values).
-// Layout [col+strip][strip][k] with the R (padded to RP) rows of a strip adjacent: one fill store
-// instruction writes one contiguous run of 32 x RP words, and the backtrace finds (r,c) and (r-1,c)
-// in the same 16-byte chunk two times out of three.
-BT2_HD uint32_t hef_index(uint32_t r, uint32_t c, uint32_t R) {
+// What the fill leaves per DP cell for the backtrace: one byte of "not equal" flags, i.e. the
+// outcome of every score comparison backtraceNucleotidesEnd2EndSseU8 makes at that cell
+// (aligner_swsse_ee_u8.cpp:820-1100), evaluated while H/E/F and their neighbours are in registers.
+// A flag bit is 0 when the equality holds.
+//   CF_D   H(r,c) == H(r-1,c-1) + sc(r,c)         CF_HE  H(r,c) == E(r,c)     CF_HF  H(r,c) == F(r,c)
+//   CF_EO  E(r,c) == H(r,c-1) - rdGapOpen         CF_EX  E(r,c) == E(r,c-1) - rdGapExtend
+//   CF_FO  F(r,c) == H(r-1,c) - rfGapOpen         CF_FX  F(r,c) == F(r-1,c) - rfGapExtend
+//   CF_MM  read char does not match the reference mask (penalty != 0)
+// The H-cell's gap-move comparisons follow from these: in a row where gaps are allowed
+// F = max(F_up - ext, H_up - open, 0), so H == H_up - open iff (H == F and F == H_up - open), and
+// H != F implies H > both; likewise for E.  (Rows inside the gap barrier never look at them.)
+// E/F flags of rows inside the gap barrier are unspecified: no backtrace can be in E or F state
+// there (E/F are 0 in those rows and every cell on a backtrace path has a raw score >= 1).
+enum { CF_D = 1, CF_HE = 2, CF_HF = 4, CF_EO = 8, CF_EX = 16, CF_FO = 32, CF_FX = 64, CF_MM = 128 };
+// Skewed layout [col+strip][strip][k], 4 bytes per (step, strip): one fill store instruction
+// writes 128 contiguous bytes, a diagonal move of the backtrace stays in its 32-bit word two
+// times out of three.  byte index = 256*c + 260*v + k  (v = r / R, k = r % R)
+BT2_HD uint32_t cell_index(uint32_t r, uint32_t c, uint32_t R) {
 	const uint32_t v = (R == 1) ? r : (R == 2 ? (r >> 1) : (r / 3));
 	const uint32_t k = r - v * R;
-	const uint32_t RP = (R == 3) ? 4u : R;
-	return (((c + v) << 6) + v) * RP + k;
+	return (((c + v) << 6) + v) * 4u + k;
 }
-#define BT2_HEF_WORDS ((BT2GPU_MAX_COLS + 64) * 64 * 4)      // per problem slot
+#define BT2_CELL_BYTES ((BT2GPU_MAX_COLS + 64) * 64 * 4)     // per problem slot
+// debug-only H|E<<8|F<<16 words in the same skewed order (bt2gpu_test_fill)
+BT2_HD uint32_t hef_index(uint32_t r, uint32_t c, uint32_t R) { return cell_index(r, c, R); }
+#define BT2_HEF_WORDS BT2_CELL_BYTES
 
 // pools shared by the per-read kernels
 struct Pools {

@@ -12,11 +12,18 @@
 // because on sm_100a the 16x2 DPX instructions (VIADDMNMX.S16x2, VIMNMX3.S16x2) are
 // native while the 8x4 video intrinsics (__vmaxu4/__vsubus4) are emulated with 4-5
 // LOP3/PRMT each (SASS evidence).  u8 saturation is exact in 16 bits:
-// subs_u8(a,b) == max(a-b,0) for 0<=a,b<=255, which is one VIADDMNMX.
-// Strip boundaries travel down with __shfl_up_sync.  Every cell is stored as one
-// 32-bit word H | E<<8 | F<<16 in a skewed layout [col+strip][strip][k] so that each
-// store instruction writes one contiguous run (16 bytes per lane for R=3).
+// subs_u8(a,b) == max(a-b,0) for 0<=a,b<=255.
+// Strip boundaries travel down with __shfl_up_sync.  The reference keeps H, E and F of
+// every cell for its backtrace; the backtrace only ever asks which of its score
+// equalities hold at a cell, so the fill answers those while the operands are in
+// registers and stores ONE byte of flags per cell (dev_common.cuh, CF_*): 1 B/cell of
+// HBM traffic instead of 3-4.  Each equality is one HSET2.NEU on the two 16-bit halves
+// (the values 0..255 and the small negative unsaturated sums are compared as fp16 bit
+// patterns: denormals compare exactly, negative values are NaN/-inf patterns and can
+// only meet a non-negative partner, where "unordered or not equal" is the right answer)
+// plus one LOP3 that drops the mask into its bit.
 #pragma once
+#include <cuda_fp16.h>
 #include "dev_common.cuh"
 
 namespace bt2 {
@@ -27,7 +34,8 @@ struct FillArgs {
 	const ReadState* states;
 	const uint8_t*   seq;
 	const uint8_t*   qual;
-	uint32_t*        hef;       // [nslots * BT2_HEF_WORDS]
+	uint8_t*         cells;     // [nslots * BT2_CELL_BYTES]
+	uint32_t*        hef_dbg;   // test hook only: [nslots * BT2_HEF_WORDS] H|E<<8|F<<16, or null
 	unsigned long long* stats;  // [0] problems [1] cells
 };
 
@@ -36,32 +44,51 @@ struct FillShared {
 	uint32_t tab[3 * 5 * 64];          // negated penalties, pre-positioned per half
 	uint8_t  refc[BT2GPU_MAX_COLS + 8]; // reference code 0..4 per column
 	uint8_t  hlast[BT2GPU_MAX_COLS + 8];
+	uint8_t  rdc[64 * 3];               // read code per row (0..3, 7 = N or beyond the read)
 	uint16_t ckey[BT2GPU_MAX_COLS + 8];
 };
 
 __device__ __forceinline__ uint32_t pack2(int lo, int hi) { return ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16); }
+// 0xffff in each half where the 16-bit patterns differ
+__device__ __forceinline__ uint32_t ne2(uint32_t a, uint32_t b) {
+	return __hneu2_mask(*reinterpret_cast<const __half2*>(&a), *reinterpret_cast<const __half2*>(&b));
+}
 
-template<int R>
-__device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillShared& sh, uint32_t* __restrict__ hef, uint32_t lane) {
+template<int R, bool DBG>
+__device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillShared& sh, uint8_t* __restrict__ cells,
+                                          uint32_t* __restrict__ hef, uint32_t lane) {
 	const int rows = pb.rows, cols = pb.cols;
 	const int nv = (rows + R - 1) / R;                 // active strips
-	const uint32_t neg_rdgo = pack2(-P.rdGapOpen, -P.rdGapOpen), neg_rdge = pack2(-P.rdGapExt, -P.rdGapExt);
-	const uint32_t neg_rfgo = pack2(-P.rfGapOpen, -P.rfGapOpen), neg_rfge = pack2(-P.rfGapExt, -P.rfGapExt);
-	// gap barrier masks per row of the two strips (aligner_swsse_ee_u8.cpp:101-115: first/last gapbar rows)
-	uint32_t gbm[R];
+	// per-row gap penalties; inside the gap barrier (aligner_swsse_ee_u8.cpp:101-115: first/last gapbar
+	// rows) they are large enough to keep E and F at 0
+	const uint32_t neg_rdge = pack2(-P.rdGapExt, -P.rdGapExt);
+	uint32_t neg_rdgo[R], neg_rfgo[R], neg_rfge[R];    // [k]: read gaps in row k; ref gaps INTO row k (from the row above)
 	#pragma unroll
 	for(int k = 0; k < R; k++) {
 		const int rlo = (int)lane * R + k, rhi = (32 + (int)lane) * R + k;
 		const bool alo = !(rlo < P.gapbar || rows - 1 - rlo < P.gapbar), ahi = !(rhi < P.gapbar || rows - 1 - rhi < P.gapbar);
-		gbm[k] = (alo ? 0xffffu : 0u) | (ahi ? 0xffff0000u : 0u);
+		neg_rdgo[k] = pack2(alo ? -P.rdGapOpen : -1024, ahi ? -P.rdGapOpen : -1024);
+		neg_rfgo[k] = pack2(alo ? -P.rfGapOpen : -1024, ahi ? -P.rfGapOpen : -1024);
+		neg_rfge[k] = pack2(alo ? -P.rfGapExt : -1024, ahi ? -P.rfGapExt : -1024);
 	}
+	uint32_t nx_rfgo, nx_rfge;                         // ref gaps into the first row of the next lane's strips
+	{
+		const int rlo = ((int)lane + 1) * R, rhi = (33 + (int)lane) * R;
+		const bool alo = !(rlo < P.gapbar || rows - 1 - rlo < P.gapbar), ahi = !(rhi < P.gapbar || rows - 1 - rhi < P.gapbar);
+		nx_rfgo = pack2(alo ? -P.rfGapOpen : -1024, ahi ? -P.rfGapOpen : -1024);
+		nx_rfge = pack2(alo ? -P.rfGapExt : -1024, ahi ? -P.rfGapExt : -1024);
+	}
+	uint32_t rdc2[R];
+	#pragma unroll
+	for(int k = 0; k < R; k++) rdc2[k] = (uint32_t)sh.rdc[(int)lane * R + k] | ((uint32_t)sh.rdc[(32 + (int)lane) * R + k] << 16);
 	const bool strip_lo = (int)lane < nv, strip_hi = 32 + (int)lane < nv;
 	// which (lane, half, k) owns the last row
 	const int vstar = (rows - 1) / R, kstar = (rows - 1) - vstar * R;
 	const bool own_lo = vstar == (int)lane, own_hi = vstar == 32 + (int)lane;
-	uint32_t Hp[R], Ep[R];
+	uint32_t Hp[R], Ep[R], Eflag[R];
 	#pragma unroll
-	for(int k = 0; k < R; k++) { Hp[k] = 0; Ep[k] = 0; }
+	for(int k = 0; k < R; k++) { Hp[k] = 0; Ep[k] = 0; Eflag[k] = (CF_EO | CF_EX) * 0x00010001u; }
+	// sendF: F for the row below in bits 0-7 of each half, the stored F of this strip's last row in bits 8-15
 	uint32_t sendH = 0, sendF = 0, prevRecvH = (lane == 0) ? 0x000000ffu : 0u;
 	const int nsteps = cols + nv - 1;
 	for(int t = 0; t < nsteps; t++) {
@@ -73,49 +100,70 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 		const uint32_t wrapH = __shfl_sync(0xffffffffu, sendH, 31), wrapF = __shfl_sync(0xffffffffu, sendF, 31);
 		if(lane == 0) { recvH = 0x00ffu | (wrapH << 16); recvF = (wrapF << 16); } // row 0: H(-1,*) = 0xff, F = 0
 		const uint32_t x_lo = act_lo ? sh.refc[c_lo] : 4u, x_hi = act_hi ? sh.refc[c_hi] : 4u;
-		uint32_t diag = prevRecvH, f = recvF;
+		const uint32_t xpk = x_lo | (x_hi << 16);
+		uint32_t diag = prevRecvH;
+		uint32_t f = recvF & 0x00ff00ffu;                 // F(r,c) before the barrier rule (already 0 there)
+		uint32_t hup = recvH;                             // H(r-1,c)
+		uint32_t fup = (recvF >> 8) & 0x00ff00ffu;        // F(r-1,c) as stored
+		uint32_t flg[R];
 		uint32_t wlo[R], whi[R];
 		#pragma unroll
 		for(int k = 0; k < R; k++) {
 			const uint32_t s = sh.tab[(k * 5 + x_lo) * 64 + lane] | sh.tab[(k * 5 + x_hi) * 64 + 32 + lane];
 			const uint32_t hd = diag; diag = Hp[k];
-			f &= gbm[k];
-			uint32_t h = __viaddmax_s16x2(hd, s, 0u);
+			const uint32_t u = __vadd2(hd, s);            // unsaturated H(r-1,c-1) + sc
 			const uint32_t e = Ep[k];
-			h = __vimax3_s16x2(h, e, f);
-			// one word per cell: H | E<<8 | F<<16
-			wlo[k] = __byte_perm(__byte_perm(h, e, 0x0040), f, 0x5410);
-			whi[k] = __byte_perm(__byte_perm(h, e, 0x0062), f, 0x7610);
+			const uint32_t h = __vimax3_s16x2_relu(u, e, f);
+			// the comparisons of the backtrace at this cell
+			const uint32_t bf = __vadd2(hup, neg_rfgo[k]), af = __vadd2(fup, neg_rfge[k]);
+			uint32_t fl = Eflag[k];
+			fl |= ne2(h, u) & (CF_D * 0x00010001u);
+			fl |= ne2(h, e) & (CF_HE * 0x00010001u);
+			fl |= ne2(h, f) & (CF_HF * 0x00010001u);
+			fl |= ne2(f, bf) & (CF_FO * 0x00010001u);
+			fl |= ne2(f, af) & (CF_FX * 0x00010001u);
+			fl |= ne2(rdc2[k], xpk) & (CF_MM * 0x00010001u);
+			flg[k] = fl;
+			if(DBG) {
+				wlo[k] = __byte_perm(__byte_perm(h, e, 0x0040), f, 0x5410);
+				whi[k] = __byte_perm(__byte_perm(h, e, 0x0062), f, 0x7610);
+			}
 			if(k == kstar) {
 				if(own_lo && act_lo) sh.hlast[c_lo] = (uint8_t)(h & 0xffu);
 				if(own_hi && act_hi) sh.hlast[c_hi] = (uint8_t)((h >> 16) & 0xffu);
 			}
-			const uint32_t t1 = __viaddmax_s16x2(h, neg_rdgo, 0u) & gbm[k];
-			const uint32_t en = __viaddmax_s16x2(e, neg_rdge, t1);
-			const uint32_t t2 = __viaddmax_s16x2(h, neg_rfgo, 0u);
-			f = __viaddmax_s16x2(f, neg_rfge, t2);
+			// E of the next column in this row and its two comparisons
+			const uint32_t be = __vadd2(h, neg_rdgo[k]), ae = __vadd2(e, neg_rdge);
+			const uint32_t en = __vimax3_s16x2_relu(ae, be, 0u);
+			Eflag[k] = (ne2(en, be) & (CF_EO * 0x00010001u)) | (ne2(en, ae) & (CF_EX * 0x00010001u));
 			Hp[k] = h & am; Ep[k] = en & am;
+			// F of the next row in this column
+			hup = h; fup = f;
+			f = __vimax3_s16x2_relu(__vadd2(f, k + 1 < R ? neg_rfge[(k + 1) % R] : nx_rfge), __vadd2(h, k + 1 < R ? neg_rfgo[(k + 1) % R] : nx_rfgo), 0u);
 		}
-		{ // one 4*RP-byte store per strip: [t][strip][k]
-			constexpr int RP = (R == 3) ? 4 : R;
-			uint32_t* olo = hef + (((uint32_t)t << 6) + lane) * RP;
-			uint32_t* ohi = olo + 32 * RP;
+		{ // one 4-byte store per strip: [t][strip][k]
+			uint32_t blo, bhi;
 			if(R == 3) {
-				if(act_lo) *reinterpret_cast<uint4*>(olo) = make_uint4(wlo[0], wlo[1 % R], wlo[2 % R], 0u);
-				if(act_hi) *reinterpret_cast<uint4*>(ohi) = make_uint4(whi[0], whi[1 % R], whi[2 % R], 0u);
+				const uint32_t x = __byte_perm(flg[0], flg[1 % R], 0x6240);
+				blo = __byte_perm(x, flg[2 % R], 0x5410); bhi = __byte_perm(x, flg[2 % R], 0x7632);
 			} else if(R == 2) {
-				if(act_lo) *reinterpret_cast<uint2*>(olo) = make_uint2(wlo[0], wlo[1 % R]);
-				if(act_hi) *reinterpret_cast<uint2*>(ohi) = make_uint2(whi[0], whi[1 % R]);
-			} else {
-				if(act_lo) *olo = wlo[0];
-				if(act_hi) *ohi = whi[0];
+				blo = __byte_perm(flg[0], flg[1 % R], 0x3340); bhi = __byte_perm(flg[0], flg[1 % R], 0x3362);
+			} else { blo = flg[0] & 0xffu; bhi = flg[0] >> 16; }
+			uint32_t* olo = reinterpret_cast<uint32_t*>(cells) + (((uint32_t)t << 6) + lane);
+			if(act_lo) olo[0] = blo;
+			if(act_hi) olo[32] = bhi;
+			if(DBG) {
+				uint32_t* dlo = hef + (((uint32_t)t << 6) + lane) * 4u;
+				#pragma unroll
+				for(int k = 0; k < R; k++) { if(act_lo) dlo[k] = wlo[k]; if(act_hi) dlo[128 + k] = whi[k]; }
 			}
 		}
-		sendH = Hp[R - 1]; sendF = f & am;
+		sendH = Hp[R - 1]; sendF = (f | (fup << 8)) & am;
 		prevRecvH = (lane == 0) ? (0x00ffu | (recvH & 0xffff0000u)) : recvH;
 	}
 }
 
+template<bool DBG>
 __global__ void __launch_bounds__(BT2_FILL_WARPS * 32) k_fill(const DevParams* __restrict__ Pp, const FillArgs a) {
 	__shared__ FillShared shs[BT2_FILL_WARPS];
 	const DevParams& P = *Pp;
@@ -139,6 +187,7 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32) k_fill(const DevParams* _
 			else { const int c0 = rseq[rows - 1 - r]; rdc = c0 > 3 ? 4 : 3 - c0; q = rqual[rows - 1 - r]; }
 			q -= 33; if(q < 0) q = 0; if(q > 255) q = 255;
 		}
+		sh.rdc[r] = (uint8_t)(rdc > 3 ? 7 : rdc);
 		#pragma unroll
 		for(int x = 0; x < 5; x++) {
 			int pen = 0;
@@ -153,10 +202,11 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32) k_fill(const DevParams* _
 		sh.hlast[c] = 0;
 	}
 	__syncwarp();
-	uint32_t* hef = a.hef + (size_t)slot * BT2_HEF_WORDS;
-	if(R == 1) fill_body<1>(P, pb, sh, hef, lane);
-	else if(R == 2) fill_body<2>(P, pb, sh, hef, lane);
-	else fill_body<3>(P, pb, sh, hef, lane);
+	uint8_t* cells = a.cells + (size_t)slot * BT2_CELL_BYTES;
+	uint32_t* hef = DBG ? a.hef_dbg + (size_t)slot * BT2_HEF_WORDS : nullptr;
+	if(R == 1) fill_body<1, DBG>(P, pb, sh, cells, hef, lane);
+	else if(R == 2) fill_body<2, DBG>(P, pb, sh, cells, hef, lane);
+	else fill_body<3, DBG>(P, pb, sh, cells, hef, lane);
 	__syncwarp();
 	// ---- last-row candidates: H-0xff >= minsc, sorted by (score desc, col desc)
 	const int minsc = pb.minsc;

@@ -123,39 +123,54 @@ __global__ void k_step(const DevParams* __restrict__ Pp, const DevIndex ix, cons
 	states[read] = rs;
 }
 
-struct BtArrays { const uint32_t* hef; uint32_t* masks; uint32_t gen; BtFrame* stacks; uint32_t* scratch; const uint8_t* seq; const uint8_t* qual; };
+struct BtArrays { const uint8_t* cells; uint32_t* masks; uint32_t gen; BtFrame* stacks; uint32_t* scratch; const uint8_t* seq; const uint8_t* qual; };
 
-// Persistent threads: every lane runs BtMachine::step in one loop and pulls the next problem
-// from `task` when its own is finished, so a warp is busy until the chunk runs dry.
-__global__ void __launch_bounds__(128) k_bt(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const Problem* probs, uint32_t count,
+// One lane per problem, persistent: a lane that finishes its problem takes the next one.
+// The lanes of a warp are in different phases (candidate pick, backtrace cell, alignment
+// post-processing, fetch); the cheap and frequent ones (candidate, cell) run every
+// iteration, the long and rare ones (post-processing, fetch + begin) are held back until
+// a quarter of the warp wants them or nothing else is left, so that they are executed
+// for several lanes at once instead of stalling 31 lanes for one.
+__global__ void __launch_bounds__(128, 8) k_bt(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const Problem* probs, uint32_t count,
                      const BtArrays ba, uint32_t* task, uint32_t* next_list, uint32_t* next_cnt, uint32_t* roundend_list, uint32_t* roundend_cnt) {
 	BtMachine m;
-	m.P = Pp; m.pools = &pools; m.gtag = ba.gen << 13;
-	bool have = false;
+	m.P = Pp; m.pools = &pools; m.gtag = ba.gen << 13; m.seqbase = ba.seq; m.qualbase = ba.qual;
+	m.phase = BP_DONE; m.result = BT_CONTINUE;
+	bool have = false, drained = false;
 	uint32_t read = 0;
 	while(true) {
-		if(!have) {
-			const uint32_t j = atomicAdd(task, 1u);
-			if(j >= count) break;
-			const Problem& pb = probs[j];
-			if(pb.read == BT2_NIL) continue;
-			read = pb.read;
-			m.rs = states[read];
-			m.pb = &pb;
-			m.hef = ba.hef + (size_t)j * BT2_HEF_WORDS;
-			m.masks = ba.masks + (size_t)j * BT2_MASK_WORDS;
-			m.stack = ba.stacks + (size_t)j * BT2_BT_STACK;
-			m.scratch = ba.scratch + (size_t)read * BT2_SCRATCH_EDITS;
-			m.rv.seq = ba.seq + m.rs.seq_off; m.rv.qual = ba.qual + m.rs.seq_off; m.rv.rdlen = m.rs.rdlen; m.rv.fw = pb.fw != 0;
-			m.begin();
-			have = true;
+		if(m.phase == BP_CAND) m.cand();
+		if(m.phase == BP_STEP) m.bt_step();
+		const uint32_t hot = __ballot_sync(0xffffffffu, m.phase == BP_CAND || m.phase == BP_STEP);
+		const uint32_t wpost = __ballot_sync(0xffffffffu, m.phase == BP_POST);
+		if(wpost && (hot == 0 || __popc(wpost) >= 8)) { if(m.phase == BP_POST) m.post(); }
+		const uint32_t wdone = __ballot_sync(0xffffffffu, m.phase == BP_DONE && !drained);
+		if(wdone && (hot == 0 || __popc(wdone) >= 8)) {
+			if(m.phase == BP_DONE && !drained) {
+				if(have) {
+					m.finish();
+					if(m.result == BT_ROUND_END) { m.rs->phase = RS_ROUND_DONE; list_append(roundend_list, roundend_cnt, read); }
+					else list_append(next_list, next_cnt, read);
+					have = false;
+				}
+				while(!have) {
+					const uint32_t j = atomicAdd(task, 1u);
+					if(j >= count) { drained = true; break; }
+					const Problem& pb = probs[j];
+					if(pb.read == BT2_NIL) continue;
+					read = pb.read;
+					m.rs = states + read;
+					m.pb = &pb;
+					m.cells = ba.cells + (size_t)j * BT2_CELL_BYTES;
+					m.masks = ba.masks + (size_t)j * BT2_MASK_WORDS;
+					m.stack = ba.stacks + (size_t)j * BT2_BT_STACK;
+					m.scratch = ba.scratch + (size_t)read * BT2_SCRATCH_EDITS;
+					m.begin();
+					have = true;
+				}
+			}
 		}
-		if(m.phase == BP_DONE || !m.step()) {
-			if(m.result == BT_ROUND_END) { m.rs.phase = RS_ROUND_DONE; list_append(roundend_list, roundend_cnt, read); }
-			else list_append(next_list, next_cnt, read);
-			states[read] = m.rs;
-			have = false;
-		}
+		if(__ballot_sync(0xffffffffu, !drained || have) == 0) break;
 	}
 }
 

@@ -19,10 +19,10 @@
 
 using namespace bt2;
 
-static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint32_t* hef) {
+static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_t* cells) {
 	const int rows = pb.rows, cols = pb.cols; const uint32_t R = pb.R;
 	auto subs = [](int a, int b) { int v = a - b; return v < 0 ? 0 : v; };
-	std::vector<int> Hprev(rows, 0), Eprev(rows, 0), Hcur(rows), Ecur(rows);
+	std::vector<int> Hprev(rows, 0), Eprev(rows, 0), Fprev(rows, 0), Hcur(rows), Ecur(rows), Fcur(rows), Eleft(rows, 0), Ehere(rows, 0);
 	int lrmax = 0; std::vector<uint16_t> cand;
 	for(int j = 0; j < cols; j++) {
 		const int refm = pb.rf[j];
@@ -39,12 +39,25 @@ static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint32
 			Ecur[r] = e2 > ho ? e2 : ho;
 			const int f2 = subs(f, P.rfGapExt), fo = subs(h, P.rfGapOpen);
 			Fpre = f2 > fo ? f2 : fo;
-			hef[hef_index(r, j, R)] = (uint32_t)h | ((uint32_t)e << 8) | ((uint32_t)f << 16);
+			Fcur[r] = f;
+			// the backtrace's comparisons at this cell, literally (raw values: the 0xff bias cancels)
+			uint32_t ne = 0;
+			const int hup = (r == 0) ? 255 : Hcur[r - 1], fup = (r == 0) ? 0 : Fcur[r - 1];
+			if(h != hd - s0) ne |= CF_D;                 // s0 = penalty >= 0 (column 0 compares with H(r-1,-1) = 0; never read)
+			if(h != e) ne |= CF_HE;
+			if(h != f) ne |= CF_HF;
+			if(!(j > 0 && e == Hprev[r] - P.rdGapOpen)) ne |= CF_EO;
+			if(!(j > 0 && e == Eleft[r] - P.rdGapExt)) ne |= CF_EX;
+			Ehere[r] = e;
+			if(!(f == hup - P.rfGapOpen)) ne |= CF_FO;
+			if(!(f == fup - P.rfGapExt)) ne |= CF_FX;
+			if(s0 != 0) ne |= CF_MM;
+			cells[cell_index(r, j, R)] = (uint8_t)ne;
 		}
 		const int lr = Hcur[rows - 1];
 		if(lr > lrmax) lrmax = lr;
 		if(lr - 255 >= pb.minsc) cand.push_back((uint16_t)((lr << 8) | j));
-		Hprev.swap(Hcur); Eprev.swap(Ecur);
+		Hprev.swap(Hcur); Eprev.swap(Ecur); Fprev.swap(Fcur); Eleft = Ehere;
 	}
 	std::sort(cand.begin(), cand.end(), [](uint16_t a, uint16_t b) { return a > b; });
 	pb.lrmax = lrmax; pb.ncand = (uint32_t)cand.size();
@@ -94,7 +107,7 @@ int main(int argc, char** argv) {
 	const uint32_t MI = BT2GPU_MAX_ITER + 8;
 	std::vector<uint16_t> ov_rng(2 * MI), ov_pos(2 * MI), ov_val(2 * MI), seen_rng(MI), seen_val(MI), conv_val(MI), r_n(W), r_cur(W), r_thresh(W), r_conv_n(W), r_nseen(W);
 	std::vector<uint8_t> r_flags(W), elim(W); std::vector<uint32_t> r_conv_off(W); std::vector<double> mass(W);
-	std::vector<uint32_t> hef(BT2_HEF_WORDS); std::vector<uint32_t> masks(BT2_MASK_WORDS, 0); uint32_t gen = 0; std::vector<BtFrame> stack(BT2_BT_STACK);
+	std::vector<uint8_t> cells(BT2_CELL_BYTES); std::vector<uint32_t> masks(BT2_MASK_WORDS, 0); uint32_t gen = 0; std::vector<BtFrame> stack(BT2_BT_STACK);
 	orc::WorkCounters wc;
 	for(uint32_t ri = 0; ri < n; ri++) {
 		ReadState& rs = states[ri];
@@ -141,15 +154,15 @@ int main(int argc, char** argv) {
 			while(true) {
 				Problem pb; pb.read = ri;
 				if(advance(P, ix, rf, pools, rs, pb) == ADV_ROUND_END) break;
-				BtMachine m; m.P = &P; m.pools = &pools; m.pb = &pb; m.hef = hef.data(); m.masks = masks.data(); m.stack = stack.data();
+				BtMachine m; m.P = &P; m.pools = &pools; m.pb = &pb; m.cells = cells.data(); m.masks = masks.data(); m.stack = stack.data();
 				if(++gen > BT2_MASK_GEN_MAX) { std::fill(masks.begin(), masks.end(), 0u); gen = 1; }
 				m.gtag = gen << 13;
 				m.scratch = scratch.data() + (size_t)ri * BT2_SCRATCH_EDITS;
-				m.rv.seq = in->seq + so; m.rv.qual = in->qual + so; m.rv.rdlen = rdlen; m.rv.fw = pb.fw != 0;
-				fill_emu(P, pb, m.rv, hef.data());
-				m.rs = rs; m.begin();
+				m.seqbase = in->seq; m.qualbase = in->qual; m.rs = &rs;
+				fill_emu(P, pb, m.view(), cells.data());
+				m.begin();
 				while(m.phase != BP_DONE && m.step()) { }
-				rs = m.rs;
+				m.finish();
 				if(m.result == BT_ROUND_END) break;
 			}
 			if(!next_round_wanted(P, rs)) break;
