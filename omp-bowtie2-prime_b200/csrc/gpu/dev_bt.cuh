@@ -30,12 +30,21 @@ enum { BP_CAND = 0, BP_STEP = 1, BP_POST = 2, BP_DONE = 3 };
 
 struct BtFrame { uint32_t a, b, c, d; }; // packed branch-stack frame
 #define BT2_BT_STACK 400
-// backtrace masks: SSEMatrix::masks_ (13 bits) + 19-bit generation tag per cell, stored by
-// diagonal ([col-row+rows-1][row]) so that a run of diagonal moves stays inside one sector;
-// a cell whose tag differs from the problem's generation reads as 0, which replaces the
-// reference's lazy per-row memset (SSEMatrix::resetRow, aligner_swsse.h)
-#define BT2_MASK_GEN_MAX ((1u << 19) - 1)
-#define BT2_MASK_WORDS ((BT2GPU_MAX_ROWS + BT2GPU_MAX_COLS) * BT2GPU_MAX_ROWS)
+// Backtrace state per cell (what SSEMatrix::masks_ holds, aligner_swsse.h:140-420), one byte,
+// stored like the cell flags: one 32-bit word per (strip, step) = the bytes of its R rows plus
+// an 8-bit generation tag in byte 3.  A word whose tag differs from the launch's generation
+// reads as "all untouched", which replaces the reference's lazy per-row memset
+// (SSEMatrix::resetRow).  The byte:
+//   bit 0      reportedThru
+//   bits 1-3   H: 0 = mask not set, n+1 = set with n options still to try
+//   bits 4-5   E: 0 = not set, 1 = set / nothing left, 2 = set / gap extension left
+//   bits 6-7   F: likewise
+// The reference stores the remaining options as a bit set; since options are always consumed in
+// the same priority order (diagonal, ref open, ref extend, read open, read extend) and the set
+// of options at a cell is a function of the fill alone, "how many are left" is the same
+// information: the remaining ones are the lowest-priority n of the original set.
+#define BT2_MASK_GEN_MAX 255u
+#define BT2_MASK_WORDS (BT2_CELL_T * 64)
 
 struct ReadView {
 	const uint8_t* seq; const uint8_t* qual; uint32_t rdlen; bool fw;
@@ -98,39 +107,44 @@ BT2_HD bool alns_overlap(const EditView& a, int64_t arefoff, const EditView& b, 
 	return false;
 }
 
+// the n lowest-priority options of an H-cell option set (priority high -> low: 16, 1, 4, 2, 8)
+BT2_HD int lowest_options(int orig, int n) {
+	int out = 0;
+	if(n > 0 && (orig & 8))  { out |= 8;  n--; }
+	if(n > 0 && (orig & 2))  { out |= 2;  n--; }
+	if(n > 0 && (orig & 4))  { out |= 4;  n--; }
+	if(n > 0 && (orig & 1))  { out |= 1;  n--; }
+	if(n > 0 && (orig & 16)) { out |= 16; n--; }
+	return out;
+}
+
 struct BtMachine {
 	// ---- context of the current problem
 	const DevParams* P; const Pools* pools;
 	const Problem* pb;
 	const uint8_t* cells;  // CF_* flag bytes of this problem (cell_index)
-	uint32_t* masks;       // diagonal-major tagged masks of this problem slot
+	uint32_t* masks;       // backtrace state words of this problem slot (same indexing / 4)
 	BtFrame* stack;        // [BT2_BT_STACK]
 	uint32_t* scratch;     // per-read edit scratch
 	const uint8_t* seqbase; const uint8_t* qualbase; // batch arrays
 	ReadState* rs;         // the read's state, updated in place
-	uint32_t gtag;         // generation << 13
+	uint32_t gtag;         // generation << 24
 	// ---- cached per problem
 	int rows, R, glo, ghi, dlo, dhi; // gaps allowed in rows [glo,ghi); core diagonals: dlo <= col-row <= dhi
 	// ---- nextAlignment state
 	int phase, result;
 	uint32_t cural, reseed;
 	// ---- backtrace state (one attempt)
-	int row, col, origCol, ct, score, ns, readGaps, refGaps, kk; // kk = row % R
-	uint32_t cidx, midx;   // cell_index(row,col), mask index of (row,col)
+	int row, col, origCol, ct, score, ns, readGaps, refGaps;
+	uint32_t cidx;         // cell_index(row,col); cidx & 3 = row % R, cidx >> 2 = state word
 	uint32_t nstack, ned, hw, fl, nsteps;
 	bool coreHit;
 
 	BT2_HD ReadView view() const { ReadView v; v.seq = seqbase + rs->seq_off; v.qual = qualbase + rs->seq_off; v.rdlen = rs->rdlen; v.fw = pb->fw != 0; return v; }
-	BT2_HD uint32_t mask_index(int r, int c) const { return (uint32_t)(c - r + rows - 1) * (uint32_t)rows + (uint32_t)r; }
-	BT2_HD uint32_t mask_at(uint32_t idx) const { const uint32_t m = masks[idx]; return ((m & ~0x1fffu) == gtag) ? (m & 0x1fffu) : 0u; }
-	BT2_HD void locate() { // (row, col) changed arbitrarily: recompute the running indices
-		const uint32_t v = (R == 1) ? (uint32_t)row : (R == 2 ? ((uint32_t)row >> 1) : ((uint32_t)row / 3u));
-		kk = row - (int)v * R;
-		cidx = (uint32_t)col * 256u + v * 260u + (uint32_t)kk;
-		midx = mask_index(row, col);
-	}
-	BT2_HD void row_dec() { row--; midx += (uint32_t)rows - 1u; if(kk > 0) { kk--; cidx--; } else { kk = R - 1; cidx -= 260u - (uint32_t)kk; } }
-	BT2_HD void col_dec() { col--; midx -= (uint32_t)rows; cidx -= 256u; }
+	BT2_HD uint32_t state_word(uint32_t widx) const { const uint32_t m = masks[widx]; return ((m & 0xff000000u) == gtag) ? m : gtag; }
+	BT2_HD void locate() { cidx = cell_index((uint32_t)row, (uint32_t)col, (uint32_t)R); } // (row, col) changed arbitrarily
+	BT2_HD void row_dec() { row--; if(cidx & 3u) cidx--; else cidx -= (BT2_CELL_T + 1) * 4u - (uint32_t)(R - 1); }
+	BT2_HD void col_dec() { col--; cidx -= 4u; }
 	BT2_HD void push_edit(uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scratch[ned] = x; ned++; if(ned > hw) hw = ned; }
 
 	// SwDriver::extendSeeds right after swa.align(): counters, then either the candidate loop or done
@@ -165,7 +179,8 @@ struct BtMachine {
 		if(cural >= pb->ncand) { phase = BP_DONE; return; }
 		const int lastRow = rows - 1;
 		const int c0 = pb->cand[cural] & 255;
-		if(mask_at(mask_index(lastRow, c0)) & 1u) { cural++; return; }
+		const uint32_t ci = cell_index((uint32_t)lastRow, (uint32_t)c0, (uint32_t)R);
+		if((state_word(ci >> 2) >> ((ci & 3u) * 8u)) & 1u) { cural++; return; }
 		Rng rnd = rs->rnd;
 		reseed = rnd.nextU32() + 1;
 		rnd.init(reseed);
@@ -200,46 +215,47 @@ struct BtMachine {
 		fl = ~(uint32_t)cells[cidx];
 		bool empty = false, canMoveThru = true, branch = false;
 		int cur = MV_DIAG;
-		uint32_t m16 = mask_at(midx);
-		if(m16 & 1u) {
+		const uint32_t widx = cidx >> 2, sh8 = (cidx & 3u) * 8u;
+		const uint32_t word = state_word(widx);
+		uint32_t st = (word >> sh8) & 0xffu;
+		if(st & 1u) {
 			canMoveThru = false;
 		} else if(row > 0) {
 			if(ct == CT_E) {
-				int mask = col > 0 ? (int)((fl >> 3) & 3u) : 0;
-				const int origMask = mask;
-				if(m16 & (1u << 7)) mask = (m16 >> 8) & 3;
-				if(mask == 3)      { cur = MV_READ_OPEN; m16 = (m16 & ~(7u << 7)) | (1u << 7) | (2u << 8); branch = true; }
-				else if(mask == 2) { cur = MV_RDGAP_EXT; m16 = (m16 & ~(7u << 7)) | (1u << 7); }
-				else if(mask == 1) { cur = MV_READ_OPEN; m16 = (m16 & ~(7u << 7)) | (1u << 7); }
+				const int origMask = col > 0 ? (int)((fl >> 3) & 3u) : 0;
+				const uint32_t es = (st >> 4) & 3u;
+				const int mask = es ? (es == 2u ? 2 : 0) : origMask;
+				if(mask == 3)      { cur = MV_READ_OPEN; st = (st & ~(3u << 4)) | (2u << 4); branch = true; }
+				else if(mask == 2) { cur = MV_RDGAP_EXT; st = (st & ~(3u << 4)) | (1u << 4); }
+				else if(mask == 1) { cur = MV_READ_OPEN; st = (st & ~(3u << 4)) | (1u << 4); }
 				else { empty = true; canMoveThru = (origMask == 0); }
 			} else if(ct == CT_F) {
-				int mask = (int)((fl >> 5) & 3u);
-				const int origMask = mask;
-				if(m16 & (1u << 10)) mask = (m16 >> 11) & 3;
-				if(mask == 3)      { cur = MV_REF_OPEN;  m16 = (m16 & ~(7u << 10)) | (1u << 10) | (2u << 11); branch = true; }
-				else if(mask == 2) { cur = MV_RFGAP_EXT; m16 = (m16 & ~(7u << 10)) | (1u << 10); }
-				else if(mask == 1) { cur = MV_REF_OPEN;  m16 = (m16 & ~(7u << 10)) | (1u << 10); }
+				const int origMask = (int)((fl >> 5) & 3u);
+				const uint32_t fs = (st >> 6) & 3u;
+				const int mask = fs ? (fs == 2u ? 2 : 0) : origMask;
+				if(mask == 3)      { cur = MV_REF_OPEN;  st = (st & ~(3u << 6)) | (2u << 6); branch = true; }
+				else if(mask == 2) { cur = MV_RFGAP_EXT; st = (st & ~(3u << 6)) | (1u << 6); }
+				else if(mask == 1) { cur = MV_REF_OPEN;  st = (st & ~(3u << 6)) | (1u << 6); }
 				else { empty = true; canMoveThru = (origMask == 0); }
 			} else {
 				const bool hasLeft = col > 0;
-				int mask = 0;
+				int origMask = 0;
 				if(row >= glo && row < ghi) { // gaps allowed in this row
-					if(fl & CF_HF) mask |= (int)(((fl >> 5) & 1u) | (((fl >> 6) & 1u) << 2));             // H_up - rfgo (1), F_up - rfge (4)
-					if(hasLeft && (fl & CF_HE)) mask |= (int)((((fl >> 3) & 1u) << 1) | (((fl >> 4) & 1u) << 3)); // H_left - rdgo (2), E_left - rdge (8)
+					if(fl & CF_HF) origMask |= (int)(((fl >> 5) & 1u) | (((fl >> 6) & 1u) << 2));             // H_up - rfgo (1), F_up - rfge (4)
+					if(hasLeft && (fl & CF_HE)) origMask |= (int)((((fl >> 3) & 1u) << 1) | (((fl >> 4) & 1u) << 3)); // H_left - rdgo (2), E_left - rdge (8)
 				}
-				if(hasLeft && (fl & CF_D)) mask |= 16;
-				const int origMask = mask;
-				if(m16 & (1u << 1)) mask = (m16 >> 2) & 31;
+				if(hasLeft && (fl & CF_D)) origMask |= 16;
+				const uint32_t hs = (st >> 1) & 7u;
+				int mask = hs ? lowest_options(origMask, (int)hs - 1) : origMask;
 				int select = -1;
 				const int opts = BT2_POPC((unsigned)mask);
 				if(opts == 1) {
 					select = BT2_CTZ((unsigned)mask);
-					m16 = (m16 & ~(31u << 1)) | (1u << 1);   // hMaskSet clears bits 1..5 only (aligner_swsse.h:362)
+					st = (st & ~(7u << 1)) | (1u << 1);
 				} else if(opts > 1) {
 					if(mask & 16) select = 4; else if(mask & 1) select = 0; else if(mask & 4) select = 2;
 					else if(mask & 2) select = 1; else select = 3;
-					mask &= ~(1 << select);
-					m16 = (m16 & ~(31u << 1)) | (1u << 1) | ((uint32_t)mask << 2);
+					st = (st & ~(7u << 1)) | ((uint32_t)opts << 1);   // opts - 1 options left
 					branch = true;
 				}
 				if(select != -1) {
@@ -247,7 +263,7 @@ struct BtMachine {
 				} else { empty = true; canMoveThru = (origMask == 0); }
 			}
 		}
-		masks[midx] = gtag | m16 | 1u;
+		masks[widx] = (word & ~(0xffu << sh8)) | ((st | 1u) << sh8);
 		if(!canMoveThru) {
 			if(nstack > 0) {
 				const BtFrame f = stack[--nstack];

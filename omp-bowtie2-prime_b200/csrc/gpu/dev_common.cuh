@@ -319,15 +319,18 @@ struct Problem {
 // E/F flags of rows inside the gap barrier are unspecified: no backtrace can be in E or F state
 // there (E/F are 0 in those rows and every cell on a backtrace path has a raw score >= 1).
 enum { CF_D = 1, CF_HE = 2, CF_HF = 4, CF_EO = 8, CF_EX = 16, CF_FO = 32, CF_FX = 64, CF_MM = 128 };
-// Skewed layout [col+strip][strip][k], 4 bytes per (step, strip): one fill store instruction
-// writes 128 contiguous bytes, a diagonal move of the backtrace stays in its 32-bit word two
-// times out of three.  byte index = 256*c + 260*v + k  (v = r / R, k = r % R)
+// Layout [strip][step][k] with step = col + strip and 4 bytes per (strip, step): a fill lane
+// writes consecutive words on consecutive steps (one 16-byte store every four steps), and the
+// cells a backtrace visits - a diagonal band, a few strips deep around the last row for the
+// failing candidates - fall into few 32-byte sectors (8 columns x R rows of one strip each).
+// byte index = ((v*BT2_CELL_T) + c + v)*4 + k   (v = r / R, k = r % R)
+#define BT2_CELL_T (BT2GPU_MAX_COLS + 64)
 BT2_HD uint32_t cell_index(uint32_t r, uint32_t c, uint32_t R) {
 	const uint32_t v = (R == 1) ? r : (R == 2 ? (r >> 1) : (r / 3));
 	const uint32_t k = r - v * R;
-	return (((c + v) << 6) + v) * 4u + k;
+	return (v * BT2_CELL_T + c + v) * 4u + k;
 }
-#define BT2_CELL_BYTES ((BT2GPU_MAX_COLS + 64) * 64 * 4)     // per problem slot
+#define BT2_CELL_BYTES (BT2_CELL_T * 64 * 4)                 // per problem slot
 // debug-only H|E<<8|F<<16 words in the same skewed order (bt2gpu_test_fill)
 BT2_HD uint32_t hef_index(uint32_t r, uint32_t c, uint32_t R) { return cell_index(r, c, R); }
 #define BT2_HEF_WORDS BT2_CELL_BYTES

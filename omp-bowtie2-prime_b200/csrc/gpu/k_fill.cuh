@@ -91,7 +91,13 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 	// sendF: F for the row below in bits 0-7 of each half, the stored F of this strip's last row in bits 8-15
 	uint32_t sendH = 0, sendF = 0, prevRecvH = (lane == 0) ? 0x000000ffu : 0u;
 	const int nsteps = cols + nv - 1;
-	for(int t = 0; t < nsteps; t++) {
+	uint4* const out_lo = reinterpret_cast<uint4*>(cells + (size_t)lane * (BT2_CELL_T * 4));
+	uint4* const out_hi = reinterpret_cast<uint4*>(cells + (size_t)(32 + lane) * (BT2_CELL_T * 4));
+	for(int t0 = 0; t0 < nsteps; t0 += 4) {
+	uint32_t accl[4], acch[4];
+	#pragma unroll
+	for(int tj = 0; tj < 4; tj++) {
+		const int t = t0 + tj;
 		const int c_lo = t - (int)lane, c_hi = c_lo - 32;
 		const bool act_lo = strip_lo && c_lo >= 0 && c_lo < cols, act_hi = strip_hi && c_hi >= 0 && c_hi < cols;
 		const uint32_t am = (act_lo ? 0xffffu : 0u) | (act_hi ? 0xffff0000u : 0u);
@@ -141,7 +147,7 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 			hup = h; fup = f;
 			f = __vimax3_s16x2_relu(__vadd2(f, k + 1 < R ? neg_rfge[(k + 1) % R] : nx_rfge), __vadd2(h, k + 1 < R ? neg_rfgo[(k + 1) % R] : nx_rfgo), 0u);
 		}
-		{ // one 4-byte store per strip: [t][strip][k]
+		{ // the strip's R flag bytes of this column as one word; four steps make one 16-byte store
 			uint32_t blo, bhi;
 			if(R == 3) {
 				const uint32_t x = __byte_perm(flg[0], flg[1 % R], 0x6240);
@@ -149,17 +155,20 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 			} else if(R == 2) {
 				blo = __byte_perm(flg[0], flg[1 % R], 0x3340); bhi = __byte_perm(flg[0], flg[1 % R], 0x3362);
 			} else { blo = flg[0] & 0xffu; bhi = flg[0] >> 16; }
-			uint32_t* olo = reinterpret_cast<uint32_t*>(cells) + (((uint32_t)t << 6) + lane);
-			if(act_lo) olo[0] = blo;
-			if(act_hi) olo[32] = bhi;
+			accl[tj] = blo; acch[tj] = bhi;
 			if(DBG) {
-				uint32_t* dlo = hef + (((uint32_t)t << 6) + lane) * 4u;
+				uint32_t* dlo = hef + ((size_t)lane * BT2_CELL_T + (uint32_t)t) * 4u;
+				uint32_t* dhi = hef + ((size_t)(32 + lane) * BT2_CELL_T + (uint32_t)t) * 4u;
 				#pragma unroll
-				for(int k = 0; k < R; k++) { if(act_lo) dlo[k] = wlo[k]; if(act_hi) dlo[128 + k] = whi[k]; }
+				for(int k = 0; k < R; k++) { if(act_lo) dlo[k] = wlo[k]; if(act_hi) dhi[k] = whi[k]; }
 			}
 		}
 		sendH = Hp[R - 1]; sendF = (f | (fup << 8)) & am;
 		prevRecvH = (lane == 0) ? (0x00ffu | (recvH & 0xffff0000u)) : recvH;
+	}
+	// [strip][step]: strip v is active at steps v .. v+cols-1
+	if(strip_lo && t0 + 3 >= (int)lane && t0 < (int)lane + cols) out_lo[t0 >> 2] = make_uint4(accl[0], accl[1], accl[2], accl[3]);
+	if(strip_hi && t0 + 3 >= 32 + (int)lane && t0 < 32 + (int)lane + cols) out_hi[t0 >> 2] = make_uint4(acch[0], acch[1], acch[2], acch[3]);
 	}
 }
 

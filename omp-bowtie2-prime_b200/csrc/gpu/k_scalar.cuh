@@ -134,7 +134,7 @@ struct BtArrays { const uint8_t* cells; uint32_t* masks; uint32_t gen; BtFrame* 
 __global__ void __launch_bounds__(128, 8) k_bt(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const Problem* probs, uint32_t count,
                      const BtArrays ba, uint32_t* task, uint32_t* next_list, uint32_t* next_cnt, uint32_t* roundend_list, uint32_t* roundend_cnt) {
 	BtMachine m;
-	m.P = Pp; m.pools = &pools; m.gtag = ba.gen << 13; m.seqbase = ba.seq; m.qualbase = ba.qual;
+	m.P = Pp; m.pools = &pools; m.gtag = ba.gen << 24; m.seqbase = ba.seq; m.qualbase = ba.qual;
 	m.phase = BP_DONE; m.result = BT_CONTINUE;
 	bool have = false, drained = false;
 	uint32_t read = 0;

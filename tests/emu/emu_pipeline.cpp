@@ -156,7 +156,7 @@ int main(int argc, char** argv) {
 				if(advance(P, ix, rf, pools, rs, pb) == ADV_ROUND_END) break;
 				BtMachine m; m.P = &P; m.pools = &pools; m.pb = &pb; m.cells = cells.data(); m.masks = masks.data(); m.stack = stack.data();
 				if(++gen > BT2_MASK_GEN_MAX) { std::fill(masks.begin(), masks.end(), 0u); gen = 1; }
-				m.gtag = gen << 13;
+				m.gtag = gen << 24;
 				m.scratch = scratch.data() + (size_t)ri * BT2_SCRATCH_EDITS;
 				m.seqbase = in->seq; m.qualbase = in->qual; m.rs = &rs;
 				fill_emu(P, pb, m.view(), cells.data());
