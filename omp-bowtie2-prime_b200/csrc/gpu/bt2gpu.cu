@@ -64,7 +64,7 @@ struct bt2gpu_ctx {
 	std::vector<void*> resident;      // index / reference allocations
 	uint32_t nslots = 0, sampSlots = 0, maxBatch = 0, btgen = 0;
 	// problem-slot arrays
-	DBuf probs, cells, masks, stacks;
+	DBuf probs, cells, vis, pcache;
 	// per-batch arrays
 	DBuf seq, qual, seq_off, rng_seed, minsc, nceil, interval;
 	DBuf states, scratch, hits, seedtasks, lists[7], counters, stats;
@@ -248,7 +248,7 @@ void do_run(bt2gpu_ctx* c) {
 	sa.r_n = c->s_rn.as<uint16_t>(); sa.r_cur = c->s_rcur.as<uint16_t>(); sa.r_thresh = c->s_rth.as<uint16_t>(); sa.r_flags = c->s_rfl.as<uint8_t>();
 	sa.r_conv_off = c->s_rco.as<uint32_t>(); sa.r_conv_n = c->s_rcn.as<uint16_t>(); sa.r_nseen = c->s_rns.as<uint16_t>();
 	sa.mass = c->s_mass.as<double>(); sa.elim = c->s_elim.as<uint8_t>();
-	BtArrays bta; bta.cells = c->cells.as<uint8_t>(); bta.masks = c->masks.as<uint32_t>(); bta.gen = 0; bta.stacks = c->stacks.as<BtFrame>();
+	BtArrays bta; bta.cells = c->cells.as<uint8_t>(); bta.vis = c->vis.as<uint32_t>(); bta.gen = 0; bta.pcache = c->pcache.as<uint32_t>();
 	bta.scratch = c->scratch.as<uint32_t>(); bta.seq = ba.seq; bta.qual = ba.qual;
 	Problem* probs = c->probs.as<Problem>();
 	const Pools pools = c->pools;
@@ -295,14 +295,14 @@ void do_run(bt2gpu_ctx* c) {
 				{ Phase ph(c, PH_RESOLVE);
 				  k_step<<<nblk(k, 128), 128, 0, st>>>(c->dP, c->ix, c->rf, pools, states, L[3 + cur], b, k, probs, L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_step++; }
 				{ Phase ph(c, PH_FILL);
-				  FillArgs fa; fa.probs = probs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.cells = c->cells.as<uint8_t>(); fa.hef_dbg = nullptr; fa.stats = stats + 8;
+				  FillArgs fa; fa.probs = probs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.cells = c->cells.as<uint8_t>(); fa.pcache = c->pcache.as<uint32_t>(); fa.hef_dbg = nullptr; fa.stats = stats + 8;
 				  k_fill<false><<<nblk(k, BT2_FILL_WARPS), BT2_FILL_WARPS * 32, 0, st>>>(c->dP, fa); LAUNCH(c); c->ctr.n_fill++; }
 				{ Phase ph(c, PH_BT);
-				  if(++c->btgen > BT2_MASK_GEN_MAX) { CK(cudaMemsetAsync(c->masks.p, 0, (size_t)c->nslots * BT2_MASK_WORDS * 4, st)); c->btgen = 1; }
+				  if(++c->btgen > BT2_VIS_GEN_MAX) { CK(cudaMemsetAsync(c->vis.p, 0, (size_t)c->nslots * BT2_VIS_WORDS * 4, st)); c->btgen = 1; }
 				  bta.gen = c->btgen;
 				  zero_counter(c, C_BTTASK);
-				  const uint32_t btBlocks = std::min<uint32_t>(nblk(k, 128), (uint32_t)btMaxBlocks);
-				  k_bt<<<btBlocks, 128, 0, st>>>(c->dP, pools, states, probs, k, bta, cnt + C_BTTASK, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_bt++; }
+				  const uint32_t btBlocks = std::min<uint32_t>(nblk(k, BT2_BT_THREADS), (uint32_t)btMaxBlocks);
+				  k_bt<<<btBlocks, BT2_BT_THREADS, 0, st>>>(c->dP, pools, states, probs, k, bta, cnt + C_BTTASK, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_bt++; }
 			}
 			ncur = read_counters(c)[nxt ? C_EXT1 : C_EXT0];
 			cur = nxt;
@@ -414,7 +414,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		// ---- problem slots
 		const char* es = getenv("BT2GPU_SLOTS"); const char* eb = getenv("BT2GPU_BATCH");
 		size_t freeB = 0, totB = 0; CK(cudaMemGetInfo(&freeB, &totB));
-		const size_t perSlot = sizeof(Problem) + (size_t)BT2_CELL_BYTES + (size_t)BT2_MASK_WORDS * 4 + (size_t)BT2_BT_STACK * sizeof(BtFrame);
+		const size_t perSlot = sizeof(Problem) + (size_t)BT2_CELL_BYTES + (size_t)BT2_VIS_WORDS * 4 + (size_t)BT2_PC_WORDS * 4;
 		uint32_t slots = es ? (uint32_t)atoi(es) : 262144u;
 		const size_t budget = (freeB / 20) * 9;
 		if((size_t)slots * perSlot > budget) slots = (uint32_t)(budget / perSlot);
@@ -423,8 +423,8 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		c->maxBatch = eb ? (uint32_t)atoi(eb) : (1u << 20);
 		if(c->maxBatch < 1) c->maxBatch = 1;
 		c->probs.ensure((size_t)slots * sizeof(Problem)); c->cells.ensure((size_t)slots * BT2_CELL_BYTES);
-		c->masks.ensure((size_t)slots * BT2_MASK_WORDS * 4);
-		CK(cudaMemset(c->masks.p, 0, (size_t)slots * BT2_MASK_WORDS * 4)); c->stacks.ensure((size_t)slots * BT2_BT_STACK * sizeof(BtFrame));
+		c->vis.ensure((size_t)slots * BT2_VIS_WORDS * 4);
+		CK(cudaMemset(c->vis.p, 0, (size_t)slots * BT2_VIS_WORDS * 4)); c->pcache.ensure((size_t)slots * BT2_PC_WORDS * 4);
 		c->counters.ensure(C_N * 4); c->stats.ensure(32 * 8); c->pooltops.ensure(16); c->poolerr.ensure(4);
 		c->h_counters.ensure(C_N * 4);
 		CK(cudaDeviceSynchronize());
@@ -497,7 +497,7 @@ int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, c
 		CK(cudaMemsetAsync(ctx->stats.p, 0, 32 * 8, st));
 		FillArgs fa; fa.probs = ctx->probs.as<Problem>(); fa.nprob = nprob; fa.states = ctx->states.as<ReadState>(); fa.seq = ctx->seq.as<uint8_t>();
 		DBuf dbg; dbg.ensure((size_t)nprob * BT2_HEF_WORDS * 4);
-		fa.qual = ctx->qual.as<uint8_t>(); fa.cells = ctx->cells.as<uint8_t>(); fa.hef_dbg = dbg.as<uint32_t>(); fa.stats = ctx->stats.as<unsigned long long>() + 8;
+		fa.qual = ctx->qual.as<uint8_t>(); fa.cells = ctx->cells.as<uint8_t>(); fa.pcache = nullptr; fa.hef_dbg = dbg.as<uint32_t>(); fa.stats = ctx->stats.as<unsigned long long>() + 8;
 		k_fill<true><<<nblk(nprob, BT2_FILL_WARPS), BT2_FILL_WARPS * 32, 0, st>>>(ctx->dP, fa);
 		CK(cudaMemcpyAsync(hp.data(), ctx->probs.p, (size_t)nprob * sizeof(Problem), cudaMemcpyDeviceToHost, st));
 		std::vector<uint32_t> w(BT2_HEF_WORDS); std::vector<uint8_t> wc(BT2_CELL_BYTES);
@@ -529,7 +529,7 @@ void bt2gpu_destroy(bt2gpu_ctx* c) {
 	cudaDeviceSynchronize();
 	for(void* p : c->resident) cudaFree(p);
 	if(c->dP) cudaFree(c->dP);
-	DBuf* all[] = { &c->probs, &c->cells, &c->masks, &c->stacks, &c->seq, &c->qual, &c->seq_off, &c->rng_seed, &c->minsc, &c->nceil, &c->interval,
+	DBuf* all[] = { &c->probs, &c->cells, &c->vis, &c->pcache, &c->seq, &c->qual, &c->seq_off, &c->rng_seed, &c->minsc, &c->nceil, &c->interval,
 		&c->states, &c->scratch, &c->hits, &c->seedtasks, &c->lists[0], &c->lists[1], &c->lists[2], &c->lists[3], &c->lists[4], &c->lists[5], &c->lists[6], &c->counters, &c->stats,
 		&c->p_sav, &c->p_sorted, &c->p_rank, &c->p_sp2, &c->p_exr, &c->p_exrfw, &c->p_nsp, &c->p_nsmall, &c->p_nexr, &c->p_nelt, &c->p_nadd,
 		&c->s_ovr, &c->s_ovp, &c->s_ovv, &c->s_sr, &c->s_sv, &c->s_cv, &c->s_rn, &c->s_rcur, &c->s_rth, &c->s_rfl, &c->s_rco, &c->s_rcn, &c->s_rns, &c->s_mass, &c->s_elim,

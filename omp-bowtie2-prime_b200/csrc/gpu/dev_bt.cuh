@@ -7,44 +7,38 @@
 //   minsc tightening                                 aligner_sw_driver.cpp:588-618
 // The per-read edit scratch reproduces SwDriver::resGap_.alres.ned_.
 //
-// Written as a flat state machine (BtMachine::step does one unit of work: take a
-// candidate, one backtrace cell, or finish an alignment) so that the lanes of a warp,
-// each working on its own problem and pulling a new one when done, stay in one loop.
+// Written as a flat state machine so that the lanes of a warp, each working on its own
+// problem and pulling a new one when done, stay in one loop.  BtMachine::hot() does one
+// unit of the frequent work (start a candidate / one backtrace cell) with exactly two
+// independent memory reads (the cell's flag byte and, when the walk leaves it, the next
+// word of the visited map); everything a cell needs besides that (read and reference
+// characters for the edits) comes from a per-lane copy of the problem in shared memory.
+//
+// What the reference's per-cell backtrace state boils down to: the reference marks a cell
+// "reported through" on EVERY visit (aligner_swsse_ee_u8.cpp:1023), before it even knows
+// whether the walk can continue, and a marked cell rejects any later visit before its
+// H/E/F option masks are looked at (:801-804).  The option masks are therefore only ever
+// read on a cell's first visit, where they still hold the fill's comparison outcome, and
+// popping a branch frame returns to a cell that is already marked: the whole branch stack
+// unwinds one frame per step without trying anything.  So the state is ONE bit per cell
+// (visited), and a failed walk costs `number of branch frames` extra steps.  Nothing of a
+// popped frame is observable: the edit count after unwinding is discarded by res.reset().
 #pragma once
 #include "dev_common.cuh"
 
 #if defined(__CUDA_ARCH__)
 #define BT2_POPC(x) __popc(x)
-#define BT2_CTZ(x) (__ffs(x) - 1)
+#define BT2_CLZ(x) __clz(x)
 #else
 #define BT2_POPC(x) __builtin_popcount(x)
-#define BT2_CTZ(x) __builtin_ctz(x)
+#define BT2_CLZ(x) ((x) ? __builtin_clz(x) : 32)
 #endif
 
 namespace bt2 {
 
 enum { BT_CONTINUE = 0, BT_ROUND_END = 1 };
 enum { CT_E = 0, CT_F = 1, CT_H = 2 };
-enum { MV_DIAG, MV_REF_OPEN, MV_READ_OPEN, MV_RFGAP_EXT, MV_RDGAP_EXT };
 enum { BP_CAND = 0, BP_STEP = 1, BP_POST = 2, BP_DONE = 3 };
-
-struct BtFrame { uint32_t a, b, c, d; }; // packed branch-stack frame
-#define BT2_BT_STACK 400
-// Backtrace state per cell (what SSEMatrix::masks_ holds, aligner_swsse.h:140-420), one byte,
-// stored like the cell flags: one 32-bit word per (strip, step) = the bytes of its R rows plus
-// an 8-bit generation tag in byte 3.  A word whose tag differs from the launch's generation
-// reads as "all untouched", which replaces the reference's lazy per-row memset
-// (SSEMatrix::resetRow).  The byte:
-//   bit 0      reportedThru
-//   bits 1-3   H: 0 = mask not set, n+1 = set with n options still to try
-//   bits 4-5   E: 0 = not set, 1 = set / nothing left, 2 = set / gap extension left
-//   bits 6-7   F: likewise
-// The reference stores the remaining options as a bit set; since options are always consumed in
-// the same priority order (diagonal, ref open, ref extend, read open, read extend) and the set
-// of options at a cell is a function of the fill alone, "how many are left" is the same
-// information: the remaining ones are the lowest-priority n of the original set.
-#define BT2_MASK_GEN_MAX 255u
-#define BT2_MASK_WORDS (BT2_CELL_T * 64)
 
 struct ReadView {
 	const uint8_t* seq; const uint8_t* qual; uint32_t rdlen; bool fw;
@@ -56,17 +50,14 @@ struct ReadView {
 	BT2_HD int q(uint32_t row) const { return fw ? qual[row] : qual[rdlen - 1 - row]; }
 };
 
-BT2_HD int mask_to_char(int m) { return m > 15 ? 'N' : "?ACMGRSVTWYHKDBN"[m]; }
-BT2_HD int sc_mm(const DevParams& P, int rdc, int refm, int q) {
-	if(q < 0) q = 0; if(q > 255) q = 255;
-	return (rdc > 3 || refm > 15) ? P.npens[q] : P.mmpens[q];
-}
 BT2_HD int sc_score(const DevParams& P, int rdc, int refm, int q) {
 	if(q < 0) q = 0; if(q > 255) q = 255;
 	if(rdc > 3 || refm > 15) return -(int)P.npens[q];
 	if((refm & (1 << rdc)) != 0) return P.matchBonus;
 	return -(int)P.mmpens[q];
 }
+// character of a 0..4 code ("ACGTN"), no memory access
+BT2_HD uint32_t code_char(uint32_t c) { return (0x4e54474341ull >> (8u * (c > 4u ? 4u : c))) & 255u; }
 
 // left-end-based view of an edit list that may be stored 5'-based for a rc read
 struct EditView {
@@ -107,56 +98,66 @@ BT2_HD bool alns_overlap(const EditView& a, int64_t arefoff, const EditView& b, 
 	return false;
 }
 
-// the n lowest-priority options of an H-cell option set (priority high -> low: 16, 1, 4, 2, 8)
-BT2_HD int lowest_options(int orig, int n) {
-	int out = 0;
-	if(n > 0 && (orig & 8))  { out |= 8;  n--; }
-	if(n > 0 && (orig & 2))  { out |= 2;  n--; }
-	if(n > 0 && (orig & 4))  { out |= 4;  n--; }
-	if(n > 0 && (orig & 1))  { out |= 1;  n--; }
-	if(n > 0 && (orig & 16)) { out |= 16; n--; }
-	return out;
-}
-
 struct BtMachine {
 	// ---- context of the current problem
 	const DevParams* P; const Pools* pools;
 	const Problem* pb;
 	const uint8_t* cells;  // CF_* flag bytes of this problem (cell_index)
-	uint32_t* masks;       // backtrace state words of this problem slot (same indexing / 4)
-	BtFrame* stack;        // [BT2_BT_STACK]
+	uint32_t* vis;         // visited map of this problem slot (vis_word)
 	uint32_t* scratch;     // per-read edit scratch
 	const uint8_t* seqbase; const uint8_t* qualbase; // batch arrays
-	ReadState* rs;         // the read's state, updated in place
-	uint32_t gtag;         // generation << 24
+	ReadState* rs;         // the read's state; rnd / scratch marks are held here while the problem runs
+	const uint32_t* pc; uint32_t pcs; // character cache of the problem: word j at pc[j * pcs]
+	uint32_t gtag;         // generation << 16
+	int rdGapOpen, rdGapExt, rfGapOpen, rfGapExt;
 	// ---- cached per problem
 	int rows, R, glo, ghi, dlo, dhi; // gaps allowed in rows [glo,ghi); core diagonals: dlo <= col-row <= dhi
+	uint32_t ncand;
+	Rng rnd; uint32_t hw, attempts, nsteps;
 	// ---- nextAlignment state
 	int phase, result;
-	uint32_t cural, reseed;
+	uint32_t cural, reseed, candNext;
 	// ---- backtrace state (one attempt)
-	int row, col, origCol, ct, score, ns, readGaps, refGaps;
-	uint32_t cidx;         // cell_index(row,col); cidx & 3 = row % R, cidx >> 2 = state word
-	uint32_t nstack, ned, hw, fl, nsteps;
+	int row, col, origCol, ct, score, readGaps, refGaps;
+	uint32_t cidx;         // cell_index(row,col)
+	uint32_t ned, nbranch;
 	bool coreHit;
+	// ---- the word of the visited map the walk is in (written back when the walk leaves it)
+	uint32_t vwi, vwv;
 
 	BT2_HD ReadView view() const { ReadView v; v.seq = seqbase + rs->seq_off; v.qual = qualbase + rs->seq_off; v.rdlen = rs->rdlen; v.fw = pb->fw != 0; return v; }
-	BT2_HD uint32_t state_word(uint32_t widx) const { const uint32_t m = masks[widx]; return ((m & 0xff000000u) == gtag) ? m : gtag; }
-	BT2_HD void locate() { cidx = cell_index((uint32_t)row, (uint32_t)col, (uint32_t)R); } // (row, col) changed arbitrarily
-	BT2_HD void row_dec() { row--; if(cidx & 3u) cidx--; else cidx -= (BT2_CELL_T + 1) * 4u - (uint32_t)(R - 1); }
-	BT2_HD void col_dec() { col--; cidx -= 4u; }
+	BT2_HD void locate() { cidx = cell_index((uint32_t)row, (uint32_t)col, (uint32_t)R); }
 	BT2_HD void push_edit(uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scratch[ned] = x; ned++; if(ned > hw) hw = ned; }
+	BT2_HD uint32_t read_char(int r) const { return code_char(pc_read_code(pc, pcs, (uint32_t)r)); }
+	BT2_HD uint32_t ref_char(int c) const { return code_char(pc_ref_code(pc, pcs, (uint32_t)c)); }
+
+	// visited(row,col); marks the cell
+	BT2_HD bool visit() {
+		const uint32_t wi = vis_word((uint32_t)row, (uint32_t)col);
+		if(wi != vwi) {
+			if(vwi != BT2_NIL) vis[vwi] = vwv;
+			const uint32_t m = vis[wi];
+			vwv = ((m & 0xffff0000u) == gtag) ? m : gtag;
+			vwi = wi;
+		}
+		const uint32_t bit = 1u << ((uint32_t)row & 15u);
+		const bool was = (vwv & bit) != 0;
+		vwv |= bit;
+		return was;
+	}
 
 	// SwDriver::extendSeeds right after swa.align(): counters, then either the candidate loop or done
 	BT2_HD void begin() {
 		const DevParams& Pr = *P;
-		rows = pb->rows; R = pb->R;
+		rows = pb->rows; R = pb->R; ncand = pb->ncand;
 		glo = Pr.gapbar; ghi = rows - Pr.gapbar;
 		dlo = (pb->corel > 0 ? pb->corel : 0) - pb->triml; dhi = pb->corer - pb->triml;
-		nsteps = 0;
+		rdGapOpen = Pr.rdGapOpen; rdGapExt = Pr.rdGapExt; rfGapOpen = Pr.rfGapOpen; rfGapExt = Pr.rfGapExt;
+		nsteps = 0; attempts = 0; vwi = BT2_NIL; vwv = 0;
+		rnd = rs->rnd; hw = rs->scr_hw;
 		rs->dpCells += (uint64_t)pb->rows * pb->cols;
 		const int32_t bestCell = pb->lrmax - 255;
-		const bool found = bestCell >= pb->minsc && pb->ncand > 0;
+		const bool found = bestCell >= pb->minsc && ncand > 0;
 		rs->nExDps++;
 		result = BT_CONTINUE;
 		if(!found) {
@@ -169,145 +170,90 @@ struct BtMachine {
 		rs->nExDpSuccs++; rs->nDpLastSucc = rs->nExDps - 1;
 		if(rs->nDpFail > rs->nDpFailStreak) rs->nDpFailStreak = rs->nDpFail;
 		rs->nDpFail = 0;
-		cural = 0;
+		cural = 0; candNext = pb->cand[0];
 		phase = BP_CAND;
 	}
-	BT2_HD void finish() { rs->btSteps += nsteps; }
-
-	// SwAligner::nextAlignment: next candidate whose start cell has not been reported through
-	BT2_HD void cand() {
-		if(cural >= pb->ncand) { phase = BP_DONE; return; }
-		const int lastRow = rows - 1;
-		const int c0 = pb->cand[cural] & 255;
-		const uint32_t ci = cell_index((uint32_t)lastRow, (uint32_t)c0, (uint32_t)R);
-		if((state_word(ci >> 2) >> ((ci & 3u) * 8u)) & 1u) { cural++; return; }
-		Rng rnd = rs->rnd;
-		reseed = rnd.nextU32() + 1;
-		rnd.init(reseed);
-		rs->rnd = rnd;
-		row = lastRow; col = c0; origCol = c0; ct = CT_H;
-		locate();
-		score = 0; ns = 0; readGaps = 0; refGaps = 0; nstack = 0; ned = 0; hw = rs->scr_hw; coreHit = false;
-		rs->btAttempts++;
-		phase = BP_STEP;
+	BT2_HD void finish() {
+		rs->btSteps += nsteps; rs->btAttempts += attempts;
+		rs->rnd = rnd; rs->scr_hw = (uint16_t)hw;
 	}
+	BT2_HD void next_cand() { cural++; candNext = cural < ncand ? pb->cand[cural] : 0u; }
 
 	BT2_HD void attempt_failed() { // backtrace returned false: scratch keeps what was written (res.reset() only drops the count)
-		rs->scr_cur = (uint16_t)ned; rs->scr_hw = (uint16_t)hw;
-		rs->rnd.init(reseed + 1);
-		cural++;
+		rnd.init(reseed + 1);
+		next_cand();
 		phase = BP_CAND;
 	}
 
-	// the diagonal move / the last cell of a path: mismatch edit, N count, score
-	BT2_HD void take_cell() {
+	// the diagonal move / the last cell of a path: mismatch edit (its penalty and N count are taken in post())
+	BT2_HD void take_cell(uint32_t fl) {
 		if(fl & CF_MM) return;    // (fl holds the equalities that are TRUE: bit set = match; matchBonus is 0 end-to-end)
-		const ReadView rv = view();
-		const int readc = rv.rd((uint32_t)row), refm = pb->rf[col];
-		push_edit(pack_edit((uint32_t)row, (uint32_t)mask_to_char(refm), (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_MM));
-		score -= sc_mm(*P, readc, refm, rv.q((uint32_t)row) - 33);
-		if(readc > 3 || refm > 15) ns++;
+		push_edit(pack_edit((uint32_t)row, ref_char(col), read_char(row), BT2GPU_EDIT_MM));
 	}
 
-	// one cell of backtraceNucleotidesEnd2EndSseU8
-	BT2_HD void bt_step() {
+	// One unit of the frequent work: SwAligner::nextAlignment picking the next candidate whose start
+	// cell has not been reported through, and one cell of backtraceNucleotidesEnd2EndSseU8.
+	BT2_HD void hot() {
+		bool starting = false;
+		if(phase == BP_CAND) {
+			if(cural >= ncand) { phase = BP_DONE; return; }
+			row = rows - 1; col = (int)(candNext & 255u);
+			locate();
+			starting = true;
+		}
+		const uint32_t fl = ~(uint32_t)cells[cidx];
+		const bool was = visit();
+		if(starting) {
+			if(was) { next_cand(); return; }
+			reseed = rnd.nextU32() + 1;
+			rnd.init(reseed);
+			origCol = col; ct = CT_H;
+			score = 0; readGaps = 0; refGaps = 0; nbranch = 0; ned = 0; coreHit = false;
+			attempts++;
+			phase = BP_STEP;
+		}
 		nsteps++;
-		fl = ~(uint32_t)cells[cidx];
-		bool empty = false, canMoveThru = true, branch = false;
-		int cur = MV_DIAG;
-		const uint32_t widx = cidx >> 2, sh8 = (cidx & 3u) * 8u;
-		const uint32_t word = state_word(widx);
-		uint32_t st = (word >> sh8) & 0xffu;
-		if(st & 1u) {
-			canMoveThru = false;
-		} else if(row > 0) {
+		if(was) { nsteps += nbranch; attempt_failed(); return; } // every branch frame pops onto a marked cell
+		// options of the cell, highest priority first: bit4 diagonal, bit3 ref-gap open, bit2 ref-gap extend,
+		// bit1 read-gap open, bit0 read-gap extend (H); E and F cells have only their own open/extend pair
+		uint32_t opts = 0;
+		if(row > 0) {
+			const bool hasLeft = col > 0;
 			if(ct == CT_E) {
-				const int origMask = col > 0 ? (int)((fl >> 3) & 3u) : 0;
-				const uint32_t es = (st >> 4) & 3u;
-				const int mask = es ? (es == 2u ? 2 : 0) : origMask;
-				if(mask == 3)      { cur = MV_READ_OPEN; st = (st & ~(3u << 4)) | (2u << 4); branch = true; }
-				else if(mask == 2) { cur = MV_RDGAP_EXT; st = (st & ~(3u << 4)) | (1u << 4); }
-				else if(mask == 1) { cur = MV_READ_OPEN; st = (st & ~(3u << 4)) | (1u << 4); }
-				else { empty = true; canMoveThru = (origMask == 0); }
+				if(hasLeft) opts = ((fl >> 2) & 2u) | ((fl >> 4) & 1u);            // EO -> bit1, EX -> bit0
 			} else if(ct == CT_F) {
-				const int origMask = (int)((fl >> 5) & 3u);
-				const uint32_t fs = (st >> 6) & 3u;
-				const int mask = fs ? (fs == 2u ? 2 : 0) : origMask;
-				if(mask == 3)      { cur = MV_REF_OPEN;  st = (st & ~(3u << 6)) | (2u << 6); branch = true; }
-				else if(mask == 2) { cur = MV_RFGAP_EXT; st = (st & ~(3u << 6)) | (1u << 6); }
-				else if(mask == 1) { cur = MV_REF_OPEN;  st = (st & ~(3u << 6)) | (1u << 6); }
-				else { empty = true; canMoveThru = (origMask == 0); }
+				opts = ((fl >> 2) & 8u) | ((fl >> 4) & 4u);                      // FO -> bit3, FX -> bit2
 			} else {
-				const bool hasLeft = col > 0;
-				int origMask = 0;
-				if(row >= glo && row < ghi) { // gaps allowed in this row
-					if(fl & CF_HF) origMask |= (int)(((fl >> 5) & 1u) | (((fl >> 6) & 1u) << 2));             // H_up - rfgo (1), F_up - rfge (4)
-					if(hasLeft && (fl & CF_HE)) origMask |= (int)((((fl >> 3) & 1u) << 1) | (((fl >> 4) & 1u) << 3)); // H_left - rdgo (2), E_left - rdge (8)
+				if(row >= glo && row < ghi) {
+					if(fl & CF_HF) opts |= ((fl >> 2) & 8u) | ((fl >> 4) & 4u);
+					if(hasLeft && (fl & CF_HE)) opts |= ((fl >> 2) & 2u) | ((fl >> 4) & 1u);
 				}
-				if(hasLeft && (fl & CF_D)) origMask |= 16;
-				const uint32_t hs = (st >> 1) & 7u;
-				int mask = hs ? lowest_options(origMask, (int)hs - 1) : origMask;
-				int select = -1;
-				const int opts = BT2_POPC((unsigned)mask);
-				if(opts == 1) {
-					select = BT2_CTZ((unsigned)mask);
-					st = (st & ~(7u << 1)) | (1u << 1);
-				} else if(opts > 1) {
-					if(mask & 16) select = 4; else if(mask & 1) select = 0; else if(mask & 4) select = 2;
-					else if(mask & 2) select = 1; else select = 3;
-					st = (st & ~(7u << 1)) | ((uint32_t)opts << 1);   // opts - 1 options left
-					branch = true;
-				}
-				if(select != -1) {
-					cur = select == 4 ? MV_DIAG : select == 0 ? MV_REF_OPEN : select == 1 ? MV_READ_OPEN : select == 2 ? MV_RFGAP_EXT : MV_RDGAP_EXT;
-				} else { empty = true; canMoveThru = (origMask == 0); }
+				if(hasLeft && (fl & CF_D)) opts |= 16u;
 			}
 		}
-		masks[widx] = (word & ~(0xffu << sh8)) | ((st | 1u) << sh8);
-		if(!canMoveThru) {
-			if(nstack > 0) {
-				const BtFrame f = stack[--nstack];
-				ned = f.a & 1023u; row = (int)((f.a >> 10) & 255u); col = (int)((f.a >> 18) & 255u);
-				ct = (int)((f.a >> 26) & 3u); coreHit = ((f.a >> 28) & 1u) != 0;
-				readGaps = (int)(f.b & 1023u); refGaps = (int)((f.b >> 10) & 1023u); ns = (int)((f.b >> 20) & 1023u);
-				score = (int)f.c;
-				locate();
-				return; // retry the same cell with its remaining options
-			}
-			attempt_failed();
-			return;
-		}
-		// this cell joins the path: core-diagonal test (aligner_swsse_ee_u8.cpp:1229-1262) folded in
 		const int dg = col - row;
-		const bool cellCore = dg >= dlo && dg <= dhi;
-		if(empty || row == 0) { coreHit = coreHit || cellCore; phase = BP_POST; return; }
-		if(branch && nstack < BT2_BT_STACK) {
-			BtFrame f;
-			f.a = (ned & 1023u) | ((uint32_t)row << 10) | ((uint32_t)col << 18) | ((uint32_t)ct << 26) | ((coreHit ? 1u : 0u) << 28);
-			f.b = ((uint32_t)readGaps & 1023u) | (((uint32_t)refGaps & 1023u) << 10) | (((uint32_t)ns & 1023u) << 20);
-			f.c = (uint32_t)score; f.d = 0;
-			stack[nstack++] = f;
-		}
-		coreHit = coreHit || cellCore;
-		if(cur == MV_DIAG) {
+		coreHit = coreHit || (dg >= dlo && dg <= dhi); // core-diagonal test (aligner_swsse_ee_u8.cpp:1229-1262) folded in
+		if(opts == 0) { phase = BP_POST; cidx = fl; return; } // row 0, or a cell nothing leads into: the walk ends here
+		if(opts & (opts - 1u)) nbranch++;
+		const uint32_t sel = 31u - (uint32_t)BT2_CLZ(opts);
+		if(sel == 4u) {
 			ct = CT_H;
-			take_cell();
-			row_dec(); col_dec();
-		} else if(cur == MV_REF_OPEN || cur == MV_RFGAP_EXT) {
-			const int readc = view().rd((uint32_t)row);
-			push_edit(pack_edit((uint32_t)row, '-', (uint32_t)"ACGTN"[readc], BT2GPU_EDIT_REF_GAP));
-			row_dec();
-			ct = (cur == MV_REF_OPEN) ? CT_H : CT_F;
-			score -= (cur == MV_REF_OPEN) ? P->rfGapOpen : P->rfGapExt;
+			take_cell(fl);
+			row--; col--;
+		} else if(sel >= 2u) {
+			push_edit(pack_edit((uint32_t)row, '-', read_char(row), BT2GPU_EDIT_REF_GAP));
+			row--;
+			ct = (sel == 3u) ? CT_H : CT_F;
+			score -= (sel == 3u) ? rfGapOpen : rfGapExt;
 			refGaps++;
 		} else {
-			const int refm = pb->rf[col];
-			push_edit(pack_edit((uint32_t)row + 1, (uint32_t)mask_to_char(refm), '-', BT2GPU_EDIT_READ_GAP));
-			col_dec();
-			ct = (cur == MV_READ_OPEN) ? CT_H : CT_E;
-			score -= (cur == MV_READ_OPEN) ? P->rdGapOpen : P->rdGapExt;
+			push_edit(pack_edit((uint32_t)row + 1, ref_char(col), '-', BT2GPU_EDIT_READ_GAP));
+			col--;
+			ct = (sel == 1u) ? CT_H : CT_E;
+			score -= (sel == 1u) ? rdGapOpen : rdGapExt;
 			readGaps++;
 		}
+		locate();
 	}
 
 	// end of a backtrace that reached row 0 / an empty cell, then the rest of nextAlignment and of
@@ -315,21 +261,33 @@ struct BtMachine {
 	BT2_HD void post() {
 		const DevParams& Pr = *P; const Problem& p = *pb;
 		if(!coreHit) { attempt_failed(); return; }
-		take_cell();
+		take_cell(cidx); // (hot() left the last cell's flags in cidx)
 		ReadState& rs = *this->rs;
+		// mismatch penalties and N count of the path, from its edits
+		int ns = 0;
+		if(ned <= BT2_SCRATCH_EDITS) {
+			const ReadView rv = view();
+			for(uint32_t i = 0; i < ned; i++) {
+				const uint32_t x = scratch[i];
+				if(edit_type(x) != BT2GPU_EDIT_MM) continue;
+				const bool isn = edit_chr(x) == 'N' || edit_qchr(x) == 'N';
+				int q = rv.q(edit_pos(x)) - 33; if(q < 0) q = 0; if(q > 255) q = 255;
+				score -= isn ? (int)Pr.npens[q] : (int)Pr.mmpens[q];
+				if(isn) ns++;
+			}
+		}
 		if(ns > rs.nceil || ned > BT2_SCRATCH_EDITS) { attempt_failed(); return; } // (> capacity: beyond the reference's own DList<Edit,160>)
 		const uint32_t ne = ned;
 		for(uint32_t i = 0; i < ne / 2; i++) { const uint32_t t = scratch[i]; scratch[i] = scratch[ne - 1 - i]; scratch[ne - 1 - i] = t; }
-		rs.scr_cur = (uint16_t)ned; rs.scr_hw = (uint16_t)hw;
-		rs.rnd.init(reseed + 1);
-		cural++;
+		rnd.init(reseed + 1);
+		next_cand();
 		phase = BP_CAND;
 		AlnRec a;
 		a.fw = p.fw; a.tidx = p.tidx; a.refoff = (int64_t)col + p.refl;
 		a.score = score; a.ns = ns; a.gaps = readGaps + refGaps; a.edits = (int32_t)ne;
 		a.basesAligned = (int32_t)p.rows - (int32_t)ne;   // trimEnd is 0: candidates come from the last row only
 		int refns = 0;
-		for(int i = col; i <= origCol; i++) if(p.rf[i] > 15) refns++;
+		for(int i = col; i <= origCol; i++) if(pc_ref_code(pc, pcs, (uint32_t)i) > 3u) refns++;
 		a.refns = refns; a.n_edits = (uint16_t)ne;
 		if(!p.fw) { // AlnRes::invertEdits: scratch becomes 5'-based
 			for(uint32_t i = 0; i < ne / 2; i++) { const uint32_t t = scratch[i]; scratch[i] = scratch[ne - 1 - i]; scratch[ne - 1 - i] = t; }
@@ -384,8 +342,7 @@ struct BtMachine {
 
 	// one unit of work; returns false once the problem is finished (result / rs are final)
 	BT2_HD bool step() {
-		if(phase == BP_STEP) bt_step();
-		else if(phase == BP_CAND) cand();
+		if(phase == BP_STEP || phase == BP_CAND) hot();
 		else if(phase == BP_POST) post();
 		return phase != BP_DONE;
 	}

@@ -335,6 +335,25 @@ BT2_HD uint32_t cell_index(uint32_t r, uint32_t c, uint32_t R) {
 BT2_HD uint32_t hef_index(uint32_t r, uint32_t c, uint32_t R) { return cell_index(r, c, R); }
 #define BT2_HEF_WORDS BT2_CELL_BYTES
 
+// Visited map of the backtrace (SSEMatrix "reportedThrough", see dev_bt.cuh): one bit per cell,
+// diagonal-major so that a walk along a diagonal stays in one word for 16 steps and in one
+// 32-byte sector for its whole length.  Word = 16 rows of one diagonal in the low half and a
+// 16-bit generation tag in the high half: a word whose tag is not the launch's generation reads
+// as "nothing visited", so the map is never cleared between problems.
+#define BT2_VIS_WPD   ((BT2GPU_MAX_ROWS + 15) / 16)                  // words per diagonal
+#define BT2_VIS_WORDS ((BT2GPU_MAX_ROWS + BT2GPU_MAX_COLS) * BT2_VIS_WPD)
+#define BT2_VIS_GEN_MAX 65535u
+BT2_HD uint32_t vis_word(uint32_t r, uint32_t c) { return (c + BT2GPU_MAX_ROWS - r) * BT2_VIS_WPD + (r >> 4); }
+
+// Per-problem character cache handed from the fill to the backtrace: 4-bit codes, 8 per word.
+//   words [0, BT2_PC_RD)            read characters in the orientation of the problem's strand (0..3, 4 = N)
+//   words [BT2_PC_RD, BT2_PC_WORDS) reference characters of the window's columns (0..3, 4 = N)
+#define BT2_PC_RD    ((BT2GPU_MAX_ROWS + 7) / 8)
+#define BT2_PC_RF    ((BT2GPU_MAX_COLS + 8 + 7) / 8)
+#define BT2_PC_WORDS 48
+BT2_HD uint32_t pc_read_code(const uint32_t* pc, uint32_t stride, uint32_t row) { return (pc[(row >> 3) * stride] >> ((row & 7u) * 4u)) & 15u; }
+BT2_HD uint32_t pc_ref_code(const uint32_t* pc, uint32_t stride, uint32_t col) { return (pc[(BT2_PC_RD + (col >> 3)) * stride] >> ((col & 7u) * 4u)) & 15u; }
+
 // pools shared by the per-read kernels
 struct Pools {
 	Chunk*    chunks;   uint32_t* chunk_top;  uint32_t chunk_cap;

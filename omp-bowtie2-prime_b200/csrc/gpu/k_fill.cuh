@@ -35,6 +35,7 @@ struct FillArgs {
 	const uint8_t*   seq;
 	const uint8_t*   qual;
 	uint8_t*         cells;     // [nslots * BT2_CELL_BYTES]
+	uint32_t*        pcache;    // [nslots * BT2_PC_WORDS] character cache for the backtrace, or null
 	uint32_t*        hef_dbg;   // test hook only: [nslots * BT2_HEF_WORDS] H|E<<8|F<<16, or null
 	unsigned long long* stats;  // [0] problems [1] cells
 };
@@ -211,6 +212,19 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32) k_fill(const DevParams* _
 		sh.hlast[c] = 0;
 	}
 	__syncwarp();
+	if(a.pcache) { // the problem's characters as 4-bit codes, for the backtrace's edits (dev_common.cuh)
+		uint32_t* pcw = a.pcache + (size_t)slot * BT2_PC_WORDS;
+		uint32_t wr = 0, wf = 0;
+		#pragma unroll
+		for(int i = 0; i < 8; i++) {
+			const int r = (int)lane * 8 + i, c = (int)lane * 8 + i;
+			const uint32_t rc = r < rows ? (uint32_t)sh.rdc[r] : 0u;
+			wr |= (rc > 3u ? 4u : rc) << (4 * i);
+			wf |= (c < cols ? (uint32_t)sh.refc[c] : 0u) << (4 * i);
+		}
+		if(lane < BT2_PC_RD) pcw[lane] = wr;
+		if(lane < BT2_PC_RF) pcw[BT2_PC_RD + lane] = wf;
+	}
 	uint8_t* cells = a.cells + (size_t)slot * BT2_CELL_BYTES;
 	uint32_t* hef = DBG ? a.hef_dbg + (size_t)slot * BT2_HEF_WORDS : nullptr;
 	if(R == 1) fill_body<1, DBG>(P, pb, sh, cells, hef, lane);

@@ -19,7 +19,7 @@
 
 using namespace bt2;
 
-static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_t* cells) {
+static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_t* cells, uint32_t* pcache) {
 	const int rows = pb.rows, cols = pb.cols; const uint32_t R = pb.R;
 	auto subs = [](int a, int b) { int v = a - b; return v < 0 ? 0 : v; };
 	std::vector<int> Hprev(rows, 0), Eprev(rows, 0), Fprev(rows, 0), Hcur(rows), Ecur(rows), Fcur(rows), Eleft(rows, 0), Ehere(rows, 0);
@@ -59,6 +59,10 @@ static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_
 		if(lr - 255 >= pb.minsc) cand.push_back((uint16_t)((lr << 8) | j));
 		Hprev.swap(Hcur); Eprev.swap(Ecur); Fprev.swap(Fcur); Eleft = Ehere;
 	}
+	// character cache (what K_fill leaves for the backtrace's edits)
+	for(int j = 0; j < BT2_PC_WORDS; j++) pcache[j] = 0;
+	for(int r = 0; r < rows; r++) { const uint32_t c = (uint32_t)rv.rd(r); pcache[r >> 3] |= (c > 3 ? 4u : c) << ((r & 7) * 4); }
+	for(int j = 0; j < cols; j++) { const uint32_t m = pb.rf[j]; const uint32_t c = m > 15 ? 4u : (uint32_t)__builtin_ctz(m); pcache[BT2_PC_RD + (j >> 3)] |= c << ((j & 7) * 4); }
 	std::sort(cand.begin(), cand.end(), [](uint16_t a, uint16_t b) { return a > b; });
 	pb.lrmax = lrmax; pb.ncand = (uint32_t)cand.size();
 	for(size_t i = 0; i < cand.size(); i++) pb.cand[i] = cand[i];
@@ -107,7 +111,7 @@ int main(int argc, char** argv) {
 	const uint32_t MI = BT2GPU_MAX_ITER + 8;
 	std::vector<uint16_t> ov_rng(2 * MI), ov_pos(2 * MI), ov_val(2 * MI), seen_rng(MI), seen_val(MI), conv_val(MI), r_n(W), r_cur(W), r_thresh(W), r_conv_n(W), r_nseen(W);
 	std::vector<uint8_t> r_flags(W), elim(W); std::vector<uint32_t> r_conv_off(W); std::vector<double> mass(W);
-	std::vector<uint8_t> cells(BT2_CELL_BYTES); std::vector<uint32_t> masks(BT2_MASK_WORDS, 0); uint32_t gen = 0; std::vector<BtFrame> stack(BT2_BT_STACK);
+	std::vector<uint8_t> cells(BT2_CELL_BYTES); std::vector<uint32_t> vis(BT2_VIS_WORDS, 0), pcache(BT2_PC_WORDS, 0); uint32_t gen = 0;
 	orc::WorkCounters wc;
 	for(uint32_t ri = 0; ri < n; ri++) {
 		ReadState& rs = states[ri];
@@ -154,12 +158,12 @@ int main(int argc, char** argv) {
 			while(true) {
 				Problem pb; pb.read = ri;
 				if(advance(P, ix, rf, pools, rs, pb) == ADV_ROUND_END) break;
-				BtMachine m; m.P = &P; m.pools = &pools; m.pb = &pb; m.cells = cells.data(); m.masks = masks.data(); m.stack = stack.data();
-				if(++gen > BT2_MASK_GEN_MAX) { std::fill(masks.begin(), masks.end(), 0u); gen = 1; }
-				m.gtag = gen << 24;
+				BtMachine m; m.P = &P; m.pools = &pools; m.pb = &pb; m.cells = cells.data(); m.vis = vis.data(); m.pc = pcache.data(); m.pcs = 1;
+				if(++gen > BT2_VIS_GEN_MAX) { std::fill(vis.begin(), vis.end(), 0u); gen = 1; }
+				m.gtag = gen << 16;
 				m.scratch = scratch.data() + (size_t)ri * BT2_SCRATCH_EDITS;
 				m.seqbase = in->seq; m.qualbase = in->qual; m.rs = &rs;
-				fill_emu(P, pb, m.view(), cells.data());
+				fill_emu(P, pb, m.view(), cells.data(), pcache.data());
 				m.begin();
 				while(m.phase != BP_DONE && m.step()) { }
 				m.finish();
