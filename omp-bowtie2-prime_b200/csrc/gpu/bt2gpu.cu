@@ -248,11 +248,12 @@ void do_run(bt2gpu_ctx* c) {
 	sa.r_n = c->s_rn.as<uint16_t>(); sa.r_cur = c->s_rcur.as<uint16_t>(); sa.r_thresh = c->s_rth.as<uint16_t>(); sa.r_flags = c->s_rfl.as<uint8_t>();
 	sa.r_conv_off = c->s_rco.as<uint32_t>(); sa.r_conv_n = c->s_rcn.as<uint16_t>(); sa.r_nseen = c->s_rns.as<uint16_t>();
 	sa.mass = c->s_mass.as<double>(); sa.elim = c->s_elim.as<uint8_t>();
-	BtArrays bta; bta.cells = c->cells.as<uint8_t>(); bta.vis = c->vis.as<uint32_t>(); bta.gen = 0; bta.pcache = c->pcache.as<uint32_t>();
-	bta.scratch = c->scratch.as<uint32_t>(); bta.seq = ba.seq; bta.qual = ba.qual;
+	BtCtx bcx; bcx.P = c->P; bcx.pools = c->pools; bcx.states = states; bcx.probs = c->probs.as<Problem>();
+	bcx.cells = c->cells.as<uint8_t>(); bcx.vis = c->vis.as<uint32_t>(); bcx.pcache = c->pcache.as<uint32_t>();
+	bcx.scratch = c->scratch.as<uint32_t>(); bcx.seq = ba.seq; bcx.qual = ba.qual; bcx.gtag = 0;
 	Problem* probs = c->probs.as<Problem>();
 	const Pools pools = c->pools;
-	int seedBlocks = 0, btMaxBlocks = 0; { int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device); seedBlocks = nsm * 8; btMaxBlocks = nsm * 8; }
+	int seedBlocks = 0, btMaxBlocks = 0; { int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device); seedBlocks = nsm * 8; btMaxBlocks = nsm * BT2_BT_BLOCKS_PER_SM; }
 
 	k_begin<<<nblk(n, 256), 256, 0, st>>>(ba, states, L[0], cnt + C_CAND0); LAUNCH(c);
 	uint32_t ncand = read_counters(c)[C_CAND0];
@@ -299,10 +300,10 @@ void do_run(bt2gpu_ctx* c) {
 				  k_fill<false><<<nblk(k, BT2_FILL_WARPS), BT2_FILL_WARPS * 32, 0, st>>>(c->dP, fa); LAUNCH(c); c->ctr.n_fill++; }
 				{ Phase ph(c, PH_BT);
 				  if(++c->btgen > BT2_VIS_GEN_MAX) { CK(cudaMemsetAsync(c->vis.p, 0, (size_t)c->nslots * BT2_VIS_WORDS * 4, st)); c->btgen = 1; }
-				  bta.gen = c->btgen;
+				  bcx.gtag = c->btgen << 16;
 				  zero_counter(c, C_BTTASK);
 				  const uint32_t btBlocks = std::min<uint32_t>(nblk(k, BT2_BT_THREADS), (uint32_t)btMaxBlocks);
-				  k_bt<<<btBlocks, BT2_BT_THREADS, 0, st>>>(c->dP, pools, states, probs, k, bta, cnt + C_BTTASK, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_bt++; }
+				  k_bt<<<btBlocks, BT2_BT_THREADS, 0, st>>>(bcx, k, cnt + C_BTTASK, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_bt++; }
 			}
 			ncur = read_counters(c)[nxt ? C_EXT1 : C_EXT0];
 			cur = nxt;

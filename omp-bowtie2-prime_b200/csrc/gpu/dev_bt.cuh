@@ -98,102 +98,126 @@ BT2_HD bool alns_overlap(const EditView& a, int64_t arefoff, const EditView& b, 
 	return false;
 }
 
+// launch-wide context of the backtrace stage (device: one kernel parameter, i.e. constant bank)
+struct BtCtx {
+	DevParams P;
+	Pools pools;
+	ReadState* states; const Problem* probs;
+	const uint8_t* cells;    // [nslots * BT2_CELL_BYTES] CF_* flag bytes (cell_index)
+	uint32_t* vis;           // [nslots * BT2_VIS_WORDS] visited maps (vis_index)
+	const uint32_t* pcache;  // [nslots * BT2_PC_WORDS]
+	uint32_t* scratch;       // [nreads * BT2_SCRATCH_EDITS] per-read edit scratch
+	const uint8_t* seq; const uint8_t* qual; // batch arrays
+	uint32_t gtag;           // generation << 16
+};
+
 struct BtMachine {
-	// ---- context of the current problem
-	const DevParams* P; const Pools* pools;
-	const Problem* pb;
-	const uint8_t* cells;  // CF_* flag bytes of this problem (cell_index)
-	uint32_t* vis;         // visited map of this problem slot (vis_word)
-	uint32_t* scratch;     // per-read edit scratch
-	const uint8_t* seqbase; const uint8_t* qualbase; // batch arrays
-	ReadState* rs;         // the read's state; rnd / scratch marks are held here while the problem runs
+	// ---- the current problem
+	uint32_t slot, read;
 	const uint32_t* pc; uint32_t pcs; // character cache of the problem: word j at pc[j * pcs]
-	uint32_t gtag;         // generation << 16
-	int rdGapOpen, rdGapExt, rfGapOpen, rfGapExt;
+	// two 16-byte chunks of the cell array: the one the walk is in and the one it is predicted to enter next
+	// (asynchronous copy issued when a chunk is entered, so that its latency overlaps the steps in between)
+	uint8_t* cbuf; uint32_t cstride;  // chunk b of this lane at cbuf + b * cstride
+	uint32_t ctag0, ctag1, ccur;
+	// the word of the visited map the walk is in (written back when the walk leaves it)
+	uint32_t vwi, vwv;
 	// ---- cached per problem
-	int rows, R, glo, ghi, dlo, dhi; // gaps allowed in rows [glo,ghi); core diagonals: dlo <= col-row <= dhi
+	int rows, R, dlo, dhi;            // core diagonals: dlo <= col-row <= dhi
 	uint32_t ncand;
 	Rng rnd; uint32_t hw, attempts, nsteps;
 	// ---- nextAlignment state
 	int phase, result;
-	uint32_t cural, reseed, candNext;
+	uint32_t cural, reseed, candNext, candAhead;
 	// ---- backtrace state (one attempt)
-	int row, col, origCol, ct, score, readGaps, refGaps;
-	uint32_t cidx;         // cell_index(row,col)
-	uint32_t ned, nbranch;
+	int row, col, origCol, ct, score;
+	uint32_t cidx;                    // cell_index(row,col)
+	uint32_t ned, nbranch, lastfl;
 	bool coreHit;
-	// ---- the word of the visited map the walk is in (written back when the walk leaves it)
-	uint32_t vwi, vwv;
 
-	BT2_HD ReadView view() const { ReadView v; v.seq = seqbase + rs->seq_off; v.qual = qualbase + rs->seq_off; v.rdlen = rs->rdlen; v.fw = pb->fw != 0; return v; }
+	BT2_HD const Problem& pb(const BtCtx& cx) const { return cx.probs[slot]; }
+	BT2_HD ReadState& rs(const BtCtx& cx) const { return cx.states[read]; }
+	BT2_HD uint32_t* scratch(const BtCtx& cx) const { return cx.scratch + (size_t)read * BT2_SCRATCH_EDITS; }
+	BT2_HD ReadView view(const BtCtx& cx) const {
+		const ReadState& r = rs(cx);
+		ReadView v; v.seq = cx.seq + r.seq_off; v.qual = cx.qual + r.seq_off; v.rdlen = r.rdlen; v.fw = pb(cx).fw != 0; return v;
+	}
 	BT2_HD void locate() { cidx = cell_index((uint32_t)row, (uint32_t)col, (uint32_t)R); }
-	BT2_HD void push_edit(uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scratch[ned] = x; ned++; if(ned > hw) hw = ned; }
+	BT2_HD void push_edit(const BtCtx& cx, uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scratch(cx)[ned] = x; ned++; }
 	BT2_HD uint32_t read_char(int r) const { return code_char(pc_read_code(pc, pcs, (uint32_t)r)); }
 	BT2_HD uint32_t ref_char(int c) const { return code_char(pc_ref_code(pc, pcs, (uint32_t)c)); }
 
-	// visited(row,col); marks the cell
-	BT2_HD bool visit() {
-		const uint32_t wi = vis_word((uint32_t)row, (uint32_t)col);
-		if(wi != vwi) {
-			if(vwi != BT2_NIL) vis[vwi] = vwv;
-			const uint32_t m = vis[wi];
-			vwv = ((m & 0xffff0000u) == gtag) ? m : gtag;
-			vwi = wi;
-		}
-		const uint32_t bit = 1u << ((uint32_t)row & 15u);
-		const bool was = (vwv & bit) != 0;
-		vwv |= bit;
-		return was;
+	BT2_HD void chunk_fetch(const BtCtx& cx, uint32_t b, uint32_t ch) {
+		const uint8_t* src = cx.cells + (size_t)slot * BT2_CELL_BYTES + (size_t)ch * 16u;
+#if defined(__CUDA_ARCH__)
+		const uint32_t sa = (uint32_t)__cvta_generic_to_shared(cbuf + b * cstride);
+		asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"(sa), "l"(src) : "memory");
+#else
+		for(int i = 0; i < 16; i++) cbuf[b * cstride + i] = src[i];
+#endif
+	}
+	BT2_HD static void chunk_wait() {
+#if defined(__CUDA_ARCH__)
+		asm volatile("cp.async.wait_all;" ::: "memory");
+#endif
+	}
+	// chunk the walk most likely enters after the one holding (row, col): the next strip up the diagonal
+	BT2_HD uint32_t predict_chunk() const {
+		const uint32_t k = cidx & 3u;
+		const int r2 = row - (int)k - 1, c2 = col - (int)k - 1;
+		return (r2 >= 0 && c2 >= 0) ? (cell_index((uint32_t)r2, (uint32_t)c2, (uint32_t)R) >> 4) : BT2_NIL;
 	}
 
 	// SwDriver::extendSeeds right after swa.align(): counters, then either the candidate loop or done
-	BT2_HD void begin() {
-		const DevParams& Pr = *P;
-		rows = pb->rows; R = pb->R; ncand = pb->ncand;
-		glo = Pr.gapbar; ghi = rows - Pr.gapbar;
-		dlo = (pb->corel > 0 ? pb->corel : 0) - pb->triml; dhi = pb->corer - pb->triml;
-		rdGapOpen = Pr.rdGapOpen; rdGapExt = Pr.rdGapExt; rfGapOpen = Pr.rfGapOpen; rfGapExt = Pr.rfGapExt;
-		nsteps = 0; attempts = 0; vwi = BT2_NIL; vwv = 0;
-		rnd = rs->rnd; hw = rs->scr_hw;
-		rs->dpCells += (uint64_t)pb->rows * pb->cols;
-		const int32_t bestCell = pb->lrmax - 255;
-		const bool found = bestCell >= pb->minsc && ncand > 0;
-		rs->nExDps++;
+	BT2_HD void begin(const BtCtx& cx) {
+		const DevParams& Pr = cx.P; const Problem& p = pb(cx); ReadState& r = rs(cx);
+		rows = p.rows; R = p.R; ncand = p.ncand;
+		dlo = (p.corel > 0 ? p.corel : 0) - p.triml; dhi = p.corer - p.triml;
+		nsteps = 0; attempts = 0; vwi = BT2_NIL; vwv = 0; ctag0 = BT2_NIL; ctag1 = BT2_NIL; ccur = 0;
+		rnd = r.rnd; hw = r.scr_hw;
+		r.dpCells += (uint64_t)p.rows * p.cols;
+		const int32_t bestCell = p.lrmax - 255;
+		const bool found = bestCell >= p.minsc && ncand > 0;
+		r.nExDps++;
 		result = BT_CONTINUE;
 		if(!found) {
-			rs->nExDpFails++; rs->nDpFail++;
-			if(rs->nDpFail >= (uint32_t)Pr.streak) { rs->status = BT2GPU_ST_SOFT_LIMIT; result = BT_ROUND_END; }
-			else if(bestCell > rs->bestLtMinsc) rs->bestLtMinsc = bestCell;
+			r.nExDpFails++; r.nDpFail++;
+			if(r.nDpFail >= (uint32_t)Pr.streak) { r.status = BT2GPU_ST_SOFT_LIMIT; result = BT_ROUND_END; }
+			else if(bestCell > r.bestLtMinsc) r.bestLtMinsc = bestCell;
 			phase = BP_DONE;
 			return;
 		}
-		rs->nExDpSuccs++; rs->nDpLastSucc = rs->nExDps - 1;
-		if(rs->nDpFail > rs->nDpFailStreak) rs->nDpFailStreak = rs->nDpFail;
-		rs->nDpFail = 0;
-		cural = 0; candNext = pb->cand[0];
+		r.nExDpSuccs++; r.nDpLastSucc = r.nExDps - 1;
+		if(r.nDpFail > r.nDpFailStreak) r.nDpFailStreak = r.nDpFail;
+		r.nDpFail = 0;
+		cural = 0; candNext = p.cand[0]; candAhead = ncand > 1 ? p.cand[1] : 0u;
 		phase = BP_CAND;
 	}
-	BT2_HD void finish() {
-		rs->btSteps += nsteps; rs->btAttempts += attempts;
-		rs->rnd = rnd; rs->scr_hw = (uint16_t)hw;
+	BT2_HD void finish(const BtCtx& cx) {
+		ReadState& r = rs(cx);
+		r.btSteps += nsteps; r.btAttempts += attempts;
+		r.rnd = rnd; r.scr_hw = (uint16_t)hw;
 	}
-	BT2_HD void next_cand() { cural++; candNext = cural < ncand ? pb->cand[cural] : 0u; }
+	// candNext = cand[cural]; candAhead = cand[cural + 1], loaded one candidate early
+	BT2_HD void next_cand(const BtCtx& cx) { cural++; candNext = candAhead; candAhead = cural + 1 < ncand ? pb(cx).cand[cural + 1] : 0u; }
 
-	BT2_HD void attempt_failed() { // backtrace returned false: scratch keeps what was written (res.reset() only drops the count)
+	BT2_HD void attempt_failed(const BtCtx& cx) { // backtrace returned false: scratch keeps what was written (res.reset() only drops the count)
+		if(ned > hw) hw = ned;
 		rnd.init(reseed + 1);
-		next_cand();
+		next_cand(cx);
 		phase = BP_CAND;
 	}
 
 	// the diagonal move / the last cell of a path: mismatch edit (its penalty and N count are taken in post())
-	BT2_HD void take_cell(uint32_t fl) {
+	BT2_HD void take_cell(const BtCtx& cx, uint32_t fl) {
 		if(fl & CF_MM) return;    // (fl holds the equalities that are TRUE: bit set = match; matchBonus is 0 end-to-end)
-		push_edit(pack_edit((uint32_t)row, ref_char(col), read_char(row), BT2GPU_EDIT_MM));
+		push_edit(cx, pack_edit((uint32_t)row, ref_char(col), read_char(row), BT2GPU_EDIT_MM));
 	}
 
 	// One unit of the frequent work: SwAligner::nextAlignment picking the next candidate whose start
 	// cell has not been reported through, and one cell of backtraceNucleotidesEnd2EndSseU8.
-	BT2_HD void hot() {
+	// All memory the cell needs is requested up front and waited for at ONE point, so that the lanes
+	// of a warp (each in its own problem) pay one memory latency per call, not one per kind of miss.
+	BT2_HD void hot(const BtCtx& cx) {
 		bool starting = false;
 		if(phase == BP_CAND) {
 			if(cural >= ncand) { phase = BP_DONE; return; }
@@ -201,90 +225,110 @@ struct BtMachine {
 			locate();
 			starting = true;
 		}
-		const uint32_t fl = ~(uint32_t)cells[cidx];
-		const bool was = visit();
+		// ---- memory stage
+		uint32_t* const vis = cx.vis + (size_t)slot * BT2_VIS_WORDS;
+		const uint32_t wi = vis_index((uint32_t)row, (uint32_t)col);
+		const uint32_t ch = cidx >> 4;
+		const uint32_t curtag = ccur ? ctag1 : ctag0, othtag = ccur ? ctag0 : ctag1;
+		const bool needV = wi != vwi, newC = ch != curtag, needC = newC && ch != othtag;
+		uint32_t mv = 0;
+		if(needV) { if(vwi != BT2_NIL) vis[vwi] = vwv; mv = vis[wi]; }
+		if(needC) chunk_fetch(cx, ccur, ch);
+		chunk_wait();
+		if(needV) { vwv = ((mv & 0xffff0000u) == cx.gtag) ? mv : cx.gtag; vwi = wi; }
+		if(newC) {
+			if(needC) { if(ccur) ctag1 = ch; else ctag0 = ch; } else ccur ^= 1u;
+			const uint32_t nx = predict_chunk();
+			if(nx != BT2_NIL) chunk_fetch(cx, ccur ^ 1u, nx);
+			if(ccur) ctag0 = nx; else ctag1 = nx;
+		}
+		const uint32_t fl = ~(uint32_t)*(volatile const uint8_t*)(cbuf + ccur * cstride + (cidx & 15u));
+		const uint32_t bit = vis_bit((uint32_t)row, (uint32_t)col);
+		const bool was = (vwv & bit) != 0;
+		vwv |= bit;
+		// ---- candidate start
 		if(starting) {
-			if(was) { next_cand(); return; }
+			if(was) { next_cand(cx); return; }
 			reseed = rnd.nextU32() + 1;
 			rnd.init(reseed);
 			origCol = col; ct = CT_H;
-			score = 0; readGaps = 0; refGaps = 0; nbranch = 0; ned = 0; coreHit = false;
+			score = 0; nbranch = 0; ned = 0; coreHit = false;
 			attempts++;
 			phase = BP_STEP;
 		}
 		nsteps++;
-		if(was) { nsteps += nbranch; attempt_failed(); return; } // every branch frame pops onto a marked cell
+		if(was) { nsteps += nbranch; attempt_failed(cx); return; } // every branch frame pops onto a marked cell
 		// options of the cell, highest priority first: bit4 diagonal, bit3 ref-gap open, bit2 ref-gap extend,
 		// bit1 read-gap open, bit0 read-gap extend (H); E and F cells have only their own open/extend pair
 		uint32_t opts = 0;
 		if(row > 0) {
 			const bool hasLeft = col > 0;
-			if(ct == CT_E) {
-				if(hasLeft) opts = ((fl >> 2) & 2u) | ((fl >> 4) & 1u);            // EO -> bit1, EX -> bit0
-			} else if(ct == CT_F) {
-				opts = ((fl >> 2) & 8u) | ((fl >> 4) & 4u);                      // FO -> bit3, FX -> bit2
-			} else {
-				if(row >= glo && row < ghi) {
-					if(fl & CF_HF) opts |= ((fl >> 2) & 8u) | ((fl >> 4) & 4u);
-					if(hasLeft && (fl & CF_HE)) opts |= ((fl >> 2) & 2u) | ((fl >> 4) & 1u);
+			const uint32_t eopts = hasLeft ? (((fl >> 2) & 2u) | ((fl >> 4) & 1u)) : 0u;   // EO -> bit1, EX -> bit0
+			const uint32_t fopts = ((fl >> 2) & 8u) | ((fl >> 4) & 4u);                      // FO -> bit3, FX -> bit2
+			if(ct == CT_E) opts = eopts;
+			else if(ct == CT_F) opts = fopts;
+			else {
+				if(row >= cx.P.gapbar && row < rows - cx.P.gapbar) { // gaps allowed in this row
+					if(fl & CF_HF) opts |= fopts;
+					if(fl & CF_HE) opts |= eopts;
 				}
 				if(hasLeft && (fl & CF_D)) opts |= 16u;
 			}
 		}
 		const int dg = col - row;
 		coreHit = coreHit || (dg >= dlo && dg <= dhi); // core-diagonal test (aligner_swsse_ee_u8.cpp:1229-1262) folded in
-		if(opts == 0) { phase = BP_POST; cidx = fl; return; } // row 0, or a cell nothing leads into: the walk ends here
+		if(opts == 0) { phase = BP_POST; lastfl = fl; return; } // row 0, or a cell nothing leads into: the walk ends here
 		if(opts & (opts - 1u)) nbranch++;
 		const uint32_t sel = 31u - (uint32_t)BT2_CLZ(opts);
 		if(sel == 4u) {
 			ct = CT_H;
-			take_cell(fl);
+			take_cell(cx, fl);
 			row--; col--;
 		} else if(sel >= 2u) {
-			push_edit(pack_edit((uint32_t)row, '-', read_char(row), BT2GPU_EDIT_REF_GAP));
+			push_edit(cx, pack_edit((uint32_t)row, '-', read_char(row), BT2GPU_EDIT_REF_GAP));
 			row--;
 			ct = (sel == 3u) ? CT_H : CT_F;
-			score -= (sel == 3u) ? rfGapOpen : rfGapExt;
-			refGaps++;
+			score -= (sel == 3u) ? cx.P.rfGapOpen : cx.P.rfGapExt;
 		} else {
-			push_edit(pack_edit((uint32_t)row + 1, ref_char(col), '-', BT2GPU_EDIT_READ_GAP));
+			push_edit(cx, pack_edit((uint32_t)row + 1, ref_char(col), '-', BT2GPU_EDIT_READ_GAP));
 			col--;
 			ct = (sel == 1u) ? CT_H : CT_E;
-			score -= (sel == 1u) ? rdGapOpen : rdGapExt;
-			readGaps++;
+			score -= (sel == 1u) ? cx.P.rdGapOpen : cx.P.rdGapExt;
 		}
 		locate();
 	}
 
 	// end of a backtrace that reached row 0 / an empty cell, then the rest of nextAlignment and of
 	// the extendSeeds body for one alignment: redundancy, report, policy, tighten
-	BT2_HD void post() {
-		const DevParams& Pr = *P; const Problem& p = *pb;
-		if(!coreHit) { attempt_failed(); return; }
-		take_cell(cidx); // (hot() left the last cell's flags in cidx)
-		ReadState& rs = *this->rs;
-		// mismatch penalties and N count of the path, from its edits
-		int ns = 0;
+	BT2_HD void post(const BtCtx& cx) {
+		const DevParams& Pr = cx.P; const Problem& p = pb(cx); const Pools* pools = &cx.pools;
+		uint32_t* const scratch = this->scratch(cx);
+		if(!coreHit) { attempt_failed(cx); return; }
+		take_cell(cx, lastfl);
+		ReadState& rs = this->rs(cx);
+		// mismatch penalties, N count and gap counts of the path, from its edits
+		int ns = 0, gaps = 0;
 		if(ned <= BT2_SCRATCH_EDITS) {
-			const ReadView rv = view();
+			const ReadView rv = view(cx);
 			for(uint32_t i = 0; i < ned; i++) {
 				const uint32_t x = scratch[i];
-				if(edit_type(x) != BT2GPU_EDIT_MM) continue;
+				if(edit_type(x) != BT2GPU_EDIT_MM) { gaps++; continue; }
 				const bool isn = edit_chr(x) == 'N' || edit_qchr(x) == 'N';
 				int q = rv.q(edit_pos(x)) - 33; if(q < 0) q = 0; if(q > 255) q = 255;
 				score -= isn ? (int)Pr.npens[q] : (int)Pr.mmpens[q];
 				if(isn) ns++;
 			}
 		}
-		if(ns > rs.nceil || ned > BT2_SCRATCH_EDITS) { attempt_failed(); return; } // (> capacity: beyond the reference's own DList<Edit,160>)
+		if(ns > rs.nceil || ned > BT2_SCRATCH_EDITS) { attempt_failed(cx); return; } // (> capacity: beyond the reference's own DList<Edit,160>)
 		const uint32_t ne = ned;
 		for(uint32_t i = 0; i < ne / 2; i++) { const uint32_t t = scratch[i]; scratch[i] = scratch[ne - 1 - i]; scratch[ne - 1 - i] = t; }
+		if(ned > hw) hw = ned;
 		rnd.init(reseed + 1);
-		next_cand();
+		next_cand(cx);
 		phase = BP_CAND;
 		AlnRec a;
 		a.fw = p.fw; a.tidx = p.tidx; a.refoff = (int64_t)col + p.refl;
-		a.score = score; a.ns = ns; a.gaps = readGaps + refGaps; a.edits = (int32_t)ne;
+		a.score = score; a.ns = ns; a.gaps = gaps; a.edits = (int32_t)ne;
 		a.basesAligned = (int32_t)p.rows - (int32_t)ne;   // trimEnd is 0: candidates come from the last row only
 		int refns = 0;
 		for(int i = col; i <= origCol; i++) if(pc_ref_code(pc, pcs, (uint32_t)i) > 3u) refns++;
@@ -340,10 +384,10 @@ struct BtMachine {
 		}
 	}
 
-	// one unit of work; returns false once the problem is finished (result / rs are final)
-	BT2_HD bool step() {
-		if(phase == BP_STEP || phase == BP_CAND) hot();
-		else if(phase == BP_POST) post();
+	// one unit of work; returns false once the problem is finished (result / the read's state are final)
+	BT2_HD bool step(const BtCtx& cx) {
+		if(phase == BP_STEP || phase == BP_CAND) hot(cx);
+		else if(phase == BP_POST) post(cx);
 		return phase != BP_DONE;
 	}
 };

@@ -319,31 +319,44 @@ struct Problem {
 // E/F flags of rows inside the gap barrier are unspecified: no backtrace can be in E or F state
 // there (E/F are 0 in those rows and every cell on a backtrace path has a raw score >= 1).
 enum { CF_D = 1, CF_HE = 2, CF_HF = 4, CF_EO = 8, CF_EX = 16, CF_FO = 32, CF_FX = 64, CF_MM = 128 };
-// Layout [strip][step][k] with step = col + strip and 4 bytes per (strip, step): a fill lane
-// writes consecutive words on consecutive steps (one 16-byte store every four steps), and the
-// cells a backtrace visits - a diagonal band, a few strips deep around the last row for the
-// failing candidates - fall into few 32-byte sectors (8 columns x R rows of one strip each).
-// byte index = ((v*BT2_CELL_T) + c + v)*4 + k   (v = r / R, k = r % R)
-#define BT2_CELL_T (BT2GPU_MAX_COLS + 64)
+// Layout: rows are cut into 64 strips of R rows (the fill's lanes); one 32-bit word holds the R
+// cells of a strip that lie on one diagonal d = col - row (byte k = row % R), words of four
+// consecutive diagonals form a 16-byte chunk, and the chunks of the 64 strips of a diagonal group
+// are adjacent:  byte index = ((e >> 2) * 64 + v) * 16 + (e & 3) * 4 + k,  v = row / R,
+// e = d + BT2_CELL_DOFF + (s_v & 3),  s_v = v * (R + 1) + R - 1.
+// A fill lane completes the word (v, d) at step d + s_v, so the per-strip shift (s_v & 3) makes
+// every lane finish a chunk on the same step: one 16-byte store per lane every four steps.  A
+// backtrace that follows a diagonal reads 16 bytes per strip, 64 strips contiguous: the whole
+// path lies in a few 128-byte lines instead of one sector per strip.
+#define BT2_CELL_DOFF   BT2GPU_MAX_ROWS                                   // multiple of 4; d >= -(MAX_ROWS-1)
+#define BT2_CELL_GROUPS ((BT2GPU_MAX_ROWS + BT2GPU_MAX_COLS + 4 + 3) / 4)
+BT2_HD uint32_t strip_of(uint32_t r, uint32_t R) { return (R == 1) ? r : (R == 2 ? (r >> 1) : ((r * 171u) >> 9)); } // r / R for R <= 3, r < 512
 BT2_HD uint32_t cell_index(uint32_t r, uint32_t c, uint32_t R) {
-	const uint32_t v = (R == 1) ? r : (R == 2 ? (r >> 1) : (r / 3));
+	const uint32_t v = strip_of(r, R);
 	const uint32_t k = r - v * R;
-	return (v * BT2_CELL_T + c + v) * 4u + k;
+	const uint32_t e = c + BT2_CELL_DOFF - r + ((v * (R + 1) + R - 1) & 3u);
+	return ((e >> 2) * 64u + v) * 16u + (e & 3u) * 4u + k;
 }
-#define BT2_CELL_BYTES (BT2_CELL_T * 64 * 4)                 // per problem slot
-// debug-only H|E<<8|F<<16 words in the same skewed order (bt2gpu_test_fill)
-BT2_HD uint32_t hef_index(uint32_t r, uint32_t c, uint32_t R) { return cell_index(r, c, R); }
-#define BT2_HEF_WORDS BT2_CELL_BYTES
+#define BT2_CELL_BYTES (BT2_CELL_GROUPS * 64 * 16)           // per problem slot
+// debug-only H|E<<8|F<<16 words, [strip][step][k] with step = col + strip (bt2gpu_test_fill)
+#define BT2_HEF_T (BT2GPU_MAX_COLS + 64)
+BT2_HD uint32_t hef_index(uint32_t r, uint32_t c, uint32_t R) {
+	const uint32_t v = strip_of(r, R);
+	return (v * BT2_HEF_T + c + v) * 4u + (r - v * R);
+}
+#define BT2_HEF_WORDS (BT2_HEF_T * 64 * 4)
 
-// Visited map of the backtrace (SSEMatrix "reportedThrough", see dev_bt.cuh): one bit per cell,
-// diagonal-major so that a walk along a diagonal stays in one word for 16 steps and in one
-// 32-byte sector for its whole length.  Word = 16 rows of one diagonal in the low half and a
-// 16-bit generation tag in the high half: a word whose tag is not the launch's generation reads
-// as "nothing visited", so the map is never cleared between problems.
-#define BT2_VIS_WPD   ((BT2GPU_MAX_ROWS + 15) / 16)                  // words per diagonal
-#define BT2_VIS_WORDS ((BT2GPU_MAX_ROWS + BT2GPU_MAX_COLS) * BT2_VIS_WPD)
+// Visited map of the backtrace (SSEMatrix "reportedThrough", see dev_bt.cuh): one bit per cell.
+// A word covers a tile of 4 diagonals x 4 rows (16 bits) and carries a 16-bit generation tag in
+// its high half: a word whose tag is not the launch's generation reads as "nothing visited", so
+// the map is never cleared between problems.  Tiles keep a walk in one word for four steps
+// whether it runs along a diagonal, a row (read-gap run) or a column (reference-gap run); the
+// words of a diagonal group are contiguous (8 words = 32 rows per 32-byte sector).
+#define BT2_VIS_RT    ((BT2GPU_MAX_ROWS + 3) / 4)                         // row tiles per diagonal group
+#define BT2_VIS_WORDS (((BT2GPU_MAX_ROWS + BT2GPU_MAX_COLS + 3) / 4) * BT2_VIS_RT)
 #define BT2_VIS_GEN_MAX 65535u
-BT2_HD uint32_t vis_word(uint32_t r, uint32_t c) { return (c + BT2GPU_MAX_ROWS - r) * BT2_VIS_WPD + (r >> 4); }
+BT2_HD uint32_t vis_index(uint32_t r, uint32_t c) { return ((c + BT2GPU_MAX_ROWS - r) >> 2) * BT2_VIS_RT + (r >> 2); }
+BT2_HD uint32_t vis_bit(uint32_t r, uint32_t c) { return 1u << ((((c + BT2GPU_MAX_ROWS - r) & 3u) << 2) | (r & 3u)); }
 
 // Per-problem character cache handed from the fill to the backtrace: 4-bit codes, 8 per word.
 //   words [0, BT2_PC_RD)            read characters in the orientation of the problem's strand (0..3, 4 = N)

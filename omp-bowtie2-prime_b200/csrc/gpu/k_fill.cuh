@@ -91,9 +91,13 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 	for(int k = 0; k < R; k++) { Hp[k] = 0; Ep[k] = 0; Eflag[k] = (CF_EO | CF_EX) * 0x00010001u; }
 	// sendF: F for the row below in bits 0-7 of each half, the stored F of this strip's last row in bits 8-15
 	uint32_t sendH = 0, sendF = 0, prevRecvH = (lane == 0) ? 0x000000ffu : 0u;
-	const int nsteps = cols + nv - 1;
-	uint4* const out_lo = reinterpret_cast<uint4*>(cells + (size_t)lane * (BT2_CELL_T * 4));
-	uint4* const out_hi = reinterpret_cast<uint4*>(cells + (size_t)(32 + lane) * (BT2_CELL_T * 4));
+	// A word of the cell array holds the R cells of a strip on one diagonal (dev_common.cuh): byte k comes from
+	// the step R-1-k before the one that completes it, so the flag bytes pass through a short register pipeline
+	// (pipe1: row 0 of the previous step; pipe2: rows 0,1 of the two previous steps) and the sweep runs R-1 steps longer.
+	const int nsteps = cols + nv - 1 + (R - 1);
+	uint32_t pipe1 = 0, pipe2 = 0;
+	uint4* const out = reinterpret_cast<uint4*>(cells);
+	const int g_lo = BT2_CELL_DOFF / 4 - (int)((lane * (R + 1) + R - 1) >> 2), g_hi = BT2_CELL_DOFF / 4 - (int)(((32 + lane) * (R + 1) + R - 1) >> 2);
 	for(int t0 = 0; t0 < nsteps; t0 += 4) {
 	uint32_t accl[4], acch[4];
 	#pragma unroll
@@ -151,15 +155,16 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 		{ // the strip's R flag bytes of this column as one word; four steps make one 16-byte store
 			uint32_t blo, bhi;
 			if(R == 3) {
-				const uint32_t x = __byte_perm(flg[0], flg[1 % R], 0x6240);
-				blo = __byte_perm(x, flg[2 % R], 0x5410); bhi = __byte_perm(x, flg[2 % R], 0x7632);
+				blo = __byte_perm(pipe2, flg[2 % R], 0x4410); bhi = __byte_perm(pipe2, flg[2 % R], 0x6632);
+				pipe2 = __byte_perm(pipe1, flg[1 % R], 0x6240); pipe1 = flg[0];
 			} else if(R == 2) {
-				blo = __byte_perm(flg[0], flg[1 % R], 0x3340); bhi = __byte_perm(flg[0], flg[1 % R], 0x3362);
+				blo = __byte_perm(pipe1, flg[1 % R], 0x4440); bhi = __byte_perm(pipe1, flg[1 % R], 0x6662);
+				pipe1 = flg[0];
 			} else { blo = flg[0] & 0xffu; bhi = flg[0] >> 16; }
 			accl[tj] = blo; acch[tj] = bhi;
 			if(DBG) {
-				uint32_t* dlo = hef + ((size_t)lane * BT2_CELL_T + (uint32_t)t) * 4u;
-				uint32_t* dhi = hef + ((size_t)(32 + lane) * BT2_CELL_T + (uint32_t)t) * 4u;
+				uint32_t* dlo = hef + ((size_t)lane * BT2_HEF_T + (uint32_t)t) * 4u;
+				uint32_t* dhi = hef + ((size_t)(32 + lane) * BT2_HEF_T + (uint32_t)t) * 4u;
 				#pragma unroll
 				for(int k = 0; k < R; k++) { if(act_lo) dlo[k] = wlo[k]; if(act_hi) dhi[k] = whi[k]; }
 			}
@@ -167,9 +172,9 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 		sendH = Hp[R - 1]; sendF = (f | (fup << 8)) & am;
 		prevRecvH = (lane == 0) ? (0x00ffu | (recvH & 0xffff0000u)) : recvH;
 	}
-	// [strip][step]: strip v is active at steps v .. v+cols-1
-	if(strip_lo && t0 + 3 >= (int)lane && t0 < (int)lane + cols) out_lo[t0 >> 2] = make_uint4(accl[0], accl[1], accl[2], accl[3]);
-	if(strip_hi && t0 + 3 >= 32 + (int)lane && t0 < 32 + (int)lane + cols) out_hi[t0 >> 2] = make_uint4(acch[0], acch[1], acch[2], acch[3]);
+	// strip v is active at steps v .. v+cols-1 and its last words complete R-1 steps later
+	if(strip_lo && t0 + 3 >= (int)lane && t0 - (R - 1) < (int)lane + cols) out[(g_lo + (t0 >> 2)) * 64 + (int)lane] = make_uint4(accl[0], accl[1], accl[2], accl[3]);
+	if(strip_hi && t0 + 3 >= 32 + (int)lane && t0 - (R - 1) < 32 + (int)lane + cols) out[(g_hi + (t0 >> 2)) * 64 + 32 + (int)lane] = make_uint4(acch[0], acch[1], acch[2], acch[3]);
 	}
 }
 

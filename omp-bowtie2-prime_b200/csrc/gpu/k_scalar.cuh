@@ -123,8 +123,8 @@ __global__ void k_step(const DevParams* __restrict__ Pp, const DevIndex ix, cons
 	states[read] = rs;
 }
 
-struct BtArrays { const uint8_t* cells; uint32_t* vis; uint32_t gen; const uint32_t* pcache; uint32_t* scratch; const uint8_t* seq; const uint8_t* qual; };
 #define BT2_BT_THREADS 128
+#define BT2_BT_BLOCKS_PER_SM 6
 
 // One lane per problem, persistent: a lane that finishes its problem takes the next one.
 // The lanes of a warp are in different phases (candidate pick, backtrace cell, alignment
@@ -133,49 +133,44 @@ struct BtArrays { const uint8_t* cells; uint32_t* vis; uint32_t gen; const uint3
 // a quarter of the warp wants them or nothing else is left, so that they are executed
 // for several lanes at once instead of stalling 31 lanes for one.
 // Shared memory holds each lane's copy of its problem's characters (word j of lane t at
-// [j * BT2_BT_THREADS + t]: conflict-free whatever j the lanes ask for).
-__global__ void __launch_bounds__(BT2_BT_THREADS, 8) k_bt(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const Problem* probs, uint32_t count,
-                     const BtArrays ba, uint32_t* task, uint32_t* next_list, uint32_t* next_cnt, uint32_t* roundend_list, uint32_t* roundend_cnt) {
+// [j * BT2_BT_THREADS + t]: conflict-free whatever j the lanes ask for) and its two cell chunks.
+__global__ void __launch_bounds__(BT2_BT_THREADS, BT2_BT_BLOCKS_PER_SM) k_bt(const __grid_constant__ BtCtx cx, uint32_t count,
+                     uint32_t* task, uint32_t* next_list, uint32_t* next_cnt, uint32_t* roundend_list, uint32_t* roundend_cnt) {
 	__shared__ uint32_t pcs[BT2_PC_WORDS * BT2_BT_THREADS];
+	__shared__ __align__(16) uint8_t chunks[2 * 16 * BT2_BT_THREADS];
 	BtMachine m;
-	m.P = Pp; m.pools = &pools; m.gtag = ba.gen << 16; m.seqbase = ba.seq; m.qualbase = ba.qual;
 	m.pc = pcs + threadIdx.x; m.pcs = BT2_BT_THREADS;
+	m.cbuf = chunks + 16 * threadIdx.x; m.cstride = 16 * BT2_BT_THREADS;
 	m.phase = BP_DONE; m.result = BT_CONTINUE;
 	bool have = false, drained = false;
-	uint32_t read = 0;
 	while(true) {
-		if(m.phase == BP_CAND || m.phase == BP_STEP) m.hot();
+		if(m.phase == BP_CAND || m.phase == BP_STEP) m.hot(cx);
 		const uint32_t hot = __ballot_sync(0xffffffffu, m.phase == BP_CAND || m.phase == BP_STEP);
 		const uint32_t wpost = __ballot_sync(0xffffffffu, m.phase == BP_POST);
-		if(wpost && (hot == 0 || __popc(wpost) >= 8)) { if(m.phase == BP_POST) m.post(); }
+		if(wpost && (hot == 0 || __popc(wpost) >= 8)) { if(m.phase == BP_POST) m.post(cx); }
 		const uint32_t wdone = __ballot_sync(0xffffffffu, m.phase == BP_DONE && !drained);
 		if(wdone && (hot == 0 || __popc(wdone) >= 8)) {
 			if(m.phase == BP_DONE && !drained) {
 				if(have) {
-					m.finish();
-					if(m.result == BT_ROUND_END) { m.rs->phase = RS_ROUND_DONE; list_append(roundend_list, roundend_cnt, read); }
-					else list_append(next_list, next_cnt, read);
+					m.finish(cx);
+					if(m.result == BT_ROUND_END) { cx.states[m.read].phase = RS_ROUND_DONE; list_append(roundend_list, roundend_cnt, m.read); }
+					else list_append(next_list, next_cnt, m.read);
 					have = false;
 				}
 				while(!have) {
 					const uint32_t j = atomicAdd(task, 1u);
 					if(j >= count) { drained = true; break; }
-					const Problem& pb = probs[j];
-					if(pb.read == BT2_NIL) continue;
-					read = pb.read;
-					m.rs = states + read;
-					m.pb = &pb;
-					m.cells = ba.cells + (size_t)j * BT2_CELL_BYTES;
-					m.vis = ba.vis + (size_t)j * BT2_VIS_WORDS;
-					m.scratch = ba.scratch + (size_t)read * BT2_SCRATCH_EDITS;
-					const uint4* src = reinterpret_cast<const uint4*>(ba.pcache + (size_t)j * BT2_PC_WORDS);
+					const uint32_t rd = cx.probs[j].read;
+					if(rd == BT2_NIL) continue;
+					m.slot = j; m.read = rd;
+					const uint4* src = reinterpret_cast<const uint4*>(cx.pcache + (size_t)j * BT2_PC_WORDS);
 					#pragma unroll
 					for(int q = 0; q < BT2_PC_WORDS / 4; q++) {
 						const uint4 w = src[q];
 						pcs[(4 * q + 0) * BT2_BT_THREADS + threadIdx.x] = w.x; pcs[(4 * q + 1) * BT2_BT_THREADS + threadIdx.x] = w.y;
 						pcs[(4 * q + 2) * BT2_BT_THREADS + threadIdx.x] = w.z; pcs[(4 * q + 3) * BT2_BT_THREADS + threadIdx.x] = w.w;
 					}
-					m.begin();
+					m.begin(cx);
 					have = true;
 				}
 			}

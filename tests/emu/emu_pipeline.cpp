@@ -158,15 +158,14 @@ int main(int argc, char** argv) {
 			while(true) {
 				Problem pb; pb.read = ri;
 				if(advance(P, ix, rf, pools, rs, pb) == ADV_ROUND_END) break;
-				BtMachine m; m.P = &P; m.pools = &pools; m.pb = &pb; m.cells = cells.data(); m.vis = vis.data(); m.pc = pcache.data(); m.pcs = 1;
 				if(++gen > BT2_VIS_GEN_MAX) { std::fill(vis.begin(), vis.end(), 0u); gen = 1; }
-				m.gtag = gen << 16;
-				m.scratch = scratch.data() + (size_t)ri * BT2_SCRATCH_EDITS;
-				m.seqbase = in->seq; m.qualbase = in->qual; m.rs = &rs;
-				fill_emu(P, pb, m.view(), cells.data(), pcache.data());
-				m.begin();
-				while(m.phase != BP_DONE && m.step()) { }
-				m.finish();
+				BtCtx cx; cx.P = P; cx.pools = pools; cx.states = states.data(); cx.probs = &pb; cx.cells = cells.data(); cx.vis = vis.data();
+				cx.pcache = pcache.data(); cx.scratch = scratch.data(); cx.seq = in->seq; cx.qual = in->qual; cx.gtag = gen << 16;
+				BtMachine m; m.slot = 0; m.read = ri; m.pc = pcache.data(); m.pcs = 1; uint8_t cbuf[32]; m.cbuf = cbuf; m.cstride = 16;
+				fill_emu(P, pb, m.view(cx), cells.data(), pcache.data());
+				m.begin(cx);
+				while(m.phase != BP_DONE && m.step(cx)) { }
+				m.finish(cx);
 				if(m.result == BT_ROUND_END) break;
 			}
 			if(!next_round_wanted(P, rs)) break;
