@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define BT2GPU_ABI_VERSION 1
+#define BT2GPU_ABI_VERSION 2
 
 /* Limits inherited from the reference's fixed DP buffers
  * (aligner_result.h:42-43 ALN_MAX_ROWS/ALN_MAX_COLS, aligner_sw_driver.h:95 ALN_MAX_ITER). */
@@ -246,6 +246,9 @@ typedef struct bt2gpu_counters {
 	double   ms_seed, ms_glue, ms_resolve, ms_fill, ms_bt, ms_h2d, ms_d2h, ms_run;
 	uint64_t launches;          /* kernels launched by the library                 */
 	uint64_t n_seed, n_step, n_fill, n_bt; /* launches of the four main kernels    */
+	uint64_t ext_text_steps;    /* MultiSeedAligner::extend steps of single-row ranges, done as
+	                             * direct text comparisons through the device's full suffix array
+	                             * (each replaces one mapLF1 step of the reference)      */
 } bt2gpu_counters;
 
 typedef struct bt2gpu_ctx bt2gpu_ctx;

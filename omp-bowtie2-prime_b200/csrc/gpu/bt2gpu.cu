@@ -16,6 +16,7 @@
 #include <algorithm>
 #include "bt2gpu.h"
 #include "dev_common.cuh"
+#include "k_index.cuh"
 #include "k_seed.cuh"
 #include "k_fill.cuh"
 #include "k_scalar.cuh"
@@ -27,7 +28,7 @@ using namespace bt2;
 	throw std::string(b_); } } while(0)
 
 enum { PH_SEED = 0, PH_GLUE, PH_RESOLVE, PH_FILL, PH_BT, PH_H2D, PH_D2H, PH_RUN, PH_N };
-enum { C_CAND0 = 0, C_CAND1, C_ACTIVE, C_EXT0, C_EXT1, C_ROUNDEND, C_SAMP, C_SEEDTASK, C_BTTASK, C_SEEDNT, C_N = 16 };
+enum { C_CAND0 = 0, C_CAND1, C_ACTIVE, C_EXT0, C_EXT1, C_ROUNDEND, C_SAMP, C_SEEDTASK, C_BTTASK, C_SEEDNT, C_XTASKN, C_XTASK, C_N = 16 };
 
 struct DBuf { // growable device buffer
 	void* p = nullptr; size_t cap = 0;
@@ -63,11 +64,12 @@ struct bt2gpu_ctx {
 	DevIndex ix; DevRef rf;
 	std::vector<void*> resident;      // index / reference allocations
 	uint32_t nslots = 0, sampSlots = 0, maxBatch = 0, btgen = 0;
+	bool textOk = false;              // the 2-bit reference is the index's joined text (same length)
 	// problem-slot arrays
 	DBuf probs, cells, vis, pcache;
 	// per-batch arrays
 	DBuf seq, qual, seq_off, rng_seed, minsc, nceil, interval;
-	DBuf states, scratch, hits, seedtasks, lists[7], counters, stats;
+	DBuf states, scratch, hits, seedtasks, exttasks, lists[7], counters, stats;
 	DBuf p_sav, p_sorted, p_rank, p_sp2, p_exr, p_exrfw, p_nsp, p_nsmall, p_nexr, p_nelt, p_nadd;
 	DBuf s_ovr, s_ovp, s_ovv, s_sr, s_sv, s_cv, s_rn, s_rcur, s_rth, s_rfl, s_rco, s_rcn, s_rns, s_mass, s_elim;
 	DBuf chunks, sats, alnp, editp, pooltops, poolerr;
@@ -147,7 +149,7 @@ void ensure_batch(bt2gpu_ctx* c, uint32_t n, uint64_t nbases, uint32_t maxOffs) 
 	c->seq_off.ensure(nn * 4); c->rng_seed.ensure(nn * 4); c->minsc.ensure(nn * 4); c->nceil.ensure(nn * 4); c->interval.ensure(nn * 4);
 	c->states.ensure(nn * sizeof(ReadState));
 	c->scratch.ensure(nn * BT2_SCRATCH_EDITS * 4);
-	c->hits.ensure(nn * W * sizeof(SeedHit)); c->seedtasks.ensure(nn * W * sizeof(SeedTask));
+	c->hits.ensure(nn * W * sizeof(SeedHit)); c->seedtasks.ensure(nn * W * sizeof(SeedTask)); c->exttasks.ensure(nn * W * sizeof(SeedTask));
 	for(int i = 0; i < 7; i++) c->lists[i].ensure(nn * 4);
 	c->p_sav.ensure(nn * W * 2); c->p_sorted.ensure(nn * W); c->p_rank.ensure(nn * W * 2); c->p_sp2.ensure(nn * W * 2);
 	c->p_exr.ensure(nn * W * sizeof(ExRange16)); c->p_exrfw.ensure(nn * W);
@@ -260,7 +262,7 @@ void do_run(bt2gpu_ctx* c) {
 	int cand = 0;
 	for(uint32_t round = 0; ncand > 0; round++) {
 		zero_counter(c, C_ACTIVE); zero_counter(c, C_EXT0); zero_counter(c, C_EXT1); zero_counter(c, C_ROUNDEND);
-		zero_counter(c, C_SAMP); zero_counter(c, C_SEEDTASK); zero_counter(c, C_SEEDNT); zero_counter(c, cand ? C_CAND0 : C_CAND1);
+		zero_counter(c, C_SAMP); zero_counter(c, C_SEEDTASK); zero_counter(c, C_SEEDNT); zero_counter(c, C_XTASKN); zero_counter(c, C_XTASK); zero_counter(c, cand ? C_CAND0 : C_CAND1);
 		k_round_select<<<nblk(ncand, 256), 256, 0, st>>>(c->dP, states, L[cand], ncand, round, L[2], cnt + C_ACTIVE); LAUNCH(c);
 		const uint32_t nactive = read_counters(c)[C_ACTIVE];
 		if(nactive == 0) break;
@@ -268,12 +270,14 @@ void do_run(bt2gpu_ctx* c) {
 			Phase ph(c, PH_SEED);
 			SeedKernelArgs sk; sk.active = L[2]; sk.nactive = nactive; sk.W = W; sk.maxOffs = maxOffs; sk.states = states; sk.seq = ba.seq;
 			sk.hits = c->hits.as<SeedHit>(); sk.tasks = c->seedtasks.as<SeedTask>(); sk.ntasks = cnt + C_SEEDNT; sk.counter = cnt + C_SEEDTASK; sk.stats = stats;
+			sk.xtasks = c->exttasks.as<SeedTask>(); sk.nxtasks = cnt + C_XTASKN; sk.xcounter = cnt + C_XTASK; sk.text = (c->ix.sa32 && c->textOk) ? c->rf.buf : nullptr;
 			const uint64_t nslots = (uint64_t)nactive * W;
 			k_seed_init<<<(uint32_t)((nslots + 255) / 256), 256, 0, st>>>(c->ix, c->dP, sk); LAUNCH(c);
 			const uint32_t blocks = (uint32_t)std::min<uint64_t>((uint64_t)seedBlocks, (nslots + 31) / 32);
 			if(c->ix.len < 0xfffffff0ull) k_seed_walk<uint32_t><<<blocks, 256, 0, st>>>(c->ix, c->dP, sk);
 			else k_seed_walk<uint64_t><<<blocks, 256, 0, st>>>(c->ix, c->dP, sk);
 			LAUNCH(c); c->ctr.n_seed++;
+			if(sk.text) { k_seed_ext1<<<blocks, 256, 0, st>>>(c->ix, sk); LAUNCH(c); }
 		}
 		uint32_t ncur, nsamp;
 		{
@@ -342,7 +346,7 @@ void do_run(bt2gpu_ctx* c) {
 	CK(cudaMemcpyAsync(hs, c->stats.p, sizeof(hs), cudaMemcpyDeviceToHost, st));
 	CK(cudaStreamSynchronize(st));
 	CK(cudaGetLastError());
-	c->ctr.reads += n; c->ctr.seeds_searched += hs[0]; c->ctr.lf_steps_search += hs[1]; c->ctr.lf_steps_extend += hs[2]; c->ctr.lf_sides_touched += hs[3];
+	c->ctr.reads += n; c->ctr.seeds_searched += hs[0]; c->ctr.lf_steps_search += hs[1]; c->ctr.lf_steps_extend += hs[2]; c->ctr.lf_sides_touched += hs[3]; c->ctr.ext_text_steps += hs[4];
 	c->ctr.dp_problems += hs[8]; c->ctr.dp_cells += hs[9];
 	c->ctr.sa_rows_resolved += hs[16]; c->ctr.lf_steps_resolve += hs[17]; c->ctr.bt_attempts += hs[18]; c->ctr.bt_steps += hs[19]; c->ctr.alns_reported += hs[20];
 	flush_spans(c);
@@ -397,6 +401,26 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		ix.offs = upload(c, hix->offs, hix->offsLen); ix.rstarts = upload(c, hix->rstarts, hix->nFrag * 3); ix.plen = upload(c, hix->plen, hix->nPat);
 		for(int i = 0; i < 5; i++) ix.fchr[i] = hix->fchr[i];
 		ix.len = hix->len; ix.zOff = hix->zOff; ix.nFrag = hix->nFrag; ix.nPat = hix->nPat; ix.offRate = hix->offRate; ix.ftabChars = hix->ftabChars;
+		ix.sa32 = nullptr;
+		// ---- full suffix array (k_index.cuh); BT2GPU_FULL_SA=0 keeps the sampled one (LF walks), e.g. to save 4 B/row
+		{ const char* efs = getenv("BT2GPU_FULL_SA");
+		  if(!(efs && atoi(efs) == 0) && hix->len < 0xfffffff0ull && hix->offRate >= 0 && hix->offRate < 31) {
+			const uint64_t nrows = hix->len + 1;
+			uint32_t* sa = nullptr;
+			CK(cudaMalloc((void**)&sa, nrows * 4 + 16)); c->resident.push_back(sa);
+			CK(cudaMemset(sa, 0xff, nrows * 4));
+			const uint64_t nsample = (nrows + ((1ull << hix->offRate) - 1)) >> hix->offRate;
+			if(nsample > hix->offsLen) throw std::string("bt2gpu_create: SA sample shorter than the index needs");
+			k_build_sa<<<(uint32_t)((nsample + 127) / 128), 128>>>(ix, sa, nsample);
+			unsigned long long* dbad = nullptr; unsigned long long hbad = 0;
+			CK(cudaMalloc((void**)&dbad, 8)); CK(cudaMemset(dbad, 0, 8));
+			k_fix_sa<<<(uint32_t)((nrows + 255) / 256), 256>>>(ix, sa, nrows, 1, dbad);
+			k_fix_sa<<<(uint32_t)((nrows + 255) / 256), 256>>>(ix, sa, nrows, 0, dbad);
+			CK(cudaMemcpy(&hbad, dbad, 8, cudaMemcpyDeviceToHost)); CK(cudaFree(dbad));
+			CK(cudaGetLastError());
+			if(hbad) throw std::string("bt2gpu_create: inconsistent index (suffix-array expansion left rows unresolved)");
+			ix.sa32 = sa;
+		  } }
 		// ---- reference
 		std::vector<uint64_t> tstart(hrf->nrecs), cum(hrf->nrecs), rec0;
 		{ uint64_t cu = 0, pos = 0;
@@ -409,6 +433,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		}
 		DevRef& rf = c->rf;
 		rf.buf = upload(c, hrf->buf, (hrf->bufBases + 3) / 4);
+		c->textOk = hrf->bufBases == hix->len;
 		rf.rec_off = upload(c, hrf->rec_off, hrf->nrecs); rf.rec_len = upload(c, hrf->rec_len, hrf->nrecs);
 		rf.rec_tstart = upload(c, tstart.data(), tstart.size()); rf.rec_cum = upload(c, cum.data(), cum.size());
 		rf.ref_rec0 = upload(c, rec0.data(), rec0.size()); rf.nrecs = hrf->nrecs;
@@ -531,7 +556,7 @@ void bt2gpu_destroy(bt2gpu_ctx* c) {
 	for(void* p : c->resident) cudaFree(p);
 	if(c->dP) cudaFree(c->dP);
 	DBuf* all[] = { &c->probs, &c->cells, &c->vis, &c->pcache, &c->seq, &c->qual, &c->seq_off, &c->rng_seed, &c->minsc, &c->nceil, &c->interval,
-		&c->states, &c->scratch, &c->hits, &c->seedtasks, &c->lists[0], &c->lists[1], &c->lists[2], &c->lists[3], &c->lists[4], &c->lists[5], &c->lists[6], &c->counters, &c->stats,
+		&c->states, &c->scratch, &c->hits, &c->seedtasks, &c->exttasks, &c->lists[0], &c->lists[1], &c->lists[2], &c->lists[3], &c->lists[4], &c->lists[5], &c->lists[6], &c->counters, &c->stats,
 		&c->p_sav, &c->p_sorted, &c->p_rank, &c->p_sp2, &c->p_exr, &c->p_exrfw, &c->p_nsp, &c->p_nsmall, &c->p_nexr, &c->p_nelt, &c->p_nadd,
 		&c->s_ovr, &c->s_ovp, &c->s_ovv, &c->s_sr, &c->s_sv, &c->s_cv, &c->s_rn, &c->s_rcur, &c->s_rth, &c->s_rfl, &c->s_rco, &c->s_rcn, &c->s_rns, &c->s_mass, &c->s_elim,
 		&c->chunks, &c->sats, &c->alnp, &c->editp, &c->pooltops, &c->poolerr, &c->nal, &c->ned, &c->albase, &c->edbase, &c->cubtmp, &c->o_rr, &c->o_alns, &c->o_edits };

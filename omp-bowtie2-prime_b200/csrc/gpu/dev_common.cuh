@@ -46,6 +46,7 @@ struct DevIndex {
 	const uint64_t* offs;
 	const uint64_t* rstarts;  // 3 per fragment
 	const uint64_t* plen;
+	const uint32_t* sa32;     // device-built full suffix array (one entry per BWT row), or null (see k_index.cuh)
 	uint64_t fchr[5];
 	uint64_t len, zOff, nFrag, nPat;
 	int32_t  offRate, ftabChars;
@@ -136,6 +137,7 @@ BT2_HD uint64_t rank_c(const DevIndex& ix, int c, uint64_t row) {
 
 // SA[row] by LF-walking to the next sampled row (== what GroupWalk2S::advanceElement resolves)
 BT2_HD uint64_t sa_offset(const DevIndex& ix, uint64_t row, uint32_t* steps) {
+	if(ix.sa32) return ix.sa32[row];
 	uint64_t jumps = 0;
 	const uint64_t offMask = OFF_MASK_U64 << ix.offRate;
 	while(true) {

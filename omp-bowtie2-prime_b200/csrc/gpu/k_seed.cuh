@@ -5,7 +5,14 @@
 //   MultiSeedAligner::extend                                     aligner_seed.cpp:603-672
 //   Ebwt::countBt2SideEx / mapBiLFEx / mapLF1 / ftabHi / ftabLo  bt2_idx.h:1940-1972, 2474-2564, 1430-1607
 //
-// Two kernels.  k_seed_init (one thread per seed): validity (no N), the 2-bit key,
+// Left extension of a hit whose range is a single row is not walked through the FM index: with the
+// device's full suffix array (k_index.cuh) the row's text offset is one gather, and "the BWT
+// character of the row equals the read character, step to LF(row)" is the same statement as "the
+// text character before the offset equals the read character, step the offset down" (the row of
+// offset 0 is the '$' row).  k_seed_ext1 does that comparison against the 2-bit reference, one
+// thread per hit: no dependent random reads.  Ranges of several rows keep the LF walk.
+//
+// Three kernels.  k_seed_init (one thread per seed): validity (no N), the 2-bit key,
 // the ftab jump over the last ftabChars bases; seeds that still need LF steps are
 // appended to a task list.  k_seed_walk: a group of 8 lanes owns one task.  One LF
 // step = the group reads the 128-byte side(s) of top and bot with one 16-byte load per
@@ -41,8 +48,12 @@ struct SeedKernelArgs {
 	SeedHit*         hits;      // [nactive*W]
 	SeedTask*        tasks;     // [nactive*W]
 	uint32_t*        ntasks;    // tasks appended by k_seed_init
+	SeedTask*        xtasks;    // [nactive*W] single-row hits waiting for their left extension (k_seed_ext1)
+	uint32_t*        nxtasks;
+	uint32_t*        xcounter;  // task counter of k_seed_ext1
+	const uint8_t*   text;      // 2-bit joined text (DevRef::buf), or null: no text-compare extension
 	uint32_t*        counter;   // task counter of k_seed_walk
-	unsigned long long* stats;  // [0] seeds searched [1] LF steps search [2] LF steps extend [3] sides loaded
+	unsigned long long* stats;  // [0] seeds searched [1] LF steps search [2] LF steps extend [3] sides loaded [4] text-compare extension steps
 };
 
 __device__ __forceinline__ uint4 ldg_u4(const uint8_t* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
@@ -65,7 +76,7 @@ __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevP
 	const DevParams& P = *Pp;
 	const uint64_t tk = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	const bool in_range = tk < (uint64_t)a.nactive * a.W;
-	bool searched = false, live = false;
+	bool searched = false, live = false, livex = false;
 	SeedTask t; t.hit = 0; t.seq_off = 0; t.rdlen = 0; t.pos = 0; t.seed_lo = 0; t.rc = 0;
 	if(in_range) {
 		const uint32_t ai = (uint32_t)(tk / a.W), h = (uint32_t)(tk - (uint64_t)ai * a.W);
@@ -112,7 +123,8 @@ __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevP
 		out->top = hit ? top : 0; out->len = hit ? bot - top : 0; out->key = key; out->nlex = 0;
 		out->valid = (hit && done) ? 1u : 0u;
 		if(hit && !done) {
-			live = true;
+			// a single-row range that is already complete goes straight to the text-compare extension
+			if(whole && bot - top == 1 && a.text) livex = true; else live = true;
 			t.hit = (uint32_t)tk; t.seq_off = rs.seq_off; t.rdlen = (uint16_t)rdlen; t.pos = (int16_t)pos; t.seed_lo = (int16_t)seed_lo; t.rc = rc ? 1 : 0;
 		}
 	}
@@ -123,6 +135,11 @@ __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevP
 	if(lane == 0 && bal) base = atomicAdd(a.ntasks, (uint32_t)__popc(bal));
 	base = __shfl_sync(0xffffffffu, base, 0);
 	if(live) a.tasks[base + __popc(bal & ((1u << lane) - 1))] = t;
+	const uint32_t balx = __ballot_sync(0xffffffffu, livex);
+	uint32_t basex = 0;
+	if(lane == 0 && balx) basex = atomicAdd(a.nxtasks, (uint32_t)__popc(balx));
+	basex = __shfl_sync(0xffffffffu, basex, 0);
+	if(livex) a.xtasks[basex + __popc(balx & ((1u << lane) - 1))] = t;
 	const uint32_t sb = __ballot_sync(0xffffffffu, searched);
 	if(lane == 0 && sb) atomicAdd(&a.stats[0], (unsigned long long)__popc(sb));
 }
@@ -255,6 +272,14 @@ __global__ void __launch_bounds__(256) k_seed_walk(const DevIndex ix, const DevP
 						extending = true;
 						if(l8 == 0) { out->top = (uint64_t)top; out->len = (uint64_t)(bot - top); }
 						if(!doExtend || pos < 0) finished = true;
+						else if(bot - top == 1 && a.text) { // single row: hand over to k_seed_ext1
+							if(l8 == 0) {
+								SeedTask x; x.hit = (uint32_t)(out - a.hits); x.seq_off = (uint32_t)(rseq - a.seq); x.rdlen = (uint16_t)rdlen;
+								x.pos = (int16_t)pos; x.seed_lo = (int16_t)seed_lo; x.rc = rc ? 1 : 0;
+								a.xtasks[atomicAdd(a.nxtasks, 1u)] = x;
+							}
+							finished = true;
+						}
 					}
 				}
 			} else {
@@ -284,6 +309,49 @@ __global__ void __launch_bounds__(256) k_seed_walk(const DevIndex ix, const DevP
 		atomicAdd(&a.stats[1], (unsigned long long)st_search);
 		atomicAdd(&a.stats[2], (unsigned long long)st_extend); atomicAdd(&a.stats[3], (unsigned long long)st_sides);
 	}
+}
+
+// Left extension of single-row hits by text comparison (MultiSeedAligner::extend, aligner_seed.cpp:603-672,
+// range == 1 branch: mapLF1 on the row, stop at the first read character that is not the BWT character;
+// an N in the read never stops it; at the '$' row only Ns keep counting).  One thread per hit, a warp
+// takes 32 tasks at a time.
+__global__ void __launch_bounds__(256) k_seed_ext1(const DevIndex ix, const SeedKernelArgs a) {
+	const uint32_t lane = threadIdx.x & 31;
+	const uint32_t ntasks = *a.nxtasks;
+	unsigned long long steps = 0;
+	while(true) {
+		uint32_t t0 = 0;
+		if(lane == 0) t0 = atomicAdd(a.xcounter, 32u);
+		t0 = __shfl_sync(0xffffffffu, t0, 0);
+		if(t0 >= ntasks) break;
+		const uint32_t ti = t0 + lane;
+		if(ti < ntasks) {
+			const SeedTask t = a.xtasks[ti];
+			SeedHit* out = a.hits + t.hit;
+			const uint8_t* rseq = a.seq + t.seq_off;
+			const uint32_t rdlen = t.rdlen; const bool rc = t.rc != 0;
+			uint64_t off = ix.sa32[out->top];
+			int pos = t.pos; uint32_t nlex = 0;
+			while(true) {
+				steps++;
+				const uint32_t p = rc ? (rdlen - 1 - (uint32_t)pos) : (uint32_t)pos;
+				const int b = rseq[p];
+				const int ch = rc ? (b > 3 ? 4 : 3 - b) : b;
+				if(off == 0) { if(ch <= 3) break; }
+				else {
+					const uint64_t x = off - 1;
+					const int c = (a.text[x >> 2] >> ((x & 3) * 2)) & 3;
+					if(c != ch && ch <= 3) break;
+					off = x;
+				}
+				nlex++; pos--;
+				if(nlex == 255 || pos < 0) break;
+			}
+			out->nlex = nlex; out->valid = 1;
+		}
+	}
+	for(int o = 16; o > 0; o >>= 1) steps += __shfl_xor_sync(0xffffffffu, steps, o);
+	if(lane == 0 && steps) atomicAdd(&a.stats[4], steps);
 }
 
 } // namespace bt2

@@ -29,7 +29,9 @@ def test_gpu_matches_oracle_and_golden(name):
     c = gpu.counters()
     oc = orc.counters()
     assert c["dp_problems"] == oc["dps"] and c["dp_cells"] == oc["cells"]
-    assert c["lf_steps_search"] == oc["lfSearch"] and c["lf_steps_extend"] == oc["lfExtend"]
+    assert c["lf_steps_search"] == oc["lfSearch"]
+    # single-row extensions are text comparisons through the full suffix array, one per reference LF step
+    assert c["lf_steps_extend"] + c["ext_text_steps"] == oc["lfExtend"]
     assert c["bt_steps"] == oc["btSteps"] and c["sa_rows_resolved"] == oc["saRows"]
     assert c["launches"] > 0
     gpu.close(); orc.close()
