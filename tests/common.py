@@ -21,6 +21,7 @@ CASES = {
     "syn150_sensitive_dpad12": ("syn", "syn150", "--sensitive --dpad 12", "syn150_sensitive_dpad12.sam"),
     "syn100_default": ("syn", "syn100", "", "syn100_default.sam"),
     "syn100_k5": ("syn", "syn100", "-k 5", "syn100_k5.sam"),
+    "synN120_default": ("synN", "synN120", "", "synN120_default.sam"),
 }
 
 
@@ -47,6 +48,9 @@ def index_base(name):
     elif name == "syn":
         fa = base + ".fa"
         gen(["ref", fa, 300000, "--seed", 4242, "--repeats", 0.2, "--nseq", 3])
+    elif name == "synN":
+        fa = base + ".fa"
+        gen(["ref", fa, 200000, "--seed", 99, "--repeats", 0.1, "--nseq", 2, "--ngaps", 40])
     elif name.startswith("iid"):  # iid<len>
         fa = base + ".fa"
         gen(["ref", fa, int(name[3:]), "--seed", 12345])
@@ -62,6 +66,10 @@ def reads_path(name):
         return os.path.join(GOLD, "lambda_reads_1k.fq")
     p = os.path.join(WORK, name + ".fq")
     if os.path.exists(p):
+        return p
+    if name == "synN120":
+        index_base("synN")
+        gen(["reads", os.path.join(WORK, "synN.fa"), p, 1500, 120, "--seed", 9, "--randqual"])
         return p
     index_base("syn")
     fa = os.path.join(WORK, "syn.fa")

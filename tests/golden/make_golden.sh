@@ -25,5 +25,10 @@ python "$ROOT/tools/gen_data.py" reads "$T/syn.fa" "$T/syn100.fq" 1500 100 --see
 run syn150_sensitive_dpad12 "$T/syn" "$T/syn150.fq" "--sensitive --dpad 12"
 run syn100_default          "$T/syn" "$T/syn100.fq" ""
 run syn100_k5               "$T/syn" "$T/syn100.fq" "-k 5"
+# reference with runs of N (record boundaries inside sequences, N at both ends of the text), 2 sequences
+python "$ROOT/tools/gen_data.py" ref "$T/synN.fa" 200000 --seed 99 --repeats 0.1 --nseq 2 --ngaps 40
+"$B/bowtie2-build-l" "$T/synN.fa" "$T/synN" >/dev/null 2>&1
+python "$ROOT/tools/gen_data.py" reads "$T/synN.fa" "$T/synN120.fq" 1500 120 --seed 9 --randqual
+run synN120_default         "$T/synN" "$T/synN120.fq" ""
 rm -rf "$T"
 ls -la "$HERE"

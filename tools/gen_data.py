@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Deterministic synthetic reference + simulated reads (SURVEY 8(d) C2-C4 restated; the
 reference's own scripts/sim needs Math::Random, absent here).
-  gen_data.py ref  OUT.fa  LEN  [--seed S] [--repeats FRAC] [--nseq K]
+  gen_data.py ref  OUT.fa  LEN  [--seed S] [--repeats FRAC] [--nseq K] [--ngaps G]
   gen_data.py reads REF.fa OUT.fq N LEN [--seed S] [--subst 0.01] [--indel 0.10] [--randqual] [--nfrac 0.0]
 """
 import sys, argparse
@@ -25,6 +25,12 @@ def gen_ref(a):
             f[m] = (f[m] + rng.integers(1, 4, size=int(m.sum()), dtype=np.uint8)) % 4
             codes[p:p + flen] = f
     seq = BASES[codes]
+    if a.ngaps > 0:
+        # runs of N (1..150 bp) at random places, one of them at the very start and one at the very end of the text
+        seq = seq.copy()
+        starts = rng.integers(0, a.len - 200, size=a.ngaps); lens = rng.integers(1, 151, size=a.ngaps)
+        starts[0] = 0; starts[-1] = a.len - int(lens[-1])
+        for st, ln in zip(starts, lens): seq[st:st + ln] = ord('N')
     with open(a.out, 'wb') as f:
         per = a.len // a.nseq
         for k in range(a.nseq):
@@ -71,7 +77,7 @@ def gen_reads(a):
 def main():
     ap = argparse.ArgumentParser(); sub = ap.add_subparsers(dest='cmd')
     p = sub.add_parser('ref'); p.add_argument('out'); p.add_argument('len', type=int); p.add_argument('--seed', type=int, default=12345)
-    p.add_argument('--repeats', type=float, default=0.0); p.add_argument('--nseq', type=int, default=1)
+    p.add_argument('--repeats', type=float, default=0.0); p.add_argument('--nseq', type=int, default=1); p.add_argument('--ngaps', type=int, default=0)
     p = sub.add_parser('reads'); p.add_argument('ref'); p.add_argument('out'); p.add_argument('n', type=int); p.add_argument('len', type=int)
     p.add_argument('--seed', type=int, default=2); p.add_argument('--subst', type=float, default=0.01); p.add_argument('--indel', type=float, default=0.10)
     p.add_argument('--randqual', action='store_true'); p.add_argument('--nfrac', type=float, default=0.0); p.add_argument('--maxlen', type=int, default=0)
