@@ -13,15 +13,22 @@
 // native while the 8x4 video intrinsics (__vmaxu4/__vsubus4) are emulated with 4-5
 // LOP3/PRMT each (SASS evidence).  u8 saturation is exact in 16 bits:
 // subs_u8(a,b) == max(a-b,0) for 0<=a,b<=255.
-// Strip boundaries travel down with __shfl_up_sync.  The reference keeps H, E and F of
-// every cell for its backtrace; the backtrace only ever asks which of its score
-// equalities hold at a cell, so the fill answers those while the operands are in
-// registers and stores ONE byte of flags per cell (dev_common.cuh, CF_*): 1 B/cell of
-// HBM traffic instead of 3-4.  Each equality is one HSET2.NEU on the two 16-bit halves
-// (the values 0..255 and the small negative unsaturated sums are compared as fp16 bit
-// patterns: denormals compare exactly, negative values are NaN/-inf patterns and can
-// only meet a non-negative partner, where "unordered or not equal" is the right answer)
-// plus one LOP3 that drops the mask into its bit.
+// Strip boundaries travel down with one rotating __shfl_sync per value.
+//
+// The reference keeps H, E and F of every cell for its backtrace; the backtrace only ever
+// asks which of its score equalities hold at a cell, so the fill answers those while the
+// operands are in registers and stores ONE byte of flags per cell (dev_common.cuh, CF_*).
+// The kernel is bound by instruction issue, with the integer ALU pipe (half rate) next, so
+// the flag work is kept off the ALU pipe: each equality is one HSET2.BF.NEU on the two 16-bit
+// halves (values 0..255 and the small negative unsaturated sums compared as fp16 bit patterns:
+// denormals compare exactly, negative values are NaN/-inf patterns and can only meet a
+// non-negative partner, where "unordered or not equal" is the right answer) giving 1.0 / 0.0,
+// and one HFMA2 that adds the flag's weight to an accumulator that starts at 1024.0: the fp16
+// pattern of 1024+x is 0x6400|x, so the low byte of each half IS the flag byte, partial
+// accumulators merge with a plain OR, and no conversion is ever needed.
+// The substitution score needs no table either: score = mismatch mask AND the row's penalty
+// (a second penalty when the reference character is N; that variant of the loop is only
+// run for windows that contain an N).
 #pragma once
 #include <cuda_fp16.h>
 #include "dev_common.cuh"
@@ -41,29 +48,133 @@ struct FillArgs {
 };
 
 #define BT2_FILL_WARPS 4
+#define BT2_FILL_REFPAD 80             // columns read past the window's end by strips that are done (<= 63 + R)
 struct FillShared {
-	uint32_t tab[3 * 5 * 64];          // negated penalties, pre-positioned per half
-	uint8_t  refc[BT2GPU_MAX_COLS + 8]; // reference code 0..4 per column
+	uint8_t  refc[BT2GPU_MAX_COLS + 8 + BT2_FILL_REFPAD]; // reference code 0..4 per column, 4 beyond the window
 	uint8_t  hlast[BT2GPU_MAX_COLS + 8];
 	uint8_t  rdc[64 * 3];               // read code per row (0..3, 7 = N or beyond the read)
+	uint8_t  pen[64 * 3], penN[64 * 3]; // penalty of the row against a mismatching / an N reference character
 	uint16_t ckey[BT2GPU_MAX_COLS + 8];
 };
 
 __device__ __forceinline__ uint32_t pack2(int lo, int hi) { return ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16); }
+__device__ __forceinline__ __half2 as_h2(uint32_t a) { return *reinterpret_cast<const __half2*>(&a); }
+__device__ __forceinline__ uint32_t as_u32(__half2 a) { return *reinterpret_cast<const uint32_t*>(&a); }
 // 0xffff in each half where the 16-bit patterns differ
-__device__ __forceinline__ uint32_t ne2(uint32_t a, uint32_t b) {
-	return __hneu2_mask(*reinterpret_cast<const __half2*>(&a), *reinterpret_cast<const __half2*>(&b));
+__device__ __forceinline__ uint32_t ne2(uint32_t a, uint32_t b) { return __hneu2_mask(as_h2(a), as_h2(b)); }
+// acc + w in each half where the 16-bit patterns of a and b differ (acc, w: fp16 pairs)
+__device__ __forceinline__ uint32_t flag_ne(uint32_t a, uint32_t b, uint32_t w, uint32_t acc) {
+	return as_u32(__hfma2(__hneu2(as_h2(a), as_h2(b)), as_h2(w), as_h2(acc)));
+}
+#define BT2_FL_BASE 0x64006400u                                  // 1024.0 | 1024.0
+#define BT2_FL_W(log2bit) ((0x3c00u + 0x400u * (log2bit)) * 0x00010001u)   // 2^log2bit in both halves
+
+// The steps [t0, t_end) of the sweep, four per iteration (one 16-byte store per lane and half).
+// MASK: some strips have not reached column 0 yet (steps < 64): their H/E must stay 0.  REFN: the window contains an N.
+template<int R, bool DBG, bool MASK, bool REFN>
+__device__ __forceinline__ void fill_steps(int t0, const int t_end, const int cols, const uint32_t lane, FillShared& sh,
+		const bool strip_lo, const bool strip_hi, const bool own_lo, const bool own_hi, const int kstar,
+		const uint32_t (&rdc2)[R], const uint32_t (&negpen)[R], const uint32_t (&negpenN)[R],
+		const uint32_t (&neg_rdgo)[R], const uint32_t (&neg_rfgo)[R], const uint32_t (&neg_rfge)[R], const uint32_t neg_rdge,
+		const uint32_t nx_rfgo, const uint32_t nx_rfge,
+		uint32_t (&Hp)[R], uint32_t (&Ep)[R], uint32_t (&Ecar)[R], uint32_t& sendH, uint32_t& sendF, uint32_t& prevRecvH,
+		uint32_t& pipe1, uint32_t& pipe2, uint4* __restrict__ out, const int g_lo, const int g_hi, uint32_t* __restrict__ hef) {
+	const uint32_t W_D = BT2_FL_W(0), W_HE = BT2_FL_W(1), W_HF = BT2_FL_W(2), W_EO = BT2_FL_W(3), W_EX = BT2_FL_W(4), W_FO = BT2_FL_W(5), W_FX = BT2_FL_W(6);
+	const uint32_t rot = (lane + 31u) & 31u;
+	for(; t0 < t_end; t0 += 4) {
+		uint32_t accl[4], acch[4];
+		#pragma unroll
+		for(int tj = 0; tj < 4; tj++) {
+			const int t = t0 + tj;
+			const int c_lo = t - (int)lane, c_hi = c_lo - 32;
+			// values produced by the strip above in the previous step (lane 0: the strip above its high half is lane 31's low half)
+			uint32_t recvH = __shfl_sync(0xffffffffu, sendH, rot), recvF = __shfl_sync(0xffffffffu, sendF, rot);
+			if(lane == 0) { recvH = 0x00ffu | (recvH << 16); recvF = ((uint32_t)(CF_FO | CF_FX) << 8) | (recvF << 16); } // row 0: H(-1,*) = 0xff, F = 0
+			uint32_t x_lo, x_hi, am = 0xffffffffu;
+			bool act_lo = true, act_hi = true;
+			if(MASK) {
+				act_lo = strip_lo && c_lo >= 0 && c_lo < cols; act_hi = strip_hi && c_hi >= 0 && c_hi < cols;
+				am = (act_lo ? 0xffffu : 0u) | (act_hi ? 0xffff0000u : 0u);
+				x_lo = c_lo >= 0 ? sh.refc[c_lo] : 4u; x_hi = c_hi >= 0 ? sh.refc[c_hi] : 4u;
+			} else { x_lo = sh.refc[c_lo]; x_hi = sh.refc[c_hi]; }
+			const uint32_t xpk = x_lo | (x_hi << 16);
+			const uint32_t nmask = REFN ? __heq2_mask(as_h2(xpk), as_h2(0x00040004u)) : 0u;
+			uint32_t diag = prevRecvH;
+			uint32_t f = recvF & 0x00ff00ffu;                              // F(r,c)
+			uint32_t Fcar = ((recvF >> 8) & 0x00ff00ffu) | BT2_FL_BASE;     // its two comparisons, made where it was produced
+			uint32_t flg[R];
+			uint32_t wlo[R], whi[R];
+			#pragma unroll
+			for(int k = 0; k < R; k++) {
+				const uint32_t mm = ne2(rdc2[k], xpk);
+				const uint32_t pen = REFN ? ((negpen[k] & ~nmask) | (negpenN[k] & nmask)) : negpen[k];
+				const uint32_t s = mm & pen;
+				const uint32_t hd = diag; diag = Hp[k];
+				const uint32_t u = __vadd2(hd, s);            // unsaturated H(r-1,c-1) + sc
+				const uint32_t e = Ep[k];
+				const uint32_t h = __vimax3_s16x2_relu(u, e, f);
+				// the comparisons of the backtrace at this cell
+				uint32_t fl = Ecar[k] | Fcar | (mm & (CF_MM * 0x00010001u));
+				fl = flag_ne(h, u, W_D, fl);
+				fl = flag_ne(h, e, W_HE, fl);
+				fl = flag_ne(h, f, W_HF, fl);
+				flg[k] = fl;
+				if(DBG) {
+					wlo[k] = __byte_perm(__byte_perm(h, e, 0x0040), f, 0x5410);
+					whi[k] = __byte_perm(__byte_perm(h, e, 0x0062), f, 0x7610);
+				}
+				if(k == kstar) {
+					if(own_lo && act_lo && c_lo < cols) sh.hlast[c_lo] = (uint8_t)(h & 0xffu);
+					if(own_hi && act_hi && c_hi < cols) sh.hlast[c_hi] = (uint8_t)((h >> 16) & 0xffu);
+				}
+				// E of the next column in this row and its two comparisons
+				const uint32_t be = __vadd2(h, neg_rdgo[k]), ae = __vadd2(e, neg_rdge);
+				const uint32_t en = __vimax_s16x2_relu(ae, be);
+				Ecar[k] = flag_ne(en, be, W_EO, flag_ne(en, ae, W_EX, BT2_FL_BASE));
+				if(MASK) { Hp[k] = h & am; Ep[k] = en & am; } else { Hp[k] = h; Ep[k] = en; }
+				// F of the next row in this column and its two comparisons
+				const uint32_t bf = __vadd2(h, k + 1 < R ? neg_rfgo[(k + 1) % R] : nx_rfgo), af = __vadd2(f, k + 1 < R ? neg_rfge[(k + 1) % R] : nx_rfge);
+				f = __vimax_s16x2_relu(af, bf);
+				Fcar = flag_ne(f, bf, W_FO, flag_ne(f, af, W_FX, BT2_FL_BASE));
+			}
+			{ // a word of the cell array = the strip's R cells on one diagonal: byte k comes from the step R-1-k before this one
+				uint32_t blo, bhi;
+				if(R == 3) {
+					blo = __byte_perm(pipe2, flg[2 % R], 0x4410); bhi = __byte_perm(pipe2, flg[2 % R], 0x6632);
+					pipe2 = __byte_perm(pipe1, flg[1 % R], 0x6240); pipe1 = flg[0];
+				} else if(R == 2) {
+					blo = __byte_perm(pipe1, flg[1 % R], 0x4440); bhi = __byte_perm(pipe1, flg[1 % R], 0x6662);
+					pipe1 = flg[0];
+				} else { blo = flg[0] & 0xffu; bhi = (flg[0] >> 16) & 0xffu; }
+				accl[tj] = blo; acch[tj] = bhi;
+				if(DBG) {
+					uint32_t* dlo = hef + ((size_t)lane * BT2_HEF_T + (uint32_t)t) * 4u;
+					uint32_t* dhi = hef + ((size_t)(32 + lane) * BT2_HEF_T + (uint32_t)t) * 4u;
+					#pragma unroll
+					for(int k = 0; k < R; k++) { if(act_lo) dlo[k] = wlo[k]; if(act_hi) dhi[k] = whi[k]; }
+				}
+			}
+			sendH = Hp[R - 1];
+			sendF = f | ((Fcar & 0x00ff00ffu) << 8);
+			if(MASK) sendF &= am;
+			prevRecvH = recvH;
+		}
+		// strip v is active at steps v .. v+cols-1 and its last words complete R-1 steps later
+		if(strip_lo && t0 + 3 >= (int)lane && t0 - (R - 1) < (int)lane + cols) out[(g_lo + (t0 >> 2)) * 64 + (int)lane] = make_uint4(accl[0], accl[1], accl[2], accl[3]);
+		if(strip_hi && t0 + 3 >= 32 + (int)lane && t0 - (R - 1) < 32 + (int)lane + cols) out[(g_hi + (t0 >> 2)) * 64 + 32 + (int)lane] = make_uint4(acch[0], acch[1], acch[2], acch[3]);
+	}
 }
 
 template<int R, bool DBG>
 __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillShared& sh, uint8_t* __restrict__ cells,
-                                          uint32_t* __restrict__ hef, uint32_t lane) {
+                                          uint32_t* __restrict__ hef, uint32_t lane, bool refHasN) {
 	const int rows = pb.rows, cols = pb.cols;
 	const int nv = (rows + R - 1) / R;                 // active strips
 	// per-row gap penalties; inside the gap barrier (aligner_swsse_ee_u8.cpp:101-115: first/last gapbar
 	// rows) they are large enough to keep E and F at 0
 	const uint32_t neg_rdge = pack2(-P.rdGapExt, -P.rdGapExt);
 	uint32_t neg_rdgo[R], neg_rfgo[R], neg_rfge[R];    // [k]: read gaps in row k; ref gaps INTO row k (from the row above)
+	uint32_t rdc2[R], negpen[R], negpenN[R];           // read character and (negated) penalties of row k, both halves
 	#pragma unroll
 	for(int k = 0; k < R; k++) {
 		const int rlo = (int)lane * R + k, rhi = (32 + (int)lane) * R + k;
@@ -71,6 +182,9 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 		neg_rdgo[k] = pack2(alo ? -P.rdGapOpen : -1024, ahi ? -P.rdGapOpen : -1024);
 		neg_rfgo[k] = pack2(alo ? -P.rfGapOpen : -1024, ahi ? -P.rfGapOpen : -1024);
 		neg_rfge[k] = pack2(alo ? -P.rfGapExt : -1024, ahi ? -P.rfGapExt : -1024);
+		rdc2[k] = (uint32_t)sh.rdc[rlo] | ((uint32_t)sh.rdc[rhi] << 16);
+		negpen[k] = pack2(-(int)sh.pen[rlo], -(int)sh.pen[rhi]);
+		negpenN[k] = pack2(-(int)sh.penN[rlo], -(int)sh.penN[rhi]);
 	}
 	uint32_t nx_rfgo, nx_rfge;                         // ref gaps into the first row of the next lane's strips
 	{
@@ -79,17 +193,14 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 		nx_rfgo = pack2(alo ? -P.rfGapOpen : -1024, ahi ? -P.rfGapOpen : -1024);
 		nx_rfge = pack2(alo ? -P.rfGapExt : -1024, ahi ? -P.rfGapExt : -1024);
 	}
-	uint32_t rdc2[R];
-	#pragma unroll
-	for(int k = 0; k < R; k++) rdc2[k] = (uint32_t)sh.rdc[(int)lane * R + k] | ((uint32_t)sh.rdc[(32 + (int)lane) * R + k] << 16);
 	const bool strip_lo = (int)lane < nv, strip_hi = 32 + (int)lane < nv;
 	// which (lane, half, k) owns the last row
 	const int vstar = (rows - 1) / R, kstar = (rows - 1) - vstar * R;
 	const bool own_lo = vstar == (int)lane, own_hi = vstar == 32 + (int)lane;
-	uint32_t Hp[R], Ep[R], Eflag[R];
+	uint32_t Hp[R], Ep[R], Ecar[R];
 	#pragma unroll
-	for(int k = 0; k < R; k++) { Hp[k] = 0; Ep[k] = 0; Eflag[k] = (CF_EO | CF_EX) * 0x00010001u; }
-	// sendF: F for the row below in bits 0-7 of each half, the stored F of this strip's last row in bits 8-15
+	for(int k = 0; k < R; k++) { Hp[k] = 0; Ep[k] = 0; Ecar[k] = BT2_FL_BASE | ((CF_EO | CF_EX) * 0x00010001u); }
+	// sendF: F for the row below in bits 0-7 of each half, its two comparison flags in bits 8-15
 	uint32_t sendH = 0, sendF = 0, prevRecvH = (lane == 0) ? 0x000000ffu : 0u;
 	// A word of the cell array holds the R cells of a strip on one diagonal (dev_common.cuh): byte k comes from
 	// the step R-1-k before the one that completes it, so the flag bytes pass through a short register pipeline
@@ -98,84 +209,17 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 	uint32_t pipe1 = 0, pipe2 = 0;
 	uint4* const out = reinterpret_cast<uint4*>(cells);
 	const int g_lo = BT2_CELL_DOFF / 4 - (int)((lane * (R + 1) + R - 1) >> 2), g_hi = BT2_CELL_DOFF / 4 - (int)(((32 + lane) * (R + 1) + R - 1) >> 2);
-	for(int t0 = 0; t0 < nsteps; t0 += 4) {
-	uint32_t accl[4], acch[4];
-	#pragma unroll
-	for(int tj = 0; tj < 4; tj++) {
-		const int t = t0 + tj;
-		const int c_lo = t - (int)lane, c_hi = c_lo - 32;
-		const bool act_lo = strip_lo && c_lo >= 0 && c_lo < cols, act_hi = strip_hi && c_hi >= 0 && c_hi < cols;
-		const uint32_t am = (act_lo ? 0xffffu : 0u) | (act_hi ? 0xffff0000u : 0u);
-		// values produced by the strip above in the previous step
-		uint32_t recvH = __shfl_up_sync(0xffffffffu, sendH, 1), recvF = __shfl_up_sync(0xffffffffu, sendF, 1);
-		const uint32_t wrapH = __shfl_sync(0xffffffffu, sendH, 31), wrapF = __shfl_sync(0xffffffffu, sendF, 31);
-		if(lane == 0) { recvH = 0x00ffu | (wrapH << 16); recvF = (wrapF << 16); } // row 0: H(-1,*) = 0xff, F = 0
-		const uint32_t x_lo = act_lo ? sh.refc[c_lo] : 4u, x_hi = act_hi ? sh.refc[c_hi] : 4u;
-		const uint32_t xpk = x_lo | (x_hi << 16);
-		uint32_t diag = prevRecvH;
-		uint32_t f = recvF & 0x00ff00ffu;                 // F(r,c) before the barrier rule (already 0 there)
-		uint32_t hup = recvH;                             // H(r-1,c)
-		uint32_t fup = (recvF >> 8) & 0x00ff00ffu;        // F(r-1,c) as stored
-		uint32_t flg[R];
-		uint32_t wlo[R], whi[R];
-		#pragma unroll
-		for(int k = 0; k < R; k++) {
-			const uint32_t s = sh.tab[(k * 5 + x_lo) * 64 + lane] | sh.tab[(k * 5 + x_hi) * 64 + 32 + lane];
-			const uint32_t hd = diag; diag = Hp[k];
-			const uint32_t u = __vadd2(hd, s);            // unsaturated H(r-1,c-1) + sc
-			const uint32_t e = Ep[k];
-			const uint32_t h = __vimax3_s16x2_relu(u, e, f);
-			// the comparisons of the backtrace at this cell
-			const uint32_t bf = __vadd2(hup, neg_rfgo[k]), af = __vadd2(fup, neg_rfge[k]);
-			uint32_t fl = Eflag[k];
-			fl |= ne2(h, u) & (CF_D * 0x00010001u);
-			fl |= ne2(h, e) & (CF_HE * 0x00010001u);
-			fl |= ne2(h, f) & (CF_HF * 0x00010001u);
-			fl |= ne2(f, bf) & (CF_FO * 0x00010001u);
-			fl |= ne2(f, af) & (CF_FX * 0x00010001u);
-			fl |= ne2(rdc2[k], xpk) & (CF_MM * 0x00010001u);
-			flg[k] = fl;
-			if(DBG) {
-				wlo[k] = __byte_perm(__byte_perm(h, e, 0x0040), f, 0x5410);
-				whi[k] = __byte_perm(__byte_perm(h, e, 0x0062), f, 0x7610);
-			}
-			if(k == kstar) {
-				if(own_lo && act_lo) sh.hlast[c_lo] = (uint8_t)(h & 0xffu);
-				if(own_hi && act_hi) sh.hlast[c_hi] = (uint8_t)((h >> 16) & 0xffu);
-			}
-			// E of the next column in this row and its two comparisons
-			const uint32_t be = __vadd2(h, neg_rdgo[k]), ae = __vadd2(e, neg_rdge);
-			const uint32_t en = __vimax3_s16x2_relu(ae, be, 0u);
-			Eflag[k] = (ne2(en, be) & (CF_EO * 0x00010001u)) | (ne2(en, ae) & (CF_EX * 0x00010001u));
-			Hp[k] = h & am; Ep[k] = en & am;
-			// F of the next row in this column
-			hup = h; fup = f;
-			f = __vimax3_s16x2_relu(__vadd2(f, k + 1 < R ? neg_rfge[(k + 1) % R] : nx_rfge), __vadd2(h, k + 1 < R ? neg_rfgo[(k + 1) % R] : nx_rfgo), 0u);
-		}
-		{ // the strip's R flag bytes of this column as one word; four steps make one 16-byte store
-			uint32_t blo, bhi;
-			if(R == 3) {
-				blo = __byte_perm(pipe2, flg[2 % R], 0x4410); bhi = __byte_perm(pipe2, flg[2 % R], 0x6632);
-				pipe2 = __byte_perm(pipe1, flg[1 % R], 0x6240); pipe1 = flg[0];
-			} else if(R == 2) {
-				blo = __byte_perm(pipe1, flg[1 % R], 0x4440); bhi = __byte_perm(pipe1, flg[1 % R], 0x6662);
-				pipe1 = flg[0];
-			} else { blo = flg[0] & 0xffu; bhi = flg[0] >> 16; }
-			accl[tj] = blo; acch[tj] = bhi;
-			if(DBG) {
-				uint32_t* dlo = hef + ((size_t)lane * BT2_HEF_T + (uint32_t)t) * 4u;
-				uint32_t* dhi = hef + ((size_t)(32 + lane) * BT2_HEF_T + (uint32_t)t) * 4u;
-				#pragma unroll
-				for(int k = 0; k < R; k++) { if(act_lo) dlo[k] = wlo[k]; if(act_hi) dhi[k] = whi[k]; }
-			}
-		}
-		sendH = Hp[R - 1]; sendF = (f | (fup << 8)) & am;
-		prevRecvH = (lane == 0) ? (0x00ffu | (recvH & 0xffff0000u)) : recvH;
+	const int t_mask = DBG ? nsteps : (nsteps < 64 ? nsteps : 64);   // every strip has started after step 63
+	#define BT2_FILL_ARGS cols, lane, sh, strip_lo, strip_hi, own_lo, own_hi, kstar, rdc2, negpen, negpenN, neg_rdgo, neg_rfgo, neg_rfge, neg_rdge, \
+		nx_rfgo, nx_rfge, Hp, Ep, Ecar, sendH, sendF, prevRecvH, pipe1, pipe2, out, g_lo, g_hi, hef
+	if(refHasN) {
+		fill_steps<R, DBG, true, true>(0, t_mask, BT2_FILL_ARGS);
+		if(!DBG) fill_steps<R, false, false, true>((t_mask + 3) & ~3, nsteps, BT2_FILL_ARGS);
+	} else {
+		fill_steps<R, DBG, true, false>(0, t_mask, BT2_FILL_ARGS);
+		if(!DBG) fill_steps<R, false, false, false>((t_mask + 3) & ~3, nsteps, BT2_FILL_ARGS);
 	}
-	// strip v is active at steps v .. v+cols-1 and its last words complete R-1 steps later
-	if(strip_lo && t0 + 3 >= (int)lane && t0 - (R - 1) < (int)lane + cols) out[(g_lo + (t0 >> 2)) * 64 + (int)lane] = make_uint4(accl[0], accl[1], accl[2], accl[3]);
-	if(strip_hi && t0 + 3 >= 32 + (int)lane && t0 - (R - 1) < 32 + (int)lane + cols) out[(g_hi + (t0 >> 2)) * 64 + 32 + (int)lane] = make_uint4(acch[0], acch[1], acch[2], acch[3]);
-	}
+	#undef BT2_FILL_ARGS
 }
 
 template<bool DBG>
@@ -192,10 +236,8 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32) k_fill(const DevParams* _
 	const int rows = pb.rows, cols = pb.cols, R = pb.R;
 	const bool fw = pb.fw != 0;
 	const uint8_t* rseq = a.seq + rs.seq_off; const uint8_t* rqual = a.qual + rs.seq_off;
-	// query profile: tab[(k*5+x)*64 + v] = -(penalty of row v*R+k against reference code x), positioned in its half
-	for(int idx = (int)lane; idx < R * 64; idx += 32) {
-		const int k = idx / 64, v = idx - k * 64;
-		const int r = v * R + k;
+	// query profile: per row its character and its penalty against a mismatching / an N reference character
+	for(int r = (int)lane; r < R * 64; r += 32) {
 		int rdc = 4, q = 0;
 		if(r < rows) {
 			if(fw) { rdc = rseq[r]; q = rqual[r]; }
@@ -203,19 +245,16 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32) k_fill(const DevParams* _
 			q -= 33; if(q < 0) q = 0; if(q > 255) q = 255;
 		}
 		sh.rdc[r] = (uint8_t)(rdc > 3 ? 7 : rdc);
-		#pragma unroll
-		for(int x = 0; x < 5; x++) {
-			int pen = 0;
-			if(r < rows) pen = (x == 4 || rdc > 3) ? (int)P.npens[q] : (x == rdc ? 0 : (int)P.mmpens[q]);
-			const uint32_t neg = (uint32_t)(-pen) & 0xffffu;
-			sh.tab[(k * 5 + x) * 64 + v] = v < 32 ? neg : (neg << 16);
-		}
+		sh.pen[r] = r < rows ? (rdc > 3 ? P.npens[q] : P.mmpens[q]) : (uint8_t)0;
+		sh.penN[r] = r < rows ? P.npens[q] : (uint8_t)0;
 	}
-	for(int c = (int)lane; c < cols; c += 32) {
-		const uint32_t m = pb.rf[c];
-		sh.refc[c] = (uint8_t)(m > 15 ? 4 : (31 - __clz(m)));
-		sh.hlast[c] = 0;
+	bool hasN = false;
+	for(int c = (int)lane; c < cols + BT2_FILL_REFPAD; c += 32) {
+		uint32_t code = 4;
+		if(c < cols) { const uint32_t m = pb.rf[c]; code = m > 15 ? 4u : (uint32_t)(31 - __clz(m)); hasN = hasN || code == 4u; sh.hlast[c] = 0; }
+		sh.refc[c] = (uint8_t)code;
 	}
+	const bool refHasN = __any_sync(0xffffffffu, hasN);
 	__syncwarp();
 	if(a.pcache) { // the problem's characters as 4-bit codes, for the backtrace's edits (dev_common.cuh)
 		uint32_t* pcw = a.pcache + (size_t)slot * BT2_PC_WORDS;
@@ -232,9 +271,9 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32) k_fill(const DevParams* _
 	}
 	uint8_t* cells = a.cells + (size_t)slot * BT2_CELL_BYTES;
 	uint32_t* hef = DBG ? a.hef_dbg + (size_t)slot * BT2_HEF_WORDS : nullptr;
-	if(R == 1) fill_body<1, DBG>(P, pb, sh, cells, hef, lane);
-	else if(R == 2) fill_body<2, DBG>(P, pb, sh, cells, hef, lane);
-	else fill_body<3, DBG>(P, pb, sh, cells, hef, lane);
+	if(R == 1) fill_body<1, DBG>(P, pb, sh, cells, hef, lane, refHasN);
+	else if(R == 2) fill_body<2, DBG>(P, pb, sh, cells, hef, lane, refHasN);
+	else fill_body<3, DBG>(P, pb, sh, cells, hef, lane, refHasN);
 	__syncwarp();
 	// ---- last-row candidates: H-0xff >= minsc, sorted by (score desc, col desc)
 	const int minsc = pb.minsc;
