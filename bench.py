@@ -285,25 +285,33 @@ def main():
     total_reads = n * world * args.steps
     value = total_reads / dev_s
     peak, peak_src = peaks()
-    # dominant kernel by device time, algorithmic bytes per launch (DESIGN.md "Kernels")
-    phases = {"k_seed": (ctr["ms_seed"], ctr["n_seed"], 128.0 * ctr["lf_sides_touched"] + 16.0 * ctr["seeds_searched"]),
-              "k_step": (ctr["ms_resolve"], ctr["n_step"], 128.0 * ctr["lf_steps_resolve"] + 8.0 * ctr["sa_rows_resolved"] + 60.0 * ctr["dp_problems"]),
-              "k_fill": (ctr["ms_fill"], ctr["n_fill"], 4.0 * ctr["dp_cells"]),
-              "k_bt": (ctr["ms_bt"], ctr["n_bt"], 12.0 * ctr["bt_steps"])}
+    # dominant kernel by device time, algorithmic bytes per launch (DESIGN.md "Kernels"):
+    #   k_seed  128 B per distinct BWT side touched by an LF step + 16 B per ftab jump + 4 B SA gather and 1 B of text per compared base
+    #   k_step  4 B SA gather per resolved row + ~60 B of packed reference and 208 B of window written per DP problem
+    #   k_fill  1 B of flags stored per DP cell + ~0.9 KB of inputs/outputs per problem (read, qualities, window, character cache, candidates)
+    #   k_bt    1 B of flags + 2 B of visited-map traffic per backtrace step
+    phases = {"k_seed": (ctr["ms_seed"], ctr["n_seed"], 128.0 * ctr["lf_sides_touched"] + 16.0 * ctr["seeds_searched"] + 1.25 * ctr["ext_text_steps"]),
+              "k_step": (ctr["ms_resolve"], ctr["n_step"], 128.0 * ctr["lf_steps_resolve"] + 4.0 * ctr["sa_rows_resolved"] + 268.0 * ctr["dp_problems"]),
+              "k_fill": (ctr["ms_fill"], ctr["n_fill"], 1.0 * ctr["dp_cells"] + 900.0 * ctr["dp_problems"]),
+              "k_bt": (ctr["ms_bt"], ctr["n_bt"], 3.0 * ctr["bt_steps"])}
     dom = max(phases, key=lambda k: phases[k][0])
     ms, nl, byts = phases[dom]
     achieved = (byts / max(nl, 1)) / ((ms / max(nl, 1)) * 1e-3) / 1e9 if ms > 0 else 0.0
+    # ncu --set full capture of the same command (profiles/): dram bytes read+written per launch of the dominant kernel
+    traffic = {"k_fill": 13.99e9}.get(dom) if n == 1000000 and world == 1 else None
     line = {"metric": METRIC, "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1000.0 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic",
             "config": {"workload": "configs[1]: 5 Mbp i.i.d. reference, 1M x 150 bp simulated reads, unpaired, %s" % OPTS,
-                       "reads_per_step_per_gpu": n, "l2": "inputs larger than L2 (300 MB of reads + 160 KB of DP scratch per problem per step)",
+                       "reads_per_step_per_gpu": n, "l2": "inputs larger than L2 (300 MB of reads + 92 KB of cell flags per DP problem per step; 126 MB L2)",
                        "aligned_fraction": aligned / float(n), "parallelism": "reads sharded, index replicated per GPU"},
             "gcups": ctr["dp_cells"] * world / dev_s / 1e9 if dev_s > 0 else None,
             "gcups_fill_kernel": ctr["dp_cells"] / (ctr["ms_fill"] * 1e-3) / 1e9 if ctr["ms_fill"] > 0 else None,
             "phase_ms_per_step": {k: phases[k][0] / args.steps for k in phases} | {"glue": ctr["ms_glue"] / args.steps, "wall": 1000.0 * wall / args.steps},
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src},
+                         "traffic": traffic, "peak_source": peak_src, "launches": int(nl), "ms_per_launch": ms / max(nl, 1),
+                         "note": "k_fill is bound by instruction issue and the half-rate integer/half2 pipes, not by HBM: ncu r1 has issue slots 79 % busy, "
+                                 "ALU pipe 81 %; measured pipe rates in profiles/r1_pipe_bench.txt"},
             "e2e": {"value": total_reads / e2e_s, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(ctr["launches"]), "clocks": clocks}
     if rank == 0:

@@ -49,8 +49,10 @@ struct FillArgs {
 
 #define BT2_FILL_WARPS 4
 #define BT2_FILL_REFPAD 80             // columns read past the window's end by strips that are done (<= 63 + R)
+#define BT2_FILL_REFOFF 32             // columns before the window's start asked for by strips that have not started
 struct FillShared {
 	uint8_t  refc[BT2GPU_MAX_COLS + 8 + BT2_FILL_REFPAD]; // reference code 0..4 per column, 4 beyond the window
+	uint32_t refw[BT2_FILL_REFOFF + BT2GPU_MAX_COLS + 8 + BT2_FILL_REFPAD]; // [REFOFF + c] = code(c) | code(c-32) << 16, 4 outside the window
 	uint8_t  hlast[BT2GPU_MAX_COLS + 8];
 	uint8_t  rdc[64 * 3];               // read code per row (0..3, 7 = N or beyond the read)
 	uint8_t  pen[64 * 3], penN[64 * 3]; // penalty of the row against a mismatching / an N reference character
@@ -90,20 +92,21 @@ __device__ __forceinline__ void fill_steps(int t0, const int t_end, const int co
 			// values produced by the strip above in the previous step (lane 0: the strip above its high half is lane 31's low half)
 			uint32_t recvH = __shfl_sync(0xffffffffu, sendH, rot), recvF = __shfl_sync(0xffffffffu, sendF, rot);
 			if(lane == 0) { recvH = 0x00ffu | (recvH << 16); recvF = ((uint32_t)(CF_FO | CF_FX) << 8) | (recvF << 16); } // row 0: H(-1,*) = 0xff, F = 0
-			uint32_t x_lo, x_hi, am = 0xffffffffu;
+			uint32_t am = 0xffffffffu;
 			bool act_lo = true, act_hi = true;
 			if(MASK) {
 				act_lo = strip_lo && c_lo >= 0 && c_lo < cols; act_hi = strip_hi && c_hi >= 0 && c_hi < cols;
 				am = (act_lo ? 0xffffu : 0u) | (act_hi ? 0xffff0000u : 0u);
-				x_lo = c_lo >= 0 ? sh.refc[c_lo] : 4u; x_hi = c_hi >= 0 ? sh.refc[c_hi] : 4u;
-			} else { x_lo = sh.refc[c_lo]; x_hi = sh.refc[c_hi]; }
-			const uint32_t xpk = x_lo | (x_hi << 16);
+			}
+			const uint32_t xpk = sh.refw[BT2_FILL_REFOFF + c_lo];  // reference characters of the two halves' columns
 			const uint32_t nmask = REFN ? __heq2_mask(as_h2(xpk), as_h2(0x00040004u)) : 0u;
 			uint32_t diag = prevRecvH;
 			uint32_t f = recvF & 0x00ff00ffu;                              // F(r,c)
-			uint32_t Fcar = ((recvF >> 8) & 0x00ff00ffu) | BT2_FL_BASE;     // its two comparisons, made where it was produced
+			// the cell's flag accumulator: the two comparisons of its E (made one step ago) and of its F (made one row up)
+			uint32_t car = __byte_perm(recvF, 0u, 0x4341) | Ecar[0];
 			uint32_t flg[R];
 			uint32_t wlo[R], whi[R];
+			uint32_t hstar = 0;
 			#pragma unroll
 			for(int k = 0; k < R; k++) {
 				const uint32_t mm = ne2(rdc2[k], xpk);
@@ -114,7 +117,7 @@ __device__ __forceinline__ void fill_steps(int t0, const int t_end, const int co
 				const uint32_t e = Ep[k];
 				const uint32_t h = __vimax3_s16x2_relu(u, e, f);
 				// the comparisons of the backtrace at this cell
-				uint32_t fl = Ecar[k] | Fcar | (mm & (CF_MM * 0x00010001u));
+				uint32_t fl = car | (mm & (CF_MM * 0x00010001u));
 				fl = flag_ne(h, u, W_D, fl);
 				fl = flag_ne(h, e, W_HE, fl);
 				fl = flag_ne(h, f, W_HF, fl);
@@ -123,10 +126,7 @@ __device__ __forceinline__ void fill_steps(int t0, const int t_end, const int co
 					wlo[k] = __byte_perm(__byte_perm(h, e, 0x0040), f, 0x5410);
 					whi[k] = __byte_perm(__byte_perm(h, e, 0x0062), f, 0x7610);
 				}
-				if(k == kstar) {
-					if(own_lo && act_lo && c_lo < cols) sh.hlast[c_lo] = (uint8_t)(h & 0xffu);
-					if(own_hi && act_hi && c_hi < cols) sh.hlast[c_hi] = (uint8_t)((h >> 16) & 0xffu);
-				}
+				if(k == kstar) hstar = h;
 				// E of the next column in this row and its two comparisons
 				const uint32_t be = __vadd2(h, neg_rdgo[k]), ae = __vadd2(e, neg_rdge);
 				const uint32_t en = __vimax_s16x2_relu(ae, be);
@@ -135,7 +135,11 @@ __device__ __forceinline__ void fill_steps(int t0, const int t_end, const int co
 				// F of the next row in this column and its two comparisons
 				const uint32_t bf = __vadd2(h, k + 1 < R ? neg_rfgo[(k + 1) % R] : nx_rfgo), af = __vadd2(f, k + 1 < R ? neg_rfge[(k + 1) % R] : nx_rfge);
 				f = __vimax_s16x2_relu(af, bf);
-				Fcar = flag_ne(f, bf, W_FO, flag_ne(f, af, W_FX, BT2_FL_BASE));
+				car = flag_ne(f, bf, W_FO, flag_ne(f, af, W_FX, k + 1 < R ? Ecar[(k + 1) % R] : BT2_FL_BASE));
+			}
+			if(own_lo || own_hi) { // the last row lives in one half of one lane
+				if(own_lo && act_lo && c_lo < cols) sh.hlast[c_lo] = (uint8_t)(hstar & 0xffu);
+				if(own_hi && act_hi && c_hi < cols) sh.hlast[c_hi] = (uint8_t)((hstar >> 16) & 0xffu);
 			}
 			{ // a word of the cell array = the strip's R cells on one diagonal: byte k comes from the step R-1-k before this one
 				uint32_t blo, bhi;
@@ -155,7 +159,7 @@ __device__ __forceinline__ void fill_steps(int t0, const int t_end, const int co
 				}
 			}
 			sendH = Hp[R - 1];
-			sendF = f | ((Fcar & 0x00ff00ffu) << 8);
+			sendF = __byte_perm(f, car, 0x6240);   // F in the low byte of each half, its two flags in the high byte
 			if(MASK) sendF &= am;
 			prevRecvH = recvH;
 		}
@@ -255,6 +259,12 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32) k_fill(const DevParams* _
 		sh.refc[c] = (uint8_t)code;
 	}
 	const bool refHasN = __any_sync(0xffffffffu, hasN);
+	__syncwarp();
+	for(int i = (int)lane; i < BT2_FILL_REFOFF + cols + BT2_FILL_REFPAD; i += 32) {
+		const int c = i - BT2_FILL_REFOFF;
+		const uint32_t lo = c >= 0 ? (uint32_t)sh.refc[c] : 4u, hi = c >= 32 ? (uint32_t)sh.refc[c - 32] : 4u;
+		sh.refw[i] = lo | (hi << 16);
+	}
 	__syncwarp();
 	if(a.pcache) { // the problem's characters as 4-bit codes, for the backtrace's edits (dev_common.cuh)
 		uint32_t* pcw = a.pcache + (size_t)slot * BT2_PC_WORDS;
