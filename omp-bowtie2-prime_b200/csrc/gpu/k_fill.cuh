@@ -53,7 +53,7 @@ struct FillArgs {
 struct FillShared {
 	uint8_t  refc[BT2GPU_MAX_COLS + 8 + BT2_FILL_REFPAD]; // reference code 0..4 per column, 4 beyond the window
 	uint32_t refw[BT2_FILL_REFOFF + BT2GPU_MAX_COLS + 8 + BT2_FILL_REFPAD]; // [REFOFF + c] = code(c) | code(c-32) << 16, 4 outside the window
-	uint8_t  hlast[BT2GPU_MAX_COLS + 8];
+	uint32_t hl[BT2GPU_MAX_COLS + 64 + 8];  // [step]: H of the strip that owns the last row (both halves of its lane), step = col + strip
 	uint8_t  rdc[64 * 3];               // read code per row (0..3, 7 = N or beyond the read)
 	uint8_t  pen[64 * 3], penN[64 * 3]; // penalty of the row against a mismatching / an N reference character
 	uint16_t ckey[BT2GPU_MAX_COLS + 8];
@@ -73,9 +73,9 @@ __device__ __forceinline__ uint32_t flag_ne(uint32_t a, uint32_t b, uint32_t w, 
 
 // The steps [t0, t_end) of the sweep, four per iteration (one 16-byte store per lane and half).
 // MASK: some strips have not reached column 0 yet (steps < 64): their H/E must stay 0.  REFN: the window contains an N.
-template<int R, bool DBG, bool MASK, bool REFN>
+template<int R, int KS, bool DBG, bool MASK, bool REFN>
 __device__ __forceinline__ void fill_steps(int t0, const int t_end, const int cols, const uint32_t lane, FillShared& sh,
-		const bool strip_lo, const bool strip_hi, const bool own_lo, const bool own_hi, const int kstar,
+		const bool strip_lo, const bool strip_hi, const bool own_any,
 		const uint32_t (&rdc2)[R], const uint32_t (&negpen)[R], const uint32_t (&negpenN)[R],
 		const uint32_t (&neg_rdgo)[R], const uint32_t (&neg_rfgo)[R], const uint32_t (&neg_rfge)[R], const uint32_t neg_rdge,
 		const uint32_t nx_rfgo, const uint32_t nx_rfge,
@@ -106,7 +106,6 @@ __device__ __forceinline__ void fill_steps(int t0, const int t_end, const int co
 			uint32_t car = __byte_perm(recvF, 0u, 0x4341) | Ecar[0];
 			uint32_t flg[R];
 			uint32_t wlo[R], whi[R];
-			uint32_t hstar = 0;
 			#pragma unroll
 			for(int k = 0; k < R; k++) {
 				const uint32_t mm = ne2(rdc2[k], xpk);
@@ -126,7 +125,6 @@ __device__ __forceinline__ void fill_steps(int t0, const int t_end, const int co
 					wlo[k] = __byte_perm(__byte_perm(h, e, 0x0040), f, 0x5410);
 					whi[k] = __byte_perm(__byte_perm(h, e, 0x0062), f, 0x7610);
 				}
-				if(k == kstar) hstar = h;
 				// E of the next column in this row and its two comparisons
 				const uint32_t be = __vadd2(h, neg_rdgo[k]), ae = __vadd2(e, neg_rdge);
 				const uint32_t en = __vimax_s16x2_relu(ae, be);
@@ -137,10 +135,7 @@ __device__ __forceinline__ void fill_steps(int t0, const int t_end, const int co
 				f = __vimax_s16x2_relu(af, bf);
 				car = flag_ne(f, bf, W_FO, flag_ne(f, af, W_FX, k + 1 < R ? Ecar[(k + 1) % R] : BT2_FL_BASE));
 			}
-			if(own_lo || own_hi) { // the last row lives in one half of one lane
-				if(own_lo && act_lo && c_lo < cols) sh.hlast[c_lo] = (uint8_t)(hstar & 0xffu);
-				if(own_hi && act_hi && c_hi < cols) sh.hlast[c_hi] = (uint8_t)((hstar >> 16) & 0xffu);
-			}
+			if(own_any) sh.hl[t] = Hp[KS];   // the last row is row KS of one half of one lane (the reader picks the half)
 			{ // a word of the cell array = the strip's R cells on one diagonal: byte k comes from the step R-1-k before this one
 				uint32_t blo, bhi;
 				if(R == 3) {
@@ -164,12 +159,12 @@ __device__ __forceinline__ void fill_steps(int t0, const int t_end, const int co
 			prevRecvH = recvH;
 		}
 		// strip v is active at steps v .. v+cols-1 and its last words complete R-1 steps later
-		if(strip_lo && t0 + 3 >= (int)lane && t0 - (R - 1) < (int)lane + cols) out[(g_lo + (t0 >> 2)) * 64 + (int)lane] = make_uint4(accl[0], accl[1], accl[2], accl[3]);
-		if(strip_hi && t0 + 3 >= 32 + (int)lane && t0 - (R - 1) < 32 + (int)lane + cols) out[(g_hi + (t0 >> 2)) * 64 + 32 + (int)lane] = make_uint4(acch[0], acch[1], acch[2], acch[3]);
+		if(strip_lo && (!MASK || t0 + 3 >= (int)lane) && t0 - (R - 1) < (int)lane + cols) out[(g_lo + (t0 >> 2)) * 64 + (int)lane] = make_uint4(accl[0], accl[1], accl[2], accl[3]);
+		if(strip_hi && (!MASK || t0 + 3 >= 32 + (int)lane) && t0 - (R - 1) < 32 + (int)lane + cols) out[(g_hi + (t0 >> 2)) * 64 + 32 + (int)lane] = make_uint4(acch[0], acch[1], acch[2], acch[3]);
 	}
 }
 
-template<int R, bool DBG>
+template<int R, int KS, bool DBG>
 __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillShared& sh, uint8_t* __restrict__ cells,
                                           uint32_t* __restrict__ hef, uint32_t lane, bool refHasN) {
 	const int rows = pb.rows, cols = pb.cols;
@@ -199,8 +194,8 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 	}
 	const bool strip_lo = (int)lane < nv, strip_hi = 32 + (int)lane < nv;
 	// which (lane, half, k) owns the last row
-	const int vstar = (rows - 1) / R, kstar = (rows - 1) - vstar * R;
-	const bool own_lo = vstar == (int)lane, own_hi = vstar == 32 + (int)lane;
+	const int vstar = (rows - 1) / R;                  // (rows - 1) % R == KS
+	const bool own_any = (vstar & 31) == (int)lane;
 	uint32_t Hp[R], Ep[R], Ecar[R];
 	#pragma unroll
 	for(int k = 0; k < R; k++) { Hp[k] = 0; Ep[k] = 0; Ecar[k] = BT2_FL_BASE | ((CF_EO | CF_EX) * 0x00010001u); }
@@ -214,14 +209,14 @@ __device__ __forceinline__ void fill_body(const DevParams& P, Problem& pb, FillS
 	uint4* const out = reinterpret_cast<uint4*>(cells);
 	const int g_lo = BT2_CELL_DOFF / 4 - (int)((lane * (R + 1) + R - 1) >> 2), g_hi = BT2_CELL_DOFF / 4 - (int)(((32 + lane) * (R + 1) + R - 1) >> 2);
 	const int t_mask = DBG ? nsteps : (nsteps < 64 ? nsteps : 64);   // every strip has started after step 63
-	#define BT2_FILL_ARGS cols, lane, sh, strip_lo, strip_hi, own_lo, own_hi, kstar, rdc2, negpen, negpenN, neg_rdgo, neg_rfgo, neg_rfge, neg_rdge, \
+	#define BT2_FILL_ARGS cols, lane, sh, strip_lo, strip_hi, own_any, rdc2, negpen, negpenN, neg_rdgo, neg_rfgo, neg_rfge, neg_rdge, \
 		nx_rfgo, nx_rfge, Hp, Ep, Ecar, sendH, sendF, prevRecvH, pipe1, pipe2, out, g_lo, g_hi, hef
 	if(refHasN) {
-		fill_steps<R, DBG, true, true>(0, t_mask, BT2_FILL_ARGS);
-		if(!DBG) fill_steps<R, false, false, true>((t_mask + 3) & ~3, nsteps, BT2_FILL_ARGS);
+		fill_steps<R, KS, DBG, true, true>(0, t_mask, BT2_FILL_ARGS);
+		if(!DBG) fill_steps<R, KS, false, false, true>((t_mask + 3) & ~3, nsteps, BT2_FILL_ARGS);
 	} else {
-		fill_steps<R, DBG, true, false>(0, t_mask, BT2_FILL_ARGS);
-		if(!DBG) fill_steps<R, false, false, false>((t_mask + 3) & ~3, nsteps, BT2_FILL_ARGS);
+		fill_steps<R, KS, DBG, true, false>(0, t_mask, BT2_FILL_ARGS);
+		if(!DBG) fill_steps<R, KS, false, false, false>((t_mask + 3) & ~3, nsteps, BT2_FILL_ARGS);
 	}
 	#undef BT2_FILL_ARGS
 }
@@ -255,7 +250,7 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32) k_fill(const DevParams* _
 	bool hasN = false;
 	for(int c = (int)lane; c < cols + BT2_FILL_REFPAD; c += 32) {
 		uint32_t code = 4;
-		if(c < cols) { const uint32_t m = pb.rf[c]; code = m > 15 ? 4u : (uint32_t)(31 - __clz(m)); hasN = hasN || code == 4u; sh.hlast[c] = 0; }
+		if(c < cols) { const uint32_t m = pb.rf[c]; code = m > 15 ? 4u : (uint32_t)(31 - __clz(m)); hasN = hasN || code == 4u; }
 		sh.refc[c] = (uint8_t)code;
 	}
 	const bool refHasN = __any_sync(0xffffffffu, hasN);
@@ -281,16 +276,19 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32) k_fill(const DevParams* _
 	}
 	uint8_t* cells = a.cells + (size_t)slot * BT2_CELL_BYTES;
 	uint32_t* hef = DBG ? a.hef_dbg + (size_t)slot * BT2_HEF_WORDS : nullptr;
-	if(R == 1) fill_body<1, DBG>(P, pb, sh, cells, hef, lane, refHasN);
-	else if(R == 2) fill_body<2, DBG>(P, pb, sh, cells, hef, lane, refHasN);
-	else fill_body<3, DBG>(P, pb, sh, cells, hef, lane, refHasN);
+	const int vstar = (rows - 1) / R, kstar = (rows - 1) - vstar * R;   // the strip and the row within it that hold the last row
+	if(R == 1) fill_body<1, 0, DBG>(P, pb, sh, cells, hef, lane, refHasN);
+	else if(R == 2) { if(kstar == 0) fill_body<2, 0, DBG>(P, pb, sh, cells, hef, lane, refHasN); else fill_body<2, 1, DBG>(P, pb, sh, cells, hef, lane, refHasN); }
+	else if(kstar == 0) fill_body<3, 0, DBG>(P, pb, sh, cells, hef, lane, refHasN);
+	else if(kstar == 1) fill_body<3, 1, DBG>(P, pb, sh, cells, hef, lane, refHasN);
+	else fill_body<3, 2, DBG>(P, pb, sh, cells, hef, lane, refHasN);
 	__syncwarp();
 	// ---- last-row candidates: H-0xff >= minsc, sorted by (score desc, col desc)
 	const int minsc = pb.minsc;
 	int lrmax = 0; uint32_t ncand = 0;
 	for(int c0 = 0; c0 < cols; c0 += 32) {
 		const int c = c0 + (int)lane;
-		const int hv = c < cols ? (int)sh.hlast[c] : 0;
+		const int hv = c < cols ? (int)((sh.hl[c + vstar] >> (vstar & 32 ? 16 : 0)) & 0xffu) : 0;
 		lrmax = max(lrmax, hv);
 		const bool isc = c < cols && (hv - 255) >= minsc;
 		const uint32_t bal = __ballot_sync(0xffffffffu, isc);
