@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <ctime>
 #include <string>
 #include <vector>
 #include <algorithm>
@@ -68,16 +69,22 @@ struct bt2gpu_ctx {
 	// problem-slot arrays
 	DBuf probs, cells, vis, pcache;
 	// per-batch arrays
-	DBuf seq, qual, seq_off, rng_seed, minsc, nceil, interval;
+	// two sets of input arrays and of packed results: while one sub-batch is being aligned the next one is
+	// uploaded and the previous one's results are copied back (bt2gpu_align_batch, separate copy streams)
+	struct InSet { DBuf seq, qual, seq_off, rng_seed, minsc, nceil, interval; } in[2];
+	struct OutSet { DBuf o_rr, o_alns, o_edits; } out[2];
+	struct CopySpan { cudaEvent_t a = nullptr, b = nullptr; bool pending = false; } h2dspan[2], d2hspan[2];
+	cudaStream_t h2d = nullptr, d2h = nullptr;
+	int cur = 0;                      // set the resident batch lives in
+	uint32_t seq_base = 0;            // seq_off[0] of the resident batch (offsets are rebased on the device)
+	uint32_t pipeChunk = 0;           // reads per sub-batch of the pipelined bt2gpu_align_batch
 	DBuf states, scratch, hits, seedtasks, exttasks, lists[7], counters, stats;
 	DBuf p_sav, p_sorted, p_rank, p_sp2, p_exr, p_exrfw, p_nsp, p_nsmall, p_nexr, p_nelt, p_nadd;
 	DBuf s_ovr, s_ovp, s_ovv, s_sr, s_sv, s_cv, s_rn, s_rcur, s_rth, s_rfl, s_rco, s_rcn, s_rns, s_mass, s_elim;
 	DBuf chunks, sats, alnp, editp, pooltops, poolerr;
 	DBuf nal, ned, albase, edbase, cubtmp;
-	DBuf o_rr, o_alns, o_edits;
-	HBuf h_counters, h_rr, h_alns, h_edits, h_in;
-	// multi sub-batch accumulation
-	std::vector<bt2gpu_read_result> acc_rr; std::vector<bt2gpu_aln> acc_alns; std::vector<bt2gpu_edit> acc_edits;
+	HBuf h_rr, h_alns, h_edits;
+	volatile HostBox* hbox = nullptr; HostBox* dbox = nullptr;   // mapped pinned mailbox (k_scalar.cuh)
 	// state of the current resident batch
 	uint32_t n = 0, W = 0, maxOffs = 0; uint64_t nbases = 0;
 	uint64_t out_alns = 0, out_edits = 0;
@@ -119,13 +126,12 @@ inline uint32_t nblk(uint64_t n, uint32_t t) { return (uint32_t)((n + t - 1) / t
 
 // copy the device counters to the host and wait
 const uint32_t* read_counters(bt2gpu_ctx* c) {
-	CK(cudaMemcpyAsync(c->h_counters.p, c->counters.p, C_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+	k_publish_counters<<<1, 32, 0, c->stream>>>(c->dbox, c->counters.as<uint32_t>());
 	CK(cudaStreamSynchronize(c->stream));
-	return c->h_counters.as<uint32_t>();
+	return const_cast<const uint32_t*>(c->hbox->counters);
 }
-void zero_counter(bt2gpu_ctx* c, int which) {
-	CK(cudaMemsetAsync(c->counters.as<uint32_t>() + which, 0, sizeof(uint32_t), c->stream));
-}
+void zero_counters(bt2gpu_ctx* c, uint32_t mask) { k_zero<<<1, 32, 0, c->stream>>>(c->counters.as<uint32_t>(), mask); }
+void zero_counter(bt2gpu_ctx* c, int which) { zero_counters(c, 1u << which); }
 
 void setup_params(bt2gpu_ctx* c, const bt2gpu_params* p) {
 	DevParams& P = c->P; memset(&P, 0, sizeof(P));
@@ -145,8 +151,6 @@ void setup_params(bt2gpu_ctx* c, const bt2gpu_params* p) {
 void ensure_batch(bt2gpu_ctx* c, uint32_t n, uint64_t nbases, uint32_t maxOffs) {
 	const uint32_t W = 2 * maxOffs;
 	const size_t nn = (size_t)n + 1;
-	c->seq.ensure(nbases + 16); c->qual.ensure(nbases + 16);
-	c->seq_off.ensure(nn * 4); c->rng_seed.ensure(nn * 4); c->minsc.ensure(nn * 4); c->nceil.ensure(nn * 4); c->interval.ensure(nn * 4);
 	c->states.ensure(nn * sizeof(ReadState));
 	c->scratch.ensure(nn * BT2_SCRATCH_EDITS * 4);
 	c->hits.ensure(nn * W * sizeof(SeedHit)); c->seedtasks.ensure(nn * W * sizeof(SeedTask)); c->exttasks.ensure(nn * W * sizeof(SeedTask));
@@ -174,74 +178,84 @@ void ensure_batch(bt2gpu_ctx* c, uint32_t n, uint64_t nbases, uint32_t maxOffs) 
 	c->nal.ensure(nn * 4); c->ned.ensure(nn * 4); c->albase.ensure(nn * 4); c->edbase.ensure(nn * 4);
 	size_t tmp = 0; cub::DeviceScan::ExclusiveSum(nullptr, tmp, (uint32_t*)nullptr, (uint32_t*)nullptr, (int)nn);
 	c->cubtmp.ensure(tmp + 256);
-	c->o_rr.ensure(nn * sizeof(bt2gpu_read_result));
-	c->h_rr.ensure(nn * sizeof(bt2gpu_read_result));
 }
 
-uint32_t max_offs_of(const bt2gpu_ctx* c, const bt2gpu_reads* in, uint32_t lo, uint32_t hi) {
-	uint32_t m = 1;
-	for(uint32_t i = lo; i < hi; i++) {
-		const uint32_t L = in->seq_off[i + 1] - in->seq_off[i];
-		const uint32_t iv = (uint32_t)std::max(1, in->interval[i]);
-		uint32_t k = 1;
-		if((int)L > c->P.seedLen) k += (L - (uint32_t)c->P.seedLen) / iv;
-		m = std::max(m, k);
-	}
-	return m;
+struct Staged { uint32_t n = 0, maxOffs = 1, base = 0; uint64_t nb = 0; int set = 0; };
+
+void settle(bt2gpu_ctx::CopySpan& sp, double& acc) { // the copy a span brackets is over (or is waited for here): add its time
+	if(!sp.pending) return;
+	CK(cudaEventSynchronize(sp.b));
+	float ms = 0; if(cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) acc += ms;
+	sp.pending = false;
 }
 
-void do_upload(bt2gpu_ctx* c, const bt2gpu_reads* in, uint32_t lo, uint32_t hi) {
-	const uint32_t n = hi - lo;
-	const uint32_t b0 = in->seq_off[lo], b1 = in->seq_off[hi];
-	const uint64_t nb = b1 - b0;
+// validates reads [lo, hi) and starts their copy into input set `set` on stream `st` (asynchronous when the
+// caller's buffers are pinned); the batch becomes the resident one with bind_staged()
+Staged stage_upload(bt2gpu_ctx* c, const bt2gpu_reads* in, uint32_t lo, uint32_t hi, int set, cudaStream_t st) {
+	Staged g; g.n = hi - lo; g.set = set; g.base = in->seq_off[lo]; g.nb = (uint64_t)in->seq_off[hi] - g.base;
+	const uint32_t seedLen = (uint32_t)c->P.seedLen;
+	uint32_t lastL = 0; int32_t lastIv = 1;          // most batches have one read length: divide only when (L, interval) changes
 	for(uint32_t i = lo; i < hi; i++) {
-		if(in->interval[i] < 1) throw std::string("bt2gpu: interval must be >= 1");
-		if(in->seq_off[i + 1] < in->seq_off[i]) throw std::string("bt2gpu: seq_off must be non-decreasing");
+		const int32_t iv = in->interval[i];
+		const uint32_t o0 = in->seq_off[i], o1 = in->seq_off[i + 1];
+		if(iv < 1) throw std::string("bt2gpu: interval must be >= 1");
+		if(o1 < o0) throw std::string("bt2gpu: seq_off must be non-decreasing");
+		const uint32_t L = o1 - o0;
+		if(L == lastL && iv == lastIv) continue;
+		lastL = L; lastIv = iv;
+		if(L > seedLen) { const uint32_t k = 1 + (L - seedLen) / (uint32_t)iv; if(k > g.maxOffs) g.maxOffs = k; }
 	}
-	const uint32_t maxOffs = max_offs_of(c, in, lo, hi);
-	if(2 * maxOffs > 65535u) throw std::string("bt2gpu: too many seeds per read");
-	ensure_batch(c, n, nb, maxOffs);
-	c->n = n; c->nbases = nb; c->maxOffs = maxOffs; c->W = 2 * maxOffs;
-	Phase ph(c, PH_H2D);
-	// offsets are rebased to the sub-batch
-	c->h_in.ensure(((size_t)n + 1) * 4);
-	uint32_t* ho = c->h_in.as<uint32_t>();
-	for(uint32_t i = 0; i <= n; i++) ho[i] = in->seq_off[lo + i] - b0;
-	CK(cudaMemcpyAsync(c->seq_off.p, ho, ((size_t)n + 1) * 4, cudaMemcpyHostToDevice, c->stream));
-	if(nb) {
-		CK(cudaMemcpyAsync(c->seq.p, in->seq + b0, nb, cudaMemcpyHostToDevice, c->stream));
-		CK(cudaMemcpyAsync(c->qual.p, in->qual + b0, nb, cudaMemcpyHostToDevice, c->stream));
+	if(2 * g.maxOffs > 65535u) throw std::string("bt2gpu: too many seeds per read");
+	bt2gpu_ctx::InSet& I = c->in[set];
+	const size_t nn = (size_t)g.n + 1;
+	I.seq.ensure(g.nb + 16); I.qual.ensure(g.nb + 16);
+	I.seq_off.ensure(nn * 4); I.rng_seed.ensure(nn * 4); I.minsc.ensure(nn * 4); I.nceil.ensure(nn * 4); I.interval.ensure(nn * 4);
+	bt2gpu_ctx::CopySpan& sp = c->h2dspan[set];
+	settle(sp, c->ctr.ms_h2d);
+	CK(cudaEventRecord(sp.a, st));
+	CK(cudaMemcpyAsync(I.seq_off.p, in->seq_off + lo, nn * 4, cudaMemcpyHostToDevice, st)); // rebased by k_begin
+	if(g.nb) {
+		CK(cudaMemcpyAsync(I.seq.p, in->seq + g.base, g.nb, cudaMemcpyHostToDevice, st));
+		CK(cudaMemcpyAsync(I.qual.p, in->qual + g.base, g.nb, cudaMemcpyHostToDevice, st));
 	}
-	if(n) {
-		CK(cudaMemcpyAsync(c->rng_seed.p, in->rng_seed + lo, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
-		CK(cudaMemcpyAsync(c->minsc.p, in->minsc + lo, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
-		CK(cudaMemcpyAsync(c->nceil.p, in->nceil + lo, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
-		CK(cudaMemcpyAsync(c->interval.p, in->interval + lo, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+	if(g.n) {
+		CK(cudaMemcpyAsync(I.rng_seed.p, in->rng_seed + lo, (size_t)g.n * 4, cudaMemcpyHostToDevice, st));
+		CK(cudaMemcpyAsync(I.minsc.p, in->minsc + lo, (size_t)g.n * 4, cudaMemcpyHostToDevice, st));
+		CK(cudaMemcpyAsync(I.nceil.p, in->nceil + lo, (size_t)g.n * 4, cudaMemcpyHostToDevice, st));
+		CK(cudaMemcpyAsync(I.interval.p, in->interval + lo, (size_t)g.n * 4, cudaMemcpyHostToDevice, st));
 	}
-	CK(cudaStreamSynchronize(c->stream)); // h_in is reused by the next upload
+	CK(cudaEventRecord(sp.b, st)); sp.pending = true;
+	return g;
+}
+
+// makes a staged batch the resident one (no kernel of the context may be running) and orders the compute
+// stream after its copy
+void bind_staged(bt2gpu_ctx* c, const Staged& g) {
+	c->cur = g.set; c->n = g.n; c->nbases = g.nb; c->maxOffs = g.maxOffs; c->W = 2 * g.maxOffs; c->seq_base = g.base;
+	ensure_batch(c, g.n, g.nb, g.maxOffs);
+	CK(cudaStreamWaitEvent(c->stream, c->h2dspan[g.set].b, 0));
 }
 
 #define LAUNCH(c) (c)->ctr.launches++
 
-void do_run(bt2gpu_ctx* c) {
+// aligns the resident batch; the packed results stay in out[cur] with offsets shifted by (aln_glob, edit_glob)
+void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 	const uint32_t n = c->n, W = c->W, maxOffs = c->maxOffs;
+	bt2gpu_ctx::InSet& I = c->in[c->cur]; bt2gpu_ctx::OutSet& O = c->out[c->cur];
 	cudaStream_t st = c->stream;
 	c->out_alns = c->out_edits = 0;
 	if(n == 0) return;
 	bt2gpu_ctx::Span runspan; runspan.ph = PH_RUN; runspan.a = get_event(c); runspan.b = get_event(c);
 	CK(cudaEventRecord(runspan.a, st));
-	CK(cudaMemsetAsync(c->counters.p, 0, C_N * 4, st));
-	CK(cudaMemsetAsync(c->pooltops.p, 0, 16, st));
-	CK(cudaMemsetAsync(c->poolerr.p, 0, 4, st));
-	CK(cudaMemsetAsync(c->stats.p, 0, 32 * 8, st));
-	CK(cudaMemsetAsync(c->scratch.p, 0, (size_t)n * BT2_SCRATCH_EDITS * 4, st));
+	k_reset<<<1, 32, 0, st>>>(c->counters.as<uint32_t>(), c->pooltops.as<uint32_t>(), c->poolerr.as<uint32_t>(), c->stats.as<unsigned long long>());
+	k_clear16<<<148 * 8, 256, 0, st>>>(c->scratch.as<uint4>(), (size_t)n * BT2_SCRATCH_EDITS / 4);
 	uint32_t* cnt = c->counters.as<uint32_t>();
 	unsigned long long* stats = c->stats.as<unsigned long long>();
 	ReadState* states = c->states.as<ReadState>();
 	uint32_t* L[7]; for(int i = 0; i < 7; i++) L[i] = c->lists[i].as<uint32_t>();
 	// L0/L1 round candidates, L2 active, L3/L4 extension ping-pong, L5 round end, L6 sampling
-	BatchArrays ba; ba.n = n; ba.seq_off = c->seq_off.as<uint32_t>(); ba.seq = c->seq.as<uint8_t>(); ba.qual = c->qual.as<uint8_t>();
-	ba.rng_seed = c->rng_seed.as<uint32_t>(); ba.minsc = c->minsc.as<int32_t>(); ba.nceil = c->nceil.as<int32_t>(); ba.interval = c->interval.as<int32_t>();
+	BatchArrays ba; ba.n = n; ba.seq_base = c->seq_base; ba.seq_off = I.seq_off.as<uint32_t>(); ba.seq = I.seq.as<uint8_t>(); ba.qual = I.qual.as<uint8_t>();
+	ba.rng_seed = I.rng_seed.as<uint32_t>(); ba.minsc = I.minsc.as<int32_t>(); ba.nceil = I.nceil.as<int32_t>(); ba.interval = I.interval.as<int32_t>();
 	PrioArrays pa; pa.sav = c->p_sav.as<uint16_t>(); pa.sorted = c->p_sorted.as<uint8_t>(); pa.rank = c->p_rank.as<uint16_t>(); pa.sp2 = c->p_sp2.as<uint16_t>();
 	pa.exr = c->p_exr.as<ExRange16>(); pa.exrfw = c->p_exrfw.as<uint8_t>(); pa.nsp = c->p_nsp.as<uint32_t>(); pa.nsmall = c->p_nsmall.as<uint32_t>();
 	pa.nexr = c->p_nexr.as<uint32_t>(); pa.nelt = c->p_nelt.as<uint64_t>(); pa.nelt_added = c->p_nadd.as<uint32_t>();
@@ -261,8 +275,8 @@ void do_run(bt2gpu_ctx* c) {
 	uint32_t ncand = read_counters(c)[C_CAND0];
 	int cand = 0;
 	for(uint32_t round = 0; ncand > 0; round++) {
-		zero_counter(c, C_ACTIVE); zero_counter(c, C_EXT0); zero_counter(c, C_EXT1); zero_counter(c, C_ROUNDEND);
-		zero_counter(c, C_SAMP); zero_counter(c, C_SEEDTASK); zero_counter(c, C_SEEDNT); zero_counter(c, C_XTASKN); zero_counter(c, C_XTASK); zero_counter(c, cand ? C_CAND0 : C_CAND1);
+		zero_counters(c, (1u << C_ACTIVE) | (1u << C_EXT0) | (1u << C_EXT1) | (1u << C_ROUNDEND) | (1u << C_SAMP) | (1u << C_SEEDTASK) | (1u << C_SEEDNT)
+		               | (1u << C_XTASKN) | (1u << C_XTASK) | (1u << (cand ? C_CAND0 : C_CAND1)));
 		k_round_select<<<nblk(ncand, 256), 256, 0, st>>>(c->dP, states, L[cand], ncand, round, L[2], cnt + C_ACTIVE); LAUNCH(c);
 		const uint32_t nactive = read_counters(c)[C_ACTIVE];
 		if(nactive == 0) break;
@@ -326,25 +340,22 @@ void do_run(bt2gpu_ctx* c) {
 		CK(cub::DeviceScan::ExclusiveSum(c->cubtmp.p, tmp, c->nal.as<uint32_t>(), c->albase.as<uint32_t>(), (int)n, st)); LAUNCH(c);
 		tmp = c->cubtmp.cap;
 		CK(cub::DeviceScan::ExclusiveSum(c->cubtmp.p, tmp, c->ned.as<uint32_t>(), c->edbase.as<uint32_t>(), (int)n, st)); LAUNCH(c);
-		uint32_t last[4];
-		CK(cudaMemcpyAsync(&last[0], c->albase.as<uint32_t>() + (n - 1), 4, cudaMemcpyDeviceToHost, st));
-		CK(cudaMemcpyAsync(&last[1], c->nal.as<uint32_t>() + (n - 1), 4, cudaMemcpyDeviceToHost, st));
-		CK(cudaMemcpyAsync(&last[2], c->edbase.as<uint32_t>() + (n - 1), 4, cudaMemcpyDeviceToHost, st));
-		CK(cudaMemcpyAsync(&last[3], c->ned.as<uint32_t>() + (n - 1), 4, cudaMemcpyDeviceToHost, st));
-		uint32_t perr = 0;
-		CK(cudaMemcpyAsync(&perr, c->poolerr.p, 4, cudaMemcpyDeviceToHost, st));
+		k_publish_tail<<<1, 32, 0, st>>>(c->dbox, c->albase.as<uint32_t>(), c->nal.as<uint32_t>(), c->edbase.as<uint32_t>(), c->ned.as<uint32_t>(), n, c->poolerr.as<uint32_t>());
 		CK(cudaStreamSynchronize(st));
+		const volatile uint32_t* last = c->hbox->last; const uint32_t perr = c->hbox->perr;
 		if(perr) { char b[128]; snprintf(b, sizeof(b), "bt2gpu: device pool exhausted (mask %u); use smaller batches", perr); throw std::string(b); }
 		c->out_alns = (uint64_t)last[0] + last[1]; c->out_edits = (uint64_t)last[2] + last[3];
-		c->o_alns.ensure((c->out_alns + 1) * sizeof(bt2gpu_aln)); c->o_edits.ensure((c->out_edits + 1) * sizeof(bt2gpu_edit));
-		k_gather<<<nblk(n, 128), 128, 0, st>>>(states, pools, c->scratch.as<uint32_t>(), n, c->albase.as<uint32_t>(), c->edbase.as<uint32_t>(),
-		                                       c->o_rr.as<bt2gpu_read_result>(), c->o_alns.as<bt2gpu_aln>(), c->o_edits.as<bt2gpu_edit>()); LAUNCH(c);
+		settle(c->d2hspan[c->cur], c->ctr.ms_d2h);   // the previous results in this set have been copied out
+		O.o_rr.ensure(((size_t)n + 1) * sizeof(bt2gpu_read_result));
+		O.o_alns.ensure((c->out_alns + 1) * sizeof(bt2gpu_aln)); O.o_edits.ensure((c->out_edits + 1) * sizeof(bt2gpu_edit));
+		k_gather<<<nblk(n, 128), 128, 0, st>>>(states, pools, c->scratch.as<uint32_t>(), n, c->albase.as<uint32_t>(), c->edbase.as<uint32_t>(), aln_glob, edit_glob,
+		                                       O.o_rr.as<bt2gpu_read_result>(), O.o_alns.as<bt2gpu_aln>(), O.o_edits.as<bt2gpu_edit>()); LAUNCH(c);
 	}
 	CK(cudaEventRecord(runspan.b, st)); c->spans.push_back(runspan);
 	// ---- counters
-	unsigned long long hs[32];
-	CK(cudaMemcpyAsync(hs, c->stats.p, sizeof(hs), cudaMemcpyDeviceToHost, st));
+	k_publish_stats<<<1, 32, 0, st>>>(c->dbox, c->stats.as<unsigned long long>());
 	CK(cudaStreamSynchronize(st));
+	const volatile unsigned long long* hs = c->hbox->stats;
 	CK(cudaGetLastError());
 	c->ctr.reads += n; c->ctr.seeds_searched += hs[0]; c->ctr.lf_steps_search += hs[1]; c->ctr.lf_steps_extend += hs[2]; c->ctr.lf_sides_touched += hs[3]; c->ctr.ext_text_steps += hs[4];
 	c->ctr.dp_problems += hs[8]; c->ctr.dp_cells += hs[9];
@@ -352,19 +363,75 @@ void do_run(bt2gpu_ctx* c) {
 	flush_spans(c);
 }
 
+// grows a pinned result buffer, keeping what is already in it
+void grow_keep(HBuf& h, size_t keep, size_t want) {
+	if(want <= h.cap) return;
+	HBuf nb; nb.ensure(std::max(want, h.cap * 2));
+	if(keep) memcpy(nb.p, h.p, keep);
+	h.release(); h = nb;
+}
+
+// starts the copy of the resident batch's packed results to the pinned host arrays at (read, alignment, edit)
+// offsets (rb, ab, eb) on stream `st`; the compute stream has been synchronised by do_run
+void start_fetch(bt2gpu_ctx* c, size_t rb, size_t ab, size_t eb, cudaStream_t st) {
+	const uint32_t n = c->n;
+	bt2gpu_ctx::OutSet& O = c->out[c->cur];
+	bt2gpu_ctx::CopySpan& sp = c->d2hspan[c->cur];
+	settle(sp, c->ctr.ms_d2h);
+	CK(cudaEventRecord(sp.a, st));
+	if(n) CK(cudaMemcpyAsync(c->h_rr.as<bt2gpu_read_result>() + rb, O.o_rr.p, (size_t)n * sizeof(bt2gpu_read_result), cudaMemcpyDeviceToHost, st));
+	if(c->out_alns) CK(cudaMemcpyAsync(c->h_alns.as<bt2gpu_aln>() + ab, O.o_alns.p, c->out_alns * sizeof(bt2gpu_aln), cudaMemcpyDeviceToHost, st));
+	if(c->out_edits) CK(cudaMemcpyAsync(c->h_edits.as<bt2gpu_edit>() + eb, O.o_edits.p, c->out_edits * sizeof(bt2gpu_edit), cudaMemcpyDeviceToHost, st));
+	CK(cudaEventRecord(sp.b, st)); sp.pending = true;
+}
+
 void do_fetch(bt2gpu_ctx* c, bt2gpu_results* out) {
 	const uint32_t n = c->n;
+	c->h_rr.ensure(((size_t)n + 1) * sizeof(bt2gpu_read_result));
 	c->h_alns.ensure((c->out_alns + 1) * sizeof(bt2gpu_aln)); c->h_edits.ensure((c->out_edits + 1) * sizeof(bt2gpu_edit));
-	{
-		Phase ph(c, PH_D2H);
-		if(n) CK(cudaMemcpyAsync(c->h_rr.p, c->o_rr.p, (size_t)n * sizeof(bt2gpu_read_result), cudaMemcpyDeviceToHost, c->stream));
-		if(c->out_alns) CK(cudaMemcpyAsync(c->h_alns.p, c->o_alns.p, c->out_alns * sizeof(bt2gpu_aln), cudaMemcpyDeviceToHost, c->stream));
-		if(c->out_edits) CK(cudaMemcpyAsync(c->h_edits.p, c->o_edits.p, c->out_edits * sizeof(bt2gpu_edit), cudaMemcpyDeviceToHost, c->stream));
-	}
-	CK(cudaStreamSynchronize(c->stream));
-	flush_spans(c);
+	start_fetch(c, 0, 0, 0, c->stream);
+	settle(c->d2hspan[c->cur], c->ctr.ms_d2h);
 	out->n = n; out->reads = c->h_rr.as<bt2gpu_read_result>(); out->alns = c->h_alns.as<bt2gpu_aln>(); out->n_alns = c->out_alns;
 	out->edits = c->h_edits.as<bt2gpu_edit>(); out->n_edits = c->out_edits;
+}
+
+// bt2gpu_align_batch for more reads than one sub-batch: sub-batch s+1 is uploaded and sub-batch s-1's results are
+// copied back while sub-batch s is aligned (input / result sets alternate; copies run on their own streams)
+void do_align_pipelined(bt2gpu_ctx* c, const bt2gpu_reads* in, bt2gpu_results* out, uint32_t chunk) {
+	const uint32_t n = in->n;
+	c->h_rr.ensure(((size_t)n + 1) * sizeof(bt2gpu_read_result));
+	grow_keep(c->h_alns, 0, ((size_t)n + (n >> 2) + 1024) * sizeof(bt2gpu_aln));
+	grow_keep(c->h_edits, 0, ((size_t)n * 4 + 4096) * sizeof(bt2gpu_edit));
+	size_t rb = 0, ab = 0, eb = 0;
+	static const bool trace = getenv("BT2GPU_TRACE") != nullptr;
+	auto now = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
+	const double t00 = now();
+	Staged g = stage_upload(c, in, 0, std::min(n, chunk), 0, c->h2d);
+	for(uint32_t lo = 0; lo < n; lo += chunk) {
+		const uint32_t hi = std::min(n, lo + chunk);
+		Staged nx;
+		const double t0 = now();
+		if(hi < n) nx = stage_upload(c, in, hi, std::min(n, hi + chunk), g.set ^ 1, c->h2d); // the other set's batch finished before this point
+		const double t1 = now();
+		bind_staged(c, g);
+		if(ab > 0xf0000000ull || eb > 0xf0000000ull) throw std::string("bt2gpu_align_batch: more than 2^32 alignments or edits in one call; use smaller batches");
+		do_run(c, (uint32_t)ab, (uint32_t)eb);
+		const double t2 = now();
+		if(trace) fprintf(stderr, "[bt2gpu] sub-batch at %u: +%.2f ms  stage next %.2f ms  run %.2f ms\n", lo, t0 - t00, t1 - t0, t2 - t1);
+		if((ab + c->out_alns + 1) * sizeof(bt2gpu_aln) > c->h_alns.cap || (eb + c->out_edits + 1) * sizeof(bt2gpu_edit) > c->h_edits.cap) {
+			CK(cudaStreamSynchronize(c->d2h)); // copies into the old arrays are over before they move
+			grow_keep(c->h_alns, ab * sizeof(bt2gpu_aln), (ab + c->out_alns + 1) * sizeof(bt2gpu_aln));
+			grow_keep(c->h_edits, eb * sizeof(bt2gpu_edit), (eb + c->out_edits + 1) * sizeof(bt2gpu_edit));
+		}
+		start_fetch(c, rb, ab, eb, c->d2h);
+		rb += c->n; ab += c->out_alns; eb += c->out_edits;
+		g = nx;
+	}
+	const double t3 = now();
+	for(int k = 0; k < 2; k++) { settle(c->d2hspan[k], c->ctr.ms_d2h); settle(c->h2dspan[k], c->ctr.ms_h2d); }
+	if(trace) fprintf(stderr, "[bt2gpu] drain %.2f ms, total %.2f ms\n", now() - t3, now() - t00);
+	out->n = n; out->reads = c->h_rr.as<bt2gpu_read_result>(); out->alns = c->h_alns.as<bt2gpu_aln>(); out->n_alns = ab;
+	out->edits = c->h_edits.as<bt2gpu_edit>(); out->n_edits = eb;
 }
 
 } // namespace
@@ -391,6 +458,10 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		c->device = device; c->hp = *p;
 		memset(&c->ctr, 0, sizeof(c->ctr));
 		CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+		CK(cudaStreamCreateWithFlags(&c->h2d, cudaStreamNonBlocking)); CK(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
+		for(int k = 0; k < 2; k++) {
+			CK(cudaEventCreate(&c->h2dspan[k].a)); CK(cudaEventCreate(&c->h2dspan[k].b)); CK(cudaEventCreate(&c->d2hspan[k].a)); CK(cudaEventCreate(&c->d2hspan[k].b));
+		}
 		setup_params(c, p);
 		CK(cudaMalloc((void**)&c->dP, sizeof(DevParams)));
 		CK(cudaMemcpy(c->dP, &c->P, sizeof(DevParams), cudaMemcpyHostToDevice));
@@ -448,11 +519,13 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		c->nslots = slots; c->sampSlots = 2048;
 		c->maxBatch = eb ? (uint32_t)atoi(eb) : (1u << 20);
 		if(c->maxBatch < 1) c->maxBatch = 1;
+		{ const char* ep = getenv("BT2GPU_PIPE"); c->pipeChunk = ep ? (uint32_t)std::max(1, atoi(ep)) : 262144u; }
 		c->probs.ensure((size_t)slots * sizeof(Problem)); c->cells.ensure((size_t)slots * BT2_CELL_BYTES);
 		c->vis.ensure((size_t)slots * BT2_VIS_WORDS * 4);
 		CK(cudaMemset(c->vis.p, 0, (size_t)slots * BT2_VIS_WORDS * 4)); c->pcache.ensure((size_t)slots * BT2_PC_WORDS * 4);
 		c->counters.ensure(C_N * 4); c->stats.ensure(32 * 8); c->pooltops.ensure(16); c->poolerr.ensure(4);
-		c->h_counters.ensure(C_N * 4);
+		{ void* hb = nullptr; CK(cudaHostAlloc(&hb, sizeof(HostBox), cudaHostAllocMapped)); memset(hb, 0, sizeof(HostBox));
+		  c->hbox = reinterpret_cast<volatile HostBox*>(hb); void* db = nullptr; CK(cudaHostGetDevicePointer(&db, hb, 0)); c->dbox = reinterpret_cast<HostBox*>(db); }
 		CK(cudaDeviceSynchronize());
 	} catch(const std::string& e) {
 		if(err && errlen) snprintf(err, errlen, "%s", e.c_str());
@@ -471,8 +544,8 @@ int bt2gpu_upload(bt2gpu_ctx* ctx, const bt2gpu_reads* in) {
 	API_GUARD({
 		if(!in) throw std::string("bt2gpu_upload: null batch");
 		if(in->n > ctx->maxBatch) throw std::string("bt2gpu_upload: batch larger than BT2GPU_BATCH; use bt2gpu_align_batch");
-		do_upload(ctx, in, 0, in->n);
-		flush_spans(ctx);
+		bind_staged(ctx, stage_upload(ctx, in, 0, in->n, 0, ctx->stream));
+		settle(ctx->h2dspan[0], ctx->ctr.ms_h2d);
 	})
 }
 int bt2gpu_run_resident(bt2gpu_ctx* ctx) { API_GUARD({ do_run(ctx); }) }
@@ -481,22 +554,9 @@ int bt2gpu_fetch(bt2gpu_ctx* ctx, bt2gpu_results* out) { API_GUARD({ if(!out) th
 int bt2gpu_align_batch(bt2gpu_ctx* ctx, const bt2gpu_reads* in, bt2gpu_results* out) {
 	API_GUARD({
 		if(!in || !out) throw std::string("bt2gpu_align_batch: null argument");
-		if(in->n <= ctx->maxBatch) {
-			do_upload(ctx, in, 0, in->n); do_run(ctx); do_fetch(ctx, out);
-		} else {
-			ctx->acc_rr.clear(); ctx->acc_alns.clear(); ctx->acc_edits.clear();
-			for(uint32_t lo = 0; lo < in->n; lo += ctx->maxBatch) {
-				const uint32_t hi = std::min(in->n, lo + ctx->maxBatch);
-				bt2gpu_results r;
-				do_upload(ctx, in, lo, hi); do_run(ctx); do_fetch(ctx, &r);
-				const uint32_t ab = (uint32_t)ctx->acc_alns.size(), eb2 = (uint32_t)ctx->acc_edits.size();
-				for(uint32_t i = 0; i < r.n; i++) { bt2gpu_read_result x = r.reads[i]; x.aln_off += ab; x.scratch_off += eb2; ctx->acc_rr.push_back(x); }
-				for(uint64_t i = 0; i < r.n_alns; i++) { bt2gpu_aln x = r.alns[i]; x.edit_off += eb2; ctx->acc_alns.push_back(x); }
-				ctx->acc_edits.insert(ctx->acc_edits.end(), r.edits, r.edits + r.n_edits);
-			}
-			out->n = in->n; out->reads = ctx->acc_rr.data(); out->alns = ctx->acc_alns.data(); out->n_alns = ctx->acc_alns.size();
-			out->edits = ctx->acc_edits.data(); out->n_edits = ctx->acc_edits.size();
-		}
+		const uint32_t chunk = std::min(ctx->pipeChunk, ctx->maxBatch);
+		if(in->n <= chunk) { bind_staged(ctx, stage_upload(ctx, in, 0, in->n, 0, ctx->stream)); do_run(ctx); do_fetch(ctx, out); }
+		else do_align_pipelined(ctx, in, out, chunk);
 	})
 }
 
@@ -515,15 +575,15 @@ int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, c
 			memcpy(hp[i].rf, rf + rf_off[i], (size_t)cols[i] + 1);
 			nb = std::max<uint64_t>(nb, (uint64_t)seq_off[i] + rows[i]);
 		}
-		ctx->seq.ensure(nb + 16); ctx->qual.ensure(nb + 16); ctx->states.ensure((size_t)nprob * sizeof(ReadState));
+		ctx->in[0].seq.ensure(nb + 16); ctx->in[0].qual.ensure(nb + 16); ctx->states.ensure((size_t)nprob * sizeof(ReadState));
 		cudaStream_t st = ctx->stream;
-		CK(cudaMemcpyAsync(ctx->seq.p, seq, nb, cudaMemcpyHostToDevice, st)); CK(cudaMemcpyAsync(ctx->qual.p, qual, nb, cudaMemcpyHostToDevice, st));
+		CK(cudaMemcpyAsync(ctx->in[0].seq.p, seq, nb, cudaMemcpyHostToDevice, st)); CK(cudaMemcpyAsync(ctx->in[0].qual.p, qual, nb, cudaMemcpyHostToDevice, st));
 		CK(cudaMemcpyAsync(ctx->states.p, hs.data(), (size_t)nprob * sizeof(ReadState), cudaMemcpyHostToDevice, st));
 		CK(cudaMemcpyAsync(ctx->probs.p, hp.data(), (size_t)nprob * sizeof(Problem), cudaMemcpyHostToDevice, st));
 		CK(cudaMemsetAsync(ctx->stats.p, 0, 32 * 8, st));
-		FillArgs fa; fa.probs = ctx->probs.as<Problem>(); fa.nprob = nprob; fa.states = ctx->states.as<ReadState>(); fa.seq = ctx->seq.as<uint8_t>();
+		FillArgs fa; fa.probs = ctx->probs.as<Problem>(); fa.nprob = nprob; fa.states = ctx->states.as<ReadState>(); fa.seq = ctx->in[0].seq.as<uint8_t>();
 		DBuf dbg; dbg.ensure((size_t)nprob * BT2_HEF_WORDS * 4);
-		fa.qual = ctx->qual.as<uint8_t>(); fa.cells = ctx->cells.as<uint8_t>(); fa.pcache = nullptr; fa.hef_dbg = dbg.as<uint32_t>(); fa.stats = ctx->stats.as<unsigned long long>() + 8;
+		fa.qual = ctx->in[0].qual.as<uint8_t>(); fa.cells = ctx->cells.as<uint8_t>(); fa.pcache = nullptr; fa.hef_dbg = dbg.as<uint32_t>(); fa.stats = ctx->stats.as<unsigned long long>() + 8;
 		k_fill<true><<<nblk(nprob, BT2_FILL_WARPS), BT2_FILL_WARPS * 32, 0, st>>>(ctx->dP, fa);
 		CK(cudaMemcpyAsync(hp.data(), ctx->probs.p, (size_t)nprob * sizeof(Problem), cudaMemcpyDeviceToHost, st));
 		std::vector<uint32_t> w(BT2_HEF_WORDS); std::vector<uint8_t> wc(BT2_CELL_BYTES);
@@ -555,13 +615,23 @@ void bt2gpu_destroy(bt2gpu_ctx* c) {
 	cudaDeviceSynchronize();
 	for(void* p : c->resident) cudaFree(p);
 	if(c->dP) cudaFree(c->dP);
-	DBuf* all[] = { &c->probs, &c->cells, &c->vis, &c->pcache, &c->seq, &c->qual, &c->seq_off, &c->rng_seed, &c->minsc, &c->nceil, &c->interval,
+	DBuf* all[] = { &c->probs, &c->cells, &c->vis, &c->pcache,
 		&c->states, &c->scratch, &c->hits, &c->seedtasks, &c->exttasks, &c->lists[0], &c->lists[1], &c->lists[2], &c->lists[3], &c->lists[4], &c->lists[5], &c->lists[6], &c->counters, &c->stats,
 		&c->p_sav, &c->p_sorted, &c->p_rank, &c->p_sp2, &c->p_exr, &c->p_exrfw, &c->p_nsp, &c->p_nsmall, &c->p_nexr, &c->p_nelt, &c->p_nadd,
 		&c->s_ovr, &c->s_ovp, &c->s_ovv, &c->s_sr, &c->s_sv, &c->s_cv, &c->s_rn, &c->s_rcur, &c->s_rth, &c->s_rfl, &c->s_rco, &c->s_rcn, &c->s_rns, &c->s_mass, &c->s_elim,
-		&c->chunks, &c->sats, &c->alnp, &c->editp, &c->pooltops, &c->poolerr, &c->nal, &c->ned, &c->albase, &c->edbase, &c->cubtmp, &c->o_rr, &c->o_alns, &c->o_edits };
+		&c->chunks, &c->sats, &c->alnp, &c->editp, &c->pooltops, &c->poolerr, &c->nal, &c->ned, &c->albase, &c->edbase, &c->cubtmp };
 	for(DBuf* b : all) b->release();
-	HBuf* hall[] = { &c->h_counters, &c->h_rr, &c->h_alns, &c->h_edits, &c->h_in };
+	for(int k = 0; k < 2; k++) {
+		DBuf* io[] = { &c->in[k].seq, &c->in[k].qual, &c->in[k].seq_off, &c->in[k].rng_seed, &c->in[k].minsc, &c->in[k].nceil, &c->in[k].interval,
+			&c->out[k].o_rr, &c->out[k].o_alns, &c->out[k].o_edits };
+		for(DBuf* b : io) b->release();
+		cudaEvent_t ev[] = { c->h2dspan[k].a, c->h2dspan[k].b, c->d2hspan[k].a, c->d2hspan[k].b };
+		for(cudaEvent_t e : ev) if(e) cudaEventDestroy(e);
+	}
+	if(c->h2d) cudaStreamDestroy(c->h2d);
+	if(c->d2h) cudaStreamDestroy(c->d2h);
+	if(c->hbox) cudaFreeHost(const_cast<HostBox*>(c->hbox));
+	HBuf* hall[] = { &c->h_rr, &c->h_alns, &c->h_edits };
 	for(HBuf* b : hall) b->release();
 	for(cudaEvent_t e : c->evpool) cudaEventDestroy(e);
 	if(c->stream) cudaStreamDestroy(c->stream);

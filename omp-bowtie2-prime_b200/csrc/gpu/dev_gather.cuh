@@ -1,3 +1,4 @@
+// (aln_glob, edit_glob): where this batch's arrays start in the caller-visible result arrays (pipelined sub-batches).
 // Packs the per-read device state into the C-ABI result arrays (include/bt2gpu.h):
 // what AlnSinkWrap::report received, in call order, plus what the host restores
 // before AlnSinkWrap::finishRead (RNG state, minsc, PerReadMetrics, F14 scratch).
@@ -25,9 +26,9 @@ BT2_HD uint32_t read_edit_count(const ReadState& rs, const Pools& pools) {
 }
 
 BT2_HD void gather_read(const ReadState& rs, const Pools& pools, const uint32_t* scratch,
-                        uint32_t aln_base, uint32_t edit_base,
+                        uint32_t aln_base, uint32_t edit_base, uint32_t aln_glob, uint32_t edit_glob,
                         bt2gpu_read_result& rr, bt2gpu_aln* alns, bt2gpu_edit* edits) {
-	rr.aln_off = aln_base; rr.n_alns = rs.n_alns;
+	rr.aln_off = aln_base + aln_glob; rr.n_alns = rs.n_alns;
 	rr.rng_last = rs.rnd.last; rr.rng_lastOff = rs.rnd.lastOff;
 	rr.minsc = rs.minsc; rr.status = rs.status; rr.flags = rs.flags; rr.rounds = rs.roundsRun; rr.done_policy = rs.donePolicy;
 	rr.nExIters = rs.nExIters; rr.nExDps = rs.nExDps; rr.nExDpSuccs = rs.nExDpSuccs; rr.nExDpFails = rs.nExDpFails;
@@ -47,13 +48,13 @@ BT2_HD void gather_read(const ReadState& rs, const Pools& pools, const uint32_t*
 		end -= a.n_edits;
 		bt2gpu_aln& o = alns[aln_base + k];
 		o.refoff = a.refoff; o.tidx = a.tidx; o.score = a.score; o.minsc = a.minsc; o.ns = a.ns; o.gaps = a.gaps;
-		o.edits = a.edits; o.basesAligned = a.basesAligned; o.refns = a.refns; o.edit_off = end; o.n_edits = a.n_edits;
+		o.edits = a.edits; o.basesAligned = a.basesAligned; o.refns = a.refns; o.edit_off = end + edit_glob; o.n_edits = a.n_edits;
 		o.fw = a.fw; o.pad = 0;
 		for(uint32_t i = 0; i < a.n_edits; i++) unpack_edit(pools.edits[a.edit_off + i], edits[end + i]);
 	}
 	eo = edit_base + tot;
 	const uint32_t ns = scratch_count(rs, pools);
-	rr.scratch_off = eo; rr.n_scratch = ns;
+	rr.scratch_off = eo + edit_glob; rr.n_scratch = ns;
 	for(uint32_t i = 0; i < ns; i++) unpack_edit(scratch[i], edits[eo + i]);
 }
 

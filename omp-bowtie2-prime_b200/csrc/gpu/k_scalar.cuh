@@ -12,10 +12,31 @@
 namespace bt2 {
 
 struct BatchArrays {
-	uint32_t n;
+	uint32_t n, seq_base;      // seq_off[i] - seq_base indexes seq/qual
 	const uint32_t* seq_off; const uint8_t* seq; const uint8_t* qual;
 	const uint32_t* rng_seed; const int32_t* minsc; const int32_t* nceil; const int32_t* interval;
 };
+
+// What the host reads between phases: written by tiny kernels straight into mapped pinned host memory, so the
+// compute stream never queues a transfer behind the bulk copies of the neighbouring sub-batches (copy engines).
+struct HostBox { uint32_t counters[16]; uint32_t last[4]; uint32_t perr; uint32_t pad[3]; unsigned long long stats[32]; };
+
+__global__ void k_zero(uint32_t* cnt, uint32_t mask) { if(threadIdx.x < 16 && ((mask >> threadIdx.x) & 1u)) cnt[threadIdx.x] = 0; }
+__global__ void k_reset(uint32_t* cnt, uint32_t* pooltops, uint32_t* poolerr, unsigned long long* stats) {
+	const uint32_t t = threadIdx.x;
+	if(t < 16) cnt[t] = 0;
+	if(t < 4) pooltops[t] = 0;
+	if(t == 0) *poolerr = 0;
+	if(t < 32) stats[t] = 0;
+}
+__global__ void k_clear16(uint4* p, size_t n16) { // zero n16 16-byte words
+	for(size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) p[i] = make_uint4(0, 0, 0, 0);
+}
+__global__ void k_publish_counters(HostBox* box, const uint32_t* cnt) { if(threadIdx.x < 16) box->counters[threadIdx.x] = cnt[threadIdx.x]; }
+__global__ void k_publish_tail(HostBox* box, const uint32_t* albase, const uint32_t* nal, const uint32_t* edbase, const uint32_t* ned, uint32_t n, const uint32_t* poolerr) {
+	if(threadIdx.x == 0) { box->last[0] = albase[n - 1]; box->last[1] = nal[n - 1]; box->last[2] = edbase[n - 1]; box->last[3] = ned[n - 1]; box->perr = *poolerr; }
+}
+__global__ void k_publish_stats(HostBox* box, const unsigned long long* stats) { if(threadIdx.x < 32) box->stats[threadIdx.x] = stats[threadIdx.x]; }
 
 __device__ __forceinline__ void list_append(uint32_t* list, uint32_t* cnt, uint32_t v) { list[atomicAdd(cnt, 1u)] = v; }
 
@@ -24,7 +45,7 @@ __global__ void k_begin(const BatchArrays b, ReadState* states, uint32_t* list, 
 	if(i >= b.n) return;
 	ReadState rs;
 	const uint32_t so = b.seq_off[i];
-	read_begin(rs, so, b.seq_off[i + 1] - so, b.rng_seed[i], b.minsc[i], b.nceil[i], b.interval[i]);
+	read_begin(rs, so - b.seq_base, b.seq_off[i + 1] - so, b.rng_seed[i], b.minsc[i], b.nceil[i], b.interval[i]);
 	states[i] = rs;
 	if(rs.phase != RS_FINISHED) list_append(list, cnt, i);
 }
@@ -207,12 +228,12 @@ __global__ void k_count(const ReadState* states, const Pools pools, uint32_t n, 
 }
 
 __global__ void k_gather(const ReadState* states, const Pools pools, const uint32_t* scratch, uint32_t n,
-                         const uint32_t* aln_base, const uint32_t* edit_base,
+                         const uint32_t* aln_base, const uint32_t* edit_base, uint32_t aln_glob, uint32_t edit_glob,
                          bt2gpu_read_result* rr, bt2gpu_aln* alns, bt2gpu_edit* edits) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if(i >= n) return;
 	bt2gpu_read_result r;
-	gather_read(states[i], pools, scratch + (size_t)i * BT2_SCRATCH_EDITS, aln_base[i], edit_base[i], r, alns, edits);
+	gather_read(states[i], pools, scratch + (size_t)i * BT2_SCRATCH_EDITS, aln_base[i], edit_base[i], aln_glob, edit_glob, r, alns, edits);
 	rr[i] = r;
 }
 

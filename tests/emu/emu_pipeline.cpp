@@ -178,7 +178,7 @@ int main(int argc, char** argv) {
 	uint32_t ab = 0, eb = 0;
 	for(uint32_t i = 0; i < n; i++) {
 		memset(&rres[i], 0, sizeof(rres[i]));
-		gather_read(states[i], pools, scratch.data() + (size_t)i * BT2_SCRATCH_EDITS, ab, eb, rres[i], oal.data(), oed.data());
+		gather_read(states[i], pools, scratch.data() + (size_t)i * BT2_SCRATCH_EDITS, ab, eb, 0, 0, rres[i], oal.data(), oed.data());
 		ab += states[i].n_alns; eb += read_edit_count(states[i], pools);
 	}
 	bt2gpu_results res; res.n = n; res.reads = rres.data(); res.alns = oal.data(); res.n_alns = ab; res.edits = oed.data(); res.n_edits = eb;
