@@ -315,7 +315,7 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 				  k_step<<<nblk(k, 128), 128, 0, st>>>(c->dP, c->ix, c->rf, pools, states, L[3 + cur], b, k, probs, L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_step++; }
 				{ Phase ph(c, PH_FILL);
 				  FillArgs fa; fa.probs = probs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.cells = c->cells.as<uint8_t>(); fa.pcache = c->pcache.as<uint32_t>(); fa.hef_dbg = nullptr; fa.stats = stats + 8;
-				  k_fill<false><<<nblk(k, BT2_FILL_WARPS), BT2_FILL_WARPS * 32, 0, st>>>(c->dP, fa); LAUNCH(c); c->ctr.n_fill++; }
+				  k_fill<false><<<nblk(k, BT2_FILL_WARPS * 2), BT2_FILL_WARPS * 32, 0, st>>>(c->dP, fa); LAUNCH(c); c->ctr.n_fill++; }
 				{ Phase ph(c, PH_BT);
 				  if(++c->btgen > BT2_VIS_GEN_MAX) { CK(cudaMemsetAsync(c->vis.p, 0, (size_t)c->nslots * BT2_VIS_WORDS * 4, st)); c->btgen = 1; }
 				  bcx.gtag = c->btgen << 16;
@@ -571,7 +571,7 @@ int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, c
 			if(rows[i] < 1 || rows[i] > BT2GPU_MAX_ROWS || cols[i] < 1 || cols[i] >= BT2GPU_MAX_COLS) throw std::string("bt2gpu_test_fill: bad problem size");
 			memset(&hs[i], 0, sizeof(ReadState)); hs[i].seq_off = seq_off[i]; hs[i].rdlen = rows[i];
 			memset(&hp[i], 0, sizeof(Problem));
-			hp[i].read = i; hp[i].rows = rows[i]; hp[i].cols = cols[i]; hp[i].fw = 1; hp[i].R = (uint8_t)((rows[i] + 63) / 64); hp[i].minsc = minsc[i];
+			hp[i].read = i; hp[i].rows = rows[i]; hp[i].cols = cols[i]; hp[i].fw = 1; hp[i].R = (uint8_t)fill_R(rows[i]); hp[i].minsc = minsc[i];
 			memcpy(hp[i].rf, rf + rf_off[i], (size_t)cols[i] + 1);
 			nb = std::max<uint64_t>(nb, (uint64_t)seq_off[i] + rows[i]);
 		}
@@ -584,7 +584,7 @@ int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, c
 		FillArgs fa; fa.probs = ctx->probs.as<Problem>(); fa.nprob = nprob; fa.states = ctx->states.as<ReadState>(); fa.seq = ctx->in[0].seq.as<uint8_t>();
 		DBuf dbg; dbg.ensure((size_t)nprob * BT2_HEF_WORDS * 4);
 		fa.qual = ctx->in[0].qual.as<uint8_t>(); fa.cells = ctx->cells.as<uint8_t>(); fa.pcache = nullptr; fa.hef_dbg = dbg.as<uint32_t>(); fa.stats = ctx->stats.as<unsigned long long>() + 8;
-		k_fill<true><<<nblk(nprob, BT2_FILL_WARPS), BT2_FILL_WARPS * 32, 0, st>>>(ctx->dP, fa);
+		k_fill<true><<<nblk(nprob, BT2_FILL_WARPS * 2), BT2_FILL_WARPS * 32, 0, st>>>(ctx->dP, fa);
 		CK(cudaMemcpyAsync(hp.data(), ctx->probs.p, (size_t)nprob * sizeof(Problem), cudaMemcpyDeviceToHost, st));
 		std::vector<uint32_t> w(BT2_HEF_WORDS); std::vector<uint8_t> wc(BT2_CELL_BYTES);
 		for(uint32_t i = 0; i < nprob; i++) {
@@ -592,10 +592,11 @@ int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, c
 			CK(cudaMemcpyAsync(wc.data(), ctx->cells.as<uint8_t>() + (size_t)i * BT2_CELL_BYTES, (size_t)BT2_CELL_BYTES, cudaMemcpyDeviceToHost, st));
 			CK(cudaStreamSynchronize(st));
 			for(uint32_t r = 0; r < rows[i]; r++) for(uint32_t cc = 0; cc < cols[i]; cc++) {
-				const uint32_t x = w[hef_index(r, cc, hp[i].R)];
+				const uint32_t rp = r + fill_shift(rows[i], hp[i].R);
+				const uint32_t x = w[hef_index(rp, cc, hp[i].R)];
 				const uint64_t o = hef_off[i] + (uint64_t)r * cols[i] + cc;
 				H[o] = (uint8_t)x; E[o] = (uint8_t)(x >> 8); F[o] = (uint8_t)(x >> 16);
-				flags[o] = wc[cell_index(r, cc, hp[i].R)];
+				flags[o] = wc[cell_index(rp, cc, hp[i].R)];
 			}
 			ncand[i] = hp[i].ncand; lrmax[i] = hp[i].lrmax;
 			for(uint32_t k = 0; k < hp[i].ncand && k < 256; k++) cand[256 * (size_t)i + k] = hp[i].cand[k];

@@ -122,7 +122,7 @@ struct BtMachine {
 	// the word of the visited map the walk is in (written back when the walk leaves it)
 	uint32_t vwi, vwv;
 	// ---- cached per problem
-	int rows, R, dlo, dhi;            // core diagonals: dlo <= col-row <= dhi
+	int rows, R, shift, dlo, dhi;     // fill layout (dev_common.cuh); core diagonals: dlo <= col-row <= dhi
 	uint32_t ncand;
 	Rng rnd; uint32_t hw, attempts, nsteps;
 	// ---- nextAlignment state
@@ -130,7 +130,7 @@ struct BtMachine {
 	uint32_t cural, reseed, candNext, candAhead;
 	// ---- backtrace state (one attempt)
 	int row, col, origCol, ct, score;
-	uint32_t cidx;                    // cell_index(row,col)
+	uint32_t cidx, sv, sk;            // cell_index(row + shift, col) and the strip / row within the strip it lies in
 	uint32_t ned, nbranch, lastfl;
 	bool coreHit;
 
@@ -141,7 +141,11 @@ struct BtMachine {
 		const ReadState& r = rs(cx);
 		ReadView v; v.seq = cx.seq + r.seq_off; v.qual = cx.qual + r.seq_off; v.rdlen = r.rdlen; v.fw = pb(cx).fw != 0; return v;
 	}
-	BT2_HD void locate() { cidx = cell_index((uint32_t)row, (uint32_t)col, (uint32_t)R); }
+	BT2_HD void locate() {
+		const uint32_t rp = (uint32_t)(row + shift);
+		sv = strip_of(rp, (uint32_t)R); sk = rp - sv * (uint32_t)R;
+		cidx = cell_index_vk(sv, sk, (uint32_t)col, (uint32_t)R);
+	}
 	BT2_HD void push_edit(const BtCtx& cx, uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scratch(cx)[ned] = x; ned++; }
 	BT2_HD uint32_t read_char(int r) const { return code_char(pc_read_code(pc, pcs, (uint32_t)r)); }
 	BT2_HD uint32_t ref_char(int c) const { return code_char(pc_ref_code(pc, pcs, (uint32_t)c)); }
@@ -162,15 +166,15 @@ struct BtMachine {
 	}
 	// chunk the walk most likely enters after the one holding (row, col): the next strip up the diagonal
 	BT2_HD uint32_t predict_chunk() const {
-		const uint32_t k = cidx & 3u;
-		const int r2 = row - (int)k - 1, c2 = col - (int)k - 1;
-		return (r2 >= 0 && c2 >= 0) ? (cell_index((uint32_t)r2, (uint32_t)c2, (uint32_t)R) >> 4) : BT2_NIL;
+		const int c2 = col - (int)sk - 1;
+		if(sv == 0u || c2 < 0) return BT2_NIL;
+		return cell_index_vk(sv - 1u, (uint32_t)R - 1u, (uint32_t)c2, (uint32_t)R) >> 4;   // row R-1 of the strip above, same diagonal
 	}
 
 	// SwDriver::extendSeeds right after swa.align(): counters, then either the candidate loop or done
 	BT2_HD void begin(const BtCtx& cx) {
 		const DevParams& Pr = cx.P; const Problem& p = pb(cx); ReadState& r = rs(cx);
-		rows = p.rows; R = p.R; ncand = p.ncand;
+		rows = p.rows; R = p.R; shift = (int)fill_shift((uint32_t)p.rows, (uint32_t)p.R); ncand = p.ncand;
 		dlo = (p.corel > 0 ? p.corel : 0) - p.triml; dhi = p.corer - p.triml;
 		nsteps = 0; attempts = 0; vwi = BT2_NIL; vwv = 0; ctag0 = BT2_NIL; ctag1 = BT2_NIL; ccur = 0;
 		rnd = r.rnd; hw = r.scr_hw;

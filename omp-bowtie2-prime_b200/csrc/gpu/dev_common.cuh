@@ -321,32 +321,41 @@ struct Problem {
 // E/F flags of rows inside the gap barrier are unspecified: no backtrace can be in E or F state
 // there (E/F are 0 in those rows and every cell on a backtrace path has a raw score >= 1).
 enum { CF_D = 1, CF_HE = 2, CF_HF = 4, CF_EO = 8, CF_EX = 16, CF_FO = 32, CF_FX = 64, CF_MM = 128 };
-// Layout: rows are cut into 64 strips of R rows (the fill's lanes); one 32-bit word holds the R
-// cells of a strip that lie on one diagonal d = col - row (byte k = row % R), words of four
-// consecutive diagonals form a 16-byte chunk, and the chunks of the 64 strips of a diagonal group
-// are adjacent:  byte index = ((e >> 2) * 64 + v) * 16 + (e & 3) * 4 + k,  v = row / R,
-// e = d + BT2_CELL_DOFF + (s_v & 3),  s_v = v * (R + 1) + R - 1.
-// A fill lane completes the word (v, d) at step d + s_v, so the per-strip shift (s_v & 3) makes
-// every lane finish a chunk on the same step: one 16-byte store per lane every four steps.  A
-// backtrace that follows a diagonal reads 16 bytes per strip, 64 strips contiguous: the whole
-// path lies in a few 128-byte lines instead of one sector per strip.
-#define BT2_CELL_DOFF   BT2GPU_MAX_ROWS                                   // multiple of 4; d >= -(MAX_ROWS-1)
-#define BT2_CELL_GROUPS ((BT2GPU_MAX_ROWS + BT2GPU_MAX_COLS + 4 + 3) / 4)
-BT2_HD uint32_t strip_of(uint32_t r, uint32_t R) { return (R == 1) ? r : (R == 2 ? (r >> 1) : ((r * 171u) >> 9)); } // r / R for R <= 3, r < 512
-BT2_HD uint32_t cell_index(uint32_t r, uint32_t c, uint32_t R) {
-	const uint32_t v = strip_of(r, R);
-	const uint32_t k = r - v * R;
-	const uint32_t e = c + BT2_CELL_DOFF - r + ((v * (R + 1) + R - 1) & 3u);
-	return ((e >> 2) * 64u + v) * 16u + (e & 3u) * 4u + k;
+// Layout: rows are cut into BT2_STRIPS = 32 strips of R = ceil(rdlen / 32) <= 5 rows (the fill's lanes), aligned to the END of
+// the read: `shift` = nv * R - rdlen virtual rows precede row 0 (nv = ceil(rdlen / R) strips in use), so that the last row is row
+// R-1 of strip nv-1; all indices below take the shifted row rp = row + shift.  The R cells of a strip that lie on one diagonal
+// form a unit of U = 4 (R <= 4) or 8 (R = 5) bytes (byte k = rp % R).  Strip v works on column c at step c + v of the fill's
+// sweep and completes the unit that holds cell (v * R + k, c) at step t = c + v + R - 1 - k; units are stored by completion
+// step, 16 / U consecutive steps to a 16-byte chunk, the chunks of the 32 strips adjacent:
+//   byte index = ((t / per) * 32 + v) * 16 + (t % per) * U + k,  per = 16 / U.
+// The fill therefore writes whole 512-byte rows (one 16-byte store per lane and problem every `per` steps, all lanes in the same
+// row); a backtrace that follows a diagonal stays in one unit for R cells and moves per / (R + 1) rows up per strip crossed.
+// A fill warp works on two problems at once and uses the larger R of the two for both; Problem::R is what it used.
+#define BT2_STRIPS 32
+#define BT2_MAX_R  ((BT2GPU_MAX_ROWS + BT2_STRIPS - 1) / BT2_STRIPS)
+#define BT2_CELL_GROUPS ((BT2GPU_MAX_COLS + BT2_STRIPS + BT2_MAX_R + 3) / 2 + 1)  // t / per < this (per >= 2)
+BT2_HD uint32_t fill_R(uint32_t rows) { return rows ? (rows + BT2_STRIPS - 1) / BT2_STRIPS : 1u; }
+BT2_HD uint32_t fill_shift(uint32_t rows, uint32_t R) { return ((rows + R - 1) / R) * R - rows; }
+BT2_HD uint32_t strip_of(uint32_t rp, uint32_t R) { // rp / R for R <= 5, rp < 256
+	return (R == 1) ? rp : (R == 2 ? (rp >> 1) : (R == 3 ? ((rp * 171u) >> 9) : (R == 4 ? (rp >> 2) : ((rp * 205u) >> 10))));
 }
-#define BT2_CELL_BYTES (BT2_CELL_GROUPS * 64 * 16)           // per problem slot
-// debug-only H|E<<8|F<<16 words, [strip][step][k] with step = col + strip (bt2gpu_test_fill)
-#define BT2_HEF_T (BT2GPU_MAX_COLS + 64)
-BT2_HD uint32_t hef_index(uint32_t r, uint32_t c, uint32_t R) {
-	const uint32_t v = strip_of(r, R);
-	return (v * BT2_HEF_T + c + v) * 4u + (r - v * R);
+BT2_HD uint32_t cell_index_vk(uint32_t v, uint32_t k, uint32_t c, uint32_t R) {
+	const uint32_t t = c + v + R - 1u - k;
+	if(R > 4) return ((t >> 1) * BT2_STRIPS + v) * 16u + (t & 1u) * 8u + k;
+	return ((t >> 2) * BT2_STRIPS + v) * 16u + (t & 3u) * 4u + k;
 }
-#define BT2_HEF_WORDS (BT2_HEF_T * 64 * 4)
+BT2_HD uint32_t cell_index(uint32_t rp, uint32_t c, uint32_t R) {
+	const uint32_t v = strip_of(rp, R);
+	return cell_index_vk(v, rp - v * R, c, R);
+}
+#define BT2_CELL_BYTES (BT2_CELL_GROUPS * BT2_STRIPS * 16)  // per problem slot
+// debug-only H|E<<8|F<<16 words, [strip][step][k] (8 words per step) with step = col + strip (bt2gpu_test_fill)
+#define BT2_HEF_T (BT2GPU_MAX_COLS + BT2_STRIPS + 16)
+BT2_HD uint32_t hef_index(uint32_t rp, uint32_t c, uint32_t R) {
+	const uint32_t v = strip_of(rp, R);
+	return (v * BT2_HEF_T + c + v) * 8u + (rp - v * R);
+}
+#define BT2_HEF_WORDS (BT2_HEF_T * BT2_STRIPS * 8)
 
 // Visited map of the backtrace (SSEMatrix "reportedThrough", see dev_bt.cuh): one bit per cell.
 // A word covers a tile of 4 diagonals x 4 rows (16 bits) and carries a 16-bit generation tag in

@@ -111,7 +111,7 @@ BT2_HD int advance(const DevParams& P, const DevIndex& ix, const DevRef& rf, con
 		for(int64_t k = leftNs + (inner > 0 ? inner : 0); k < rflenFull; k++) prob.rf[k] = 16;
 		prob.rows = (uint16_t)rdlen; prob.cols = (uint16_t)(rflenFull - 1);
 		prob.fw = fw ? 1 : 0;
-		prob.R = (uint8_t)((rdlen + 63) / 64);
+		prob.R = (uint8_t)fill_R(rdlen);   // the fill may raise it to its pair's (k_fill.cuh)
 		prob.minsc = rs.minsc < -254 ? -254 : rs.minsc;
 		prob.tidx = (uint32_t)tidx; prob.refl = refl;
 		prob.triml = (int32_t)triml; prob.corel = (int32_t)maxgap; prob.corer = (int32_t)(3 * maxgap);

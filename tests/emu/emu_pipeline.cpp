@@ -20,7 +20,7 @@
 using namespace bt2;
 
 static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_t* cells, uint32_t* pcache) {
-	const int rows = pb.rows, cols = pb.cols; const uint32_t R = pb.R;
+	const int rows = pb.rows, cols = pb.cols; const uint32_t R = pb.R, shift = fill_shift((uint32_t)rows, R);
 	auto subs = [](int a, int b) { int v = a - b; return v < 0 ? 0 : v; };
 	std::vector<int> Hprev(rows, 0), Eprev(rows, 0), Fprev(rows, 0), Hcur(rows), Ecur(rows), Fcur(rows), Eleft(rows, 0), Ehere(rows, 0);
 	int lrmax = 0; std::vector<uint16_t> cand;
@@ -52,7 +52,7 @@ static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_
 			if(!(f == hup - P.rfGapOpen)) ne |= CF_FO;
 			if(!(f == fup - P.rfGapExt)) ne |= CF_FX;
 			if(s0 != 0) ne |= CF_MM;
-			cells[cell_index(r, j, R)] = (uint8_t)ne;
+			cells[cell_index(r + shift, j, R)] = (uint8_t)ne;
 		}
 		const int lr = Hcur[rows - 1];
 		if(lr > lrmax) lrmax = lr;
