@@ -57,7 +57,13 @@ BT2_HD int sc_score(const DevParams& P, int rdc, int refm, int q) {
 	return -(int)P.mmpens[q];
 }
 // character of a 0..4 code ("ACGTN"), no memory access
-BT2_HD uint32_t code_char(uint32_t c) { return (0x4e54474341ull >> (8u * (c > 4u ? 4u : c))) & 255u; }
+BT2_HD uint32_t code_char(uint32_t c) {
+#if defined(__CUDA_ARCH__)
+	return __byte_perm(0x54474341u, 0x4eu, c > 4u ? 4u : c) & 255u;   // one PRMT
+#else
+	return (uint32_t)((0x4e54474341ull >> (8u * (c > 4u ? 4u : c))) & 255u);
+#endif
+}
 
 // left-end-based view of an edit list that may be stored 5'-based for a rc read
 struct EditView {
@@ -118,6 +124,7 @@ struct BtMachine {
 	// two 16-byte chunks of the cell array: the one the walk is in and the one it is predicted to enter next
 	// (asynchronous copy issued when a chunk is entered, so that its latency overlaps the steps in between)
 	uint8_t* cbuf; uint32_t cstride;  // chunk b of this lane at cbuf + b * cstride
+	uint32_t cbuf_sa;                 // cbuf as a shared-window address (device)
 	uint32_t ctag0, ctag1, ccur;
 	// the word of the visited map the walk is in (written back when the walk leaves it)
 	uint32_t vwi, vwv;
@@ -141,11 +148,16 @@ struct BtMachine {
 		const ReadState& r = rs(cx);
 		ReadView v; v.seq = cx.seq + r.seq_off; v.qual = cx.qual + r.seq_off; v.rdlen = r.rdlen; v.fw = pb(cx).fw != 0; return v;
 	}
-	BT2_HD void locate() {
+	BT2_HD void locate() {   // (row, col) set from scratch: a candidate's start cell
 		const uint32_t rp = (uint32_t)(row + shift);
 		sv = strip_of(rp, (uint32_t)R); sk = rp - sv * (uint32_t)R;
 		cidx = cell_index_vk(sv, sk, (uint32_t)col, (uint32_t)R);
 	}
+	BT2_HD void row_up() {   // row-- : the strip / row-in-strip pair follows without a division
+		row--;
+		if(sk == 0u) { sk = (uint32_t)R - 1u; sv--; } else sk--;
+	}
+	BT2_HD void relocate() { cidx = cell_index_vk(sv, sk, (uint32_t)col, (uint32_t)R); }
 	BT2_HD void push_edit(const BtCtx& cx, uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scratch(cx)[ned] = x; ned++; }
 	BT2_HD uint32_t read_char(int r) const { return code_char(pc_read_code(pc, pcs, (uint32_t)r)); }
 	BT2_HD uint32_t ref_char(int c) const { return code_char(pc_ref_code(pc, pcs, (uint32_t)c)); }
@@ -153,7 +165,7 @@ struct BtMachine {
 	BT2_HD void chunk_fetch(const BtCtx& cx, uint32_t b, uint32_t ch) {
 		const uint8_t* src = cx.cells + (size_t)slot * BT2_CELL_BYTES + (size_t)ch * 16u;
 #if defined(__CUDA_ARCH__)
-		const uint32_t sa = (uint32_t)__cvta_generic_to_shared(cbuf + b * cstride);
+		const uint32_t sa = cbuf_sa + b * cstride;
 		asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"(sa), "l"(src) : "memory");
 #else
 		for(int i = 0; i < 16; i++) cbuf[b * cstride + i] = src[i];
@@ -287,10 +299,10 @@ struct BtMachine {
 		if(sel == 4u) {
 			ct = CT_H;
 			take_cell(cx, fl);
-			row--; col--;
+			row_up(); col--;
 		} else if(sel >= 2u) {
 			push_edit(cx, pack_edit((uint32_t)row, '-', read_char(row), BT2GPU_EDIT_REF_GAP));
-			row--;
+			row_up();
 			ct = (sel == 3u) ? CT_H : CT_F;
 			score -= (sel == 3u) ? cx.P.rfGapOpen : cx.P.rfGapExt;
 		} else {
@@ -299,7 +311,7 @@ struct BtMachine {
 			ct = (sel == 1u) ? CT_H : CT_E;
 			score -= (sel == 1u) ? cx.P.rdGapOpen : cx.P.rdGapExt;
 		}
-		locate();
+		relocate();
 	}
 
 	// end of a backtrace that reached row 0 / an empty cell, then the rest of nextAlignment and of

@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(BT2_BT_THREADS, BT2_BT_BLOCKS_PER_SM) k_bt(con
 	__shared__ __align__(16) uint8_t chunks[2 * 16 * BT2_BT_THREADS];
 	BtMachine m;
 	m.pc = pcs + threadIdx.x; m.pcs = BT2_BT_THREADS;
-	m.cbuf = chunks + 16 * threadIdx.x; m.cstride = 16 * BT2_BT_THREADS;
+	m.cbuf = chunks + 16 * threadIdx.x; m.cstride = 16 * BT2_BT_THREADS; m.cbuf_sa = (uint32_t)__cvta_generic_to_shared(m.cbuf);
 	m.phase = BP_DONE; m.result = BT_CONTINUE;
 	bool have = false, drained = false;
 	while(true) {
