@@ -128,7 +128,7 @@ typedef struct bt2gpu_params {
 	int32_t mxDp;
 	int32_t streak;          /* maxDpStreak (-D) + (k-1)*maxStreakIncr                  */
 	int32_t doExtend;        /* seed left-extension (nlex) on                           */
-	int32_t enable8;         /* u8 DP allowed (always true without ENABLE_I16)          */
+	int32_t enable8;         /* u8 DP allowed (--no-sse8 clears it; only honoured when i16) */
 	int32_t tighten;         /* --tighten, default 3                                    */
 	int32_t khits;           /* -k                                                      */
 	int32_t mhits;           /* -M (0 = unset)                                          */
@@ -138,7 +138,9 @@ typedef struct bt2gpu_params {
 	int32_t gapbar;
 	int32_t rdGapConst, rdGapLinear, rfGapConst, rfGapLinear;
 	int32_t matchBonus;      /* 0 in end-to-end mode (the only mode, F5)                */
-	int32_t i16;             /* 1: emulate the -DENABLE_I16 build's RNG protocol / limits */
+	int32_t i16;             /* 1: behave as the reference built with -DENABLE_I16: with enable8 == 0 its 16-bit
+	                          * DP path (aligner_sw.cpp:239-241, 336-348) is taken; reads whose minsc < -254 make
+	                          * bt2gpu_align_batch fail (16-bit score range not implemented)              */
 	int32_t reserved[7];
 	int32_t mmpens[256];     /* Scoring::mmpens                                         */
 	int32_t npens[256];      /* Scoring::npens                                          */

@@ -141,7 +141,7 @@ void setup_params(bt2gpu_ctx* c, const bt2gpu_params* p) {
 	P.nofw = p->nofw; P.norc = p->norc; P.gapbar = p->gapbar;
 	P.rdGapOpen = p->rdGapConst + p->rdGapLinear; P.rdGapExt = p->rdGapLinear;
 	P.rfGapOpen = p->rfGapConst + p->rfGapLinear; P.rfGapExt = p->rfGapLinear;
-	P.matchBonus = p->matchBonus; P.i16 = p->i16;
+	P.matchBonus = p->matchBonus; P.i16 = p->i16; P.i16path = (p->i16 && !p->enable8) ? 1 : 0;
 	for(int i = 0; i < 256; i++) {
 		P.mmpens[i] = (uint8_t)std::min(255, std::max(0, p->mmpens[i]));
 		P.npens[i] = (uint8_t)std::min(255, std::max(0, p->npens[i]));
@@ -343,6 +343,7 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 		k_publish_tail<<<1, 32, 0, st>>>(c->dbox, c->albase.as<uint32_t>(), c->nal.as<uint32_t>(), c->edbase.as<uint32_t>(), c->ned.as<uint32_t>(), n, c->poolerr.as<uint32_t>());
 		CK(cudaStreamSynchronize(st));
 		const volatile uint32_t* last = c->hbox->last; const uint32_t perr = c->hbox->perr;
+		if(perr & 16u) throw std::string("bt2gpu: a read's minimum score is below -254: the -DENABLE_I16 build aligns it with the 16-bit score range, which this library does not implement");
 		if(perr) { char b[128]; snprintf(b, sizeof(b), "bt2gpu: device pool exhausted (mask %u); use smaller batches", perr); throw std::string(b); }
 		c->out_alns = (uint64_t)last[0] + last[1]; c->out_edits = (uint64_t)last[2] + last[3];
 		settle(c->d2hspan[c->cur], c->ctr.ms_d2h);   // the previous results in this set have been copied out
@@ -447,7 +448,6 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		if(p->abi_version != BT2GPU_ABI_VERSION) throw std::string("bt2gpu_create: ABI version mismatch");
 		if(hix->lineRate != 7) throw std::string("bt2gpu_create: only 128-byte sides (.bt2l, lineRate 7) are supported");
 		if(p->matchBonus != 0) throw std::string("bt2gpu_create: end-to-end mode only (matchBonus must be 0)");
-		if(p->i16) throw std::string("bt2gpu_create: the -DENABLE_I16 protocol is not implemented in this build");
 		if(p->seedLen < 1 || p->seedLen > 32) throw std::string("bt2gpu_create: seedLen must be within [1,32]");
 		if(p->mxIter > BT2GPU_MAX_ITER) throw std::string("bt2gpu_create: mxIter too big");
 		int ndev = 0;

@@ -218,7 +218,7 @@ struct BtMachine {
 
 	BT2_HD void attempt_failed(const BtCtx& cx) { // backtrace returned false: scratch keeps what was written (res.reset() only drops the count)
 		if(ned > hw) hw = ned;
-		rnd.init(reseed + 1);
+		rnd.init(cx.P.i16path ? reseed : reseed + 1);
 		next_cand(cx);
 		phase = BP_CAND;
 	}
@@ -266,7 +266,7 @@ struct BtMachine {
 		if(starting) {
 			if(was) { next_cand(cx); return; }
 			reseed = rnd.nextU32() + 1;
-			rnd.init(reseed);
+			if(!cx.P.i16path) rnd.init(reseed);   // u8: reseed before and reseed+1 after the backtrace; i16: reseed after only (aligner_sw.cpp:324-348)
 			origCol = col; ct = CT_H;
 			score = 0; nbranch = 0; ned = 0; coreHit = false;
 			attempts++;
@@ -339,7 +339,7 @@ struct BtMachine {
 		const uint32_t ne = ned;
 		for(uint32_t i = 0; i < ne / 2; i++) { const uint32_t t = scratch[i]; scratch[i] = scratch[ne - 1 - i]; scratch[ne - 1 - i] = t; }
 		if(ned > hw) hw = ned;
-		rnd.init(reseed + 1);
+		rnd.init(cx.P.i16path ? reseed : reseed + 1);
 		next_cand(cx);
 		phase = BP_CAND;
 		AlnRec a;

@@ -34,6 +34,7 @@ struct DevParams {
 	int32_t seedLen, seedMms, nSeedRounds, seedBoostThresh, maxhalf, mxIter, mxUg, mxDp, streak;
 	int32_t doExtend, enable8, tighten, khits, mhits, msample, nofw, norc, gapbar;
 	int32_t rdGapOpen, rdGapExt, rfGapOpen, rfGapExt, matchBonus, i16;
+	int32_t i16path;         // the -DENABLE_I16 build with --no-sse8: SwAligner takes its 16-bit path (same cells for minsc >= -254, other RNG protocol)
 	uint8_t mmpens[256]; // Scoring::mmpens (<= 255 in u8 mode)
 	uint8_t npens[256];
 };

@@ -97,7 +97,8 @@ bool parse_options(Options& o, const std::string& args, std::string& err) {
 		else if(t == "--phred33" || t == "-q" || t == "--reorder" || t == "-t") { }
 		else if(t == "--no-unal") o.noUnal = true;
 		else if(t == "--no-yf-quirk") o.yfQuirk = false;
-		else if(t == "--i16") p.i16 = 1;
+		else if(t == "--i16") p.i16 = 1;            // emulate a reference built with -DENABLE_I16
+		else if(t == "--no-sse8") p.enable8 = 0;    // bt2_search.cpp:1353: only that build honours it (the default one warns and goes on)
 		else if(t == "-p" || t == "--threads") { if(!(a = need(i))) return false; } // batch multiplier in the reference (F8); no meaning here
 		else { err = "unsupported option: " + t; return false; }
 	}

@@ -42,6 +42,7 @@ build_build() {
 
 build_align bowtie2-align-l &
 build_build &
+# the opt-in 16-bit build (SURVEY 8c oracle mode B): pins the i16 protocol (tests/golden/*_i16.sam)
+if [ -z "$NO_I16" ]; then build_align bowtie2-align-l-i16 -DENABLE_I16 & fi
 wait
-if [ -n "$WITH_I16" ]; then build_align bowtie2-align-l-i16 -DENABLE_I16; fi
 ls -la "$OUT" >&2

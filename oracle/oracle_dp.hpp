@@ -132,13 +132,16 @@ struct SwProblem {
 			const int lr = Hcur[rows - 1];
 			if(lr > lrmax) lrmax = lr;
 			if((int64_t)(lr - hi) >= minsc) {
-				// u8 stores the raw byte as the candidate score, i16 the offset score
-				Cand c; c.row = rows - 1; c.col = j; c.score = i16 ? (int64_t)(lr - hi) : (int64_t)lr;
+				// both fills store the RAW last-row word as the candidate's score (aligner_swsse_ee_u8.cpp:~520,
+				// aligner_swsse_ee_i16.cpp:528 `init(nrow-1, i, lr)`), so nextAlignment's `score < minsc` filter never fires
+				Cand c; c.row = rows - 1; c.col = j; c.score = (int64_t)lr;
 				cands.push_back(c);
 			}
 			Hprev.swap(Hcur); Eprev.swap(Ecur);
 		}
-		const int64_t score = (int64_t)lrmax - hi;
+		// the 16-bit fill also subtracts 0xff here, not 0x7fff (aligner_swsse_ee_i16.cpp:640): with it the test below never
+		// fires and `best` is the raw word minus 255; reproduced as is
+		const int64_t score = (int64_t)lrmax - 0xff;
 		if(score < minsc) { best = score; return false; }
 		if(lrmax == lo) { best = LLONG_MIN; return false; }
 		if(!cands.empty()) {

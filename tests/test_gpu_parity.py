@@ -22,7 +22,7 @@ def test_gpu_matches_oracle_and_golden(name):
     want = orc.align(batch)
     gpu = _gpu(job)
     got = gpu.align(batch)
-    diffs = common.compare_results(want, got)
+    diffs = common.compare_results(want, got, i16path="--no-sse8" in opts)
     assert not diffs, "\n".join(diffs[:10])
     sam = common.sorted_records(job.sam(batch, got, mode=1))
     assert sam == common.golden_records(gold)
@@ -94,3 +94,14 @@ def test_gpu_larger_iid_vs_oracle():
     assert not diffs, "\n".join(diffs[:10])
     assert job.sam(batch, got, 1) == job.sam(batch, want, 1)
     gpu.close(); orc.close()
+
+
+def test_gpu_i16_build_needs_8bit_range():
+    """-DENABLE_I16 protocol: a minimum score below -254 would select the reference's 16-bit fill, whose score range the
+    CUDA fill does not have: the call fails loudly instead of returning 8-bit results."""
+    job = pkg.Job(common.index_base("syn"), "--i16 --score-min L,-300,0")
+    batch = job.fastq(common.reads_path("syn100"), 0, 50)
+    gpu = _gpu(job)
+    with pytest.raises(RuntimeError, match="16-bit"):
+        gpu.align(batch)
+    gpu.close()
