@@ -288,11 +288,12 @@ def main():
     value = total_reads / dev_s
     peak, peak_src = peaks()
     # dominant kernel by device time, algorithmic bytes per launch (DESIGN.md "Kernels"):
-    #   k_seed  128 B per distinct BWT side touched by an LF step + 16 B per ftab jump + 4 B SA gather and 1 B of text per compared base
+    #   k_seed  16 B per ftab jump + 16 B per suffix-array probe (4 B gather + 12 B of text) + 128 B per distinct BWT side touched by an LF step
+    #           (multi-row left extension) + 4 B SA gather and 1 B of text per compared base of a single-row extension
     #   k_step  4 B SA gather per resolved row + ~60 B of packed reference and 208 B of window written per DP problem
     #   k_fill  1 B of flags per DP cell (stored as 8-byte units of 5 cells for 129..160 bp reads) + ~0.9 KB of inputs/outputs per problem
     #   k_bt    1 B of flags + 2 B of visited-map traffic per backtrace step
-    phases = {"k_seed": (ctr["ms_seed"], ctr["n_seed"], 128.0 * ctr["lf_sides_touched"] + 16.0 * ctr["seeds_searched"] + 1.25 * ctr["ext_text_steps"]),
+    phases = {"k_seed": (ctr["ms_seed"], ctr["n_seed"], 128.0 * ctr["lf_sides_touched"] + 16.0 * ctr["seeds_searched"] + 16.0 * ctr["sa_probes"] + 1.25 * ctr["ext_text_steps"]),
               "k_step": (ctr["ms_resolve"], ctr["n_step"], 128.0 * ctr["lf_steps_resolve"] + 4.0 * ctr["sa_rows_resolved"] + 268.0 * ctr["dp_problems"]),
               "k_fill": (ctr["ms_fill"], ctr["n_fill"], 1.0 * ctr["dp_cells"] + 900.0 * ctr["dp_problems"]),
               "k_bt": (ctr["ms_bt"], ctr["n_bt"], 3.0 * ctr["bt_steps"])}
@@ -308,7 +309,7 @@ def main():
             "ms_per_step": 1000.0 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic",
             "config": {"workload": "configs[1]: 5 Mbp i.i.d. reference, 1M x 150 bp simulated reads, unpaired, %s" % OPTS,
-                       "reads_per_step_per_gpu": n, "l2": "inputs larger than L2 (300 MB of reads + 92 KB of cell flags per DP problem per step; 126 MB L2)",
+                       "reads_per_step_per_gpu": n, "l2": "inputs larger than L2 (300 MB of reads + 49 KB of cell flags written per DP problem per step; 126 MB L2)",
                        "aligned_fraction": aligned / float(n), "parallelism": "reads sharded, index replicated per GPU"},
             "gcups": ctr["dp_cells"] * world / dev_s / 1e9 if dev_s > 0 else None,
             "gcups_fill_kernel": ctr["dp_cells"] / (ctr["ms_fill"] * 1e-3) / 1e9 if ctr["ms_fill"] > 0 else None,

@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define BT2GPU_ABI_VERSION 2
+#define BT2GPU_ABI_VERSION 3
 
 /* Limits inherited from the reference's fixed DP buffers
  * (aligner_result.h:42-43 ALN_MAX_ROWS/ALN_MAX_COLS, aligner_sw_driver.h:95 ALN_MAX_ITER). */
@@ -251,6 +251,9 @@ typedef struct bt2gpu_counters {
 	uint64_t ext_text_steps;    /* MultiSeedAligner::extend steps of single-row ranges, done as
 	                             * direct text comparisons through the device's full suffix array
 	                             * (each replaces one mapLF1 step of the reference)      */
+	uint64_t sa_probes;         /* searchSeedBi done as binary searches over the device's full suffix array: probes
+	                             * (one 4-byte suffix-array gather + 12 bytes of text each); lf_steps_search then only
+	                             * counts the seeds that took the LF walk                                   */
 } bt2gpu_counters;
 
 typedef struct bt2gpu_ctx bt2gpu_ctx;

@@ -65,7 +65,7 @@ class bt2gpu_counters(C.Structure):
                 ("reads", "seeds_searched", "lf_steps_search", "lf_steps_extend", "lf_sides_touched", "sa_rows_resolved",
                  "lf_steps_resolve", "dp_problems", "dp_cells", "bt_attempts", "bt_steps", "alns_reported")] + \
                [(n, C.c_double) for n in ("ms_seed", "ms_glue", "ms_resolve", "ms_fill", "ms_bt", "ms_h2d", "ms_d2h", "ms_run")] + \
-               [(n, C.c_uint64) for n in ("launches", "n_seed", "n_step", "n_fill", "n_bt", "ext_text_steps")]
+               [(n, C.c_uint64) for n in ("launches", "n_seed", "n_step", "n_fill", "n_bt", "ext_text_steps", "sa_probes")]
 
 
 READ_DT = np.dtype([(n, t) for n, t in

@@ -358,7 +358,7 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 	CK(cudaStreamSynchronize(st));
 	const volatile unsigned long long* hs = c->hbox->stats;
 	CK(cudaGetLastError());
-	c->ctr.reads += n; c->ctr.seeds_searched += hs[0]; c->ctr.lf_steps_search += hs[1]; c->ctr.lf_steps_extend += hs[2]; c->ctr.lf_sides_touched += hs[3]; c->ctr.ext_text_steps += hs[4];
+	c->ctr.reads += n; c->ctr.seeds_searched += hs[0]; c->ctr.lf_steps_search += hs[1]; c->ctr.lf_steps_extend += hs[2]; c->ctr.lf_sides_touched += hs[3]; c->ctr.ext_text_steps += hs[4]; c->ctr.sa_probes += hs[5];
 	c->ctr.dp_problems += hs[8]; c->ctr.dp_cells += hs[9];
 	c->ctr.sa_rows_resolved += hs[16]; c->ctr.lf_steps_resolve += hs[17]; c->ctr.bt_attempts += hs[18]; c->ctr.bt_steps += hs[19]; c->ctr.alns_reported += hs[20];
 	flush_spans(c);

@@ -12,8 +12,16 @@
 // offset 0 is the '$' row).  k_seed_ext1 does that comparison against the 2-bit reference, one
 // thread per hit: no dependent random reads.  Ranges of several rows keep the LF walk.
 //
+// With the full suffix array and the joined text resident (k_index.cuh), the exact search itself needs no LF walk
+// either: the rows whose suffix starts with the seed are one interval of the suffix array, the ftab gives the interval
+// of the seed's FIRST ftabChars bases (the table is symmetric: "k-mer -> rows whose suffix starts with it"), and two
+// binary searches over that interval compare the rest of the seed with the text behind each row's offset (one 4-byte
+// gather from the suffix array + 12 bytes of text per probe instead of a dependent 128-byte side per base).  The
+// interval is the same (top, bot) the reference's backward search ends with.  Seeds shorter than the ftab, indexes
+// without the device suffix array (>= 2^32 rows) and left extension of multi-row ranges keep the LF walk below.
+//
 // Three kernels.  k_seed_init (one thread per seed): validity (no N), the 2-bit key,
-// the ftab jump over the last ftabChars bases; seeds that still need LF steps are
+// the suffix-array search or (fallback) the ftab jump over the last ftabChars bases; seeds that still need LF steps are
 // appended to a task list.  k_seed_walk: a group of 8 lanes owns one task.  One LF
 // step = the group reads the 128-byte side(s) of top and bot with one 16-byte load per
 // lane (a full line per group, four lines per warp instruction), each of the six BWT
@@ -53,7 +61,7 @@ struct SeedKernelArgs {
 	uint32_t*        xcounter;  // task counter of k_seed_ext1
 	const uint8_t*   text;      // 2-bit joined text (DevRef::buf), or null: no text-compare extension
 	uint32_t*        counter;   // task counter of k_seed_walk
-	unsigned long long* stats;  // [0] seeds searched [1] LF steps search [2] LF steps extend [3] sides loaded [4] text-compare extension steps
+	unsigned long long* stats;  // [0] seeds searched [1] LF steps search [2] LF steps extend [3] sides loaded [4] text-compare extension steps [5] suffix-array probes
 };
 
 __device__ __forceinline__ uint4 ldg_u4(const uint8_t* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
@@ -72,11 +80,38 @@ __device__ __forceinline__ uint64_t fchr_at(const DevIndex& ix, int c) { // no d
 	return c == 0 ? ix.fchr[0] : c == 1 ? ix.fchr[1] : c == 2 ? ix.fchr[2] : c == 3 ? ix.fchr[3] : ix.fchr[4];
 }
 
+// up to 32 bases of the 2-bit text starting at base x, first base in the lowest bits (16 bases per 32-bit word)
+__device__ __forceinline__ uint64_t text_bases32(const uint32_t* __restrict__ tw, uint64_t x) {
+	const uint64_t w = x >> 4; const uint32_t sh = (uint32_t)(x & 15u) * 2u;
+	const uint32_t w0 = __ldg(tw + w), w1 = __ldg(tw + w + 1), w2 = __ldg(tw + w + 2);
+	return (uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32);
+}
+// reverses the order of the 32 base pairs of v: the first base becomes the most significant one
+__device__ __forceinline__ uint64_t rev_pairs64(uint64_t v) {
+	v = __brevll(v);
+	return ((v & 0x5555555555555555ull) << 1) | ((v >> 1) & 0x5555555555555555ull);
+}
+// Compares the T bases that follow the first `fl` bases of row r's suffix with the pattern tail `pv` (T bases, first base
+// most significant): -1 suffix < pattern, 0 suffix starts with the pattern, +1 suffix > pattern.  A suffix that ends
+// inside the pattern is smaller ('$' sorts first).
+__device__ __forceinline__ int sa_cmp(const DevIndex& ix, const uint32_t* __restrict__ tw, uint32_t r, uint32_t fl, uint32_t T, uint64_t pv) {
+	const uint64_t x = (uint64_t)__ldg(ix.sa32 + r) + fl;
+	const uint64_t avail = ix.len - x;                 // rows of an ftab interval have at least fl bases
+	const uint32_t m = avail < (uint64_t)T ? (uint32_t)avail : T;
+	if(m == 0) return -1;
+	const uint64_t sv = rev_pairs64(text_bases32(tw, x)) >> (64u - 2u * m);
+	const uint64_t pm = pv >> (2u * (T - m));
+	if(sv < pm) return -1;
+	if(sv > pm) return 1;
+	return m < T ? -1 : 0;
+}
+
 __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevParams* __restrict__ Pp, const SeedKernelArgs a) {
 	const DevParams& P = *Pp;
 	const uint64_t tk = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	const bool in_range = tk < (uint64_t)a.nactive * a.W;
 	bool searched = false, live = false, livex = false;
+	uint32_t probes = 0;
 	SeedTask t; t.hit = 0; t.seq_off = 0; t.rdlen = 0; t.pos = 0; t.seed_lo = 0; t.rc = 0;
 	if(in_range) {
 		const uint32_t ai = (uint32_t)(tk / a.W), h = (uint32_t)(tk - (uint64_t)ai * a.W);
@@ -99,10 +134,26 @@ __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevP
 		bool hit = false; int pos = 0;
 		if(ok) {
 			searched = true;
-			// startSearchSeedBi: ftab jump over the last ftabChars bases
 			const int fl = ix.ftabChars;
 			int step = 0;
-			if(fl > 1 && fl <= L) {
+			if(a.text && fl > 1 && fl <= L && L - fl <= 32) {
+				// suffix-array search: interval of the first fl bases from the ftab, the other L - fl bases by binary search
+				uint64_t k = 0;
+				for(int q = 0; q < fl; q++) k = (k << 2) | (uint64_t)STRAND_CH(seed_lo + q);
+				uint32_t lo = (uint32_t)ftab_hi(ix, k), hi = (uint32_t)ftab_lo(ix, k + 1);
+				const uint32_t T = (uint32_t)(L - fl);
+				if(T > 0 && hi > lo) {
+					const uint32_t* tw = reinterpret_cast<const uint32_t*>(a.text);
+					const uint64_t pv = key & (T >= 32u ? ~0ull : ((1ull << (2u * T)) - 1ull));   // the last T bases of the seed
+					uint32_t l0 = lo, h0 = hi;
+					while(l0 < h0) { const uint32_t mid = l0 + ((h0 - l0) >> 1); probes++; if(sa_cmp(ix, tw, mid, (uint32_t)fl, T, pv) < 0) l0 = mid + 1; else h0 = mid; }
+					uint32_t l1 = l0, h1 = hi;
+					while(l1 < h1) { const uint32_t mid = l1 + ((h1 - l1) >> 1); probes++; if(sa_cmp(ix, tw, mid, (uint32_t)fl, T, pv) <= 0) l1 = mid + 1; else h1 = mid; }
+					lo = l0; hi = l1;
+				}
+				top = lo; bot = hi;
+				step = L;
+			} else if(fl > 1 && fl <= L) { // startSearchSeedBi: ftab jump over the last ftabChars bases
 				uint64_t k = 0;
 				for(int q = 0; q < fl; q++) k = (k << 2) | (uint64_t)STRAND_CH(seed_lo + L - fl + q);
 				top = ftab_hi(ix, k); bot = ftab_lo(ix, k + 1);
@@ -142,6 +193,9 @@ __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevP
 	if(livex) a.xtasks[basex + __popc(balx & ((1u << lane) - 1))] = t;
 	const uint32_t sb = __ballot_sync(0xffffffffu, searched);
 	if(lane == 0 && sb) atomicAdd(&a.stats[0], (unsigned long long)__popc(sb));
+	#pragma unroll
+	for(int o = 16; o > 0; o >>= 1) probes += __shfl_xor_sync(0xffffffffu, probes, o);
+	if(lane == 0 && probes) atomicAdd(&a.stats[5], (unsigned long long)probes);
 }
 
 // # of code c among the first n (<= 0 .. >= 64) bases held in the four 32-bit words of w (16 bases each)

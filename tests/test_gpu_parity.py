@@ -29,7 +29,8 @@ def test_gpu_matches_oracle_and_golden(name):
     c = gpu.counters()
     oc = orc.counters()
     assert c["dp_problems"] == oc["dps"] and c["dp_cells"] == oc["cells"]
-    assert c["lf_steps_search"] == oc["lfSearch"]
+    # seeds are searched through the device's full suffix array (binary search) where it exists; the rest take the reference's LF walk
+    assert c["lf_steps_search"] <= oc["lfSearch"] and (c["sa_probes"] > 0 or c["lf_steps_search"] == oc["lfSearch"])
     # single-row extensions are text comparisons through the full suffix array, one per reference LF step
     assert c["lf_steps_extend"] + c["ext_text_steps"] == oc["lfExtend"]
     assert c["bt_steps"] == oc["btSteps"] and c["sa_rows_resolved"] == oc["saRows"]
