@@ -35,7 +35,7 @@ REF_LEN = 5_000_000
 READ_LEN = 150
 METRIC = "aligned_reads_per_sec_150bp_sensitive_e2e"
 ALU_WARP_INST_PER_CLK_SM = 1.95   # VIMNMX.S16x2 / HSET2 / LOP3 share this pipe (measured, profiles/r1_pipe_bench.txt)
-NCU_TRAFFIC = {"k_fill": None, "k_bt": None}  # filled from profiles/r1_ncu_full_raw.csv (dram__bytes_read.sum + dram__bytes_write.sum per launch)
+NCU_TRAFFIC = {"k_fill": 13.25e9, "k_bt": 11.99e9}  # filled from profiles/r1_ncu_full_raw.csv (dram__bytes_read.sum + dram__bytes_write.sum per launch)
 
 
 def log(*a):

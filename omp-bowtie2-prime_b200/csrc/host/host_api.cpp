@@ -2,9 +2,14 @@
 #include "host_internal.hpp"
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 namespace bt2host {
-void sam_for_read(Job& job, const Batch& b, const bt2gpu_results& res, uint32_t ri, int mode, std::string& o);
+void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_results& res, uint32_t ri, int mode, std::string& o);
 std::string sam_header(const Job& job);
 }
 
@@ -62,12 +67,34 @@ static char* dup_out(const std::string& s, size_t* len) {
 }
 char* bt2host_sam_header(const bt2host_job* job) { return dup_out(bt2host::sam_header(job->j), nullptr); }
 char* bt2host_sam_records(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, size_t* len) {
-	std::string o;
+	// AlnSinkWrap::finishRead -> AlnSinkSam::append per read (aln_sink.cpp:643,1477): reads are independent (their RNG state
+	// comes back with the results), so contiguous blocks of reads are formatted by OpenMP threads and concatenated in order
 	const uint32_t n = res->n;
-	o.reserve((size_t)n * 400);
 	bt2host::Job& j = const_cast<bt2host_job*>(job)->j;
-	for(uint32_t i = 0; i < n; i++) bt2host::sam_for_read(j, b->b, *res, i, mode, o);
-	return dup_out(o, len);
+	int nt = 1;
+#ifdef _OPENMP
+	nt = std::max(1, std::min(omp_get_max_threads(), (int)(n / 2048) + 1));
+#endif
+	std::vector<std::string> parts((size_t)nt);
+	std::vector<uint64_t> mets((size_t)nt * 4, 0);
+	#pragma omp parallel for num_threads(nt) schedule(static, 1)
+	for(int t = 0; t < nt; t++) {
+		const uint32_t lo = (uint32_t)((uint64_t)n * t / nt), hi = (uint32_t)((uint64_t)n * (t + 1) / nt);
+		std::string& o = parts[(size_t)t];
+		o.reserve((size_t)(hi - lo) * 420);
+		for(uint32_t i = lo; i < hi; i++) bt2host::sam_for_read(j, &mets[(size_t)t * 4], b->b, *res, i, mode, o);
+	}
+	size_t tot = 0; for(const std::string& o : parts) tot += o.size();
+	for(int t = 0; t < nt; t++) for(int k = 0; k < 4; k++) j.met[k] += mets[(size_t)t * 4 + k];
+	char* out = (char*)malloc(tot + 1);
+	if(!out) return nullptr;
+	std::vector<size_t> offs((size_t)nt + 1, 0);
+	for(int t = 0; t < nt; t++) offs[(size_t)t + 1] = offs[(size_t)t] + parts[(size_t)t].size();
+	#pragma omp parallel for num_threads(nt) schedule(static, 1)
+	for(int t = 0; t < nt; t++) memcpy(out + offs[(size_t)t], parts[(size_t)t].data(), parts[(size_t)t].size());
+	out[tot] = 0;
+	if(len) *len = tot;
+	return out;
 }
 void bt2host_free(void* p) { free(p); }
 void bt2host_job_metrics(const bt2host_job* job, uint64_t out[4]) { for(int i = 0; i < 4; i++) out[i] = job->j.met[i]; }

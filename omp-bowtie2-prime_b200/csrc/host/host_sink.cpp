@@ -182,7 +182,7 @@ int mapq_v2(bool hasSecbest, int64_t best, int64_t secbestIn, int64_t scMin, int
 } // namespace
 
 // One read -> SAM text appended to `o`.
-void sam_for_read(Job& job, const Batch& b, const bt2gpu_results& res, uint32_t ri, int mode, std::string& o) {
+void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_results& res, uint32_t ri, int mode, std::string& o) {
 	const Options& opt = job.opt;
 	const bt2gpu_read_result& rr = res.reads[ri];
 	const uint8_t* seq = b.seq.data() + b.off[ri];
@@ -198,8 +198,8 @@ void sam_for_read(Job& job, const Batch& b, const bt2gpu_results& res, uint32_t 
 		else if(mhitsSet && n > (uint64_t)opt.p.mhits) { maxed = true; nrep = 1; }
 		else nrep = std::min<uint64_t>(n, (uint64_t)opt.p.khits);
 	}
-	job.met[0]++;
-	if(nrep == 0) job.met[1]++; else if(maxed || n > 1) job.met[3]++; else job.met[2]++;
+	met[0]++;
+	if(nrep == 0) met[1]++; else if(maxed || n > 1) met[3]++; else met[2]++;
 	auto qname = [&]() {
 		for(size_t i = 0; i < name.size() && i < 255; i++) { if(isspace((unsigned char)name[i])) break; o.push_back(name[i]); }
 	};
