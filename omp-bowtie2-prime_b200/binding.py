@@ -188,6 +188,14 @@ class Job:
         self._h.bt2host_free(p)
         return s
 
+    def sam_bytes(self, batch, results, mode=1):
+        """SAM records as bytes (no text decoding)."""
+        n = C.c_size_t(0)
+        p = self._h.bt2host_sam_records(self.ptr, batch.ptr, C.byref(results.raw), mode, C.byref(n))
+        s = C.string_at(p, n.value)
+        self._h.bt2host_free(p)
+        return s
+
     def metrics(self):
         a = (C.c_uint64 * 4)()
         self._h.bt2host_job_metrics(self.ptr, C.byref(a))

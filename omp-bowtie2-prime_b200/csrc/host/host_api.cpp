@@ -81,7 +81,7 @@ char* bt2host_sam_records(const bt2host_job* job, const bt2host_batch* b, const 
 	for(int t = 0; t < nt; t++) {
 		const uint32_t lo = (uint32_t)((uint64_t)n * t / nt), hi = (uint32_t)((uint64_t)n * (t + 1) / nt);
 		std::string& o = parts[(size_t)t];
-		o.reserve((size_t)(hi - lo) * 420);
+		o.reserve((size_t)(hi - lo) * 480);
 		for(uint32_t i = lo; i < hi; i++) bt2host::sam_for_read(j, &mets[(size_t)t * 4], b->b, *res, i, mode, o);
 	}
 	size_t tot = 0; for(const std::string& o : parts) tot += o.size();

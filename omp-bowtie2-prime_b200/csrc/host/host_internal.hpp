@@ -5,6 +5,9 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <memory>
+#include <utility>
+#include <new>
 #include <cmath>
 #include <limits>
 #include "bt2host.h"
@@ -59,9 +62,17 @@ struct Job {
 	uint64_t met[4] = {0, 0, 0, 0};
 };
 
+// vector storage that is not zero-filled by resize(): the readers overwrite every element (and do so on several threads)
+template<typename T> struct NoInitAlloc : std::allocator<T> {
+	template<typename U> struct rebind { typedef NoInitAlloc<U> other; };
+	template<typename U> void construct(U* p) noexcept { ::new((void*)p) U; }
+	template<typename U, typename... A> void construct(U* p, A&&... a) { ::new((void*)p) U(std::forward<A>(a)...); }
+};
+typedef std::vector<uint8_t, NoInitAlloc<uint8_t>> ByteVec;
+
 struct Batch {
 	std::vector<uint32_t> off;
-	std::vector<uint8_t> seq, qual;
+	ByteVec seq, qual;
 	std::vector<uint32_t> seed;
 	std::vector<int32_t> minsc, nceil, interval;
 	std::vector<std::string> names;

@@ -1,6 +1,13 @@
 // Option parsing, FASTQ input and the per-read scalars of phase P0.
 #include "host_internal.hpp"
+#include <algorithm>
+#include <cctype>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 #include <cstdio>
+#include <unistd.h>
+#include <ctime>
 #include <cstdlib>
 #include <sstream>
 #include <algorithm>
@@ -155,6 +162,7 @@ void Batch::finalize() {
 void fill_p0(const Job& job, Batch& b) {
 	const size_t n = b.off.size() - 1;
 	b.minsc.resize(n); b.nceil.resize(n); b.interval.resize(n);
+	#pragma omp parallel for schedule(static) if(n > 65536)
 	for(size_t i = 0; i < n; i++) {
 		const size_t rdlen = b.off[i + 1] - b.off[i];
 		int64_t ms = job.opt.scoreMin.f<int64_t>((double)rdlen);
@@ -198,7 +206,15 @@ static bool getline_trim(FILE* f, std::string& line) {
 	return any;
 }
 
-bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_t skip, uint64_t maxn, std::string& err) {
+// per-character tables of the fast reader: kept[c] = c is '.' or alphabetic (pat.cpp:1151-1163), code[c] = asc2dna with '.' as N
+struct FqTables {
+	uint8_t kept[256], code[256];
+	FqTables() { for(int c = 0; c < 256; c++) { kept[c] = (c == '.' || isalpha(c)) ? 1 : 0; code[c] = asc2dna(c == '.' ? 'N' : c); } }
+};
+static const FqTables kFq;
+
+// the serial parser: handles every layout the fast path below declines (blank lines, CR line ends)
+static bool batch_from_fastq_serial(const Job& job, Batch& b, const std::string& path, uint64_t skip, uint64_t maxn, std::string& err) {
 	FILE* f = fopen(path.c_str(), "rb");
 	if(!f) { err = "cannot open " + path; return false; }
 	b.off.assign(1, 0);
@@ -218,6 +234,119 @@ bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_
 	fclose(f);
 	fill_p0(job, b);
 	b.finalize();
+	return true;
+}
+
+// FastqPatternSource light + heavy parse (pat.cpp:1027-1213) for a whole file at once: the file is read into memory, line
+// starts are found by OpenMP threads over equal slices, and records (four lines each) are converted straight into the batch's
+// SoA arrays in two passes (lengths -> offsets -> bases/qualities/seed/name).  Same results as the serial parser; files
+// with CR line ends, blank lines or a truncated last record take the serial parser.
+bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_t skip, uint64_t maxn, std::string& err) {
+	FILE* f = fopen(path.c_str(), "rb");
+	if(!f) { err = "cannot open " + path; return false; }
+	std::vector<char, NoInitAlloc<char>> buf;
+	{
+		fseek(f, 0, SEEK_END); const long sz = ftell(f); fseek(f, 0, SEEK_SET);
+		if(sz < 0) { fclose(f); return batch_from_fastq_serial(job, b, path, skip, maxn, err); }
+		buf.resize((size_t)sz);
+		// slices of the file are read by several threads (pread: no shared file position)
+		const int fd = fileno(f);
+		int nr = 1;
+#ifdef _OPENMP
+		nr = std::max(1, std::min(omp_get_max_threads(), (int)((size_t)sz >> 24) + 1));
+#endif
+		bool ok = true;
+		#pragma omp parallel for num_threads(nr) schedule(static, 1) reduction(&&: ok)
+		for(int t = 0; t < nr; t++) {
+			size_t lo = (size_t)sz * (size_t)t / (size_t)nr; const size_t hi = (size_t)sz * (size_t)(t + 1) / (size_t)nr;
+			while(lo < hi) { const ssize_t g = pread(fd, buf.data() + lo, hi - lo, (off_t)lo); if(g <= 0) { ok = false; break; } lo += (size_t)g; }
+		}
+		fclose(f);
+		if(!ok) { err = "cannot read " + path; return false; }
+	}
+	static const bool trace = getenv("BT2HOST_TRACE") != nullptr;
+	auto now = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
+	const double tA = now();
+	const size_t N = buf.size();
+	if(N == 0 || memchr(buf.data(), '\r', N)) return batch_from_fastq_serial(job, b, path, skip, maxn, err);
+	// ---- line starts
+	int nt = 1;
+#ifdef _OPENMP
+	nt = std::max(1, std::min(omp_get_max_threads(), (int)(N >> 20) + 1));
+#endif
+	std::vector<std::vector<size_t>> nl((size_t)nt);   // positions of '\n' per slice
+	#pragma omp parallel for num_threads(nt) schedule(static, 1)
+	for(int t = 0; t < nt; t++) {
+		const size_t lo = N * (size_t)t / (size_t)nt, hi = N * (size_t)(t + 1) / (size_t)nt;
+		std::vector<size_t>& v = nl[(size_t)t];
+		v.reserve((hi - lo) / 64 + 16);
+		const char* p = buf.data() + lo; const char* e = buf.data() + hi;
+		while(p < e) { const char* q = (const char*)memchr(p, '\n', (size_t)(e - p)); if(!q) break; v.push_back((size_t)(q - buf.data())); p = q + 1; }
+	}
+	std::vector<size_t> ls;                             // ls[i] = start of line i; ls[nlines] = one past the last line's '\n'
+	{
+		size_t tot = 0; for(auto& v : nl) tot += v.size();
+		ls.reserve(tot + 2); ls.push_back(0);
+		for(auto& v : nl) for(size_t x : v) ls.push_back(x + 1);
+		if(ls.back() != N) ls.push_back(N + 1);          // last line without '\n': pretend one follows
+	}
+	const double tB = now();
+	const size_t nlines = ls.size() - 1;
+	if(nlines % 4 != 0) return batch_from_fastq_serial(job, b, path, skip, maxn, err);
+	const size_t nrec = nlines / 4;
+	const size_t r0 = std::min<size_t>((size_t)skip, nrec), r1 = maxn ? std::min<size_t>(nrec, r0 + (size_t)maxn) : nrec;
+	const size_t n = r1 - r0;
+	auto line_len = [&](size_t i) { return ls[i + 1] - 1 - ls[i]; };
+	// ---- pass 1: every record starts with '@' on a non-empty line; trimmed read lengths
+	std::vector<uint32_t> len(n);
+	bool regular = true;
+	#pragma omp parallel for num_threads(nt) schedule(static) reduction(&&: regular)
+	for(size_t r = 0; r < nrec; r++) {
+		const size_t h = 4 * r;
+		if(line_len(h) == 0 || buf[ls[h]] != '@') regular = false;
+		if(r < r0 || r >= r1) continue;
+		const char* sq = buf.data() + ls[h + 1]; const size_t sl = line_len(h + 1);
+		size_t alpha = 0;
+		for(size_t i = 0; i < sl; i++) alpha += kFq.kept[(unsigned char)sq[i]];
+		const size_t t5 = std::min<size_t>((size_t)job.opt.trim5, alpha), rem = alpha - t5, t3 = std::min<size_t>((size_t)job.opt.trim3, rem);
+		len[r - r0] = (uint32_t)(rem - t3);
+	}
+	const double tC = now();
+	if(!regular) return batch_from_fastq_serial(job, b, path, skip, maxn, err);
+	b.off.assign(n + 1, 0);
+	for(size_t i = 0; i < n; i++) b.off[i + 1] = b.off[i] + len[i];
+	b.seq.resize(b.off[n]); b.qual.resize(b.off[n]); b.seed.resize(n); b.names.resize(n);
+	// ---- pass 2
+	#pragma omp parallel for num_threads(nt) schedule(static)
+	for(size_t i = 0; i < n; i++) {
+		const size_t h = 4 * (r0 + i);
+		const char* sq = buf.data() + ls[h + 1]; const size_t sl = line_len(h + 1);
+		const char* ql = buf.data() + ls[h + 3]; const size_t qn = line_len(h + 3);
+		const size_t t5 = (size_t)job.opt.trim5;
+		uint8_t* oseq = b.seq.data() + b.off[i]; uint8_t* oq = b.qual.data() + b.off[i];
+		const size_t L = len[i];
+		size_t a = 0, w = 0;                              // a: index among the alphabetic characters of the line
+		for(size_t k = 0; k < sl && w < L; k++) {
+			const unsigned char c = (unsigned char)sq[k];
+			if(!kFq.kept[c]) continue;
+			if(a >= t5) {
+				oseq[w] = kFq.code[c];
+				int qc = (a < qn) ? (unsigned char)ql[a] : 'I';
+				if(job.opt.phred64) qc -= 31;
+				oq[w] = (uint8_t)qc;
+				w++;
+			}
+			a++;
+		}
+		std::string name(buf.data() + ls[h] + 1, line_len(h) - 1);
+		if(name.empty()) name = std::to_string(i);
+		b.seed[i] = gen_rand_seed(oseq, oq, L, name, job.opt.seed);
+		b.names[i] = std::move(name);
+	}
+	const double tD = now();
+	fill_p0(job, b);
+	b.finalize();
+	if(trace) fprintf(stderr, "[bt2host] fastq: lines %.1f ms, lengths %.1f ms, convert %.1f ms, P0 %.1f ms (%d threads)\n", tB - tA, tC - tB, tD - tC, now() - tD, nt);
 	return true;
 }
 

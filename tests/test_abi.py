@@ -60,3 +60,33 @@ def test_no_gpu_fails_loudly():
         assert "no CUDA device" in str(e)
     else:
         raise AssertionError("GpuAligner must not work without a GPU")
+
+
+def test_fastq_fast_path_equals_serial_parser(tmp_path):
+    """the OpenMP whole-file FASTQ reader and the serial one (taken for CR line ends) build the same batch"""
+    import numpy as np
+    import common
+    from common import pkg
+    if not common.have_builder():
+        import pytest
+        pytest.skip("no builder")
+    src = common.reads_path("lambda_reads_1k")
+    crlf = tmp_path / "crlf.fq"
+    crlf.write_bytes(open(src, "rb").read().replace(b"\n", b"\r\n"))
+    for opts in ("", "--trim5 3 --trim3 7"):
+        job = pkg.Job(common.index_base("lambda"), opts)
+        a, b = job.fastq(src), job.fastq(str(crlf))
+        ra, rb = a.reads.contents, b.reads.contents
+        assert ra.n == rb.n == 1000
+        for f, dt, cnt in (("seq_off", np.uint32, ra.n + 1), ("rng_seed", np.uint32, ra.n), ("minsc", np.int32, ra.n), ("interval", np.int32, ra.n)):
+            xa = np.ctypeslib.as_array(ctypes.cast(getattr(ra, f), ctypes.POINTER(np.ctypeslib.as_ctypes_type(dt))), shape=(cnt,))
+            xb = np.ctypeslib.as_array(ctypes.cast(getattr(rb, f), ctypes.POINTER(np.ctypeslib.as_ctypes_type(dt))), shape=(cnt,))
+            assert (xa == xb).all(), f
+        nb = a.nbases()
+        for f in ("seq", "qual"):
+            xa = np.ctypeslib.as_array(ctypes.cast(getattr(ra, f), ctypes.POINTER(ctypes.c_uint8)), shape=(nb,))
+            xb = np.ctypeslib.as_array(ctypes.cast(getattr(rb, f), ctypes.POINTER(ctypes.c_uint8)), shape=(nb,))
+            assert (xa == xb).all(), f
+        # part of the file: skip / max_reads
+        c, d = job.fastq(src, 100, 250), job.fastq(str(crlf), 100, 250)
+        assert c.reads.contents.n == d.reads.contents.n == 250 and c.nbases() == d.nbases()
