@@ -35,7 +35,8 @@ REF_LEN = 5_000_000
 READ_LEN = 150
 METRIC = "aligned_reads_per_sec_150bp_sensitive_e2e"
 ALU_WARP_INST_PER_CLK_SM = 1.95   # VIMNMX.S16x2 / HSET2 / LOP3 share this pipe (measured, profiles/r1_pipe_bench.txt)
-NCU_TRAFFIC = {"k_fill": 13.25e9, "k_bt": 11.99e9}  # filled from profiles/r1_ncu_full_raw.csv (dram__bytes_read.sum + dram__bytes_write.sum per launch)
+# profiles/r1_ncu_full_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum of one launch over 262 144 DP problems, per problem
+NCU_TRAFFIC_PER_PROBLEM = {"k_fill": 13.25e9 / 262144, "k_bt": 11.99e9 / 262144}
 
 
 def log(*a):
@@ -292,18 +293,19 @@ def main():
     #           (multi-row left extension) + 4 B SA gather and 1 B of text per compared base of a single-row extension
     #   k_step  4 B SA gather per resolved row + ~60 B of packed reference and 208 B of window written per DP problem
     #   k_fill  1 B of flags per DP cell (stored as 8-byte units of 5 cells for 129..160 bp reads) + ~0.9 KB of inputs/outputs per problem
-    #   k_bt    1 B of flags + 2 B of visited-map traffic per backtrace step
+    #   k_bt    1 B of flags read + 1 B written (visited mark) per backtrace step
     phases = {"k_seed": (ctr["ms_seed"], ctr["n_seed"], 128.0 * ctr["lf_sides_touched"] + 16.0 * ctr["seeds_searched"] + 16.0 * ctr["sa_probes"] + 1.25 * ctr["ext_text_steps"]),
               "k_step": (ctr["ms_resolve"], ctr["n_step"], 128.0 * ctr["lf_steps_resolve"] + 4.0 * ctr["sa_rows_resolved"] + 268.0 * ctr["dp_problems"]),
               "k_fill": (ctr["ms_fill"], ctr["n_fill"], 1.0 * ctr["dp_cells"] + 900.0 * ctr["dp_problems"]),
-              "k_bt": (ctr["ms_bt"], ctr["n_bt"], 3.0 * ctr["bt_steps"])}
+              "k_bt": (ctr["ms_bt"], ctr["n_bt"], 2.0 * ctr["bt_steps"])}
     dom = max(phases, key=lambda k: phases[k][0])
     ms, nl, byts = phases[dom]
     achieved = (byts / max(nl, 1)) / ((ms / max(nl, 1)) * 1e-3) / 1e9 if ms > 0 else 0.0
-    # ncu --set full capture of the same command (profiles/): dram bytes read+written per launch (262 144 problems) of the dominant kernel
-    traffic = NCU_TRAFFIC.get(dom) if n == 1000000 and world == 1 else None
-    # K_fill against the integer ALU pipe: 13 ALU-pipe warp-instructions per 64 cells at the measured issue rate
-    alu_peak = 148 * 1.965e9 * ALU_WARP_INST_PER_CLK_SM * 64.0 / 13.0 / 1e9
+    # ncu --set full capture of the same command (profiles/): dram bytes read+written by the dominant kernel, scaled from the captured
+    # launch to this run's average launch (problems per launch), so that it compares with `achieved` x ms_per_launch
+    traffic = NCU_TRAFFIC_PER_PROBLEM[dom] * ctr["dp_problems"] / max(nl, 1) if dom in NCU_TRAFFIC_PER_PROBLEM else None
+    # K_fill against the integer ALU pipe: 12 ALU-pipe warp-instructions per 64 cells at the measured issue rate
+    alu_peak = 148 * 1.965e9 * ALU_WARP_INST_PER_CLK_SM * 64.0 / 12.0 / 1e9
     fill_gcups = ctr["dp_cells"] / (ctr["ms_fill"] * 1e-3) / 1e9 if ctr["ms_fill"] > 0 else 0.0
     line = {"metric": METRIC, "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1000.0 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
@@ -318,7 +320,7 @@ def main():
                          "traffic": traffic, "peak_source": peak_src, "launches": int(nl), "ms_per_launch": ms / max(nl, 1),
                          "note": "the DP fill and the backtrace are not HBM-bound (integer ALU pipe / divergent issue); see int_alu and DESIGN.md section 4"},
             "int_alu": {"kernel": "k_fill", "achieved_gcups": fill_gcups, "peak_gcups": alu_peak, "frac": fill_gcups / alu_peak,
-                        "how": "peak = 148 SMs x 1.965 GHz x %.2f ALU-pipe warp-inst/clk/SM (tools/pipe_bench.cu, profiles/r1_pipe_bench.txt) x 64 cells / 13 ALU-pipe instructions" % ALU_WARP_INST_PER_CLK_SM},
+                        "how": "peak = 148 SMs x 1.965 GHz x %.2f ALU-pipe warp-inst/clk/SM (tools/pipe_bench.cu, profiles/r1_pipe_bench.txt) x 64 cells / 12 ALU-pipe instructions" % ALU_WARP_INST_PER_CLK_SM},
             "e2e": {"value": total_reads / e2e_s, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(ctr["launches"]), "clocks": clocks}
     if rank == 0:

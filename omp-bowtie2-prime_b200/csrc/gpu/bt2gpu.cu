@@ -64,10 +64,10 @@ struct bt2gpu_ctx {
 	DevParams P; DevParams* dP = nullptr;
 	DevIndex ix; DevRef rf;
 	std::vector<void*> resident;      // index / reference allocations
-	uint32_t nslots = 0, sampSlots = 0, maxBatch = 0, btgen = 0;
+	uint32_t nslots = 0, sampSlots = 0, maxBatch = 0;
 	bool textOk = false;              // the 2-bit reference is the index's joined text (same length)
 	// problem-slot arrays
-	DBuf probs, cells, vis, pcache;
+	DBuf probs, cells, pcache;
 	// per-batch arrays
 	// two sets of input arrays and of packed results: while one sub-batch is being aligned the next one is
 	// uploaded and the previous one's results are copied back (bt2gpu_align_batch, separate copy streams)
@@ -265,8 +265,8 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 	sa.r_conv_off = c->s_rco.as<uint32_t>(); sa.r_conv_n = c->s_rcn.as<uint16_t>(); sa.r_nseen = c->s_rns.as<uint16_t>();
 	sa.mass = c->s_mass.as<double>(); sa.elim = c->s_elim.as<uint8_t>();
 	BtCtx bcx; bcx.P = c->P; bcx.pools = c->pools; bcx.states = states; bcx.probs = c->probs.as<Problem>();
-	bcx.cells = c->cells.as<uint8_t>(); bcx.vis = c->vis.as<uint32_t>(); bcx.pcache = c->pcache.as<uint32_t>();
-	bcx.scratch = c->scratch.as<uint32_t>(); bcx.seq = ba.seq; bcx.qual = ba.qual; bcx.gtag = 0;
+	bcx.cells = c->cells.as<uint8_t>(); bcx.pcache = c->pcache.as<uint32_t>();
+	bcx.scratch = c->scratch.as<uint32_t>(); bcx.seq = ba.seq; bcx.qual = ba.qual; bcx.set_pens();
 	Problem* probs = c->probs.as<Problem>();
 	const Pools pools = c->pools;
 	int seedBlocks = 0, btMaxBlocks = 0; { int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device); seedBlocks = nsm * 8; btMaxBlocks = nsm * BT2_BT_BLOCKS_PER_SM; }
@@ -317,8 +317,6 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 				  FillArgs fa; fa.probs = probs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.cells = c->cells.as<uint8_t>(); fa.pcache = c->pcache.as<uint32_t>(); fa.hef_dbg = nullptr; fa.stats = stats + 8;
 				  k_fill<false><<<nblk(k, BT2_FILL_WARPS * 2), BT2_FILL_WARPS * 32, 0, st>>>(c->dP, fa); LAUNCH(c); c->ctr.n_fill++; }
 				{ Phase ph(c, PH_BT);
-				  if(++c->btgen > BT2_VIS_GEN_MAX) { CK(cudaMemsetAsync(c->vis.p, 0, (size_t)c->nslots * BT2_VIS_WORDS * 4, st)); c->btgen = 1; }
-				  bcx.gtag = c->btgen << 16;
 				  zero_counter(c, C_BTTASK);
 				  const uint32_t btBlocks = std::min<uint32_t>(nblk(k, BT2_BT_THREADS), (uint32_t)btMaxBlocks);
 				  k_bt<<<btBlocks, BT2_BT_THREADS, 0, st>>>(bcx, k, cnt + C_BTTASK, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_bt++; }
@@ -511,7 +509,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		// ---- problem slots
 		const char* es = getenv("BT2GPU_SLOTS"); const char* eb = getenv("BT2GPU_BATCH");
 		size_t freeB = 0, totB = 0; CK(cudaMemGetInfo(&freeB, &totB));
-		const size_t perSlot = sizeof(Problem) + (size_t)BT2_CELL_BYTES + (size_t)BT2_VIS_WORDS * 4 + (size_t)BT2_PC_WORDS * 4;
+		const size_t perSlot = sizeof(Problem) + (size_t)BT2_CELL_BYTES + (size_t)BT2_PC_WORDS * 4;
 		uint32_t slots = es ? (uint32_t)atoi(es) : 262144u;
 		const size_t budget = (freeB / 20) * 9;
 		if((size_t)slots * perSlot > budget) slots = (uint32_t)(budget / perSlot);
@@ -521,8 +519,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		if(c->maxBatch < 1) c->maxBatch = 1;
 		{ const char* ep = getenv("BT2GPU_PIPE"); c->pipeChunk = ep ? (uint32_t)std::max(1, atoi(ep)) : 262144u; }
 		c->probs.ensure((size_t)slots * sizeof(Problem)); c->cells.ensure((size_t)slots * BT2_CELL_BYTES);
-		c->vis.ensure((size_t)slots * BT2_VIS_WORDS * 4);
-		CK(cudaMemset(c->vis.p, 0, (size_t)slots * BT2_VIS_WORDS * 4)); c->pcache.ensure((size_t)slots * BT2_PC_WORDS * 4);
+		c->pcache.ensure((size_t)slots * BT2_PC_WORDS * 4);
 		c->counters.ensure(C_N * 4); c->stats.ensure(32 * 8); c->pooltops.ensure(16); c->poolerr.ensure(4);
 		{ void* hb = nullptr; CK(cudaHostAlloc(&hb, sizeof(HostBox), cudaHostAllocMapped)); memset(hb, 0, sizeof(HostBox));
 		  c->hbox = reinterpret_cast<volatile HostBox*>(hb); void* db = nullptr; CK(cudaHostGetDevicePointer(&db, hb, 0)); c->dbox = reinterpret_cast<HostBox*>(db); }
@@ -616,7 +613,7 @@ void bt2gpu_destroy(bt2gpu_ctx* c) {
 	cudaDeviceSynchronize();
 	for(void* p : c->resident) cudaFree(p);
 	if(c->dP) cudaFree(c->dP);
-	DBuf* all[] = { &c->probs, &c->cells, &c->vis, &c->pcache,
+	DBuf* all[] = { &c->probs, &c->cells, &c->pcache,
 		&c->states, &c->scratch, &c->hits, &c->seedtasks, &c->exttasks, &c->lists[0], &c->lists[1], &c->lists[2], &c->lists[3], &c->lists[4], &c->lists[5], &c->lists[6], &c->counters, &c->stats,
 		&c->p_sav, &c->p_sorted, &c->p_rank, &c->p_sp2, &c->p_exr, &c->p_exrfw, &c->p_nsp, &c->p_nsmall, &c->p_nexr, &c->p_nelt, &c->p_nadd,
 		&c->s_ovr, &c->s_ovp, &c->s_ovv, &c->s_sr, &c->s_sv, &c->s_cv, &c->s_rn, &c->s_rcur, &c->s_rth, &c->s_rfl, &c->s_rco, &c->s_rcn, &c->s_rns, &c->s_mass, &c->s_elim,

@@ -9,10 +9,12 @@
 //
 // Written as a flat state machine so that the lanes of a warp, each working on its own
 // problem and pulling a new one when done, stay in one loop.  BtMachine::hot() does one
-// unit of the frequent work (start a candidate / one backtrace cell) with exactly two
-// independent memory reads (the cell's flag byte and, when the walk leaves it, the next
-// word of the visited map); everything a cell needs besides that (read and reference
-// characters for the edits) comes from a per-lane copy of the problem in shared memory.
+// unit of the frequent work (start a candidate / one backtrace cell) with ONE memory read,
+// the 16-byte chunk of the cell array the walk enters (copied to shared memory, the chunk it
+// is predicted to enter next copied ahead); everything a cell needs besides that (read and
+// reference characters for the edits) comes from a per-lane copy of the problem in shared
+// memory.  The paths of the state machine that differ between lanes (which move, whether it
+// makes an edit) are computed with selects and share one copy of the code that follows.
 //
 // What the reference's per-cell backtrace state boils down to: the reference marks a cell
 // "reported through" on EVERY visit (aligner_swsse_ee_u8.cpp:1023), before it even knows
@@ -23,6 +25,9 @@
 // unwinds one frame per step without trying anything.  So the state is ONE bit per cell
 // (visited), and a failed walk costs `number of branch frames` extra steps.  Nothing of a
 // popped frame is observable: the edit count after unwinding is discarded by res.reset().
+// That bit is bit 7 of the cell's own flag byte (CF_VIS; the fill writes it as 0, so every
+// fill of a slot starts with nothing visited): the visit test comes with the flags, and
+// marking is one byte store to the chunk's copy and one to the cell array.
 #pragma once
 #include "dev_common.cuh"
 
@@ -32,6 +37,14 @@
 #else
 #define BT2_POPC(x) __builtin_popcount(x)
 #define BT2_CLZ(x) ((x) ? __builtin_clz(x) : 32)
+#endif
+
+// host-only work counters of the emulator build (tests/emu, -DBT2_BT_PROFILE): what the lane iterations of k_bt are spent on
+#if defined(BT2_BT_PROFILE) && !defined(__CUDA_ARCH__)
+#define BT2_PROF(i, n) (bt2::g_bt_prof[i] += (n))
+namespace bt2 { static unsigned long long g_bt_prof[32]; }
+#else
+#define BT2_PROF(i, n) ((void)0)
 #endif
 
 namespace bt2 {
@@ -109,12 +122,12 @@ struct BtCtx {
 	DevParams P;
 	Pools pools;
 	ReadState* states; const Problem* probs;
-	const uint8_t* cells;    // [nslots * BT2_CELL_BYTES] CF_* flag bytes (cell_index)
-	uint32_t* vis;           // [nslots * BT2_VIS_WORDS] visited maps (vis_index)
+	uint8_t* cells;          // [nslots * BT2_CELL_BYTES] CF_* flag bytes (cell_index); bit 7 = visited, set here
 	const uint32_t* pcache;  // [nslots * BT2_PC_WORDS]
 	uint32_t* scratch;       // [nreads * BT2_SCRATCH_EDITS] per-read edit scratch
 	const uint8_t* seq; const uint8_t* qual; // batch arrays
-	uint32_t gtag;           // generation << 16
+	int32_t pen[8];          // penalty of a move by its option bit: read-gap extend, open, ref-gap extend, open, diagonal (0)
+	void set_pens() { pen[0] = P.rdGapExt; pen[1] = P.rdGapOpen; pen[2] = P.rfGapExt; pen[3] = P.rfGapOpen; pen[4] = pen[5] = pen[6] = pen[7] = 0; }
 };
 
 struct BtMachine {
@@ -126,10 +139,11 @@ struct BtMachine {
 	uint8_t* cbuf; uint32_t cstride;  // chunk b of this lane at cbuf + b * cstride
 	uint32_t cbuf_sa;                 // cbuf as a shared-window address (device)
 	uint32_t ctag0, ctag1, ccur;
-	// the word of the visited map the walk is in (written back when the walk leaves it)
-	uint32_t vwi, vwv;
 	// ---- cached per problem
-	int rows, R, shift, dlo, dhi;     // fill layout (dev_common.cuh); core diagonals: dlo <= col-row <= dhi
+	uint8_t* cellp; uint32_t* scr;    // the problem's cells, the read's edit scratch
+	int rows, R, dlo;                 // core diagonals: dlo <= col-row < dlo + dspan
+	uint32_t dspan, lg, svLast;       // fill layout (dev_common.cuh): log2(units per chunk), strip of the last row
+	uint32_t glo, gspan;              // rows glo <= row < glo + gspan allow gaps
 	uint32_t ncand;
 	Rng rnd; uint32_t hw, attempts, nsteps;
 	// ---- nextAlignment state
@@ -138,35 +152,42 @@ struct BtMachine {
 	// ---- backtrace state (one attempt)
 	int row, col, origCol, ct, score;
 	uint32_t cidx, sv, sk;            // cell_index(row + shift, col) and the strip / row within the strip it lies in
-	uint32_t ned, nbranch, lastfl;
+	uint32_t ned, nbranch;
 	bool coreHit;
 
 	BT2_HD const Problem& pb(const BtCtx& cx) const { return cx.probs[slot]; }
 	BT2_HD ReadState& rs(const BtCtx& cx) const { return cx.states[read]; }
-	BT2_HD uint32_t* scratch(const BtCtx& cx) const { return cx.scratch + (size_t)read * BT2_SCRATCH_EDITS; }
+	BT2_HD uint32_t* scratch(const BtCtx&) const { return scr; }
 	BT2_HD ReadView view(const BtCtx& cx) const {
 		const ReadState& r = rs(cx);
 		ReadView v; v.seq = cx.seq + r.seq_off; v.qual = cx.qual + r.seq_off; v.rdlen = r.rdlen; v.fw = pb(cx).fw != 0; return v;
 	}
-	BT2_HD void locate() {   // (row, col) set from scratch: a candidate's start cell
-		const uint32_t rp = (uint32_t)(row + shift);
-		sv = strip_of(rp, (uint32_t)R); sk = rp - sv * (uint32_t)R;
-		cidx = cell_index_vk(sv, sk, (uint32_t)col, (uint32_t)R);
+	BT2_HD unsigned nsteps_attempt() const { return (unsigned)(rows - 1 - row) + (unsigned)(origCol - col) + 1u; }
+	// cell_index_vk without the branch on R
+	BT2_HD uint32_t cell_at(uint32_t v, uint32_t k, uint32_t c) const {
+		const uint32_t t = c + v + (uint32_t)R - 1u - k;
+		return ((((t >> lg) << 5) + v) << 4) + ((t & ((1u << lg) - 1u)) << (4u - lg)) + k;
+	}
+	// the next candidate's start cell (last row: row R-1 of strip svLast), or the end of the candidate loop
+	BT2_HD void seek_cand() {
+		if(cural >= ncand) { phase = BP_DONE; return; }
+		row = rows - 1; col = (int)(candNext & 255u);
+		sv = svLast; sk = (uint32_t)R - 1u;
+		cidx = cell_at(sv, sk, (uint32_t)col);
+		phase = BP_CAND;
 	}
 	BT2_HD void row_up() {   // row-- : the strip / row-in-strip pair follows without a division
 		row--;
 		if(sk == 0u) { sk = (uint32_t)R - 1u; sv--; } else sk--;
 	}
-	BT2_HD void relocate() { cidx = cell_index_vk(sv, sk, (uint32_t)col, (uint32_t)R); }
-	BT2_HD void push_edit(const BtCtx& cx, uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scratch(cx)[ned] = x; ned++; }
-	BT2_HD uint32_t read_char(int r) const { return code_char(pc_read_code(pc, pcs, (uint32_t)r)); }
-	BT2_HD uint32_t ref_char(int c) const { return code_char(pc_ref_code(pc, pcs, (uint32_t)c)); }
+	BT2_HD void relocate() { cidx = cell_at(sv, sk, (uint32_t)col); }
+	BT2_HD void push_edit(uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scr[ned] = x; ned++; }
 
-	BT2_HD void chunk_fetch(const BtCtx& cx, uint32_t b, uint32_t ch) {
-		const uint8_t* src = cx.cells + (size_t)slot * BT2_CELL_BYTES + (size_t)ch * 16u;
+	BT2_HD void chunk_fetch(uint32_t b, uint32_t ch) {
+		const uint8_t* src = cellp + ch * 16u;
 #if defined(__CUDA_ARCH__)
 		const uint32_t sa = cbuf_sa + b * cstride;
-		asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"(sa), "l"(src) : "memory");
+		asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(sa), "l"(src) : "memory");   // .cg: marks of earlier walks are read from L2
 #else
 		for(int i = 0; i < 16; i++) cbuf[b * cstride + i] = src[i];
 #endif
@@ -180,16 +201,21 @@ struct BtMachine {
 	BT2_HD uint32_t predict_chunk() const {
 		const int c2 = col - (int)sk - 1;
 		if(sv == 0u || c2 < 0) return BT2_NIL;
-		return cell_index_vk(sv - 1u, (uint32_t)R - 1u, (uint32_t)c2, (uint32_t)R) >> 4;   // row R-1 of the strip above, same diagonal
+		return cell_at(sv - 1u, (uint32_t)R - 1u, (uint32_t)c2) >> 4;   // row R-1 of the strip above, same diagonal
 	}
 
 	// SwDriver::extendSeeds right after swa.align(): counters, then either the candidate loop or done
 	BT2_HD void begin(const BtCtx& cx) {
 		const DevParams& Pr = cx.P; const Problem& p = pb(cx); ReadState& r = rs(cx);
-		rows = p.rows; R = p.R; shift = (int)fill_shift((uint32_t)p.rows, (uint32_t)p.R); ncand = p.ncand;
-		dlo = (p.corel > 0 ? p.corel : 0) - p.triml; dhi = p.corer - p.triml;
-		nsteps = 0; attempts = 0; vwi = BT2_NIL; vwv = 0; ctag0 = BT2_NIL; ctag1 = BT2_NIL; ccur = 0;
+		rows = p.rows; R = p.R; ncand = p.ncand;
+		lg = R > 4 ? 1u : 2u; svLast = ((uint32_t)p.rows + fill_shift((uint32_t)p.rows, (uint32_t)p.R)) / (uint32_t)p.R - 1u;
+		dlo = (p.corel > 0 ? p.corel : 0) - p.triml; { const int dhi = p.corer - p.triml; dspan = dhi >= dlo ? (uint32_t)(dhi - dlo) + 1u : 0u; }
+		glo = (uint32_t)Pr.gapbar; gspan = p.rows > 2 * Pr.gapbar ? (uint32_t)(p.rows - 2 * Pr.gapbar) : 0u;
+		cellp = cx.cells + (size_t)slot * BT2_CELL_BYTES; scr = cx.scratch + (size_t)read * BT2_SCRATCH_EDITS;
+		chunk_wait();   // a chunk copy of the previous problem may still be on its way into this lane's buffers
+		nsteps = 0; attempts = 0; ctag0 = BT2_NIL; ctag1 = BT2_NIL; ccur = 0;
 		rnd = r.rnd; hw = r.scr_hw;
+		BT2_PROF(16, 1); BT2_PROF(17, ncand);
 		r.dpCells += (uint64_t)p.rows * p.cols;
 		const int32_t bestCell = p.lrmax - 255;
 		const bool found = bestCell >= p.minsc && ncand > 0;
@@ -206,7 +232,7 @@ struct BtMachine {
 		if(r.nDpFail > r.nDpFailStreak) r.nDpFailStreak = r.nDpFail;
 		r.nDpFail = 0;
 		cural = 0; candNext = p.cand[0]; candAhead = ncand > 1 ? p.cand[1] : 0u;
-		phase = BP_CAND;
+		seek_cand();
 	}
 	BT2_HD void finish(const BtCtx& cx) {
 		ReadState& r = rs(cx);
@@ -220,51 +246,36 @@ struct BtMachine {
 		if(ned > hw) hw = ned;
 		rnd.init(cx.P.i16path ? reseed : reseed + 1);
 		next_cand(cx);
-		phase = BP_CAND;
-	}
-
-	// the diagonal move / the last cell of a path: mismatch edit (its penalty and N count are taken in post())
-	BT2_HD void take_cell(const BtCtx& cx, uint32_t fl) {
-		if(fl & CF_MM) return;    // (fl holds the equalities that are TRUE: bit set = match; matchBonus is 0 end-to-end)
-		push_edit(cx, pack_edit((uint32_t)row, ref_char(col), read_char(row), BT2GPU_EDIT_MM));
+		seek_cand();
 	}
 
 	// One unit of the frequent work: SwAligner::nextAlignment picking the next candidate whose start
 	// cell has not been reported through, and one cell of backtraceNucleotidesEnd2EndSseU8.
-	// All memory the cell needs is requested up front and waited for at ONE point, so that the lanes
-	// of a warp (each in its own problem) pay one memory latency per call, not one per kind of miss.
+	// (phase BP_CAND: positioned on a candidate's start cell, attempt not begun; BP_STEP: inside a walk.)
 	BT2_HD void hot(const BtCtx& cx) {
-		bool starting = false;
-		if(phase == BP_CAND) {
-			if(cural >= ncand) { phase = BP_DONE; return; }
-			row = rows - 1; col = (int)(candNext & 255u);
-			locate();
-			starting = true;
-		}
-		// ---- memory stage
-		uint32_t* const vis = cx.vis + (size_t)slot * BT2_VIS_WORDS;
-		const uint32_t wi = vis_index((uint32_t)row, (uint32_t)col);
+		BT2_PROF(0, 1);
+		const bool starting = phase == BP_CAND;
+		// ---- memory stage: the chunk holding the cell
 		const uint32_t ch = cidx >> 4;
 		const uint32_t curtag = ccur ? ctag1 : ctag0, othtag = ccur ? ctag0 : ctag1;
-		const bool needV = wi != vwi, newC = ch != curtag, needC = newC && ch != othtag;
-		uint32_t mv = 0;
-		if(needV) { if(vwi != BT2_NIL) vis[vwi] = vwv; mv = vis[wi]; }
-		if(needC) chunk_fetch(cx, ccur, ch);
+		const bool newC = ch != curtag, needC = newC && ch != othtag;
+		if(needC) chunk_fetch(ccur, ch);
 		chunk_wait();
-		if(needV) { vwv = ((mv & 0xffff0000u) == cx.gtag) ? mv : cx.gtag; vwi = wi; }
 		if(newC) {
 			if(needC) { if(ccur) ctag1 = ch; else ctag0 = ch; } else ccur ^= 1u;
 			const uint32_t nx = predict_chunk();
-			if(nx != BT2_NIL) chunk_fetch(cx, ccur ^ 1u, nx);
+			if(nx != BT2_NIL) chunk_fetch(ccur ^ 1u, nx);
 			if(ccur) ctag0 = nx; else ctag1 = nx;
 		}
-		const uint32_t fl = ~(uint32_t)*(volatile const uint8_t*)(cbuf + ccur * cstride + (cidx & 15u));
-		const uint32_t bit = vis_bit((uint32_t)row, (uint32_t)col);
-		const bool was = (vwv & bit) != 0;
-		vwv |= bit;
+		volatile uint8_t* const cp = cbuf + ccur * cstride + (cidx & 15u);
+		const uint32_t raw = *cp;
+		const bool was = (raw & CF_VIS) != 0;
+		if(!was) { *cp = (uint8_t)(raw | CF_VIS); cellp[cidx] = (uint8_t)(raw | CF_VIS); }
+		const uint32_t fl = ~raw;   // bit set = the comparison holds
 		// ---- candidate start
 		if(starting) {
-			if(was) { next_cand(cx); return; }
+			if(was) { BT2_PROF(2, 1); next_cand(cx); seek_cand(); return; }
+			BT2_PROF(3, 1);
 			reseed = rnd.nextU32() + 1;
 			if(!cx.P.i16path) rnd.init(reseed);   // u8: reseed before and reseed+1 after the backtrace; i16: reseed after only (aligner_sw.cpp:324-348)
 			origCol = col; ct = CT_H;
@@ -273,44 +284,37 @@ struct BtMachine {
 			phase = BP_STEP;
 		}
 		nsteps++;
-		if(was) { nsteps += nbranch; attempt_failed(cx); return; } // every branch frame pops onto a marked cell
+		if(was) { nsteps += nbranch; BT2_PROF(4, 1); attempt_failed(cx); return; } // every branch frame pops onto a marked cell
 		// options of the cell, highest priority first: bit4 diagonal, bit3 ref-gap open, bit2 ref-gap extend,
 		// bit1 read-gap open, bit0 read-gap extend (H); E and F cells have only their own open/extend pair
-		uint32_t opts = 0;
-		if(row > 0) {
-			const bool hasLeft = col > 0;
-			const uint32_t eopts = hasLeft ? (((fl >> 2) & 2u) | ((fl >> 4) & 1u)) : 0u;   // EO -> bit1, EX -> bit0
-			const uint32_t fopts = ((fl >> 2) & 8u) | ((fl >> 4) & 4u);                      // FO -> bit3, FX -> bit2
-			if(ct == CT_E) opts = eopts;
-			else if(ct == CT_F) opts = fopts;
-			else {
-				if(row >= cx.P.gapbar && row < rows - cx.P.gapbar) { // gaps allowed in this row
-					if(fl & CF_HF) opts |= fopts;
-					if(fl & CF_HE) opts |= eopts;
-				}
-				if(hasLeft && (fl & CF_D)) opts |= 16u;
-			}
+		const bool hasLeft = col > 0;
+		const uint32_t eopts = hasLeft ? (((fl >> 2) & 2u) | ((fl >> 4) & 1u)) : 0u;   // EO -> bit1, EX -> bit0
+		const uint32_t fopts = ((fl >> 2) & 8u) | ((fl >> 4) & 4u);                      // FO -> bit3, FX -> bit2
+		uint32_t hopts = (hasLeft && (fl & CF_D)) ? 16u : 0u;
+		if((uint32_t)row - glo < gspan) {   // gaps allowed in this row
+			if(fl & CF_HF) hopts |= fopts;
+			if(fl & CF_HE) hopts |= eopts;
 		}
-		const int dg = col - row;
-		coreHit = coreHit || (dg >= dlo && dg <= dhi); // core-diagonal test (aligner_swsse_ee_u8.cpp:1229-1262) folded in
-		if(opts == 0) { phase = BP_POST; lastfl = fl; return; } // row 0, or a cell nothing leads into: the walk ends here
+		uint32_t opts = ct == CT_E ? eopts : (ct == CT_F ? fopts : hopts);
+		if(row == 0) opts = 0;
+		coreHit = coreHit || (uint32_t)(col - row - dlo) < dspan; // core-diagonal test (aligner_swsse_ee_u8.cpp:1229-1262) folded in
+		if(opts == 0) { phase = BP_POST; BT2_PROF(6, 1); return; } // row 0, or a cell nothing leads into: the walk ends here
 		if(opts & (opts - 1u)) nbranch++;
 		const uint32_t sel = 31u - (uint32_t)BT2_CLZ(opts);
-		if(sel == 4u) {
-			ct = CT_H;
-			take_cell(cx, fl);
-			row_up(); col--;
-		} else if(sel >= 2u) {
-			push_edit(cx, pack_edit((uint32_t)row, '-', read_char(row), BT2GPU_EDIT_REF_GAP));
-			row_up();
-			ct = (sel == 3u) ? CT_H : CT_F;
-			score -= (sel == 3u) ? cx.P.rfGapOpen : cx.P.rfGapExt;
-		} else {
-			push_edit(cx, pack_edit((uint32_t)row + 1, ref_char(col), '-', BT2GPU_EDIT_READ_GAP));
-			col--;
-			ct = (sel == 1u) ? CT_H : CT_E;
-			score -= (sel == 1u) ? cx.P.rdGapOpen : cx.P.rdGapExt;
+		BT2_PROF(8 + sel, 1);
+		// ---- the move and its edit: diagonal = mismatch edit unless the characters match (its penalty and N count are taken
+		// in post()), ref-gap (sel 2,3) and read-gap (sel 0,1) edits always
+		const bool isDiag = sel == 4u, isRead = sel < 2u, isRef = !isDiag && !isRead;
+		const uint32_t rc = pc_read_code(pc, pcs, (uint32_t)row), fc = pc_ref_code(pc, pcs, (uint32_t)col);
+		if(!(isDiag && rc == fc && rc < 4u)) {
+			const uint32_t chr = isRef ? (uint32_t)'-' : code_char(fc), qchr = isRead ? (uint32_t)'-' : code_char(rc);
+			const uint32_t type = isDiag ? (uint32_t)BT2GPU_EDIT_MM : (isRef ? (uint32_t)BT2GPU_EDIT_REF_GAP : (uint32_t)BT2GPU_EDIT_READ_GAP);
+			push_edit(pack_edit((uint32_t)row + (isRead ? 1u : 0u), chr, qchr, type));
 		}
+		score -= cx.pen[sel];
+		ct = sel == 2u ? CT_F : (sel == 0u ? CT_E : CT_H);
+		if(sel >= 2u) row_up();
+		if(!isRef) col--;
 		relocate();
 	}
 
@@ -320,7 +324,10 @@ struct BtMachine {
 		const DevParams& Pr = cx.P; const Problem& p = pb(cx); const Pools* pools = &cx.pools;
 		uint32_t* const scratch = this->scratch(cx);
 		if(!coreHit) { attempt_failed(cx); return; }
-		take_cell(cx, lastfl);
+		{ // the last cell of the path: mismatch edit unless the characters match
+			const uint32_t rc = pc_read_code(pc, pcs, (uint32_t)row), fc = pc_ref_code(pc, pcs, (uint32_t)col);
+			if(!(rc == fc && rc < 4u)) push_edit(pack_edit((uint32_t)row, code_char(fc), code_char(rc), BT2GPU_EDIT_MM));
+		}
 		ReadState& rs = this->rs(cx);
 		// mismatch penalties, N count and gap counts of the path, from its edits
 		int ns = 0, gaps = 0;
@@ -340,8 +347,6 @@ struct BtMachine {
 		for(uint32_t i = 0; i < ne / 2; i++) { const uint32_t t = scratch[i]; scratch[i] = scratch[ne - 1 - i]; scratch[ne - 1 - i] = t; }
 		if(ned > hw) hw = ned;
 		rnd.init(cx.P.i16path ? reseed : reseed + 1);
-		next_cand(cx);
-		phase = BP_CAND;
 		AlnRec a;
 		a.fw = p.fw; a.tidx = p.tidx; a.refoff = (int64_t)col + p.refl;
 		a.score = score; a.ns = ns; a.gaps = gaps; a.edits = (int32_t)ne;
@@ -365,7 +370,7 @@ struct BtMachine {
 			EditView ov; ov.e = pools->edits + o.edit_off; ov.n = o.n_edits; ov.inv = !o.fw; ov.rdlen = rs.rdlen;
 			olap = alns_overlap(nv, a.refoff, ov, o.refoff, rs.rdlen);
 		}
-		if(olap) return;
+		if(olap) { next_cand(cx); seek_cand(); return; }
 		// ---- report
 		const uint32_t slot = atomic_bump(pools->aln_top, 1);
 		const uint32_t eoff = ne ? atomic_bump(pools->edit_top, ne) : 0;
@@ -398,6 +403,7 @@ struct BtMachine {
 				if(bot >= rs.minsc) { rs.minsc = bot; if(rs.minsc < perfect) rs.minsc++; }
 			}
 		}
+		next_cand(cx); seek_cand();
 	}
 
 	// one unit of work; returns false once the problem is finished (result / the read's state are final)

@@ -315,13 +315,13 @@ struct Problem {
 //   CF_D   H(r,c) == H(r-1,c-1) + sc(r,c)         CF_HE  H(r,c) == E(r,c)     CF_HF  H(r,c) == F(r,c)
 //   CF_EO  E(r,c) == H(r,c-1) - rdGapOpen         CF_EX  E(r,c) == E(r,c-1) - rdGapExtend
 //   CF_FO  F(r,c) == H(r-1,c) - rfGapOpen         CF_FX  F(r,c) == F(r-1,c) - rfGapExtend
-//   CF_MM  read char does not match the reference mask (penalty != 0)
+//   CF_VIS (bit 7) is not a comparison: the fill writes 0, the backtrace sets it when it visits the cell (dev_bt.cuh)
 // The H-cell's gap-move comparisons follow from these: in a row where gaps are allowed
 // F = max(F_up - ext, H_up - open, 0), so H == H_up - open iff (H == F and F == H_up - open), and
 // H != F implies H > both; likewise for E.  (Rows inside the gap barrier never look at them.)
 // E/F flags of rows inside the gap barrier are unspecified: no backtrace can be in E or F state
 // there (E/F are 0 in those rows and every cell on a backtrace path has a raw score >= 1).
-enum { CF_D = 1, CF_HE = 2, CF_HF = 4, CF_EO = 8, CF_EX = 16, CF_FO = 32, CF_FX = 64, CF_MM = 128 };
+enum { CF_D = 1, CF_HE = 2, CF_HF = 4, CF_EO = 8, CF_EX = 16, CF_FO = 32, CF_FX = 64, CF_VIS = 128 };
 // Layout: rows are cut into BT2_STRIPS = 32 strips of R = ceil(rdlen / 32) <= 5 rows (the fill's lanes), aligned to the END of
 // the read: `shift` = nv * R - rdlen virtual rows precede row 0 (nv = ceil(rdlen / R) strips in use), so that the last row is row
 // R-1 of strip nv-1; all indices below take the shifted row rp = row + shift.  The R cells of a strip that lie on one diagonal
@@ -357,18 +357,6 @@ BT2_HD uint32_t hef_index(uint32_t rp, uint32_t c, uint32_t R) {
 	return (v * BT2_HEF_T + c + v) * 8u + (rp - v * R);
 }
 #define BT2_HEF_WORDS (BT2_HEF_T * BT2_STRIPS * 8)
-
-// Visited map of the backtrace (SSEMatrix "reportedThrough", see dev_bt.cuh): one bit per cell.
-// A word covers a tile of 4 diagonals x 4 rows (16 bits) and carries a 16-bit generation tag in
-// its high half: a word whose tag is not the launch's generation reads as "nothing visited", so
-// the map is never cleared between problems.  Tiles keep a walk in one word for four steps
-// whether it runs along a diagonal, a row (read-gap run) or a column (reference-gap run); the
-// words of a diagonal group are contiguous (8 words = 32 rows per 32-byte sector).
-#define BT2_VIS_RT    ((BT2GPU_MAX_ROWS + 3) / 4)                         // row tiles per diagonal group
-#define BT2_VIS_WORDS (((BT2GPU_MAX_ROWS + BT2GPU_MAX_COLS + 3) / 4) * BT2_VIS_RT)
-#define BT2_VIS_GEN_MAX 65535u
-BT2_HD uint32_t vis_index(uint32_t r, uint32_t c) { return ((c + BT2GPU_MAX_ROWS - r) >> 2) * BT2_VIS_RT + (r >> 2); }
-BT2_HD uint32_t vis_bit(uint32_t r, uint32_t c) { return 1u << ((((c + BT2GPU_MAX_ROWS - r) & 3u) << 2) | (r & 3u)); }
 
 // Per-problem character cache handed from the fill to the backtrace: 4-bit codes, 8 per word.
 //   words [0, BT2_PC_RD)            read characters in the orientation of the problem's strand (0..3, 4 = N)

@@ -129,7 +129,7 @@ __device__ __forceinline__ void fill_steps(int t0, const int t_end, const FillHa
 				const uint32_t e = Ep[k];
 				const uint32_t h = __vimax3_s16x2_relu(u, e, f);
 				// the comparisons of the backtrace at this cell
-				uint32_t fl = car | (mm & (CF_MM * 0x00010001u));
+				uint32_t fl = car;                            // (bit 7 stays 0: not visited)
 				fl = flag_ne(h, u, W_D, fl);
 				fl = flag_ne(h, e, W_HE, fl);
 				fl = flag_ne(h, f, W_HF, fl);

@@ -51,7 +51,6 @@ static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_
 			Ehere[r] = e;
 			if(!(f == hup - P.rfGapOpen)) ne |= CF_FO;
 			if(!(f == fup - P.rfGapExt)) ne |= CF_FX;
-			if(s0 != 0) ne |= CF_MM;
 			cells[cell_index(r + shift, j, R)] = (uint8_t)ne;
 		}
 		const int lr = Hcur[rows - 1];
@@ -68,7 +67,18 @@ static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_
 	for(size_t i = 0; i < cand.size(); i++) pb.cand[i] = cand[i];
 }
 
+#ifdef BT2_BT_PROFILE
+static void print_bt_prof() {
+	static const char* nm[32] = {"hot calls", "cand loop ends", "cand start visited", "attempts", "attempts ending on a visited cell", "cells of those (row+col distance)", "walks reaching an end cell", "",
+		"read-gap ext", "read-gap open", "ref-gap ext", "ref-gap open", "diagonal", "", "", "", "problems", "candidates"};
+	for(int i = 0; i < 18; i++) if(nm[i][0]) fprintf(stderr, "[bt prof] %-36s %llu\n", nm[i], bt2::g_bt_prof[i]);
+}
+#endif
+
 int main(int argc, char** argv) {
+#ifdef BT2_BT_PROFILE
+	atexit(print_bt_prof);
+#endif
 	if(argc < 5) { fprintf(stderr, "usage\n"); return 2; }
 	char err[512] = {0};
 	bt2host_job* job = bt2host_job_create(argv[1], argv[3], err, sizeof(err));
@@ -111,7 +121,7 @@ int main(int argc, char** argv) {
 	const uint32_t MI = BT2GPU_MAX_ITER + 8;
 	std::vector<uint16_t> ov_rng(2 * MI), ov_pos(2 * MI), ov_val(2 * MI), seen_rng(MI), seen_val(MI), conv_val(MI), r_n(W), r_cur(W), r_thresh(W), r_conv_n(W), r_nseen(W);
 	std::vector<uint8_t> r_flags(W), elim(W); std::vector<uint32_t> r_conv_off(W); std::vector<double> mass(W);
-	std::vector<uint8_t> cells(BT2_CELL_BYTES); std::vector<uint32_t> vis(BT2_VIS_WORDS, 0), pcache(BT2_PC_WORDS, 0); uint32_t gen = 0;
+	std::vector<uint8_t> cells(BT2_CELL_BYTES); std::vector<uint32_t> pcache(BT2_PC_WORDS, 0);
 	orc::WorkCounters wc;
 	for(uint32_t ri = 0; ri < n; ri++) {
 		ReadState& rs = states[ri];
@@ -158,9 +168,8 @@ int main(int argc, char** argv) {
 			while(true) {
 				Problem pb; pb.read = ri;
 				if(advance(P, ix, rf, pools, rs, pb) == ADV_ROUND_END) break;
-				if(++gen > BT2_VIS_GEN_MAX) { std::fill(vis.begin(), vis.end(), 0u); gen = 1; }
-				BtCtx cx; cx.P = P; cx.pools = pools; cx.states = states.data(); cx.probs = &pb; cx.cells = cells.data(); cx.vis = vis.data();
-				cx.pcache = pcache.data(); cx.scratch = scratch.data(); cx.seq = in->seq; cx.qual = in->qual; cx.gtag = gen << 16;
+				BtCtx cx; cx.P = P; cx.pools = pools; cx.states = states.data(); cx.probs = &pb; cx.cells = cells.data();
+				cx.pcache = pcache.data(); cx.scratch = scratch.data(); cx.seq = in->seq; cx.qual = in->qual; cx.set_pens();
 				BtMachine m; m.slot = 0; m.read = ri; m.pc = pcache.data(); m.pcs = 1; uint8_t cbuf[32]; m.cbuf = cbuf; m.cstride = 16;
 				fill_emu(P, pb, m.view(cx), cells.data(), pcache.data());
 				m.begin(cx);

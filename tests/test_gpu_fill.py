@@ -12,7 +12,7 @@ from common import pkg
 
 pytestmark = pytest.mark.gpu
 
-CF_D, CF_HE, CF_HF, CF_EO, CF_EX, CF_FO, CF_FX, CF_MM = 1, 2, 4, 8, 16, 32, 64, 128
+CF_D, CF_HE, CF_HF, CF_EO, CF_EX, CF_FO, CF_FX, CF_VIS = 1, 2, 4, 8, 16, 32, 64, 128   # CF_VIS: written 0 by the fill (the backtrace's visited bit)
 
 
 def expected_flags(P, rd, qual, masks, oH, oE, oF):
@@ -40,13 +40,12 @@ def expected_flags(P, rd, qual, masks, oH, oE, oF):
     ne |= np.where(E != El - rdge, CF_EX, 0).astype(np.uint8)
     ne |= np.where(F != Hu - rfgo, CF_FO, 0).astype(np.uint8)
     ne |= np.where(F != Fu - rfge, CF_FX, 0).astype(np.uint8)
-    ne |= np.where(pen != 0, CF_MM, 0).astype(np.uint8)
     care = np.full((r, c), 255, np.uint8)
     care[:, 0] &= ~np.uint8(CF_EO | CF_EX)
     rows_i = np.arange(r)
     barrier = (rows_i < P.gapbar) | (r - 1 - rows_i < P.gapbar)
     care[barrier, :] &= ~np.uint8(CF_EO | CF_EX | CF_FO | CF_FX | CF_HE | CF_HF)
-    care[0, :] = CF_MM | CF_D
+    care[0, :] = CF_VIS | CF_D
     return ne, care
 
 

@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Print the handful of ncu raw-page metrics the profiles/ summaries quote.
-usage: ncu_summary.py report.ncu-rep [more metrics...]"""
+usage: ncu_summary.py report.ncu-rep|raw_page.csv [more metrics...]"""
 import csv, subprocess, sys, io
 WANT = ['gpu__time_duration.sum', 'launch__grid_size', 'launch__block_size', 'launch__registers_per_thread',
         'smsp__inst_executed.sum', 'smsp__thread_inst_executed_per_inst_executed.ratio',
@@ -18,7 +18,7 @@ WANT = ['gpu__time_duration.sum', 'launch__grid_size', 'launch__block_size', 'la
         'smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio', 'smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio',
         'smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio', 'smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio']
 rep = sys.argv[1]; extra = sys.argv[2:]
-out = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+out = open(rep).read() if rep.endswith('.csv') else subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hdr, units = rows[0], rows[1]
 for r in rows[2:]:
