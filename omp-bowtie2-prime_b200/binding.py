@@ -107,6 +107,8 @@ def load_host():
         h.bt2host_sam_header.argtypes = [C.c_void_p]
         h.bt2host_sam_records.restype = C.c_void_p
         h.bt2host_sam_records.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(bt2gpu_results), C.c_int, C.POINTER(C.c_size_t)]
+        h.bt2host_sam_write.restype = C.c_int
+        h.bt2host_sam_write.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(bt2gpu_results), C.c_int, C.c_int, C.POINTER(C.c_size_t)]
         h.bt2host_free.argtypes = [C.c_void_p]
         h.bt2host_job_metrics.argtypes = [C.c_void_p, C.POINTER(C.c_uint64 * 4)]
         _host = h
@@ -195,6 +197,14 @@ class Job:
         s = C.string_at(p, n.value)
         self._h.bt2host_free(p)
         return s
+
+    def sam_write(self, batch, results, fileobj, mode=1):
+        """SAM records written to an open binary file (bt2host_sam_write); returns the number of bytes."""
+        fileobj.flush()
+        n = C.c_size_t(0)
+        if self._h.bt2host_sam_write(self.ptr, batch.ptr, C.byref(results.raw), mode, fileobj.fileno(), C.byref(n)) != 0:
+            raise OSError("bt2host_sam_write failed")
+        return n.value
 
     def metrics(self):
         a = (C.c_uint64 * 4)()

@@ -1,4 +1,6 @@
 // C-ABI of libbt2host.so (include/bt2host.h).
+#include <unistd.h>
+#include <cerrno>
 #include "host_internal.hpp"
 #include <cstdio>
 #include <cstdlib>
@@ -66,16 +68,16 @@ static char* dup_out(const std::string& s, size_t* len) {
 	return p;
 }
 char* bt2host_sam_header(const bt2host_job* job) { return dup_out(bt2host::sam_header(job->j), nullptr); }
-char* bt2host_sam_records(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, size_t* len) {
-	// AlnSinkWrap::finishRead -> AlnSinkSam::append per read (aln_sink.cpp:643,1477): reads are independent (their RNG state
-	// comes back with the results), so contiguous blocks of reads are formatted by OpenMP threads and concatenated in order
+// AlnSinkWrap::finishRead -> AlnSinkSam::append per read (aln_sink.cpp:643,1477): reads are independent (their RNG state
+// comes back with the results), so contiguous blocks of reads are formatted by OpenMP threads; the blocks are in read order
+static void sam_blocks(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, std::vector<std::string>& parts) {
 	const uint32_t n = res->n;
 	bt2host::Job& j = const_cast<bt2host_job*>(job)->j;
 	int nt = 1;
 #ifdef _OPENMP
 	nt = std::max(1, std::min(omp_get_max_threads(), (int)(n / 2048) + 1));
 #endif
-	std::vector<std::string> parts((size_t)nt);
+	parts.assign((size_t)nt, std::string());
 	std::vector<uint64_t> mets((size_t)nt * 4, 0);
 	#pragma omp parallel for num_threads(nt) schedule(static, 1)
 	for(int t = 0; t < nt; t++) {
@@ -84,8 +86,13 @@ char* bt2host_sam_records(const bt2host_job* job, const bt2host_batch* b, const 
 		o.reserve((size_t)(hi - lo) * 480);
 		for(uint32_t i = lo; i < hi; i++) bt2host::sam_for_read(j, &mets[(size_t)t * 4], b->b, *res, i, mode, o);
 	}
-	size_t tot = 0; for(const std::string& o : parts) tot += o.size();
 	for(int t = 0; t < nt; t++) for(int k = 0; k < 4; k++) j.met[k] += mets[(size_t)t * 4 + k];
+}
+char* bt2host_sam_records(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, size_t* len) {
+	std::vector<std::string> parts;
+	sam_blocks(job, b, res, mode, parts);
+	const int nt = (int)parts.size();
+	size_t tot = 0; for(const std::string& o : parts) tot += o.size();
 	char* out = (char*)malloc(tot + 1);
 	if(!out) return nullptr;
 	std::vector<size_t> offs((size_t)nt + 1, 0);
@@ -95,6 +102,22 @@ char* bt2host_sam_records(const bt2host_job* job, const bt2host_batch* b, const 
 	out[tot] = 0;
 	if(len) *len = tot;
 	return out;
+}
+int bt2host_sam_write(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, int fd, size_t* len) {
+	std::vector<std::string> parts;
+	sam_blocks(job, b, res, mode, parts);
+	size_t tot = 0;
+	for(const std::string& o : parts) {
+		size_t done = 0;
+		while(done < o.size()) {
+			const ssize_t w = write(fd, o.data() + done, o.size() - done);
+			if(w < 0) { if(errno == EINTR) continue; return -1; }
+			done += (size_t)w;
+		}
+		tot += o.size();
+	}
+	if(len) *len = tot;
+	return 0;
 }
 void bt2host_free(void* p) { free(p); }
 void bt2host_job_metrics(const bt2host_job* job, uint64_t out[4]) { for(int i = 0; i < 4; i++) out[i] = job->j.met[i]; }

@@ -33,6 +33,16 @@ struct Rng { // RandomSource (random_source.h:33-150)
 	size_t nextSizeT() { return (size_t)nextU64(); } // sizeof(size_t)==8 branch, random_source.h
 };
 
+// decimal text of an integer appended without a temporary string
+static inline void put_int(std::string& o, long long v) {
+	char t[24]; int n = 0;
+	unsigned long long u = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
+	do { t[n++] = (char)('0' + u % 10); u /= 10; } while(u);
+	if(v < 0) t[n++] = '-';
+	const size_t at = o.size(); o.resize(at + (size_t)n);
+	for(int i = 0; i < n; i++) o[at + (size_t)i] = t[n - 1 - i];
+}
+
 struct Ed { uint32_t pos; uint8_t chr, qchr, type; };
 
 // Edit::invertPoss(edits, sz, 0, n, sort=false) on the first n entries
@@ -48,12 +58,16 @@ struct Stacked { // StackedAln
 		ref.clear(); rel.clear(); read.clear();
 		size_t rdoff = 0;
 		auto rdc = [&](size_t i) -> char { return (i < slen && s[i] <= 4) ? "ACGTN"[s[i]] : 'A'; }; // past-the-end reads are UB in the reference; its buffers are zero-filled in practice
+		auto matched = [&](size_t upto) { // '=' columns for the read offsets [rdoff, upto)
+			if(upto <= rdoff) return;
+			const size_t cnt = upto - rdoff, at = ref.size();
+			ref.resize(at + cnt); read.resize(at + cnt); rel.append(cnt, '=');
+			for(size_t k = 0; k < cnt; k++) { const char c = rdc(rdoff + k); ref[at + k] = c; read[at + k] = c; }
+			rdoff = upto;
+		};
 		for(size_t i = 0; i < n; i++) {
 			const size_t pos = ed[i].pos;
-			while(rdoff < pos && rdoff < slen + 1024) { // (guard only bites on the reference's aliased garbage)
-				char c = rdc(rdoff++);
-				ref.push_back(c); rel.push_back('='); read.push_back(c);
-			}
+			if(rdoff < pos) matched(std::min(pos, slen + 1024)); // (guard only bites on the reference's aliased garbage)
 			if(ed[i].type == BT2GPU_EDIT_MM) {
 				char c = rdc(rdoff++);
 				ref.push_back((char)ed[i].chr); rel.push_back('X'); read.push_back(c);
@@ -64,10 +78,7 @@ struct Stacked { // StackedAln
 				ref.push_back((char)ed[i].chr); rel.push_back('D'); read.push_back('-');
 			}
 		}
-		while(rdoff < slen) {
-			char c = rdc(rdoff++);
-			ref.push_back(c); rel.push_back('='); read.push_back(c);
-		}
+		matched(slen);
 	}
 	void leftAlign() { // pastMms=false
 		const size_t ln = ref.size();
@@ -100,7 +111,7 @@ struct Stacked { // StackedAln
 				if(op2 != op) break;
 			}
 			i += (run - 1);
-			o += std::to_string(run); o.push_back(op);
+			put_int(o, (long long)run); o.push_back(op);
 		}
 	}
 	void mdz(std::string& o) const {
@@ -115,7 +126,7 @@ struct Stacked { // StackedAln
 				}
 				i += (run - 1);
 				if(run - nins > 0) {
-					o += std::to_string(run - nins);
+					put_int(o, (long long)(run - nins));
 					first_print = false; mm_last = false; rdgap_last = false;
 				}
 			} else if(op == 'X') {
@@ -205,11 +216,13 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 	};
 	auto seqqual = [&](bool fw) {
 		if(rdlen == 0) { o += "*\t*"; return; }
-		if(fw) { for(size_t i = 0; i < rdlen; i++) o.push_back("ACGTN"[seq[i]]); }
-		else   { for(size_t i = 0; i < rdlen; i++) { uint8_t c = seq[rdlen - 1 - i]; o.push_back("TGCAN"[c]); } }
-		o.push_back('\t');
-		if(fw) { for(size_t i = 0; i < rdlen; i++) o.push_back((char)qual[i]); }
-		else   { for(size_t i = 0; i < rdlen; i++) o.push_back((char)qual[rdlen - 1 - i]); }
+		const size_t at = o.size(); o.resize(at + 2 * rdlen + 1);
+		char* w = &o[at];
+		if(fw) { for(size_t i = 0; i < rdlen; i++) w[i] = "ACGTN"[seq[i]]; }
+		else   { for(size_t i = 0; i < rdlen; i++) w[i] = "TGCAN"[seq[rdlen - 1 - i]]; }
+		w[rdlen] = '\t'; w += rdlen + 1;
+		if(fw) memcpy(w, qual, rdlen);
+		else   { for(size_t i = 0; i < rdlen; i++) w[i] = (char)qual[rdlen - 1 - i]; }
 	};
 	if(nrep == 0) {
 		if(opt.noUnal) return;
@@ -222,7 +235,8 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 	}
 	// selectByScore
 	const bt2gpu_aln* al = res.alns + rr.aln_off;
-	std::vector<std::pair<int64_t, size_t> > buf(n);
+	static thread_local std::vector<std::pair<int64_t, size_t> > buf;   // per-thread scratch: no allocation per read
+	buf.resize(n);
 	for(size_t i = 0; i < n; i++) { buf[i].first = al[i].score; buf[i].second = i; }
 	std::sort(buf.begin(), buf.end());
 	std::reverse(buf.begin(), buf.end());
@@ -248,9 +262,10 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 	const int64_t scMin = opt.scoreMin.f<int64_t>((double)(float)rdlen);
 	const int64_t scPer = (int64_t)rdlen * opt.p.matchBonus;
 	// the aliased edit scratch
-	std::vector<Ed> ed;
-	Stacked st;
-	std::vector<uint8_t> rcbuf(rdlen);
+	static thread_local std::vector<Ed> ed;
+	static thread_local Stacked st;
+	static thread_local std::vector<uint8_t> rcbuf;
+	rcbuf.resize(rdlen);
 	for(size_t i = 0; i < rdlen; i++) { uint8_t c = seq[rdlen - 1 - i]; rcbuf[i] = c > 3 ? 4 : (uint8_t)(3 - c); }
 	for(uint64_t k = 0; k < nrep; k++) {
 		const bt2gpu_aln& a = al[buf[k].second];
@@ -273,20 +288,20 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 		int fl = 0;
 		if(!primary) fl |= 256;
 		if(!a.fw) fl |= 16;
-		o.push_back('\t'); o += std::to_string(fl); o.push_back('\t');
+		o.push_back('\t'); put_int(o, fl); o.push_back('\t');
 		if(a.tidx < job.refnames.size()) { // SamConfig::printRefNameFromIndex: up to the first whitespace
 			const std::string& nm = job.refnames[a.tidx];
 			for(size_t k = 0; k < nm.size(); k++) { if(isspace((unsigned char)nm[k])) break; o.push_back(nm[k]); }
 		} else o.push_back('*');
-		o.push_back('\t'); o += std::to_string((long long)a.refoff + 1); o.push_back('\t');
-		o += std::to_string(mapq_v2(hasSec, best, secbest, scMin, scPer, primary, mhitsSet, false));
+		o.push_back('\t'); put_int(o, (long long)a.refoff + 1); o.push_back('\t');
+		put_int(o, mapq_v2(hasSec, best, secbest, scMin, scPer, primary, mhitsSet, false));
 		o.push_back('\t');
 		st.cigar(o);
 		o += "\t*\t0\t0\t";
 		seqqual(a.fw != 0);
-		o += "\tAS:i:"; o += std::to_string(a.score);
-		if(hasSec) { o += "\tXS:i:"; o += std::to_string((long long)secbest); }
-		o += "\tXN:i:"; o += std::to_string(a.refns);
+		o += "\tAS:i:"; put_int(o, a.score);
+		if(hasSec) { o += "\tXS:i:"; put_int(o, (long long)secbest); }
+		o += "\tXN:i:"; put_int(o, a.refns);
 		size_t num_mm = 0, num_go = 0, num_gx = 0;
 		for(size_t i = 0; i < ne; i++) {
 			if(ed[i].type == BT2GPU_EDIT_MM) num_mm++;
@@ -298,10 +313,10 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 				while(i < ne - 1 && ed[i + 1].pos == ed[i].pos + 1 && ed[i + 1].type == BT2GPU_EDIT_REF_GAP) { i++; num_gx++; }
 			}
 		}
-		o += "\tXM:i:"; o += std::to_string(num_mm);
-		o += "\tXO:i:"; o += std::to_string(num_go);
-		o += "\tXG:i:"; o += std::to_string(num_gx);
-		o += "\tNM:i:"; o += std::to_string(ne);
+		o += "\tXM:i:"; put_int(o, (long long)num_mm);
+		o += "\tXO:i:"; put_int(o, (long long)num_go);
+		o += "\tXG:i:"; put_int(o, (long long)num_gx);
+		o += "\tNM:i:"; put_int(o, (long long)ne);
 		o += "\tMD:Z:"; st.mdz(o);
 		o += "\tYT:Z:UU";
 		if(opt.yfQuirk) o += "\tYF:Z:LN";

@@ -32,3 +32,22 @@ def test_oracle_thread_count_independent():
     a = job.sam(batch, orc.align(batch, 1), 1)
     b = job.sam(batch, orc.align(batch, 4), 1)
     assert a == b
+
+
+def test_sink_to_file_equals_sink_to_buffer(tmp_path):
+    """bt2host_sam_write (blocks written to a descriptor in read order) == bt2host_sam_records, and the summary counters add up"""
+    if not common.have_builder():
+        pytest.skip("no builder")
+    job = pkg.Job(common.index_base("syn"), "-k 3")
+    batch = job.fastq(common.reads_path("syn100"), 0, 5000)    # > 2048 reads: more than one block
+    orc = common.Oracle(job)
+    res = orc.align(batch, 4)
+    want = job.sam_bytes(batch, res, 1)
+    m0 = job.metrics()
+    with open(tmp_path / "o.sam", "wb") as f:
+        f.write(b"@HD\n")
+        n = job.sam_write(batch, res, f, 1)
+    m1 = job.metrics()
+    assert n == len(want)
+    assert (tmp_path / "o.sam").read_bytes() == b"@HD\n" + want
+    assert m1[0] - m0[0] == batch.n

@@ -21,8 +21,19 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     job = pkg.Job(idx, " ".join(a))
-    n = sum(1 for _ in open(fq, "rb")) // 4
     gpu = pkg.GpuAligner(job, local)
+    if world == 1:   # one GPU: parse, align, and let the sink write its blocks straight to the file
+        batch = job.fastq(fq)
+        res = gpu.align(batch)
+        with open(out, "wb") as f:
+            f.write(job.sam_header().encode("latin-1"))
+            job.sam_write(batch, res, f, 1)
+        met = job.metrics()
+        print("%d reads; %d (%.2f%%) aligned 0 times; %d aligned exactly 1 time; %d aligned >1 times" %
+              (met[0], met[1], 100.0 * met[1] / max(met[0], 1), met[2], met[3]), file=sys.stderr)
+        batch.close(); gpu.close()
+        return
+    n = sum(1 for _ in open(fq, "rb")) // 4
     sam, met = shard.align_sharded(job, fq, gpu.align, n, mode=1, device=torch.device("cuda", local))
     if sam is not None:
         with open(out, "w", encoding="latin-1") as f:

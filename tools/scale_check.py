@@ -1,0 +1,134 @@
+#!/usr/bin/env python
+"""SURVEY 8(d) config C3 at a size one box handles: a large i.i.d. reference (default 100 Mbp: suffix array 400 MB, well
+beyond the 126 MB L2), 150 bp simulated reads, `--sensitive --dpad 12`.
+
+  1. builds the .bt2l index with the reference's own builder (oracle/_ref/bowtie2-build-l),
+  2. aligns a sample of the reads with the UNMODIFIED reference binary (oracle/_ref/bowtie2-align-l, all host threads) -> SAM,
+  3. aligns the same sample through libbt2host.so + libbt2gpu.so -> SAM, and compares the sorted records byte for byte
+     (u8 path; with --i16 also the -DENABLE_I16 binary run with --no-sse8 against the library's i16 protocol),
+  4. times bt2gpu_align_batch on the full read set (host buffers in, pinned results out).
+
+Prints one JSON line.  Needs a GPU and oracle/_ref (built by oracle/build_ref.sh where the reference sources exist).
+usage: scale_check.py [--ref-mbp 100] [--reads 1000000] [--sample 200000] [--i16]"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+REFBIN = os.path.join(ROOT, "oracle", "_ref")
+OPTS = "--sensitive --dpad 12"
+
+
+def sorted_records(sam_bytes):
+    return sorted(l for l in sam_bytes.split(b"\n") if l and not l.startswith(b"@"))
+
+
+def run_ref(binary, base, fq, out, threads, extra):
+    env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="close", OMP_PLACES="cores")
+    t0 = time.time()
+    r = subprocess.run([os.path.join(REFBIN, binary), "-x", base, "-U", fq, "-S", out, "-p", "100"] + OPTS.split() + extra,
+                       env=env, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(binary + " failed: " + r.stderr[-300:])
+    return time.time() - t0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--ref-mbp", type=float, default=100.0)
+    ap.add_argument("--reads", type=int, default=1000000)
+    ap.add_argument("--sample", type=int, default=200000)
+    ap.add_argument("--i16", action="store_true")
+    ap.add_argument("--work", default=os.path.join(ROOT, "bench_work"))
+    args = ap.parse_args()
+    bench = importlib.import_module("bench")
+    pkg = importlib.import_module("omp-bowtie2-prime_b200")
+    os.makedirs(args.work, exist_ok=True)
+    n_ref = int(args.ref_mbp * 1e6)
+    threads = bench.cpu_cores()
+    out = {"ref_bp": n_ref, "reads": args.reads, "sample": args.sample, "opts": OPTS, "host_threads": threads}
+
+    # ---- reference + index (seed 12346: SURVEY C3)
+    base = os.path.join(args.work, "iid%dm" % int(args.ref_mbp))
+    rng = np.random.default_rng(12346)
+    codes = rng.integers(0, 4, size=n_ref, dtype=np.uint8)
+    if not os.path.exists(base + ".4.bt2l"):
+        seq = np.frombuffer(b"ACGT", dtype=np.uint8)[codes]
+        with open(base + ".fa", "wb") as f:
+            f.write(b">seq0\n")
+            lines = seq[: (n_ref // 60) * 60].reshape(-1, 60)
+            nl = np.full((lines.shape[0], 1), 10, np.uint8)
+            f.write(np.concatenate([lines, nl], axis=1).tobytes())
+            if n_ref % 60:
+                f.write(seq[(n_ref // 60) * 60:].tobytes() + b"\n")
+        t0 = time.time()
+        subprocess.run([os.path.join(REFBIN, "bowtie2-build-l"), "--threads", str(threads), base + ".fa", base], check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        out["index_build_s"] = round(time.time() - t0, 1)
+    out["index_bytes"] = sum(os.path.getsize(base + e) for e in (".1.bt2l", ".2.bt2l", ".3.bt2l", ".4.bt2l"))
+
+    # ---- reads
+    bench.REF_LEN = n_ref
+    reads = bench.simulate_reads(codes, args.reads, seed=3)
+    fq_all = os.path.join(args.work, "scale_all.fq"); fq_s = os.path.join(args.work, "scale_sample.fq")
+    bench.write_fastq(fq_all, reads)
+    bench.write_fastq(fq_s, reads[: args.sample])
+
+    # ---- the reference binary on the sample
+    sam_ref = os.path.join(args.work, "scale_ref.sam")
+    dt = run_ref("bowtie2-align-l", base, fq_s, sam_ref, threads, [])
+    out["reference_reads_per_s"] = round(args.sample / dt)
+    want = sorted_records(open(sam_ref, "rb").read())
+
+    # ---- this library on the sample
+    t0 = time.time()
+    job = pkg.Job(base, OPTS)
+    gpu = pkg.GpuAligner(job, 0)
+    out["create_s"] = round(time.time() - t0, 2)      # index load + upload + suffix-array expansion on the device
+    batch = job.fastq(fq_s)
+    res = gpu.align(batch)
+    got = sorted_records(job.sam_bytes(batch, res, 1))
+    diff = sum(1 for a, b in zip(want, got) if a != b) + abs(len(want) - len(got))
+    out["u8_records"] = len(want); out["u8_records_differing"] = diff
+    batch.close()
+
+    # ---- throughput on the full set
+    batch = job.fastq(fq_all)
+    best = 1e9
+    for rep in range(4):
+        gpu.counters(reset=True)
+        t0 = time.time(); res = gpu.align(batch); dt = time.time() - t0
+        if rep:
+            best = min(best, dt)
+    ctr = gpu.counters()
+    out["align_batch_reads_per_s"] = round(args.reads / best)
+    out["phase_ms"] = {k: round(ctr[k], 2) for k in ("ms_seed", "ms_resolve", "ms_fill", "ms_bt", "ms_glue")}
+    out["sa_probes_per_seed"] = round(ctr["sa_probes"] / max(ctr["seeds_searched"], 1), 2)
+    aligned = sum(1 for l in sorted_records(job.sam_bytes(batch, res, 1)) if not (int(l.split(b"\t")[1]) & 4))
+    out["aligned_fraction"] = aligned / args.reads
+    batch.close(); gpu.close()
+
+    # ---- the 16-bit protocol
+    if args.i16 and os.access(os.path.join(REFBIN, "bowtie2-align-l-i16"), os.X_OK):
+        run_ref("bowtie2-align-l-i16", base, fq_s, sam_ref, threads, ["--no-sse8"])
+        want = sorted_records(open(sam_ref, "rb").read())
+        job16 = pkg.Job(base, OPTS + " --i16 --no-sse8")
+        gpu16 = pkg.GpuAligner(job16, 0)
+        batch = job16.fastq(fq_s)
+        got = sorted_records(job16.sam_bytes(batch, gpu16.align(batch), 1))
+        out["i16_records"] = len(want)
+        out["i16_records_differing"] = sum(1 for a, b in zip(want, got) if a != b) + abs(len(want) - len(got))
+        batch.close(); gpu16.close()
+    print(json.dumps(out))
+    return 0 if out["u8_records_differing"] == 0 and out.get("i16_records_differing", 0) == 0 else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
