@@ -341,6 +341,7 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 		k_publish_tail<<<1, 32, 0, st>>>(c->dbox, c->albase.as<uint32_t>(), c->nal.as<uint32_t>(), c->edbase.as<uint32_t>(), c->ned.as<uint32_t>(), n, c->poolerr.as<uint32_t>());
 		CK(cudaStreamSynchronize(st));
 		const volatile uint32_t* last = c->hbox->last; const uint32_t perr = c->hbox->perr;
+		if(perr & 32u) throw std::string("bt2gpu: internal error: a backtrace lane did not finish (k_bt watchdog)");
 		if(perr & 16u) throw std::string("bt2gpu: a read's minimum score is below -254: the -DENABLE_I16 build aligns it with the 16-bit score range, which this library does not implement");
 		if(perr) { char b[128]; snprintf(b, sizeof(b), "bt2gpu: device pool exhausted (mask %u); use smaller batches", perr); throw std::string(b); }
 		c->out_alns = (uint64_t)last[0] + last[1]; c->out_edits = (uint64_t)last[2] + last[3];

@@ -174,6 +174,7 @@ struct BtMachine {
 		row = rows - 1; col = (int)(candNext & 255u);
 		sv = svLast; sk = (uint32_t)R - 1u;
 		cidx = cell_at(sv, sk, (uint32_t)col);
+		ct = CT_H;   // (the chunk prediction of the start cell reads it)
 		phase = BP_CAND;
 	}
 	BT2_HD void row_up() {   // row-- : the strip / row-in-strip pair follows without a division
@@ -197,8 +198,15 @@ struct BtMachine {
 		asm volatile("cp.async.wait_all;" ::: "memory");
 #endif
 	}
-	// chunk the walk most likely enters after the one holding (row, col): the next strip up the diagonal
+	// chunk the walk most likely enters after the one holding (row, col), assuming it keeps its direction: up the column
+	// in a reference-gap run (F), along the row in a read-gap run (E), else up the diagonal
 	BT2_HD uint32_t predict_chunk() const {
+		const uint32_t t = (uint32_t)col + sv + (uint32_t)R - 1u - sk, per = 1u << lg, tm = t & (per - 1u), ch = cidx >> 4;
+		if(ct == CT_F) {   // (row - j, col) lies in unit t + j while it stays in the strip
+			if(sk >= per - tm) return ch + BT2_STRIPS < BT2_CELL_BYTES / 16u ? ch + BT2_STRIPS : BT2_NIL;
+			return sv == 0u ? BT2_NIL : cell_at(sv - 1u, (uint32_t)R - 1u, (uint32_t)col) >> 4;
+		}
+		if(ct == CT_E) return ((uint32_t)col > tm && ch >= BT2_STRIPS) ? ch - BT2_STRIPS : BT2_NIL;   // (row, col - j): unit t - j
 		const int c2 = col - (int)sk - 1;
 		if(sv == 0u || c2 < 0) return BT2_NIL;
 		return cell_at(sv - 1u, (uint32_t)R - 1u, (uint32_t)c2) >> 4;   // row R-1 of the strip above, same diagonal

@@ -144,8 +144,13 @@ __global__ void k_step(const DevParams* __restrict__ Pp, const DevIndex ix, cons
 	states[read] = rs;
 }
 
+#define BT2_BT_SPIN_LIMIT (1u << 22)
+#ifndef BT2_BT_THREADS
 #define BT2_BT_THREADS 128
+#endif
+#ifndef BT2_BT_BLOCKS_PER_SM
 #define BT2_BT_BLOCKS_PER_SM 6
+#endif
 
 // One lane per problem, persistent: a lane that finishes its problem takes the next one.
 // The lanes of a warp are in different phases (candidate pick, backtrace cell, alignment
@@ -162,9 +167,16 @@ __global__ void __launch_bounds__(BT2_BT_THREADS, BT2_BT_BLOCKS_PER_SM) k_bt(con
 	BtMachine m;
 	m.pc = pcs + threadIdx.x; m.pcs = BT2_BT_THREADS;
 	m.cbuf = chunks + 16 * threadIdx.x; m.cstride = 16 * BT2_BT_THREADS; m.cbuf_sa = (uint32_t)__cvta_generic_to_shared(m.cbuf);
-	m.phase = BP_DONE; m.result = BT_CONTINUE;
+	m.phase = BP_DONE; m.result = BT_CONTINUE; m.ct = CT_H;
 	bool have = false, drained = false;
+	uint32_t spins = 0;   // iterations since this lane last took a problem: a problem needs far fewer (cells visited + candidates)
 	while(true) {
+		if(__any_sync(0xffffffffu, ++spins > BT2_BT_SPIN_LIMIT)) {   // never expected: fail loudly (error bit 32) instead of hanging the stream
+			if(have && spins > BT2_BT_SPIN_LIMIT)
+				printf("bt2gpu k_bt: lane stuck: slot %u read %u phase %d row %d col %d cural %u ncand %u ct %d cidx %u\n", m.slot, m.read, m.phase, m.row, m.col, m.cural, m.ncand, m.ct, m.cidx);
+			set_error(cx.pools, 32);
+			break;
+		}
 		if(m.phase == BP_CAND || m.phase == BP_STEP) m.hot(cx);
 		const uint32_t hot = __ballot_sync(0xffffffffu, m.phase == BP_CAND || m.phase == BP_STEP);
 		const uint32_t wpost = __ballot_sync(0xffffffffu, m.phase == BP_POST);
@@ -192,7 +204,7 @@ __global__ void __launch_bounds__(BT2_BT_THREADS, BT2_BT_BLOCKS_PER_SM) k_bt(con
 						pcs[(4 * q + 2) * BT2_BT_THREADS + threadIdx.x] = w.z; pcs[(4 * q + 3) * BT2_BT_THREADS + threadIdx.x] = w.w;
 					}
 					m.begin(cx);
-					have = true;
+					have = true; spins = 0;
 				}
 			}
 		}
