@@ -136,7 +136,8 @@ struct BtMachine {
 	const uint32_t* pc; uint32_t pcs; // character cache of the problem: word j at pc[j * pcs]
 	// two 16-byte chunks of the cell array: the one the walk is in and the one it is predicted to enter next
 	// (asynchronous copy issued when a chunk is entered, so that its latency overlaps the steps in between)
-	uint8_t* cbuf; uint32_t cstride;  // chunk b of this lane at cbuf + b * cstride
+	// (buffers 2 and 3: the group of 8 candidates the loop is in and the next one)
+	uint8_t* cbuf; uint32_t cstride;  // buffer b of this lane at cbuf + b * cstride
 	uint32_t cbuf_sa;                 // cbuf as a shared-window address (device)
 	uint32_t ctag0, ctag1, ccur;
 	// ---- cached per problem
@@ -148,7 +149,7 @@ struct BtMachine {
 	Rng rnd; uint32_t hw, attempts, nsteps;
 	// ---- nextAlignment state
 	int phase, result;
-	uint32_t cural, reseed, candNext, candAhead;
+	uint32_t cural, reseed;
 	// ---- backtrace state (one attempt)
 	int row, col, origCol, ct, score;
 	uint32_t cidx, sv, sk;            // cell_index(row + shift, col) and the strip / row within the strip it lies in
@@ -171,7 +172,7 @@ struct BtMachine {
 	// the next candidate's start cell (last row: row R-1 of strip svLast), or the end of the candidate loop
 	BT2_HD void seek_cand() {
 		if(cural >= ncand) { phase = BP_DONE; return; }
-		row = rows - 1; col = (int)(candNext & 255u);
+		row = rows - 1; col = (int)(cand_at(cural) & 255u);
 		sv = svLast; sk = (uint32_t)R - 1u;
 		cidx = cell_at(sv, sk, (uint32_t)col);
 		ct = CT_H;   // (the chunk prediction of the start cell reads it)
@@ -184,6 +185,20 @@ struct BtMachine {
 	BT2_HD void relocate() { cidx = cell_at(sv, sk, (uint32_t)col); }
 	BT2_HD void push_edit(uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scr[ned] = x; ned++; }
 
+	// candidate i of the problem: group i / 8 sits in buffer 2 + (i / 8) % 2
+	BT2_HD uint32_t cand_at(uint32_t i) const {
+		return *(const volatile uint16_t*)(cbuf + (2u + ((i >> 3) & 1u)) * cstride + (i & 7u) * 2u);
+	}
+	BT2_HD void cand_fetch(const BtCtx& cx, uint32_t g) {
+		const uint16_t* src = cx.probs[slot].cand + g * 8u;
+		const uint32_t b = 2u + (g & 1u);
+#if defined(__CUDA_ARCH__)
+		const uint32_t sa = cbuf_sa + b * cstride;
+		asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(sa), "l"(src) : "memory");
+#else
+		memcpy(cbuf + b * cstride, src, 16);
+#endif
+	}
 	BT2_HD void chunk_fetch(uint32_t b, uint32_t ch) {
 		const uint8_t* src = cellp + ch * 16u;
 #if defined(__CUDA_ARCH__)
@@ -239,7 +254,9 @@ struct BtMachine {
 		r.nExDpSuccs++; r.nDpLastSucc = r.nExDps - 1;
 		if(r.nDpFail > r.nDpFailStreak) r.nDpFailStreak = r.nDpFail;
 		r.nDpFail = 0;
-		cural = 0; candNext = p.cand[0]; candAhead = ncand > 1 ? p.cand[1] : 0u;
+		cural = 0;
+		cand_fetch(cx, 0); if(ncand > 8u) cand_fetch(cx, 1);
+		chunk_wait();
 		seek_cand();
 	}
 	BT2_HD void finish(const BtCtx& cx) {
@@ -247,8 +264,8 @@ struct BtMachine {
 		r.btSteps += nsteps; r.btAttempts += attempts;
 		r.rnd = rnd; r.scr_hw = (uint16_t)hw;
 	}
-	// candNext = cand[cural]; candAhead = cand[cural + 1], loaded one candidate early
-	BT2_HD void next_cand(const BtCtx& cx) { cural++; candNext = candAhead; candAhead = cural + 1 < ncand ? pb(cx).cand[cural + 1] : 0u; }
+	// entering group g = cural / 8: group g + 1 is copied into the buffer group g - 1 leaves (waited for by the next cell's chunk_wait)
+	BT2_HD void next_cand(const BtCtx& cx) { cural++; if((cural & 7u) == 0u && cural + 8u < ncand) cand_fetch(cx, (cural >> 3) + 1u); }
 
 	BT2_HD void attempt_failed(const BtCtx& cx) { // backtrace returned false: scratch keeps what was written (res.reset() only drops the count)
 		if(ned > hw) hw = ned;

@@ -14,6 +14,7 @@
 //   Scoring::maxReadGaps/maxRefGaps   scoring.cpp:42-98
 //   DynProgFramer::frameSeedExtensionRect dp_framer.cpp:81-125
 #pragma once
+#include <cstddef>
 #include <stdint.h>
 #include "bt2gpu.h"
 
@@ -293,20 +294,21 @@ struct ReadState {
 };
 
 // DPRect + SwAligner::initRef outputs for one DP problem, and what the fill leaves for the backtrace
-struct Problem {
+struct alignas(16) Problem {
 	uint32_t read;
 	uint16_t rows, cols;       // rdlen, rflen (# DP columns)
 	uint8_t  fw, R, pad[2];    // R = rows per virtual lane in the fill
 	int32_t  minsc;            // SwAligner::minsc_ (clamped to >= -254 for u8)
-	uint32_t tidx;
 	int64_t  refl;             // rect.refl
+	uint32_t tidx;
 	int32_t  triml, corel, corer;
 	// outputs of K_fill
 	int32_t  lrmax;            // max raw H in the last row
 	uint32_t ncand;
-	uint16_t cand[BT2GPU_MAX_COLS + 8]; // sorted best-first: (rawH << 8) | col
+	uint16_t cand[BT2GPU_MAX_COLS + 8]; // sorted best-first: (rawH << 8) | col; at a 16-byte boundary (read in groups of 8 by the backtrace)
 	uint8_t  rf[BT2GPU_MAX_COLS + 8];   // reference masks for columns 0..cols (cols+1 fetched)
 };
+static_assert(offsetof(Problem, cand) % 16 == 0 && sizeof(Problem) % 16 == 0, "Problem::cand is copied in 16-byte groups");
 
 // What the fill leaves per DP cell for the backtrace: one byte of "not equal" flags, i.e. the
 // outcome of every score comparison backtraceNucleotidesEnd2EndSseU8 makes at that cell

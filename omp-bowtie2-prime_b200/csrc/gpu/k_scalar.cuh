@@ -163,7 +163,7 @@ __global__ void k_step(const DevParams* __restrict__ Pp, const DevIndex ix, cons
 __global__ void __launch_bounds__(BT2_BT_THREADS, BT2_BT_BLOCKS_PER_SM) k_bt(const __grid_constant__ BtCtx cx, uint32_t count,
                      uint32_t* task, uint32_t* next_list, uint32_t* next_cnt, uint32_t* roundend_list, uint32_t* roundend_cnt) {
 	__shared__ uint32_t pcs[BT2_PC_WORDS * BT2_BT_THREADS];
-	__shared__ __align__(16) uint8_t chunks[2 * 16 * BT2_BT_THREADS];
+	__shared__ __align__(16) uint8_t chunks[4 * 16 * BT2_BT_THREADS];   // two cell chunks and two candidate groups per lane
 	BtMachine m;
 	m.pc = pcs + threadIdx.x; m.pcs = BT2_BT_THREADS;
 	m.cbuf = chunks + 16 * threadIdx.x; m.cstride = 16 * BT2_BT_THREADS; m.cbuf_sa = (uint32_t)__cvta_generic_to_shared(m.cbuf);

@@ -170,7 +170,7 @@ int main(int argc, char** argv) {
 				if(advance(P, ix, rf, pools, rs, pb) == ADV_ROUND_END) break;
 				BtCtx cx; cx.P = P; cx.pools = pools; cx.states = states.data(); cx.probs = &pb; cx.cells = cells.data();
 				cx.pcache = pcache.data(); cx.scratch = scratch.data(); cx.seq = in->seq; cx.qual = in->qual; cx.set_pens();
-				BtMachine m; m.slot = 0; m.read = ri; m.pc = pcache.data(); m.pcs = 1; uint8_t cbuf[32]; m.cbuf = cbuf; m.cstride = 16;
+				BtMachine m; m.slot = 0; m.read = ri; m.pc = pcache.data(); m.pcs = 1; uint8_t cbuf[64]; m.cbuf = cbuf; m.cstride = 16;
 				fill_emu(P, pb, m.view(cx), cells.data(), pcache.data());
 				m.begin(cx);
 				while(m.phase != BP_DONE && m.step(cx)) { }
