@@ -75,7 +75,8 @@ char *bt2host_sam_records(const bt2host_job *job, const bt2host_batch *b,
                           const bt2gpu_results *res, int mode, size_t *len);
 /* The same records written to an open file descriptor (AlnSinkSam -> OutputQueue::flush,
  * aln_sink.cpp:1477, outq.cpp): blocks of reads are formatted in parallel and written in
- * read order, without building one contiguous buffer.  Returns 0, or -1 when write(2) fails
+ * read order (side by side with pwrite when the descriptor is seekable), without building one
+ * contiguous buffer.  Returns 0, or -1 when write(2) fails
  * (errno is write's); *len receives the number of bytes written. */
 int bt2host_sam_write(const bt2host_job *job, const bt2host_batch *b,
                       const bt2gpu_results *res, int mode, int fd, size_t *len);

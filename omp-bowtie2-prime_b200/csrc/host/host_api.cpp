@@ -106,18 +106,30 @@ char* bt2host_sam_records(const bt2host_job* job, const bt2host_batch* b, const 
 int bt2host_sam_write(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, int fd, size_t* len) {
 	std::vector<std::string> parts;
 	sam_blocks(job, b, res, mode, parts);
-	size_t tot = 0;
-	for(const std::string& o : parts) {
+	const int nt = (int)parts.size();
+	std::vector<size_t> offs((size_t)nt + 1, 0);
+	for(int t = 0; t < nt; t++) offs[(size_t)t + 1] = offs[(size_t)t] + parts[(size_t)t].size();
+	const size_t tot = offs[(size_t)nt];
+	auto put = [](int fd, const char* p, size_t n, off_t at) -> bool { // at < 0: write at the descriptor's position
 		size_t done = 0;
-		while(done < o.size()) {
-			const ssize_t w = write(fd, o.data() + done, o.size() - done);
-			if(w < 0) { if(errno == EINTR) continue; return -1; }
+		while(done < n) {
+			const ssize_t w = at < 0 ? write(fd, p + done, n - done) : pwrite(fd, p + done, n - done, at + (off_t)done);
+			if(w < 0) { if(errno == EINTR) continue; return false; }
 			done += (size_t)w;
 		}
-		tot += o.size();
+		return true;
+	};
+	const off_t base = lseek(fd, 0, SEEK_CUR);
+	bool ok = true;
+	if(base >= 0 && nt > 1) {   // a seekable file: the blocks are written side by side at their final offsets
+		#pragma omp parallel for num_threads(nt) schedule(static, 1) reduction(&&: ok)
+		for(int t = 0; t < nt; t++) ok = ok && put(fd, parts[(size_t)t].data(), parts[(size_t)t].size(), base + (off_t)offs[(size_t)t]);
+		if(ok && lseek(fd, base + (off_t)tot, SEEK_SET) < 0) ok = false;
+	} else {
+		for(int t = 0; t < nt && ok; t++) ok = put(fd, parts[(size_t)t].data(), parts[(size_t)t].size(), -1);
 	}
-	if(len) *len = tot;
-	return 0;
+	if(len) *len = ok ? tot : 0;
+	return ok ? 0 : -1;
 }
 void bt2host_free(void* p) { free(p); }
 void bt2host_job_metrics(const bt2host_job* job, uint64_t out[4]) { for(int i = 0; i < 4; i++) out[i] = job->j.met[i]; }

@@ -51,3 +51,13 @@ def test_sink_to_file_equals_sink_to_buffer(tmp_path):
     assert n == len(want)
     assert (tmp_path / "o.sam").read_bytes() == b"@HD\n" + want
     assert m1[0] - m0[0] == batch.n
+    # a descriptor that cannot seek (pipe): sequential writes, same bytes
+    import os, threading
+    r, w = os.pipe()
+    got = []
+    t = threading.Thread(target=lambda: got.append(os.fdopen(r, "rb").read()))
+    t.start()
+    with os.fdopen(w, "wb") as f:
+        job.sam_write(batch, res, f, 1)
+    t.join()
+    assert got[0] == want
