@@ -143,15 +143,14 @@ struct BtMachine {
 	// ---- cached per problem
 	uint8_t* cellp; uint32_t* scr;    // the problem's cells, the read's edit scratch
 	int rows, R, dlo;                 // core diagonals: dlo <= col-row < dlo + dspan
-	uint32_t dspan, lg, svLast;       // fill layout (dev_common.cuh): log2(units per chunk), strip of the last row
-	uint32_t glo, gspan;              // rows glo <= row < glo + gspan allow gaps
+	uint32_t dspan, svLast;           // fill layout (dev_common.cuh): strip of the last row
 	uint32_t ncand;
-	Rng rnd; uint32_t hw, attempts, nsteps;
+	Rng rnd; uint32_t hw, nsteps;     // nsteps: backtrace steps in the low 24 bits, attempts in the high 8 (<= 208 candidates)
 	// ---- nextAlignment state
 	int phase, result;
 	uint32_t cural, reseed;
 	// ---- backtrace state (one attempt)
-	int row, col, origCol, ct, score;
+	int row, col, ct, score;
 	uint32_t cidx, sv, sk;            // cell_index(row + shift, col) and the strip / row within the strip it lies in
 	uint32_t ned, nbranch;
 	bool coreHit;
@@ -163,10 +162,10 @@ struct BtMachine {
 		const ReadState& r = rs(cx);
 		ReadView v; v.seq = cx.seq + r.seq_off; v.qual = cx.qual + r.seq_off; v.rdlen = r.rdlen; v.fw = pb(cx).fw != 0; return v;
 	}
-	BT2_HD unsigned nsteps_attempt() const { return (unsigned)(rows - 1 - row) + (unsigned)(origCol - col) + 1u; }
+	BT2_HD uint32_t lg2() const { return R > 4 ? 1u : 2u; }   // log2(units per 16-byte chunk)
 	// cell_index_vk without the branch on R
 	BT2_HD uint32_t cell_at(uint32_t v, uint32_t k, uint32_t c) const {
-		const uint32_t t = c + v + (uint32_t)R - 1u - k;
+		const uint32_t t = c + v + (uint32_t)R - 1u - k, lg = lg2();
 		return ((((t >> lg) << 5) + v) << 4) + ((t & ((1u << lg) - 1u)) << (4u - lg)) + k;
 	}
 	// the next candidate's start cell (last row: row R-1 of strip svLast), or the end of the candidate loop
@@ -216,7 +215,7 @@ struct BtMachine {
 	// chunk the walk most likely enters after the one holding (row, col), assuming it keeps its direction: up the column
 	// in a reference-gap run (F), along the row in a read-gap run (E), else up the diagonal
 	BT2_HD uint32_t predict_chunk() const {
-		const uint32_t t = (uint32_t)col + sv + (uint32_t)R - 1u - sk, per = 1u << lg, tm = t & (per - 1u), ch = cidx >> 4;
+		const uint32_t t = (uint32_t)col + sv + (uint32_t)R - 1u - sk, per = 1u << lg2(), tm = t & (per - 1u), ch = cidx >> 4;
 		if(ct == CT_F) {   // (row - j, col) lies in unit t + j while it stays in the strip
 			if(sk >= per - tm) return ch + BT2_STRIPS < BT2_CELL_BYTES / 16u ? ch + BT2_STRIPS : BT2_NIL;
 			return sv == 0u ? BT2_NIL : cell_at(sv - 1u, (uint32_t)R - 1u, (uint32_t)col) >> 4;
@@ -231,12 +230,11 @@ struct BtMachine {
 	BT2_HD void begin(const BtCtx& cx) {
 		const DevParams& Pr = cx.P; const Problem& p = pb(cx); ReadState& r = rs(cx);
 		rows = p.rows; R = p.R; ncand = p.ncand;
-		lg = R > 4 ? 1u : 2u; svLast = ((uint32_t)p.rows + fill_shift((uint32_t)p.rows, (uint32_t)p.R)) / (uint32_t)p.R - 1u;
+		svLast = ((uint32_t)p.rows + fill_shift((uint32_t)p.rows, (uint32_t)p.R)) / (uint32_t)p.R - 1u;
 		dlo = (p.corel > 0 ? p.corel : 0) - p.triml; { const int dhi = p.corer - p.triml; dspan = dhi >= dlo ? (uint32_t)(dhi - dlo) + 1u : 0u; }
-		glo = (uint32_t)Pr.gapbar; gspan = p.rows > 2 * Pr.gapbar ? (uint32_t)(p.rows - 2 * Pr.gapbar) : 0u;
 		cellp = cx.cells + (size_t)slot * BT2_CELL_BYTES; scr = cx.scratch + (size_t)read * BT2_SCRATCH_EDITS;
 		chunk_wait();   // a chunk copy of the previous problem may still be on its way into this lane's buffers
-		nsteps = 0; attempts = 0; ctag0 = BT2_NIL; ctag1 = BT2_NIL; ccur = 0;
+		nsteps = 0; ctag0 = BT2_NIL; ctag1 = BT2_NIL; ccur = 0;
 		rnd = r.rnd; hw = r.scr_hw;
 		BT2_PROF(16, 1); BT2_PROF(17, ncand);
 		r.dpCells += (uint64_t)p.rows * p.cols;
@@ -261,7 +259,7 @@ struct BtMachine {
 	}
 	BT2_HD void finish(const BtCtx& cx) {
 		ReadState& r = rs(cx);
-		r.btSteps += nsteps; r.btAttempts += attempts;
+		r.btSteps += nsteps & 0xffffffu; r.btAttempts += nsteps >> 24;
 		r.rnd = rnd; r.scr_hw = (uint16_t)hw;
 	}
 	// entering group g = cural / 8: group g + 1 is copied into the buffer group g - 1 leaves (waited for by the next cell's chunk_wait)
@@ -303,9 +301,9 @@ struct BtMachine {
 			BT2_PROF(3, 1);
 			reseed = rnd.nextU32() + 1;
 			if(!cx.P.i16path) rnd.init(reseed);   // u8: reseed before and reseed+1 after the backtrace; i16: reseed after only (aligner_sw.cpp:324-348)
-			origCol = col; ct = CT_H;
+			ct = CT_H;
 			score = 0; nbranch = 0; ned = 0; coreHit = false;
-			attempts++;
+			nsteps += 1u << 24;
 			phase = BP_STEP;
 		}
 		nsteps++;
@@ -316,7 +314,7 @@ struct BtMachine {
 		const uint32_t eopts = hasLeft ? (((fl >> 2) & 2u) | ((fl >> 4) & 1u)) : 0u;   // EO -> bit1, EX -> bit0
 		const uint32_t fopts = ((fl >> 2) & 8u) | ((fl >> 4) & 4u);                      // FO -> bit3, FX -> bit2
 		uint32_t hopts = (hasLeft && (fl & CF_D)) ? 16u : 0u;
-		if((uint32_t)row - glo < gspan) {   // gaps allowed in this row
+		if(row >= cx.P.gapbar && row < rows - cx.P.gapbar) {   // gaps allowed in this row
 			if(fl & CF_HF) hopts |= fopts;
 			if(fl & CF_HE) hopts |= eopts;
 		}
@@ -377,6 +375,7 @@ struct BtMachine {
 		a.score = score; a.ns = ns; a.gaps = gaps; a.edits = (int32_t)ne;
 		a.basesAligned = (int32_t)p.rows - (int32_t)ne;   // trimEnd is 0: candidates come from the last row only
 		int refns = 0;
+		const int origCol = (int)(cand_at(cural) & 255u);   // the walk's start column
 		for(int i = col; i <= origCol; i++) if(pc_ref_code(pc, pcs, (uint32_t)i) > 3u) refns++;
 		a.refns = refns; a.n_edits = (uint16_t)ne;
 		if(!p.fw) { // AlnRes::invertEdits: scratch becomes 5'-based

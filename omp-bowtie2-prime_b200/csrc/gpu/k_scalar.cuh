@@ -172,8 +172,10 @@ __global__ void __launch_bounds__(BT2_BT_THREADS, BT2_BT_BLOCKS_PER_SM) k_bt(con
 	uint32_t spins = 0;   // iterations since this lane last took a problem: a problem needs far fewer (cells visited + candidates)
 	while(true) {
 		if(__any_sync(0xffffffffu, ++spins > BT2_BT_SPIN_LIMIT)) {   // never expected: fail loudly (error bit 32) instead of hanging the stream
+#ifdef BT2_BT_DEBUG
 			if(have && spins > BT2_BT_SPIN_LIMIT)
 				printf("bt2gpu k_bt: lane stuck: slot %u read %u phase %d row %d col %d cural %u ncand %u ct %d cidx %u\n", m.slot, m.read, m.phase, m.row, m.col, m.cural, m.ncand, m.ct, m.cidx);
+#endif
 			set_error(cx.pools, 32);
 			break;
 		}
