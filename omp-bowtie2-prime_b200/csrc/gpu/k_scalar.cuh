@@ -145,6 +145,12 @@ __global__ void k_step(const DevParams* __restrict__ Pp, const DevIndex ix, cons
 }
 
 #define BT2_BT_SPIN_LIMIT (1u << 22)
+#ifndef BT2_BT_POST_MIN
+#define BT2_BT_POST_MIN 8   // lanes that must want the rare paths before the warp takes them while others still walk
+#endif
+#ifndef BT2_BT_DONE_MIN
+#define BT2_BT_DONE_MIN 8
+#endif
 #ifndef BT2_BT_THREADS
 #define BT2_BT_THREADS 128
 #endif
@@ -182,9 +188,9 @@ __global__ void __launch_bounds__(BT2_BT_THREADS, BT2_BT_BLOCKS_PER_SM) k_bt(con
 		if(m.phase == BP_CAND || m.phase == BP_STEP) m.hot(cx);
 		const uint32_t hot = __ballot_sync(0xffffffffu, m.phase == BP_CAND || m.phase == BP_STEP);
 		const uint32_t wpost = __ballot_sync(0xffffffffu, m.phase == BP_POST);
-		if(wpost && (hot == 0 || __popc(wpost) >= 8)) { if(m.phase == BP_POST) m.post(cx); }
+		if(wpost && (hot == 0 || __popc(wpost) >= BT2_BT_POST_MIN)) { if(m.phase == BP_POST) m.post(cx); }
 		const uint32_t wdone = __ballot_sync(0xffffffffu, m.phase == BP_DONE && !drained);
-		if(wdone && (hot == 0 || __popc(wdone) >= 8)) {
+		if(wdone && (hot == 0 || __popc(wdone) >= BT2_BT_DONE_MIN)) {
 			if(m.phase == BP_DONE && !drained) {
 				if(have) {
 					m.finish(cx);
