@@ -36,7 +36,7 @@ READ_LEN = 150
 METRIC = "aligned_reads_per_sec_150bp_sensitive_e2e"
 ALU_WARP_INST_PER_CLK_SM = 1.95   # VIMNMX.S16x2 / HSET2 / LOP3 share this pipe (measured, profiles/r1_pipe_bench.txt)
 # profiles/r1_ncu_full_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum of one launch over 262 144 DP problems, per problem
-NCU_TRAFFIC_PER_PROBLEM = {"k_fill": 13.25e9 / 262144, "k_bt": 11.99e9 / 262144}
+NCU_TRAFFIC_PER_PROBLEM = {"k_fill": 13.25e9 / 262144, "k_bt": 5.68e9 / 262144}
 
 
 def log(*a):
