@@ -74,7 +74,13 @@ __device__ __forceinline__ void prio_work(const PrioArrays& pa, uint32_t ai, uin
 	w.sav = pa.sav + o; w.sorted = pa.sorted + o; w.rank = pa.rank + o; w.sp2 = pa.sp2 + o; w.exr = pa.exr + o; w.exrfw = pa.exrfw + o;
 }
 
-__global__ void k_prio1(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const uint32_t* active, uint32_t nactive,
+#ifndef BT2_STEP_BLOCKS_PER_SM
+#define BT2_STEP_BLOCKS_PER_SM 5
+#endif
+#ifndef BT2_PRIO_BLOCKS_PER_SM
+#define BT2_PRIO_BLOCKS_PER_SM 6
+#endif
+__global__ void __launch_bounds__(128, BT2_PRIO_BLOCKS_PER_SM) k_prio1(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const uint32_t* active, uint32_t nactive,
                         const SeedHit* hits, uint32_t W, uint32_t maxOffs, const PrioArrays pa,
                         uint32_t* ext_list, uint32_t* ext_cnt, uint32_t* samp_list, uint32_t* samp_cnt) {
 	const uint32_t ai = blockIdx.x * blockDim.x + threadIdx.x;
@@ -127,7 +133,7 @@ __global__ void k_prio2(const DevParams* __restrict__ Pp, const Pools pools, Rea
 }
 
 // one extension step per read of the chunk; problem slot = position in the chunk
-__global__ void k_step(const DevParams* __restrict__ Pp, const DevIndex ix, const DevRef rf, const Pools pools, ReadState* states,
+__global__ void __launch_bounds__(128, BT2_STEP_BLOCKS_PER_SM) k_step(const DevParams* __restrict__ Pp, const DevIndex ix, const DevRef rf, const Pools pools, ReadState* states,
                        const uint32_t* list, uint32_t base, uint32_t count, Problem* probs,
                        uint32_t* roundend_list, uint32_t* roundend_cnt) {
 	const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
