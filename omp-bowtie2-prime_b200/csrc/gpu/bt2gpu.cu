@@ -406,12 +406,23 @@ void do_align_pipelined(bt2gpu_ctx* c, const bt2gpu_reads* in, bt2gpu_results* o
 	static const bool trace = getenv("BT2GPU_TRACE") != nullptr;
 	auto now = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
 	const double t00 = now();
-	Staged g = stage_upload(c, in, 0, std::min(n, chunk), 0, c->h2d);
-	for(uint32_t lo = 0; lo < n; lo += chunk) {
-		const uint32_t hi = std::min(n, lo + chunk);
+	// cut points: a short first sub-batch (its upload is the only one nothing overlaps) and a short last one (likewise its download)
+	std::vector<uint32_t> cut(1, 0u);
+	{
+		static const char* er = getenv("BT2GPU_PIPE_RAMP");
+		const uint32_t small = std::max<uint32_t>(chunk / (er ? (uint32_t)std::max(1, atoi(er)) : 8u), 1u);
+		uint32_t pos = std::min(n, small);
+		cut.push_back(pos);
+		while(n - pos > chunk + small) { pos += chunk; cut.push_back(pos); }
+		if(n - pos > small && small < chunk) { pos = n - small; cut.push_back(pos); }
+		if(pos < n) cut.push_back(n);
+	}
+	Staged g = stage_upload(c, in, cut[0], cut[1], 0, c->h2d);
+	for(size_t ci = 0; ci + 1 < cut.size(); ci++) {
+		const uint32_t lo = cut[ci], hi = cut[ci + 1];
 		Staged nx;
 		const double t0 = now();
-		if(hi < n) nx = stage_upload(c, in, hi, std::min(n, hi + chunk), g.set ^ 1, c->h2d); // the other set's batch finished before this point
+		if(hi < n) nx = stage_upload(c, in, hi, cut[ci + 2], g.set ^ 1, c->h2d); // the other set's batch finished before this point
 		const double t1 = now();
 		bind_staged(c, g);
 		if(ab > 0xf0000000ull || eb > 0xf0000000ull) throw std::string("bt2gpu_align_batch: more than 2^32 alignments or edits in one call; use smaller batches");
