@@ -38,6 +38,28 @@ def test_gpu_matches_oracle_and_golden(name):
     gpu.close(); orc.close()
 
 
+@pytest.mark.parametrize("name", ["lambda_k3_vs", "syn150_sensitive_dpad12"])
+def test_gpu_without_full_suffix_array(name, monkeypatch):
+    """BT2GPU_FULL_SA=0: the path an index of 2^32 rows or more takes -- every seed through the reference's LF walk (k_seed_walk),
+    offsets through LF walks to the sampled suffix array.  Same results, and exactly the oracle's LF step counts."""
+    monkeypatch.setenv("BT2GPU_FULL_SA", "0")
+    ref, reads, opts, gold = common.CASES[name]
+    job = pkg.Job(common.index_base(ref), opts)
+    batch = job.fastq(common.reads_path(reads))
+    orc = common.Oracle(job)
+    want = orc.align(batch)
+    gpu = _gpu(job)
+    got = gpu.align(batch)
+    diffs = common.compare_results(want, got)
+    assert not diffs, "\n".join(diffs[:10])
+    assert common.sorted_records(job.sam(batch, got, mode=1)) == common.golden_records(gold)
+    c = gpu.counters(); oc = orc.counters()
+    assert c["sa_probes"] == 0 and c["ext_text_steps"] == 0
+    assert c["lf_steps_search"] == oc["lfSearch"] and c["lf_steps_extend"] == oc["lfExtend"]
+    assert c["lf_steps_resolve"] == oc["lfResolve"] if "lfResolve" in oc else True
+    gpu.close(); orc.close()
+
+
 def test_gpu_edge_cases():
     """empty read, read shorter than the seed, all-N read, read > 160 bp (dropped like the reference), Ns inside seeds"""
     job = pkg.Job(common.index_base("syn"), "")
