@@ -6,7 +6,7 @@ PKG   := omp-bowtie2-prime_b200
 GPU   := $(PKG)/csrc/gpu
 HOST  := $(PKG)/csrc/host
 NVCC  ?= nvcc
-NVFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=false -Xcompiler -fPIC -shared -Iinclude
+NVFLAGS := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=false -Xcompiler -fPIC -shared -Xcompiler -pthread -Iinclude
 GCCLIB := $(dir $(shell g++ -print-libgcc-file-name))
 CXXFLAGS := -O2 -std=c++17 -fPIC -fopenmp -B$(GCCLIB) -L$(GCCLIB) -Iinclude -w
 

@@ -14,6 +14,7 @@
 #include <ctime>
 #include <string>
 #include <vector>
+#include <future>
 #include <algorithm>
 #include "bt2gpu.h"
 #include "dev_common.cuh"
@@ -422,7 +423,14 @@ void do_align_pipelined(bt2gpu_ctx* c, const bt2gpu_reads* in, bt2gpu_results* o
 		const uint32_t lo = cut[ci], hi = cut[ci + 1];
 		Staged nx;
 		const double t0 = now();
-		if(hi < n) nx = stage_upload(c, in, hi, cut[ci + 2], g.set ^ 1, c->h2d); // the other set's batch finished before this point
+		// the next sub-batch is staged by a helper thread: a copy from pageable memory blocks its caller, and this thread has
+		// kernels to launch (the other set's batch finished before this point)
+		std::future<Staged> fut;
+		if(hi < n) {
+			const uint32_t nlo = hi, nhi = cut[ci + 2]; const int nset = g.set ^ 1; const int dev = c->device;
+			fut = std::async(std::launch::async, [c, in, nlo, nhi, nset, dev]() { CK(cudaSetDevice(dev)); return stage_upload(c, in, nlo, nhi, nset, c->h2d); });
+		}
+		struct Join { std::future<Staged>& f; ~Join() { if(f.valid()) { try { f.get(); } catch(...) { } } } } join{fut};   // never leave the helper running
 		const double t1 = now();
 		bind_staged(c, g);
 		if(ab > 0xf0000000ull || eb > 0xf0000000ull) throw std::string("bt2gpu_align_batch: more than 2^32 alignments or edits in one call; use smaller batches");
@@ -436,6 +444,7 @@ void do_align_pipelined(bt2gpu_ctx* c, const bt2gpu_reads* in, bt2gpu_results* o
 		}
 		start_fetch(c, rb, ab, eb, c->d2h);
 		rb += c->n; ab += c->out_alns; eb += c->out_edits;
+		if(fut.valid()) nx = fut.get();   // (rethrows what the helper threw)
 		g = nx;
 	}
 	const double t3 = now();
