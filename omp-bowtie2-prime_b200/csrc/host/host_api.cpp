@@ -70,14 +70,16 @@ static char* dup_out(const std::string& s, size_t* len) {
 char* bt2host_sam_header(const bt2host_job* job) { return dup_out(bt2host::sam_header(job->j), nullptr); }
 // AlnSinkWrap::finishRead -> AlnSinkSam::append per read (aln_sink.cpp:643,1477): reads are independent (their RNG state
 // comes back with the results), so contiguous blocks of reads are formatted by OpenMP threads; the blocks are in read order
-static void sam_blocks(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, std::vector<std::string>& parts) {
+static std::vector<std::string>& sam_blocks(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode) {
 	const uint32_t n = res->n;
 	bt2host::Job& j = const_cast<bt2host_job*>(job)->j;
 	int nt = 1;
 #ifdef _OPENMP
 	nt = std::max(1, std::min(omp_get_max_threads(), (int)(n / 2048) + 1));
 #endif
-	parts.assign((size_t)nt, std::string());
+	std::vector<std::string>& parts = j.sinkparts;   // the blocks' strings keep their capacity (and pages) from call to call
+	if(parts.size() < (size_t)nt) parts.resize((size_t)nt);
+	for(std::string& o : parts) o.clear();
 	std::vector<uint64_t> mets((size_t)nt * 4, 0);
 	#pragma omp parallel for num_threads(nt) schedule(static, 1)
 	for(int t = 0; t < nt; t++) {
@@ -87,10 +89,10 @@ static void sam_blocks(const bt2host_job* job, const bt2host_batch* b, const bt2
 		for(uint32_t i = lo; i < hi; i++) bt2host::sam_for_read(j, &mets[(size_t)t * 4], b->b, *res, i, mode, o);
 	}
 	for(int t = 0; t < nt; t++) for(int k = 0; k < 4; k++) j.met[k] += mets[(size_t)t * 4 + k];
+	return parts;
 }
 char* bt2host_sam_records(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, size_t* len) {
-	std::vector<std::string> parts;
-	sam_blocks(job, b, res, mode, parts);
+	std::vector<std::string>& parts = sam_blocks(job, b, res, mode);
 	const int nt = (int)parts.size();
 	size_t tot = 0; for(const std::string& o : parts) tot += o.size();
 	char* out = (char*)malloc(tot + 1);
@@ -104,8 +106,7 @@ char* bt2host_sam_records(const bt2host_job* job, const bt2host_batch* b, const 
 	return out;
 }
 int bt2host_sam_write(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, int fd, size_t* len) {
-	std::vector<std::string> parts;
-	sam_blocks(job, b, res, mode, parts);
+	std::vector<std::string>& parts = sam_blocks(job, b, res, mode);
 	const int nt = (int)parts.size();
 	std::vector<size_t> offs((size_t)nt + 1, 0);
 	for(int t = 0; t < nt; t++) offs[(size_t)t + 1] = offs[(size_t)t] + parts[(size_t)t].size();

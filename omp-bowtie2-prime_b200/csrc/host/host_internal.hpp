@@ -60,6 +60,11 @@ struct Job {
 	bt2gpu_ref rf;
 	Options opt;
 	uint64_t met[4] = {0, 0, 0, 0};
+	// buffers that keep their pages between calls (a job is used by one caller thread at a time)
+	std::vector<std::string> sinkparts;   // SAM text of the sink's blocks
+	char* file_buffer(size_t n);          // >= n bytes, not initialised, owned by the job
+	char* filemem = nullptr; size_t filecap = 0;
+	~Job();
 };
 
 // vector storage that is not zero-filled by resize(): the readers overwrite every element (and do so on several threads)

@@ -151,6 +151,12 @@ static inline uint8_t asc2dna(int c) { // alphabet.cpp:142
 	            case 'G': case 'g': return 2; case 'T': case 't': return 3; default: return 4; }
 }
 
+char* Job::file_buffer(size_t n) {
+	if(n > filecap) { free(filemem); filemem = (char*)malloc(n + (n >> 3)); filecap = filemem ? n + (n >> 3) : 0; }
+	return filemem;
+}
+Job::~Job() { free(filemem); }
+
 void Batch::finalize() {
 	view.n = (uint32_t)(off.size() - 1);
 	view.seq_off = off.data(); view.seq = seq.data(); view.qual = qual.data();
@@ -244,11 +250,12 @@ static bool batch_from_fastq_serial(const Job& job, Batch& b, const std::string&
 bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_t skip, uint64_t maxn, std::string& err) {
 	FILE* f = fopen(path.c_str(), "rb");
 	if(!f) { err = "cannot open " + path; return false; }
-	std::vector<char, NoInitAlloc<char>> buf;
+	struct View { char* p; size_t n; char* data() const { return p; } size_t size() const { return n; } char& operator[](size_t i) const { return p[i]; } } buf{nullptr, 0};
 	{
 		fseek(f, 0, SEEK_END); const long sz = ftell(f); fseek(f, 0, SEEK_SET);
 		if(sz < 0) { fclose(f); return batch_from_fastq_serial(job, b, path, skip, maxn, err); }
-		buf.resize((size_t)sz);
+		buf.p = const_cast<Job&>(job).file_buffer((size_t)sz + 1); buf.n = (size_t)sz;   // the job's buffer keeps its pages between files
+		if(!buf.p) { fclose(f); err = "out of memory reading " + path; return false; }
 		// slices of the file are read by several threads (pread: no shared file position)
 		const int fd = fileno(f);
 		int nr = 1;

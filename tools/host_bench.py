@@ -2,7 +2,7 @@
 """FASTQ file -> SAM file through libbt2host.so + libbt2gpu.so on one GPU, stage by stage (host feed and sink).
 usage: host_bench.py [n_reads]     (the bench workload: 5 Mbp i.i.d. reference, 150 bp reads, --sensitive --dpad 12)
 Prints reads/s of: FASTQ parse + P0 scalars (bt2host_batch_from_fastq), bt2gpu_align_batch (host buffers in, pinned results out),
-SAM formatting + write to a file (bt2host_sam_write), and the three in sequence."""
+SAM formatting + write to a file (bt2host_sam_write; also to /dev/null = formatting alone), and the three in sequence."""
 import importlib
 import json
 import os
@@ -31,6 +31,9 @@ def main():
         with open(os.path.join(bench.WORK, "host_bench.sam"), "wb") as f:
             nbytes = job.sam_write(batch, res, f, 1)
         t3 = time.time()
+        with open("/dev/null", "wb") as f:      # formatting alone (what the file system adds is the difference to "sam")
+            job.sam_write(batch, res, f, 1)
+        best["sam_format"] = min(best.get("sam_format", 1e9), time.time() - t3)
         for k, v in (("parse", t1 - t0), ("align", t2 - t1), ("sam", t3 - t2), ("total", t3 - t0)):
             best[k] = min(best.get(k, 1e9), v)
         out["sam_bytes"] = nbytes
