@@ -52,6 +52,14 @@ const char *bt2host_job_refname(const bt2host_job *job, uint64_t i);
 bt2host_batch *bt2host_batch_from_fastq(const bt2host_job *job, const char *path,
                                         uint64_t skip, uint64_t max_reads,
                                         char *err, size_t errlen);
+/* Streaming variant: the records that lie completely inside the byte range
+ * [offset, offset + max_bytes) of the file (offset must be a record start; 0 to begin).
+ * *next_offset receives the offset of the first record not read; at the end of the
+ * file the batch is empty (n = 0).  Files the block reader declines (CR line ends, blank
+ * lines, a truncated record) return NULL with a message: read them whole instead. */
+bt2host_batch *bt2host_batch_from_fastq_range(const bt2host_job *job, const char *path,
+                                              uint64_t offset, uint64_t max_bytes,
+                                              uint64_t *next_offset, char *err, size_t errlen);
 /* Build a batch from in-memory reads (names may be NULL -> "0","1",...). seq is
  * ASCII (ACGTN), qual Phred+33 ASCII. */
 bt2host_batch *bt2host_batch_from_arrays(const bt2host_job *job, uint32_t n,

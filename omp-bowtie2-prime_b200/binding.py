@@ -98,6 +98,10 @@ def load_host():
             getattr(h, f).argtypes = [C.c_void_p]
         h.bt2host_batch_from_fastq.restype = C.c_void_p
         h.bt2host_batch_from_fastq.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.c_uint64, C.c_char_p, C.c_size_t]
+        h.bt2host_batch_name.restype = C.c_char_p
+        h.bt2host_batch_name.argtypes = [C.c_void_p, C.c_uint32]
+        h.bt2host_batch_from_fastq_range.restype = C.c_void_p
+        h.bt2host_batch_from_fastq_range.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.c_char_p, C.c_size_t]
         h.bt2host_batch_from_arrays.restype = C.c_void_p
         h.bt2host_batch_from_arrays.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_char_p, C.c_char_p, C.c_void_p, C.c_char_p, C.c_size_t]
         h.bt2host_batch_destroy.argtypes = [C.c_void_p]
@@ -160,6 +164,15 @@ class Job:
         if not p:
             raise RuntimeError("bt2host_batch_from_fastq: " + err.value.decode())
         return Batch(self, p)
+
+    def fastq_range(self, path, offset, max_bytes):
+        """The records lying completely inside [offset, offset + max_bytes) -> (batch, offset of the next record); n == 0 at the end."""
+        err = C.create_string_buffer(512)
+        nxt = C.c_uint64(0)
+        p = self._h.bt2host_batch_from_fastq_range(self.ptr, path.encode(), offset, max_bytes, C.byref(nxt), err, 512)
+        if not p:
+            raise RuntimeError("bt2host_batch_from_fastq_range: " + err.value.decode())
+        return Batch(self, p), nxt.value
 
     def arrays(self, seqs, quals=None, names=None):
         """Build a batch from python strings (ACGTN) and Phred+33 quality strings."""
@@ -225,6 +238,10 @@ class Batch:
     @property
     def n(self):
         return self.reads.contents.n
+
+    def name(self, i):
+        p = self.job._h.bt2host_batch_name(self.ptr, i)
+        return p.decode("latin-1") if p is not None else None
 
     def nbases(self):
         r = self.reads.contents

@@ -48,6 +48,13 @@ bt2host_batch* bt2host_batch_from_fastq(const bt2host_job* job, const char* path
 	if(!bt2host::batch_from_fastq(job->j, b->b, path, skip, max_reads, e)) { set_err(err, errlen, e); delete b; return nullptr; }
 	return b;
 }
+bt2host_batch* bt2host_batch_from_fastq_range(const bt2host_job* job, const char* path, uint64_t offset, uint64_t max_bytes,
+                                              uint64_t* next_offset, char* err, size_t errlen) {
+	bt2host_batch* b = new bt2host_batch();
+	std::string e;
+	if(!bt2host::batch_from_fastq_range(job->j, b->b, path, offset, max_bytes, next_offset, e)) { set_err(err, errlen, e); delete b; return nullptr; }
+	return b;
+}
 bt2host_batch* bt2host_batch_from_arrays(const bt2host_job* job, uint32_t n, const uint32_t* off, const char* seq,
                                          const char* qual, const char* const* names, char* err, size_t errlen) {
 	bt2host_batch* b = new bt2host_batch();

@@ -91,6 +91,7 @@ uint32_t gen_rand_seed(const uint8_t* seq, const uint8_t* qual, size_t len,
                        const std::string& name, uint32_t seed);
 void fill_p0(const Job& job, Batch& b); // minsc / nceil / interval per read
 bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_t skip, uint64_t maxn, std::string& err);
+bool batch_from_fastq_range(const Job& job, Batch& b, const std::string& path, uint64_t offset, uint64_t max_bytes, uint64_t* next_off, std::string& err);
 bool batch_from_arrays(const Job& job, Batch& b, uint32_t n, const uint32_t* off, const char* seq,
                        const char* qual, const char* const* names);
 

@@ -247,16 +247,24 @@ static bool batch_from_fastq_serial(const Job& job, Batch& b, const std::string&
 // starts are found by OpenMP threads over equal slices, and records (four lines each) are converted straight into the batch's
 // SoA arrays in two passes (lengths -> offsets -> bases/qualities/seed/name).  Same results as the serial parser; files
 // with CR line ends, blank lines or a truncated last record take the serial parser.
-bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_t skip, uint64_t maxn, std::string& err) {
+// The fast reader on the bytes [foff, foff + max_bytes) of the file (max_bytes 0: to the end).  A range that stops before the end of
+// the file is cut back to its last complete record; *next_off receives where the next range starts.  Returns 1, 0 when the layout
+// needs the serial parser (nothing read into `b`), -1 on error.
+static int fastq_fast(const Job& job, Batch& b, const std::string& path, uint64_t foff, uint64_t max_bytes, uint64_t skip, uint64_t maxn,
+                      uint64_t* next_off, std::string& err) {
 	FILE* f = fopen(path.c_str(), "rb");
-	if(!f) { err = "cannot open " + path; return false; }
+	if(!f) { err = "cannot open " + path; return -1; }
 	struct View { char* p; size_t n; char* data() const { return p; } size_t size() const { return n; } char& operator[](size_t i) const { return p[i]; } } buf{nullptr, 0};
+	bool to_eof = true;
 	{
-		fseek(f, 0, SEEK_END); const long sz = ftell(f); fseek(f, 0, SEEK_SET);
-		if(sz < 0) { fclose(f); return batch_from_fastq_serial(job, b, path, skip, maxn, err); }
+		fseek(f, 0, SEEK_END); const long fsz = ftell(f); fseek(f, 0, SEEK_SET);
+		if(fsz < 0) { fclose(f); return 0; }
+		if(foff > (uint64_t)fsz) foff = (uint64_t)fsz;
+		uint64_t sz = (uint64_t)fsz - foff;
+		if(max_bytes && max_bytes < sz) { sz = max_bytes; to_eof = false; }
 		buf.p = const_cast<Job&>(job).file_buffer((size_t)sz + 1); buf.n = (size_t)sz;   // the job's buffer keeps its pages between files
-		if(!buf.p) { fclose(f); err = "out of memory reading " + path; return false; }
-		// slices of the file are read by several threads (pread: no shared file position)
+		if(!buf.p) { fclose(f); err = "out of memory reading " + path; return -1; }
+		// slices of the range are read by several threads (pread: no shared file position)
 		const int fd = fileno(f);
 		int nr = 1;
 #ifdef _OPENMP
@@ -266,16 +274,18 @@ bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_
 		#pragma omp parallel for num_threads(nr) schedule(static, 1) reduction(&&: ok)
 		for(int t = 0; t < nr; t++) {
 			size_t lo = (size_t)sz * (size_t)t / (size_t)nr; const size_t hi = (size_t)sz * (size_t)(t + 1) / (size_t)nr;
-			while(lo < hi) { const ssize_t g = pread(fd, buf.data() + lo, hi - lo, (off_t)lo); if(g <= 0) { ok = false; break; } lo += (size_t)g; }
+			while(lo < hi) { const ssize_t g = pread(fd, buf.data() + lo, hi - lo, (off_t)(foff + lo)); if(g <= 0) { ok = false; break; } lo += (size_t)g; }
 		}
 		fclose(f);
-		if(!ok) { err = "cannot read " + path; return false; }
+		if(!ok) { err = "cannot read " + path; return -1; }
 	}
 	static const bool trace = getenv("BT2HOST_TRACE") != nullptr;
 	auto now = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
 	const double tA = now();
-	const size_t N = buf.size();
-	if(N == 0 || memchr(buf.data(), '\r', N)) return batch_from_fastq_serial(job, b, path, skip, maxn, err);
+	size_t N = buf.size();
+	if(next_off) *next_off = foff + N;
+	if(N == 0) { if(foff == 0) return 0; b.off.assign(1, 0); fill_p0(job, b); b.finalize(); return 1; }   // past the last record: an empty batch
+	if(memchr(buf.data(), '\r', N)) return 0;
 	// ---- line starts
 	int nt = 1;
 #ifdef _OPENMP
@@ -295,11 +305,16 @@ bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_
 		size_t tot = 0; for(auto& v : nl) tot += v.size();
 		ls.reserve(tot + 2); ls.push_back(0);
 		for(auto& v : nl) for(size_t x : v) ls.push_back(x + 1);
-		if(ls.back() != N) ls.push_back(N + 1);          // last line without '\n': pretend one follows
+		if(!to_eof) {                                    // cut the range back to its last complete record
+			const size_t full = ((ls.size() - 1) / 4) * 4;
+			if(full == 0) { err = "FASTQ record longer than the read range in " + path; return -1; }
+			ls.resize(full + 1); N = ls[full];
+			if(next_off) *next_off = foff + N;
+		} else if(ls.back() != N) ls.push_back(N + 1);   // last line without '\n': pretend one follows
 	}
 	const double tB = now();
 	const size_t nlines = ls.size() - 1;
-	if(nlines % 4 != 0) return batch_from_fastq_serial(job, b, path, skip, maxn, err);
+	if(nlines % 4 != 0) return 0;
 	const size_t nrec = nlines / 4;
 	const size_t r0 = std::min<size_t>((size_t)skip, nrec), r1 = maxn ? std::min<size_t>(nrec, r0 + (size_t)maxn) : nrec;
 	const size_t n = r1 - r0;
@@ -319,7 +334,7 @@ bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_
 		len[r - r0] = (uint32_t)(rem - t3);
 	}
 	const double tC = now();
-	if(!regular) return batch_from_fastq_serial(job, b, path, skip, maxn, err);
+	if(!regular) return 0;
 	b.off.assign(n + 1, 0);
 	for(size_t i = 0; i < n; i++) b.off[i + 1] = b.off[i] + len[i];
 	b.seq.resize(b.off[n]); b.qual.resize(b.off[n]); b.seed.resize(n); b.names.resize(n);
@@ -354,7 +369,20 @@ bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_
 	fill_p0(job, b);
 	b.finalize();
 	if(trace) fprintf(stderr, "[bt2host] fastq: lines %.1f ms, lengths %.1f ms, convert %.1f ms, P0 %.1f ms (%d threads)\n", tB - tA, tC - tB, tD - tC, now() - tD, nt);
-	return true;
+	return 1;
+}
+
+bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_t skip, uint64_t maxn, std::string& err) {
+	const int r = fastq_fast(job, b, path, 0, 0, skip, maxn, nullptr, err);
+	if(r == 0) return batch_from_fastq_serial(job, b, path, skip, maxn, err);
+	return r > 0;
+}
+
+// One range of a FASTQ file for a streaming caller: the records that lie completely inside [offset, offset + max_bytes).
+bool batch_from_fastq_range(const Job& job, Batch& b, const std::string& path, uint64_t offset, uint64_t max_bytes, uint64_t* next_off, std::string& err) {
+	const int r = fastq_fast(job, b, path, offset, max_bytes, 0, 0, next_off, err);
+	if(r == 0) err = "FASTQ layout needs the serial parser (CR line ends, blank lines or a truncated record): read the whole file with bt2host_batch_from_fastq";
+	return r > 0;
 }
 
 bool batch_from_arrays(const Job& job, Batch& b, uint32_t n, const uint32_t* off, const char* seq,

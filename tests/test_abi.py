@@ -90,3 +90,38 @@ def test_fastq_fast_path_equals_serial_parser(tmp_path):
         # part of the file: skip / max_reads
         c, d = job.fastq(src, 100, 250), job.fastq(str(crlf), 100, 250)
         assert c.reads.contents.n == d.reads.contents.n == 250 and c.nbases() == d.nbases()
+
+
+def test_fastq_ranges_equal_whole_file():
+    """bt2host_batch_from_fastq_range: the batches of consecutive byte ranges, concatenated, are the whole-file batch"""
+    import numpy as np
+    import pytest
+    if not common.have_builder():
+        pytest.skip("no builder")
+    src = common.reads_path("lambda_reads_1k")
+    job = pkg.Job(common.index_base("lambda"), "--trim5 2")
+    whole = job.fastq(src)
+    rw = whole.reads.contents
+
+    def arr(r, f, dt, cnt):
+        return np.ctypeslib.as_array(ctypes.cast(getattr(r, f), ctypes.POINTER(np.ctypeslib.as_ctypes_type(dt))), shape=(cnt,)).copy()
+    for chunk in (3000, 50000, 10 ** 9):
+        off, n, seq, qual, seed, names, lens = 0, 0, [], [], [], [], []
+        while True:
+            b, nxt = job.fastq_range(src, off, chunk)
+            r = b.reads.contents
+            if r.n == 0:
+                assert nxt == off
+                break
+            so = arr(r, "seq_off", np.uint32, r.n + 1)
+            lens.append(np.diff(so)); seq.append(arr(r, "seq", np.uint8, b.nbases())); qual.append(arr(r, "qual", np.uint8, b.nbases()))
+            seed.append(arr(r, "rng_seed", np.uint32, r.n)); names += [b.name(i) for i in range(r.n)]
+            n += r.n; assert nxt > off; off = nxt; b.close()
+        assert n == rw.n and off == __import__("os").path.getsize(src)
+        assert (np.concatenate(lens) == np.diff(arr(rw, "seq_off", np.uint32, rw.n + 1))).all()
+        assert (np.concatenate(seq) == arr(rw, "seq", np.uint8, whole.nbases())).all()
+        assert (np.concatenate(qual) == arr(rw, "qual", np.uint8, whole.nbases())).all()
+        assert (np.concatenate(seed) == arr(rw, "rng_seed", np.uint32, rw.n)).all()
+        assert names == [whole.name(i) for i in range(rw.n)]
+    with pytest.raises(RuntimeError, match="longer than the read range"):
+        job.fastq_range(src, 0, 20)

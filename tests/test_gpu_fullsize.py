@@ -125,3 +125,19 @@ def test_full_size_properties(monkeypatch):
     g2.close()
     check_properties(rd, al, ed, reads, codes, 0.9995)
     batch.close(); job.close()
+
+
+@pytest.mark.gpu
+def test_streamed_fastq_to_sam_equals_one_batch(tmp_path):
+    """the reader / aligner / sink pipeline over byte ranges of the 1 M read file (two contexts on the device) writes the SAM of one batch"""
+    import importlib
+    stream = importlib.import_module("omp-bowtie2-prime_b200.stream")
+    job, batch, reads, codes = _workload(N_READS)
+    gpu = pkg.GpuAligner(job, 0)
+    want = job.sam_header().encode("latin-1") + job.sam_bytes(batch, gpu.align(batch), 1)
+    gpu.close()
+    import bench
+    n, nbytes = stream.fastq_to_sam(job, os.path.join(bench.WORK, "fullsize_%d.fq" % N_READS), str(tmp_path / "s.sam"), chunk_bytes=64 << 20)
+    assert n == N_READS
+    assert (tmp_path / "s.sam").read_bytes() == want
+    batch.close(); job.close()

@@ -61,3 +61,23 @@ def test_sink_to_file_equals_sink_to_buffer(tmp_path):
         job.sam_write(batch, res, f, 1)
     t.join()
     assert got[0] == want
+
+
+def test_streamed_fastq_to_sam_equals_whole_file(tmp_path):
+    """stream.fastq_to_sam (reader / aligner / sink threads over byte ranges of the file) writes the same SAM as one batch;
+    two oracle instances stand in for the two GPU contexts"""
+    if not common.have_builder():
+        pytest.skip("no builder")
+    import importlib
+    stream = importlib.import_module("omp-bowtie2-prime_b200.stream")
+    job = pkg.Job(common.index_base("lambda"), "")
+    src = common.reads_path("lambda_reads_1k")
+    batch = job.fastq(src)
+    o1, o2 = common.Oracle(job), common.Oracle(job)
+    want = job.sam_header().encode("latin-1") + job.sam_bytes(batch, o1.align(batch, 4), 1)
+    m0 = job.metrics()
+    n, nbytes = stream.fastq_to_sam(job, src, str(tmp_path / "s.sam"), chunk_bytes=40000, aligners=[o1, o2])
+    got = (tmp_path / "s.sam").read_bytes()
+    assert n == 1000 and got == want and nbytes == len(want) - len(job.sam_header().encode("latin-1"))
+    assert job.metrics()[0] - m0[0] == 1000
+    o1.close(); o2.close(); batch.close(); job.close()

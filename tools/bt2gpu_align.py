@@ -21,18 +21,25 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     job = pkg.Job(idx, " ".join(a))
-    gpu = pkg.GpuAligner(job, local)
-    if world == 1:   # one GPU: parse, align, and let the sink write its blocks straight to the file
-        batch = job.fastq(fq)
-        res = gpu.align(batch)
-        with open(out, "wb") as f:
-            f.write(job.sam_header().encode("latin-1"))
-            job.sam_write(batch, res, f, 1)
+    if world == 1:   # one GPU: reader, aligner and sink run as a pipeline over byte ranges of the file
+        stream = importlib.import_module("omp-bowtie2-prime_b200.stream")
+        try:
+            stream.fastq_to_sam(job, fq, out, device=local)
+        except RuntimeError as e:
+            if "serial parser" not in str(e):
+                raise
+            gpu = pkg.GpuAligner(job, local)   # CR line ends / blank lines: whole file through the serial parser
+            batch = job.fastq(fq)
+            res = gpu.align(batch)
+            with open(out, "wb") as f:
+                f.write(job.sam_header().encode("latin-1"))
+                job.sam_write(batch, res, f, 1)
+            batch.close(); gpu.close()
         met = job.metrics()
         print("%d reads; %d (%.2f%%) aligned 0 times; %d aligned exactly 1 time; %d aligned >1 times" %
               (met[0], met[1], 100.0 * met[1] / max(met[0], 1), met[2], met[3]), file=sys.stderr)
-        batch.close(); gpu.close()
         return
+    gpu = pkg.GpuAligner(job, local)
     n = sum(1 for _ in open(fq, "rb")) // 4
     sam, met = shard.align_sharded(job, fq, gpu.align, n, mode=1, device=torch.device("cuda", local))
     if sam is not None:

@@ -2,7 +2,7 @@
 """FASTQ file -> SAM file through libbt2host.so + libbt2gpu.so on one GPU, stage by stage (host feed and sink).
 usage: host_bench.py [n_reads]     (the bench workload: 5 Mbp i.i.d. reference, 150 bp reads, --sensitive --dpad 12)
 Prints reads/s of: FASTQ parse + P0 scalars (bt2host_batch_from_fastq), bt2gpu_align_batch (host buffers in, pinned results out),
-SAM formatting + write to a file (bt2host_sam_write; also to /dev/null = formatting alone), and the three in sequence."""
+SAM formatting + write to a file (bt2host_sam_write; also to /dev/null = formatting alone), the three in sequence ("total"), and the three as a pipeline over byte ranges of the file ("pipelined")."""
 import importlib
 import json
 import os
@@ -38,6 +38,14 @@ def main():
             best[k] = min(best.get(k, 1e9), v)
         out["sam_bytes"] = nbytes
         batch.close()
+    # the same three stages as a pipeline over byte ranges of the file (omp-bowtie2-prime_b200/stream.py)
+    stream = importlib.import_module("omp-bowtie2-prime_b200.stream")
+    pair = [gpu, pkg.GpuAligner(job, 0)]
+    for rep in range(3):
+        t0 = time.time()
+        stream.fastq_to_sam(job, fq, os.path.join(bench.WORK, "host_bench.sam"), aligners=pair)
+        best["pipelined"] = min(best.get("pipelined", 1e9), time.time() - t0)
+    pair[1].close()
     for k, v in best.items():
         out[k + "_s"] = round(v, 4); out[k + "_reads_per_s"] = round(n / v)
     print(json.dumps(out))
