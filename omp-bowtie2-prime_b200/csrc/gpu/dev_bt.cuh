@@ -216,14 +216,13 @@ struct BtMachine {
 	// in a reference-gap run (F), along the row in a read-gap run (E), else up the diagonal
 	BT2_HD uint32_t predict_chunk() const {
 		const uint32_t t = (uint32_t)col + sv + (uint32_t)R - 1u - sk, per = 1u << lg2(), tm = t & (per - 1u), ch = cidx >> 4;
-		if(ct == CT_F) {   // (row - j, col) lies in unit t + j while it stays in the strip
-			if(sk >= per - tm) return ch + BT2_STRIPS < BT2_CELL_BYTES / 16u ? ch + BT2_STRIPS : BT2_NIL;
-			return sv == 0u ? BT2_NIL : cell_at(sv - 1u, (uint32_t)R - 1u, (uint32_t)col) >> 4;
-		}
-		if(ct == CT_E) return ((uint32_t)col > tm && ch >= BT2_STRIPS) ? ch - BT2_STRIPS : BT2_NIL;   // (row, col - j): unit t - j
-		const int c2 = col - (int)sk - 1;
+		// same strip: a reference-gap run reaches unit t + (per - tm) (row - j lies in unit t + j), a read-gap run unit t - tm - 1
+		if(ct == CT_F && sk >= per - tm) return ch + BT2_STRIPS < BT2_CELL_BYTES / 16u ? ch + BT2_STRIPS : BT2_NIL;
+		if(ct == CT_E) return ((uint32_t)col > tm && ch >= BT2_STRIPS) ? ch - BT2_STRIPS : BT2_NIL;
+		// else the strip above: in this column (reference-gap run) or on this diagonal; its row R-1
+		const int c2 = ct == CT_F ? col : col - (int)sk - 1;
 		if(sv == 0u || c2 < 0) return BT2_NIL;
-		return cell_at(sv - 1u, (uint32_t)R - 1u, (uint32_t)c2) >> 4;   // row R-1 of the strip above, same diagonal
+		return cell_at(sv - 1u, (uint32_t)R - 1u, (uint32_t)c2) >> 4;
 	}
 
 	// SwDriver::extendSeeds right after swa.align(): counters, then either the candidate loop or done
