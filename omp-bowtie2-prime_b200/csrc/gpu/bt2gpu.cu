@@ -491,7 +491,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		ix.offs = upload(c, hix->offs, hix->offsLen); ix.rstarts = upload(c, hix->rstarts, hix->nFrag * 3); ix.plen = upload(c, hix->plen, hix->nPat);
 		for(int i = 0; i < 5; i++) ix.fchr[i] = hix->fchr[i];
 		ix.len = hix->len; ix.zOff = hix->zOff; ix.nFrag = hix->nFrag; ix.nPat = hix->nPat; ix.offRate = hix->offRate; ix.ftabChars = hix->ftabChars;
-		ix.sa32 = nullptr;
+		ix.sa32 = nullptr; ix.ktab = nullptr; ix.ktabChars = 0;
 		// ---- full suffix array (k_index.cuh); BT2GPU_FULL_SA=0 keeps the sampled one (LF walks), e.g. to save 4 B/row
 		{ const char* efs = getenv("BT2GPU_FULL_SA");
 		  if(!(efs && atoi(efs) == 0) && hix->len < 0xfffffff0ull && hix->offRate >= 0 && hix->offRate < 31) {
@@ -524,6 +524,39 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		DevRef& rf = c->rf;
 		rf.buf = upload(c, hrf->buf, (hrf->bufBases + 3) / 4);
 		c->textOk = hrf->bufBases == hix->len;
+		// ---- prefix table over the suffix array (k_index.cuh); BT2GPU_KTAB=0 keeps the index's own 10-mer ftab for the seed search
+		{ const char* ek = getenv("BT2GPU_KTAB");
+		  if(ix.sa32 && c->textOk && !(ek && atoi(ek) == 0) && hix->len > 0) {
+			int K = 1; while(K < 16 && (1ull << (2 * K)) <= hix->len) K++;          // 4^K > len: about one row per key or fewer
+			K = std::max(K, (int)hix->ftabChars); K = std::min(K, hix->len > (1ull << 30) ? 14 : 13);
+			if(ek && atoi(ek) > 0) K = std::min(std::max(atoi(ek), 2), 14);
+			if(K > hix->ftabChars || (ek && atoi(ek) > 0)) {
+				const uint64_t nk = 1ull << (2 * K), nrows = hix->len + 1;
+				uint32_t* kt = nullptr;
+				CK(cudaMalloc((void**)&kt, (nk + 1) * 4 + 16)); c->resident.push_back(kt);
+				const uint32_t* tw = reinterpret_cast<const uint32_t*>(rf.buf);
+				k_build_ktab<<<(uint32_t)((nrows + 255) / 256), 256>>>(ix, tw, kt, nrows, (uint32_t)K);
+				k_ktab_tail<<<(uint32_t)((nk + 255) / 256), 256>>>(ix, tw, kt, nrows, (uint32_t)K);
+				CK(cudaGetLastError()); CK(cudaDeviceSynchronize());
+				if(getenv("BT2GPU_CHECK_INDEX")) {   // self-test: every row lies in the interval of its own K-mer, the table is monotone
+					std::vector<uint32_t> hk(nk + 1), hs(nrows);
+					CK(cudaMemcpy(hk.data(), kt, (nk + 1) * 4, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(hs.data(), ix.sa32, nrows * 4, cudaMemcpyDeviceToHost));
+					const uint8_t* tb = hrf->buf;
+					auto base = [&](uint64_t j) { return (uint64_t)((tb[j >> 2] >> ((j & 3) * 2)) & 3); };
+					if(hk[0] != 0 || hk[nk] != nrows) { char b[160]; snprintf(b, sizeof(b), "bt2gpu_create: prefix table ends wrong (%u, %u of %llu rows)", hk[0], hk[nk], (unsigned long long)nrows); throw std::string(b); }
+					for(uint64_t k = 0; k < nk; k++) if(hk[k] > hk[k + 1]) throw std::string("bt2gpu_create: prefix table not monotone");
+					for(uint64_t i = 0; i < nrows; i++) {
+						uint64_t key = 0; const uint64_t p = hs[i];
+						for(int q = 0; q < K; q++) key = (key << 2) | (p + q < hix->len ? base(p + q) : 3);   // the end of the text sorts after T
+						if(!(hk[key] <= i && i < hk[key + 1])) {
+							char b[200]; snprintf(b, sizeof(b), "bt2gpu_create: prefix table wrong at row %llu (sa %llu key %llu: interval [%u, %u))", (unsigned long long)i, (unsigned long long)p, (unsigned long long)key, hk[key], hk[key + 1]);
+							throw std::string(b);
+						}
+					}
+				}
+				ix.ktab = kt; ix.ktabChars = K;
+			}
+		  } }
 		rf.rec_off = upload(c, hrf->rec_off, hrf->nrecs); rf.rec_len = upload(c, hrf->rec_len, hrf->nrecs);
 		rf.rec_tstart = upload(c, tstart.data(), tstart.size()); rf.rec_cum = upload(c, cum.data(), cum.size());
 		rf.ref_rec0 = upload(c, rec0.data(), rec0.size()); rf.nrecs = hrf->nrecs;

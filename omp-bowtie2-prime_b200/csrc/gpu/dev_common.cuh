@@ -49,6 +49,8 @@ struct DevIndex {
 	const uint64_t* rstarts;  // 3 per fragment
 	const uint64_t* plen;
 	const uint32_t* sa32;     // device-built full suffix array (one entry per BWT row), or null (see k_index.cuh)
+	const uint32_t* ktab;     // device-built prefix table: first row whose suffix starts with a ktabChars-mer >= the key, or null
+	int32_t  ktabChars;
 	uint64_t fchr[5];
 	uint64_t len, zOff, nFrag, nPat;
 	int32_t  offRate, ftabChars;

@@ -93,17 +93,17 @@ __device__ __forceinline__ uint64_t rev_pairs64(uint64_t v) {
 }
 // Compares the T bases that follow the first `fl` bases of row r's suffix with the pattern tail `pv` (T bases, first base
 // most significant): -1 suffix < pattern, 0 suffix starts with the pattern, +1 suffix > pattern.  A suffix that ends
-// inside the pattern is smaller ('$' sorts first).
+// inside the pattern is GREATER: the index sorts the end of the text after every base ("ACG$" follows "ACGT...").
 __device__ __forceinline__ int sa_cmp(const DevIndex& ix, const uint32_t* __restrict__ tw, uint32_t r, uint32_t fl, uint32_t T, uint64_t pv) {
 	const uint64_t x = (uint64_t)__ldg(ix.sa32 + r) + fl;
-	const uint64_t avail = ix.len - x;                 // rows of an ftab interval have at least fl bases
+	if(x >= ix.len) return 1;                          // a suffix of at most fl bases
+	const uint64_t avail = ix.len - x;
 	const uint32_t m = avail < (uint64_t)T ? (uint32_t)avail : T;
-	if(m == 0) return -1;
 	const uint64_t sv = rev_pairs64(text_bases32(tw, x)) >> (64u - 2u * m);
 	const uint64_t pm = pv >> (2u * (T - m));
 	if(sv < pm) return -1;
 	if(sv > pm) return 1;
-	return m < T ? -1 : 0;
+	return m < T ? 1 : 0;
 }
 
 __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevParams* __restrict__ Pp, const SeedKernelArgs a) {
@@ -134,13 +134,14 @@ __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevP
 		bool hit = false; int pos = 0;
 		if(ok) {
 			searched = true;
-			const int fl = ix.ftabChars;
+			const bool kt = a.text && ix.ktab && ix.ktabChars < L;        // the device's prefix table (k_index.cuh), else the index's ftab
+			const int fl = kt ? ix.ktabChars : ix.ftabChars;
 			int step = 0;
 			if(a.text && fl > 1 && fl <= L && L - fl <= 32) {
-				// suffix-array search: interval of the first fl bases from the ftab, the other L - fl bases by binary search
+				// suffix-array search: interval of the first fl bases from the table, the other L - fl bases by binary search
 				uint64_t k = 0;
 				for(int q = 0; q < fl; q++) k = (k << 2) | (uint64_t)STRAND_CH(seed_lo + q);
-				uint32_t lo = (uint32_t)ftab_hi(ix, k), hi = (uint32_t)ftab_lo(ix, k + 1);
+				uint32_t lo = kt ? __ldg(ix.ktab + k) : (uint32_t)ftab_hi(ix, k), hi = kt ? __ldg(ix.ktab + k + 1) : (uint32_t)ftab_lo(ix, k + 1);
 				const uint32_t T = (uint32_t)(L - fl);
 				if(T > 0 && hi > lo) {
 					const uint32_t* tw = reinterpret_cast<const uint32_t*>(a.text);

@@ -94,7 +94,7 @@ int main(int argc, char** argv) {
 	P.gapbar = hp->gapbar; P.rdGapOpen = hp->rdGapConst + hp->rdGapLinear; P.rdGapExt = hp->rdGapLinear;
 	P.rfGapOpen = hp->rfGapConst + hp->rfGapLinear; P.rfGapExt = hp->rfGapLinear; P.matchBonus = hp->matchBonus; P.i16 = hp->i16; P.i16path = (hp->i16 && !hp->enable8) ? 1 : 0;
 	for(int i = 0; i < 256; i++) { P.mmpens[i] = (uint8_t)hp->mmpens[i]; P.npens[i] = (uint8_t)hp->npens[i]; }
-	DevIndex ix; ix.sa32 = nullptr; ix.ebwt = hix->ebwt; ix.ftab = hix->ftab; ix.eftab = hix->eftab; ix.offs = hix->offs; ix.rstarts = hix->rstarts; ix.plen = hix->plen;
+	DevIndex ix; ix.sa32 = nullptr; ix.ktab = nullptr; ix.ktabChars = 0; ix.ebwt = hix->ebwt; ix.ftab = hix->ftab; ix.eftab = hix->eftab; ix.offs = hix->offs; ix.rstarts = hix->rstarts; ix.plen = hix->plen;
 	for(int i = 0; i < 5; i++) ix.fchr[i] = hix->fchr[i];
 	ix.len = hix->len; ix.zOff = hix->zOff; ix.nFrag = hix->nFrag; ix.nPat = hix->nPat; ix.offRate = hix->offRate; ix.ftabChars = hix->ftabChars;
 	std::vector<uint64_t> tstart(hrf->nrecs), cum(hrf->nrecs), rec0;

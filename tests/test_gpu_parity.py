@@ -79,6 +79,37 @@ def test_gpu_edge_cases():
     gpu.close(); orc.close()
 
 
+@pytest.mark.parametrize("ktab", ["", "12"])
+def test_gpu_reads_at_the_end_of_the_text(ktab, monkeypatch):
+    """seeds that match the last bases of the joined text: the suffixes there run off the end, which the index sorts AFTER
+    every base (the suffix-array search has to agree); with the device prefix table forced on for a small index as well
+    (BT2GPU_KTAB=12) and its self-check on (BT2GPU_CHECK_INDEX)"""
+    if ktab:
+        monkeypatch.setenv("BT2GPU_KTAB", ktab)
+    monkeypatch.setenv("BT2GPU_CHECK_INDEX", "1")
+    comp = {"A": "T", "C": "G", "G": "C", "T": "A", "N": "N"}
+    for ref in ("syn", "lambda"):
+        job = pkg.Job(common.index_base(ref), "")
+        fa = open(common.index_base(ref) + ".fa").read() if ref != "lambda" else open(common.os.path.join(common.GOLD, "lambda_virus.fa")).read()
+        last = "".join(fa.split(">")[-1].split("\n")[1:]).upper()     # the last sequence: its end is the end of the joined text
+        seqs = []
+        for end in range(0, 12):                                       # reads ending 0..11 bases before the end, three lengths
+            for L in (60, 100, 150):
+                r = last[len(last) - end - L: len(last) - end]
+                seqs += [r, "".join(comp[c] for c in reversed(r))]
+        seqs += [last[-22:], last[-30:], last[-23:-1]]
+        batch = job.arrays(seqs, ["I" * len(x) for x in seqs])
+        orc = common.Oracle(job)
+        want = orc.align(batch)
+        gpu = _gpu(job)
+        got = gpu.align(batch)
+        diffs = common.compare_results(want, got)
+        assert not diffs, ref + ": " + "\n".join(diffs[:10])
+        assert job.sam(batch, got, 1) == job.sam(batch, want, 1)
+        assert (got.reads["n_alns"] > 0).mean() > 0.9
+        gpu.close(); orc.close()
+
+
 def test_gpu_batch_split_and_determinism(monkeypatch):
     """results do not depend on the internal batch size or the number of DP slots (SURVEY 8b determinism contract)"""
     job = pkg.Job(common.index_base("syn"), "-k 2")
