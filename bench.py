@@ -289,12 +289,12 @@ def main():
     value = total_reads / dev_s
     peak, peak_src = peaks()
     # dominant kernel by device time, algorithmic bytes per launch (DESIGN.md "Kernels"):
-    #   k_seed  16 B per ftab jump + 16 B per suffix-array probe (4 B gather + 12 B of text) + 128 B per distinct BWT side touched by an LF step
+    #   k_seed  8 B per prefix-table lookup + 16 B per suffix-array probe (4 B gather + 12 B of text) + 128 B per distinct BWT side touched by an LF step
     #           (multi-row left extension) + 4 B SA gather and 1 B of text per compared base of a single-row extension
     #   k_step  4 B SA gather per resolved row + ~60 B of packed reference and 208 B of window written per DP problem
     #   k_fill  1 B of flags per DP cell (stored as 8-byte units of 5 cells for 129..160 bp reads) + ~0.9 KB of inputs/outputs per problem
     #   k_bt    1 B of flags read + 1 B written (visited mark) per backtrace step
-    phases = {"k_seed": (ctr["ms_seed"], ctr["n_seed"], 128.0 * ctr["lf_sides_touched"] + 16.0 * ctr["seeds_searched"] + 16.0 * ctr["sa_probes"] + 1.25 * ctr["ext_text_steps"]),
+    phases = {"k_seed": (ctr["ms_seed"], ctr["n_seed"], 128.0 * ctr["lf_sides_touched"] + 8.0 * ctr["seeds_searched"] + 16.0 * ctr["sa_probes"] + 1.25 * ctr["ext_text_steps"]),
               "k_step": (ctr["ms_resolve"], ctr["n_step"], 128.0 * ctr["lf_steps_resolve"] + 4.0 * ctr["sa_rows_resolved"] + 268.0 * ctr["dp_problems"]),
               "k_fill": (ctr["ms_fill"], ctr["n_fill"], 1.0 * ctr["dp_cells"] + 900.0 * ctr["dp_problems"]),
               "k_bt": (ctr["ms_bt"], ctr["n_bt"], 2.0 * ctr["bt_steps"])}
