@@ -528,8 +528,8 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		{ const char* ek = getenv("BT2GPU_KTAB");
 		  if(ix.sa32 && c->textOk && !(ek && atoi(ek) == 0) && hix->len > 0) {
 			int K = 1; while(K < 16 && (1ull << (2 * K)) <= hix->len) K++;          // 4^K > len: about one row per key or fewer
-			K = std::max(K, (int)hix->ftabChars); K = std::min(K, hix->len > (1ull << 30) ? 14 : 13);
-			if(ek && atoi(ek) > 0) K = std::min(std::max(atoi(ek), 2), 14);
+			K = std::max(K, (int)hix->ftabChars); K = std::min(K, hix->len > (1ull << 28) ? 14 : 13);   // 268 MB / 1 GB; measured: below ~3 probes per seed a bigger table gains nothing
+			if(ek && atoi(ek) > 0) K = std::min(std::max(atoi(ek), 2), 15);
 			if(K > hix->ftabChars || (ek && atoi(ek) > 0)) {
 				const uint64_t nk = 1ull << (2 * K), nrows = hix->len + 1;
 				uint32_t* kt = nullptr;
