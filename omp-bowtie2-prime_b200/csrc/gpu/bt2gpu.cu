@@ -69,6 +69,7 @@ struct bt2gpu_ctx {
 	bool textOk = false;              // the 2-bit reference is the index's joined text (same length)
 	// problem-slot arrays
 	DBuf probs, cells, pcache;
+	DBuf pk, nm;                      // 2-bit packed reads and their N masks (k_pack_reads)
 	// per-batch arrays
 	// two sets of input arrays and of packed results: while one sub-batch is being aligned the next one is
 	// uploaded and the previous one's results are copied back (bt2gpu_align_batch, separate copy streams)
@@ -154,6 +155,7 @@ void ensure_batch(bt2gpu_ctx* c, uint32_t n, uint64_t nbases, uint32_t maxOffs) 
 	const size_t nn = (size_t)n + 1;
 	c->states.ensure(nn * sizeof(ReadState));
 	c->scratch.ensure(nn * BT2_SCRATCH_EDITS * 4);
+	c->pk.ensure(nn * BT2_PK_WORDS * 4); c->nm.ensure(nn * BT2_NM_WORDS * 4);
 	c->hits.ensure(nn * W * sizeof(SeedHit)); c->seedtasks.ensure(nn * W * sizeof(SeedTask)); c->exttasks.ensure(nn * W * sizeof(SeedTask));
 	for(int i = 0; i < 7; i++) c->lists[i].ensure(nn * 4);
 	c->p_sav.ensure(nn * W * 2); c->p_sorted.ensure(nn * W); c->p_rank.ensure(nn * W * 2); c->p_sp2.ensure(nn * W * 2);
@@ -273,6 +275,7 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 	int seedBlocks = 0, btMaxBlocks = 0; { int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device); seedBlocks = nsm * 8; btMaxBlocks = nsm * BT2_BT_BLOCKS_PER_SM; }
 
 	k_begin<<<nblk(n, 256), 256, 0, st>>>(ba, states, L[0], cnt + C_CAND0); LAUNCH(c);
+	k_pack_reads<<<nblk(n, 128), 128, 0, st>>>(ba, states, c->pk.as<uint32_t>(), c->nm.as<uint32_t>()); LAUNCH(c);
 	uint32_t ncand = read_counters(c)[C_CAND0];
 	int cand = 0;
 	for(uint32_t round = 0; ncand > 0; round++) {
@@ -284,7 +287,7 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 		{
 			Phase ph(c, PH_SEED);
 			SeedKernelArgs sk; sk.active = L[2]; sk.nactive = nactive; sk.W = W; sk.maxOffs = maxOffs; sk.states = states; sk.seq = ba.seq;
-			sk.hits = c->hits.as<SeedHit>(); sk.tasks = c->seedtasks.as<SeedTask>(); sk.ntasks = cnt + C_SEEDNT; sk.counter = cnt + C_SEEDTASK; sk.stats = stats;
+			sk.pk = c->pk.as<uint32_t>(); sk.nm = c->nm.as<uint32_t>(); sk.hits = c->hits.as<SeedHit>(); sk.tasks = c->seedtasks.as<SeedTask>(); sk.ntasks = cnt + C_SEEDNT; sk.counter = cnt + C_SEEDTASK; sk.stats = stats;
 			sk.xtasks = c->exttasks.as<SeedTask>(); sk.nxtasks = cnt + C_XTASKN; sk.xcounter = cnt + C_XTASK; sk.text = (c->ix.sa32 && c->textOk) ? c->rf.buf : nullptr;
 			const uint64_t nslots = (uint64_t)nactive * W;
 			k_seed_init<<<(uint32_t)((nslots + 255) / 256), 256, 0, st>>>(c->ix, c->dP, sk); LAUNCH(c);
@@ -669,7 +672,7 @@ void bt2gpu_destroy(bt2gpu_ctx* c) {
 	cudaDeviceSynchronize();
 	for(void* p : c->resident) cudaFree(p);
 	if(c->dP) cudaFree(c->dP);
-	DBuf* all[] = { &c->probs, &c->cells, &c->pcache,
+	DBuf* all[] = { &c->probs, &c->cells, &c->pcache, &c->pk, &c->nm,
 		&c->states, &c->scratch, &c->hits, &c->seedtasks, &c->exttasks, &c->lists[0], &c->lists[1], &c->lists[2], &c->lists[3], &c->lists[4], &c->lists[5], &c->lists[6], &c->counters, &c->stats,
 		&c->p_sav, &c->p_sorted, &c->p_rank, &c->p_sp2, &c->p_exr, &c->p_exrfw, &c->p_nsp, &c->p_nsmall, &c->p_nexr, &c->p_nelt, &c->p_nadd,
 		&c->s_ovr, &c->s_ovp, &c->s_ovv, &c->s_sr, &c->s_sv, &c->s_cv, &c->s_rn, &c->s_rcur, &c->s_rth, &c->s_rfl, &c->s_rco, &c->s_rcn, &c->s_rns, &c->s_mass, &c->s_elim,

@@ -336,6 +336,8 @@ enum { CF_D = 1, CF_HE = 2, CF_HF = 4, CF_EO = 8, CF_EX = 16, CF_FO = 32, CF_FX 
 // The fill therefore writes whole 512-byte rows (one 16-byte store per lane and problem every `per` steps, all lanes in the same
 // row); a backtrace that follows a diagonal stays in one unit for R cells and moves per / (R + 1) rows up per strip crossed.
 // A fill warp works on two problems at once and uses the larger R of the two for both; Problem::R is what it used.
+#define BT2_PK_WORDS 12   // 2-bit packed read: 16 bases per word (+ words a 32-base window may touch)
+#define BT2_NM_WORDS 6    // its N mask: 32 bases per word
 #define BT2_STRIPS 32
 #define BT2_MAX_R  ((BT2GPU_MAX_ROWS + BT2_STRIPS - 1) / BT2_STRIPS)
 #define BT2_CELL_GROUPS ((BT2GPU_MAX_COLS + BT2_STRIPS + BT2_MAX_R + 3) / 2 + 1)  // t / per < this (per >= 2)

@@ -50,6 +50,26 @@ __global__ void k_begin(const BatchArrays b, ReadState* states, uint32_t* list, 
 	if(rs.phase != RS_FINISHED) list_append(list, cnt, i);
 }
 
+// 2-bit copy of every read (forward strand; N -> 0 plus a bit in the N mask) for the seed kernels: a seed's key is then a
+// funnel shift instead of a loop of byte loads.  Base j: bits 2 (j % 16) of word j / 16; N mask bit j % 32 of word j / 32.
+__global__ void k_pack_reads(const BatchArrays b, const ReadState* __restrict__ states, uint32_t* __restrict__ pk, uint32_t* __restrict__ nm) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= b.n) return;
+	uint32_t* po = pk + (size_t)i * BT2_PK_WORDS; uint32_t* no = nm + (size_t)i * BT2_NM_WORDS;
+	const uint32_t len = states[i].rdlen <= BT2GPU_MAX_ROWS ? states[i].rdlen : 0u;   // (longer reads never reach the seed search)
+	const uint8_t* s = b.seq + states[i].seq_off;
+	uint32_t nw = 0;
+	for(uint32_t w = 0; w < BT2_PK_WORDS; w++) {
+		uint32_t v = 0;
+		for(uint32_t j = w * 16u; j < w * 16u + 16u && j < len; j++) {
+			const uint32_t c = s[j];
+			if(c > 3u) nw |= 1u << (j & 31u); else v |= c << ((j & 15u) * 2u);
+		}
+		po[w] = v;
+		if(w & 1u) { no[w >> 1] = nw; nw = 0; }
+	}
+}
+
 // reads that want seed round `round` go to `out`; the others are finished
 __global__ void k_round_select(const DevParams* __restrict__ Pp, ReadState* states, const uint32_t* in, uint32_t nin,
                                uint32_t round, uint32_t* out, uint32_t* cnt) {

@@ -59,6 +59,8 @@ struct SeedKernelArgs {
 	SeedTask*        xtasks;    // [nactive*W] single-row hits waiting for their left extension (k_seed_ext1)
 	uint32_t*        nxtasks;
 	uint32_t*        xcounter;  // task counter of k_seed_ext1
+	const uint32_t*  pk;        // [n * BT2_PK_WORDS] 2-bit packed reads, by read id (k_pack_reads)
+	const uint32_t*  nm;        // [n * BT2_NM_WORDS] their N masks
 	const uint8_t*   text;      // 2-bit joined text (DevRef::buf), or null: no text-compare extension
 	uint32_t*        counter;   // task counter of k_seed_walk
 	unsigned long long* stats;  // [0] seeds searched [1] LF steps search [2] LF steps extend [3] sides loaded [4] text-compare extension steps [5] suffix-array probes
@@ -117,7 +119,7 @@ __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevP
 		const uint32_t ai = (uint32_t)(tk / a.W), h = (uint32_t)(tk - (uint64_t)ai * a.W);
 		const uint32_t s = h / a.maxOffs, i = h - s * a.maxOffs;
 		const ReadState& rs = a.states[a.active[ai]];
-		const uint32_t rdlen = rs.rdlen; const uint8_t* rseq = a.seq + rs.seq_off; const bool rc = (s == 1);
+		const uint32_t rdlen = rs.rdlen; const bool rc = (s == 1);
 		SeedHit* out = a.hits + tk;
 		uint32_t offset = 0; round_wanted(P, rs, rs.round, offset);
 		const SeedGeom g = seed_geom(P, rdlen, offset, (uint32_t)rs.interval, a.maxOffs);
@@ -127,9 +129,18 @@ __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevP
 		const int seed_lo = rc ? ((int)rdlen - depth - L) : depth;
 		if(ok && (seed_lo < 0 || seed_lo + L > (int)rdlen)) ok = false;
 		uint64_t key = 0, top = 0, bot = 0;
-		#define STRAND_CH(p) (rc ? (rseq[rdlen - 1 - (p)] > 3 ? 4 : 3 - rseq[rdlen - 1 - (p)]) : (int)rseq[(p)])
-		if(ok) { // InstantiatedSeed::instantiateExact: no N inside the seed
-			for(int k = 0; k < L; k++) { const int ch = STRAND_CH(seed_lo + k); if(ch > 3) ok = false; key = (key << 2) | (uint64_t)(ch & 3); }
+		if(ok) { // InstantiatedSeed::instantiateExact: no N inside the seed; the key from the packed read
+			const uint32_t read = a.active[ai];
+			const uint32_t* pk = a.pk + (size_t)read * BT2_PK_WORDS; const uint32_t* nm = a.nm + (size_t)read * BT2_NM_WORDS;
+			const uint32_t f0 = rc ? rdlen - (uint32_t)seed_lo - (uint32_t)L : (uint32_t)seed_lo;   // the seed's first base on the forward strand
+			const uint64_t maskL = L >= 32 ? ~0ull : ((1ull << (2 * L)) - 1ull);
+			const uint32_t w = f0 >> 4, sh = (f0 & 15u) * 2u;
+			const uint32_t w0 = pk[w], w1 = pk[w + 1], w2 = pk[w + 2];
+			const uint64_t v = ((uint64_t)__funnelshift_r(w0, w1, sh) | ((uint64_t)__funnelshift_r(w1, w2, sh) << 32)) & maskL;   // base f0 + j at bits 2j
+			const uint32_t nb = __funnelshift_r(nm[f0 >> 5], nm[(f0 >> 5) + 1], f0 & 31u) & (L >= 32 ? ~0u : ((1u << L) - 1u));
+			if(nb) ok = false;
+			// first strand base most significant; the reverse-complement strand reads the same window backwards, complemented
+			key = rc ? (~v & maskL) : (rev_pairs64(v) >> (64 - 2 * L));
 		}
 		bool hit = false; int pos = 0;
 		if(ok) {
@@ -139,8 +150,7 @@ __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevP
 			int step = 0;
 			if(a.text && fl > 1 && fl <= L && L - fl <= 32) {
 				// suffix-array search: interval of the first fl bases from the table, the other L - fl bases by binary search
-				uint64_t k = 0;
-				for(int q = 0; q < fl; q++) k = (k << 2) | (uint64_t)STRAND_CH(seed_lo + q);
+				const uint64_t k = key >> (2 * (L - fl));   // the first fl bases
 				uint32_t lo = kt ? __ldg(ix.ktab + k) : (uint32_t)ftab_hi(ix, k), hi = kt ? __ldg(ix.ktab + k + 1) : (uint32_t)ftab_lo(ix, k + 1);
 				const uint32_t T = (uint32_t)(L - fl);
 				if(T > 0 && hi > lo) {
@@ -155,19 +165,17 @@ __global__ void __launch_bounds__(256) k_seed_init(const DevIndex ix, const DevP
 				top = lo; bot = hi;
 				step = L;
 			} else if(fl > 1 && fl <= L) { // startSearchSeedBi: ftab jump over the last ftabChars bases
-				uint64_t k = 0;
-				for(int q = 0; q < fl; q++) k = (k << 2) | (uint64_t)STRAND_CH(seed_lo + L - fl + q);
+				const uint64_t k = key & ((1ull << (2 * fl)) - 1ull);   // the last fl bases
 				top = ftab_hi(ix, k); bot = ftab_lo(ix, k + 1);
 				step = fl;
 			} else if(L > 0) {
-				const int ch = STRAND_CH(seed_lo + L - 1);
+				const int ch = (int)(key & 3ull);
 				top = fchr_at(ix, ch); bot = fchr_at(ix, ch + 1);
 				step = 1;
 			} else { top = 0; bot = ix.fchr[4]; }
 			hit = bot != top;
 			pos = seed_lo + L - 1 - step;
 		}
-		#undef STRAND_CH
 		// (top, len) is the range reported when the whole seed was consumed here; k_seed_walk
 		// overwrites it with the range at the end of the search and fills nlex / valid
 		const bool whole = hit && pos < seed_lo;
@@ -383,23 +391,46 @@ __global__ void __launch_bounds__(256) k_seed_ext1(const DevIndex ix, const Seed
 		if(ti < ntasks) {
 			const SeedTask t = a.xtasks[ti];
 			SeedHit* out = a.hits + t.hit;
-			const uint8_t* rseq = a.seq + t.seq_off;
+			const uint32_t read = a.active[t.hit / a.W];
+			const uint32_t* pk = a.pk + (size_t)read * BT2_PK_WORDS; const uint32_t* nm = a.nm + (size_t)read * BT2_NM_WORDS;
+			const uint32_t* tw = reinterpret_cast<const uint32_t*>(a.text);
 			const uint32_t rdlen = t.rdlen; const bool rc = t.rc != 0;
 			uint64_t off = ix.sa32[out->top];
 			int pos = t.pos; uint32_t nlex = 0;
+			// The reference compares one base per LF step: strand base `pos` with the text base before `off`, both stepping down;
+			// an N in the read matches anything, and at text offset 0 only Ns go on (without moving).  Here up to 16 steps at a
+			// time: the packed read window against the packed text window, the first mismatch in step order ends the run.
 			while(true) {
-				steps++;
-				const uint32_t p = rc ? (rdlen - 1 - (uint32_t)pos) : (uint32_t)pos;
-				const int b = rseq[p];
-				const int ch = rc ? (b > 3 ? 4 : 3 - b) : b;
-				if(off == 0) { if(ch <= 3) break; }
-				else {
-					const uint64_t x = off - 1;
-					const int c = (a.text[x >> 2] >> ((x & 3) * 2)) & 3;
-					if(c != ch && ch <= 3) break;
-					off = x;
+				if(off == 0) {   // the '$' row: nothing precedes it
+					steps++;
+					const uint32_t q = rc ? (rdlen - 1u - (uint32_t)pos) : (uint32_t)pos;
+					if(!((nm[q >> 5] >> (q & 31u)) & 1u)) break;
+					nlex++; pos--;
+					if(nlex == 255 || pos < 0) break;
+					continue;
 				}
-				nlex++; pos--;
+				uint32_t cnt = 16u;
+				if(off < cnt) cnt = (uint32_t)off;
+				if((uint32_t)pos + 1u < cnt) cnt = (uint32_t)pos + 1u;
+				if(255u - nlex < cnt) cnt = 255u - nlex;
+				const uint32_t cmask = cnt >= 16u ? ~0u : ((1u << (2u * cnt)) - 1u);
+				const uint64_t x = off - cnt;                                        // text bases [x, off), base x + j at bits 2j
+				const uint32_t tv = __funnelshift_r(__ldg(tw + (x >> 4)), __ldg(tw + (x >> 4) + 1), (uint32_t)(x & 15u) * 2u);
+				const uint32_t q0 = rc ? (rdlen - 1u - (uint32_t)pos) : ((uint32_t)pos + 1u - cnt);   // forward-strand bases [q0, q0 + cnt)
+				const uint32_t rv = __funnelshift_r(pk[q0 >> 4], pk[(q0 >> 4) + 1], (q0 & 15u) * 2u);
+				uint32_t nb = __funnelshift_r(nm[q0 >> 5], nm[(q0 >> 5) + 1], q0 & 31u) & 0xffffu;
+				nb = (nb | (nb << 8)) & 0x00ff00ffu; nb = (nb | (nb << 4)) & 0x0f0f0f0fu; nb = (nb | (nb << 2)) & 0x33333333u; nb = (nb | (nb << 1)) & 0x55555555u;
+				uint32_t matched;
+				if(!rc) {   // step i compares forward base pos - i with text base off - 1 - i: both windows ascending, steps run from the top
+					uint32_t d = (tv ^ rv) & cmask; d = (d | (d >> 1)) & 0x55555555u & ~nb;
+					matched = d ? cnt - 1u - ((31u - (uint32_t)__clz(d)) >> 1) : cnt;
+				} else {    // step i compares the complement of forward base q0 + i with text base off - 1 - i: the text window reversed
+					uint32_t tr = __brev(tv & cmask); tr = ((tr & 0x55555555u) << 1) | ((tr >> 1) & 0x55555555u); tr >>= (32u - 2u * cnt);
+					uint32_t d = (tr ^ ~rv) & cmask; d = (d | (d >> 1)) & 0x55555555u & ~nb;
+					matched = d ? ((uint32_t)__ffs(d) - 1u) >> 1 : cnt;
+				}
+				nlex += matched; pos -= (int)matched; off -= matched; steps += matched;
+				if(matched < cnt) { steps++; break; }                                 // the comparison that failed was a step too
 				if(nlex == 255 || pos < 0) break;
 			}
 			out->nlex = nlex; out->valid = 1;
