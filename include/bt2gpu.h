@@ -294,6 +294,32 @@ int bt2gpu_test_fill(bt2gpu_ctx *ctx, uint32_t nprob, const uint32_t *seq_off, c
                      const uint64_t *hef_off, uint8_t *H, uint8_t *E, uint8_t *F, uint8_t *flags,
                      uint16_t *cand, uint32_t *ncand, int32_t *lrmax);
 
+/* DP fill without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  The same production fill kernel as bt2gpu_align_batch
+ * runs, on the same per-problem inputs and with the same per-problem outputs as bt2gpu_test_fill
+ * (minus the debug H/E/F matrices), but
+ *   - every pointer is a DEVICE pointer supplied by the caller (inputs and outputs alike), and the
+ *     work is only ENQUEUED on `stream` (a cudaStream_t; NULL = the legacy default stream): the
+ *     outputs are valid once the caller has synchronised that stream;
+ *   - the kernel's scratch (problem records, cell flags) is a file-scope device array of fixed
+ *     size, ~7.7 MB, held by every GPU that loads the library until the process exits: at most
+ *     BT2GPU_NOALLOC_MAX_PROBLEMS problems per call, more is rejected with an error;
+ *   - the call itself performs no cudaMalloc / cudaFree and calls no allocating library routine
+ *     (the context it is given was allocated by bt2gpu_create beforehand).
+ * All calls on a device share that one array: two calls whose kernels overlap on the GPU (different
+ * streams, different contexts or processes' threads) race; issue them on one stream or order them
+ * with events.  What has to start at zero is cleared by the call.  A problem whose size is out of
+ * range (rows 1..160, cols 1..199) gets ncand = 0, lrmax = -1 and no flags.
+ * flags: rows[i] x cols[i] bytes, row-major, at flags + flags_off[i]; cand: 256 entries per problem. */
+#define BT2GPU_NOALLOC_MAX_PROBLEMS 128
+int bt2gpu_fill_noalloc(bt2gpu_ctx *ctx, void *stream, uint32_t nprob,
+                        const uint32_t *d_seq_off, const uint8_t *d_seq, const uint8_t *d_qual,
+                        const uint16_t *d_rows, const uint16_t *d_cols,
+                        const uint32_t *d_rf_off, const uint8_t *d_rf, const int32_t *d_minsc,
+                        const uint64_t *d_flags_off, uint8_t *d_flags,
+                        uint16_t *d_cand, uint32_t *d_ncand, int32_t *d_lrmax);
+
 #ifdef __cplusplus
 }
 #endif

@@ -15,6 +15,7 @@
 #include <string>
 #include <vector>
 #include <future>
+#include <mutex>
 #include <algorithm>
 #include "bt2gpu.h"
 #include "dev_common.cuh"
@@ -459,6 +460,64 @@ void do_align_pipelined(bt2gpu_ctx* c, const bt2gpu_reads* in, bt2gpu_results* o
 	out->edits = c->h_edits.as<bt2gpu_edit>(); out->n_edits = eb;
 }
 
+// ---------------------------------------------------------------- DP fill without any allocation (bt2gpu_fill_noalloc)
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops).  The scratch k_fill needs -- the Problem / ReadState records it reads
+// and the cell flags it writes -- lives in a file-scope device array that every GPU loading this library holds until exit.
+struct NoAllocScratch {
+	unsigned long long stats[32];
+	Problem   probs[BT2GPU_NOALLOC_MAX_PROBLEMS];
+	ReadState states[BT2GPU_NOALLOC_MAX_PROBLEMS];
+	alignas(256) uint8_t cells[(size_t)BT2GPU_NOALLOC_MAX_PROBLEMS * BT2_CELL_BYTES];
+};
+// (a byte array: no dynamic initialisation of device objects; ~7.7 MB)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+
+// builds the records k_fill reads from the caller's arrays; a problem with a size out of range is switched off (read = NIL)
+__global__ void k_na_setup(NoAllocScratch* sc, uint32_t nprob, const uint32_t* seq_off, const uint16_t* rows, const uint16_t* cols,
+                           const uint32_t* rf_off, const uint8_t* rf, const int32_t* minsc) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i < 32) sc->stats[i] = 0;   // the array keeps the previous call's contents
+	if(i >= nprob) return;
+	Problem& pb = sc->probs[i];
+	const uint32_t r = rows[i], c = cols[i];
+	const bool ok = r >= 1 && r <= BT2GPU_MAX_ROWS && c >= 1 && c < BT2GPU_MAX_COLS;
+	pb.read = ok ? i : BT2_NIL; pb.rows = (uint16_t)r; pb.cols = (uint16_t)c; pb.fw = 1; pb.R = (uint8_t)fill_R(ok ? r : 1); pb.pad[0] = pb.pad[1] = 0;
+	pb.minsc = minsc[i]; pb.refl = 0; pb.tidx = 0; pb.triml = pb.corel = pb.corer = 0; pb.lrmax = -1; pb.ncand = 0;
+	if(ok) for(uint32_t k = 0; k <= c; k++) pb.rf[k] = rf[rf_off[i] + k];
+	ReadState& rs = sc->states[i];
+	rs.seq_off = seq_off[i]; rs.rdlen = (uint16_t)r;
+}
+// one block per problem: dense flags (row-major rows x cols) out of the cell layout, candidates, counts
+__global__ void k_na_export(const NoAllocScratch* sc, const uint64_t* flags_off, uint8_t* flags, uint16_t* cand, uint32_t* ncand, int32_t* lrmax) {
+	const uint32_t i = blockIdx.x;
+	const Problem& pb = sc->probs[i];
+	const bool ok = pb.read != BT2_NIL;
+	if(threadIdx.x == 0) { ncand[i] = ok ? pb.ncand : 0u; lrmax[i] = ok ? pb.lrmax : -1; }
+	if(!ok) return;
+	for(uint32_t k = threadIdx.x; k < pb.ncand; k += blockDim.x) cand[256u * i + k] = pb.cand[k];
+	const uint32_t rows = pb.rows, cols = pb.cols, R = pb.R, shift = fill_shift(rows, R);
+	const uint8_t* cells = sc->cells + (size_t)i * BT2_CELL_BYTES;
+	uint8_t* out = flags + flags_off[i];
+	for(uint32_t k = threadIdx.x; k < rows * cols; k += blockDim.x) out[k] = cells[cell_index(k / cols + shift, k % cols, R)];
+}
+
+// device address of the scratch array, resolved once per device with that device current: in host code the array's name is a
+// host-side stand-in, not a device address
+NoAllocScratch* noalloc_scratch(int device) {
+	static std::mutex mu;
+	static void* ptr[64] = { nullptr };
+	if(device < 0 || device >= 64) throw std::string("bt2gpu_fill_noalloc: device ordinal out of range");
+	std::lock_guard<std::mutex> lk(mu);
+	if(!ptr[device]) {
+		void* p = nullptr;
+		CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+		if(!p) throw std::string("bt2gpu_fill_noalloc: cudaGetSymbolAddress returned no address");
+		ptr[device] = p;
+	}
+	return reinterpret_cast<NoAllocScratch*>(ptr[device]);
+}
+
 } // namespace
 
 extern "C" {
@@ -665,6 +724,28 @@ int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, c
 int bt2gpu_get_counters(bt2gpu_ctx* ctx, bt2gpu_counters* c) { if(!ctx || !c) return -1; *c = ctx->ctr; return 0; }
 int bt2gpu_reset_counters(bt2gpu_ctx* ctx) { if(!ctx) return -1; memset(&ctx->ctr, 0, sizeof(ctx->ctr)); return 0; }
 const char* bt2gpu_last_error(const bt2gpu_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int bt2gpu_fill_noalloc(bt2gpu_ctx* ctx, void* stream, uint32_t nprob, const uint32_t* d_seq_off, const uint8_t* d_seq, const uint8_t* d_qual,
+                        const uint16_t* d_rows, const uint16_t* d_cols, const uint32_t* d_rf_off, const uint8_t* d_rf, const int32_t* d_minsc,
+                        const uint64_t* d_flags_off, uint8_t* d_flags, uint16_t* d_cand, uint32_t* d_ncand, int32_t* d_lrmax) {
+	API_GUARD({
+		if(nprob > BT2GPU_NOALLOC_MAX_PROBLEMS) {
+			char b[160]; snprintf(b, sizeof(b), "bt2gpu_fill_noalloc: %u problems, the static scratch holds at most %d", nprob, BT2GPU_NOALLOC_MAX_PROBLEMS);
+			throw std::string(b);
+		}
+		if(!d_seq_off || !d_seq || !d_qual || !d_rows || !d_cols || !d_rf_off || !d_rf || !d_minsc || !d_flags_off || !d_flags || !d_cand || !d_ncand || !d_lrmax)
+			throw std::string("bt2gpu_fill_noalloc: null argument");
+		if(nprob == 0) return 0;
+		NoAllocScratch* sc = noalloc_scratch(ctx->device);
+		cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+		k_na_setup<<<nblk(std::max(nprob, 32u), 128), 128, 0, st>>>(sc, nprob, d_seq_off, d_rows, d_cols, d_rf_off, d_rf, d_minsc);
+		FillArgs fa; fa.probs = sc->probs; fa.nprob = nprob; fa.states = sc->states; fa.seq = d_seq; fa.qual = d_qual; fa.cells = sc->cells;
+		fa.pcache = nullptr; fa.hef_dbg = nullptr; fa.stats = sc->stats;
+		k_fill<false><<<nblk(nprob, BT2_FILL_WARPS * 2), BT2_FILL_WARPS * 32, 0, st>>>(ctx->dP, fa);
+		k_na_export<<<nprob, 256, 0, st>>>(sc, d_flags_off, d_flags, d_cand, d_ncand, d_lrmax);
+		CK(cudaPeekAtLastError());
+	})
+}
 
 void bt2gpu_destroy(bt2gpu_ctx* c) {
 	if(!c) return;
