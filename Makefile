@@ -21,11 +21,13 @@ $(PKG)/libbt2host.so: $(wildcard $(HOST)/*.cpp $(HOST)/*.hpp) include/bt2gpu.h i
 oracle:
 	$(MAKE) -C oracle all
 
-emu: tests/emu/emu_pipeline
-tests/emu/emu_pipeline: tests/emu/emu_pipeline.cpp $(wildcard $(GPU)/*.cuh oracle/*.hpp $(HOST)/*.cpp)
+emu: tests/emu/emu_pipeline tests/emu/emu_fill
+tests/emu/emu_fill: tests/emu/emu_fill.cpp tests/emu/fill_scalar.hpp $(wildcard $(GPU)/*.cuh)
+	g++ -O1 -std=c++17 -Iinclude -w -o $@ tests/emu/emu_fill.cpp
+tests/emu/emu_pipeline: tests/emu/emu_pipeline.cpp tests/emu/fill_scalar.hpp $(wildcard $(GPU)/*.cuh oracle/*.hpp $(HOST)/*.cpp)
 	g++ $(CXXFLAGS) -Ioracle -o $@ tests/emu/emu_pipeline.cpp $(HOST)/host_index.cpp $(HOST)/host_reads.cpp $(HOST)/host_sink.cpp $(HOST)/host_api.cpp
 
 clean:
-	rm -f $(PKG)/*.so oracle/liboracle.so oracle/oracle_align tests/emu/emu_pipeline
+	rm -f $(PKG)/*.so oracle/liboracle.so oracle/oracle_align tests/emu/emu_pipeline tests/emu/emu_fill
 
 .PHONY: all oracle emu clean

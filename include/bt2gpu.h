@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define BT2GPU_ABI_VERSION 3
+#define BT2GPU_ABI_VERSION 4
 
 /* Limits inherited from the reference's fixed DP buffers
  * (aligner_result.h:42-43 ALN_MAX_ROWS/ALN_MAX_COLS, aligner_sw_driver.h:95 ALN_MAX_ITER). */
@@ -128,7 +128,7 @@ typedef struct bt2gpu_params {
 	int32_t mxDp;
 	int32_t streak;          /* maxDpStreak (-D) + (k-1)*maxStreakIncr                  */
 	int32_t doExtend;        /* seed left-extension (nlex) on                           */
-	int32_t enable8;         /* u8 DP allowed (--no-sse8 clears it; only honoured when i16) */
+	int32_t enable8;         /* u8 DP allowed; --no-sse8 clears it, which matters only with i16 = 1 (the default build has no other DP) */
 	int32_t tighten;         /* --tighten, default 3                                    */
 	int32_t khits;           /* -k                                                      */
 	int32_t mhits;           /* -M (0 = unset)                                          */
@@ -141,7 +141,12 @@ typedef struct bt2gpu_params {
 	int32_t i16;             /* 1: behave as the reference built with -DENABLE_I16: with enable8 == 0 its 16-bit
 	                          * DP path (aligner_sw.cpp:239-241, 336-348) is taken; reads whose minsc < -254 make
 	                          * bt2gpu_align_batch fail (16-bit score range not implemented)              */
-	int32_t reserved[7];
+	int32_t exactBestLtMinsc;/* 0 (default): K_fill computes only the band of DP diagonals an alignment scoring >= minsc can lie in
+	                          * (every alignment, edit, counter and random draw is the full rectangle's); the best score of a
+	                          * window WITHOUT any valid alignment, prm.bestLtMinscMate1 (printed only as Xs:i / ZT:Z with
+	                          * --sam-opt-config, sam.cpp:287-296,544), is then a lower bound.  1: fill the whole rectangle
+	                          * like EEU8_alignNucleotides (aligner_swsse_ee_u8.cpp:398) so that it is exact as well.    */
+	int32_t reserved[6];
 	int32_t mmpens[256];     /* Scoring::mmpens                                         */
 	int32_t npens[256];      /* Scoring::npens                                          */
 } bt2gpu_params;
@@ -216,6 +221,9 @@ typedef struct bt2gpu_read_result {
 	uint32_t scratch_off;  /* index of first scratch edit in bt2gpu_results.edits; the image is
 	                        * cut at the largest n_edits of the read's alignments     */
 	uint32_t n_scratch;
+	/* the rest of what bt2_search.cpp:2846-2854 hands to finishReadOne / what sam.cpp may print */
+	uint32_t nExUgs;       /* prm.nExUgs: ungapped extensions run; always 0 (extendSeeds never runs one, aligner_sw_driver.cpp:371) */
+	uint32_t exhaustive;   /* exhaustive[mate] of bt2_search.cpp:2399,2527: extendSeeds never sets it, always 0 */
 } bt2gpu_read_result;
 
 /* Library-owned (pinned) output, valid until the next call on the same ctx. */
@@ -238,7 +246,7 @@ typedef struct bt2gpu_counters {
 	uint64_t sa_rows_resolved;
 	uint64_t lf_steps_resolve;
 	uint64_t dp_problems;
-	uint64_t dp_cells;          /* sum rdlen*rflen of the DPs the control flow ran */
+	uint64_t dp_cells;          /* sum rdlen*rflen of the DPs the control flow ran (what the reference computes) */
 	uint64_t bt_attempts;
 	uint64_t bt_steps;
 	uint64_t alns_reported;
@@ -251,6 +259,7 @@ typedef struct bt2gpu_counters {
 	uint64_t ext_text_steps;    /* MultiSeedAligner::extend steps of single-row ranges, done as
 	                             * direct text comparisons through the device's full suffix array
 	                             * (each replaces one mapLF1 step of the reference)      */
+	uint64_t dp_cells_computed; /* cells K_fill actually computed for them: rdlen x (32 lanes x K diagonals of the band)   */
 	uint64_t sa_probes;         /* searchSeedBi done as binary searches over the device's full suffix array: probes
 	                             * (one 4-byte suffix-array gather + 12 bytes of text each); lf_steps_search then only
 	                             * counts the seeds that took the LF walk                                   */
@@ -283,16 +292,20 @@ int bt2gpu_abi_version(void);
  * on nprob independent problems.  Problem i uses rows[i] read bases at seq/qual +
  * seq_off[i] (already oriented: the strand buffer the fill sees), cols[i] reference
  * columns whose masks (1<<base, N=16; cols[i]+1 entries) start at rf + rf_off[i], and
- * minsc[i].  Outputs, per problem: dense raw-u8 H/E/F matrices (row-major rows x cols)
- * at hef_off[i] in H/E/F (kept by a debug instantiation of the kernel only), the byte of
- * backtrace comparison flags the production kernel stores per cell in `flags` (same
- * indexing; bit meanings: DESIGN.md "cell flags"), the sorted candidate list
- * ((rawH<<8)|col) at cand + 256*i, ncand[i] and lrmax[i].  nprob <= 4096. */
+ * minsc[i].  mode 0: the test instantiation of the kernel over the WHOLE rectangle; it also
+ * dumps dense raw-u8 H/E/F matrices (row-major rows x cols) at hef_off[i] in H/E/F.
+ * mode 1: the production instantiation over the band of diagonals bt2gpu_align_batch would
+ * compute (H/E/F untouched); mode 2: the same with the widest lane layout (K = 16, the one
+ * bt2gpu_fill_noalloc uses).  Outputs, per problem: the byte of backtrace comparison flags
+ * stored per cell in `flags` (same indexing as H; 0x80 for a cell outside the computed band; bit
+ * meanings: DESIGN.md "cell flags"), the sorted candidate list ((rawH<<8)|col) at
+ * cand + 256*i, ncand[i], lrmax[i], and band[2*i], band[2*i+1] = first diagonal (col - row)
+ * and number of diagonals computed.  nprob <= 4096. */
 int bt2gpu_test_fill(bt2gpu_ctx *ctx, uint32_t nprob, const uint32_t *seq_off, const uint8_t *seq,
                      const uint8_t *qual, const uint16_t *rows, const uint16_t *cols,
                      const uint32_t *rf_off, const uint8_t *rf, const int32_t *minsc,
                      const uint64_t *hef_off, uint8_t *H, uint8_t *E, uint8_t *F, uint8_t *flags,
-                     uint16_t *cand, uint32_t *ncand, int32_t *lrmax);
+                     uint16_t *cand, uint32_t *ncand, int32_t *lrmax, int32_t mode, int32_t *band);
 
 /* DP fill without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
@@ -303,7 +316,7 @@ int bt2gpu_test_fill(bt2gpu_ctx *ctx, uint32_t nprob, const uint32_t *seq_off, c
  *     work is only ENQUEUED on `stream` (a cudaStream_t; NULL = the legacy default stream): the
  *     outputs are valid once the caller has synchronised that stream;
  *   - the kernel's scratch (problem records, cell flags) is a file-scope device array of fixed
- *     size, ~7.7 MB, held by every GPU that loads the library until the process exits: at most
+ *     size, ~11.6 MB, held by every GPU that loads the library until the process exits: at most
  *     BT2GPU_NOALLOC_MAX_PROBLEMS problems per call, more is rejected with an error;
  *   - the call itself performs no cudaMalloc / cudaFree and calls no allocating library routine
  *     (the context it is given was allocated by bt2gpu_create beforehand).
@@ -311,7 +324,8 @@ int bt2gpu_test_fill(bt2gpu_ctx *ctx, uint32_t nprob, const uint32_t *seq_off, c
  * streams, different contexts or processes' threads) race; issue them on one stream or order them
  * with events.  What has to start at zero is cleared by the call.  A problem whose size is out of
  * range (rows 1..160, cols 1..199) gets ncand = 0, lrmax = -1 and no flags.
- * flags: rows[i] x cols[i] bytes, row-major, at flags + flags_off[i]; cand: 256 entries per problem. */
+ * flags: rows[i] x cols[i] bytes, row-major, at flags + flags_off[i] (0x80 for a cell outside the band of
+ * diagonals the kernel computes for the problem's minsc); cand: 256 entries per problem. */
 #define BT2GPU_NOALLOC_MAX_PROBLEMS 128
 int bt2gpu_fill_noalloc(bt2gpu_ctx *ctx, void *stream, uint32_t nprob,
                         const uint32_t *d_seq_off, const uint8_t *d_seq, const uint8_t *d_qual,

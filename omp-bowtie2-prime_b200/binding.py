@@ -27,8 +27,8 @@ class bt2gpu_params(C.Structure):
     _fields_ = [(n, C.c_int32) for n in
                 ("abi_version", "seedLen", "seedMms", "nSeedRounds", "seedBoostThresh", "maxhalf", "mxIter", "mxUg", "mxDp",
                  "streak", "doExtend", "enable8", "tighten", "khits", "mhits", "msample", "nofw", "norc", "gapbar",
-                 "rdGapConst", "rdGapLinear", "rfGapConst", "rfGapLinear", "matchBonus", "i16")] + \
-               [("reserved", C.c_int32 * 7), ("mmpens", C.c_int32 * 256), ("npens", C.c_int32 * 256)]
+                 "rdGapConst", "rdGapLinear", "rfGapConst", "rfGapLinear", "matchBonus", "i16", "exactBestLtMinsc")] + \
+               [("reserved", C.c_int32 * 6), ("mmpens", C.c_int32 * 256), ("npens", C.c_int32 * 256)]
 
 
 class bt2gpu_reads(C.Structure):
@@ -52,7 +52,8 @@ class bt2gpu_read_result(C.Structure):
                 ("nExIters", C.c_uint32), ("nExDps", C.c_uint32), ("nExDpSuccs", C.c_uint32), ("nExDpFails", C.c_uint32),
                 ("nDpFail", C.c_uint32), ("nDpFailStreak", C.c_uint32), ("nDpLastSucc", C.c_uint32), ("nRedundants", C.c_uint32),
                 ("bestLtMinsc", C.c_int32), ("nonzTot", C.c_uint32), ("numElts", C.c_uint32), ("numRanges", C.c_uint32),
-                ("nSeedsTried", C.c_uint32), ("scratch_off", C.c_uint32), ("n_scratch", C.c_uint32)]
+                ("nSeedsTried", C.c_uint32), ("scratch_off", C.c_uint32), ("n_scratch", C.c_uint32),
+                ("nExUgs", C.c_uint32), ("exhaustive", C.c_uint32)]
 
 
 class bt2gpu_results(C.Structure):
@@ -65,7 +66,7 @@ class bt2gpu_counters(C.Structure):
                 ("reads", "seeds_searched", "lf_steps_search", "lf_steps_extend", "lf_sides_touched", "sa_rows_resolved",
                  "lf_steps_resolve", "dp_problems", "dp_cells", "bt_attempts", "bt_steps", "alns_reported")] + \
                [(n, C.c_double) for n in ("ms_seed", "ms_glue", "ms_resolve", "ms_fill", "ms_bt", "ms_h2d", "ms_d2h", "ms_run")] + \
-               [(n, C.c_uint64) for n in ("launches", "n_seed", "n_step", "n_fill", "n_bt", "ext_text_steps", "sa_probes")]
+               [(n, C.c_uint64) for n in ("launches", "n_seed", "n_step", "n_fill", "n_bt", "ext_text_steps", "dp_cells_computed", "sa_probes")]
 
 
 READ_DT = np.dtype([(n, t) for n, t in
@@ -74,7 +75,7 @@ READ_DT = np.dtype([(n, t) for n, t in
                      ("nExIters", "<u4"), ("nExDps", "<u4"), ("nExDpSuccs", "<u4"), ("nExDpFails", "<u4"), ("nDpFail", "<u4"),
                      ("nDpFailStreak", "<u4"), ("nDpLastSucc", "<u4"), ("nRedundants", "<u4"), ("bestLtMinsc", "<i4"),
                      ("nonzTot", "<u4"), ("numElts", "<u4"), ("numRanges", "<u4"), ("nSeedsTried", "<u4"),
-                     ("scratch_off", "<u4"), ("n_scratch", "<u4")]])
+                     ("scratch_off", "<u4"), ("n_scratch", "<u4"), ("nExUgs", "<u4"), ("exhaustive", "<u4")]])
 ALN_DT = np.dtype([("refoff", "<i8"), ("tidx", "<u4"), ("score", "<i4"), ("minsc", "<i4"), ("ns", "<i4"), ("gaps", "<i4"),
                    ("edits", "<i4"), ("basesAligned", "<i4"), ("refns", "<i4"), ("edit_off", "<u4"), ("n_edits", "<u2"),
                    ("fw", "u1"), ("pad", "u1")])

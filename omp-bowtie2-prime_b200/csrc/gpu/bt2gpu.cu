@@ -67,6 +67,7 @@ struct bt2gpu_ctx {
 	DevIndex ix; DevRef rf;
 	std::vector<void*> resident;      // index / reference allocations
 	uint32_t nslots = 0, sampSlots = 0, maxBatch = 0;
+	uint32_t fillK = 4; size_t cellStride = 0; uint32_t chunkSlots = 0;   // of the resident batch: the fill's K, bytes of cell flags per problem slot, slots usable
 	bool textOk = false;              // the 2-bit reference is the index's joined text (same length)
 	// problem-slot arrays
 	DBuf probs, cells, pcache;
@@ -98,6 +99,17 @@ struct bt2gpu_ctx {
 };
 
 namespace {
+
+// the K (diagonals per lane) K_fill needs for reads of length L with minimum score minsc: the widest band any of their windows
+// can have (dev_common.cuh: fill_band; windows are framed as in dev_step.cuh: cols = L + 4 maxgap, at most 199)
+uint32_t fill_K_of(const DevParams& P, uint32_t L, int32_t minsc, bool exact) {
+	if(L == 0 || L > BT2GPU_MAX_ROWS) return 2;
+	const int rg = max_read_gaps(P, minsc, L), fg = max_ref_gaps(P, minsc, L);
+	int64_t maxgap = rg > fg ? rg : fg; if(maxgap > P.maxhalf) maxgap = P.maxhalf; if(maxgap < 0) maxgap = 0;
+	int64_t cols = (int64_t)L + 4 * maxgap; if(cols > BT2GPU_MAX_COLS - 1) cols = BT2GPU_MAX_COLS - 1;
+	int dlo, dhi; fill_band(P, (int)L, (int)cols, minsc < -254 ? -254 : minsc, exact, dlo, dhi);
+	return fill_K_for(dhi - dlo + 1);
+}
 
 template<typename T> T* upload(bt2gpu_ctx* c, const T* src, size_t n) {
 	T* d = nullptr;
@@ -184,7 +196,16 @@ void ensure_batch(bt2gpu_ctx* c, uint32_t n, uint64_t nbases, uint32_t maxOffs) 
 	c->cubtmp.ensure(tmp + 256);
 }
 
-struct Staged { uint32_t n = 0, maxOffs = 1, base = 0; uint64_t nb = 0; int set = 0; };
+// K_fill for the batch's K (template parameter: the cells of a step live in registers); dbg = the test instantiation that also
+// dumps H, E and F
+void launch_fill(uint32_t K, bool dbg, const DevParams* dP, const FillArgs& fa, cudaStream_t st) {
+	const dim3 grid(nblk(fa.nprob, BT2_FILL_WARPS * 4)), block(BT2_FILL_WARPS * 32);
+	#define BT2_LF(KK) { if(dbg) k_fill<KK, true><<<grid, block, 0, st>>>(dP, fa); else k_fill<KK, false><<<grid, block, 0, st>>>(dP, fa); }
+	switch(K) { case 2: BT2_LF(2) break; case 4: BT2_LF(4) break; case 8: BT2_LF(8) break; default: BT2_LF(16) break; }
+	#undef BT2_LF
+}
+
+struct Staged { uint32_t n = 0, maxOffs = 1, base = 0; uint64_t nb = 0; int set = 0; uint32_t fillK = 2, maxRows = 1; };
 
 void settle(bt2gpu_ctx::CopySpan& sp, double& acc) { // the copy a span brackets is over (or is waited for here): add its time
 	if(!sp.pending) return;
@@ -198,16 +219,18 @@ void settle(bt2gpu_ctx::CopySpan& sp, double& acc) { // the copy a span brackets
 Staged stage_upload(bt2gpu_ctx* c, const bt2gpu_reads* in, uint32_t lo, uint32_t hi, int set, cudaStream_t st) {
 	Staged g; g.n = hi - lo; g.set = set; g.base = in->seq_off[lo]; g.nb = (uint64_t)in->seq_off[hi] - g.base;
 	const uint32_t seedLen = (uint32_t)c->P.seedLen;
-	uint32_t lastL = 0; int32_t lastIv = 1;          // most batches have one read length: divide only when (L, interval) changes
+	uint32_t lastL = 0; int32_t lastIv = 1, lastMin = 1;   // most batches have one read length: divide only when (L, interval, minsc) changes
+	const bool exact = c->hp.exactBestLtMinsc != 0;
 	for(uint32_t i = lo; i < hi; i++) {
-		const int32_t iv = in->interval[i];
+		const int32_t iv = in->interval[i], ms = in->minsc[i];
 		const uint32_t o0 = in->seq_off[i], o1 = in->seq_off[i + 1];
 		if(iv < 1) throw std::string("bt2gpu: interval must be >= 1");
 		if(o1 < o0) throw std::string("bt2gpu: seq_off must be non-decreasing");
 		const uint32_t L = o1 - o0;
-		if(L == lastL && iv == lastIv) continue;
-		lastL = L; lastIv = iv;
+		if(L == lastL && iv == lastIv && ms == lastMin) continue;
+		lastL = L; lastIv = iv; lastMin = ms;
 		if(L > seedLen) { const uint32_t k = 1 + (L - seedLen) / (uint32_t)iv; if(k > g.maxOffs) g.maxOffs = k; }
+		if(L <= BT2GPU_MAX_ROWS) { const uint32_t K = fill_K_of(c->P, L, ms, exact); if(K > g.fillK) g.fillK = K; if(L > g.maxRows) g.maxRows = L; }
 	}
 	if(2 * g.maxOffs > 65535u) throw std::string("bt2gpu: too many seeds per read");
 	bt2gpu_ctx::InSet& I = c->in[set];
@@ -236,6 +259,13 @@ Staged stage_upload(bt2gpu_ctx* c, const bt2gpu_reads* in, uint32_t lo, uint32_t
 // stream after its copy
 void bind_staged(bt2gpu_ctx* c, const Staged& g) {
 	c->cur = g.set; c->n = g.n; c->nbases = g.nb; c->maxOffs = g.maxOffs; c->W = 2 * g.maxOffs; c->seq_base = g.base;
+	{ // the layout of the cell flags follows the batch: K from its lowest minimum score, rows from its longest read
+	  static const char* ek = getenv("BT2GPU_FILL_K");
+	  uint32_t K = g.fillK; if(ek && atoi(ek) > (int)K) K = (uint32_t)atoi(ek);
+	  if(K != 2 && K != 4 && K != 8 && K != 16) K = 16;
+	  c->fillK = K; c->cellStride = fill_cell_bytes(g.maxRows, K);
+	  c->chunkSlots = (uint32_t)std::min<size_t>(c->nslots, c->cells.cap / c->cellStride) & ~3u;
+	  if(c->chunkSlots < 4) throw std::string("bt2gpu: not enough device memory for the DP cell flags"); }
 	ensure_batch(c, g.n, g.nb, g.maxOffs);
 	CK(cudaStreamWaitEvent(c->stream, c->h2dspan[g.set].b, 0));
 }
@@ -269,7 +299,7 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 	sa.r_conv_off = c->s_rco.as<uint32_t>(); sa.r_conv_n = c->s_rcn.as<uint16_t>(); sa.r_nseen = c->s_rns.as<uint16_t>();
 	sa.mass = c->s_mass.as<double>(); sa.elim = c->s_elim.as<uint8_t>();
 	BtCtx bcx; bcx.P = c->P; bcx.pools = c->pools; bcx.states = states; bcx.probs = c->probs.as<Problem>();
-	bcx.cells = c->cells.as<uint8_t>(); bcx.pcache = c->pcache.as<uint32_t>();
+	bcx.cells = c->cells.as<uint8_t>(); bcx.cell_stride = c->cellStride; bcx.pcache = c->pcache.as<uint32_t>();
 	bcx.scratch = c->scratch.as<uint32_t>(); bcx.seq = ba.seq; bcx.qual = ba.qual; bcx.set_pens();
 	Problem* probs = c->probs.as<Problem>();
 	const Pools pools = c->pools;
@@ -314,13 +344,14 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 		while(ncur > 0) {
 			const int nxt = cur ^ 1;
 			zero_counter(c, nxt ? C_EXT1 : C_EXT0);
-			for(uint32_t b = 0; b < ncur; b += c->nslots) {
-				const uint32_t k = std::min(c->nslots, ncur - b);
+			for(uint32_t b = 0; b < ncur; b += c->chunkSlots) {
+				const uint32_t k = std::min(c->chunkSlots, ncur - b);
 				{ Phase ph(c, PH_RESOLVE);
 				  k_step<<<nblk(k, 128), 128, 0, st>>>(c->dP, c->ix, c->rf, pools, states, L[3 + cur], b, k, probs, L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_step++; }
 				{ Phase ph(c, PH_FILL);
-				  FillArgs fa; fa.probs = probs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.cells = c->cells.as<uint8_t>(); fa.pcache = c->pcache.as<uint32_t>(); fa.hef_dbg = nullptr; fa.stats = stats + 8;
-				  k_fill<false><<<nblk(k, BT2_FILL_WARPS * 2), BT2_FILL_WARPS * 32, 0, st>>>(c->dP, fa); LAUNCH(c); c->ctr.n_fill++; }
+				  FillArgs fa; fa.probs = probs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.cells = c->cells.as<uint8_t>(); fa.cell_stride = c->cellStride;
+				  fa.pcache = c->pcache.as<uint32_t>(); fa.hef_dbg = nullptr; fa.stats = stats + 8; fa.error = c->poolerr.as<uint32_t>(); fa.exact = c->hp.exactBestLtMinsc;
+				  launch_fill(c->fillK, false, c->dP, fa, st); LAUNCH(c); c->ctr.n_fill++; }
 				{ Phase ph(c, PH_BT);
 				  zero_counter(c, C_BTTASK);
 				  const uint32_t btBlocks = std::min<uint32_t>(nblk(k, BT2_BT_THREADS), (uint32_t)btMaxBlocks);
@@ -363,7 +394,7 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 	const volatile unsigned long long* hs = c->hbox->stats;
 	CK(cudaGetLastError());
 	c->ctr.reads += n; c->ctr.seeds_searched += hs[0]; c->ctr.lf_steps_search += hs[1]; c->ctr.lf_steps_extend += hs[2]; c->ctr.lf_sides_touched += hs[3]; c->ctr.ext_text_steps += hs[4]; c->ctr.sa_probes += hs[5];
-	c->ctr.dp_problems += hs[8]; c->ctr.dp_cells += hs[9];
+	c->ctr.dp_problems += hs[8]; c->ctr.dp_cells += hs[9]; c->ctr.dp_cells_computed += hs[10];
 	c->ctr.sa_rows_resolved += hs[16]; c->ctr.lf_steps_resolve += hs[17]; c->ctr.bt_attempts += hs[18]; c->ctr.bt_steps += hs[19]; c->ctr.alns_reported += hs[20];
 	flush_spans(c);
 }
@@ -464,13 +495,16 @@ void do_align_pipelined(bt2gpu_ctx* c, const bt2gpu_reads* in, bt2gpu_results* o
 // No counterpart in the reference; added for callers that cannot call cudaMalloc
 // (code under CUDA graph capture, tight serving loops).  The scratch k_fill needs -- the Problem / ReadState records it reads
 // and the cell flags it writes -- lives in a file-scope device array that every GPU loading this library holds until exit.
+#define BT2_NA_K 16                                                     // every band fits (32 x 16 diagonals >= 160 + 199)
+#define BT2_NA_STRIDE ((size_t)((BT2GPU_MAX_ROWS + BT2_SKEW) * BT2_LANES * BT2_NA_K))   // fill_cell_bytes(160, 16)
 struct NoAllocScratch {
 	unsigned long long stats[32];
+	uint32_t  error[4];
 	Problem   probs[BT2GPU_NOALLOC_MAX_PROBLEMS];
 	ReadState states[BT2GPU_NOALLOC_MAX_PROBLEMS];
-	alignas(256) uint8_t cells[(size_t)BT2GPU_NOALLOC_MAX_PROBLEMS * BT2_CELL_BYTES];
+	alignas(256) uint8_t cells[(size_t)BT2GPU_NOALLOC_MAX_PROBLEMS * BT2_NA_STRIDE];
 };
-// (a byte array: no dynamic initialisation of device objects; ~7.7 MB)
+// (a byte array: no dynamic initialisation of device objects; ~11.6 MB)
 static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
 
 // builds the records k_fill reads from the caller's arrays; a problem with a size out of range is switched off (read = NIL)
@@ -478,17 +512,18 @@ __global__ void k_na_setup(NoAllocScratch* sc, uint32_t nprob, const uint32_t* s
                            const uint32_t* rf_off, const uint8_t* rf, const int32_t* minsc) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if(i < 32) sc->stats[i] = 0;   // the array keeps the previous call's contents
+	if(i < 4) sc->error[i] = 0;
 	if(i >= nprob) return;
 	Problem& pb = sc->probs[i];
 	const uint32_t r = rows[i], c = cols[i];
 	const bool ok = r >= 1 && r <= BT2GPU_MAX_ROWS && c >= 1 && c < BT2GPU_MAX_COLS;
-	pb.read = ok ? i : BT2_NIL; pb.rows = (uint16_t)r; pb.cols = (uint16_t)c; pb.fw = 1; pb.R = (uint8_t)fill_R(ok ? r : 1); pb.pad[0] = pb.pad[1] = 0;
+	pb.read = ok ? i : BT2_NIL; pb.rows = (uint16_t)r; pb.cols = (uint16_t)c; pb.fw = 1; pb.lay = 0; pb.d0 = 0;
 	pb.minsc = minsc[i]; pb.refl = 0; pb.tidx = 0; pb.triml = pb.corel = pb.corer = 0; pb.lrmax = -1; pb.ncand = 0;
 	if(ok) for(uint32_t k = 0; k <= c; k++) pb.rf[k] = rf[rf_off[i] + k];
 	ReadState& rs = sc->states[i];
 	rs.seq_off = seq_off[i]; rs.rdlen = (uint16_t)r;
 }
-// one block per problem: dense flags (row-major rows x cols) out of the cell layout, candidates, counts
+// one block per problem: dense flags (row-major rows x cols; 0x80 outside the band) out of the cell layout, candidates, counts
 __global__ void k_na_export(const NoAllocScratch* sc, const uint64_t* flags_off, uint8_t* flags, uint16_t* cand, uint32_t* ncand, int32_t* lrmax) {
 	const uint32_t i = blockIdx.x;
 	const Problem& pb = sc->probs[i];
@@ -496,10 +531,13 @@ __global__ void k_na_export(const NoAllocScratch* sc, const uint64_t* flags_off,
 	if(threadIdx.x == 0) { ncand[i] = ok ? pb.ncand : 0u; lrmax[i] = ok ? pb.lrmax : -1; }
 	if(!ok) return;
 	for(uint32_t k = threadIdx.x; k < pb.ncand; k += blockDim.x) cand[256u * i + k] = pb.cand[k];
-	const uint32_t rows = pb.rows, cols = pb.cols, R = pb.R, shift = fill_shift(rows, R);
-	const uint8_t* cells = sc->cells + (size_t)i * BT2_CELL_BYTES;
+	const uint32_t rows = pb.rows, cols = pb.cols, K = prob_K(pb), y = prob_y(pb); const int d0 = pb.d0;
+	const uint8_t* cells = sc->cells + (size_t)i * BT2_NA_STRIDE;
 	uint8_t* out = flags + flags_off[i];
-	for(uint32_t k = threadIdx.x; k < rows * cols; k += blockDim.x) out[k] = cells[cell_index(k / cols + shift, k % cols, R)];
+	for(uint32_t k = threadIdx.x; k < rows * cols; k += blockDim.x) {
+		const uint32_t r = k / cols, c = k % cols; const int dd = (int)c - (int)r - d0;
+		out[k] = (dd >= 0 && dd < (int)(BT2_LANES * K)) ? cells[cell_index(r, c, d0, K, y)] : (uint8_t)0x80;
+	}
 }
 
 // device address of the scratch array, resolved once per device with that device current: in host code the array's name is a
@@ -627,7 +665,8 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		// ---- problem slots
 		const char* es = getenv("BT2GPU_SLOTS"); const char* eb = getenv("BT2GPU_BATCH");
 		size_t freeB = 0, totB = 0; CK(cudaMemGetInfo(&freeB, &totB));
-		const size_t perSlot = sizeof(Problem) + (size_t)BT2_CELL_BYTES + (size_t)BT2_PC_WORDS * 4;
+		const size_t slotCells = fill_cell_bytes(BT2GPU_MAX_ROWS, 4);   // K = 4 holds every band of the default scoring scheme; a batch that needs more gets fewer slots
+		const size_t perSlot = sizeof(Problem) + slotCells + (size_t)BT2_PC_WORDS * 4;
 		uint32_t slots = es ? (uint32_t)atoi(es) : 262144u;
 		const size_t budget = (freeB / 20) * 9;
 		if((size_t)slots * perSlot > budget) slots = (uint32_t)(budget / perSlot);
@@ -636,7 +675,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		c->maxBatch = eb ? (uint32_t)atoi(eb) : (1u << 20);
 		if(c->maxBatch < 1) c->maxBatch = 1;
 		{ const char* ep = getenv("BT2GPU_PIPE"); c->pipeChunk = ep ? (uint32_t)std::max(1, atoi(ep)) : 262144u; }
-		c->probs.ensure((size_t)slots * sizeof(Problem)); c->cells.ensure((size_t)slots * BT2_CELL_BYTES);
+		c->probs.ensure((size_t)slots * sizeof(Problem)); c->cells.ensure((size_t)slots * slotCells);
 		c->pcache.ensure((size_t)slots * BT2_PC_WORDS * 4);
 		c->counters.ensure(C_N * 4); c->stats.ensure(32 * 8); c->pooltops.ensure(16); c->poolerr.ensure(4);
 		{ void* hb = nullptr; CK(cudaHostAlloc(&hb, sizeof(HostBox), cudaHostAllocMapped)); memset(hb, 0, sizeof(HostBox));
@@ -677,47 +716,66 @@ int bt2gpu_align_batch(bt2gpu_ctx* ctx, const bt2gpu_reads* in, bt2gpu_results* 
 
 int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, const uint8_t* seq, const uint8_t* qual,
                      const uint16_t* rows, const uint16_t* cols, const uint32_t* rf_off, const uint8_t* rf, const int32_t* minsc,
-                     const uint64_t* hef_off, uint8_t* H, uint8_t* E, uint8_t* F, uint8_t* flags, uint16_t* cand, uint32_t* ncand, int32_t* lrmax) {
+                     const uint64_t* hef_off, uint8_t* H, uint8_t* E, uint8_t* F, uint8_t* flags, uint16_t* cand, uint32_t* ncand, int32_t* lrmax,
+                     int32_t mode, int32_t* band) {
 	API_GUARD({
-		if(nprob > ctx->nslots || nprob > 4096) throw std::string("bt2gpu_test_fill: more problems than DP slots (or than 4096)");
+		if(nprob > 4096) throw std::string("bt2gpu_test_fill: more than 4096 problems");
+		const bool exact = mode == 0;
 		std::vector<ReadState> hs(nprob); std::vector<Problem> hp(nprob);
-		uint64_t nb = 0;
+		uint64_t nb = 0; uint32_t K = 2, maxRows = 1;
 		for(uint32_t i = 0; i < nprob; i++) {
 			if(rows[i] < 1 || rows[i] > BT2GPU_MAX_ROWS || cols[i] < 1 || cols[i] >= BT2GPU_MAX_COLS) throw std::string("bt2gpu_test_fill: bad problem size");
 			memset(&hs[i], 0, sizeof(ReadState)); hs[i].seq_off = seq_off[i]; hs[i].rdlen = rows[i];
 			memset(&hp[i], 0, sizeof(Problem));
-			hp[i].read = i; hp[i].rows = rows[i]; hp[i].cols = cols[i]; hp[i].fw = 1; hp[i].R = (uint8_t)fill_R(rows[i]); hp[i].minsc = minsc[i];
+			hp[i].read = i; hp[i].rows = rows[i]; hp[i].cols = cols[i]; hp[i].fw = 1; hp[i].minsc = minsc[i];
 			memcpy(hp[i].rf, rf + rf_off[i], (size_t)cols[i] + 1);
 			nb = std::max<uint64_t>(nb, (uint64_t)seq_off[i] + rows[i]);
+			int dlo, dhi; fill_band(ctx->P, rows[i], cols[i], minsc[i], exact, dlo, dhi);
+			K = std::max(K, fill_K_for(dhi - dlo + 1)); maxRows = std::max<uint32_t>(maxRows, rows[i]);
 		}
-		ctx->in[0].seq.ensure(nb + 16); ctx->in[0].qual.ensure(nb + 16); ctx->states.ensure((size_t)nprob * sizeof(ReadState));
+		if(mode == 2) K = BT2_NA_K;   // the layout bt2gpu_fill_noalloc uses
+		const size_t stride = fill_cell_bytes(maxRows, K);
+		DBuf cells, probs, states, dbg;
+		struct Rel { DBuf* b[4]; ~Rel() { for(DBuf* x : b) x->release(); } } rel{{&cells, &probs, &states, &dbg}};
+		const uint32_t np4 = (nprob + 3u) & ~3u;
+		cells.ensure((size_t)np4 * stride); probs.ensure((size_t)np4 * sizeof(Problem)); states.ensure((size_t)np4 * sizeof(ReadState));
+		if(exact) dbg.ensure((size_t)np4 * BT2_HEF_WORDS * 4);
+		ctx->in[0].seq.ensure(nb + 16); ctx->in[0].qual.ensure(nb + 16);
 		cudaStream_t st = ctx->stream;
 		CK(cudaMemcpyAsync(ctx->in[0].seq.p, seq, nb, cudaMemcpyHostToDevice, st)); CK(cudaMemcpyAsync(ctx->in[0].qual.p, qual, nb, cudaMemcpyHostToDevice, st));
-		CK(cudaMemcpyAsync(ctx->states.p, hs.data(), (size_t)nprob * sizeof(ReadState), cudaMemcpyHostToDevice, st));
-		CK(cudaMemcpyAsync(ctx->probs.p, hp.data(), (size_t)nprob * sizeof(Problem), cudaMemcpyHostToDevice, st));
-		CK(cudaMemsetAsync(ctx->stats.p, 0, 32 * 8, st));
-		FillArgs fa; fa.probs = ctx->probs.as<Problem>(); fa.nprob = nprob; fa.states = ctx->states.as<ReadState>(); fa.seq = ctx->in[0].seq.as<uint8_t>();
-		DBuf dbg; dbg.ensure((size_t)nprob * BT2_HEF_WORDS * 4);
-		fa.qual = ctx->in[0].qual.as<uint8_t>(); fa.cells = ctx->cells.as<uint8_t>(); fa.pcache = nullptr; fa.hef_dbg = dbg.as<uint32_t>(); fa.stats = ctx->stats.as<unsigned long long>() + 8;
-		k_fill<true><<<nblk(nprob, BT2_FILL_WARPS * 2), BT2_FILL_WARPS * 32, 0, st>>>(ctx->dP, fa);
-		CK(cudaMemcpyAsync(hp.data(), ctx->probs.p, (size_t)nprob * sizeof(Problem), cudaMemcpyDeviceToHost, st));
-		std::vector<uint32_t> w(BT2_HEF_WORDS); std::vector<uint8_t> wc(BT2_CELL_BYTES);
+		CK(cudaMemcpyAsync(states.p, hs.data(), (size_t)nprob * sizeof(ReadState), cudaMemcpyHostToDevice, st));
+		CK(cudaMemcpyAsync(probs.p, hp.data(), (size_t)nprob * sizeof(Problem), cudaMemcpyHostToDevice, st));
+		CK(cudaMemsetAsync(ctx->stats.p, 0, 32 * 8, st)); CK(cudaMemsetAsync(ctx->poolerr.p, 0, 4, st));
+		CK(cudaMemsetAsync(cells.p, 0x80, (size_t)np4 * stride, st));
+		FillArgs fa; fa.probs = probs.as<Problem>(); fa.nprob = nprob; fa.states = states.as<ReadState>(); fa.seq = ctx->in[0].seq.as<uint8_t>();
+		fa.qual = ctx->in[0].qual.as<uint8_t>(); fa.cells = cells.as<uint8_t>(); fa.cell_stride = stride; fa.pcache = nullptr; fa.hef_dbg = exact ? dbg.as<uint32_t>() : nullptr;
+		fa.stats = ctx->stats.as<unsigned long long>() + 8; fa.error = ctx->poolerr.as<uint32_t>(); fa.exact = exact ? 1 : 0;
+		launch_fill(K, exact, ctx->dP, fa, st);
+		CK(cudaMemcpyAsync(hp.data(), probs.p, (size_t)nprob * sizeof(Problem), cudaMemcpyDeviceToHost, st));
+		uint32_t ferr = 0; CK(cudaMemcpyAsync(&ferr, ctx->poolerr.p, 4, cudaMemcpyDeviceToHost, st));
+		std::vector<uint32_t> w(exact ? BT2_HEF_WORDS : 1); std::vector<uint8_t> wc(stride);
 		for(uint32_t i = 0; i < nprob; i++) {
-			CK(cudaMemcpyAsync(w.data(), dbg.as<uint32_t>() + (size_t)i * BT2_HEF_WORDS, (size_t)BT2_HEF_WORDS * 4, cudaMemcpyDeviceToHost, st));
-			CK(cudaMemcpyAsync(wc.data(), ctx->cells.as<uint8_t>() + (size_t)i * BT2_CELL_BYTES, (size_t)BT2_CELL_BYTES, cudaMemcpyDeviceToHost, st));
+			if(exact) CK(cudaMemcpyAsync(w.data(), dbg.as<uint32_t>() + (size_t)i * BT2_HEF_WORDS, (size_t)BT2_HEF_WORDS * 4, cudaMemcpyDeviceToHost, st));
+			CK(cudaMemcpyAsync(wc.data(), cells.as<uint8_t>() + (size_t)i * stride, stride, cudaMemcpyDeviceToHost, st));
 			CK(cudaStreamSynchronize(st));
+			if(ferr) throw std::string("bt2gpu_test_fill: a band did not fit the fill's lanes");
+			const uint32_t pk = prob_K(hp[i]), py = prob_y(hp[i]); const int d0 = hp[i].d0;
+			if(pk != K) throw std::string("bt2gpu_test_fill: the kernel did not record its layout");
+			if(band) { band[2 * i] = d0; band[2 * i + 1] = (int32_t)(BT2_LANES * pk); }
 			for(uint32_t r = 0; r < rows[i]; r++) for(uint32_t cc = 0; cc < cols[i]; cc++) {
-				const uint32_t rp = r + fill_shift(rows[i], hp[i].R);
-				const uint32_t x = w[hef_index(rp, cc, hp[i].R)];
 				const uint64_t o = hef_off[i] + (uint64_t)r * cols[i] + cc;
-				H[o] = (uint8_t)x; E[o] = (uint8_t)(x >> 8); F[o] = (uint8_t)(x >> 16);
-				flags[o] = wc[cell_index(rp, cc, hp[i].R)];
+				const int dd = (int)cc - (int)r - d0;
+				const bool in = dd >= 0 && dd < (int)(BT2_LANES * pk);
+				if(exact) {
+					const uint32_t x = in ? w[(size_t)r * (BT2_LANES * pk) + dd] : 0u;
+					H[o] = (uint8_t)x; E[o] = (uint8_t)(x >> 8); F[o] = (uint8_t)(x >> 16);
+				}
+				flags[o] = in ? wc[cell_index(r, cc, d0, pk, py)] : (uint8_t)0x80;
 			}
 			ncand[i] = hp[i].ncand; lrmax[i] = hp[i].lrmax;
 			for(uint32_t k = 0; k < hp[i].ncand && k < 256; k++) cand[256 * (size_t)i + k] = hp[i].cand[k];
 		}
 		CK(cudaGetLastError());
-		cudaFree(dbg.p);
 	})
 }
 
@@ -739,9 +797,9 @@ int bt2gpu_fill_noalloc(bt2gpu_ctx* ctx, void* stream, uint32_t nprob, const uin
 		NoAllocScratch* sc = noalloc_scratch(ctx->device);
 		cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
 		k_na_setup<<<nblk(std::max(nprob, 32u), 128), 128, 0, st>>>(sc, nprob, d_seq_off, d_rows, d_cols, d_rf_off, d_rf, d_minsc);
-		FillArgs fa; fa.probs = sc->probs; fa.nprob = nprob; fa.states = sc->states; fa.seq = d_seq; fa.qual = d_qual; fa.cells = sc->cells;
-		fa.pcache = nullptr; fa.hef_dbg = nullptr; fa.stats = sc->stats;
-		k_fill<false><<<nblk(nprob, BT2_FILL_WARPS * 2), BT2_FILL_WARPS * 32, 0, st>>>(ctx->dP, fa);
+		FillArgs fa; fa.probs = sc->probs; fa.nprob = nprob; fa.states = sc->states; fa.seq = d_seq; fa.qual = d_qual; fa.cells = sc->cells; fa.cell_stride = BT2_NA_STRIDE;
+		fa.pcache = nullptr; fa.hef_dbg = nullptr; fa.stats = sc->stats; fa.error = sc->error; fa.exact = 0;
+		launch_fill(BT2_NA_K, false, ctx->dP, fa, st);   // the production kernel, banded per problem; K = 16 holds any band
 		k_na_export<<<nprob, 256, 0, st>>>(sc, d_flags_off, d_flags, d_cand, d_ncand, d_lrmax);
 		CK(cudaPeekAtLastError());
 	})

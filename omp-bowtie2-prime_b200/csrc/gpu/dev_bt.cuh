@@ -122,7 +122,8 @@ struct BtCtx {
 	DevParams P;
 	Pools pools;
 	ReadState* states; const Problem* probs;
-	uint8_t* cells;          // [nslots * BT2_CELL_BYTES] CF_* flag bytes (cell_index); bit 7 = visited, set here
+	uint8_t* cells;          // [nslots * cell_stride] CF_* flag bytes (cell_index); bit 7 = visited, set here
+	size_t cell_stride;      // bytes of cell flags per problem slot (fill_cell_bytes of the batch's longest read and its K)
 	const uint32_t* pcache;  // [nslots * BT2_PC_WORDS]
 	uint32_t* scratch;       // [nreads * BT2_SCRATCH_EDITS] per-read edit scratch
 	const uint8_t* seq; const uint8_t* qual; // batch arrays
@@ -142,8 +143,9 @@ struct BtMachine {
 	uint32_t ctag0, ctag1, ccur;
 	// ---- cached per problem
 	uint8_t* cellp; uint32_t* scr;    // the problem's cells, the read's edit scratch
-	int rows, R, dlo;                 // core diagonals: dlo <= col-row < dlo + dspan
-	uint32_t dspan, svLast;           // fill layout (dev_common.cuh): strip of the last row
+	int rows, dlo;                    // core diagonals: dlo <= col-row < dlo + dspan
+	uint32_t dspan;
+	int d0; uint32_t lgK, yy;         // fill layout (dev_common.cuh)
 	uint32_t ncand;
 	Rng rnd; uint32_t hw, nsteps;     // nsteps: backtrace steps in the low 24 bits, attempts in the high 8 (<= 208 candidates)
 	// ---- nextAlignment state
@@ -151,7 +153,7 @@ struct BtMachine {
 	uint32_t cural, reseed;
 	// ---- backtrace state (one attempt)
 	int row, col, ct, score;
-	uint32_t cidx, sv, sk;            // cell_index(row + shift, col) and the strip / row within the strip it lies in
+	uint32_t cidx;                    // cell_index(row, col)
 	uint32_t ned, nbranch;
 	bool coreHit;
 
@@ -162,26 +164,21 @@ struct BtMachine {
 		const ReadState& r = rs(cx);
 		ReadView v; v.seq = cx.seq + r.seq_off; v.qual = cx.qual + r.seq_off; v.rdlen = r.rdlen; v.fw = pb(cx).fw != 0; return v;
 	}
-	BT2_HD uint32_t lg2() const { return R > 4 ? 1u : 2u; }   // log2(units per 16-byte chunk)
-	// cell_index_vk without the branch on R
-	BT2_HD uint32_t cell_at(uint32_t v, uint32_t k, uint32_t c) const {
-		const uint32_t t = c + v + (uint32_t)R - 1u - k, lg = lg2();
-		return ((((t >> lg) << 5) + v) << 4) + ((t & ((1u << lg) - 1u)) << (4u - lg)) + k;
+	// cell_index() with the problem's layout constants in registers
+	BT2_HD uint32_t cell_at(int r, int c) const {
+		const uint32_t dd = (uint32_t)(c - r - d0), v = dd >> lgK, j = dd & ((1u << lgK) - 1u);
+		const uint32_t i = (uint32_t)r + ((v + yy) >> 1);
+		return ((((i >> (4u - lgK)) << 5) + v) << 4) + ((i & ((16u >> lgK) - 1u)) << lgK) + j;
 	}
-	// the next candidate's start cell (last row: row R-1 of strip svLast), or the end of the candidate loop
+	// the next candidate's start cell (last row), or the end of the candidate loop
 	BT2_HD void seek_cand() {
 		if(cural >= ncand) { phase = BP_DONE; return; }
 		row = rows - 1; col = (int)(cand_at(cural) & 255u);
-		sv = svLast; sk = (uint32_t)R - 1u;
-		cidx = cell_at(sv, sk, (uint32_t)col);
+		cidx = cell_at(row, col);
 		ct = CT_H;   // (the chunk prediction of the start cell reads it)
 		phase = BP_CAND;
 	}
-	BT2_HD void row_up() {   // row-- : the strip / row-in-strip pair follows without a division
-		row--;
-		if(sk == 0u) { sk = (uint32_t)R - 1u; sv--; } else sk--;
-	}
-	BT2_HD void relocate() { cidx = cell_at(sv, sk, (uint32_t)col); }
+	BT2_HD void relocate() { cidx = cell_at(row, col); }
 	BT2_HD void push_edit(uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scr[ned] = x; ned++; }
 
 	// candidate i of the problem: group i / 8 sits in buffer 2 + (i / 8) % 2
@@ -212,26 +209,26 @@ struct BtMachine {
 		asm volatile("cp.async.wait_all;" ::: "memory");
 #endif
 	}
-	// chunk the walk most likely enters after the one holding (row, col), assuming it keeps its direction: up the column
-	// in a reference-gap run (F), along the row in a read-gap run (E), else up the diagonal
+	// chunk the walk enters next if it keeps its direction: up the column in a reference-gap run (F), along the row in a
+	// read-gap run (E), else up the diagonal.  Inside a chunk (16 / K iterations x K diagonals of one lane) a diagonal move
+	// keeps j and goes one iteration back, a column move goes to j + 1 one iteration back, a row move to j - 1.
 	BT2_HD uint32_t predict_chunk() const {
-		const uint32_t t = (uint32_t)col + sv + (uint32_t)R - 1u - sk, per = 1u << lg2(), tm = t & (per - 1u), ch = cidx >> 4;
-		// same strip: a reference-gap run reaches unit t + (per - tm) (row - j lies in unit t + j), a read-gap run unit t - tm - 1
-		if(ct == CT_F && sk >= per - tm) return ch + BT2_STRIPS < BT2_CELL_BYTES / 16u ? ch + BT2_STRIPS : BT2_NIL;
-		if(ct == CT_E) return ((uint32_t)col > tm && ch >= BT2_STRIPS) ? ch - BT2_STRIPS : BT2_NIL;
-		// else the strip above: in this column (reference-gap run) or on this diagonal; its row R-1
-		const int c2 = ct == CT_F ? col : col - (int)sk - 1;
-		if(sv == 0u || c2 < 0) return BT2_NIL;
-		return cell_at(sv - 1u, (uint32_t)R - 1u, (uint32_t)c2) >> 4;
+		const uint32_t K = 1u << lgK, j = cidx & (K - 1u), iw = (cidx & 15u) >> lgK;   // position inside the chunk
+		int r2 = row, c2 = col;
+		if(ct == CT_E) c2 -= (int)j + 1;                                             // leaves through the chunk's left edge
+		else if(ct == CT_F) { const uint32_t n = iw + 1u < K - j ? iw + 1u : K - j; r2 -= (int)n; }   // through its top or right edge
+		else { r2 -= (int)iw + 1; c2 -= (int)iw + 1; }
+		if(r2 < 0 || c2 < 0 || (uint32_t)(c2 - r2 - d0) >= (K << 5)) return BT2_NIL;
+		return cell_at(r2, c2) >> 4;
 	}
 
 	// SwDriver::extendSeeds right after swa.align(): counters, then either the candidate loop or done
 	BT2_HD void begin(const BtCtx& cx) {
 		const DevParams& Pr = cx.P; const Problem& p = pb(cx); ReadState& r = rs(cx);
-		rows = p.rows; R = p.R; ncand = p.ncand;
-		svLast = ((uint32_t)p.rows + fill_shift((uint32_t)p.rows, (uint32_t)p.R)) / (uint32_t)p.R - 1u;
+		rows = p.rows; ncand = p.ncand;
+		d0 = p.d0; lgK = fill_lgK(prob_K(p)); yy = prob_y(p);
 		dlo = (p.corel > 0 ? p.corel : 0) - p.triml; { const int dhi = p.corer - p.triml; dspan = dhi >= dlo ? (uint32_t)(dhi - dlo) + 1u : 0u; }
-		cellp = cx.cells + (size_t)slot * BT2_CELL_BYTES; scr = cx.scratch + (size_t)read * BT2_SCRATCH_EDITS;
+		cellp = cx.cells + (size_t)slot * cx.cell_stride; scr = cx.scratch + (size_t)read * BT2_SCRATCH_EDITS;
 		chunk_wait();   // a chunk copy of the previous problem may still be on its way into this lane's buffers
 		nsteps = 0; ctag0 = BT2_NIL; ctag1 = BT2_NIL; ccur = 0;
 		rnd = r.rnd; hw = r.scr_hw;
@@ -335,7 +332,7 @@ struct BtMachine {
 		}
 		score -= cx.pen[sel];
 		ct = sel == 2u ? CT_F : (sel == 0u ? CT_E : CT_H);
-		if(sel >= 2u) row_up();
+		if(sel >= 2u) row--;
 		if(!isRef) col--;
 		relocate();
 	}

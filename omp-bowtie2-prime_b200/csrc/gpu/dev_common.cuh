@@ -299,7 +299,8 @@ struct ReadState {
 struct alignas(16) Problem {
 	uint32_t read;
 	uint16_t rows, cols;       // rdlen, rflen (# DP columns)
-	uint8_t  fw, R, pad[2];    // R = rows per virtual lane in the fill
+	uint8_t  fw, lay;          // lay = K | y << 7: the fill's layout (below): K diagonals per lane, y = which of the warp's two interleaved pairs
+	int16_t  d0;               // leftmost diagonal (col - row) of the band the fill computed
 	int32_t  minsc;            // SwAligner::minsc_ (clamped to >= -254 for u8)
 	int64_t  refl;             // rect.refl
 	uint32_t tidx;
@@ -310,6 +311,8 @@ struct alignas(16) Problem {
 	uint16_t cand[BT2GPU_MAX_COLS + 8]; // sorted best-first: (rawH << 8) | col; at a 16-byte boundary (read in groups of 8 by the backtrace)
 	uint8_t  rf[BT2GPU_MAX_COLS + 8];   // reference masks for columns 0..cols (cols+1 fetched)
 };
+BT2_HD uint32_t prob_K(const Problem& p) { return p.lay & 0x7fu; }
+BT2_HD uint32_t prob_y(const Problem& p) { return p.lay >> 7; }
 static_assert(offsetof(Problem, cand) % 16 == 0 && sizeof(Problem) % 16 == 0, "Problem::cand is copied in 16-byte groups");
 
 // What the fill leaves per DP cell for the backtrace: one byte of "not equal" flags, i.e. the
@@ -326,43 +329,60 @@ static_assert(offsetof(Problem, cand) % 16 == 0 && sizeof(Problem) % 16 == 0, "P
 // E/F flags of rows inside the gap barrier are unspecified: no backtrace can be in E or F state
 // there (E/F are 0 in those rows and every cell on a backtrace path has a raw score >= 1).
 enum { CF_D = 1, CF_HE = 2, CF_HF = 4, CF_EO = 8, CF_EX = 16, CF_FO = 32, CF_FX = 64, CF_VIS = 128 };
-// Layout: rows are cut into BT2_STRIPS = 32 strips of R = ceil(rdlen / 32) <= 5 rows (the fill's lanes), aligned to the END of
-// the read: `shift` = nv * R - rdlen virtual rows precede row 0 (nv = ceil(rdlen / R) strips in use), so that the last row is row
-// R-1 of strip nv-1; all indices below take the shifted row rp = row + shift.  The R cells of a strip that lie on one diagonal
-// form a unit of U = 4 (R <= 4) or 8 (R = 5) bytes (byte k = rp % R).  Strip v works on column c at step c + v of the fill's
-// sweep and completes the unit that holds cell (v * R + k, c) at step t = c + v + R - 1 - k; units are stored by completion
-// step, 16 / U consecutive steps to a 16-byte chunk, the chunks of the 32 strips adjacent:
-//   byte index = ((t / per) * 32 + v) * 16 + (t % per) * U + k,  per = 16 / U.
-// The fill therefore writes whole 512-byte rows (one 16-byte store per lane and problem every `per` steps, all lanes in the same
-// row); a backtrace that follows a diagonal stays in one unit for R cells and moves per / (R + 1) rows up per strip crossed.
-// A fill warp works on two problems at once and uses the larger R of the two for both; Problem::R is what it used.
+// Which cells are filled.  A backtrace only ever stands on cells that lie on a full path (row 0 .. last row inside the window)
+// scoring >= minsc: it starts from a last-row cell with H >= minsc and every move follows a score equality, so the value at
+// the cell it stands on plus the penalties already walked is that candidate's score.  A path scoring >= minsc holds at most
+// g = fill_gap_bound() gap positions, starts in a column >= 0 and ends in a column < cols, hence never leaves the band of
+// diagonals  -g <= col - row <= cols - rows + g.  Values outside the band are taken as 0 (the saturation floor): every value inside
+// is then <= the full rectangle's and equal to it wherever a full path scoring >= minsc passes, and so is every comparison a
+// backtrace reads (an equality that holds in the full rectangle continues such a path; one that fails compares with a value that
+// can only have become smaller).  Candidates, alignments, edits, the visited marks and the random draws are those of the full
+// rectangle; the one observable difference is the best score of a window WITHOUT any candidate (prm.bestLtMinscMate1), which
+// becomes a lower bound -- bt2gpu_params.exactBestLtMinsc fills the whole rectangle instead.
+//
+// Layout.  The fill's lane v owns the K consecutive diagonals d0 + v K .. d0 + v K + K-1 and sweeps the rows; lane v works on
+// row r at iteration i = r + ((v + y) >> 1) (two steps per row and lane: the cell above-right comes from lane v+1, the cell to
+// the left from lane v-1; a warp interleaves two pairs of problems, y = 0 / 1, on the alternate steps).  The K cells of a lane
+// and iteration form a unit of K bytes, 16 / K consecutive iterations a 16-byte chunk, the chunks of the 32 lanes are adjacent:
+//   dd = col - row - d0,  v = dd / K,  j = dd % K,  i = row + ((v + y) >> 1),  per = 16 / K
+//   byte index = ((i / per) * 32 + v) * 16 + (i % per) * K + j
+// The fill writes whole 512-byte rows (every lane of the warp stores its chunk of the same iterations at the same time); a
+// backtrace that follows a diagonal stays with one lane and crosses into a new chunk every 16 / K rows.
 #define BT2_PK_WORDS 12   // 2-bit packed read: 16 bases per word (+ words a 32-base window may touch)
 #define BT2_NM_WORDS 6    // its N mask: 32 bases per word
-#define BT2_STRIPS 32
-#define BT2_MAX_R  ((BT2GPU_MAX_ROWS + BT2_STRIPS - 1) / BT2_STRIPS)
-#define BT2_CELL_GROUPS ((BT2GPU_MAX_COLS + BT2_STRIPS + BT2_MAX_R + 3) / 2 + 1)  // t / per < this (per >= 2)
-BT2_HD uint32_t fill_R(uint32_t rows) { return rows ? (rows + BT2_STRIPS - 1) / BT2_STRIPS : 1u; }
-BT2_HD uint32_t fill_shift(uint32_t rows, uint32_t R) { return ((rows + R - 1) / R) * R - rows; }
-BT2_HD uint32_t strip_of(uint32_t rp, uint32_t R) { // rp / R for R <= 5, rp < 256
-	return (R == 1) ? rp : (R == 2 ? (rp >> 1) : (R == 3 ? ((rp * 171u) >> 9) : (R == 4 ? (rp >> 2) : ((rp * 205u) >> 10))));
+#define BT2_LANES 32
+#define BT2_SKEW  (BT2_LANES / 2)           // iterations the last lane lags behind the first
+#define BT2_KMAX  16
+BT2_HD uint32_t fill_lgK(uint32_t K) { return K == 2 ? 1u : (K == 4 ? 2u : (K == 8 ? 3u : 4u)); }
+// iterations of the sweep / bytes of cell flags of one problem slot
+BT2_HD uint32_t fill_iters(uint32_t rows, uint32_t K) { const uint32_t per = 16u / K; return ((rows + BT2_SKEW + per - 1u) / per) * per; }
+BT2_HD size_t fill_cell_bytes(uint32_t rows, uint32_t K) { return (size_t)(fill_iters(rows, K) / (16u / K)) * BT2_LANES * 16u; }
+BT2_HD uint32_t cell_index(uint32_t row, uint32_t col, int d0, uint32_t K, uint32_t y) {
+	const uint32_t lg = fill_lgK(K), dd = (uint32_t)((int)col - (int)row - d0), v = dd >> lg, j = dd & (K - 1u);
+	const uint32_t i = row + ((v + y) >> 1);
+	return ((((i >> (4u - lg)) << 5) + v) << 4) + ((i & ((16u >> lg) - 1u)) << lg) + j;
 }
-BT2_HD uint32_t cell_index_vk(uint32_t v, uint32_t k, uint32_t c, uint32_t R) {
-	const uint32_t t = c + v + R - 1u - k;
-	if(R > 4) return ((t >> 1) * BT2_STRIPS + v) * 16u + (t & 1u) * 8u + k;
-	return ((t >> 2) * BT2_STRIPS + v) * 16u + (t & 3u) * 4u + k;
+// most gap positions a path scoring >= minsc can hold (perfect score 0: end-to-end, no match bonus)
+BT2_HD int fill_gap_bound(const DevParams& P, int minsc) {
+	const int omin = P.rdGapOpen < P.rfGapOpen ? P.rdGapOpen : P.rfGapOpen;
+	int emin = P.rdGapExt < P.rfGapExt ? P.rdGapExt : P.rfGapExt; if(omin < emin) emin = omin;
+	const int budget = -minsc;
+	if(budget < omin) return 0;
+	if(emin <= 0) return 1 << 20;
+	return 1 + (budget - omin) / emin;
 }
-BT2_HD uint32_t cell_index(uint32_t rp, uint32_t c, uint32_t R) {
-	const uint32_t v = strip_of(rp, R);
-	return cell_index_vk(v, rp - v * R, c, R);
+// band of diagonals [dlo, dhi] of a rows x cols problem
+BT2_HD void fill_band(const DevParams& P, int rows, int cols, int minsc, bool exact, int& dlo, int& dhi) {
+	dlo = -(rows - 1); dhi = cols - 1;
+	if(exact) return;
+	const int g = fill_gap_bound(P, minsc);
+	if(-g > dlo) dlo = -g;
+	if((cols - rows) + g < dhi) dhi = (cols - rows) + g;
+	if(dhi < dlo) dhi = dlo;       // no path fits the window: nothing can be a candidate, any band will do
 }
-#define BT2_CELL_BYTES (BT2_CELL_GROUPS * BT2_STRIPS * 16)  // per problem slot
-// debug-only H|E<<8|F<<16 words, [strip][step][k] (8 words per step) with step = col + strip (bt2gpu_test_fill)
-#define BT2_HEF_T (BT2GPU_MAX_COLS + BT2_STRIPS + 16)
-BT2_HD uint32_t hef_index(uint32_t rp, uint32_t c, uint32_t R) {
-	const uint32_t v = strip_of(rp, R);
-	return (v * BT2_HEF_T + c + v) * 8u + (rp - v * R);
-}
-#define BT2_HEF_WORDS (BT2_HEF_T * BT2_STRIPS * 8)
+BT2_HD uint32_t fill_K_for(int width) { return width <= 64 ? 2u : (width <= 128 ? 4u : (width <= 256 ? 8u : 16u)); }
+// debug-only H|E<<8|F<<16 words of the fill's test instantiation: [row][dd], dd = col - row - d0 < 32 K (bt2gpu_test_fill)
+#define BT2_HEF_WORDS (BT2GPU_MAX_ROWS * BT2_LANES * BT2_KMAX)
 
 // Per-problem character cache handed from the fill to the backtrace: 4-bit codes, 8 per word.
 //   words [0, BT2_PC_RD)            read characters in the orientation of the problem's strand (0..3, 4 = N)

@@ -55,6 +55,7 @@ BT2_HD void gather_read(const ReadState& rs, const Pools& pools, const uint32_t*
 	eo = edit_base + tot;
 	const uint32_t ns = scratch_count(rs, pools);
 	rr.scratch_off = eo + edit_glob; rr.n_scratch = ns;
+	rr.nExUgs = 0; rr.exhaustive = 0;   // extendSeeds runs no ungapped extension and never sets `exhaustive` (aligner_sw_driver.cpp:371, 302)
 	for(uint32_t i = 0; i < ns; i++) unpack_edit(scratch[i], edits[eo + i]);
 }
 

@@ -111,7 +111,7 @@ BT2_HD int advance(const DevParams& P, const DevIndex& ix, const DevRef& rf, con
 		for(int64_t k = leftNs + (inner > 0 ? inner : 0); k < rflenFull; k++) prob.rf[k] = 16;
 		prob.rows = (uint16_t)rdlen; prob.cols = (uint16_t)(rflenFull - 1);
 		prob.fw = fw ? 1 : 0;
-		prob.R = (uint8_t)fill_R(rdlen);   // the fill may raise it to its pair's (k_fill.cuh)
+		prob.lay = 0; prob.d0 = 0;   // set by the fill (k_fill.cuh)
 		// u8 build: minsc is clamped (aligner_sw.cpp:84).  -DENABLE_I16 build: minsc < -254 selects the 16-bit fill
 		// (aligner_sw.cpp:79), whose score range this library does not have: flagged, the batch call fails.
 		if(P.i16 && rs.minsc < -254) set_error(pools, 16);

@@ -78,6 +78,7 @@ bool parse_options(Options& o, const std::string& args, std::string& err) {
 		else if(t == "--sensitive")      { maxDpStreak = 15; p.nSeedRounds = 2; p.seedLen = 22; o.msIval.init(3, 1.0, DMAX, 1.0, 1.15); }
 		else if(t == "--very-sensitive") { maxDpStreak = 20; p.nSeedRounds = 3; p.seedLen = 20; o.msIval.init(3, 1.0, DMAX, 1.0, 0.50); }
 		else if(t == "--end-to-end") { }
+		else if(t == "--exact-xs") { p.exactBestLtMinsc = 1; }   // (not a reference option) bt2gpu_params.exactBestLtMinsc: fill whole DP rectangles
 		else if(t == "-D") { if(!(a = need(i))) return false; maxDpStreak = atoi(a->c_str()); }
 		else if(t == "-R") { if(!(a = need(i))) return false; p.nSeedRounds = atoi(a->c_str()); }
 		else if(t == "-L") { if(!(a = need(i))) return false; p.seedLen = atoi(a->c_str());

@@ -126,8 +126,11 @@ class Oracle:
             self.ptr = None
 
 
-def compare_results(a, b, check_counters=True, i16path=False):
+def compare_results(a, b, check_counters=True, i16path=False, exact_xs=False):
     """Field-for-field comparison of two Results (oracle vs CUDA). Returns a list of differences.
+    prm.bestLtMinscMate1 (the best score of a read's windows that had NO valid alignment; reaches SAM only as Xs:i / ZT:Z under
+    --sam-opt-config): K_fill computes the band of diagonals valid alignments can lie in, so b's value is a lower bound of a's
+    unless the job runs with --exact-xs (bt2gpu_params.exactBestLtMinsc), where it is compared exactly.
     i16path: prm.bestLtMinscMate1 is left out -- under the 16-bit path the reference stores `raw 16-bit word - 0xff` there
     (aligner_swsse_ee_i16.cpp:640), which needs the unsaturated score of windows that fail; the CUDA fill keeps 8-bit saturation."""
     import numpy as np
@@ -138,8 +141,13 @@ def compare_results(a, b, check_counters=True, i16path=False):
     if check_counters:
         fields += ["nExIters", "nExDps", "nExDpSuccs", "nExDpFails", "nDpFail", "nDpFailStreak", "nDpLastSucc", "nRedundants",
                    "bestLtMinsc", "nonzTot", "numElts", "numRanges", "nSeedsTried", "n_scratch"]
-    if i16path and "bestLtMinsc" in fields:
+    if "bestLtMinsc" in fields and (i16path or not exact_xs):
         fields.remove("bestLtMinsc")
+        if not i16path:
+            lo = np.iinfo(np.int32).min
+            bad = np.nonzero((b.reads["bestLtMinsc"] > a.reads["bestLtMinsc"]) | ((a.reads["bestLtMinsc"] == lo) != (b.reads["bestLtMinsc"] == lo)))[0]
+            if len(bad):
+                diffs.append("reads.bestLtMinsc is not a lower bound for %d reads, first %d: %s vs %s" % (len(bad), bad[0], a.reads["bestLtMinsc"][bad[0]], b.reads["bestLtMinsc"][bad[0]]))
     for f in fields:
         bad = np.nonzero(a.reads[f] != b.reads[f])[0]
         if len(bad):

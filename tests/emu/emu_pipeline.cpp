@@ -19,53 +19,7 @@
 
 using namespace bt2;
 
-static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_t* cells, uint32_t* pcache) {
-	const int rows = pb.rows, cols = pb.cols; const uint32_t R = pb.R, shift = fill_shift((uint32_t)rows, R);
-	auto subs = [](int a, int b) { int v = a - b; return v < 0 ? 0 : v; };
-	std::vector<int> Hprev(rows, 0), Eprev(rows, 0), Fprev(rows, 0), Hcur(rows), Ecur(rows), Fcur(rows), Eleft(rows, 0), Ehere(rows, 0);
-	int lrmax = 0; std::vector<uint16_t> cand;
-	for(int j = 0; j < cols; j++) {
-		const int refm = pb.rf[j];
-		int Fpre = 0;
-		for(int r = 0; r < rows; r++) {
-			const bool gb = (r < P.gapbar) || (rows - 1 - r < P.gapbar);
-			const int s0 = -sc_score(P, rv.rd(r), refm, rv.q(r) - 33);
-			int f = (r == 0) ? 0 : Fpre; if(gb) f = 0;
-			const int hd = (r == 0) ? 255 : Hprev[r - 1];
-			const int e = Eprev[r];
-			int h = subs(hd, s0); if(e > h) h = e; if(f > h) h = f;
-			Hcur[r] = h;
-			const int e2 = subs(e, P.rdGapExt), ho = gb ? 0 : subs(h, P.rdGapOpen);
-			Ecur[r] = e2 > ho ? e2 : ho;
-			const int f2 = subs(f, P.rfGapExt), fo = subs(h, P.rfGapOpen);
-			Fpre = f2 > fo ? f2 : fo;
-			Fcur[r] = f;
-			// the backtrace's comparisons at this cell, literally (raw values: the 0xff bias cancels)
-			uint32_t ne = 0;
-			const int hup = (r == 0) ? 255 : Hcur[r - 1], fup = (r == 0) ? 0 : Fcur[r - 1];
-			if(h != hd - s0) ne |= CF_D;                 // s0 = penalty >= 0 (column 0 compares with H(r-1,-1) = 0; never read)
-			if(h != e) ne |= CF_HE;
-			if(h != f) ne |= CF_HF;
-			if(!(j > 0 && e == Hprev[r] - P.rdGapOpen)) ne |= CF_EO;
-			if(!(j > 0 && e == Eleft[r] - P.rdGapExt)) ne |= CF_EX;
-			Ehere[r] = e;
-			if(!(f == hup - P.rfGapOpen)) ne |= CF_FO;
-			if(!(f == fup - P.rfGapExt)) ne |= CF_FX;
-			cells[cell_index(r + shift, j, R)] = (uint8_t)ne;
-		}
-		const int lr = Hcur[rows - 1];
-		if(lr > lrmax) lrmax = lr;
-		if(lr - 255 >= pb.minsc) cand.push_back((uint16_t)((lr << 8) | j));
-		Hprev.swap(Hcur); Eprev.swap(Ecur); Fprev.swap(Fcur); Eleft = Ehere;
-	}
-	// character cache (what K_fill leaves for the backtrace's edits)
-	for(int j = 0; j < BT2_PC_WORDS; j++) pcache[j] = 0;
-	for(int r = 0; r < rows; r++) { const uint32_t c = (uint32_t)rv.rd(r); pcache[r >> 3] |= (c > 3 ? 4u : c) << ((r & 7) * 4); }
-	for(int j = 0; j < cols; j++) { const uint32_t m = pb.rf[j]; const uint32_t c = m > 15 ? 4u : (uint32_t)__builtin_ctz(m); pcache[BT2_PC_RD + (j >> 3)] |= c << ((j & 7) * 4); }
-	std::sort(cand.begin(), cand.end(), [](uint16_t a, uint16_t b) { return a > b; });
-	pb.lrmax = lrmax; pb.ncand = (uint32_t)cand.size();
-	for(size_t i = 0; i < cand.size(); i++) pb.cand[i] = cand[i];
-}
+#include "fill_scalar.hpp"
 
 #ifdef BT2_BT_PROFILE
 static void print_bt_prof() {
@@ -121,7 +75,8 @@ int main(int argc, char** argv) {
 	const uint32_t MI = BT2GPU_MAX_ITER + 8;
 	std::vector<uint16_t> ov_rng(2 * MI), ov_pos(2 * MI), ov_val(2 * MI), seen_rng(MI), seen_val(MI), conv_val(MI), r_n(W), r_cur(W), r_thresh(W), r_conv_n(W), r_nseen(W);
 	std::vector<uint8_t> r_flags(W), elim(W); std::vector<uint32_t> r_conv_off(W); std::vector<double> mass(W);
-	std::vector<uint8_t> cells(BT2_CELL_BYTES); std::vector<uint32_t> pcache(BT2_PC_WORDS, 0);
+	std::vector<uint8_t> cells(fill_cell_bytes(BT2GPU_MAX_ROWS, BT2_KMAX));
+	const bool exactFill = getenv("EMU_EXACT_FILL") != nullptr; uint32_t nprob = 0; std::vector<uint32_t> pcache(BT2_PC_WORDS, 0);
 	orc::WorkCounters wc;
 	for(uint32_t ri = 0; ri < n; ri++) {
 		ReadState& rs = states[ri];
@@ -168,10 +123,10 @@ int main(int argc, char** argv) {
 			while(true) {
 				Problem pb; pb.read = ri;
 				if(advance(P, ix, rf, pools, rs, pb) == ADV_ROUND_END) break;
-				BtCtx cx; cx.P = P; cx.pools = pools; cx.states = states.data(); cx.probs = &pb; cx.cells = cells.data();
+				BtCtx cx; cx.P = P; cx.pools = pools; cx.states = states.data(); cx.probs = &pb; cx.cells = cells.data(); cx.cell_stride = 0;
 				cx.pcache = pcache.data(); cx.scratch = scratch.data(); cx.seq = in->seq; cx.qual = in->qual; cx.set_pens();
 				BtMachine m; m.slot = 0; m.read = ri; m.pc = pcache.data(); m.pcs = 1; uint8_t cbuf[64]; m.cbuf = cbuf; m.cstride = 16;
-				fill_emu(P, pb, m.view(cx), cells.data(), pcache.data());
+				fill_emu(P, pb, m.view(cx), cells.data(), pcache.data(), exactFill, (nprob++) & 1u);
 				m.begin(cx);
 				while(m.phase != BP_DONE && m.step(cx)) { }
 				m.finish(cx);
@@ -195,6 +150,6 @@ int main(int argc, char** argv) {
 	size_t len = 0; char* s = bt2host_sam_records(job, b, &res, atoi(argv[4]), &len);
 	fwrite(s, 1, len, stdout); bt2host_free(s);
 	uint64_t dps = 0, bts = 0, bta = 0; for(uint32_t i = 0; i < n; i++) { dps += states[i].nExDps; bts += states[i].btSteps; bta += states[i].btAttempts; }
-	fprintf(stderr, "emu: reads %u dps %lu btAttempts %lu btSteps %lu alns %u\n", n, dps, bta, bts, atop);
+	fprintf(stderr, "emu: reads %u dps %lu btAttempts %lu btSteps %lu alns %u cells in band %zu of %zu\n", n, dps, bta, bts, atop, g_cells_in_band, g_cells_rect);
 	return 0;
 }

@@ -21,7 +21,7 @@ def test_bt2gpu_exports():
     for n in names:
         assert hasattr(lib, n), n
     lib.bt2gpu_abi_version.restype = ctypes.c_int
-    assert lib.bt2gpu_abi_version() == 3  # BT2GPU_ABI_VERSION in include/bt2gpu.h
+    assert lib.bt2gpu_abi_version() == 4  # BT2GPU_ABI_VERSION in include/bt2gpu.h
 
 
 def test_bt2host_exports():

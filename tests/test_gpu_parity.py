@@ -38,6 +38,31 @@ def test_gpu_matches_oracle_and_golden(name):
     gpu.close(); orc.close()
 
 
+@pytest.mark.parametrize("name", ["syn100_default", "syn100_k5", "lambda_default"])
+def test_gpu_whole_rectangle_fill(name):
+    """--exact-xs (bt2gpu_params.exactBestLtMinsc = 1): K_fill computes whole rectangles like the reference's EEU8_alignNucleotides and
+    prm.bestLtMinscMate1 -- the one field the banded fill only bounds from below (checked as such in the other tests) -- is equal too;
+    everything else is what the banded fill gives (same SAM bytes), and the kernel reports having computed more cells."""
+    ref, reads, opts, gold = common.CASES[name]
+    job = pkg.Job(common.index_base(ref), (opts + " --exact-xs").strip())
+    batch = job.fastq(common.reads_path(reads))
+    orc = common.Oracle(job)
+    want = orc.align(batch)
+    gpu = _gpu(job)
+    got = gpu.align(batch)
+    diffs = common.compare_results(want, got, exact_xs=True)
+    assert not diffs, "\n".join(diffs[:10])
+    assert common.sorted_records(job.sam(batch, got, mode=1)) == common.golden_records(gold)
+    cx = gpu.counters()
+    gpu.close()
+    jb = pkg.Job(common.index_base(ref), opts)
+    gb = _gpu(jb)
+    gb.align(batch)
+    cb = gb.counters()
+    assert cb["dp_cells"] == cx["dp_cells"] and cb["dp_cells_computed"] < cx["dp_cells_computed"]
+    gb.close(); orc.close()
+
+
 @pytest.mark.parametrize("name", ["lambda_k3_vs", "syn150_sensitive_dpad12"])
 def test_gpu_without_full_suffix_array(name, monkeypatch):
     """BT2GPU_FULL_SA=0: the path an index of 2^32 rows or more takes -- every seed through the reference's LF walk (k_seed_walk),

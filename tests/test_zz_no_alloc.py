@@ -49,20 +49,20 @@ def _pack(probs):
 
 
 def _existing(g, gpu, a):
-    """bt2gpu_test_fill: host pointers in, host pointers out"""
+    """bt2gpu_test_fill (mode 2: the production kernel in the lane layout the no-allocation entry point uses): host pointers in and out"""
     n, nf = a["n"], a["nflags"]
     H = np.zeros(nf, np.uint8); E = np.zeros(nf, np.uint8); F = np.zeros(nf, np.uint8); FL = np.zeros(nf, np.uint8)
-    cand = np.zeros(256 * n, np.uint16); ncand = np.zeros(n, np.uint32); lrmax = np.zeros(n, np.int32)
+    cand = np.zeros(256 * n, np.uint16); ncand = np.zeros(n, np.uint32); lrmax = np.zeros(n, np.int32); band = np.zeros(2 * n, np.int32)
     ptr = lambda x: x.ctypes.data_as(C.c_void_p)
-    g.bt2gpu_test_fill.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 16
+    g.bt2gpu_test_fill.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 16 + [C.c_int32, C.c_void_p]
     rc = g.bt2gpu_test_fill(gpu.ptr, n, ptr(a["seq_off"]), ptr(a["seq"]), ptr(a["qual"]), ptr(a["rows"]), ptr(a["cols"]), ptr(a["rf_off"]),
-                            ptr(a["rf"]), ptr(a["minsc"]), ptr(a["fl_off"]), ptr(H), ptr(E), ptr(F), ptr(FL), ptr(cand), ptr(ncand), ptr(lrmax))
+                            ptr(a["rf"]), ptr(a["minsc"]), ptr(a["fl_off"]), ptr(H), ptr(E), ptr(F), ptr(FL), ptr(cand), ptr(ncand), ptr(lrmax), 2, ptr(band))
     assert rc == 0, g.bt2gpu_last_error(gpu.ptr)
     return FL, cand, ncand, lrmax
 
 
-def _noalloc(g, gpu, a, torch, poison):
-    """bt2gpu_fill_noalloc: device pointers in and out, work enqueued on the legacy default stream"""
+def _noalloc(g, gpu, a, torch, poison, stream=None):
+    """bt2gpu_fill_noalloc: device pointers in and out, work enqueued on `stream` (None: the legacy default stream)"""
     n, nf = a["n"], a["nflags"]
     dev = torch.device("cuda", 0)
     up = lambda x: torch.from_numpy(x.view(np.uint8) if x.dtype != np.uint8 else x).to(dev)     # bytes of the array, as is
@@ -74,7 +74,7 @@ def _noalloc(g, gpu, a, torch, poison):
     torch.cuda.synchronize()
     g.bt2gpu_fill_noalloc.restype = C.c_int
     g.bt2gpu_fill_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32] + [C.c_void_p] * 13
-    rc = g.bt2gpu_fill_noalloc(gpu.ptr, None, n, d["seq_off"].data_ptr(), d["seq"].data_ptr(), d["qual"].data_ptr(), d["rows"].data_ptr(),
+    rc = g.bt2gpu_fill_noalloc(gpu.ptr, C.c_void_p(stream.cuda_stream) if stream is not None else None, n, d["seq_off"].data_ptr(), d["seq"].data_ptr(), d["qual"].data_ptr(), d["rows"].data_ptr(),
                                d["cols"].data_ptr(), d["rf_off"].data_ptr(), d["rf"].data_ptr(), d["minsc"].data_ptr(), d["fl_off"].data_ptr(),
                                o_fl.data_ptr(), o_cand.data_ptr(), o_ncand.data_ptr(), o_lrmax.data_ptr())
     assert rc == 0, g.bt2gpu_last_error(gpu.ptr)
@@ -89,12 +89,15 @@ def test_fill_noalloc_equals_existing_entry_point_twice():
     g = pkg.load_gpu()
     rng = np.random.default_rng(2024)
     # first call: the full 128 problems, big ones first (fills the scratch); second call: fewer, smaller, other sizes
+    # third call: on a stream of the caller's, after the two on the default stream
     calls = [_problems(rng, MAXP, [(160, 199), (150, 199), (129, 150), (128, 199), (65, 70), (64, 100), (1, 1), (2, 5)]),
-             _problems(rng, 37, [(1, 3), (33, 40), (100, 120), (160, 1)])]
+             _problems(rng, 37, [(1, 3), (33, 40), (100, 120), (160, 1)]),
+             _problems(rng, 61, [(150, 199), (7, 190)])]
+    side = torch.cuda.Stream(device=0)
     for k, probs in enumerate(calls):
         a = _pack(probs)
         FL, cand, ncand, lrmax = _existing(g, gpu, a)
-        gFL, gcand, gncand, glrmax = _noalloc(g, gpu, a, torch, poison=0xA5 if k == 0 else 0x5A)
+        gFL, gcand, gncand, glrmax = _noalloc(g, gpu, a, torch, poison=0xA5 if k == 0 else 0x5A, stream=side if k == 2 else None)
         assert np.array_equal(glrmax, lrmax), "call %d: lrmax" % k
         assert np.array_equal(gncand, ncand), "call %d: ncand" % k
         for i in range(a["n"]):
@@ -103,6 +106,14 @@ def test_fill_noalloc_equals_existing_entry_point_twice():
             j = int(np.nonzero(gFL != FL)[0][0]); i = int(np.searchsorted(a["fl_off"], j, side="right") - 1)
             raise AssertionError("call %d problem %d (%dx%d): flag byte %d differs: %02x vs %02x" %
                                  (k, i, a["rows"][i], a["cols"][i], j - int(a["fl_off"][i]), gFL[j], FL[j]))
+    # a problem whose size is out of range (161 rows): switched off, its outputs say so and its flags are not touched
+    probs = _problems(rng, 3, [(20, 30), (160, 199), (40, 60)])
+    a = _pack(probs)
+    a["rows"][1] = 161
+    gFL, gcand, gncand, glrmax = _noalloc(g, gpu, a, torch, poison=0x77)
+    assert gncand[1] == 0 and glrmax[1] == -1
+    lo, hi = int(a["fl_off"][1]), int(a["fl_off"][2])
+    assert (gFL[lo:hi] == 0x77).all() and (gFL[:lo] != 0x77).any()
     # beyond the static scratch: rejected with a message, nothing launched
     a = _pack(_problems(rng, 4, []))
     g.bt2gpu_last_error.restype = C.c_char_p
