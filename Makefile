@@ -18,10 +18,12 @@ $(PKG)/libbt2gpu.so: $(wildcard $(GPU)/*.cu $(GPU)/*.cuh) include/bt2gpu.h
 $(PKG)/libbt2host.so: $(wildcard $(HOST)/*.cpp $(HOST)/*.hpp) include/bt2gpu.h include/bt2host.h
 	g++ $(CXXFLAGS) -shared -o $@ $(HOST)/host_index.cpp $(HOST)/host_reads.cpp $(HOST)/host_sink.cpp $(HOST)/host_api.cpp
 
-oracle:
+oracle: $(PKG)/libbt2gpu.so
 	$(MAKE) -C oracle all
 
-emu: tests/emu/emu_pipeline tests/emu/emu_fill
+emu: tests/emu/emu_pipeline tests/emu/emu_fill tests/emu/libbt2gpu_shim.so
+tests/emu/libbt2gpu_shim.so: tests/emu/bt2gpu_oracle_shim.cpp oracle/oracle_capi.cpp $(wildcard oracle/*.hpp) include/bt2gpu.h
+	g++ $(CXXFLAGS) -Ioracle -shared -o $@ tests/emu/bt2gpu_oracle_shim.cpp oracle/oracle_capi.cpp
 tests/emu/emu_fill: tests/emu/emu_fill.cpp tests/emu/fill_scalar.hpp $(wildcard $(GPU)/*.cuh)
 	g++ -O1 -std=c++17 -Iinclude -w -o $@ tests/emu/emu_fill.cpp
 tests/emu/emu_pipeline: tests/emu/emu_pipeline.cpp tests/emu/fill_scalar.hpp $(wildcard $(GPU)/*.cuh oracle/*.hpp $(HOST)/*.cpp)

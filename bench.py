@@ -35,8 +35,12 @@ REF_LEN = 5_000_000
 READ_LEN = 150
 METRIC = "aligned_reads_per_sec_150bp_sensitive_e2e"
 ALU_WARP_INST_PER_CLK_SM = 1.95   # VIMNMX.S16x2 / HSET2 / LOP3 share this pipe (measured, profiles/r1_pipe_bench.txt)
-# profiles/r1_ncu_full_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum of one launch over 262 144 DP problems, per problem
-NCU_TRAFFIC_PER_PROBLEM = {"k_fill": 13.25e9 / 262144, "k_bt": 5.68e9 / 262144}
+# ALU-pipe instructions a pair of DP cells needs in K_fill (one warp-instruction = 32 lanes x 2 problems = 64 cells): 3 VIMNMX(3).S16x2 of the
+# recurrence + 1 HSET2 (mismatch mask) + 1 LOP3 (mask & penalty) + 7 HSET2 (the backtrace's comparisons) + 1 LOP3 (merge of the carried flags)
+ALU_INST_PER_CELL_PAIR = 13
+# profiles/r2_ncu_fill_raw.csv: dram__bytes_read.sum + dram__bytes_write.sum of one K_fill launch over 262 144 DP problems, per problem;
+# profiles/r1_ncu_full_raw.csv for k_bt
+NCU_TRAFFIC_PER_PROBLEM = {"k_fill": (0.368e9 + 5.85e9) / 262144, "k_bt": 5.68e9 / 262144}
 
 
 def log(*a):
@@ -271,6 +275,32 @@ def workload_config(n=None):
             "l2": "inputs larger than L2 (300 MB of reads per step, DP cell flags written per problem; 126 MB L2)"}
 
 
+def file_to_file(pkg, job, ascii_reads, device):
+    """FASTQ file -> SAM file on one GPU (omp-bowtie2-prime_b200/stream.py: reader thread, aligner, sink thread), both files on
+    tmpfs: the like-for-like of the reference process's wall time (cpu_baseline.wall_reads_per_s: FASTQ file -> SAM to /dev/null)."""
+    stream = importlib.import_module("omp-bowtie2-prime_b200.stream")
+    tmp = "/dev/shm" if os.path.isdir("/dev/shm") else WORK
+    fq, sam = os.path.join(tmp, "bt2gpu_bench.fq"), os.path.join(tmp, "bt2gpu_bench.sam")
+    write_fastq(fq, ascii_reads)
+    try:
+        al = [pkg.GpuAligner(job, device), pkg.GpuAligner(job, device)]
+        stream.fastq_to_sam(job, fq, sam, device, aligners=al)          # warm-up (page cache, pinned buffers)
+        best = None
+        for _ in range(2):
+            t0 = time.time()
+            nr, nb = stream.fastq_to_sam(job, fq, sam, device, aligners=al)
+            dt = time.time() - t0
+            best = dt if best is None or dt < best else best
+        for g in al:
+            g.close()
+        return {"value": nr / best, "unit": "reads/s", "reads": nr, "fastq_bytes": os.path.getsize(fq), "sam_bytes": nb, "seconds": best,
+                "where": tmp, "note": "FASTQ file -> parse -> bt2gpu_align_batch -> SAM formatting -> SAM file, pipelined over byte ranges of the file"}
+    finally:
+        for f in (fq, sam):
+            if os.path.exists(f):
+                os.remove(f)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -279,6 +309,7 @@ def main():
     ap.add_argument("--impl", default="bt2gpu")
     ap.add_argument("--reads", type=int, default=int(os.environ.get("BT2_BENCH_READS", "1000000")))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-file-to-file", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
@@ -377,27 +408,45 @@ def main():
               "k_bt": (ctr["ms_bt"], ctr["n_bt"], 2.0 * ctr["bt_steps"])}
     dom = max(phases, key=lambda k: phases[k][0])
     ms, nl, byts = phases[dom]
-    achieved = (byts / max(nl, 1)) / ((ms / max(nl, 1)) * 1e-3) / 1e9 if ms > 0 else 0.0
+    if dom == "k_fill":   # what the fill stores: one flag byte per cell it COMPUTES (the band) + its inputs / outputs
+        byts = 1.0 * ctr["dp_cells_computed"] + 900.0 * ctr["dp_problems"]
+    hbm_achieved = (byts / max(nl, 1)) / ((ms / max(nl, 1)) * 1e-3) / 1e9 if ms > 0 else 0.0
     # ncu --set full capture of the same command (profiles/): dram bytes read+written by the dominant kernel, scaled from the captured
-    # launch to this run's average launch (problems per launch), so that it compares with `achieved` x ms_per_launch
+    # launch to this run's average launch (problems per launch), so that it compares with the algorithmic bytes per launch
     traffic = NCU_TRAFFIC_PER_PROBLEM[dom] * ctr["dp_problems"] / max(nl, 1) if dom in NCU_TRAFFIC_PER_PROBLEM else None
-    # K_fill against the integer ALU pipe: 12 ALU-pipe warp-instructions per 64 cells at the measured issue rate
-    alu_peak = 148 * 1.965e9 * ALU_WARP_INST_PER_CLK_SM * 64.0 / 12.0 / 1e9
+    # K_fill against the integer ALU pipe.  GCUPS counts the cells the REFERENCE computes for the same DP problems
+    # (rdlen x rflen each); the kernel computes only the band of diagonals an alignment >= minsc can reach (cells_computed)
+    alu_peak = 148 * 1.965e9 * ALU_WARP_INST_PER_CLK_SM * 64.0 / ALU_INST_PER_CELL_PAIR / 1e9
     fill_gcups = ctr["dp_cells"] / (ctr["ms_fill"] * 1e-3) / 1e9 if ctr["ms_fill"] > 0 else 0.0
+    fill_gcups_computed = ctr["dp_cells_computed"] / (ctr["ms_fill"] * 1e-3) / 1e9 if ctr["ms_fill"] > 0 else 0.0
+    hbm = {"achieved": hbm_achieved, "peak": peak, "unit": "GB/s", "frac": hbm_achieved / peak, "peak_source": peak_src, "algorithmic_bytes_per_launch": byts / max(nl, 1)}
+    if dom == "k_fill":
+        roofline = {"bound": "int_alu", "kernel": dom, "achieved": fill_gcups, "peak": alu_peak, "unit": "GCUPS", "frac": fill_gcups / alu_peak,
+                    "traffic": traffic, "launches": int(nl), "ms_per_launch": ms / max(nl, 1),
+                    "cells": {"reference_equivalent": int(ctr["dp_cells"] // max(args.steps, 1)), "computed": int(ctr["dp_cells_computed"] // max(args.steps, 1)),
+                              "gcups_on_computed_cells": fill_gcups_computed, "frac_on_computed_cells": fill_gcups_computed / alu_peak},
+                    "how": "peak = 148 SMs x 1.965 GHz x %.2f ALU-pipe warp-inst/clk/SM (tools/pipe_bench.cu, profiles/r1_pipe_bench.txt) x 64 cells / %d ALU-pipe "
+                           "instructions per cell pair; achieved = rdlen x rflen cells of the DP problems the reference's control flow runs / K_fill time"
+                           % (ALU_WARP_INST_PER_CLK_SM, ALU_INST_PER_CELL_PAIR),
+                    "hbm": hbm}
+    else:
+        roofline = dict(hbm, bound="hbm", kernel=dom, traffic=traffic, launches=int(nl), ms_per_launch=ms / max(nl, 1))
     line = {"metric": METRIC, "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1000.0 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic",
             "config": workload_config(n), "aligned_fraction": aligned / float(n),
             "gcups": ctr["dp_cells"] * world / dev_s / 1e9 if dev_s > 0 else None,
-            "gcups_fill_kernel": ctr["dp_cells"] / (ctr["ms_fill"] * 1e-3) / 1e9 if ctr["ms_fill"] > 0 else None,
+            "gcups_fill_kernel": fill_gcups,
             "phase_ms_per_step": {k: phases[k][0] / args.steps for k in phases} | {"glue": ctr["ms_glue"] / args.steps, "wall": 1000.0 * wall / args.steps},
-            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src, "launches": int(nl), "ms_per_launch": ms / max(nl, 1),
-                         "note": "the DP fill and the backtrace are not HBM-bound (integer ALU pipe / divergent issue); see int_alu and DESIGN.md section 4"},
-            "int_alu": {"kernel": "k_fill", "achieved_gcups": fill_gcups, "peak_gcups": alu_peak, "frac": fill_gcups / alu_peak,
-                        "how": "peak = 148 SMs x 1.965 GHz x %.2f ALU-pipe warp-inst/clk/SM (tools/pipe_bench.cu, profiles/r1_pipe_bench.txt) x 64 cells / 12 ALU-pipe instructions" % ALU_WARP_INST_PER_CLK_SM},
+            "roofline": roofline,
+            "int_alu": {"kernel": "k_fill", "achieved_gcups": fill_gcups, "peak_gcups": alu_peak, "frac": fill_gcups / alu_peak},
             "e2e": {"value": total_reads / e2e_s, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(ctr["launches"]), "clocks": clocks}
+    if rank == 0 and world == 1 and not args.no_file_to_file:
+        try:
+            line["file_to_file"] = file_to_file(pkg, job, ascii_reads, local)
+        except Exception as e:
+            line["file_to_file"] = {"value": None, "error": str(e)[:200]}
     if rank == 0:
         if not args.no_cpu_baseline and world == 1:
             try:   # bounded: a two-point -p sweep on 60 k reads, then one run on a 200 k-read prefix of the workload (~20 s of CPU work)

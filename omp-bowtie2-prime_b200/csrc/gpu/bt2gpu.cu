@@ -93,6 +93,8 @@ struct bt2gpu_ctx {
 	uint32_t n = 0, W = 0, maxOffs = 0; uint64_t nbases = 0;
 	uint64_t out_alns = 0, out_edits = 0;
 	Pools pools;
+	uint32_t poolScale[4] = { 1, 1, 1, 1 };   // chunk / sat / aln / edit pool: doubled when a batch overflows it (the batch is then run again)
+	uint64_t poolRetries = 0;
 	bt2gpu_counters ctr;
 	std::vector<cudaEvent_t> evpool; size_t evused = 0;
 	struct Span { int ph; cudaEvent_t a, b; }; std::vector<Span> spans;
@@ -181,10 +183,11 @@ void ensure_batch(bt2gpu_ctx* c, uint32_t n, uint64_t nbases, uint32_t maxOffs) 
 	c->s_rco.ensure(S * W * 4); c->s_rcn.ensure(S * W * 2); c->s_rns.ensure(S * W * 2); c->s_mass.ensure(S * W * 8); c->s_elim.ensure(S * W);
 	// pools
 	Pools& p = c->pools;
-	p.chunk_cap = (uint32_t)std::min<size_t>(nn * 6 + 4096, 0x7fffffff);
-	p.sat_cap   = (uint32_t)std::min<size_t>(nn * 48 + 65536, 0x7fffffff);
-	p.aln_cap   = (uint32_t)std::min<size_t>(nn * 6 + 4096, 0x7fffffff);
-	p.edit_cap  = (uint32_t)std::min<size_t>(nn * 96 + 65536, 0x7fffffff);
+	static const size_t pdiv = getenv("BT2GPU_POOL_DIV") ? (size_t)std::max(1, atoi(getenv("BT2GPU_POOL_DIV"))) : 1;   // test knob: start with pools this much too small
+	p.chunk_cap = (uint32_t)std::min<size_t>((nn * 6 + 4096) / pdiv * c->poolScale[0] + 8, 0x7fffffff);
+	p.sat_cap   = (uint32_t)std::min<size_t>((nn * 48 + 65536) / pdiv * c->poolScale[1] + 8, 0x7fffffff);
+	p.aln_cap   = (uint32_t)std::min<size_t>((nn * 6 + 4096) / pdiv * c->poolScale[2] + 8, 0x7fffffff);
+	p.edit_cap  = (uint32_t)std::min<size_t>((nn * 96 + 65536) / pdiv * c->poolScale[3] + 8, 0x7fffffff);
 	c->chunks.ensure((size_t)p.chunk_cap * sizeof(Chunk)); c->sats.ensure((size_t)p.sat_cap * sizeof(SatEntry));
 	c->alnp.ensure((size_t)p.aln_cap * sizeof(AlnRec)); c->editp.ensure((size_t)p.edit_cap * 4);
 	p.chunks = c->chunks.as<Chunk>(); p.sats = c->sats.as<SatEntry>(); p.alns = c->alnp.as<AlnRec>(); p.edits = c->editp.as<uint32_t>();
@@ -271,6 +274,8 @@ void bind_staged(bt2gpu_ctx* c, const Staged& g) {
 }
 
 #define LAUNCH(c) (c)->ctr.launches++
+
+struct PoolOverflow { uint32_t mask; };
 
 // aligns the resident batch; the packed results stay in out[cur] with offsets shifted by (aln_glob, edit_glob)
 void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
@@ -399,6 +404,23 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 	flush_spans(c);
 }
 
+// do_run; a batch that overflows one of the bump-allocated pools (seen-diagonal / seed-range chunks, prioritised SA rows, alignments,
+// edits: sized for typical reads, -k 50 on a repeat-rich reference needs more) is run again from its inputs with that pool doubled --
+// a run starts from the uploaded reads alone (k_begin), so nothing of the aborted attempt survives.
+void do_run_grow(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
+	for(int attempt = 0;; attempt++) {
+		try { do_run(c, aln_glob, edit_glob); return; }
+		catch(const PoolOverflow& po) {
+			c->spans.clear(); c->evused = 0;
+			if(attempt >= 8) throw std::string("bt2gpu: device pools still exhausted after growing them 8 times; use smaller batches");
+			for(int k = 0; k < 4; k++) if(po.mask & (1u << k)) c->poolScale[k] *= 2;
+			c->poolRetries++;
+			if(getenv("BT2GPU_TRACE")) fprintf(stderr, "[bt2gpu] pool overflow (mask %u): scales now %u %u %u %u, running the batch again\n", po.mask, c->poolScale[0], c->poolScale[1], c->poolScale[2], c->poolScale[3]);
+			ensure_batch(c, c->n, c->nbases, c->maxOffs);
+		}
+	}
+}
+
 // grows a pinned result buffer, keeping what is already in it
 void grow_keep(HBuf& h, size_t keep, size_t want) {
 	if(want <= h.cap) return;
@@ -471,7 +493,7 @@ void do_align_pipelined(bt2gpu_ctx* c, const bt2gpu_reads* in, bt2gpu_results* o
 		const double t1 = now();
 		bind_staged(c, g);
 		if(ab > 0xf0000000ull || eb > 0xf0000000ull) throw std::string("bt2gpu_align_batch: more than 2^32 alignments or edits in one call; use smaller batches");
-		do_run(c, (uint32_t)ab, (uint32_t)eb);
+		do_run_grow(c, (uint32_t)ab, (uint32_t)eb);
 		const double t2 = now();
 		if(trace) fprintf(stderr, "[bt2gpu] sub-batch at %u: +%.2f ms  stage next %.2f ms  run %.2f ms\n", lo, t0 - t00, t1 - t0, t2 - t1);
 		if((ab + c->out_alns + 1) * sizeof(bt2gpu_aln) > c->h_alns.cap || (eb + c->out_edits + 1) * sizeof(bt2gpu_edit) > c->h_edits.cap) {
@@ -702,14 +724,14 @@ int bt2gpu_upload(bt2gpu_ctx* ctx, const bt2gpu_reads* in) {
 		settle(ctx->h2dspan[0], ctx->ctr.ms_h2d);
 	})
 }
-int bt2gpu_run_resident(bt2gpu_ctx* ctx) { API_GUARD({ do_run(ctx); }) }
+int bt2gpu_run_resident(bt2gpu_ctx* ctx) { API_GUARD({ do_run_grow(ctx); }) }
 int bt2gpu_fetch(bt2gpu_ctx* ctx, bt2gpu_results* out) { API_GUARD({ if(!out) throw std::string("bt2gpu_fetch: null out"); do_fetch(ctx, out); }) }
 
 int bt2gpu_align_batch(bt2gpu_ctx* ctx, const bt2gpu_reads* in, bt2gpu_results* out) {
 	API_GUARD({
 		if(!in || !out) throw std::string("bt2gpu_align_batch: null argument");
 		const uint32_t chunk = std::min(ctx->pipeChunk, ctx->maxBatch);
-		if(in->n <= chunk) { bind_staged(ctx, stage_upload(ctx, in, 0, in->n, 0, ctx->stream)); do_run(ctx); do_fetch(ctx, out); }
+		if(in->n <= chunk) { bind_staged(ctx, stage_upload(ctx, in, 0, in->n, 0, ctx->stream)); do_run_grow(ctx); do_fetch(ctx, out); }
 		else do_align_pipelined(ctx, in, out, chunk);
 	})
 }

@@ -40,8 +40,28 @@ build_build() {
   g++ -include "$OUT/pre.h" -O2 -msse2 $COMMON -o "$OUT/bowtie2-build-l" $S -lpthread -lz
 }
 
+# The reference with its phases P1-P6 redirected to libbt2gpu.so (the drop-in, built for real): a scratch copy of the
+# reference + integration/bt2_search_gpu.patch (3 friend declarations, one if() around P1-P6) + integration/gpu_batch.cpp (ours),
+# compiled with the flags above and linked against the in-tree library.  Runs the GPU path only with BT2GPU=1 in the environment.
+build_gpu() {
+  local LIB="$HERE/../omp-bowtie2-prime_b200/libbt2gpu.so" INT="$HERE/../integration"
+  if [ ! -f "$LIB" ]; then echo "[build_ref] libbt2gpu.so not built yet: skipping bowtie2-align-l-gpu" >&2; return; fi
+  if [ "$OUT/bowtie2-align-l-gpu" -nt "$INT/gpu_batch.cpp" ] && [ "$OUT/bowtie2-align-l-gpu" -nt "$INT/bt2_search_gpu.patch" ] && \
+     [ "$OUT/bowtie2-align-l-gpu" -nt "$HERE/../include/bt2gpu.h" ] && [ -z "$FORCE" ]; then return; fi
+  echo "[build_ref] bowtie2-align-l-gpu" >&2
+  local T; T=$(mktemp -d /tmp/bt2ref_gpu.XXXXXX)
+  cp -r "$REF"/. "$T"/ && chmod -R u+w "$T"
+  (cd "$T" && patch -p1 -s < "$INT/bt2_search_gpu.patch") || { echo "[build_ref] patch does not apply" >&2; rm -rf "$T"; return 1; }
+  cp "$INT/gpu_batch.cpp" "$HERE/../include/bt2gpu.h" "$T"/
+  local C2="${COMMON//$REF/$T}"
+  g++ -O3 -msse2 $C2 -DBT2GPU -o "$OUT/bowtie2-align-l-gpu" "$T/bowtie2-align.cpp" -L"$(dirname "$LIB")" -lbt2gpu \
+      -Wl,-rpath,'$ORIGIN/../../omp-bowtie2-prime_b200' -lpthread -lz || { rm -rf "$T"; return 1; }
+  rm -rf "$T"
+}
+
 build_align bowtie2-align-l &
 build_build &
+build_gpu &
 # the opt-in 16-bit build (SURVEY 8c oracle mode B): pins the i16 protocol (tests/golden/*_i16.sam)
 if [ -z "$NO_I16" ]; then build_align bowtie2-align-l-i16 -DENABLE_I16 & fi
 wait

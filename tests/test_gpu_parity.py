@@ -156,6 +156,23 @@ def test_gpu_batch_split_and_determinism(monkeypatch):
     g2.close(); g3.close()
 
 
+def test_gpu_pool_overflow_grows_and_reruns(monkeypatch):
+    """-k 20 on the repeat-rich reference with the device pools started 400x too small (BT2GPU_POOL_DIV): the batch overflows them, the
+    library doubles the pool that ran out and runs the batch again until it fits -- same results as the oracle, no "pool exhausted" error."""
+    monkeypatch.setenv("BT2GPU_POOL_DIV", "400")
+    job = pkg.Job(common.index_base("syn"), "-k 20 -D 5 -R 3")
+    batch = job.fastq(common.reads_path("syn100"))
+    orc = common.Oracle(job)
+    want = orc.align(batch)
+    gpu = _gpu(job)
+    got = gpu.align(batch)
+    diffs = common.compare_results(want, got)
+    assert not diffs, "\n".join(diffs[:10])
+    assert job.sam(batch, got, 1) == job.sam(batch, want, 1)
+    assert int(got.reads["n_alns"].max()) > 6          # more alignments per read than the default pools budget
+    gpu.close(); orc.close()
+
+
 def test_gpu_larger_iid_vs_oracle():
     """5 Mbp i.i.d. reference, 150 bp reads, --sensitive --dpad 12 (BASELINE config 2 at reduced read count)"""
     base = common.index_base("iid5000000")
