@@ -72,7 +72,8 @@ struct Bt2GpuBridge {
 			seq_off.push_back((uint32_t)seq.size()); slot_of.push_back(m);
 			seq.insert(seq.end(), (const uint8_t*)rd.patFw.buf(), (const uint8_t*)rd.patFw.buf() + len);      // codes 0..4
 			qual.insert(qual.end(), (const uint8_t*)rd.qual.buf(), (const uint8_t*)rd.qual.buf() + len);      // Phred+33
-			rng_seed.push_back(rd.seed); minsc32.push_back((int32_t)minsc[m]); nceil32.push_back(nceil[m]); interval32.push_back(intervals[m]);
+			rng_seed.push_back(rd.seed); minsc32.push_back((int32_t)minsc[m]); interval32.push_back(intervals[m]);
+			nceil32.push_back(k.sc.nCeil.f<int>((double)len));   // what SwAligner::initRead takes (aligner_sw.cpp:44), not the caller's min(.., rdlen) (:2555)
 		}
 		const uint32_t n = (uint32_t)slot_of.size();
 		if(n == 0) return;

@@ -165,6 +165,15 @@ void setup_params(bt2gpu_ctx* c, const bt2gpu_params* p) {
 	}
 }
 
+// scratch of the row sampler (k_prio2: RowSampler + Random1toN of SwDriver::prioritizeSATups), one slot per read sampled at a time
+void ensure_sample(bt2gpu_ctx* c, uint32_t W) {
+	const size_t S = c->sampSlots, MI = BT2_SAMPLE_MI;
+	c->s_ovr.ensure(S * 2 * MI * 2); c->s_ovp.ensure(S * 2 * MI * 2); c->s_ovv.ensure(S * 2 * MI * 2);
+	c->s_sr.ensure(S * MI * 2); c->s_sv.ensure(S * MI * 2); c->s_cv.ensure(S * MI * 2);
+	c->s_rn.ensure(S * W * 2); c->s_rcur.ensure(S * W * 2); c->s_rth.ensure(S * W * 2); c->s_rfl.ensure(S * W);
+	c->s_rco.ensure(S * W * 4); c->s_rcn.ensure(S * W * 2); c->s_rns.ensure(S * W * 2); c->s_mass.ensure(S * W * 8); c->s_elim.ensure(S * W);
+}
+
 void ensure_batch(bt2gpu_ctx* c, uint32_t n, uint64_t nbases, uint32_t maxOffs) {
 	const uint32_t W = 2 * maxOffs;
 	const size_t nn = (size_t)n + 1;
@@ -176,11 +185,7 @@ void ensure_batch(bt2gpu_ctx* c, uint32_t n, uint64_t nbases, uint32_t maxOffs) 
 	c->p_sav.ensure(nn * W * 2); c->p_sorted.ensure(nn * W); c->p_rank.ensure(nn * W * 2); c->p_sp2.ensure(nn * W * 2);
 	c->p_exr.ensure(nn * W * sizeof(ExRange16)); c->p_exrfw.ensure(nn * W);
 	c->p_nsp.ensure(nn * 4); c->p_nsmall.ensure(nn * 4); c->p_nexr.ensure(nn * 4); c->p_nelt.ensure(nn * 8); c->p_nadd.ensure(nn * 4);
-	const size_t S = c->sampSlots, MI = BT2_SAMPLE_MI;
-	c->s_ovr.ensure(S * 2 * MI * 2); c->s_ovp.ensure(S * 2 * MI * 2); c->s_ovv.ensure(S * 2 * MI * 2);
-	c->s_sr.ensure(S * MI * 2); c->s_sv.ensure(S * MI * 2); c->s_cv.ensure(S * MI * 2);
-	c->s_rn.ensure(S * W * 2); c->s_rcur.ensure(S * W * 2); c->s_rth.ensure(S * W * 2); c->s_rfl.ensure(S * W);
-	c->s_rco.ensure(S * W * 4); c->s_rcn.ensure(S * W * 2); c->s_rns.ensure(S * W * 2); c->s_mass.ensure(S * W * 8); c->s_elim.ensure(S * W);
+	ensure_sample(c, W);
 	// pools
 	Pools& p = c->pools;
 	static const size_t pdiv = getenv("BT2GPU_POOL_DIV") ? (size_t)std::max(1, atoi(getenv("BT2GPU_POOL_DIV"))) : 1;   // test knob: start with pools this much too small
@@ -298,11 +303,6 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 	PrioArrays pa; pa.sav = c->p_sav.as<uint16_t>(); pa.sorted = c->p_sorted.as<uint8_t>(); pa.rank = c->p_rank.as<uint16_t>(); pa.sp2 = c->p_sp2.as<uint16_t>();
 	pa.exr = c->p_exr.as<ExRange16>(); pa.exrfw = c->p_exrfw.as<uint8_t>(); pa.nsp = c->p_nsp.as<uint32_t>(); pa.nsmall = c->p_nsmall.as<uint32_t>();
 	pa.nexr = c->p_nexr.as<uint32_t>(); pa.nelt = c->p_nelt.as<uint64_t>(); pa.nelt_added = c->p_nadd.as<uint32_t>();
-	SampleArrays sa; sa.ov_rng = c->s_ovr.as<uint16_t>(); sa.ov_pos = c->s_ovp.as<uint16_t>(); sa.ov_val = c->s_ovv.as<uint16_t>();
-	sa.seen_rng = c->s_sr.as<uint16_t>(); sa.seen_val = c->s_sv.as<uint16_t>(); sa.conv_val = c->s_cv.as<uint16_t>();
-	sa.r_n = c->s_rn.as<uint16_t>(); sa.r_cur = c->s_rcur.as<uint16_t>(); sa.r_thresh = c->s_rth.as<uint16_t>(); sa.r_flags = c->s_rfl.as<uint8_t>();
-	sa.r_conv_off = c->s_rco.as<uint32_t>(); sa.r_conv_n = c->s_rcn.as<uint16_t>(); sa.r_nseen = c->s_rns.as<uint16_t>();
-	sa.mass = c->s_mass.as<double>(); sa.elim = c->s_elim.as<uint8_t>();
 	BtCtx bcx; bcx.P = c->P; bcx.pools = c->pools; bcx.states = states; bcx.probs = c->probs.as<Problem>();
 	bcx.cells = c->cells.as<uint8_t>(); bcx.cell_stride = c->cellStride; bcx.pcache = c->pcache.as<uint32_t>();
 	bcx.scratch = c->scratch.as<uint32_t>(); bcx.seq = ba.seq; bcx.qual = ba.qual; bcx.set_pens();
@@ -340,6 +340,17 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 			                                            L[3], cnt + C_EXT0, L[6], cnt + C_SAMP); LAUNCH(c);
 			const uint32_t* hc = read_counters(c);
 			ncur = hc[C_EXT0]; nsamp = hc[C_SAMP];
+			// reads with large seed ranges (repeats) are sampled row by row, a thread per read with ~16 KB of scratch each: the
+			// slots grow with the demand (a repeat-rich batch sends a tenth of its reads here), up to 128 Ki (2 GB)
+			if(nsamp > c->sampSlots && c->sampSlots < (1u << 17)) {
+				c->sampSlots = std::min<uint32_t>((nsamp + 4095u) & ~4095u, 1u << 17);
+				ensure_sample(c, W);
+			}
+			SampleArrays sa; sa.ov_rng = c->s_ovr.as<uint16_t>(); sa.ov_pos = c->s_ovp.as<uint16_t>(); sa.ov_val = c->s_ovv.as<uint16_t>();
+			sa.seen_rng = c->s_sr.as<uint16_t>(); sa.seen_val = c->s_sv.as<uint16_t>(); sa.conv_val = c->s_cv.as<uint16_t>();
+			sa.r_n = c->s_rn.as<uint16_t>(); sa.r_cur = c->s_rcur.as<uint16_t>(); sa.r_thresh = c->s_rth.as<uint16_t>(); sa.r_flags = c->s_rfl.as<uint8_t>();
+			sa.r_conv_off = c->s_rco.as<uint32_t>(); sa.r_conv_n = c->s_rcn.as<uint16_t>(); sa.r_nseen = c->s_rns.as<uint16_t>();
+			sa.mass = c->s_mass.as<double>(); sa.elim = c->s_elim.as<uint8_t>();
 			for(uint32_t b = 0; b < nsamp; b += c->sampSlots) {
 				const uint32_t k = std::min(c->sampSlots, nsamp - b);
 				k_prio2<<<nblk(k, 64), 64, 0, st>>>(c->dP, pools, states, L[2], c->hits.as<SeedHit>(), W, maxOffs, pa, sa, L[6], b, k); LAUNCH(c);
@@ -383,8 +394,10 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 		CK(cudaStreamSynchronize(st));
 		const volatile uint32_t* last = c->hbox->last; const uint32_t perr = c->hbox->perr;
 		if(perr & 32u) throw std::string("bt2gpu: internal error: a backtrace lane did not finish (k_bt watchdog)");
+		if(perr & 64u) throw std::string("bt2gpu: internal error: a DP problem's band is wider than the fill's lanes hold");
 		if(perr & 16u) throw std::string("bt2gpu: a read's minimum score is below -254: the -DENABLE_I16 build aligns it with the 16-bit score range, which this library does not implement");
-		if(perr) { char b[128]; snprintf(b, sizeof(b), "bt2gpu: device pool exhausted (mask %u); use smaller batches", perr); throw std::string(b); }
+		if(perr & 15u) throw PoolOverflow{perr & 15u};   // a bump-allocated pool ran out: do_run_grow() enlarges it and runs the batch again
+		if(perr) { char b[128]; snprintf(b, sizeof(b), "bt2gpu: internal error (device error mask %u)", perr); throw std::string(b); }
 		c->out_alns = (uint64_t)last[0] + last[1]; c->out_edits = (uint64_t)last[2] + last[3];
 		settle(c->d2hspan[c->cur], c->ctr.ms_d2h);   // the previous results in this set have been copied out
 		O.o_rr.ensure(((size_t)n + 1) * sizeof(bt2gpu_read_result));

@@ -89,6 +89,7 @@ bool parse_options(Options& o, const std::string& args, std::string& err) {
 		else if(t == "--n-ceil") { if(!(a = need(i))) return false; if(!parse_func(o.nCeil, *a)) { err = "bad --n-ceil"; return false; } }
 		else if(t == "--dpad") { if(!(a = need(i))) return false; p.maxhalf = atoi(a->c_str()); }
 		else if(t == "--gbar") { if(!(a = need(i))) return false; p.gapbar = std::max(1, atoi(a->c_str())); }
+		else if(t == "-M") { if(!(a = need(i))) return false; p.mhits = (int32_t)std::max(0, atoi(a->c_str())); p.msample = 1; p.khits = 1; sawK = false; }   // bt2_search.cpp:1177-1190
 		else if(t == "-k") { if(!(a = need(i))) return false; p.khits = std::max(1, atoi(a->c_str())); sawK = true; }
 		else if(t == "--mp") { if(!(a = need(i))) return false; // "MX,MN" (bt2_search.cpp ARG "mp")
 			int mx = 6, mn = 2; if(sscanf(a->c_str(), "%d,%d", &mx, &mn) < 2) mn = std::min(mn, mx); mmMax = mx; mmMin = std::min(mn, mx); }

@@ -154,8 +154,21 @@ template<int K> static void run_all(const DevParams& P, const std::vector<TProb>
 	}
 }
 
+// The reference's own known-answer values for Scoring::maxReadGaps / maxRefGaps (scoring.cpp:194-280, its SCORING_MAIN self-test):
+// case 1 = Scoring::base1() (match bonus 1, gaps 11 + 4 per position), case 2 = match bonus 4, gaps 25 + 10; minimum score 0.
+static void scoring_kats() {
+	DevParams P; memset(&P, 0, sizeof(P));
+	P.matchBonus = 1; P.rdGapOpen = P.rfGapOpen = 15; P.rdGapExt = P.rfGapExt = 4;
+	static const int rf1[12] = {0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 2}, rd1[12] = {0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2};
+	for(int i = 0; i < 12; i++) { CHECK(max_ref_gaps(P, 0, 10 + i) == rf1[i], "maxRefGaps(0, %d)", 10 + i); CHECK(max_read_gaps(P, 0, 10 + i) == rd1[i], "maxReadGaps(0, %d)", 10 + i); }
+	P.matchBonus = 4; P.rdGapOpen = P.rfGapOpen = 35; P.rdGapExt = P.rfGapExt = 10;
+	static const int rf2[7] = {0, 0, 1, 1, 1, 1, 2}, rd2[7] = {0, 1, 1, 1, 2, 2, 3};
+	for(int i = 0; i < 7; i++) { CHECK(max_ref_gaps(P, 0, 8 + i) == rf2[i], "case 2 maxRefGaps(0, %d)", 8 + i); CHECK(max_read_gaps(P, 0, 8 + i) == rd2[i], "case 2 maxReadGaps(0, %d)", 8 + i); }
+}
+
 int main(int argc, char** argv) {
 	const int n = argc > 1 ? atoi(argv[1]) : 200; const uint32_t seed = argc > 2 ? (uint32_t)atoi(argv[2]) : 99u;
+	scoring_kats();
 	DevParams P; memset(&P, 0, sizeof(P));
 	P.gapbar = 4; P.rdGapOpen = 8; P.rdGapExt = 3; P.rfGapOpen = 8; P.rfGapExt = 3; P.matchBonus = 0;
 	for(int q = 0; q < 256; q++) { const int qq = q < 40 ? q : 40; P.mmpens[q] = (uint8_t)(2 + (int)((qq / 40.0f) * 4)); P.npens[q] = 1; }

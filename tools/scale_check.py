@@ -9,7 +9,9 @@ beyond the 126 MB L2), 150 bp simulated reads, `--sensitive --dpad 12`.
   4. times bt2gpu_align_batch on the full read set (host buffers in, pinned results out).
 
 Prints one JSON line.  Needs a GPU and oracle/_ref (built by oracle/build_ref.sh where the reference sources exist).
-usage: scale_check.py [--ref-mbp 100] [--reads 1000000] [--sample 200000] [--i16]"""
+--repeats FRAC makes the reference repeat-rich (SURVEY 8d, C4 variant: FRAC of the text covered by copies of 50 families x 300 bp with 2 %
+divergence), the workload where -D streaks, several DPs per read, row sampling and MAPQ < 42 occur; --opts replaces the aligner options.
+usage: scale_check.py [--ref-mbp 100] [--reads 1000000] [--sample 200000] [--i16] [--repeats 0.1] [--opts "--very-sensitive --dpad 12"] [--tag c4rep]"""
 import argparse
 import importlib
 import json
@@ -30,10 +32,10 @@ def sorted_records(sam_bytes):
     return sorted(l for l in sam_bytes.split(b"\n") if l and not l.startswith(b"@"))
 
 
-def run_ref(binary, base, fq, out, threads, extra):
+def run_ref(binary, base, fq, out, threads, extra, pmult=100):
     env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="close", OMP_PLACES="cores")
     t0 = time.time()
-    r = subprocess.run([os.path.join(REFBIN, binary), "-x", base, "-U", fq, "-S", out, "-p", "100"] + OPTS.split() + extra,
+    r = subprocess.run([os.path.join(REFBIN, binary), "-x", base, "-U", fq, "-S", out, "-p", str(pmult)] + OPTS.split() + extra,
                        env=env, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(binary + " failed: " + r.stderr[-300:])
@@ -47,18 +49,37 @@ def main():
     ap.add_argument("--sample", type=int, default=200000)
     ap.add_argument("--i16", action="store_true")
     ap.add_argument("--work", default=os.path.join(ROOT, "bench_work"))
+    ap.add_argument("--repeats", type=float, default=0.0)
+    ap.add_argument("--opts", default=None)
+    ap.add_argument("--tag", default=None)
+    ap.add_argument("--seed", type=int, default=12346)
+    ap.add_argument("--keep", action="store_true", help="keep the index and the FASTQ files")
     args = ap.parse_args()
+    global OPTS
+    if args.opts:
+        OPTS = args.opts
     bench = importlib.import_module("bench")
     pkg = importlib.import_module("omp-bowtie2-prime_b200")
     os.makedirs(args.work, exist_ok=True)
     n_ref = int(args.ref_mbp * 1e6)
     threads = bench.cpu_cores()
-    out = {"ref_bp": n_ref, "reads": args.reads, "sample": args.sample, "opts": OPTS, "host_threads": threads}
+    out = {"config": args.tag, "ref_bp": n_ref, "repeat_fraction": args.repeats, "reads": args.reads, "sample": args.sample, "opts": OPTS, "host_threads": threads}
 
     # ---- reference + index (seed 12346: SURVEY C3)
-    base = os.path.join(args.work, "iid%dm" % int(args.ref_mbp))
-    rng = np.random.default_rng(12346)
+    base = os.path.join(args.work, "%s%dm" % ("rep" if args.repeats > 0 else "iid", int(args.ref_mbp)))
+    rng = np.random.default_rng(args.seed)
     codes = rng.integers(0, 4, size=n_ref, dtype=np.uint8)
+    if args.repeats > 0:
+        nfam, flen = 50, 300
+        fams = rng.integers(0, 4, size=(nfam, flen), dtype=np.uint8)
+        ncop = int(args.repeats * n_ref / flen)
+        for c0 in range(0, ncop, 65536):                    # copies in blocks: (block, flen) arrays, scattered with one fancy assignment
+            nb = min(65536, ncop - c0)
+            pos = rng.integers(0, n_ref - flen, size=nb)
+            cp = fams[rng.integers(0, nfam, size=nb)].copy()
+            m = rng.random((nb, flen)) < 0.02
+            cp[m] = (cp[m] + rng.integers(1, 4, size=int(m.sum()), dtype=np.uint8)) % 4
+            codes[pos[:, None] + np.arange(flen)[None, :]] = cp
     if not os.path.exists(base + ".4.bt2l"):
         seq = np.frombuffer(b"ACGT", dtype=np.uint8)[codes]
         with open(base + ".fa", "wb") as f:
@@ -111,6 +132,16 @@ def main():
     out["align_batch_reads_per_s"] = round(args.reads / best)
     out["phase_ms"] = {k: round(ctr[k], 2) for k in ("ms_seed", "ms_resolve", "ms_fill", "ms_bt", "ms_glue")}
     out["sa_probes_per_seed"] = round(ctr["sa_probes"] / max(ctr["seeds_searched"], 1), 2)
+    out["dp_problems_per_read"] = round(ctr["dp_problems"] / args.reads, 3)
+    out["lf_steps_per_read"] = round((ctr["lf_steps_search"] + ctr["lf_steps_extend"] + ctr["lf_steps_resolve"]) / args.reads, 2)
+    out["gcups_fill_kernel"] = round(ctr["dp_cells"] / (ctr["ms_fill"] * 1e-3) / 1e9, 1) if ctr["ms_fill"] > 0 else None
+    if args.reads <= (1 << 20):   # inputs resident in HBM: device time of the whole hot path (CUDA events)
+        gpu.upload(batch); gpu.run_resident(); gpu.counters(reset=True)
+        for _ in range(3):
+            gpu.run_resident()
+        c2 = gpu.counters()
+        out["resident_reads_per_s"] = round(3 * args.reads / (c2["ms_run"] * 1e-3))
+        out["resident_phase_ms_per_run"] = {k: round(c2[k] / 3, 2) for k in ("ms_seed", "ms_resolve", "ms_fill", "ms_bt", "ms_glue", "ms_run")}
     aligned = sum(1 for l in sorted_records(job.sam_bytes(batch, res, 1)) if not (int(l.split(b"\t")[1]) & 4))
     out["aligned_fraction"] = aligned / args.reads
     batch.close(); gpu.close()
@@ -126,6 +157,10 @@ def main():
         out["i16_records"] = len(want)
         out["i16_records_differing"] = sum(1 for a, b in zip(want, got) if a != b) + abs(len(want) - len(got))
         batch.close(); gpu16.close()
+    if not args.keep:
+        for f in (fq_all, fq_s, sam_ref):
+            if os.path.exists(f):
+                os.remove(f)
     print(json.dumps(out))
     return 0 if out["u8_records_differing"] == 0 and out.get("i16_records_differing", 0) == 0 else 1
 
