@@ -168,7 +168,7 @@ void setup_params(bt2gpu_ctx* c, const bt2gpu_params* p) {
 // scratch of the row sampler (k_prio2: RowSampler + Random1toN of SwDriver::prioritizeSATups), one slot per read sampled at a time
 void ensure_sample(bt2gpu_ctx* c, uint32_t W) {
 	const size_t S = c->sampSlots, MI = BT2_SAMPLE_MI;
-	c->s_ovr.ensure(S * 2 * MI * 2); c->s_ovp.ensure(S * 2 * MI * 2); c->s_ovv.ensure(S * 2 * MI * 2);
+	c->s_ovr.ensure(S * BT2_SAMPLE_HASH * 4); c->s_ovv.ensure(S * BT2_SAMPLE_HASH * 2);   // hash table of the sparse Random1toN (dev_prio.cuh)
 	c->s_sr.ensure(S * MI * 2); c->s_sv.ensure(S * MI * 2); c->s_cv.ensure(S * MI * 2);
 	c->s_rn.ensure(S * W * 2); c->s_rcur.ensure(S * W * 2); c->s_rth.ensure(S * W * 2); c->s_rfl.ensure(S * W);
 	c->s_rco.ensure(S * W * 4); c->s_rcn.ensure(S * W * 2); c->s_rns.ensure(S * W * 2); c->s_mass.ensure(S * W * 8); c->s_elim.ensure(S * W);
@@ -346,13 +346,14 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 				c->sampSlots = std::min<uint32_t>((nsamp + 4095u) & ~4095u, 1u << 17);
 				ensure_sample(c, W);
 			}
-			SampleArrays sa; sa.ov_rng = c->s_ovr.as<uint16_t>(); sa.ov_pos = c->s_ovp.as<uint16_t>(); sa.ov_val = c->s_ovv.as<uint16_t>();
+			SampleArrays sa; sa.hkey = c->s_ovr.as<uint32_t>(); sa.hval = c->s_ovv.as<uint16_t>();
 			sa.seen_rng = c->s_sr.as<uint16_t>(); sa.seen_val = c->s_sv.as<uint16_t>(); sa.conv_val = c->s_cv.as<uint16_t>();
 			sa.r_n = c->s_rn.as<uint16_t>(); sa.r_cur = c->s_rcur.as<uint16_t>(); sa.r_thresh = c->s_rth.as<uint16_t>(); sa.r_flags = c->s_rfl.as<uint8_t>();
 			sa.r_conv_off = c->s_rco.as<uint32_t>(); sa.r_conv_n = c->s_rcn.as<uint16_t>(); sa.r_nseen = c->s_rns.as<uint16_t>();
 			sa.mass = c->s_mass.as<double>(); sa.elim = c->s_elim.as<uint8_t>();
 			for(uint32_t b = 0; b < nsamp; b += c->sampSlots) {
 				const uint32_t k = std::min(c->sampSlots, nsamp - b);
+				CK(cudaMemsetAsync(sa.hkey, 0xff, (size_t)k * BT2_SAMPLE_HASH * 4, st));
 				k_prio2<<<nblk(k, 64), 64, 0, st>>>(c->dP, pools, states, L[2], c->hits.as<SeedHit>(), W, maxOffs, pa, sa, L[6], b, k); LAUNCH(c);
 			}
 		}

@@ -181,13 +181,16 @@ BT2_HD bool prio_stage1(const DevParams& P, const Pools& pools, ReadState& rs, c
 	return sample;
 }
 
-// ---- Stage 2 (rare): row sampling over the large ranges.
-// Sparse Random1toN: the swap list is the identity (or, once "converted", the sorted
-// complement of the values seen so far) plus an overlay of the swapped positions.
+// ---- Stage 2: row sampling over the large ranges (reads that fall into repeats).
+// Sparse Random1toN: the swap list of a range is the identity (or, once "converted", the sorted complement of the values
+// seen so far) plus an overlay of the swapped positions.  A read makes at most BT2GPU_MAX_ITER draws over all its ranges, a
+// range may have 65 535 rows: the overlay and the "seen" sets live in ONE open-addressing hash table per read (global memory,
+// cleared by the host before the launch), so that a draw costs a handful of probes whatever came before it.
+#define BT2_SAMPLE_HASH 4096u             // >= 3 * (BT2GPU_MAX_ITER + 8): two overlay entries and one seen entry per draw at most
+#define BT2_SAMPLE_EMPTY 0xffffffffu
 struct SampleWork {
-	// capacities are bounded by the number of draws (<= BT2GPU_MAX_ITER)
-	uint16_t* ov_rng; uint16_t* ov_pos; uint16_t* ov_val; uint32_t nov;      // [2*MAX_ITER]
-	uint16_t* seen_rng; uint16_t* seen_val; uint32_t nseen;                  // [MAX_ITER] unsorted, per range in draw order
+	uint32_t* hkey; uint16_t* hval;                                          // [BT2_SAMPLE_HASH]: key = range << 16 | position (overlay), bit 31 | range << 16 | value (seen)
+	uint16_t* seen_rng; uint16_t* seen_val; uint32_t nseen;                  // [MAX_ITER] unsorted, per range in draw order (read back when a range converts)
 	uint16_t* conv_val; uint32_t nconv;                                      // [MAX_ITER] sorted seen values of converted ranges
 	// per large range (index = position in sp2 minus nsmall), [W]
 	uint16_t* r_n; uint16_t* r_cur; uint16_t* r_thresh; uint8_t* r_flags;    // flags: 1 inited, 2 swaplist, 4 converted
@@ -195,22 +198,29 @@ struct SampleWork {
 	double*   mass; uint8_t* elim;                                           // RowSampler
 };
 
+BT2_HD uint32_t sample_slot(uint32_t key) { return (key * 2654435761u) >> 20; }   // 12 bits
+// slot holding `key`, or the empty slot where it belongs
+BT2_HD uint32_t sample_find(const SampleWork& s, uint32_t key) {
+	uint32_t h = sample_slot(key);
+	while(s.hkey[h] != BT2_SAMPLE_EMPTY && s.hkey[h] != key) h = (h + 1u) & (BT2_SAMPLE_HASH - 1u);
+	return h;
+}
+
 BT2_HD uint16_t r1n_base(const SampleWork& s, uint32_t ri, uint16_t j) {
 	if(!(s.r_flags[ri] & 4)) return j;
-	// j-th smallest value not among the sorted converted-seen values of this range
+	// j-th smallest value not among the sorted converted-seen values of this range: j + #{k : cv[k] - k <= j}
 	const uint16_t* cv = s.conv_val + s.r_conv_off[ri];
-	const uint32_t nc = s.r_conv_n[ri];
-	uint32_t v = j;
-	for(uint32_t k = 0; k < nc; k++) { if(cv[k] <= v) v++; else break; }
-	return (uint16_t)v;
+	uint32_t lo = 0, hi = s.r_conv_n[ri];
+	while(lo < hi) { const uint32_t mid = (lo + hi) >> 1; if((uint32_t)cv[mid] - mid <= (uint32_t)j) lo = mid + 1; else hi = mid; }
+	return (uint16_t)(j + lo);
 }
 BT2_HD uint16_t r1n_get(const SampleWork& s, uint32_t ri, uint16_t pos) {
-	for(uint32_t k = s.nov; k > 0; k--) if(s.ov_rng[k - 1] == ri && s.ov_pos[k - 1] == pos) return s.ov_val[k - 1];
-	return r1n_base(s, ri, pos);
+	const uint32_t key = (ri << 16) | pos, h = sample_find(s, key);
+	return s.hkey[h] == key ? s.hval[h] : r1n_base(s, ri, pos);
 }
 BT2_HD void r1n_set(SampleWork& s, uint32_t ri, uint16_t pos, uint16_t val) {
-	for(uint32_t k = 0; k < s.nov; k++) if(s.ov_rng[k] == ri && s.ov_pos[k] == pos) { s.ov_val[k] = val; return; }
-	s.ov_rng[s.nov] = (uint16_t)ri; s.ov_pos[s.nov] = pos; s.ov_val[s.nov] = val; s.nov++;
+	const uint32_t key = (ri << 16) | pos, h = sample_find(s, key);
+	s.hkey[h] = key; s.hval[h] = val;
 }
 
 BT2_HD uint16_t r1n_next(SampleWork& s, uint32_t ri, Rng& rnd) {
@@ -229,17 +239,12 @@ BT2_HD uint16_t r1n_next(SampleWork& s, uint32_t ri, Rng& rnd) {
 		return ret;
 	}
 	// "seen" list mode
-	bool again = true; uint16_t rn = 0;
-	const uint32_t seenSz = s.r_nseen[ri];
-	while(again) {
+	uint16_t rn = 0; uint32_t hs = 0;
+	while(true) {
 		rn = (uint16_t)(rnd.nextU32() % (uint32_t)n);
-		again = false;
-		uint32_t cnt = 0;
-		for(uint32_t k = 0; k < s.nseen && cnt < seenSz; k++) {
-			if(s.seen_rng[k] != ri) continue;
-			cnt++;
-			if(s.seen_val[k] == rn) { again = true; break; }
-		}
+		const uint32_t key = 0x80000000u | (ri << 16) | rn;
+		hs = sample_find(s, key);
+		if(s.hkey[hs] != key) { s.hkey[hs] = key; s.hval[hs] = 0; break; }   // not seen before
 	}
 	s.seen_rng[s.nseen] = (uint16_t)ri; s.seen_val[s.nseen] = rn; s.nseen++;
 	s.r_nseen[ri]++;
@@ -270,7 +275,7 @@ BT2_HD void prio_stage2(const DevParams& P, const Pools& pools, ReadState& rs, c
 	const uint32_t M = g.maxOffs, nsmall = w.nsmall, nl = w.nsp - w.nsmall;
 	const uint32_t maxelt = (uint32_t)P.mxIter;
 	Rng rnd = rs.rnd;
-	s.nov = s.nseen = s.nconv = 0;
+	s.nseen = s.nconv = 0;
 	double mass = 0.0f;
 	for(uint32_t i = 0; i < nl; i++) {
 		const SeedHit& sv = hits[w.sav[w.sp2[nsmall + i]]];

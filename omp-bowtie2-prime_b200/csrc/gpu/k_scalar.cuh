@@ -123,7 +123,8 @@ __global__ void __launch_bounds__(128, BT2_PRIO_BLOCKS_PER_SM) k_prio1(const Dev
 }
 
 struct SampleArrays { // per sampling slot
-	uint16_t* ov_rng; uint16_t* ov_pos; uint16_t* ov_val; uint16_t* seen_rng; uint16_t* seen_val; uint16_t* conv_val; // [slots * (2*MI | MI)]
+	uint32_t* hkey; uint16_t* hval;                                  // [slots * BT2_SAMPLE_HASH], keys cleared to BT2_SAMPLE_EMPTY before the launch
+	uint16_t* seen_rng; uint16_t* seen_val; uint16_t* conv_val;      // [slots * MI]
 	uint16_t* r_n; uint16_t* r_cur; uint16_t* r_thresh; uint8_t* r_flags; uint32_t* r_conv_off; uint16_t* r_conv_n; uint16_t* r_nseen;
 	double* mass; uint8_t* elim; // [slots * W]
 };
@@ -143,8 +144,8 @@ __global__ void k_prio2(const DevParams* __restrict__ Pp, const Pools pools, Rea
 	PrioWork w; prio_work(pa, ai, W, w);
 	w.nsp = pa.nsp[ai]; w.nsmall = pa.nsmall[ai]; w.nexr = pa.nexr[ai]; w.nelt = pa.nelt[ai]; w.nelt_added = pa.nelt_added[ai];
 	SampleWork s;
-	const size_t o2 = (size_t)j * 2 * BT2_SAMPLE_MI, o1 = (size_t)j * BT2_SAMPLE_MI, ow = (size_t)j * W;
-	s.ov_rng = sa.ov_rng + o2; s.ov_pos = sa.ov_pos + o2; s.ov_val = sa.ov_val + o2;
+	const size_t oh = (size_t)j * BT2_SAMPLE_HASH, o1 = (size_t)j * BT2_SAMPLE_MI, ow = (size_t)j * W;
+	s.hkey = sa.hkey + oh; s.hval = sa.hval + oh;
 	s.seen_rng = sa.seen_rng + o1; s.seen_val = sa.seen_val + o1; s.conv_val = sa.conv_val + o1;
 	s.r_n = sa.r_n + ow; s.r_cur = sa.r_cur + ow; s.r_thresh = sa.r_thresh + ow; s.r_flags = sa.r_flags + ow;
 	s.r_conv_off = sa.r_conv_off + ow; s.r_conv_n = sa.r_conv_n + ow; s.r_nseen = sa.r_nseen + ow; s.mass = sa.mass + ow; s.elim = sa.elim + ow;

@@ -22,6 +22,9 @@ CASES = {
     "syn100_default": ("syn", "syn100", "", "syn100_default.sam"),
     "syn100_k5": ("syn", "syn100", "-k 5", "syn100_k5.sam"),
     "synN120_default": ("synN", "synN120", "", "synN120_default.sam"),
+    # high-copy repeats: seed ranges of 128+ rows (row sampling in "seen list" mode and its conversion), -D streaks, several DPs per read
+    "synR100_default": ("synR", "synR100", "", "synR100_default.sam"),
+    "synR100_k3_vs": ("synR", "synR100", "-k 3 --very-sensitive", "synR100_k3_vs.sam"),
     # the reference built with -DENABLE_I16 and run with --no-sse8: its 16-bit DP path (other RNG protocol)
     "syn100_k5_i16": ("syn", "syn100", "-k 5 --i16 --no-sse8", "syn100_k5_i16.sam"),
     "syn150_sens_i16": ("syn", "syn150", "--i16 --no-sse8 --sensitive --dpad 12", "syn150_sens_i16.sam"),
@@ -54,6 +57,9 @@ def index_base(name):
     elif name == "synN":
         fa = base + ".fa"
         gen(["ref", fa, 200000, "--seed", 99, "--repeats", 0.1, "--nseq", 2, "--ngaps", 40])
+    elif name == "synR":
+        fa = base + ".fa"
+        gen(["ref", fa, 200000, "--seed", 77, "--repeats", 0.45, "--nfam", 2])
     elif name.startswith("iid"):  # iid<len>
         fa = base + ".fa"
         gen(["ref", fa, int(name[3:]), "--seed", 12345])
@@ -73,6 +79,10 @@ def reads_path(name):
     if name == "synN120":
         index_base("synN")
         gen(["reads", os.path.join(WORK, "synN.fa"), p, 1500, 120, "--seed", 9, "--randqual"])
+        return p
+    if name == "synR100":
+        index_base("synR")
+        gen(["reads", os.path.join(WORK, "synR.fa"), p, 1500, 100, "--seed", 11, "--subst", 0.02])
         return p
     index_base("syn")
     fa = os.path.join(WORK, "syn.fa")

@@ -59,7 +59,7 @@ int main(int argc, char** argv) {
 	orc::Fm fm(hix);
 	const uint32_t n = in->n;
 	// pools
-	std::vector<Chunk> chunks(4 * n + 1024); std::vector<SatEntry> sats(64 * n + 4096); std::vector<AlnRec> alnp(8 * n + 1024); std::vector<uint32_t> editp(256 * n + 4096);
+	std::vector<Chunk> chunks(64 * (size_t)n + 1024); std::vector<SatEntry> sats(2048 * (size_t)n + 4096); std::vector<AlnRec> alnp(8 * n + 1024); std::vector<uint32_t> editp(256 * n + 4096);
 	uint32_t ctop = 0, stop = 0, atop = 0, etop = 0, perr = 0;
 	Pools pools; pools.chunks = chunks.data(); pools.chunk_top = &ctop; pools.chunk_cap = (uint32_t)chunks.size();
 	pools.sats = sats.data(); pools.sat_top = &stop; pools.sat_cap = (uint32_t)sats.size();
@@ -73,7 +73,7 @@ int main(int argc, char** argv) {
 	std::vector<SeedHit> hits(W);
 	std::vector<uint16_t> wsav(W), wrank(W), wsp2(W); std::vector<uint8_t> wsorted(W), wexrfw(W); std::vector<ExRange16> wexr(W);
 	const uint32_t MI = BT2GPU_MAX_ITER + 8;
-	std::vector<uint16_t> ov_rng(2 * MI), ov_pos(2 * MI), ov_val(2 * MI), seen_rng(MI), seen_val(MI), conv_val(MI), r_n(W), r_cur(W), r_thresh(W), r_conv_n(W), r_nseen(W);
+	std::vector<uint32_t> hkey(BT2_SAMPLE_HASH); std::vector<uint16_t> hval(BT2_SAMPLE_HASH), seen_rng(MI), seen_val(MI), conv_val(MI), r_n(W), r_cur(W), r_thresh(W), r_conv_n(W), r_nseen(W);
 	std::vector<uint8_t> r_flags(W), elim(W); std::vector<uint32_t> r_conv_off(W); std::vector<double> mass(W);
 	std::vector<uint8_t> cells(fill_cell_bytes(BT2GPU_MAX_ROWS, BT2_KMAX));
 	const bool exactFill = getenv("EMU_EXACT_FILL") != nullptr; uint32_t nprob = 0; std::vector<uint32_t> pcache(BT2_PC_WORDS, 0);
@@ -114,7 +114,7 @@ int main(int argc, char** argv) {
 			const bool sample = prio_stage1(P, pools, rs, hits.data(), g, w);
 			if(rs.numRanges == 0 || rs.nonzTot == 0) { rs.flags |= BT2GPU_RF_NO_SEED_HITS; break; }
 			if(sample) {
-				SampleWork s; s.ov_rng = ov_rng.data(); s.ov_pos = ov_pos.data(); s.ov_val = ov_val.data(); s.seen_rng = seen_rng.data(); s.seen_val = seen_val.data();
+				SampleWork s; std::fill(hkey.begin(), hkey.end(), BT2_SAMPLE_EMPTY); s.hkey = hkey.data(); s.hval = hval.data(); s.seen_rng = seen_rng.data(); s.seen_val = seen_val.data();
 				s.conv_val = conv_val.data(); s.r_n = r_n.data(); s.r_cur = r_cur.data(); s.r_thresh = r_thresh.data(); s.r_flags = r_flags.data();
 				s.r_conv_off = r_conv_off.data(); s.r_conv_n = r_conv_n.data(); s.r_nseen = r_nseen.data(); s.mass = mass.data(); s.elim = elim.data();
 				prio_stage2(P, pools, rs, hits.data(), g, w, s);

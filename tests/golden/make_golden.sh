@@ -34,5 +34,12 @@ python "$ROOT/tools/gen_data.py" ref "$T/synN.fa" 200000 --seed 99 --repeats 0.1
 "$B/bowtie2-build-l" "$T/synN.fa" "$T/synN" >/dev/null 2>&1
 python "$ROOT/tools/gen_data.py" reads "$T/synN.fa" "$T/synN120.fq" 1500 120 --seed 9 --randqual
 run synN120_default         "$T/synN" "$T/synN120.fq" ""
+# high-copy repeats (2 families x ~150 copies with 2 % divergence): seed ranges of 128+ rows, i.e. Random1toN's "seen list" mode and
+# its conversion to a swap list, RowSampler masses, -D streaks, several DPs per read
+python "$ROOT/tools/gen_data.py" ref "$T/synR.fa" 200000 --seed 77 --repeats 0.45 --nfam 2
+"$B/bowtie2-build-l" "$T/synR.fa" "$T/synR" >/dev/null 2>&1
+python "$ROOT/tools/gen_data.py" reads "$T/synR.fa" "$T/synR100.fq" 1500 100 --seed 11 --subst 0.02
+run synR100_default         "$T/synR" "$T/synR100.fq" ""
+run synR100_k3_vs           "$T/synR" "$T/synR100.fq" "-k 3 --very-sensitive"
 rm -rf "$T"
 ls -la "$HERE"

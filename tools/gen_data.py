@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Deterministic synthetic reference + simulated reads (SURVEY 8(d) C2-C4 restated; the
 reference's own scripts/sim needs Math::Random, absent here).
-  gen_data.py ref  OUT.fa  LEN  [--seed S] [--repeats FRAC] [--nseq K] [--ngaps G]
+  gen_data.py ref  OUT.fa  LEN  [--seed S] [--repeats FRAC] [--nfam F] [--nseq K] [--ngaps G]
   gen_data.py reads REF.fa OUT.fq N LEN [--seed S] [--subst 0.01] [--indel 0.10] [--randqual] [--nfrac 0.0]
 """
 import sys, argparse
@@ -15,7 +15,7 @@ def gen_ref(a):
     codes = rng.integers(0, 4, size=a.len, dtype=np.uint8)
     if a.repeats > 0:
         # repeat families: 50 families x 300 bp, copies with 2% divergence until FRAC of the text is covered
-        nfam, flen = 50, 300
+        nfam, flen = a.nfam, 300
         fams = rng.integers(0, 4, size=(nfam, flen), dtype=np.uint8)
         ncopies = int(a.repeats * a.len / flen)
         pos = rng.integers(0, a.len - flen, size=ncopies)
@@ -77,7 +77,7 @@ def gen_reads(a):
 def main():
     ap = argparse.ArgumentParser(); sub = ap.add_subparsers(dest='cmd')
     p = sub.add_parser('ref'); p.add_argument('out'); p.add_argument('len', type=int); p.add_argument('--seed', type=int, default=12345)
-    p.add_argument('--repeats', type=float, default=0.0); p.add_argument('--nseq', type=int, default=1); p.add_argument('--ngaps', type=int, default=0)
+    p.add_argument('--repeats', type=float, default=0.0); p.add_argument('--nfam', type=int, default=50); p.add_argument('--nseq', type=int, default=1); p.add_argument('--ngaps', type=int, default=0)
     p = sub.add_parser('reads'); p.add_argument('ref'); p.add_argument('out'); p.add_argument('n', type=int); p.add_argument('len', type=int)
     p.add_argument('--seed', type=int, default=2); p.add_argument('--subst', type=float, default=0.01); p.add_argument('--indel', type=float, default=0.10)
     p.add_argument('--randqual', action='store_true'); p.add_argument('--nfrac', type=float, default=0.0); p.add_argument('--maxlen', type=int, default=0)
