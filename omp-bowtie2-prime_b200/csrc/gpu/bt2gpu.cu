@@ -486,7 +486,8 @@ void do_align_pipelined(bt2gpu_ctx* c, const bt2gpu_reads* in, bt2gpu_results* o
 		const uint32_t small = std::max<uint32_t>(chunk / (er ? (uint32_t)std::max(1, atoi(er)) : 8u), 1u);
 		uint32_t pos = std::min(n, small);
 		cut.push_back(pos);
-		while(n - pos > chunk + small) { pos += chunk; cut.push_back(pos); }
+		const uint32_t lastMax = std::max(chunk, std::min(chunk + small, c->maxBatch));   // no sub-batch beyond BT2GPU_BATCH
+		while(n - pos > lastMax) { pos += chunk; cut.push_back(pos); }
 		static const char* et = getenv("BT2GPU_PIPE_TAIL");
 		if((et ? atoi(et) != 0 : false) && n - pos > small && small < chunk) { pos = n - small; cut.push_back(pos); }
 		if(pos < n) cut.push_back(n);
@@ -578,18 +579,26 @@ __global__ void k_na_export(const NoAllocScratch* sc, const uint64_t* flags_off,
 
 // device address of the scratch array, resolved once per device with that device current: in host code the array's name is a
 // host-side stand-in, not a device address
-NoAllocScratch* noalloc_scratch(int device) {
-	static std::mutex mu;
-	static void* ptr[64] = { nullptr };
+struct NoAllocDevice { void* ptr = nullptr; cudaEvent_t done = nullptr; bool used = false; };
+static std::mutex g_na_mu;
+static NoAllocDevice g_na_dev[64];
+// Set-up, once per device, with that device current (called by bt2gpu_create, so that the first bt2gpu_fill_noalloc of a device does
+// nothing but enqueue): the address of the scratch array, the modules of the three kernels (lazy loading), and the event that orders
+// consecutive calls on different streams.
+NoAllocDevice& noalloc_device(int device) {
 	if(device < 0 || device >= 64) throw std::string("bt2gpu_fill_noalloc: device ordinal out of range");
-	std::lock_guard<std::mutex> lk(mu);
-	if(!ptr[device]) {
+	std::lock_guard<std::mutex> lk(g_na_mu);
+	NoAllocDevice& d = g_na_dev[device];
+	if(!d.ptr) {
 		void* p = nullptr;
 		CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
 		if(!p) throw std::string("bt2gpu_fill_noalloc: cudaGetSymbolAddress returned no address");
-		ptr[device] = p;
+		cudaFuncAttributes fa;
+		CK(cudaFuncGetAttributes(&fa, k_na_setup)); CK(cudaFuncGetAttributes(&fa, k_na_export)); CK(cudaFuncGetAttributes(&fa, k_fill<BT2_NA_K, false>));
+		CK(cudaEventCreateWithFlags(&d.done, cudaEventDisableTiming));
+		d.ptr = p;
 	}
-	return reinterpret_cast<NoAllocScratch*>(ptr[device]);
+	return d;
 }
 
 } // namespace
@@ -716,6 +725,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		c->counters.ensure(C_N * 4); c->stats.ensure(32 * 8); c->pooltops.ensure(16); c->poolerr.ensure(4);
 		{ void* hb = nullptr; CK(cudaHostAlloc(&hb, sizeof(HostBox), cudaHostAllocMapped)); memset(hb, 0, sizeof(HostBox));
 		  c->hbox = reinterpret_cast<volatile HostBox*>(hb); void* db = nullptr; CK(cudaHostGetDevicePointer(&db, hb, 0)); c->dbox = reinterpret_cast<HostBox*>(db); }
+		noalloc_device(device);   // bt2gpu_fill_noalloc's per-device set-up happens here, not inside its first call
 		CK(cudaDeviceSynchronize());
 	} catch(const std::string& e) {
 		if(err && errlen) snprintf(err, errlen, "%s", e.c_str());
@@ -725,9 +735,11 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 	return c;
 }
 
+// every entry point runs with the context's device current and puts the caller's device back before it returns
+struct DeviceScope { int prev = -1; explicit DeviceScope(int dev) { cudaGetDevice(&prev); if(prev != dev) cudaSetDevice(dev); else prev = -1; } ~DeviceScope() { if(prev >= 0) cudaSetDevice(prev); } };
 #define API_GUARD(...) \
 	if(!ctx) return -1; \
-	try { cudaSetDevice(ctx->device); __VA_ARGS__; } catch(const std::string& e) { ctx->err = e; ctx->spans.clear(); ctx->evused = 0; return -2; } \
+	try { DeviceScope ds_(ctx->device); __VA_ARGS__; } catch(const std::string& e) { ctx->err = e; ctx->spans.clear(); ctx->evused = 0; return -2; } \
 	return 0;
 
 int bt2gpu_upload(bt2gpu_ctx* ctx, const bt2gpu_reads* in) {
@@ -830,14 +842,22 @@ int bt2gpu_fill_noalloc(bt2gpu_ctx* ctx, void* stream, uint32_t nprob, const uin
 		if(!d_seq_off || !d_seq || !d_qual || !d_rows || !d_cols || !d_rf_off || !d_rf || !d_minsc || !d_flags_off || !d_flags || !d_cand || !d_ncand || !d_lrmax)
 			throw std::string("bt2gpu_fill_noalloc: null argument");
 		if(nprob == 0) return 0;
-		NoAllocScratch* sc = noalloc_scratch(ctx->device);
+		NoAllocDevice& nd = noalloc_device(ctx->device);   // (resolved by bt2gpu_create already)
+		NoAllocScratch* sc = reinterpret_cast<NoAllocScratch*>(nd.ptr);
 		cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+		// all calls on a device share the scratch: a call waits (on the device, stream-ordered) for the previous call's kernels, whatever
+		// stream they ran on.  Not under stream capture, where an event recorded outside the capture cannot be waited for.
+		cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+		if(cudaStreamIsCapturing(st, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+		std::lock_guard<std::mutex> lk(g_na_mu);
+		if(cap == cudaStreamCaptureStatusNone && nd.used) CK(cudaStreamWaitEvent(st, nd.done, 0));
 		k_na_setup<<<nblk(std::max(nprob, 32u), 128), 128, 0, st>>>(sc, nprob, d_seq_off, d_rows, d_cols, d_rf_off, d_rf, d_minsc);
 		FillArgs fa; fa.probs = sc->probs; fa.nprob = nprob; fa.states = sc->states; fa.seq = d_seq; fa.qual = d_qual; fa.cells = sc->cells; fa.cell_stride = BT2_NA_STRIDE;
 		fa.pcache = nullptr; fa.hef_dbg = nullptr; fa.stats = sc->stats; fa.error = sc->error; fa.exact = 0;
 		launch_fill(BT2_NA_K, false, ctx->dP, fa, st);   // the production kernel, banded per problem; K = 16 holds any band
 		k_na_export<<<nprob, 256, 0, st>>>(sc, d_flags_off, d_flags, d_cand, d_ncand, d_lrmax);
 		CK(cudaPeekAtLastError());
+		if(cap == cudaStreamCaptureStatusNone) { CK(cudaEventRecord(nd.done, st)); nd.used = true; }
 	})
 }
 

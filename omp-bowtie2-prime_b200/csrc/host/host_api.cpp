@@ -1,5 +1,6 @@
 // C-ABI of libbt2host.so (include/bt2host.h).
 #include <unistd.h>
+#include <fcntl.h>
 #include <cerrno>
 #include "host_internal.hpp"
 #include <cstdio>
@@ -128,8 +129,10 @@ int bt2host_sam_write(const bt2host_job* job, const bt2host_batch* b, const bt2g
 		return true;
 	};
 	const off_t base = lseek(fd, 0, SEEK_CUR);
+	const int fl = fcntl(fd, F_GETFL);
+	const bool append = fl >= 0 && (fl & O_APPEND);   // pwrite ignores its offset on an O_APPEND descriptor (Linux): blocks would land in completion order
 	bool ok = true;
-	if(base >= 0 && nt > 1) {   // a seekable file: the blocks are written side by side at their final offsets
+	if(base >= 0 && nt > 1 && !append) {   // a seekable file: the blocks are written side by side at their final offsets
 		#pragma omp parallel for num_threads(nt) schedule(static, 1) reduction(&&: ok)
 		for(int t = 0; t < nt; t++) ok = ok && put(fd, parts[(size_t)t].data(), parts[(size_t)t].size(), base + (off_t)offs[(size_t)t]);
 		if(ok && lseek(fd, base + (off_t)tot, SEEK_SET) < 0) ok = false;

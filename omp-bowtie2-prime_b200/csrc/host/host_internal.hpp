@@ -64,6 +64,7 @@ struct Job {
 	std::vector<std::string> sinkparts;   // SAM text of the sink's blocks
 	char* file_buffer(size_t n);          // >= n bytes, not initialised, owned by the job
 	char* filemem = nullptr; size_t filecap = 0;
+	mutable uint64_t range_next_id = 0;   // reads handed out by batch_from_fastq_range so far (ranges are taken in file order, from offset 0)
 	~Job();
 };
 
@@ -81,6 +82,7 @@ struct Batch {
 	std::vector<uint32_t> seed;
 	std::vector<int32_t> minsc, nceil, interval;
 	std::vector<std::string> names;
+	uint64_t first_id = 0;   // global index (Read::rdid) of the batch's first read: a read without a name is named by its rdid
 	bt2gpu_reads view;
 	void finalize();
 };

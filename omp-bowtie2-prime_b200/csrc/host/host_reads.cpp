@@ -188,7 +188,7 @@ static void add_read(const Job& job, Batch& b, std::string name, const std::stri
 	size_t rem = s.size() - t5;
 	size_t t3 = std::min<size_t>((size_t)job.opt.trim3, rem);
 	size_t len = rem - t3;
-	if(name.empty()) name = std::to_string(b.names.size());
+	if(name.empty()) name = std::to_string(b.first_id + b.names.size());   // the reference names it by its global read id
 	const size_t base = b.seq.size();
 	for(size_t i = 0; i < len; i++) {
 		int c = s[t5 + i]; if(c == '.') c = 'N';
@@ -363,7 +363,7 @@ static int fastq_fast(const Job& job, Batch& b, const std::string& path, uint64_
 			a++;
 		}
 		std::string name(buf.data() + ls[h] + 1, line_len(h) - 1);
-		if(name.empty()) name = std::to_string(i);
+		if(name.empty()) name = std::to_string(b.first_id + i);   // the reference names it by its global read id
 		b.seed[i] = gen_rand_seed(oseq, oq, L, name, job.opt.seed);
 		b.names[i] = std::move(name);
 	}
@@ -375,6 +375,7 @@ static int fastq_fast(const Job& job, Batch& b, const std::string& path, uint64_
 }
 
 bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_t skip, uint64_t maxn, std::string& err) {
+	b.first_id = skip;
 	const int r = fastq_fast(job, b, path, 0, 0, skip, maxn, nullptr, err);
 	if(r == 0) return batch_from_fastq_serial(job, b, path, skip, maxn, err);
 	return r > 0;
@@ -382,7 +383,10 @@ bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_
 
 // One range of a FASTQ file for a streaming caller: the records that lie completely inside [offset, offset + max_bytes).
 bool batch_from_fastq_range(const Job& job, Batch& b, const std::string& path, uint64_t offset, uint64_t max_bytes, uint64_t* next_off, std::string& err) {
+	if(offset == 0) job.range_next_id = 0;         // ranges are taken in file order (stream.py); unnamed reads get their global index
+	b.first_id = job.range_next_id;
 	const int r = fastq_fast(job, b, path, offset, max_bytes, 0, 0, next_off, err);
+	if(r > 0) job.range_next_id += b.names.size();
 	if(r == 0) err = "FASTQ layout needs the serial parser (CR line ends, blank lines or a truncated record): read the whole file with bt2host_batch_from_fastq";
 	return r > 0;
 }

@@ -61,25 +61,67 @@ def _existing(g, gpu, a):
     return FL, cand, ncand, lrmax
 
 
-def _noalloc(g, gpu, a, torch, poison, stream=None):
-    """bt2gpu_fill_noalloc: device pointers in and out, work enqueued on `stream` (None: the legacy default stream)"""
+def _noalloc_prepare(a, torch, poison):
     n, nf = a["n"], a["nflags"]
     dev = torch.device("cuda", 0)
     up = lambda x: torch.from_numpy(x.view(np.uint8) if x.dtype != np.uint8 else x).to(dev)     # bytes of the array, as is
     d = {k: up(a[k]) for k in ("seq_off", "seq", "qual", "rows", "cols", "rf_off", "rf", "minsc", "fl_off")}
-    o_fl = torch.full((nf,), poison, dtype=torch.uint8, device=dev)
-    o_cand = torch.zeros(256 * n * 2, dtype=torch.uint8, device=dev)
-    o_ncand = torch.full((n * 4,), poison, dtype=torch.uint8, device=dev)
-    o_lrmax = torch.full((n * 4,), poison, dtype=torch.uint8, device=dev)
-    torch.cuda.synchronize()
+    o = {"fl": torch.full((nf,), poison, dtype=torch.uint8, device=dev), "cand": torch.zeros(256 * n * 2, dtype=torch.uint8, device=dev),
+         "ncand": torch.full((n * 4,), poison, dtype=torch.uint8, device=dev), "lrmax": torch.full((n * 4,), poison, dtype=torch.uint8, device=dev)}
+    return d, o
+
+
+def _noalloc_launch(g, gpu, a, d, o, stream=None):
+    """bt2gpu_fill_noalloc: device pointers in and out, work only ENQUEUED on `stream` (None: the legacy default stream)"""
     g.bt2gpu_fill_noalloc.restype = C.c_int
     g.bt2gpu_fill_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32] + [C.c_void_p] * 13
-    rc = g.bt2gpu_fill_noalloc(gpu.ptr, C.c_void_p(stream.cuda_stream) if stream is not None else None, n, d["seq_off"].data_ptr(), d["seq"].data_ptr(), d["qual"].data_ptr(), d["rows"].data_ptr(),
-                               d["cols"].data_ptr(), d["rf_off"].data_ptr(), d["rf"].data_ptr(), d["minsc"].data_ptr(), d["fl_off"].data_ptr(),
-                               o_fl.data_ptr(), o_cand.data_ptr(), o_ncand.data_ptr(), o_lrmax.data_ptr())
+    rc = g.bt2gpu_fill_noalloc(gpu.ptr, C.c_void_p(stream.cuda_stream) if stream is not None else None, a["n"], d["seq_off"].data_ptr(), d["seq"].data_ptr(),
+                               d["qual"].data_ptr(), d["rows"].data_ptr(), d["cols"].data_ptr(), d["rf_off"].data_ptr(), d["rf"].data_ptr(),
+                               d["minsc"].data_ptr(), d["fl_off"].data_ptr(), o["fl"].data_ptr(), o["cand"].data_ptr(), o["ncand"].data_ptr(), o["lrmax"].data_ptr())
     assert rc == 0, g.bt2gpu_last_error(gpu.ptr)
+
+
+def _collect(o):
+    return (o["fl"].cpu().numpy(), o["cand"].cpu().numpy().view(np.uint16), o["ncand"].cpu().numpy().view(np.uint32), o["lrmax"].cpu().numpy().view(np.int32))
+
+
+def _noalloc(g, gpu, a, torch, poison, stream=None):
+    d, o = _noalloc_prepare(a, torch, poison)
     torch.cuda.synchronize()
-    return (o_fl.cpu().numpy(), o_cand.cpu().numpy().view(np.uint16), o_ncand.cpu().numpy().view(np.uint32), o_lrmax.cpu().numpy().view(np.int32))
+    _noalloc_launch(g, gpu, a, d, o, stream)
+    torch.cuda.synchronize()
+    return _collect(o)
+
+
+def _same(a, got, want, what):
+    FL, cand, ncand, lrmax = want
+    gFL, gcand, gncand, glrmax = got
+    assert np.array_equal(glrmax, lrmax), what + ": lrmax"
+    assert np.array_equal(gncand, ncand), what + ": ncand"
+    for i in range(a["n"]):
+        assert np.array_equal(gcand[256 * i:256 * i + ncand[i]], cand[256 * i:256 * i + ncand[i]]), "%s problem %d: candidates" % (what, i)
+    assert np.array_equal(gFL, FL), what + ": flags"
+
+
+def test_fill_noalloc_calls_on_two_streams_are_ordered():
+    """Two calls enqueued back to back on two different non-default streams, nothing synchronised in between: they share the static scratch,
+    so the second one's kernels must wait for the first one's (the library orders them with an event) -- both results are right."""
+    torch = pytest.importorskip("torch")
+    job = pkg.Job(common.index_base("lambda"), "")
+    gpu = pkg.GpuAligner(job, 0)
+    g = pkg.load_gpu()
+    rng = np.random.default_rng(77)
+    a1 = _pack(_problems(rng, MAXP, [(160, 199), (150, 199)])); a2 = _pack(_problems(rng, 90, [(150, 199), (33, 60)]))
+    w1, w2 = _existing(g, gpu, a1), _existing(g, gpu, a2)
+    s1, s2 = torch.cuda.Stream(device=0), torch.cuda.Stream(device=0)
+    for rep in range(3):
+        (d1, o1), (d2, o2) = _noalloc_prepare(a1, torch, 0x11), _noalloc_prepare(a2, torch, 0x22)
+        torch.cuda.synchronize()
+        _noalloc_launch(g, gpu, a1, d1, o1, s1)
+        _noalloc_launch(g, gpu, a2, d2, o2, s2)        # enqueued while the first call's kernels are still running
+        torch.cuda.synchronize()
+        _same(a1, _collect(o1), w1, "stream 1 (rep %d)" % rep); _same(a2, _collect(o2), w2, "stream 2 (rep %d)" % rep)
+    gpu.close()
 
 
 def test_fill_noalloc_equals_existing_entry_point_twice():
