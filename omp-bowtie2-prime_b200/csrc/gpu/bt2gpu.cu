@@ -109,7 +109,8 @@ uint32_t fill_K_of(const DevParams& P, uint32_t L, int32_t minsc, bool exact) {
 	const int rg = max_read_gaps(P, minsc, L), fg = max_ref_gaps(P, minsc, L);
 	int64_t maxgap = rg > fg ? rg : fg; if(maxgap > P.maxhalf) maxgap = P.maxhalf; if(maxgap < 0) maxgap = 0;
 	int64_t cols = (int64_t)L + 4 * maxgap; if(cols > BT2GPU_MAX_COLS - 1) cols = BT2GPU_MAX_COLS - 1;
-	int dlo, dhi; fill_band(P, (int)L, (int)cols, minsc < -254 ? -254 : minsc, exact, dlo, dhi);
+	const bool i16 = P.i16 && (!P.enable8 || minsc < -254);      // the problem's path (dev_step.cuh)
+	int dlo, dhi; fill_band(P, (int)L, (int)cols, (!i16 && minsc < -254) ? -254 : minsc, exact, dlo, dhi);
 	return fill_K_for(dhi - dlo + 1);
 }
 
@@ -158,7 +159,7 @@ void setup_params(bt2gpu_ctx* c, const bt2gpu_params* p) {
 	P.nofw = p->nofw; P.norc = p->norc; P.gapbar = p->gapbar;
 	P.rdGapOpen = p->rdGapConst + p->rdGapLinear; P.rdGapExt = p->rdGapLinear;
 	P.rfGapOpen = p->rfGapConst + p->rfGapLinear; P.rfGapExt = p->rfGapLinear;
-	P.matchBonus = p->matchBonus; P.i16 = p->i16; P.i16path = (p->i16 && !p->enable8) ? 1 : 0;
+	P.matchBonus = p->matchBonus; P.i16 = p->i16;
 	for(int i = 0; i < 256; i++) {
 		P.mmpens[i] = (uint8_t)std::min(255, std::max(0, p->mmpens[i]));
 		P.npens[i] = (uint8_t)std::min(255, std::max(0, p->npens[i]));
@@ -396,7 +397,7 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 		const volatile uint32_t* last = c->hbox->last; const uint32_t perr = c->hbox->perr;
 		if(perr & 32u) throw std::string("bt2gpu: internal error: a backtrace lane did not finish (k_bt watchdog)");
 		if(perr & 64u) throw std::string("bt2gpu: internal error: a DP problem's band is wider than the fill's lanes hold");
-		if(perr & 16u) throw std::string("bt2gpu: a read's minimum score is below -254: the -DENABLE_I16 build aligns it with the 16-bit score range, which this library does not implement");
+		if(perr & 16u) throw std::string("bt2gpu: a read's minimum score is below -28416, beyond the score range of the 16-bit DP path");
 		if(perr & 15u) throw PoolOverflow{perr & 15u};   // a bump-allocated pool ran out: do_run_grow() enlarges it and runs the batch again
 		if(perr) { char b[128]; snprintf(b, sizeof(b), "bt2gpu: internal error (device error mask %u)", perr); throw std::string(b); }
 		c->out_alns = (uint64_t)last[0] + last[1]; c->out_edits = (uint64_t)last[2] + last[3];

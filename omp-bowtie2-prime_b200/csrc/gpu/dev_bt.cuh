@@ -146,6 +146,7 @@ struct BtMachine {
 	int rows, dlo;                    // core diagonals: dlo <= col-row < dlo + dspan
 	uint32_t dspan;
 	int d0; uint32_t lgK, yy;         // fill layout (dev_common.cuh)
+	bool pi16;                        // the problem runs on the reference's 16-bit path (prob_i16)
 	uint32_t ncand;
 	Rng rnd; uint32_t hw, nsteps;     // nsteps: backtrace steps in the low 24 bits, attempts in the high 8 (<= 208 candidates)
 	// ---- nextAlignment state
@@ -181,12 +182,12 @@ struct BtMachine {
 	BT2_HD void relocate() { cidx = cell_at(row, col); }
 	BT2_HD void push_edit(uint32_t x) { if(ned < BT2_SCRATCH_EDITS) scr[ned] = x; ned++; }
 
-	// candidate i of the problem: group i / 8 sits in buffer 2 + (i / 8) % 2
+	// candidate i of the problem: group i / 4 sits in buffer 2 + (i / 4) % 2
 	BT2_HD uint32_t cand_at(uint32_t i) const {
-		return *(const volatile uint16_t*)(cbuf + (2u + ((i >> 3) & 1u)) * cstride + (i & 7u) * 2u);
+		return *(const volatile uint32_t*)(cbuf + (2u + ((i >> 2) & 1u)) * cstride + (i & 3u) * 4u);
 	}
 	BT2_HD void cand_fetch(const BtCtx& cx, uint32_t g) {
-		const uint16_t* src = cx.probs[slot].cand + g * 8u;
+		const uint32_t* src = cx.probs[slot].cand + g * 4u;
 		const uint32_t b = 2u + (g & 1u);
 #if defined(__CUDA_ARCH__)
 		const uint32_t sa = cbuf_sa + b * cstride;
@@ -226,7 +227,7 @@ struct BtMachine {
 	BT2_HD void begin(const BtCtx& cx) {
 		const DevParams& Pr = cx.P; const Problem& p = pb(cx); ReadState& r = rs(cx);
 		rows = p.rows; ncand = p.ncand;
-		d0 = p.d0; lgK = fill_lgK(prob_K(p)); yy = prob_y(p);
+		d0 = p.d0; lgK = fill_lgK(prob_K(p)); yy = prob_y(p); pi16 = prob_i16(p);
 		dlo = (p.corel > 0 ? p.corel : 0) - p.triml; { const int dhi = p.corer - p.triml; dspan = dhi >= dlo ? (uint32_t)(dhi - dlo) + 1u : 0u; }
 		cellp = cx.cells + (size_t)slot * cx.cell_stride; scr = cx.scratch + (size_t)read * BT2_SCRATCH_EDITS;
 		chunk_wait();   // a chunk copy of the previous problem may still be on its way into this lane's buffers
@@ -234,7 +235,9 @@ struct BtMachine {
 		rnd = r.rnd; hw = r.scr_hw;
 		BT2_PROF(16, 1); BT2_PROF(17, ncand);
 		r.dpCells += (uint64_t)p.rows * p.cols;
-		const int32_t bestCell = p.lrmax - 255;
+		// 8-bit: best = lrmax - 0xff, found iff best >= minsc (then the last row holds a candidate).  16-bit: the reference subtracts 0xff from
+		// the RAW word (bias 0x7fff) as well (aligner_swsse_ee_i16.cpp:640), so its test never fails and found = some candidate exists
+		const int32_t bestCell = pi16 ? (0x7fff + (p.lrmax - BT2_I16_START)) - 255 : p.lrmax - 255;
 		const bool found = bestCell >= p.minsc && ncand > 0;
 		r.nExDps++;
 		result = BT_CONTINUE;
@@ -249,7 +252,7 @@ struct BtMachine {
 		if(r.nDpFail > r.nDpFailStreak) r.nDpFailStreak = r.nDpFail;
 		r.nDpFail = 0;
 		cural = 0;
-		cand_fetch(cx, 0); if(ncand > 8u) cand_fetch(cx, 1);
+		cand_fetch(cx, 0); if(ncand > 4u) cand_fetch(cx, 1);
 		chunk_wait();
 		seek_cand();
 	}
@@ -258,12 +261,12 @@ struct BtMachine {
 		r.btSteps += nsteps & 0xffffffu; r.btAttempts += nsteps >> 24;
 		r.rnd = rnd; r.scr_hw = (uint16_t)hw;
 	}
-	// entering group g = cural / 8: group g + 1 is copied into the buffer group g - 1 leaves (waited for by the next cell's chunk_wait)
-	BT2_HD void next_cand(const BtCtx& cx) { cural++; if((cural & 7u) == 0u && cural + 8u < ncand) cand_fetch(cx, (cural >> 3) + 1u); }
+	// entering group g = cural / 4: group g + 1 is copied into the buffer group g - 1 leaves (waited for by the next cell's chunk_wait)
+	BT2_HD void next_cand(const BtCtx& cx) { cural++; if((cural & 3u) == 0u && cural + 4u < ncand) cand_fetch(cx, (cural >> 2) + 1u); }
 
 	BT2_HD void attempt_failed(const BtCtx& cx) { // backtrace returned false: scratch keeps what was written (res.reset() only drops the count)
 		if(ned > hw) hw = ned;
-		rnd.init(cx.P.i16path ? reseed : reseed + 1);
+		rnd.init(pi16 ? reseed : reseed + 1);
 		next_cand(cx);
 		seek_cand();
 	}
@@ -296,7 +299,7 @@ struct BtMachine {
 			if(was) { BT2_PROF(2, 1); next_cand(cx); seek_cand(); return; }
 			BT2_PROF(3, 1);
 			reseed = rnd.nextU32() + 1;
-			if(!cx.P.i16path) rnd.init(reseed);   // u8: reseed before and reseed+1 after the backtrace; i16: reseed after only (aligner_sw.cpp:324-348)
+			if(!pi16) rnd.init(reseed);   // u8: reseed before and reseed+1 after the backtrace; i16: reseed after only (aligner_sw.cpp:324-348)
 			ct = CT_H;
 			score = 0; nbranch = 0; ned = 0; coreHit = false;
 			nsteps += 1u << 24;
@@ -365,7 +368,7 @@ struct BtMachine {
 		const uint32_t ne = ned;
 		for(uint32_t i = 0; i < ne / 2; i++) { const uint32_t t = scratch[i]; scratch[i] = scratch[ne - 1 - i]; scratch[ne - 1 - i] = t; }
 		if(ned > hw) hw = ned;
-		rnd.init(cx.P.i16path ? reseed : reseed + 1);
+		rnd.init(pi16 ? reseed : reseed + 1);
 		AlnRec a;
 		a.fw = p.fw; a.tidx = p.tidx; a.refoff = (int64_t)col + p.refl;
 		a.score = score; a.ns = ns; a.gaps = gaps; a.edits = (int32_t)ne;

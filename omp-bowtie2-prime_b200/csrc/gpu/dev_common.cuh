@@ -35,7 +35,6 @@ struct DevParams {
 	int32_t seedLen, seedMms, nSeedRounds, seedBoostThresh, maxhalf, mxIter, mxUg, mxDp, streak;
 	int32_t doExtend, enable8, tighten, khits, mhits, msample, nofw, norc, gapbar;
 	int32_t rdGapOpen, rdGapExt, rfGapOpen, rfGapExt, matchBonus, i16;
-	int32_t i16path;         // the -DENABLE_I16 build with --no-sse8: SwAligner takes its 16-bit path (same cells for minsc >= -254, other RNG protocol)
 	uint8_t mmpens[256]; // Scoring::mmpens (<= 255 in u8 mode)
 	uint8_t npens[256];
 };
@@ -299,19 +298,29 @@ struct ReadState {
 struct alignas(16) Problem {
 	uint32_t read;
 	uint16_t rows, cols;       // rdlen, rflen (# DP columns)
-	uint8_t  fw, lay;          // lay = K | y << 7: the fill's layout (below): K diagonals per lane, y = which of the warp's two interleaved pairs
+	uint8_t  fw, lay;          // lay = K | i16 << 6 | y << 7: the fill's layout (below): K diagonals per lane, y = which of the warp's two interleaved
+	                           // pairs; i16 (set by the extension step): the reference takes its 16-bit DP path for this problem (prob_i16)
 	int16_t  d0;               // leftmost diagonal (col - row) of the band the fill computed
-	int32_t  minsc;            // SwAligner::minsc_ (clamped to >= -254 for u8)
+	int32_t  minsc;            // SwAligner::minsc_ (clamped to >= -254 on the 8-bit path)
 	int64_t  refl;             // rect.refl
 	uint32_t tidx;
 	int32_t  triml, corel, corer;
 	// outputs of K_fill
 	int32_t  lrmax;            // max raw H in the last row
 	uint32_t ncand;
-	uint16_t cand[BT2GPU_MAX_COLS + 8]; // sorted best-first: (rawH << 8) | col; at a 16-byte boundary (read in groups of 8 by the backtrace)
+	uint32_t cand[BT2GPU_MAX_COLS + 8]; // sorted best-first: (rawH << 8) | col; at a 16-byte boundary (read in groups of 4 by the backtrace)
 	uint8_t  rf[BT2GPU_MAX_COLS + 8];   // reference masks for columns 0..cols (cols+1 fetched)
 };
-BT2_HD uint32_t prob_K(const Problem& p) { return p.lay & 0x7fu; }
+BT2_HD uint32_t prob_K(const Problem& p) { return p.lay & 0x3fu; }
+// The reference built with -DENABLE_I16 runs a problem through its 16-bit fill when 8-bit SSE is off (--no-sse8) or the minimum score is
+// below -254 (aligner_sw.cpp:77-83).  The recurrence is the same with another bias and floor (start 0x7fff, floor -0x8000 instead of 0xff
+// and 0); here the scores live in signed 16-bit lanes either way, so the 16-bit path only changes H of row -1 -- BT2_I16_START instead of
+// 0xff: the largest bias whose scores still compare exactly as fp16 bit patterns (simd16.cuh), floor at a score of -28 672, far below
+// any minimum score a read of <= 160 bp can have -- the candidate threshold, and the protocol around the fill: nextAlignment reseeds the
+// generator only after the backtrace (aligner_sw.cpp:336-348) and `best` is the raw 16-bit word minus 0xff (aligner_swsse_ee_i16.cpp:640).
+#define BT2_I16_START 0x7000
+BT2_HD bool prob_i16(const Problem& p) { return (p.lay & 0x40u) != 0; }
+BT2_HD int prob_start(const Problem& p) { return prob_i16(p) ? BT2_I16_START : 0xff; }
 BT2_HD uint32_t prob_y(const Problem& p) { return p.lay >> 7; }
 static_assert(offsetof(Problem, cand) % 16 == 0 && sizeof(Problem) % 16 == 0, "Problem::cand is copied in 16-byte groups");
 

@@ -111,11 +111,14 @@ BT2_HD int advance(const DevParams& P, const DevIndex& ix, const DevRef& rf, con
 		for(int64_t k = leftNs + (inner > 0 ? inner : 0); k < rflenFull; k++) prob.rf[k] = 16;
 		prob.rows = (uint16_t)rdlen; prob.cols = (uint16_t)(rflenFull - 1);
 		prob.fw = fw ? 1 : 0;
-		prob.lay = 0; prob.d0 = 0;   // set by the fill (k_fill.cuh)
-		// u8 build: minsc is clamped (aligner_sw.cpp:84).  -DENABLE_I16 build: minsc < -254 selects the 16-bit fill
-		// (aligner_sw.cpp:79), whose score range this library does not have: flagged, the batch call fails.
-		if(P.i16 && rs.minsc < -254) set_error(pools, 16);
-		prob.minsc = rs.minsc < -254 ? -254 : rs.minsc;
+		prob.d0 = 0;   // set by the fill (k_fill.cuh)
+		// default build: 8-bit fill, minsc clamped (bt2_search.cpp:2487-2491, aligner_sw.cpp:84).  -DENABLE_I16 build: --no-sse8 or
+		// minsc < -254 selects the 16-bit fill for THIS problem (aligner_sw.cpp:77-83; minsc is tightened as alignments are found, so a
+		// read may change paths between two of its problems)
+		const bool i16 = P.i16 && (!P.enable8 || rs.minsc < -254);
+		if(i16 && rs.minsc < -(BT2_I16_START - 0x100)) set_error(pools, 16);   // beyond the range the fill keeps (never with reads <= 160 bp and sane penalties)
+		prob.lay = i16 ? 0x40 : 0;
+		prob.minsc = (!i16 && rs.minsc < -254) ? -254 : rs.minsc;
 		prob.tidx = (uint32_t)tidx; prob.refl = refl;
 		prob.triml = (int32_t)triml; prob.corel = (int32_t)maxgap; prob.corer = (int32_t)(3 * maxgap);
 		prob.lrmax = 0; prob.ncand = 0;

@@ -56,8 +56,10 @@ struct FillArgs {
 #endif
 #define BT2_FILL_ROWPAD BT2_SKEW                       // virtual rows before row 0 (and rows past the end the last lanes touch)
 #define BT2_FILL_NROW (BT2_FILL_ROWPAD + BT2GPU_MAX_ROWS + BT2_SKEW + 4)
-#define BT2_FILL_START 255                             // H of row -1 (0xff: the u8 scores are biased by it)
 
+// "No gap here": a penalty no score survives.  H + NOGAP is negative for every H in 0 .. BT2_I16_START, and its 16-bit pattern
+// (0x8c00 .. 0xfc00) is a negative fp16 number, -inf or NaN, never -0: the comparison with the (non-negative) maximum says "differs".
+#define BT2_FILL_NOGAP (-0x7400)
 struct FillRow { uint32_t rdc2, negpen, neg_rdgo, neg_rfgo_nx; };   // row r: characters, mismatch penalty, read-gap open; ref-gap open INTO row r+1
 struct FillRow2 { uint32_t neg_rfge_nx, negpenN; };                 // ref-gap extension into row r+1; penalty against an N reference character
 
@@ -66,10 +68,10 @@ template<int K> struct FillShared {
 	FillRow2 row2[2][BT2_FILL_NROW];
 	uint32_t refw[2][BT2_FILL_ROWPAD + BT2GPU_MAX_ROWS + BT2_SKEW + BT2_LANES * K + 24];   // [set][BT2_FILL_ROWPAD + t]: code_A(t + d0_A) | code_B(t + d0_B) << 16
 	uint16_t hl[4][BT2GPU_MAX_COLS + 8];            // [problem][col]: H of the last row (0 outside the band)
-	uint16_t ckey[BT2GPU_MAX_COLS + 8];
+	uint32_t ckey[BT2GPU_MAX_COLS + 8];
 };
 
-struct FillProb { int rows, cols, d0; bool on; };
+struct FillProb { int rows, cols, d0, start; bool on; };   // start: H of row -1 (0xff, or BT2_I16_START on the reference's 16-bit path)
 
 // What one lane holds of one problem set.
 template<int K> struct FillSet {
@@ -188,7 +190,7 @@ template<int K> BT2_SIMD void fill_set_init(FillSet<K>& S, FillShared<K>& sh, co
 	for(int j = 0; j < K; j++) {
 		// diagonals that start in row 0 take H(-1, c-1) = 0xff; the others start left of the window (H = 0)
 		const int dA = A.d0 + (int)lane * K + j, dB = B.d0 + (int)lane * K + j;
-		S.Hd[j] = v_pack2(dA >= 0 ? BT2_FILL_START : 0, dB >= 0 ? BT2_FILL_START : 0);
+		S.Hd[j] = v_pack2(dA >= 0 ? A.start : 0, dB >= 0 ? B.start : 0);
 		S.Fdn[j] = 0; S.Fc[j] = BT2_FL_BASE | ((uint32_t)(CF_FO | CF_FX) * 0x00010001u);
 	}
 	#pragma unroll
@@ -221,9 +223,9 @@ template<int K> BT2_SIMD void fill_build_rows(const DevParams& P, FillShared<K>&
 			const bool gaps_ok = real && !(r < P.gapbar || X.rows - 1 - r < P.gapbar);
 			const int r1 = r + 1;
 			const bool into_ok = X.on && r1 > 0 && r1 < X.rows && !(r1 < P.gapbar || X.rows - 1 - r1 < P.gapbar);
-			rdgo[x] = gaps_ok ? -P.rdGapOpen : -1024;
-			rfgo[x] = into_ok ? -P.rfGapOpen : -1024;
-			rfge[x] = into_ok ? -P.rfGapExt : -1024;
+			rdgo[x] = gaps_ok ? -P.rdGapOpen : BT2_FILL_NOGAP;
+			rfgo[x] = into_ok ? -P.rfGapOpen : BT2_FILL_NOGAP;
+			rfge[x] = into_ok ? -P.rfGapExt : BT2_FILL_NOGAP;
 		}
 		FillRow w; w.rdc2 = v_pack2(rdc[0], rdc[1]); w.negpen = v_pack2(-pen[0], -pen[1]); w.neg_rdgo = v_pack2(rdgo[0], rdgo[1]); w.neg_rfgo_nx = v_pack2(rfgo[0], rfgo[1]);
 		FillRow2 w2; w2.neg_rfge_nx = v_pack2(rfge[0], rfge[1]); w2.negpenN = v_pack2(-penN[0], -penN[1]);
@@ -306,7 +308,7 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 7 : 4) k_fill(co
 		const uint32_t slot = slot0 + q;
 		FillProb& X = pr[q];
 		X.on = slot < a.nprob && a.probs[slot].read != BT2_NIL;
-		X.rows = X.on ? a.probs[slot].rows : 0; X.cols = X.on ? a.probs[slot].cols : 0; X.d0 = 0;
+		X.rows = X.on ? a.probs[slot].rows : 0; X.cols = X.on ? a.probs[slot].cols : 0; X.d0 = 0; X.start = X.on ? prob_start(a.probs[slot]) : 0xff;
 		if(!X.on) continue;
 		any = true;
 		int dlo, dhi; fill_band(P, X.rows, X.cols, a.probs[slot].minsc, a.exact != 0, dlo, dhi);
@@ -314,7 +316,7 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 7 : 4) k_fill(co
 		X.d0 = dlo;
 		if(X.rows > rowsW) rowsW = X.rows;
 		if(-dlo > mask_to) mask_to = -dlo;
-		if(lane == 0) { a.probs[slot].lay = (uint8_t)(K | ((q >> 1) << 7)); a.probs[slot].d0 = (int16_t)dlo; }
+		if(lane == 0) { a.probs[slot].lay = (uint8_t)((a.probs[slot].lay & 0x40u) | K | ((q >> 1) << 7)); a.probs[slot].d0 = (int16_t)dlo; }
 	}
 	if(!any) return;
 	constexpr int PER = 16 / K;
@@ -398,9 +400,9 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 7 : 4) k_fill(co
 			const int c = c0 + (int)lane;
 			const int hv8 = c < cols ? (int)sh.hl[q][c] : 0;
 			lrmax = max(lrmax, hv8);
-			const bool isc = c < cols && (hv8 - BT2_FILL_START) >= minsc;
+			const bool isc = c < cols && (hv8 - pr[q].start) >= minsc;
 			const uint32_t bal = __ballot_sync(0xffffffffu, isc);
-			if(isc) sh.ckey[ncand + __popc(bal & ((1u << lane) - 1))] = (uint16_t)((hv8 << 8) | c);
+			if(isc) sh.ckey[ncand + __popc(bal & ((1u << lane) - 1))] = ((uint32_t)hv8 << 8) | (uint32_t)c;
 			ncand += __popc(bal);
 		}
 		#pragma unroll
@@ -410,7 +412,7 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 7 : 4) k_fill(co
 			const uint32_t key = sh.ckey[j];
 			uint32_t rank = 0;
 			for(uint32_t k = 0; k < ncand; k++) rank += (sh.ckey[k] > key) ? 1u : 0u;
-			pb.cand[rank] = (uint16_t)key;
+			pb.cand[rank] = key;
 		}
 		__syncwarp();
 		if(lane == 0) {

@@ -28,6 +28,8 @@ CASES = {
     # the reference built with -DENABLE_I16 and run with --no-sse8: its 16-bit DP path (other RNG protocol)
     "syn100_k5_i16": ("syn", "syn100", "-k 5 --i16 --no-sse8", "syn100_k5_i16.sam"),
     "syn150_sens_i16": ("syn", "syn150", "--i16 --no-sse8 --sensitive --dpad 12", "syn150_sens_i16.sam"),
+    # minimum score -300 < -254: that build takes the 16-bit path with 8-bit SSE still enabled; the score range a8-bit fill does not have
+    "syn100_min300_i16": ("syn", "syn100", "--i16 --score-min L,-300,0 -k 3", "syn100_min300_i16.sam"),
 }
 
 

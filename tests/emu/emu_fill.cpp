@@ -12,7 +12,7 @@
 #include "fill_scalar.hpp"
 #include "../../omp-bowtie2-prime_b200/csrc/gpu/k_fill.cuh"
 
-struct TProb { std::vector<uint8_t> rd, qual, rf; int rows, cols, minsc; };
+struct TProb { std::vector<uint8_t> rd, qual, rf; int rows, cols, minsc; bool i16; };
 
 static TProb make_problem(std::mt19937& g, int idx) {
 	static const int fr[9] = {1, 2, 63, 64, 65, 128, 129, 150, 160}, fc[9] = {1, 5, 199, 100, 70, 199, 150, 199, 199};
@@ -32,6 +32,8 @@ static TProb make_problem(std::mt19937& g, int idx) {
 	if(g() % 10 < 3) p.rf[rnd(0, p.cols - 1)] = 16;
 	p.qual.resize(p.rows); for(auto& q : p.qual) q = (uint8_t)rnd(35, 73);
 	p.minsc = -(int)(g() % 120);
+	p.i16 = (g() % 4) == 0;                                   // the reference's 16-bit path: another bias, minimum scores below -254 allowed
+	if(p.i16 && (g() & 1)) p.minsc = -(int)(g() % 400);
 	return p;
 }
 
@@ -44,7 +46,7 @@ template<int K, bool DBG> static void run_warp(const DevParams& P, const TProb* 
 	static FillShared<K> sh; memset(&sh, 0xcd, sizeof(sh));
 	FillProb pr[4]; int rowsW = 0, mask_to = 0;
 	for(int q = 0; q < 4; q++) {
-		FillProb& X = pr[q]; X.on = tp[q] != nullptr; X.rows = X.on ? tp[q]->rows : 0; X.cols = X.on ? tp[q]->cols : 0; X.d0 = 0;
+		FillProb& X = pr[q]; X.on = tp[q] != nullptr; X.rows = X.on ? tp[q]->rows : 0; X.cols = X.on ? tp[q]->cols : 0; X.d0 = 0; X.start = (X.on && tp[q]->i16) ? BT2_I16_START : 0xff;
 		if(!X.on) continue;
 		int dlo, dhi; fill_band(P, X.rows, X.cols, tp[q]->minsc, exact, dlo, dhi);
 		if(dhi - dlo + 1 > BT2_LANES * K) { g_skipped++; return; }   // this K cannot hold the problem (the host picks K so that it can)
@@ -109,7 +111,7 @@ template<int K, bool DBG> static void run_warp(const DevParams& P, const TProb* 
 	for(int q = 0; q < 4; q++) {
 		if(!tp[q]) continue;
 		const TProb& t = *tp[q];
-		Problem pb; memset(&pb, 0, sizeof(pb)); pb.rows = (uint16_t)t.rows; pb.cols = (uint16_t)t.cols; pb.fw = 1; pb.minsc = t.minsc;
+		Problem pb; memset(&pb, 0, sizeof(pb)); pb.rows = (uint16_t)t.rows; pb.cols = (uint16_t)t.cols; pb.fw = 1; pb.minsc = t.minsc; pb.lay = t.i16 ? 0x40 : 0;
 		memcpy(pb.rf, t.rf.data(), t.cols + 1);
 		ReadView rv; rv.seq = t.rd.data(); rv.qual = t.qual.data(); rv.rdlen = (uint32_t)t.rows; rv.fw = true;
 		std::vector<uint8_t> want(fill_cell_bytes(BT2GPU_MAX_ROWS, K), 0); std::vector<uint32_t> pc(BT2_PC_WORDS), HEF((size_t)t.rows * t.cols, 0);
@@ -128,16 +130,16 @@ template<int K, bool DBG> static void run_warp(const DevParams& P, const TProb* 
 			const uint32_t ci = cell_index((uint32_t)r, (uint32_t)c, d0, K, y);
 			const uint8_t got = cells[q][ci], exp = want[ci]; g_cells++;
 			if(((got ^ exp) & care) != 0 || (got & CF_VIS)) { if(nbad++ < 3) CHECK(false, "K=%d exact=%d problem %dx%d minsc %d d0 %d set %d: flags differ at row %d col %d: lanes %02x scalar %02x (care %02x)", K, exact, t.rows, t.cols, t.minsc, d0, (int)y, r, c, got, exp, care); }
-			if(DBG) {
+			if(DBG && !t.i16) {   // (the debug words hold 8-bit values)
 				const uint32_t hg = hef[q][(size_t)r * (BT2_LANES * K) + dd], hw = HEF[(size_t)r * t.cols + c];
 				// E at column 0 and F in row 0 are boundary values no comparison reads; inside the gap barrier the scalar code forces F to 0 as the lanes do
 				if(hg != hw) { if(nbad++ < 3) CHECK(false, "K=%d problem %dx%d: H/E/F differ at row %d col %d: lanes %06x scalar %06x", K, t.rows, t.cols, r, c, hg, hw); }
 			}
 		}
 		// last row -> candidates
-		int lrmax = 0; std::vector<uint16_t> cand;
-		for(int c = 0; c < t.cols; c++) { const int h = sh.hl[q][c]; if(h > lrmax) lrmax = h; if(h - 255 >= t.minsc) cand.push_back((uint16_t)((h << 8) | c)); }
-		std::sort(cand.begin(), cand.end(), [](uint16_t a, uint16_t b) { return a > b; });
+		int lrmax = 0; std::vector<uint32_t> cand;
+		for(int c = 0; c < t.cols; c++) { const int h = sh.hl[q][c]; if(h > lrmax) lrmax = h; if(h - pr[q].start >= t.minsc) cand.push_back(((uint32_t)h << 8) | (uint32_t)c); }
+		std::sort(cand.begin(), cand.end(), [](uint32_t a, uint32_t b) { return a > b; });
 		CHECK(lrmax == pb.lrmax, "K=%d exact=%d problem %dx%d minsc %d: lrmax %d vs %d", K, exact, t.rows, t.cols, t.minsc, lrmax, pb.lrmax);
 		CHECK(cand.size() == pb.ncand, "K=%d problem %dx%d: ncand %zu vs %u", K, t.rows, t.cols, cand.size(), pb.ncand);
 		for(size_t k = 0; k < cand.size() && k < pb.ncand; k++) CHECK(cand[k] == pb.cand[k], "cand %zu differs", k);

@@ -46,7 +46,7 @@ int main(int argc, char** argv) {
 	P.maxhalf = hp->maxhalf; P.mxIter = hp->mxIter; P.mxUg = hp->mxUg; P.mxDp = hp->mxDp; P.streak = hp->streak; P.doExtend = hp->doExtend;
 	P.enable8 = hp->enable8; P.tighten = hp->tighten; P.khits = hp->khits; P.mhits = hp->mhits; P.msample = hp->msample; P.nofw = hp->nofw; P.norc = hp->norc;
 	P.gapbar = hp->gapbar; P.rdGapOpen = hp->rdGapConst + hp->rdGapLinear; P.rdGapExt = hp->rdGapLinear;
-	P.rfGapOpen = hp->rfGapConst + hp->rfGapLinear; P.rfGapExt = hp->rfGapLinear; P.matchBonus = hp->matchBonus; P.i16 = hp->i16; P.i16path = (hp->i16 && !hp->enable8) ? 1 : 0;
+	P.rfGapOpen = hp->rfGapConst + hp->rfGapLinear; P.rfGapExt = hp->rfGapLinear; P.matchBonus = hp->matchBonus; P.i16 = hp->i16;
 	for(int i = 0; i < 256; i++) { P.mmpens[i] = (uint8_t)hp->mmpens[i]; P.npens[i] = (uint8_t)hp->npens[i]; }
 	DevIndex ix; ix.sa32 = nullptr; ix.ktab = nullptr; ix.ktabChars = 0; ix.ebwt = hix->ebwt; ix.ftab = hix->ftab; ix.eftab = hix->eftab; ix.offs = hix->offs; ix.rstarts = hix->rstarts; ix.plen = hix->plen;
 	for(int i = 0; i < 5; i++) ix.fchr[i] = hix->fchr[i];

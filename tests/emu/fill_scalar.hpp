@@ -19,11 +19,11 @@ static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_
 	int dlo, dhi; fill_band(P, rows, cols, pb.minsc, exact, dlo, dhi);
 	const uint32_t K = Kforce ? Kforce : fill_K_for(dhi - dlo + 1);
 	dhi = dlo + (int)(BT2_LANES * K) - 1;
-	pb.lay = (uint8_t)(K | (y << 7)); pb.d0 = (int16_t)dlo;
+	pb.lay = (uint8_t)((pb.lay & 0x40u) | K | (y << 7)); pb.d0 = (int16_t)dlo;
 	auto inband = [&](int r, int c) { return c - r >= dlo && c - r <= dhi; };
 	auto subs = [](int a, int b) { int v = a - b; return v < 0 ? 0 : v; };
 	std::vector<int> Hprev(rows, 0), Eprev(rows, 0), Fprev(rows, 0), Hcur(rows), Ecur(rows), Fcur(rows), Eleft(rows, 0), Ehere(rows, 0);
-	int lrmax = 0; std::vector<uint16_t> cand;
+	int lrmax = 0; std::vector<uint32_t> cand; const int S0 = prob_start(pb);
 	g_cells_rect += (size_t)rows * cols;
 	for(int j = 0; j < cols; j++) {
 		const int refm = pb.rf[j];
@@ -34,7 +34,7 @@ static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_
 			const bool gb = (r < P.gapbar) || (rows - 1 - r < P.gapbar);
 			const int s0 = -sc_score(P, rv.rd(r), refm, rv.q(r) - 33);
 			int f = (r == 0) ? 0 : Fpre; if(gb) f = 0;
-			const int hd = (r == 0) ? 255 : Hprev[r - 1];
+			const int hd = (r == 0) ? S0 : Hprev[r - 1];
 			const int e = Eprev[r];
 			int h = subs(hd, s0); if(e > h) h = e; if(f > h) h = f;
 			Hcur[r] = h;
@@ -46,7 +46,7 @@ static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_
 			if(HEF) HEF[(size_t)r * cols + j] = (uint32_t)h | ((uint32_t)e << 8) | ((uint32_t)f << 16);
 			// the backtrace's comparisons at this cell, literally (raw values: the 0xff bias cancels)
 			uint32_t ne = 0;
-			const int hup = (r == 0) ? 255 : Hcur[r - 1], fup = (r == 0) ? 0 : Fcur[r - 1];
+			const int hup = (r == 0) ? S0 : Hcur[r - 1], fup = (r == 0) ? 0 : Fcur[r - 1];
 			if(h != hd - s0) ne |= CF_D;                 // s0 = penalty >= 0 (column 0 compares with H(r-1,-1) = 0; never read)
 			if(h != e) ne |= CF_HE;
 			if(h != f) ne |= CF_HF;
@@ -61,14 +61,14 @@ static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_
 		}
 		const int lr = Hcur[rows - 1];
 		if(lr > lrmax) lrmax = lr;
-		if(lr - 255 >= pb.minsc) cand.push_back((uint16_t)((lr << 8) | j));
+		if(lr - S0 >= pb.minsc) cand.push_back(((uint32_t)lr << 8) | (uint32_t)j);
 		Hprev.swap(Hcur); Eprev.swap(Ecur); Fprev.swap(Fcur); Eleft = Ehere;
 	}
 	// character cache (what K_fill leaves for the backtrace's edits)
 	for(int j = 0; j < BT2_PC_WORDS; j++) pcache[j] = 0;
 	for(int r = 0; r < rows; r++) { const uint32_t c = (uint32_t)rv.rd(r); pcache[r >> 3] |= (c > 3 ? 4u : c) << ((r & 7) * 4); }
 	for(int j = 0; j < cols; j++) { const uint32_t m = pb.rf[j]; const uint32_t c = m > 15 ? 4u : (uint32_t)__builtin_ctz(m); pcache[BT2_PC_RD + (j >> 3)] |= c << ((j & 7) * 4); }
-	std::sort(cand.begin(), cand.end(), [](uint16_t a, uint16_t b) { return a > b; });
+	std::sort(cand.begin(), cand.end(), [](uint32_t a, uint32_t b) { return a > b; });
 	pb.lrmax = lrmax; pb.ncand = (uint32_t)cand.size();
 	for(size_t i = 0; i < cand.size(); i++) pb.cand[i] = cand[i];
 }

@@ -29,6 +29,8 @@ run syn100_k5               "$T/syn" "$T/syn100.fq" "-k 5"
 run16() { OMP_NUM_THREADS=4 "$B/bowtie2-align-l-i16" -x "$2" -U "$3" -S "$T/o.sam" -p 8 $4 2>/dev/null; grep -v '^@' "$T/o.sam" | LC_ALL=C sort > "$HERE/$1.sam"; }
 run16 syn100_k5_i16   "$T/syn" "$T/syn100.fq" "-k 5 --no-sse8"
 run16 syn150_sens_i16 "$T/syn" "$T/syn150.fq" "--no-sse8 --sensitive --dpad 12"
+# minimum score -300: below the 8-bit range, so that build takes its 16-bit path although 8-bit SSE is enabled (aligner_sw.cpp:79)
+run16 syn100_min300_i16 "$T/syn" "$T/syn100.fq" "--score-min L,-300,0 -k 3"
 # reference with runs of N (record boundaries inside sequences, N at both ends of the text), 2 sequences
 python "$ROOT/tools/gen_data.py" ref "$T/synN.fa" 200000 --seed 99 --repeats 0.1 --nseq 2 --ngaps 40
 "$B/bowtie2-build-l" "$T/synN.fa" "$T/synN" >/dev/null 2>&1

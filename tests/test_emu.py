@@ -7,7 +7,7 @@ import common
 from common import pkg
 
 
-@pytest.mark.parametrize("name", ["lambda_default", "syn100_k5", "syn150_sensitive_dpad12", "synN120_default", "syn100_k5_i16", "syn150_sens_i16",
+@pytest.mark.parametrize("name", ["lambda_default", "syn100_k5", "syn150_sensitive_dpad12", "synN120_default", "syn100_k5_i16", "syn150_sens_i16", "syn100_min300_i16",
                                   "synR100_default", "synR100_k3_vs"])
 def test_emulated_device_logic_matches_golden(name):
     if not common.have_builder():

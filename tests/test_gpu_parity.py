@@ -22,7 +22,7 @@ def test_gpu_matches_oracle_and_golden(name):
     want = orc.align(batch)
     gpu = _gpu(job)
     got = gpu.align(batch)
-    diffs = common.compare_results(want, got, i16path="--no-sse8" in opts)
+    diffs = common.compare_results(want, got, i16path="--i16" in opts and ("--no-sse8" in opts or "--score-min" in opts))
     assert not diffs, "\n".join(diffs[:10])
     sam = common.sorted_records(job.sam(batch, got, mode=1))
     assert sam == common.golden_records(gold)
@@ -192,10 +192,10 @@ def test_gpu_larger_iid_vs_oracle():
     gpu.close(); orc.close()
 
 
-def test_gpu_i16_build_needs_8bit_range():
-    """-DENABLE_I16 protocol: a minimum score below -254 would select the reference's 16-bit fill, whose score range the
-    CUDA fill does not have: the call fails loudly instead of returning 8-bit results."""
-    job = pkg.Job(common.index_base("syn"), "--i16 --score-min L,-300,0")
+def test_gpu_i16_score_range_limit():
+    """-DENABLE_I16 protocol: a minimum score below -254 selects the reference's 16-bit path (golden syn100_min300_i16: alignments down to
+    AS:i:-299).  The fill keeps scores down to -28 416; a minimum score beyond that fails loudly instead of returning clamped results."""
+    job = pkg.Job(common.index_base("syn"), "--i16 --score-min L,-30000,0")
     batch = job.fastq(common.reads_path("syn100"), 0, 50)
     gpu = _gpu(job)
     with pytest.raises(RuntimeError, match="16-bit"):
