@@ -562,7 +562,7 @@ __global__ void k_na_setup(NoAllocScratch* sc, uint32_t nprob, const uint32_t* s
 	rs.seq_off = seq_off[i]; rs.rdlen = (uint16_t)r;
 }
 // one block per problem: dense flags (row-major rows x cols; 0x80 outside the band) out of the cell layout, candidates, counts
-__global__ void k_na_export(const NoAllocScratch* sc, const uint64_t* flags_off, uint8_t* flags, uint16_t* cand, uint32_t* ncand, int32_t* lrmax) {
+__global__ void k_na_export(const DevParams* __restrict__ Pp, uint32_t nprob, const NoAllocScratch* sc, const uint64_t* flags_off, uint8_t* flags, uint16_t* cand, uint32_t* ncand, int32_t* lrmax) {
 	const uint32_t i = blockIdx.x;
 	const Problem& pb = sc->probs[i];
 	const bool ok = pb.read != BT2_NIL;
@@ -570,11 +570,19 @@ __global__ void k_na_export(const NoAllocScratch* sc, const uint64_t* flags_off,
 	if(!ok) return;
 	for(uint32_t k = threadIdx.x; k < pb.ncand; k += blockDim.x) cand[256u * i + k] = pb.cand[k];
 	const uint32_t rows = pb.rows, cols = pb.cols, K = prob_K(pb), y = prob_y(pb); const int d0 = pb.d0;
+	// diagonals the kernel completes for this problem: the lanes up to the widest band of its warp (problems 4w .. 4w+3)
+	int widthW = 1;
+	for(uint32_t q = i & ~3u; q < (i & ~3u) + 4u && q < nprob; q++) {
+		if(sc->probs[q].read == BT2_NIL) continue;
+		int lo, hi; fill_band(*Pp, sc->probs[q].rows, sc->probs[q].cols, sc->probs[q].minsc, false, lo, hi);
+		if(hi - lo + 1 > widthW) widthW = hi - lo + 1;
+	}
+	const int ndiag = ((widthW - 1) / (int)K + 1) * (int)K;
 	const uint8_t* cells = sc->cells + (size_t)i * BT2_NA_STRIDE;
 	uint8_t* out = flags + flags_off[i];
 	for(uint32_t k = threadIdx.x; k < rows * cols; k += blockDim.x) {
 		const uint32_t r = k / cols, c = k % cols; const int dd = (int)c - (int)r - d0;
-		out[k] = (dd >= 0 && dd < (int)(BT2_LANES * K)) ? cells[cell_index(r, c, d0, K, y)] : (uint8_t)0x80;
+		out[k] = (dd >= 0 && dd < ndiag) ? cells[cell_index(r, c, d0, K, y)] : (uint8_t)0x80;
 	}
 }
 
@@ -810,11 +818,15 @@ int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, c
 			if(ferr) throw std::string("bt2gpu_test_fill: a band did not fit the fill's lanes");
 			const uint32_t pk = prob_K(hp[i]), py = prob_y(hp[i]); const int d0 = hp[i].d0;
 			if(pk != K) throw std::string("bt2gpu_test_fill: the kernel did not record its layout");
-			if(band) { band[2 * i] = d0; band[2 * i + 1] = (int32_t)(BT2_LANES * pk); }
+			// diagonals the kernel completes for this problem: the lanes up to the widest band of its warp (problems 4w .. 4w+3)
+			int widthW = 1;
+			for(uint32_t q = i & ~3u; q < std::min(nprob, (i & ~3u) + 4u); q++) { int lo, hi; fill_band(ctx->P, rows[q], cols[q], minsc[q], exact, lo, hi); widthW = std::max(widthW, hi - lo + 1); }
+			const int ndiag = ((widthW - 1) / (int)pk + 1) * (int)pk;
+			if(band) { band[2 * i] = d0; band[2 * i + 1] = ndiag; }
 			for(uint32_t r = 0; r < rows[i]; r++) for(uint32_t cc = 0; cc < cols[i]; cc++) {
 				const uint64_t o = hef_off[i] + (uint64_t)r * cols[i] + cc;
 				const int dd = (int)cc - (int)r - d0;
-				const bool in = dd >= 0 && dd < (int)(BT2_LANES * pk);
+				const bool in = dd >= 0 && dd < ndiag;
 				if(exact) {
 					const uint32_t x = in ? w[(size_t)r * (BT2_LANES * pk) + dd] : 0u;
 					H[o] = (uint8_t)x; E[o] = (uint8_t)(x >> 8); F[o] = (uint8_t)(x >> 16);
@@ -856,7 +868,7 @@ int bt2gpu_fill_noalloc(bt2gpu_ctx* ctx, void* stream, uint32_t nprob, const uin
 		FillArgs fa; fa.probs = sc->probs; fa.nprob = nprob; fa.states = sc->states; fa.seq = d_seq; fa.qual = d_qual; fa.cells = sc->cells; fa.cell_stride = BT2_NA_STRIDE;
 		fa.pcache = nullptr; fa.hef_dbg = nullptr; fa.stats = sc->stats; fa.error = sc->error; fa.exact = 0;
 		launch_fill(BT2_NA_K, false, ctx->dP, fa, st);   // the production kernel, banded per problem; K = 16 holds any band
-		k_na_export<<<nprob, 256, 0, st>>>(sc, d_flags_off, d_flags, d_cand, d_ncand, d_lrmax);
+		k_na_export<<<nprob, 256, 0, st>>>(ctx->dP, nprob, sc, d_flags_off, d_flags, d_cand, d_ncand, d_lrmax);
 		CK(cudaPeekAtLastError());
 		if(cap == cudaStreamCaptureStatusNone) { CK(cudaEventRecord(nd.done, st)); nd.used = true; }
 	})

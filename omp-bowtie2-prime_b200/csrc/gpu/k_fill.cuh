@@ -68,8 +68,9 @@ template<int K> struct FillShared {
 	FillRow2 row2[2][BT2_FILL_NROW];
 	uint32_t refw[2][BT2_FILL_ROWPAD + BT2GPU_MAX_ROWS + BT2_SKEW + BT2_LANES * K + 24];   // [set][BT2_FILL_ROWPAD + t]: code_A(t + d0_A) | code_B(t + d0_B) << 16
 	uint16_t hl[4][BT2GPU_MAX_COLS + 8];            // [problem][col]: H of the last row (0 outside the band)
-	uint32_t ckey[BT2GPU_MAX_COLS + 8];
+	// (the candidate keys of the epilogue reuse row2[0]: BT2GPU_MAX_COLS + 8 words, dead after the sweep)
 };
+static_assert(sizeof(FillRow2) * BT2_FILL_NROW >= sizeof(uint32_t) * (BT2GPU_MAX_COLS + 8), "candidate keys overlay row2[0]");
 
 struct FillProb { int rows, cols, d0, start; bool on; };   // start: H of row -1 (0xff, or BT2_I16_START on the reference's 16-bit path)
 
@@ -201,21 +202,37 @@ template<int K> BT2_SIMD void fill_set_init(FillSet<K>& S, FillShared<K>& sh, co
 // against a mismatching / an N reference character, and the (negated) gap penalties; inside the gap barrier
 // (aligner_swsse_ee_u8.cpp:101-115: first/last gapbar rows), in the virtual rows and (reference gaps) into row 0 the gap
 // penalties are large enough to keep E and F at 0
+#define BT2_FILL_ROW_ITERS ((BT2_FILL_NROW + BT2_LANES - 1) / BT2_LANES)
 template<int K> BT2_SIMD void fill_build_rows(const DevParams& P, FillShared<K>& sh, const int set, const FillProb& A, const FillProb& B,
                                               const uint8_t* seqA, const uint8_t* qualA, bool fwA, const uint8_t* seqB, const uint8_t* qualB, bool fwB,
                                               const uint32_t lane, const int nrow) {
-	for(int idx = (int)lane; idx < nrow; idx += BT2_LANES) {
-		const int r = idx - BT2_FILL_ROWPAD;
-		int rdc[2], pen[2], penN[2], rdgo[2], rfgo[2], rfge[2];
+	// all of the lane's base / quality bytes first (independent loads in flight together), then the table entries
+	uint8_t cc[BT2_FILL_ROW_ITERS][2], qq[BT2_FILL_ROW_ITERS][2];
+	#pragma unroll
+	for(int it = 0; it < BT2_FILL_ROW_ITERS; it++) {
+		const int r = (int)lane + it * BT2_LANES - BT2_FILL_ROWPAD;
 		#pragma unroll
 		for(int x = 0; x < 2; x++) {
 			const FillProb& X = x ? B : A; const uint8_t* rseq = x ? seqB : seqA; const uint8_t* rqual = x ? qualB : qualA; const bool fw = x ? fwB : fwA;
 			const bool real = X.on && r >= 0 && r < X.rows;
+			const int at = fw ? r : X.rows - 1 - r;
+			cc[it][x] = real ? rseq[at] : (uint8_t)4; qq[it][x] = real ? rqual[at] : (uint8_t)0;
+		}
+	}
+	#pragma unroll
+	for(int it = 0; it < BT2_FILL_ROW_ITERS; it++) {
+		const int idx = (int)lane + it * BT2_LANES;
+		if(idx >= nrow) break;
+		const int r = idx - BT2_FILL_ROWPAD;
+		int rdc[2], pen[2], penN[2], rdgo[2], rfgo[2], rfge[2];
+		#pragma unroll
+		for(int x = 0; x < 2; x++) {
+			const FillProb& X = x ? B : A; const bool fw = x ? fwB : fwA;
+			const bool real = X.on && r >= 0 && r < X.rows;
 			int c = 4, q = 0;
 			if(real) {
-				if(fw) { c = rseq[r]; q = rqual[r]; }
-				else { const int c0 = rseq[X.rows - 1 - r]; c = c0 > 3 ? 4 : 3 - c0; q = rqual[X.rows - 1 - r]; }
-				q -= 33; if(q < 0) q = 0; if(q > 255) q = 255;
+				c = cc[it][x]; if(!fw) c = c > 3 ? 4 : 3 - c;
+				q = (int)qq[it][x] - 33; if(q < 0) q = 0; if(q > 255) q = 255;
 			}
 			rdc[x] = c > 3 ? 7 : c;
 			pen[x] = real ? (c > 3 ? P.npens[q] : P.mmpens[q]) : 0;
@@ -293,7 +310,7 @@ __device__ __forceinline__ void fill_sweep(int i0, const int i1, FillSet<K>& S0,
 }
 
 template<int K, bool DBG>
-__global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 7 : 4) k_fill(const DevParams* __restrict__ Pp, const FillArgs a) {
+__global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(const DevParams* __restrict__ Pp, const FillArgs a) {
 	__shared__ FillShared<K> shs[BT2_FILL_WARPS];
 	const DevParams& P = *Pp;
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -302,7 +319,7 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 7 : 4) k_fill(co
 	FillShared<K>& sh = shs[warp];
 	// ---- the warp's four problems: set 0 = slots 0, 1 (y = 0), set 1 = slots 2, 3 (y = 1)
 	FillProb pr[4];
-	int rowsW = 0, mask_to = 0; bool any = false;
+	int rowsW = 0, mask_to = 0, widthW = 1; bool any = false;
 	#pragma unroll
 	for(int q = 0; q < 4; q++) {
 		const uint32_t slot = slot0 + q;
@@ -316,11 +333,15 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 7 : 4) k_fill(co
 		X.d0 = dlo;
 		if(X.rows > rowsW) rowsW = X.rows;
 		if(-dlo > mask_to) mask_to = -dlo;
+		if(dhi - dlo + 1 > widthW) widthW = dhi - dlo + 1;
 		if(lane == 0) { a.probs[slot].lay = (uint8_t)((a.probs[slot].lay & 0x40u) | K | ((q >> 1) << 7)); a.probs[slot].d0 = (int16_t)dlo; }
 	}
 	if(!any) return;
 	constexpr int PER = 16 / K;
-	const int iters = (int)fill_iters((uint32_t)rowsW, K);
+	// lanes past the widest band hold no cell anyone reads: the sweep ends when the last lane that does has done its last row
+	const int vlast = (widthW - 1) / K;
+	int iters = ((rowsW + ((vlast + 2) >> 1) + PER - 1) / PER) * PER;
+	if(iters > (int)fill_iters((uint32_t)rowsW, K)) iters = (int)fill_iters((uint32_t)rowsW, K);
 	bool hasN = false;
 	#pragma unroll
 	for(int set = 0; set < 2; set++) {
@@ -390,6 +411,7 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 7 : 4) k_fill(co
 	fill_last_row<K>(S0); fill_last_row<K>(S1);
 	__syncwarp();
 	// ---- last-row candidates: H-0xff >= minsc, sorted by (score desc, col desc)
+	uint32_t* const ckey = reinterpret_cast<uint32_t*>(sh.row2[0]);
 	for(int q = 0; q < 4; q++) {
 		if(!pr[q].on) continue;
 		Problem& pb = a.probs[slot0 + q];
@@ -402,16 +424,16 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 7 : 4) k_fill(co
 			lrmax = max(lrmax, hv8);
 			const bool isc = c < cols && (hv8 - pr[q].start) >= minsc;
 			const uint32_t bal = __ballot_sync(0xffffffffu, isc);
-			if(isc) sh.ckey[ncand + __popc(bal & ((1u << lane) - 1))] = ((uint32_t)hv8 << 8) | (uint32_t)c;
+			if(isc) ckey[ncand + __popc(bal & ((1u << lane) - 1))] = ((uint32_t)hv8 << 8) | (uint32_t)c;
 			ncand += __popc(bal);
 		}
 		#pragma unroll
 		for(int o = 16; o > 0; o >>= 1) lrmax = max(lrmax, __shfl_xor_sync(0xffffffffu, lrmax, o));
 		__syncwarp();
 		for(uint32_t j = lane; j < ncand; j += 32) {
-			const uint32_t key = sh.ckey[j];
+			const uint32_t key = ckey[j];
 			uint32_t rank = 0;
-			for(uint32_t k = 0; k < ncand; k++) rank += (sh.ckey[k] > key) ? 1u : 0u;
+			for(uint32_t k = 0; k < ncand; k++) rank += (ckey[k] > key) ? 1u : 0u;
 			pb.cand[rank] = key;
 		}
 		__syncwarp();

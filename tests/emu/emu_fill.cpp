@@ -44,16 +44,19 @@ static int g_fail = 0; static long g_warps = 0, g_cells = 0, g_skipped = 0;
 template<int K, bool DBG> static void run_warp(const DevParams& P, const TProb* tp[4], bool exact) {
 	constexpr int PER = 16 / K;
 	static FillShared<K> sh; memset(&sh, 0xcd, sizeof(sh));
-	FillProb pr[4]; int rowsW = 0, mask_to = 0;
+	FillProb pr[4]; int rowsW = 0, mask_to = 0, widthW = 1;
 	for(int q = 0; q < 4; q++) {
 		FillProb& X = pr[q]; X.on = tp[q] != nullptr; X.rows = X.on ? tp[q]->rows : 0; X.cols = X.on ? tp[q]->cols : 0; X.d0 = 0; X.start = (X.on && tp[q]->i16) ? BT2_I16_START : 0xff;
 		if(!X.on) continue;
 		int dlo, dhi; fill_band(P, X.rows, X.cols, tp[q]->minsc, exact, dlo, dhi);
 		if(dhi - dlo + 1 > BT2_LANES * K) { g_skipped++; return; }   // this K cannot hold the problem (the host picks K so that it can)
-		X.d0 = dlo; if(X.rows > rowsW) rowsW = X.rows; if(-dlo > mask_to) mask_to = -dlo;
+		X.d0 = dlo; if(X.rows > rowsW) rowsW = X.rows; if(-dlo > mask_to) mask_to = -dlo; if(dhi - dlo + 1 > widthW) widthW = dhi - dlo + 1;
 	}
 	for(int q = 0; q < 4; q++) if(tp[q]) { int dlo, dhi; fill_band(P, tp[q]->rows, tp[q]->cols, tp[q]->minsc, exact, dlo, dhi); if(dhi - dlo + 1 > BT2_LANES * K) return; }
-	const int iters = (int)fill_iters((uint32_t)rowsW, K);
+	// as the kernel: the sweep ends when the last lane that holds band cells has done its last row
+	const int vlast = (widthW - 1) / K;
+	int iters = ((rowsW + ((vlast + 2) >> 1) + PER - 1) / PER) * PER;
+	if(iters > (int)fill_iters((uint32_t)rowsW, K)) iters = (int)fill_iters((uint32_t)rowsW, K);
 	bool hasN = false; g_warps++;
 	static const uint8_t dummy[256] = {0};
 	for(int set = 0; set < 2; set++) {
@@ -122,7 +125,7 @@ template<int K, bool DBG> static void run_warp(const DevParams& P, const TProb* 
 		int nbad = 0;
 		for(int r = 0; r < t.rows; r++) for(int c = 0; c < t.cols; c++) {
 			const int dd = c - r - d0;
-			if(dd < 0 || dd >= BT2_LANES * K) continue;
+			if(dd < 0 || dd >= (vlast + 1) * K) continue;   // (lanes past the warp's widest band do not finish their rows)
 			uint8_t care = 0x7f;
 			if(c == 0) care &= ~(CF_EO | CF_EX);
 			if(r < P.gapbar || t.rows - 1 - r < P.gapbar) care &= ~(CF_EO | CF_EX | CF_FO | CF_FX | CF_HE | CF_HF);
