@@ -32,6 +32,21 @@ WORK = os.path.join(ROOT, "bench_work")
 REFBIN = os.path.join(ROOT, "oracle", "_ref")
 OPTS = "--sensitive --dpad 12"
 REF_LEN = 5_000_000
+# --config: the workloads of SURVEY 8(d).  c2 (default) is BASELINE configs[1], the one the metric is quoted on; the others are the larger
+# references as one GPU takes them (index built on first use with the reference's builder: 30 s at 100 Mbp, 16 min at 3.1 Gbp)
+CONFIGS = {
+    "c2":    {"name": "configs[1]", "ref": "5 Mbp i.i.d. reference", "len": 5_000_000, "seed": 12345, "repeats": 0.0, "opts": "--sensitive --dpad 12", "base": "iid5m"},
+    "c3":    {"name": "configs[2] (unpaired, one GPU)", "ref": "100 Mbp i.i.d. reference", "len": 100_000_000, "seed": 12346, "repeats": 0.0, "opts": "--sensitive --dpad 12", "base": "iid100m"},
+    "c4":    {"name": "configs[3] (one GPU)", "ref": "3.1 Gbp i.i.d. reference", "len": 3_100_000_000, "seed": 12347, "repeats": 0.0, "opts": "--very-sensitive --dpad 12", "base": "iid3100m"},
+    "c4rep": {"name": "configs[3], repeat-rich variant at 100 Mbp", "ref": "100 Mbp reference, 10 % of it 50 repeat families x 300 bp", "len": 100_000_000, "seed": 12346, "repeats": 0.1,
+              "opts": "--very-sensitive --dpad 12", "base": "rep100m"},
+}
+CFG = CONFIGS["c2"]
+
+
+def set_config(name):
+    global CFG, OPTS, REF_LEN
+    CFG = CONFIGS[name]; OPTS = CFG["opts"]; REF_LEN = CFG["len"]
 READ_LEN = 150
 METRIC = "aligned_reads_per_sec_150bp_sensitive_e2e"
 ALU_WARP_INST_PER_CLK_SM = 1.95   # VIMNMX.S16x2 / HSET2 / LOP3 share this pipe (measured, profiles/r1_pipe_bench.txt)
@@ -48,18 +63,31 @@ def log(*a):
 
 
 def make_reference():
-    """5 Mbp i.i.d. reference (seed 12345) + its .bt2l index, built once with the reference's own builder."""
+    """The config's synthetic reference (seeded) + its .bt2l index, built once with the reference's own builder."""
     os.makedirs(WORK, exist_ok=True)
-    base = os.path.join(WORK, "iid5m")
+    base = os.path.join(WORK, CFG["base"])
     fa = base + ".fa"
-    rng = np.random.default_rng(12345)
+    rng = np.random.default_rng(CFG["seed"])
     codes = rng.integers(0, 4, size=REF_LEN, dtype=np.uint8)
+    if CFG["repeats"] > 0:      # copies of 50 families x 300 bp with 2 % divergence until that fraction of the text is covered
+        nfam, flen = 50, 300
+        fams = rng.integers(0, 4, size=(nfam, flen), dtype=np.uint8)
+        ncop = int(CFG["repeats"] * REF_LEN / flen)
+        for c0 in range(0, ncop, 65536):
+            nb = min(65536, ncop - c0)
+            pos = rng.integers(0, REF_LEN - flen, size=nb)
+            cp = fams[rng.integers(0, nfam, size=nb)].copy()
+            m = rng.random((nb, flen)) < 0.02
+            cp[m] = (cp[m] + rng.integers(1, 4, size=int(m.sum()), dtype=np.uint8)) % 4
+            codes[pos[:, None] + np.arange(flen)[None, :]] = cp
     if not os.path.exists(base + ".4.bt2l"):
         seq = np.frombuffer(b"ACGT", dtype=np.uint8)[codes]
         with open(fa, "wb") as f:
             f.write(b">seq0\n")
-            for i in range(0, REF_LEN, 60):
-                f.write(seq[i:i + 60].tobytes() + b"\n")
+            lines = seq[: (REF_LEN // 60) * 60].reshape(-1, 60)
+            f.write(np.concatenate([lines, np.full((lines.shape[0], 1), 10, np.uint8)], axis=1).tobytes())
+            if REF_LEN % 60:
+                f.write(seq[(REF_LEN // 60) * 60:].tobytes() + b"\n")
         builder = os.path.join(REFBIN, "bowtie2-build-l")
         if not os.access(builder, os.X_OK):
             raise RuntimeError("oracle/_ref/bowtie2-build-l missing: run oracle/build_ref.sh where /root/reference exists")
@@ -228,7 +256,7 @@ def summarize_reference(runs, sweep, cores):
            "wall_s": wall, "wall_reads_per_s": reads / wall if wall > 0 else None,
            "search_s": sum(r["search_s"] or 0 for r in runs),
            "hot_path_s": hot, "hot_path_reads_per_s": treads / hot if hot > 0 else None,
-           "extendSeeds_s": ext, "cpu_gcups": treads * CELLS_PER_READ / ext / 1e9 if ext > 0 else None,
+           "extendSeeds_s": ext, "cpu_gcups": treads * CELLS_PER_READ / ext / 1e9 if ext > 0 and CFG["opts"] == "--sensitive --dpad 12" else None,   # (one DP per read there)
            "phase_s": {k: round(v, 4) for k, v in ph.items()}, "phase_table_reads": treads, "p_sweep": sweep}
     return out
 
@@ -270,7 +298,7 @@ def reference_arm(args, rank, world):
 
 def workload_config(n=None):
     """The same `config` object for both arms (the reference arm runs a bounded per-step sample of it, stated in cpu_baseline.sample)."""
-    return {"workload": "configs[1]: 5 Mbp i.i.d. reference, 1M x 150 bp simulated reads (1 %% substitutions, 1-bp indel in 10 %%), unpaired, %s" % OPTS,
+    return {"workload": "%s: %s, 1M x 150 bp simulated reads (1 %% substitutions, 1-bp indel in 10 %%), unpaired, %s" % (CFG["name"], CFG["ref"], OPTS),
             "reads_per_step_per_gpu": int(n if n is not None else os.environ.get("BT2_BENCH_READS", "1000000")), "parallelism": "reads sharded, index replicated per GPU",
             "l2": "inputs larger than L2 (300 MB of reads per step, DP cell flags written per problem; 126 MB L2)"}
 
@@ -310,8 +338,10 @@ def main():
     ap.add_argument("--reads", type=int, default=int(os.environ.get("BT2_BENCH_READS", "1000000")))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-file-to-file", action="store_true")
+    ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    set_config(args.config)
     if args.impl == "reference":
         return reference_arm(args, rank, world)
 

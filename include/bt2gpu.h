@@ -282,6 +282,13 @@ int bt2gpu_upload(bt2gpu_ctx *ctx, const bt2gpu_reads *in);
 int bt2gpu_run_resident(bt2gpu_ctx *ctx);
 int bt2gpu_fetch(bt2gpu_ctx *ctx, bt2gpu_results *out);
 
+/* What bt2gpu_create spent and holds (the index load path; the host side of it is Ebwt::readIntoMemory,
+ * bt2_io.cpp:39-633, and BitPairReference's constructor, reference.cpp:50-181):
+ *   ms[0] copies of the caller's index and reference arrays to HBM, ms[1] expansion of the sampled suffix array to a full one on the
+ *   device, ms[2] K-mer prefix table over it, ms[3] the rest (problem slots, streams);  bytes[0] index + reference as uploaded,
+ *   bytes[1] full suffix array, bytes[2] prefix table, bytes[3] per-batch working memory allocated at create. */
+int bt2gpu_get_create_info(const bt2gpu_ctx *ctx, double ms[4], uint64_t bytes[4]);
+
 int bt2gpu_get_counters(bt2gpu_ctx *ctx, bt2gpu_counters *c);
 int bt2gpu_reset_counters(bt2gpu_ctx *ctx);
 const char *bt2gpu_last_error(const bt2gpu_ctx *ctx);

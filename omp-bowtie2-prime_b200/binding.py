@@ -308,6 +308,14 @@ class GpuAligner:
         self._ck(self._g.bt2gpu_fetch(self.ptr, C.byref(r)), "bt2gpu_fetch")
         return Results(r)
 
+    def create_info(self):
+        """bt2gpu_get_create_info: what bt2gpu_create spent (ms) and holds (bytes)"""
+        ms = (C.c_double * 4)(); by = (C.c_uint64 * 4)()
+        self._g.bt2gpu_get_create_info.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self._g.bt2gpu_get_create_info(self.ptr, ms, by)
+        return {"ms": dict(zip(("upload", "suffix_array", "prefix_table", "slots"), [round(x, 1) for x in ms])),
+                "bytes": dict(zip(("index_and_reference", "suffix_array", "prefix_table", "slots"), list(by)))}
+
     def counters(self, reset=False):
         c = bt2gpu_counters()
         self._g.bt2gpu_get_counters(self.ptr, C.byref(c))

@@ -93,6 +93,7 @@ struct bt2gpu_ctx {
 	uint32_t n = 0, W = 0, maxOffs = 0; uint64_t nbases = 0;
 	uint64_t out_alns = 0, out_edits = 0;
 	Pools pools;
+	double create_ms[4] = { 0, 0, 0, 0 }; uint64_t create_bytes[4] = { 0, 0, 0, 0 };   // bt2gpu_get_create_info
 	uint32_t poolScale[4] = { 1, 1, 1, 1 };   // chunk / sat / aln / edit pool: doubled when a batch overflows it (the batch is then run again)
 	uint64_t poolRetries = 0;
 	bt2gpu_counters ctr;
@@ -118,7 +119,7 @@ template<typename T> T* upload(bt2gpu_ctx* c, const T* src, size_t n) {
 	T* d = nullptr;
 	CK(cudaMalloc((void**)&d, std::max<size_t>(n, 1) * sizeof(T) + 16));
 	if(n) CK(cudaMemcpy(d, src, n * sizeof(T), cudaMemcpyHostToDevice));
-	c->resident.push_back(d);
+	c->resident.push_back(d); c->create_bytes[0] += n * sizeof(T);
 	return d;
 }
 
@@ -559,7 +560,7 @@ __global__ void k_na_setup(NoAllocScratch* sc, uint32_t nprob, const uint32_t* s
 	pb.minsc = minsc[i]; pb.refl = 0; pb.tidx = 0; pb.triml = pb.corel = pb.corer = 0; pb.lrmax = -1; pb.ncand = 0;
 	if(ok) for(uint32_t k = 0; k <= c; k++) pb.rf[k] = rf[rf_off[i] + k];
 	ReadState& rs = sc->states[i];
-	rs.seq_off = seq_off[i]; rs.rdlen = (uint16_t)r;
+	rs.seq_off = seq_off[i]; rs.rdlen = (uint16_t)r; pb.seq_off = seq_off[i];
 }
 // one block per problem: dense flags (row-major rows x cols; 0x80 outside the band) out of the cell layout, candidates, counts
 __global__ void k_na_export(const DevParams* __restrict__ Pp, uint32_t nprob, const NoAllocScratch* sc, const uint64_t* flags_off, uint8_t* flags, uint16_t* cand, uint32_t* ncand, int32_t* lrmax) {
@@ -638,6 +639,8 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 			CK(cudaEventCreate(&c->h2dspan[k].a)); CK(cudaEventCreate(&c->h2dspan[k].b)); CK(cudaEventCreate(&c->d2hspan[k].a)); CK(cudaEventCreate(&c->d2hspan[k].b));
 		}
 		setup_params(c, p);
+		auto now_ms = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
+		const double t_start = now_ms(); double t_sa = 0, t_kt = 0;
 		CK(cudaMalloc((void**)&c->dP, sizeof(DevParams)));
 		CK(cudaMemcpy(c->dP, &c->P, sizeof(DevParams), cudaMemcpyHostToDevice));
 		// ---- index
@@ -653,7 +656,8 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		  if(!(efs && atoi(efs) == 0) && hix->len < 0xfffffff0ull && hix->offRate >= 0 && hix->offRate < 31) {
 			const uint64_t nrows = hix->len + 1;
 			uint32_t* sa = nullptr;
-			CK(cudaMalloc((void**)&sa, nrows * 4 + 16)); c->resident.push_back(sa);
+			const double t0 = now_ms();
+			CK(cudaMalloc((void**)&sa, nrows * 4 + 16)); c->resident.push_back(sa); c->create_bytes[1] = nrows * 4;
 			CK(cudaMemset(sa, 0xff, nrows * 4));
 			const uint64_t nsample = (nrows + ((1ull << hix->offRate) - 1)) >> hix->offRate;
 			if(nsample > hix->offsLen) throw std::string("bt2gpu_create: SA sample shorter than the index needs");
@@ -665,7 +669,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 			CK(cudaMemcpy(&hbad, dbad, 8, cudaMemcpyDeviceToHost)); CK(cudaFree(dbad));
 			CK(cudaGetLastError());
 			if(hbad) throw std::string("bt2gpu_create: inconsistent index (suffix-array expansion left rows unresolved)");
-			ix.sa32 = sa;
+			ix.sa32 = sa; t_sa = now_ms() - t0;
 		  } }
 		// ---- reference
 		std::vector<uint64_t> tstart(hrf->nrecs), cum(hrf->nrecs), rec0;
@@ -689,7 +693,8 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 			if(K > hix->ftabChars || (ek && atoi(ek) > 0)) {
 				const uint64_t nk = 1ull << (2 * K), nrows = hix->len + 1;
 				uint32_t* kt = nullptr;
-				CK(cudaMalloc((void**)&kt, (nk + 1) * 4 + 16)); c->resident.push_back(kt);
+				const double t0 = now_ms();
+				CK(cudaMalloc((void**)&kt, (nk + 1) * 4 + 16)); c->resident.push_back(kt); c->create_bytes[2] = (nk + 1) * 4;
 				const uint32_t* tw = reinterpret_cast<const uint32_t*>(rf.buf);
 				k_build_ktab<<<(uint32_t)((nrows + 255) / 256), 256>>>(ix, tw, kt, nrows, (uint32_t)K);
 				k_ktab_tail<<<(uint32_t)((nk + 255) / 256), 256>>>(ix, tw, kt, nrows, (uint32_t)K);
@@ -710,13 +715,15 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 						}
 					}
 				}
-				ix.ktab = kt; ix.ktabChars = K;
+				ix.ktab = kt; ix.ktabChars = K; t_kt = now_ms() - t0;
 			}
 		  } }
 		rf.rec_off = upload(c, hrf->rec_off, hrf->nrecs); rf.rec_len = upload(c, hrf->rec_len, hrf->nrecs);
 		rf.rec_tstart = upload(c, tstart.data(), tstart.size()); rf.rec_cum = upload(c, cum.data(), cum.size());
 		rf.ref_rec0 = upload(c, rec0.data(), rec0.size()); rf.nrecs = hrf->nrecs;
 		// ---- problem slots
+		CK(cudaDeviceSynchronize());
+		const double t_slots = now_ms();
 		const char* es = getenv("BT2GPU_SLOTS"); const char* eb = getenv("BT2GPU_BATCH");
 		size_t freeB = 0, totB = 0; CK(cudaMemGetInfo(&freeB, &totB));
 		const size_t slotCells = fill_cell_bytes(BT2GPU_MAX_ROWS, 4);   // K = 4 holds every band of the default scoring scheme; a batch that needs more gets fewer slots
@@ -736,6 +743,9 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		  c->hbox = reinterpret_cast<volatile HostBox*>(hb); void* db = nullptr; CK(cudaHostGetDevicePointer(&db, hb, 0)); c->dbox = reinterpret_cast<HostBox*>(db); }
 		noalloc_device(device);   // bt2gpu_fill_noalloc's per-device set-up happens here, not inside its first call
 		CK(cudaDeviceSynchronize());
+		c->create_bytes[3] = c->probs.cap + c->cells.cap + c->pcache.cap;
+		{ const double t_end = now_ms(); c->create_ms[1] = t_sa; c->create_ms[2] = t_kt; c->create_ms[3] = t_end - t_slots;
+		  c->create_ms[0] = (t_slots - t_start) - t_sa - t_kt; }
 	} catch(const std::string& e) {
 		if(err && errlen) snprintf(err, errlen, "%s", e.c_str());
 		if(c) bt2gpu_destroy(c);
@@ -784,7 +794,7 @@ int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, c
 			if(rows[i] < 1 || rows[i] > BT2GPU_MAX_ROWS || cols[i] < 1 || cols[i] >= BT2GPU_MAX_COLS) throw std::string("bt2gpu_test_fill: bad problem size");
 			memset(&hs[i], 0, sizeof(ReadState)); hs[i].seq_off = seq_off[i]; hs[i].rdlen = rows[i];
 			memset(&hp[i], 0, sizeof(Problem));
-			hp[i].read = i; hp[i].rows = rows[i]; hp[i].cols = cols[i]; hp[i].fw = 1; hp[i].minsc = minsc[i];
+			hp[i].read = i; hp[i].rows = rows[i]; hp[i].cols = cols[i]; hp[i].fw = 1; hp[i].minsc = minsc[i]; hp[i].seq_off = seq_off[i];
 			memcpy(hp[i].rf, rf + rf_off[i], (size_t)cols[i] + 1);
 			nb = std::max<uint64_t>(nb, (uint64_t)seq_off[i] + rows[i]);
 			int dlo, dhi; fill_band(ctx->P, rows[i], cols[i], minsc[i], exact, dlo, dhi);
@@ -840,6 +850,11 @@ int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, c
 	})
 }
 
+int bt2gpu_get_create_info(const bt2gpu_ctx* ctx, double ms[4], uint64_t bytes[4]) {
+	if(!ctx || !ms || !bytes) return -1;
+	for(int i = 0; i < 4; i++) { ms[i] = ctx->create_ms[i]; bytes[i] = ctx->create_bytes[i]; }
+	return 0;
+}
 int bt2gpu_get_counters(bt2gpu_ctx* ctx, bt2gpu_counters* c) { if(!ctx || !c) return -1; *c = ctx->ctr; return 0; }
 int bt2gpu_reset_counters(bt2gpu_ctx* ctx) { if(!ctx) return -1; memset(&ctx->ctr, 0, sizeof(ctx->ctr)); return 0; }
 const char* bt2gpu_last_error(const bt2gpu_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }

@@ -308,6 +308,7 @@ struct alignas(16) Problem {
 	// outputs of K_fill
 	int32_t  lrmax;            // max raw H in the last row
 	uint32_t ncand;
+	uint32_t seq_off, padq[3]; // the read's offset into the batch's seq / qual arrays (ReadState::seq_off: one load less on the fill's way to them)
 	uint32_t cand[BT2GPU_MAX_COLS + 8]; // sorted best-first: (rawH << 8) | col; at a 16-byte boundary (read in groups of 4 by the backtrace)
 	uint8_t  rf[BT2GPU_MAX_COLS + 8];   // reference masks for columns 0..cols (cols+1 fetched)
 };

@@ -109,7 +109,7 @@ BT2_HD int advance(const DevParams& P, const DevIndex& ix, const DevRef& rf, con
 		for(int64_t k = 0; k < leftNs; k++) prob.rf[k] = 16;
 		if(inner > 0) ref_masks(rf, prob.rf + leftNs, tidx, rfi < 0 ? 0 : (uint64_t)rfi, (uint32_t)inner);
 		for(int64_t k = leftNs + (inner > 0 ? inner : 0); k < rflenFull; k++) prob.rf[k] = 16;
-		prob.rows = (uint16_t)rdlen; prob.cols = (uint16_t)(rflenFull - 1);
+		prob.rows = (uint16_t)rdlen; prob.cols = (uint16_t)(rflenFull - 1); prob.seq_off = rs.seq_off;
 		prob.fw = fw ? 1 : 0;
 		prob.d0 = 0;   // set by the fill (k_fill.cuh)
 		// default build: 8-bit fill, minsc clamped (bt2_search.cpp:2487-2491, aligner_sw.cpp:84).  -DENABLE_I16 build: --no-sse8 or

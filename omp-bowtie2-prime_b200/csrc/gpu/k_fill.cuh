@@ -72,7 +72,7 @@ template<int K> struct FillShared {
 };
 static_assert(sizeof(FillRow2) * BT2_FILL_NROW >= sizeof(uint32_t) * (BT2GPU_MAX_COLS + 8), "candidate keys overlay row2[0]");
 
-struct FillProb { int rows, cols, d0, start; bool on; };   // start: H of row -1 (0xff, or BT2_I16_START on the reference's 16-bit path)
+struct FillProb { int rows, cols, d0, start, minsc; bool on, fw; };   // start: H of row -1 (0xff, or BT2_I16_START on the reference's 16-bit path)
 
 // What one lane holds of one problem set.
 template<int K> struct FillSet {
@@ -202,37 +202,21 @@ template<int K> BT2_SIMD void fill_set_init(FillSet<K>& S, FillShared<K>& sh, co
 // against a mismatching / an N reference character, and the (negated) gap penalties; inside the gap barrier
 // (aligner_swsse_ee_u8.cpp:101-115: first/last gapbar rows), in the virtual rows and (reference gaps) into row 0 the gap
 // penalties are large enough to keep E and F at 0
-#define BT2_FILL_ROW_ITERS ((BT2_FILL_NROW + BT2_LANES - 1) / BT2_LANES)
 template<int K> BT2_SIMD void fill_build_rows(const DevParams& P, FillShared<K>& sh, const int set, const FillProb& A, const FillProb& B,
                                               const uint8_t* seqA, const uint8_t* qualA, bool fwA, const uint8_t* seqB, const uint8_t* qualB, bool fwB,
                                               const uint32_t lane, const int nrow) {
-	// all of the lane's base / quality bytes first (independent loads in flight together), then the table entries
-	uint8_t cc[BT2_FILL_ROW_ITERS][2], qq[BT2_FILL_ROW_ITERS][2];
-	#pragma unroll
-	for(int it = 0; it < BT2_FILL_ROW_ITERS; it++) {
-		const int r = (int)lane + it * BT2_LANES - BT2_FILL_ROWPAD;
-		#pragma unroll
-		for(int x = 0; x < 2; x++) {
-			const FillProb& X = x ? B : A; const uint8_t* rseq = x ? seqB : seqA; const uint8_t* rqual = x ? qualB : qualA; const bool fw = x ? fwB : fwA;
-			const bool real = X.on && r >= 0 && r < X.rows;
-			const int at = fw ? r : X.rows - 1 - r;
-			cc[it][x] = real ? rseq[at] : (uint8_t)4; qq[it][x] = real ? rqual[at] : (uint8_t)0;
-		}
-	}
-	#pragma unroll
-	for(int it = 0; it < BT2_FILL_ROW_ITERS; it++) {
-		const int idx = (int)lane + it * BT2_LANES;
-		if(idx >= nrow) break;
+	for(int idx = (int)lane; idx < nrow; idx += BT2_LANES) {
 		const int r = idx - BT2_FILL_ROWPAD;
 		int rdc[2], pen[2], penN[2], rdgo[2], rfgo[2], rfge[2];
 		#pragma unroll
 		for(int x = 0; x < 2; x++) {
-			const FillProb& X = x ? B : A; const bool fw = x ? fwB : fwA;
+			const FillProb& X = x ? B : A; const uint8_t* rseq = x ? seqB : seqA; const uint8_t* rqual = x ? qualB : qualA; const bool fw = x ? fwB : fwA;
 			const bool real = X.on && r >= 0 && r < X.rows;
 			int c = 4, q = 0;
 			if(real) {
-				c = cc[it][x]; if(!fw) c = c > 3 ? 4 : 3 - c;
-				q = (int)qq[it][x] - 33; if(q < 0) q = 0; if(q > 255) q = 255;
+				if(fw) { c = rseq[r]; q = rqual[r]; }
+				else { const int c0 = rseq[X.rows - 1 - r]; c = c0 > 3 ? 4 : 3 - c0; q = rqual[X.rows - 1 - r]; }
+				q -= 33; if(q < 0) q = 0; if(q > 255) q = 255;
 			}
 			rdc[x] = c > 3 ? 7 : c;
 			pen[x] = real ? (c > 3 ? P.npens[q] : P.mmpens[q]) : 0;
@@ -317,24 +301,69 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 	const uint32_t slot0 = (blockIdx.x * BT2_FILL_WARPS + warp) * 4u;
 	if(slot0 >= a.nprob) return;
 	FillShared<K>& sh = shs[warp];
-	// ---- the warp's four problems: set 0 = slots 0, 1 (y = 0), set 1 = slots 2, 3 (y = 1)
+	// ---- the warp's four problems: set 0 = slots 0, 1 (y = 0), set 1 = slots 2, 3 (y = 1).
+	// Phase A: everything the warp reads from global memory, issued together: the problems' headers (one 16-byte load each), the window
+	// masks (8 bytes per lane) and the reads' bases and qualities (a byte per lane and load), staged as they are in shared memory that
+	// the sweep's tables take over later.  (ncu r2: a third of the warps' stall samples sat in this prologue, waiting on dependent loads
+	// it had issued one by one.)
+	static_assert(offsetof(Problem, minsc) == 12 && offsetof(Problem, rf) % 8 == 0, "header is read as one uint4, the masks as uint2");
 	FillProb pr[4];
+	uint4 hd[4]; uint32_t so[4];
+	#pragma unroll
+	for(int q = 0; q < 4; q++) {
+		const bool valid = slot0 + q < a.nprob;
+		hd[q] = valid ? *reinterpret_cast<const uint4*>(&a.probs[slot0 + q]) : make_uint4(BT2_NIL, 0, 0, 0);
+		so[q] = valid ? a.probs[slot0 + q].seq_off : 0u;
+	}
+	uint8_t* const raw_rf = reinterpret_cast<uint8_t*>(&sh.hl[0][0]);        // [4][BT2GPU_MAX_COLS + 8] masks as the extension step left them
+	uint8_t* const raw_sq = reinterpret_cast<uint8_t*>(&sh.refw[0][0]);      // [4][2][BT2GPU_MAX_ROWS] bases, qualities (forward read)
+	static_assert(sizeof(sh.hl) >= 4 * (BT2GPU_MAX_COLS + 8) && sizeof(sh.refw) >= 8 * BT2GPU_MAX_ROWS, "staging fits the arrays it borrows");
+	#pragma unroll
+	for(int q = 0; q < 4; q++) {
+		FillProb& X = pr[q];
+		X.on = hd[q].x != BT2_NIL;
+		X.rows = X.on ? (int)(hd[q].y & 0xffffu) : 0; X.cols = X.on ? (int)(hd[q].y >> 16) : 0; X.d0 = 0;
+		X.fw = (hd[q].z & 0xffu) != 0; X.start = (X.on && (hd[q].z & 0x4000u)) ? BT2_I16_START : 0xff; X.minsc = (int)hd[q].w;
+	}
+	{ // loads first, all of them; the stores into the staging area (which wait for their loads) after
+		constexpr int NIT = (BT2GPU_MAX_ROWS + BT2_LANES - 1) / BT2_LANES;
+		uint2 mk[4]; uint8_t sb[4][NIT], qb[4][NIT];
+		#pragma unroll
+		for(int q = 0; q < 4; q++) {
+			const FillProb& X = pr[q];
+			mk[q] = (X.on && lane * 8u < (uint32_t)X.cols + 1u) ? *reinterpret_cast<const uint2*>(a.probs[slot0 + q].rf + lane * 8u) : make_uint2(0, 0);
+			#pragma unroll
+			for(int it = 0; it < NIT; it++) {
+				const int r = (int)lane + it * BT2_LANES;
+				const bool in = X.on && r < X.rows;
+				sb[q][it] = in ? a.seq[so[q] + r] : (uint8_t)0; qb[q][it] = in ? a.qual[so[q] + r] : (uint8_t)0;
+			}
+		}
+		#pragma unroll
+		for(int q = 0; q < 4; q++) {
+			const FillProb& X = pr[q];
+			if(!X.on) continue;
+			if(lane * 8u < (uint32_t)X.cols + 1u) *reinterpret_cast<uint2*>(raw_rf + q * (BT2GPU_MAX_COLS + 8) + lane * 8u) = mk[q];
+			#pragma unroll
+			for(int it = 0; it < NIT; it++) {
+				const int r = (int)lane + it * BT2_LANES;
+				if(r < X.rows) { raw_sq[(2 * q) * BT2GPU_MAX_ROWS + r] = sb[q][it]; raw_sq[(2 * q + 1) * BT2GPU_MAX_ROWS + r] = qb[q][it]; }
+			}
+		}
+	}
 	int rowsW = 0, mask_to = 0, widthW = 1; bool any = false;
 	#pragma unroll
 	for(int q = 0; q < 4; q++) {
-		const uint32_t slot = slot0 + q;
 		FillProb& X = pr[q];
-		X.on = slot < a.nprob && a.probs[slot].read != BT2_NIL;
-		X.rows = X.on ? a.probs[slot].rows : 0; X.cols = X.on ? a.probs[slot].cols : 0; X.d0 = 0; X.start = X.on ? prob_start(a.probs[slot]) : 0xff;
 		if(!X.on) continue;
 		any = true;
-		int dlo, dhi; fill_band(P, X.rows, X.cols, a.probs[slot].minsc, a.exact != 0, dlo, dhi);
+		int dlo, dhi; fill_band(P, X.rows, X.cols, X.minsc, a.exact != 0, dlo, dhi);
 		if(dhi - dlo + 1 > BT2_LANES * K) { if(lane == 0) atomicOr(a.error, 64u); dhi = dlo + BT2_LANES * K - 1; }
 		X.d0 = dlo;
 		if(X.rows > rowsW) rowsW = X.rows;
 		if(-dlo > mask_to) mask_to = -dlo;
 		if(dhi - dlo + 1 > widthW) widthW = dhi - dlo + 1;
-		if(lane == 0) { a.probs[slot].lay = (uint8_t)((a.probs[slot].lay & 0x40u) | K | ((q >> 1) << 7)); a.probs[slot].d0 = (int16_t)dlo; }
+		if(lane == 0) { a.probs[slot0 + q].lay = (uint8_t)(((hd[q].z >> 8) & 0x40u) | K | ((q >> 1) << 7)); a.probs[slot0 + q].d0 = (int16_t)dlo; }
 	}
 	if(!any) return;
 	constexpr int PER = 16 / K;
@@ -342,25 +371,20 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 	const int vlast = (widthW - 1) / K;
 	int iters = ((rowsW + ((vlast + 2) >> 1) + PER - 1) / PER) * PER;
 	if(iters > (int)fill_iters((uint32_t)rowsW, K)) iters = (int)fill_iters((uint32_t)rowsW, K);
+	__syncwarp();
+	// ---- phase B: the sweep's tables out of the staged bytes: row tables first (they read the bases the window table will overwrite)
+	#pragma unroll
+	for(int set = 0; set < 2; set++)
+		fill_build_rows<K>(P, sh, set, pr[2 * set], pr[2 * set + 1],
+		                   raw_sq + (4 * set) * BT2GPU_MAX_ROWS, raw_sq + (4 * set + 1) * BT2GPU_MAX_ROWS, pr[2 * set].fw,
+		                   raw_sq + (4 * set + 2) * BT2GPU_MAX_ROWS, raw_sq + (4 * set + 3) * BT2GPU_MAX_ROWS, pr[2 * set + 1].fw, lane, BT2_FILL_ROWPAD + iters + 1);
+	__syncwarp();
 	bool hasN = false;
 	#pragma unroll
-	for(int set = 0; set < 2; set++) {
-		const FillProb& A = pr[2 * set]; const FillProb& B = pr[2 * set + 1];
-		const uint8_t* sq[2] = { a.seq, a.seq }; const uint8_t* ql[2] = { a.qual, a.qual }; const uint8_t* rf[2] = { nullptr, nullptr }; bool fw[2] = { true, true };
-		#pragma unroll
-		for(int x = 0; x < 2; x++) {
-			const FillProb& X = x ? B : A;
-			if(!X.on) continue;
-			const Problem& pb = a.probs[slot0 + 2 * set + x];
-			const ReadState& rs = a.states[pb.read];
-			sq[x] = a.seq + rs.seq_off; ql[x] = a.qual + rs.seq_off; rf[x] = pb.rf; fw[x] = pb.fw != 0;
-		}
-		fill_build_rows<K>(P, sh, set, A, B, sq[0], ql[0], fw[0], sq[1], ql[1], fw[1], lane, BT2_FILL_ROWPAD + iters + 1);
-		hasN = fill_build_ref<K>(sh, set, A, B, rf[0], rf[1], lane, BT2_FILL_ROWPAD + iters + BT2_LANES * K + 1) || hasN;
-	}
-	for(int idx = (int)lane; idx < 4 * (BT2GPU_MAX_COLS + 8); idx += 32) (&sh.hl[0][0])[idx] = 0;
+	for(int set = 0; set < 2; set++)
+		hasN = fill_build_ref<K>(sh, set, pr[2 * set], pr[2 * set + 1], raw_rf + (2 * set) * (BT2GPU_MAX_COLS + 8), raw_rf + (2 * set + 1) * (BT2GPU_MAX_COLS + 8),
+		                         lane, BT2_FILL_ROWPAD + iters + BT2_LANES * K + 1) || hasN;
 	const bool refHasN = __any_sync(0xffffffffu, hasN);
-	__syncwarp();
 	if(a.pcache) { // the problems' characters as 4-bit codes, for the backtrace's edits (dev_common.cuh)
 		#pragma unroll
 		for(int q = 0; q < 4; q++) {
@@ -373,16 +397,17 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 				const int r = (int)lane * 8 + k, c = (int)lane * 8 + k;
 				const uint32_t rc = r < pr[q].rows ? ((sh.row[set][BT2_FILL_ROWPAD + r].rdc2 >> (16 * x)) & 0xffu) : 0u;
 				wr |= (rc > 3u ? 4u : rc) << (4 * k);
-				const int t = c - pr[q].d0;   // column c sits at t = c - d0 (every in-window column of the band rows; others read here directly)
 				uint32_t fc = 0;
-				if(c < pr[q].cols) { const uint32_t m = a.probs[slot0 + q].rf[c]; fc = m > 15 ? 4u : (m >= 8 ? 3u : (m >= 4 ? 2u : (m >= 2 ? 1u : 0u))); }
-				(void)t;
+				if(c < pr[q].cols) { const uint32_t m = raw_rf[q * (BT2GPU_MAX_COLS + 8) + c]; fc = m > 15 ? 4u : (m >= 8 ? 3u : (m >= 4 ? 2u : (m >= 2 ? 1u : 0u))); }
 				wf |= fc << (4 * k);
 			}
 			if(lane < BT2_PC_RD) pcw[lane] = wr;
 			if(lane < BT2_PC_RF) pcw[BT2_PC_RD + lane] = wf;
 		}
 	}
+	__syncwarp();
+	for(int idx = (int)lane; idx < 4 * (BT2GPU_MAX_COLS + 8); idx += 32) (&sh.hl[0][0])[idx] = 0;   // (the staged masks are done with)
+	__syncwarp();
 	// ---- per-lane state: slot 0 of every iteration is set (lane & 1), slot 1 the other one
 	const int set0 = (int)(lane & 1u), set1 = set0 ^ 1;
 	FillSet<K> S0, S1;
@@ -412,11 +437,12 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 	__syncwarp();
 	// ---- last-row candidates: H-0xff >= minsc, sorted by (score desc, col desc)
 	uint32_t* const ckey = reinterpret_cast<uint32_t*>(sh.row2[0]);
+	#pragma unroll
 	for(int q = 0; q < 4; q++) {
 		if(!pr[q].on) continue;
 		Problem& pb = a.probs[slot0 + q];
 		const int cols = pr[q].cols;
-		const int minsc = pb.minsc;
+		const int minsc = pr[q].minsc;
 		int lrmax = 0; uint32_t ncand = 0;
 		for(int c0 = 0; c0 < cols; c0 += 32) {
 			const int c = c0 + (int)lane;

@@ -114,8 +114,10 @@ def main():
     # ---- this library on the sample
     t0 = time.time()
     job = pkg.Job(base, OPTS)
+    out["host_index_load_s"] = round(time.time() - t0, 2)   # .bt2l files -> host arrays (libbt2host; the reference: Ebwt::loadIntoMemory)
     gpu = pkg.GpuAligner(job, 0)
     out["create_s"] = round(time.time() - t0, 2)      # index load + upload + suffix-array expansion on the device
+    out["create_info"] = gpu.create_info()
     batch = job.fastq(fq_s)
     res = gpu.align(batch)
     got = sorted_records(job.sam_bytes(batch, res, 1))
