@@ -123,12 +123,13 @@ def simulate_reads(codes, n, seed):
     return np.frombuffer(b"ACGT", dtype=np.uint8)[rd]  # ASCII [n, L]
 
 
-def write_fastq(path, ascii_reads):
+def write_fastq(path, ascii_reads, first=0, mode="wb"):
     n, L = ascii_reads.shape
     q = b"I" * L
-    with open(path, "wb") as f:
+    with open(path, mode) as f:
         for i in range(n):
-            f.write(b"@r%d\n" % i + ascii_reads[i].tobytes() + b"\n+\n" + q + b"\n")
+            f.write(b"@r%d\n" % (first + i) + ascii_reads[i].tobytes() + b"\n+\n" + q + b"\n")
+        return f.tell()
 
 
 class ClockSampler(threading.Thread):
@@ -329,6 +330,51 @@ def file_to_file(pkg, job, ascii_reads, device):
                 os.remove(f)
 
 
+def file_to_file_sharded(pkg, job, ascii_reads, device, rank, world, dist, torch):
+    """SURVEY 8(e) as a file-to-file run on N GPUs of one box: ONE FASTQ file on tmpfs (every rank appends its reads in rank order), the
+    byte range of shard r goes to rank r (its own reader / aligner / sink pipeline, index replicated), every rank writes its part of the
+    SAM, parts are concatenated in shard order.  No collective on the data path; time = barrier to barrier, max over ranks.  All ranks
+    share the host's cores for parsing and formatting, which is what limits it (file_to_file at N = 1 is already host-bound)."""
+    stream = importlib.import_module("omp-bowtie2-prime_b200.stream")
+    tmp = "/dev/shm" if os.path.isdir("/dev/shm") else WORK
+    fq = os.path.join(tmp, "bt2gpu_bench_all.fq")
+    n = ascii_reads.shape[0]
+    ends = torch.zeros(world, dtype=torch.int64, device="cuda")
+    for r in range(world):                       # ranks append in turn: one file, shard boundaries = what each rank wrote
+        if r == rank:
+            ends[r] = write_fastq(fq, ascii_reads, first=r * n, mode="wb" if r == 0 else "ab")
+        dist.barrier()
+    dist.all_reduce(ends, op=dist.ReduceOp.SUM)
+    ends = [int(x) for x in ends.tolist()]
+    start, end = (ends[rank - 1] if rank else 0), ends[rank]
+    part = os.path.join(tmp, "bt2gpu_bench.sam.%d" % rank)
+    al = [pkg.GpuAligner(job, device), pkg.GpuAligner(job, device)]
+    try:
+        stream.fastq_to_sam(job, fq, part, device, aligners=al, start=start, end=end, header=rank == 0)     # warm-up
+        best = None
+        for _ in range(2):
+            dist.barrier(); torch.cuda.synchronize()
+            t0 = time.time()
+            nr, nb = stream.fastq_to_sam(job, fq, part, device, aligners=al, start=start, end=end, header=rank == 0)
+            dist.barrier()
+            dt = torch.tensor([time.time() - t0], dtype=torch.float64, device="cuda")
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            best = float(dt.item()) if best is None else min(best, float(dt.item()))
+        tot = torch.tensor([nr, nb], dtype=torch.int64, device="cuda")
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        return {"value": int(tot[0].item()) / best, "unit": "reads/s", "reads": int(tot[0].item()), "fastq_bytes": ends[-1], "sam_bytes": int(tot[1].item()),
+                "seconds": best, "where": tmp, "shards": world, "host_cores": cpu_cores(),
+                "note": "one FASTQ file, one byte range per rank -> parse -> bt2gpu_align_batch -> SAM formatting -> one SAM part per rank (concatenated in shard "
+                        "order); limited by the host cores all ranks share for parsing and formatting"}
+    finally:
+        for g in al:
+            g.close()
+        dist.barrier()
+        for f in ([fq] if rank == 0 else []) + [part]:
+            if os.path.exists(f):
+                os.remove(f)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -472,9 +518,14 @@ def main():
             "int_alu": {"kernel": "k_fill", "achieved_gcups": fill_gcups, "peak_gcups": alu_peak, "frac": fill_gcups / alu_peak},
             "e2e": {"value": total_reads / e2e_s, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(ctr["launches"]), "clocks": clocks}
-    if rank == 0 and world == 1 and not args.no_file_to_file:
+    if not args.no_file_to_file:
         try:
-            line["file_to_file"] = file_to_file(pkg, job, ascii_reads, local)
+            if world == 1:
+                line["file_to_file"] = file_to_file(pkg, job, ascii_reads, local)
+            else:
+                f2f = file_to_file_sharded(pkg, job, ascii_reads, local, rank, world, dist, torch)
+                if rank == 0:
+                    line["file_to_file"] = f2f
         except Exception as e:
             line["file_to_file"] = {"value": None, "error": str(e)[:200]}
     if rank == 0:

@@ -11,8 +11,10 @@ import threading
 from .binding import GpuAligner
 
 
-def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=96 << 20, mode=1, aligners=None):
-    """Returns (reads, bytes written).  `aligners`: two GpuAligner of `job` to reuse (else created and closed here)."""
+def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=96 << 20, mode=1, aligners=None, start=0, end=None, header=True):
+    """Returns (reads, bytes written).  `aligners`: two GpuAligner of `job` to reuse (else created and closed here).
+    start / end: byte range of the file to take (both at record starts): a shard of a multi-GPU job (reads shard by batch,
+    every device holds a replica of the index, the per-shard SAM files are concatenated in shard order); header=False for shards > 0."""
     own = aligners is None
     if own:
         aligners = [GpuAligner(job, device), GpuAligner(job, device)]
@@ -22,9 +24,9 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=96 << 20, mode=1, a
 
     def reader():
         try:
-            off = 0
-            while not errors:
-                b, nxt = job.fastq_range(fastq, off, chunk_bytes)
+            off = start
+            while not errors and (end is None or off < end):
+                b, nxt = job.fastq_range(fastq, off, chunk_bytes if end is None else min(chunk_bytes, end - off))
                 if b.n == 0:
                     b.close()
                     break
@@ -39,7 +41,8 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=96 << 20, mode=1, a
     def sink():
         try:
             with open(out_path, "wb") as f:
-                f.write(job.sam_header().encode("latin-1"))
+                if header:
+                    f.write(job.sam_header().encode("latin-1"))
                 while True:
                     item = done.get()
                     if item is None:

@@ -16,6 +16,8 @@ run() { # name index reads opts
 }
 "$B/bowtie2-build-l" "$HERE/lambda_virus.fa" "$T/lambda" >/dev/null 2>&1
 run lambda_default "$T/lambda" "$HERE/lambda_reads_1k.fq" ""
+cp "$REF/example/reads/reads_1.fq" "$HERE/lambda_reads_10k.fq"     # BASELINE configs[0] in full
+run lambda_default_10k "$T/lambda" "$HERE/lambda_reads_10k.fq" ""
 run lambda_k3_vs   "$T/lambda" "$HERE/lambda_reads_1k.fq" "-k 3 --very-sensitive"
 # synthetic: 300 kbp i.i.d. reference, 3 sequences, 20% repeat families
 python "$ROOT/tools/gen_data.py" ref "$T/syn.fa" 300000 --seed 4242 --repeats 0.2 --nseq 3

@@ -23,6 +23,23 @@ def test_oracle_matches_reference_golden(name):
     orc.close(); batch.close(); job.close()
 
 
+def test_oracle_matches_reference_on_the_whole_shipped_example():
+    """BASELINE configs[0] in full: all 10 000 reads of example/reads/reads_1.fq on the lambda phage index; the sorted SAM the unmodified
+    reference printed here has the md5 the survey recorded (051cc442...) and 6 854 aligned reads"""
+    if not common.have_builder():
+        pytest.skip("no builder")
+    import hashlib, os
+    want = common.golden_records("lambda_default_10k.sam")
+    assert hashlib.md5(open(os.path.join(common.GOLD, "lambda_default_10k.sam"), "rb").read()).hexdigest() == "051cc442466a220ffbbce47c492a3ca2"
+    job = pkg.Job(common.index_base("lambda"), "")
+    batch = job.fastq(os.path.join(common.GOLD, "lambda_reads_10k.fq"))
+    orc = common.Oracle(job)
+    got = common.sorted_records(job.sam(batch, orc.align(batch), mode=1))
+    assert got == sorted(want, key=lambda s: s.encode("latin-1"))
+    assert sum(1 for l in got if not int(l.split("\t")[1]) & 4) == 6854
+    orc.close()
+
+
 def test_oracle_thread_count_independent():
     if not common.have_builder():
         pytest.skip("no builder")
