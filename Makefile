@@ -16,7 +16,7 @@ $(PKG)/libbt2gpu.so: $(wildcard $(GPU)/*.cu $(GPU)/*.cuh) include/bt2gpu.h
 	$(NVCC) $(NVFLAGS) -o $@ $(GPU)/bt2gpu.cu
 
 $(PKG)/libbt2host.so: $(wildcard $(HOST)/*.cpp $(HOST)/*.hpp) include/bt2gpu.h include/bt2host.h
-	g++ $(CXXFLAGS) -shared -o $@ $(HOST)/host_index.cpp $(HOST)/host_reads.cpp $(HOST)/host_sink.cpp $(HOST)/host_api.cpp
+	g++ $(CXXFLAGS) -O3 -shared -o $@ $(HOST)/host_index.cpp $(HOST)/host_reads.cpp $(HOST)/host_sink.cpp $(HOST)/host_api.cpp
 
 oracle: $(PKG)/libbt2gpu.so
 	$(MAKE) -C oracle all

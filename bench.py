@@ -304,26 +304,34 @@ def workload_config(n=None):
             "l2": "inputs larger than L2 (300 MB of reads per step, DP cell flags written per problem; 126 MB L2)"}
 
 
-def file_to_file(pkg, job, ascii_reads, device):
+def file_to_file(pkg, job, ascii_reads, device, repeat=4):
     """FASTQ file -> SAM file on one GPU (omp-bowtie2-prime_b200/stream.py: reader thread, aligner, sink thread), both files on
-    tmpfs: the like-for-like of the reference process's wall time (cpu_baseline.wall_reads_per_s: FASTQ file -> SAM to /dev/null)."""
+    tmpfs: the like-for-like of the reference process's wall time (cpu_baseline.wall_reads_per_s: FASTQ file -> SAM to /dev/null).
+    The file holds the workload's reads `repeat` times over (own names), so that the three-stage pipeline runs in its steady state."""
     stream = importlib.import_module("omp-bowtie2-prime_b200.stream")
     tmp = "/dev/shm" if os.path.isdir("/dev/shm") else WORK
     fq, sam = os.path.join(tmp, "bt2gpu_bench.fq"), os.path.join(tmp, "bt2gpu_bench.sam")
-    write_fastq(fq, ascii_reads)
+    n = ascii_reads.shape[0]
+    for r in range(repeat):
+        write_fastq(fq, ascii_reads, first=r * n, mode="ab" if r else "wb")
     try:
         al = [pkg.GpuAligner(job, device), pkg.GpuAligner(job, device)]
         stream.fastq_to_sam(job, fq, sam, device, aligners=al)          # warm-up (page cache, pinned buffers)
-        best = None
+        best, stages = None, None
         for _ in range(2):
+            st = {}
             t0 = time.time()
-            nr, nb = stream.fastq_to_sam(job, fq, sam, device, aligners=al)
+            nr, nb = stream.fastq_to_sam(job, fq, sam, device, aligners=al, stats=st)
             dt = time.time() - t0
-            best = dt if best is None or dt < best else best
+            if best is None or dt < best:
+                best, stages = dt, st
         for g in al:
             g.close()
+        busy = {k: round(stages[k], 4) for k in ("parse", "align", "sam")}
         return {"value": nr / best, "unit": "reads/s", "reads": nr, "fastq_bytes": os.path.getsize(fq), "sam_bytes": nb, "seconds": best,
-                "where": tmp, "note": "FASTQ file -> parse -> bt2gpu_align_batch -> SAM formatting -> SAM file, pipelined over byte ranges of the file"}
+                "where": tmp, "host_cores": cpu_cores(), "ranges": stages["ranges"], "stage_busy_s": busy, "limiting_stage": max(busy, key=busy.get),
+                "note": "FASTQ file -> parse -> bt2gpu_align_batch -> SAM formatting -> SAM file, pipelined over byte ranges of the file; stage_busy_s = "
+                        "seconds each of the three overlapping stages was at work (parse and sam share the host cores)"}
     finally:
         for f in (fq, sam):
             if os.path.exists(f):

@@ -65,7 +65,7 @@ bt2host_batch* bt2host_batch_from_arrays(const bt2host_job* job, uint32_t n, con
 void bt2host_batch_destroy(bt2host_batch* b) { delete b; }
 const bt2gpu_reads* bt2host_batch_reads(const bt2host_batch* b) { return &b->b.view; }
 const char* bt2host_batch_name(const bt2host_batch* b, uint32_t i) {
-	return i < b->b.names.size() ? b->b.names[i].c_str() : nullptr;
+	return i < b->b.nnames() ? b->b.name_ptr(i) : nullptr;
 }
 
 static char* dup_out(const std::string& s, size_t* len) {

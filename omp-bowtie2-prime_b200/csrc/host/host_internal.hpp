@@ -64,6 +64,8 @@ struct Job {
 	std::vector<std::string> sinkparts;   // SAM text of the sink's blocks
 	char* file_buffer(size_t n);          // >= n bytes, not initialised, owned by the job
 	char* filemem = nullptr; size_t filecap = 0;
+	mutable std::vector<std::vector<size_t>> scan_nl;   // the reader's per-thread newline positions
+	mutable std::vector<size_t> scan_ls; mutable std::vector<uint32_t> scan_len;
 	mutable uint64_t range_next_id = 0;   // reads handed out by batch_from_fastq_range so far (ranges are taken in file order, from offset 0)
 	~Job();
 };
@@ -81,7 +83,16 @@ struct Batch {
 	ByteVec seq, qual;
 	std::vector<uint32_t> seed;
 	std::vector<int32_t> minsc, nceil, interval;
-	std::vector<std::string> names;
+	// read names, NUL-terminated, back to back: name i is name_blob[name_off[i] .. name_off[i+1] - 1)
+	ByteVec name_blob; std::vector<uint32_t> name_off;
+	size_t nnames() const { return name_off.empty() ? 0 : name_off.size() - 1; }
+	const char* name_ptr(size_t i) const { return (const char*)name_blob.data() + name_off[i]; }
+	size_t name_len(size_t i) const { return name_off[i + 1] - name_off[i] - 1; }
+	void add_name(const char* p, size_t n) {
+		if(name_off.empty()) name_off.push_back(0);
+		name_blob.insert(name_blob.end(), (const uint8_t*)p, (const uint8_t*)p + n); name_blob.push_back(0);
+		name_off.push_back((uint32_t)name_blob.size());
+	}
 	uint64_t first_id = 0;   // global index (Read::rdid) of the batch's first read: a read without a name is named by its rdid
 	bt2gpu_reads view;
 	void finalize();
@@ -90,7 +101,7 @@ struct Batch {
 bool load_index(Job& job, const std::string& base, std::string& err);
 bool parse_options(Options& o, const std::string& args, std::string& err);
 uint32_t gen_rand_seed(const uint8_t* seq, const uint8_t* qual, size_t len,
-                       const std::string& name, uint32_t seed);
+                       const char* name, size_t name_len, uint32_t seed);
 void fill_p0(const Job& job, Batch& b); // minsc / nceil / interval per read
 bool batch_from_fastq(const Job& job, Batch& b, const std::string& path, uint64_t skip, uint64_t maxn, std::string& err);
 bool batch_from_fastq_range(const Job& job, Batch& b, const std::string& path, uint64_t offset, uint64_t max_bytes, uint64_t* next_off, std::string& err);

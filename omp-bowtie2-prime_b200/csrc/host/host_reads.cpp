@@ -127,23 +127,22 @@ bool parse_options(Options& o, const std::string& args, std::string& err) {
 // ---------------------------------------------------------------- reads
 // genRandSeed (pat.cpp:45-83)
 uint32_t gen_rand_seed(const uint8_t* seq, const uint8_t* qual, size_t len,
-                       const std::string& name, uint32_t seed) {
+                       const char* name, size_t name_len, uint32_t seed) {
 	uint32_t rseed = (seed + 101) * 59 * 61 * 67 * 71 * 73 * 79 * 83;
-	for(size_t i = 0; i < len; i++) {
-		int p = (int)seq[i];
-		size_t off = ((i & 15) << 1);
-		rseed ^= ((uint32_t)p << off);
+	// base i lands at bit 2*(i mod 16), quality i at bit 8*(i mod 4): whole groups are folded as words
+	size_t i = 0;
+	for(; i + 16 <= len; i += 16) {
+		uint32_t w = 0;
+		for(int k = 0; k < 16; k++) w ^= (uint32_t)seq[i + k] << (2 * k);
+		rseed ^= w;
 	}
-	for(size_t i = 0; i < len; i++) {
-		int p = (int)qual[i];
-		size_t off = ((i & 3) << 3);
-		rseed ^= (p << off);
-	}
-	for(size_t i = 0; i < name.size(); i++) {
-		int p = (int)name[i];
+	for(; i < len; i++) rseed ^= (uint32_t)seq[i] << ((i & 15) << 1);
+	for(i = 0; i + 4 <= len; i += 4) { uint32_t w; memcpy(&w, qual + i, 4); rseed ^= w; }   // little-endian: byte k at bit 8k
+	for(; i < len; i++) rseed ^= (uint32_t)qual[i] << ((i & 3) << 3);
+	for(i = 0; i < name_len; i++) {
+		const int p = (int)name[i];
 		if(p == '/') break;
-		size_t off = ((i & 3) << 3);
-		rseed ^= (p << off);
+		rseed ^= (uint32_t)(p << ((i & 3) << 3));
 	}
 	return rseed;
 }
@@ -188,7 +187,7 @@ static void add_read(const Job& job, Batch& b, std::string name, const std::stri
 	size_t rem = s.size() - t5;
 	size_t t3 = std::min<size_t>((size_t)job.opt.trim3, rem);
 	size_t len = rem - t3;
-	if(name.empty()) name = std::to_string(b.first_id + b.names.size());   // the reference names it by its global read id
+	if(name.empty()) name = std::to_string(b.first_id + b.nnames());   // the reference names it by its global read id
 	const size_t base = b.seq.size();
 	for(size_t i = 0; i < len; i++) {
 		int c = s[t5 + i]; if(c == '.') c = 'N';
@@ -198,8 +197,8 @@ static void add_read(const Job& job, Batch& b, std::string name, const std::stri
 		b.qual.push_back((uint8_t)qc);
 	}
 	b.off.push_back((uint32_t)b.seq.size());
-	b.seed.push_back(gen_rand_seed(b.seq.data() + base, b.qual.data() + base, len, name, job.opt.seed));
-	b.names.push_back(std::move(name));
+	b.seed.push_back(gen_rand_seed(b.seq.data() + base, b.qual.data() + base, len, name.data(), name.size(), job.opt.seed));
+	b.add_name(name.data(), name.size());
 }
 
 static bool getline_trim(FILE* f, std::string& line) {
@@ -270,7 +269,7 @@ static int fastq_fast(const Job& job, Batch& b, const std::string& path, uint64_
 		const int fd = fileno(f);
 		int nr = 1;
 #ifdef _OPENMP
-		nr = std::max(1, std::min(omp_get_max_threads(), (int)((size_t)sz >> 24) + 1));
+		nr = std::max(1, std::min(omp_get_max_threads(), (int)((size_t)sz >> 22) + 1));
 #endif
 		bool ok = true;
 		#pragma omp parallel for num_threads(nr) schedule(static, 1) reduction(&&: ok)
@@ -286,27 +285,34 @@ static int fastq_fast(const Job& job, Batch& b, const std::string& path, uint64_
 	const double tA = now();
 	size_t N = buf.size();
 	if(next_off) *next_off = foff + N;
-	if(N == 0) { if(foff == 0) return 0; b.off.assign(1, 0); fill_p0(job, b); b.finalize(); return 1; }   // past the last record: an empty batch
-	if(memchr(buf.data(), '\r', N)) return 0;
-	// ---- line starts
+	if(N == 0) { if(foff == 0) return 0; b.off.assign(1, 0); b.name_off.assign(1, 0); fill_p0(job, b); b.finalize(); return 1; }   // past the last record: an empty batch
+	// ---- line starts: every thread lists the '\n' of its slice (and looks for a CR, which sends the file to the serial parser)
 	int nt = 1;
 #ifdef _OPENMP
 	nt = std::max(1, std::min(omp_get_max_threads(), (int)(N >> 20) + 1));
 #endif
-	std::vector<std::vector<size_t>> nl((size_t)nt);   // positions of '\n' per slice
-	#pragma omp parallel for num_threads(nt) schedule(static, 1)
+	std::vector<std::vector<size_t>>& nl = job.scan_nl;   // kept by the job: no allocation from the second range on
+	if(nl.size() < (size_t)nt) nl.resize((size_t)nt);
+	bool has_cr = false;
+	#pragma omp parallel for num_threads(nt) schedule(static, 1) reduction(||: has_cr)
 	for(int t = 0; t < nt; t++) {
 		const size_t lo = N * (size_t)t / (size_t)nt, hi = N * (size_t)(t + 1) / (size_t)nt;
 		std::vector<size_t>& v = nl[(size_t)t];
-		v.reserve((hi - lo) / 64 + 16);
+		v.clear();
 		const char* p = buf.data() + lo; const char* e = buf.data() + hi;
-		while(p < e) { const char* q = (const char*)memchr(p, '\n', (size_t)(e - p)); if(!q) break; v.push_back((size_t)(q - buf.data())); p = q + 1; }
+		if(memchr(p, '\r', (size_t)(e - p))) { has_cr = true; continue; }
+		while(p < e) { const char* q = (const char*)memchr(p, '\n', (size_t)(e - p)); if(!q) break; v.push_back((size_t)(q - buf.data()) + 1); p = q + 1; }
 	}
-	std::vector<size_t> ls;                             // ls[i] = start of line i; ls[nlines] = one past the last line's '\n'
+	if(has_cr) return 0;
+	std::vector<size_t>& ls = job.scan_ls;               // ls[i] = start of line i; ls[nlines] = one past the last line's '\n'
 	{
-		size_t tot = 0; for(auto& v : nl) tot += v.size();
-		ls.reserve(tot + 2); ls.push_back(0);
-		for(auto& v : nl) for(size_t x : v) ls.push_back(x + 1);
+		std::vector<size_t> at((size_t)nt + 1, 1);
+		for(int t = 0; t < nt; t++) at[(size_t)t + 1] = at[(size_t)t] + nl[(size_t)t].size();
+		ls.resize(at[(size_t)nt] + 1);
+		ls[0] = 0;
+		#pragma omp parallel for num_threads(nt) schedule(static, 1)
+		for(int t = 0; t < nt; t++) if(!nl[(size_t)t].empty()) memcpy(&ls[at[(size_t)t]], nl[(size_t)t].data(), nl[(size_t)t].size() * sizeof(size_t));
+		ls.resize(at[(size_t)nt]);
 		if(!to_eof) {                                    // cut the range back to its last complete record
 			const size_t full = ((ls.size() - 1) / 4) * 4;
 			if(full == 0) { err = "FASTQ record longer than the read range in " + path; return -1; }
@@ -321,51 +327,72 @@ static int fastq_fast(const Job& job, Batch& b, const std::string& path, uint64_
 	const size_t r0 = std::min<size_t>((size_t)skip, nrec), r1 = maxn ? std::min<size_t>(nrec, r0 + (size_t)maxn) : nrec;
 	const size_t n = r1 - r0;
 	auto line_len = [&](size_t i) { return ls[i + 1] - 1 - ls[i]; };
-	// ---- pass 1: every record starts with '@' on a non-empty line; trimmed read lengths
-	std::vector<uint32_t> len(n);
+	// ---- pass 1: every record starts with '@' on a non-empty line; trimmed read lengths; name lengths
+	std::vector<uint32_t>& len = job.scan_len; len.resize(2 * n + 2);
+	uint32_t* nmlen = len.data() + n;                    // bytes of name i incl. its NUL
 	bool regular = true;
+	const size_t t5o = (size_t)job.opt.trim5, t3o = (size_t)job.opt.trim3;
 	#pragma omp parallel for num_threads(nt) schedule(static) reduction(&&: regular)
 	for(size_t r = 0; r < nrec; r++) {
 		const size_t h = 4 * r;
 		if(line_len(h) == 0 || buf[ls[h]] != '@') regular = false;
 		if(r < r0 || r >= r1) continue;
-		const char* sq = buf.data() + ls[h + 1]; const size_t sl = line_len(h + 1);
-		size_t alpha = 0;
-		for(size_t i = 0; i < sl; i++) alpha += kFq.kept[(unsigned char)sq[i]];
-		const size_t t5 = std::min<size_t>((size_t)job.opt.trim5, alpha), rem = alpha - t5, t3 = std::min<size_t>((size_t)job.opt.trim3, rem);
+		const unsigned char* sq = (const unsigned char*)buf.data() + ls[h + 1]; const size_t sl = line_len(h + 1);
+		uint32_t alpha = 0;                              // characters kept by the reference: letters and '.' (pat.cpp:1151-1163)
+		for(size_t i = 0; i < sl; i++) alpha += (uint32_t)(((uint8_t)((sq[i] | 0x20) - 'a') < 26) | (sq[i] == '.'));
+		const size_t t5 = std::min<size_t>(t5o, alpha), rem = alpha - t5, t3 = std::min<size_t>(t3o, rem);
 		len[r - r0] = (uint32_t)(rem - t3);
+		size_t nmb = line_len(h) - 1;
+		if(nmb == 0) { char t[24]; nmb = (size_t)snprintf(t, sizeof(t), "%llu", (unsigned long long)(b.first_id + (r - r0))); }
+		nmlen[r - r0] = ((uint32_t)nmb + 1) | (alpha == sl ? 0x80000000u : 0u);   // top bit: nothing on the sequence line is dropped
 	}
 	const double tC = now();
 	if(!regular) return 0;
-	b.off.assign(n + 1, 0);
-	for(size_t i = 0; i < n; i++) b.off[i + 1] = b.off[i] + len[i];
-	b.seq.resize(b.off[n]); b.qual.resize(b.off[n]); b.seed.resize(n); b.names.resize(n);
-	// ---- pass 2
+	b.off.resize(n + 1); b.name_off.resize(n + 1);
+	b.off[0] = 0; b.name_off[0] = 0;
+	{ uint64_t so = 0, no = 0;
+	  for(size_t i = 0; i < n; i++) { so += len[i]; no += nmlen[i] & 0x7fffffffu; b.off[i + 1] = (uint32_t)so; b.name_off[i + 1] = (uint32_t)no; }
+	  if(so > 0xffffffffull || no > 0xffffffffull) { err = "more than 4 G bases or name bytes in one batch: read " + path + " in ranges"; return -1; } }
+	b.seq.resize(b.off[n]); b.qual.resize(b.off[n]); b.seed.resize(n); b.name_blob.resize(b.name_off[n]);
+	// ---- pass 2: bases -> codes, qualities, name, seed
+	const bool p64 = job.opt.phred64;
 	#pragma omp parallel for num_threads(nt) schedule(static)
 	for(size_t i = 0; i < n; i++) {
 		const size_t h = 4 * (r0 + i);
-		const char* sq = buf.data() + ls[h + 1]; const size_t sl = line_len(h + 1);
-		const char* ql = buf.data() + ls[h + 3]; const size_t qn = line_len(h + 3);
-		const size_t t5 = (size_t)job.opt.trim5;
+		const unsigned char* sq = (const unsigned char*)buf.data() + ls[h + 1]; const size_t sl = line_len(h + 1);
+		const unsigned char* ql = (const unsigned char*)buf.data() + ls[h + 3]; const size_t qn = line_len(h + 3);
 		uint8_t* oseq = b.seq.data() + b.off[i]; uint8_t* oq = b.qual.data() + b.off[i];
 		const size_t L = len[i];
-		size_t a = 0, w = 0;                              // a: index among the alphabetic characters of the line
-		for(size_t k = 0; k < sl && w < L; k++) {
-			const unsigned char c = (unsigned char)sq[k];
-			if(!kFq.kept[c]) continue;
-			if(a >= t5) {
-				oseq[w] = kFq.code[c];
-				int qc = (a < qn) ? (unsigned char)ql[a] : 'I';
-				if(job.opt.phred64) qc -= 31;
-				oq[w] = (uint8_t)qc;
-				w++;
+		const size_t t5 = std::min<size_t>(t5o, sl);
+		if((nmlen[i] & 0x80000000u) && qn >= t5 + L) {
+			// the usual record: nothing but letters / '.' on the sequence line and a quality for every base
+			const unsigned char* s = sq + t5; const unsigned char* q = ql + t5;
+			for(size_t k = 0; k < L; k++) {
+				const uint8_t u = (uint8_t)(s[k] & 0xDF);    // upper case; '.' and every other letter fall through to N
+				oseq[k] = (uint8_t)(4 - 4 * (u == 'A') - 3 * (u == 'C') - 2 * (u == 'G') - (u == 'T'));
 			}
-			a++;
+			if(p64) { for(size_t k = 0; k < L; k++) oq[k] = (uint8_t)(q[k] - 31); }
+			else memcpy(oq, q, L);
+		} else {
+			size_t a = 0, w = 0;                          // a: index among the kept characters of the line
+			for(size_t k = 0; k < sl && w < L; k++) {
+				const unsigned char c = sq[k];
+				if(!kFq.kept[c]) continue;
+				if(a >= t5o) {
+					oseq[w] = kFq.code[c];
+					int qc = (a < qn) ? ql[a] : 'I';
+					if(p64) qc -= 31;
+					oq[w] = (uint8_t)qc;
+					w++;
+				}
+				a++;
+			}
 		}
-		std::string name(buf.data() + ls[h] + 1, line_len(h) - 1);
-		if(name.empty()) name = std::to_string(b.first_id + i);   // the reference names it by its global read id
-		b.seed[i] = gen_rand_seed(oseq, oq, L, name, job.opt.seed);
-		b.names[i] = std::move(name);
+		char* nm = (char*)b.name_blob.data() + b.name_off[i]; const size_t nmb = (nmlen[i] & 0x7fffffffu) - 1;
+		if(line_len(h) > 1) memcpy(nm, buf.data() + ls[h] + 1, nmb);
+		else snprintf(nm, nmb + 1, "%llu", (unsigned long long)(b.first_id + i));   // the reference names it by its global read id
+		nm[nmb] = 0;
+		b.seed[i] = gen_rand_seed(oseq, oq, L, nm, nmb, job.opt.seed);
 	}
 	const double tD = now();
 	fill_p0(job, b);
@@ -386,7 +413,7 @@ bool batch_from_fastq_range(const Job& job, Batch& b, const std::string& path, u
 	if(offset == 0) job.range_next_id = 0;         // ranges are taken in file order (stream.py); unnamed reads get their global index
 	b.first_id = job.range_next_id;
 	const int r = fastq_fast(job, b, path, offset, max_bytes, 0, 0, next_off, err);
-	if(r > 0) job.range_next_id += b.names.size();
+	if(r > 0) job.range_next_id += b.nnames();
 	if(r == 0) err = "FASTQ layout needs the serial parser (CR line ends, blank lines or a truncated record): read the whole file with bt2host_batch_from_fastq";
 	return r > 0;
 }

@@ -199,7 +199,7 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 	const uint8_t* seq = b.seq.data() + b.off[ri];
 	const uint8_t* qual = b.qual.data() + b.off[ri];
 	const size_t rdlen = b.off[ri + 1] - b.off[ri];
-	const std::string& name = b.names[ri];
+	const char* name = b.name_ptr(ri); const size_t name_n = b.name_len(ri);
 	const uint64_t n = rr.n_alns;
 	const bool mhitsSet = opt.p.mhits != 0;
 	// ReportingState::getReport
@@ -212,7 +212,7 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 	met[0]++;
 	if(nrep == 0) met[1]++; else if(maxed || n > 1) met[3]++; else met[2]++;
 	auto qname = [&]() {
-		for(size_t i = 0; i < name.size() && i < 255; i++) { if(isspace((unsigned char)name[i])) break; o.push_back(name[i]); }
+		for(size_t i = 0; i < name_n && i < 255; i++) { if(isspace((unsigned char)name[i])) break; o.push_back(name[i]); }
 	};
 	auto seqqual = [&](bool fw) {
 		if(rdlen == 0) { o += "*\t*"; return; }

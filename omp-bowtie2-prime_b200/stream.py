@@ -7,12 +7,14 @@ Two contexts on the same device take the batches alternately, because a context'
 call and the sink is still reading batch i while batch i+1 is aligned."""
 import queue
 import threading
+import time
 
 from .binding import GpuAligner
 
 
-def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=96 << 20, mode=1, aligners=None, start=0, end=None, header=True):
+def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, aligners=None, start=0, end=None, header=True, stats=None):
     """Returns (reads, bytes written).  `aligners`: two GpuAligner of `job` to reuse (else created and closed here).
+    stats: a dict that receives the seconds each stage was busy ("parse", "align", "sam": they overlap) and the number of ranges.
     start / end: byte range of the file to take (both at record starts): a shard of a multi-GPU job (reads shard by batch,
     every device holds a replica of the index, the per-shard SAM files are concatenated in shard order); header=False for shards > 0."""
     own = aligners is None
@@ -21,12 +23,15 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=96 << 20, mode=1, a
     parsed, done = queue.Queue(maxsize=2), queue.Queue(maxsize=2)
     free = [threading.Semaphore(1), threading.Semaphore(1)]   # context k may align again once the sink has written its last results
     errors = []
+    busy = {"parse": 0.0, "align": 0.0, "sam": 0.0, "ranges": 0}
 
     def reader():
         try:
             off = start
             while not errors and (end is None or off < end):
+                t0 = time.perf_counter()
                 b, nxt = job.fastq_range(fastq, off, chunk_bytes if end is None else min(chunk_bytes, end - off))
+                busy["parse"] += time.perf_counter() - t0
                 if b.n == 0:
                     b.close()
                     break
@@ -50,7 +55,9 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=96 << 20, mode=1, a
                     b, res, k = item
                     try:
                         if not errors:
+                            t0 = time.perf_counter()
                             total[1] += job.sam_write(b, res, f, mode)
+                            busy["sam"] += time.perf_counter() - t0
                             total[0] += b.n
                     finally:
                         b.close()
@@ -76,7 +83,10 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=96 << 20, mode=1, a
                 continue
             k = i & 1
             free[k].acquire()                  # (the other context's results may still be being written)
+            t0 = time.perf_counter()
             res = aligners[k].align(b)
+            busy["align"] += time.perf_counter() - t0
+            busy["ranges"] += 1
             done.put((b, res, k))
             i += 1
     except Exception as e:
@@ -90,4 +100,6 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=96 << 20, mode=1, a
             g.close()
     if errors:
         raise errors[0]
+    if stats is not None:
+        stats.update(busy)
     return total[0], total[1]

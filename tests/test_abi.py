@@ -92,6 +92,56 @@ def test_fastq_fast_path_equals_serial_parser(tmp_path):
         assert c.reads.contents.n == d.reads.contents.n == 250 and c.nbases() == d.nbases()
 
 
+def test_fastq_fast_path_odd_records(tmp_path):
+    """records off the usual shape: lower case, '.', characters the reference drops from the sequence line (pat.cpp:1151-1163), a read without
+    a name, a name with '/', a quality line shorter than the read, --phred64; fast reader == serial reader, names and seeds included"""
+    import random
+    import numpy as np
+    import common
+    from common import pkg
+    if not common.have_builder():
+        import pytest
+        pytest.skip("no builder")
+    rnd = random.Random(5)
+    recs = []
+    for i in range(600):
+        L = rnd.randint(20, 170)
+        s = "".join(rnd.choice("ACGT") for _ in range(L))
+        q = "".join(chr(rnd.randint(64, 104)) for _ in range(L))
+        k = i % 8
+        if k == 1:
+            s = s.lower()
+        elif k == 2:
+            s = s[:5] + "." + s[6:11] + "n" + s[12:]
+        elif k == 3:
+            s = s[:7] + "-*1" + s[7:]          # dropped by the reader: the read keeps L bases, qualities index the kept ones
+            q = q + "hhh"
+        elif k == 4:
+            q = q[:L - 4]
+        name = "" if k == 5 else ("frag%d/1 extra" % i if k == 6 else "r%d" % i)
+        recs.append("@%s\n%s\n+\n%s\n" % (name, s, q))
+    lf = tmp_path / "odd.fq"; lf.write_text("".join(recs))
+    crlf = tmp_path / "odd_crlf.fq"; crlf.write_bytes(lf.read_bytes().replace(b"\n", b"\r\n"))
+    for opts in ("--phred64", "--phred64 --trim5 4 --trim3 9", "--phred64 --seed 7"):
+        job = pkg.Job(common.index_base("lambda"), opts)
+        a, b = job.fastq(str(lf)), job.fastq(str(crlf))
+        ra, rb = a.reads.contents, b.reads.contents
+        assert ra.n == rb.n == 600
+        for f, dt, cnt in (("seq_off", np.uint32, ra.n + 1), ("rng_seed", np.uint32, ra.n), ("minsc", np.int32, ra.n), ("nceil", np.int32, ra.n)):
+            xa = np.ctypeslib.as_array(ctypes.cast(getattr(ra, f), ctypes.POINTER(np.ctypeslib.as_ctypes_type(dt))), shape=(cnt,))
+            xb = np.ctypeslib.as_array(ctypes.cast(getattr(rb, f), ctypes.POINTER(np.ctypeslib.as_ctypes_type(dt))), shape=(cnt,))
+            assert (xa == xb).all(), (opts, f, int((xa != xb).argmax()))
+        nb = a.nbases()
+        assert nb == b.nbases()
+        for f in ("seq", "qual"):
+            xa = np.ctypeslib.as_array(ctypes.cast(getattr(ra, f), ctypes.POINTER(ctypes.c_uint8)), shape=(nb,))
+            xb = np.ctypeslib.as_array(ctypes.cast(getattr(rb, f), ctypes.POINTER(ctypes.c_uint8)), shape=(nb,))
+            assert (xa == xb).all(), (opts, f)
+        assert [a.name(i) for i in range(600)] == [b.name(i) for i in range(600)]
+        assert a.name(5) == "5" and a.name(6).startswith("frag6/1")
+        a.close(); b.close(); job.close()
+
+
 def test_fastq_ranges_equal_whole_file():
     """bt2host_batch_from_fastq_range: the batches of consecutive byte ranges, concatenated, are the whole-file batch"""
     import numpy as np
