@@ -272,8 +272,19 @@ bt2gpu_ctx *bt2gpu_create(const bt2gpu_index *ix, const bt2gpu_ref *rf,
                           const bt2gpu_params *p, int device,
                           char *err, size_t errlen);
 
-/* Align one batch (host buffers in, pinned host results out; H2D and D2H inside). */
+/* Align one batch (host buffers in, pinned host results out; H2D and D2H inside).
+ * A context holds two sets of result arrays and successive calls take them in turn: what a call returned stays valid until the
+ * next-but-one call (bt2gpu_align_batch or bt2gpu_submit) on the context starts -- a sink can still be reading batch i while
+ * batch i+1 is aligned. */
 int bt2gpu_align_batch(bt2gpu_ctx *ctx, const bt2gpu_reads *in, bt2gpu_results *out);
+
+/* The same call in two halves, for a caller whose batch loop has one thread (the reference's: bt2_search.cpp:2414-2862, where
+ * P7 finishReadOne of batch i would otherwise wait for the device): bt2gpu_submit returns at once and the batch is aligned on a
+ * worker thread of the context; bt2gpu_wait blocks until it is done and hands out the results (same lifetime as above).  `in`
+ * and its arrays must stay as they are until bt2gpu_wait returns.  One batch in flight per context; every other call on the
+ * context except bt2gpu_last_error fails with -2 until bt2gpu_wait has been called. */
+int bt2gpu_submit(bt2gpu_ctx *ctx, const bt2gpu_reads *in);
+int bt2gpu_wait(bt2gpu_ctx *ctx, bt2gpu_results *out);
 
 /* Split form used by bench.py to time the kernels with inputs already resident:
  * upload() copies a batch to HBM, run_resident() runs all stages on it (no

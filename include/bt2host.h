@@ -93,6 +93,9 @@ void bt2host_free(void *p);
 /* Summary counters of the last bt2host_sam_records call sequence on this job
  * (ReportingMetrics, aln_sink.h:44-233): [0]=reads [1]=unaligned [2]=aligned once [3]=aligned >1 */
 void bt2host_job_metrics(const bt2host_job *job, uint64_t out[4]);
+/* OpenMP threads the FASTQ reader and the SAM sink of this job take (0: all there are, the default).  A pipeline that runs the
+ * two at the same time on neighbouring batches (stream.py) splits the cores between them instead of letting both ask for all. */
+void bt2host_job_set_threads(bt2host_job *job, int reader_threads, int sink_threads);
 
 #ifdef __cplusplus
 }

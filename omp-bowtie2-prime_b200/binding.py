@@ -116,6 +116,7 @@ def load_host():
         h.bt2host_sam_write.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(bt2gpu_results), C.c_int, C.c_int, C.POINTER(C.c_size_t)]
         h.bt2host_free.argtypes = [C.c_void_p]
         h.bt2host_job_metrics.argtypes = [C.c_void_p, C.POINTER(C.c_uint64 * 4)]
+        h.bt2host_job_set_threads.argtypes = [C.c_void_p, C.c_int, C.c_int]
         _host = h
     return _host
 
@@ -132,6 +133,8 @@ def load_gpu():
         g.bt2gpu_create.argtypes = [C.POINTER(bt2gpu_index), C.POINTER(bt2gpu_ref), C.POINTER(bt2gpu_params), C.c_int, C.c_char_p, C.c_size_t]
         for f in ("bt2gpu_align_batch",):
             getattr(g, f).argtypes = [C.c_void_p, C.POINTER(bt2gpu_reads), C.POINTER(bt2gpu_results)]
+        g.bt2gpu_submit.argtypes = [C.c_void_p, C.POINTER(bt2gpu_reads)]
+        g.bt2gpu_wait.argtypes = [C.c_void_p, C.POINTER(bt2gpu_results)]
         g.bt2gpu_upload.argtypes = [C.c_void_p, C.POINTER(bt2gpu_reads)]
         g.bt2gpu_run_resident.argtypes = [C.c_void_p]
         g.bt2gpu_fetch.argtypes = [C.c_void_p, C.POINTER(bt2gpu_results)]
@@ -220,6 +223,10 @@ class Job:
             raise OSError("bt2host_sam_write failed")
         return n.value
 
+    def set_threads(self, reader=0, sink=0):
+        """OpenMP threads of the FASTQ reader and of the SAM sink (0: all)."""
+        self._h.bt2host_job_set_threads(self.ptr, reader, sink)
+
     def metrics(self):
         a = (C.c_uint64 * 4)()
         self._h.bt2host_job_metrics(self.ptr, C.byref(a))
@@ -289,6 +296,16 @@ class GpuAligner:
     def align(self, batch):
         r = bt2gpu_results()
         self._ck(self._g.bt2gpu_align_batch(self.ptr, batch.reads, C.byref(r)), "bt2gpu_align_batch")
+        return Results(r)
+
+    def submit(self, batch):
+        """bt2gpu_submit: returns at once, the batch is aligned on the context's worker thread; keep `batch` alive until wait()."""
+        self._ck(self._g.bt2gpu_submit(self.ptr, batch.reads), "bt2gpu_submit")
+
+    def wait(self):
+        """bt2gpu_wait: the results of the submitted batch (valid until the next-but-one align / submit on this context)."""
+        r = bt2gpu_results()
+        self._ck(self._g.bt2gpu_wait(self.ptr, C.byref(r)), "bt2gpu_wait")
         return Results(r)
 
     def align_raw(self, reads_struct):

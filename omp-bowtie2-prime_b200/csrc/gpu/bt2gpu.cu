@@ -15,6 +15,7 @@
 #include <string>
 #include <vector>
 #include <future>
+#include <thread>
 #include <mutex>
 #include <algorithm>
 #include "bt2gpu.h"
@@ -31,7 +32,7 @@ using namespace bt2;
 	throw std::string(b_); } } while(0)
 
 enum { PH_SEED = 0, PH_GLUE, PH_RESOLVE, PH_FILL, PH_BT, PH_H2D, PH_D2H, PH_RUN, PH_N };
-enum { C_CAND0 = 0, C_CAND1, C_ACTIVE, C_EXT0, C_EXT1, C_ROUNDEND, C_SAMP, C_SEEDTASK, C_BTTASK, C_SEEDNT, C_XTASKN, C_XTASK, C_N = 16 };
+enum { C_CAND0 = 0, C_CAND1, C_ACTIVE, C_EXT0, C_EXT1, C_ROUNDEND, C_SAMP, C_SEEDTASK, C_BTTASK, C_SEEDNT, C_XTASKN, C_XTASK, C_BTTASK1, C_N = 16 };
 
 struct DBuf { // growable device buffer
 	void* p = nullptr; size_t cap = 0;
@@ -61,6 +62,9 @@ struct HBuf { // growable pinned host buffer
 struct bt2gpu_ctx {
 	int device = 0;
 	cudaStream_t stream = nullptr;
+	// the second slot set's stream: while one chunk of DP problems is in k_bt the next chunk's k_step + k_fill run beside it
+	cudaStream_t stream2 = nullptr; cudaEvent_t evFork = nullptr, evJoin = nullptr, evFill[2] = { nullptr, nullptr };
+	bool overlap = false; int btBlocksOverlap = 3;   // off: measured 37.6 vs 38.3 ms per 1M reads (both kernels scale with their resident warps); BT2GPU_OVERLAP=1 turns it on
 	std::string err;
 	bt2gpu_params hp;
 	DevParams P; DevParams* dP = nullptr;
@@ -87,7 +91,10 @@ struct bt2gpu_ctx {
 	DBuf s_ovr, s_ovp, s_ovv, s_sr, s_sv, s_cv, s_rn, s_rcur, s_rth, s_rfl, s_rco, s_rcn, s_rns, s_mass, s_elim;
 	DBuf chunks, sats, alnp, editp, pooltops, poolerr;
 	DBuf nal, ned, albase, edbase, cubtmp;
-	HBuf h_rr, h_alns, h_edits;
+	// two sets of pinned result arrays, taken in turn by successive calls: the results of a call stay valid while the next one runs
+	struct HostSet { HBuf rr, alns, edits; } hset[2]; int hcur = 0;
+	// bt2gpu_submit / bt2gpu_wait: the batch in flight on the context's worker thread
+	std::thread worker; bool inflight = false; int flight_rc = 0; bt2gpu_results flight_out;
 	volatile HostBox* hbox = nullptr; HostBox* dbox = nullptr;   // mapped pinned mailbox (k_scalar.cuh)
 	// state of the current resident batch
 	uint32_t n = 0, W = 0, maxOffs = 0; uint64_t nbases = 0;
@@ -129,11 +136,12 @@ cudaEvent_t get_event(bt2gpu_ctx* c) {
 }
 struct Phase {
 	bt2gpu_ctx* c; size_t idx;
-	Phase(bt2gpu_ctx* c_, int ph) : c(c_) {
+	cudaStream_t st;
+	Phase(bt2gpu_ctx* c_, int ph, cudaStream_t st_ = nullptr) : c(c_), st(st_ ? st_ : c_->stream) {
 		bt2gpu_ctx::Span s; s.ph = ph; s.a = get_event(c); s.b = get_event(c);
-		CK(cudaEventRecord(s.a, c->stream)); c->spans.push_back(s); idx = c->spans.size() - 1;
+		CK(cudaEventRecord(s.a, st)); c->spans.push_back(s); idx = c->spans.size() - 1;
 	}
-	~Phase() { cudaEventRecord(c->spans[idx].b, c->stream); }
+	~Phase() { cudaEventRecord(c->spans[idx].b, st); }
 };
 void flush_spans(bt2gpu_ctx* c) {
 	double* acc[PH_N] = { &c->ctr.ms_seed, &c->ctr.ms_glue, &c->ctr.ms_resolve, &c->ctr.ms_fill, &c->ctr.ms_bt, &c->ctr.ms_h2d, &c->ctr.ms_d2h, &c->ctr.ms_run };
@@ -149,8 +157,8 @@ const uint32_t* read_counters(bt2gpu_ctx* c) {
 	CK(cudaStreamSynchronize(c->stream));
 	return const_cast<const uint32_t*>(c->hbox->counters);
 }
-void zero_counters(bt2gpu_ctx* c, uint32_t mask) { k_zero<<<1, 32, 0, c->stream>>>(c->counters.as<uint32_t>(), mask); }
-void zero_counter(bt2gpu_ctx* c, int which) { zero_counters(c, 1u << which); }
+void zero_counters(bt2gpu_ctx* c, uint32_t mask, cudaStream_t st = nullptr) { k_zero<<<1, 32, 0, st ? st : c->stream>>>(c->counters.as<uint32_t>(), mask); }
+void zero_counter(bt2gpu_ctx* c, int which, cudaStream_t st = nullptr) { zero_counters(c, 1u << which, st); }
 
 void setup_params(bt2gpu_ctx* c, const bt2gpu_params* p) {
 	DevParams& P = c->P; memset(&P, 0, sizeof(P));
@@ -310,7 +318,7 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 	bcx.scratch = c->scratch.as<uint32_t>(); bcx.seq = ba.seq; bcx.qual = ba.qual; bcx.set_pens();
 	Problem* probs = c->probs.as<Problem>();
 	const Pools pools = c->pools;
-	int seedBlocks = 0, btMaxBlocks = 0; { int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device); seedBlocks = nsm * 8; btMaxBlocks = nsm * BT2_BT_BLOCKS_PER_SM; }
+	int seedBlocks = 0, btMaxBlocks = 0, btOvBlocks = 0; { int nsm = 148; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, c->device); seedBlocks = nsm * 8; btMaxBlocks = nsm * BT2_BT_BLOCKS_PER_SM; btOvBlocks = nsm * c->btBlocksOverlap; }
 
 	k_begin<<<nblk(n, 256), 256, 0, st>>>(ba, states, L[0], cnt + C_CAND0); LAUNCH(c);
 	k_pack_reads<<<nblk(n, 128), 128, 0, st>>>(ba, states, c->pk.as<uint32_t>(), c->nm.as<uint32_t>()); LAUNCH(c);
@@ -363,19 +371,37 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 		while(ncur > 0) {
 			const int nxt = cur ^ 1;
 			zero_counter(c, nxt ? C_EXT1 : C_EXT0);
-			for(uint32_t b = 0; b < ncur; b += c->chunkSlots) {
-				const uint32_t k = std::min(c->chunkSlots, ncur - b);
-				{ Phase ph(c, PH_RESOLVE);
-				  k_step<<<nblk(k, 128), 128, 0, st>>>(c->dP, c->ix, c->rf, pools, states, L[3 + cur], b, k, probs, L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_step++; }
-				{ Phase ph(c, PH_FILL);
-				  FillArgs fa; fa.probs = probs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.cells = c->cells.as<uint8_t>(); fa.cell_stride = c->cellStride;
-				  fa.pcache = c->pcache.as<uint32_t>(); fa.hef_dbg = nullptr; fa.stats = stats + 8; fa.error = c->poolerr.as<uint32_t>(); fa.exact = c->hp.exactBestLtMinsc;
-				  launch_fill(c->fillK, false, c->dP, fa, st); LAUNCH(c); c->ctr.n_fill++; }
-				{ Phase ph(c, PH_BT);
-				  zero_counter(c, C_BTTASK);
-				  const uint32_t btBlocks = std::min<uint32_t>(nblk(k, BT2_BT_THREADS), (uint32_t)btMaxBlocks);
-				  k_bt<<<btBlocks, BT2_BT_THREADS, 0, st>>>(bcx, k, cnt + C_BTTASK, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_bt++; }
+			// A list longer than half the problem slots is cut into chunks that alternate between two slot sets on two streams,
+			// staggered: chunk i+1's fill starts when chunk i's fill is over, so the ALU-bound fill shares the SMs with the
+			// latency-bound backtrace of the chunk before (k_bt then takes fewer blocks per SM, leaving registers for the fill).
+			const uint32_t half = (c->chunkSlots / 2) & ~3u;
+			const bool ov = c->overlap && half >= 4 && ncur > half;
+			const uint32_t per = ov ? half : c->chunkSlots;
+			if(ov) { CK(cudaEventRecord(c->evFork, st)); CK(cudaStreamWaitEvent(c->stream2, c->evFork, 0)); }
+			uint32_t ci = 0;
+			for(uint32_t b = 0; b < ncur; b += per, ci++) {
+				const uint32_t k = std::min(per, ncur - b);
+				const uint32_t set = ov ? (ci & 1u) : 0u;
+				cudaStream_t cs = set ? c->stream2 : st;
+				Problem* sprobs = probs + (size_t)set * half;
+				uint8_t* scells = c->cells.as<uint8_t>() + (size_t)set * half * c->cellStride;
+				uint32_t* spc = c->pcache.as<uint32_t>() + (size_t)set * half * BT2_PC_WORDS;
+				{ Phase ph(c, PH_RESOLVE, cs);
+				  k_step<<<nblk(k, 128), 128, 0, cs>>>(c->dP, c->ix, c->rf, pools, states, L[3 + cur], b, k, sprobs, L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_step++; }
+				if(ov && ci > 0) CK(cudaStreamWaitEvent(cs, c->evFill[set ^ 1u], 0));
+				{ Phase ph(c, PH_FILL, cs);
+				  FillArgs fa; fa.probs = sprobs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.cells = scells; fa.cell_stride = c->cellStride;
+				  fa.pcache = spc; fa.hef_dbg = nullptr; fa.stats = stats + 8; fa.error = c->poolerr.as<uint32_t>(); fa.exact = c->hp.exactBestLtMinsc;
+				  launch_fill(c->fillK, false, c->dP, fa, cs); LAUNCH(c); c->ctr.n_fill++; }
+				if(ov) CK(cudaEventRecord(c->evFill[set], cs));
+				{ Phase ph(c, PH_BT, cs);
+				  const int tc = set ? C_BTTASK1 : C_BTTASK;
+				  zero_counter(c, tc, cs);
+				  BtCtx sb = bcx; sb.probs = sprobs; sb.cells = scells; sb.pcache = spc;
+				  const uint32_t btBlocks = std::min<uint32_t>(nblk(k, BT2_BT_THREADS), (uint32_t)(ov ? btOvBlocks : btMaxBlocks));
+				  k_bt<<<btBlocks, BT2_BT_THREADS, 0, cs>>>(sb, k, cnt + tc, L[3 + nxt], cnt + (nxt ? C_EXT1 : C_EXT0), L[5], cnt + C_ROUNDEND); LAUNCH(c); c->ctr.n_bt++; }
 			}
+			if(ov) { CK(cudaEventRecord(c->evJoin, c->stream2)); CK(cudaStreamWaitEvent(st, c->evJoin, 0)); }
 			ncur = read_counters(c)[nxt ? C_EXT1 : C_EXT0];
 			cur = nxt;
 		}
@@ -453,29 +479,29 @@ void start_fetch(bt2gpu_ctx* c, size_t rb, size_t ab, size_t eb, cudaStream_t st
 	bt2gpu_ctx::CopySpan& sp = c->d2hspan[c->cur];
 	settle(sp, c->ctr.ms_d2h);
 	CK(cudaEventRecord(sp.a, st));
-	if(n) CK(cudaMemcpyAsync(c->h_rr.as<bt2gpu_read_result>() + rb, O.o_rr.p, (size_t)n * sizeof(bt2gpu_read_result), cudaMemcpyDeviceToHost, st));
-	if(c->out_alns) CK(cudaMemcpyAsync(c->h_alns.as<bt2gpu_aln>() + ab, O.o_alns.p, c->out_alns * sizeof(bt2gpu_aln), cudaMemcpyDeviceToHost, st));
-	if(c->out_edits) CK(cudaMemcpyAsync(c->h_edits.as<bt2gpu_edit>() + eb, O.o_edits.p, c->out_edits * sizeof(bt2gpu_edit), cudaMemcpyDeviceToHost, st));
+	if(n) CK(cudaMemcpyAsync(c->hset[c->hcur].rr.as<bt2gpu_read_result>() + rb, O.o_rr.p, (size_t)n * sizeof(bt2gpu_read_result), cudaMemcpyDeviceToHost, st));
+	if(c->out_alns) CK(cudaMemcpyAsync(c->hset[c->hcur].alns.as<bt2gpu_aln>() + ab, O.o_alns.p, c->out_alns * sizeof(bt2gpu_aln), cudaMemcpyDeviceToHost, st));
+	if(c->out_edits) CK(cudaMemcpyAsync(c->hset[c->hcur].edits.as<bt2gpu_edit>() + eb, O.o_edits.p, c->out_edits * sizeof(bt2gpu_edit), cudaMemcpyDeviceToHost, st));
 	CK(cudaEventRecord(sp.b, st)); sp.pending = true;
 }
 
 void do_fetch(bt2gpu_ctx* c, bt2gpu_results* out) {
 	const uint32_t n = c->n;
-	c->h_rr.ensure(((size_t)n + 1) * sizeof(bt2gpu_read_result));
-	c->h_alns.ensure((c->out_alns + 1) * sizeof(bt2gpu_aln)); c->h_edits.ensure((c->out_edits + 1) * sizeof(bt2gpu_edit));
+	c->hset[c->hcur].rr.ensure(((size_t)n + 1) * sizeof(bt2gpu_read_result));
+	c->hset[c->hcur].alns.ensure((c->out_alns + 1) * sizeof(bt2gpu_aln)); c->hset[c->hcur].edits.ensure((c->out_edits + 1) * sizeof(bt2gpu_edit));
 	start_fetch(c, 0, 0, 0, c->stream);
 	settle(c->d2hspan[c->cur], c->ctr.ms_d2h);
-	out->n = n; out->reads = c->h_rr.as<bt2gpu_read_result>(); out->alns = c->h_alns.as<bt2gpu_aln>(); out->n_alns = c->out_alns;
-	out->edits = c->h_edits.as<bt2gpu_edit>(); out->n_edits = c->out_edits;
+	out->n = n; out->reads = c->hset[c->hcur].rr.as<bt2gpu_read_result>(); out->alns = c->hset[c->hcur].alns.as<bt2gpu_aln>(); out->n_alns = c->out_alns;
+	out->edits = c->hset[c->hcur].edits.as<bt2gpu_edit>(); out->n_edits = c->out_edits;
 }
 
 // bt2gpu_align_batch for more reads than one sub-batch: sub-batch s+1 is uploaded and sub-batch s-1's results are
 // copied back while sub-batch s is aligned (input / result sets alternate; copies run on their own streams)
 void do_align_pipelined(bt2gpu_ctx* c, const bt2gpu_reads* in, bt2gpu_results* out, uint32_t chunk) {
 	const uint32_t n = in->n;
-	c->h_rr.ensure(((size_t)n + 1) * sizeof(bt2gpu_read_result));
-	grow_keep(c->h_alns, 0, ((size_t)n + (n >> 2) + 1024) * sizeof(bt2gpu_aln));
-	grow_keep(c->h_edits, 0, ((size_t)n * 4 + 4096) * sizeof(bt2gpu_edit));
+	c->hset[c->hcur].rr.ensure(((size_t)n + 1) * sizeof(bt2gpu_read_result));
+	grow_keep(c->hset[c->hcur].alns, 0, ((size_t)n + (n >> 2) + 1024) * sizeof(bt2gpu_aln));
+	grow_keep(c->hset[c->hcur].edits, 0, ((size_t)n * 4 + 4096) * sizeof(bt2gpu_edit));
 	size_t rb = 0, ab = 0, eb = 0;
 	static const bool trace = getenv("BT2GPU_TRACE") != nullptr;
 	auto now = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
@@ -513,10 +539,10 @@ void do_align_pipelined(bt2gpu_ctx* c, const bt2gpu_reads* in, bt2gpu_results* o
 		do_run_grow(c, (uint32_t)ab, (uint32_t)eb);
 		const double t2 = now();
 		if(trace) fprintf(stderr, "[bt2gpu] sub-batch at %u: +%.2f ms  stage next %.2f ms  run %.2f ms\n", lo, t0 - t00, t1 - t0, t2 - t1);
-		if((ab + c->out_alns + 1) * sizeof(bt2gpu_aln) > c->h_alns.cap || (eb + c->out_edits + 1) * sizeof(bt2gpu_edit) > c->h_edits.cap) {
+		if((ab + c->out_alns + 1) * sizeof(bt2gpu_aln) > c->hset[c->hcur].alns.cap || (eb + c->out_edits + 1) * sizeof(bt2gpu_edit) > c->hset[c->hcur].edits.cap) {
 			CK(cudaStreamSynchronize(c->d2h)); // copies into the old arrays are over before they move
-			grow_keep(c->h_alns, ab * sizeof(bt2gpu_aln), (ab + c->out_alns + 1) * sizeof(bt2gpu_aln));
-			grow_keep(c->h_edits, eb * sizeof(bt2gpu_edit), (eb + c->out_edits + 1) * sizeof(bt2gpu_edit));
+			grow_keep(c->hset[c->hcur].alns, ab * sizeof(bt2gpu_aln), (ab + c->out_alns + 1) * sizeof(bt2gpu_aln));
+			grow_keep(c->hset[c->hcur].edits, eb * sizeof(bt2gpu_edit), (eb + c->out_edits + 1) * sizeof(bt2gpu_edit));
 		}
 		start_fetch(c, rb, ab, eb, c->d2h);
 		rb += c->n; ab += c->out_alns; eb += c->out_edits;
@@ -526,8 +552,8 @@ void do_align_pipelined(bt2gpu_ctx* c, const bt2gpu_reads* in, bt2gpu_results* o
 	const double t3 = now();
 	for(int k = 0; k < 2; k++) { settle(c->d2hspan[k], c->ctr.ms_d2h); settle(c->h2dspan[k], c->ctr.ms_h2d); }
 	if(trace) fprintf(stderr, "[bt2gpu] drain %.2f ms, total %.2f ms\n", now() - t3, now() - t00);
-	out->n = n; out->reads = c->h_rr.as<bt2gpu_read_result>(); out->alns = c->h_alns.as<bt2gpu_aln>(); out->n_alns = ab;
-	out->edits = c->h_edits.as<bt2gpu_edit>(); out->n_edits = eb;
+	out->n = n; out->reads = c->hset[c->hcur].rr.as<bt2gpu_read_result>(); out->alns = c->hset[c->hcur].alns.as<bt2gpu_aln>(); out->n_alns = ab;
+	out->edits = c->hset[c->hcur].edits.as<bt2gpu_edit>(); out->n_edits = eb;
 }
 
 // ---------------------------------------------------------------- DP fill without any allocation (bt2gpu_fill_noalloc)
@@ -633,7 +659,10 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		c = new bt2gpu_ctx();
 		c->device = device; c->hp = *p;
 		memset(&c->ctr, 0, sizeof(c->ctr));
-		CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+		CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)); CK(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+		for(cudaEvent_t* e : { &c->evFork, &c->evJoin, &c->evFill[0], &c->evFill[1] }) CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+		if(const char* e = getenv("BT2GPU_OVERLAP")) c->overlap = atoi(e) != 0;                 // 0: one stream, one slot set (what the per-kernel times are read from)
+		if(const char* e = getenv("BT2GPU_BT_BLOCKS")) c->btBlocksOverlap = std::max(1, std::min(BT2_BT_BLOCKS_PER_SM, atoi(e)));
 		CK(cudaStreamCreateWithFlags(&c->h2d, cudaStreamNonBlocking)); CK(cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking));
 		for(int k = 0; k < 2; k++) {
 			CK(cudaEventCreate(&c->h2dspan[k].a)); CK(cudaEventCreate(&c->h2dspan[k].b)); CK(cudaEventCreate(&c->d2hspan[k].a)); CK(cudaEventCreate(&c->d2hspan[k].b));
@@ -761,24 +790,56 @@ struct DeviceScope { int prev = -1; explicit DeviceScope(int dev) { cudaGetDevic
 	try { DeviceScope ds_(ctx->device); __VA_ARGS__; } catch(const std::string& e) { ctx->err = e; ctx->spans.clear(); ctx->evused = 0; return -2; } \
 	return 0;
 
+#define NO_FLIGHT(what) if(ctx->inflight) throw std::string(what ": a batch submitted with bt2gpu_submit is still in flight; call bt2gpu_wait first")
+
 int bt2gpu_upload(bt2gpu_ctx* ctx, const bt2gpu_reads* in) {
 	API_GUARD({
 		if(!in) throw std::string("bt2gpu_upload: null batch");
+		NO_FLIGHT("bt2gpu_upload");
 		if(in->n > ctx->maxBatch) throw std::string("bt2gpu_upload: batch larger than BT2GPU_BATCH; use bt2gpu_align_batch");
 		bind_staged(ctx, stage_upload(ctx, in, 0, in->n, 0, ctx->stream));
 		settle(ctx->h2dspan[0], ctx->ctr.ms_h2d);
 	})
 }
-int bt2gpu_run_resident(bt2gpu_ctx* ctx) { API_GUARD({ do_run_grow(ctx); }) }
-int bt2gpu_fetch(bt2gpu_ctx* ctx, bt2gpu_results* out) { API_GUARD({ if(!out) throw std::string("bt2gpu_fetch: null out"); do_fetch(ctx, out); }) }
+int bt2gpu_run_resident(bt2gpu_ctx* ctx) { API_GUARD({ NO_FLIGHT("bt2gpu_run_resident"); do_run_grow(ctx); }) }
+int bt2gpu_fetch(bt2gpu_ctx* ctx, bt2gpu_results* out) { API_GUARD({ if(!out) throw std::string("bt2gpu_fetch: null out"); NO_FLIGHT("bt2gpu_fetch"); do_fetch(ctx, out); }) }
 
+static void align_into_next_set(bt2gpu_ctx* ctx, const bt2gpu_reads* in, bt2gpu_results* out) {
+	ctx->hcur ^= 1;   // the other set of pinned result arrays: what the previous call returned stays as it is
+	const uint32_t chunk = std::min(ctx->pipeChunk, ctx->maxBatch);
+	if(in->n <= chunk) { bind_staged(ctx, stage_upload(ctx, in, 0, in->n, 0, ctx->stream)); do_run_grow(ctx); do_fetch(ctx, out); }
+	else do_align_pipelined(ctx, in, out, chunk);
+}
 int bt2gpu_align_batch(bt2gpu_ctx* ctx, const bt2gpu_reads* in, bt2gpu_results* out) {
 	API_GUARD({
 		if(!in || !out) throw std::string("bt2gpu_align_batch: null argument");
-		const uint32_t chunk = std::min(ctx->pipeChunk, ctx->maxBatch);
-		if(in->n <= chunk) { bind_staged(ctx, stage_upload(ctx, in, 0, in->n, 0, ctx->stream)); do_run_grow(ctx); do_fetch(ctx, out); }
-		else do_align_pipelined(ctx, in, out, chunk);
+		NO_FLIGHT("bt2gpu_align_batch");
+		align_into_next_set(ctx, in, out);
 	})
+}
+
+// bt2gpu_align_batch split in two for a caller with one thread (the reference's batch loop): submit returns at once, the batch is
+// aligned by a worker thread of the context while the caller finishes the reads of the batch before (P7, the SAM sink)
+int bt2gpu_submit(bt2gpu_ctx* ctx, const bt2gpu_reads* in) {
+	API_GUARD({
+		if(!in) throw std::string("bt2gpu_submit: null batch");
+		NO_FLIGHT("bt2gpu_submit");
+		if(ctx->worker.joinable()) ctx->worker.join();
+		ctx->inflight = true; ctx->flight_rc = 0; memset(&ctx->flight_out, 0, sizeof(ctx->flight_out));
+		ctx->worker = std::thread([ctx, in]() {
+			try { DeviceScope ds(ctx->device); align_into_next_set(ctx, in, &ctx->flight_out); }
+			catch(const std::string& e) { ctx->err = e; ctx->spans.clear(); ctx->evused = 0; ctx->flight_rc = -2; }
+			catch(...) { ctx->err = "bt2gpu_submit: unexpected exception on the worker thread"; ctx->flight_rc = -2; }
+		});
+	})
+}
+int bt2gpu_wait(bt2gpu_ctx* ctx, bt2gpu_results* out) {
+	if(!ctx) return -1;
+	if(!ctx->inflight) { ctx->err = "bt2gpu_wait: nothing was submitted"; return -2; }
+	if(ctx->worker.joinable()) ctx->worker.join();
+	ctx->inflight = false;
+	if(ctx->flight_rc == 0 && out) *out = ctx->flight_out;
+	return ctx->flight_rc;
 }
 
 int bt2gpu_test_fill(bt2gpu_ctx* ctx, uint32_t nprob, const uint32_t* seq_off, const uint8_t* seq, const uint8_t* qual,
@@ -891,6 +952,7 @@ int bt2gpu_fill_noalloc(bt2gpu_ctx* ctx, void* stream, uint32_t nprob, const uin
 
 void bt2gpu_destroy(bt2gpu_ctx* c) {
 	if(!c) return;
+	if(c->worker.joinable()) c->worker.join();   // (a batch still in flight is finished first)
 	cudaSetDevice(c->device);
 	cudaDeviceSynchronize();
 	for(void* p : c->resident) cudaFree(p);
@@ -911,10 +973,11 @@ void bt2gpu_destroy(bt2gpu_ctx* c) {
 	if(c->h2d) cudaStreamDestroy(c->h2d);
 	if(c->d2h) cudaStreamDestroy(c->d2h);
 	if(c->hbox) cudaFreeHost(const_cast<HostBox*>(c->hbox));
-	HBuf* hall[] = { &c->h_rr, &c->h_alns, &c->h_edits };
-	for(HBuf* b : hall) b->release();
+	for(int k = 0; k < 2; k++) { c->hset[k].rr.release(); c->hset[k].alns.release(); c->hset[k].edits.release(); }
 	for(cudaEvent_t e : c->evpool) cudaEventDestroy(e);
 	if(c->stream) cudaStreamDestroy(c->stream);
+	if(c->stream2) cudaStreamDestroy(c->stream2);
+	for(cudaEvent_t e : { c->evFork, c->evJoin, c->evFill[0], c->evFill[1] }) if(e) cudaEventDestroy(e);
 	delete c;
 }
 

@@ -66,6 +66,7 @@ struct Job {
 	char* filemem = nullptr; size_t filecap = 0;
 	mutable std::vector<std::vector<size_t>> scan_nl;   // the reader's per-thread newline positions
 	mutable std::vector<size_t> scan_ls; mutable std::vector<uint32_t> scan_len;
+	int reader_threads = 0, sink_threads = 0;   // bt2host_job_set_threads: 0 = all the OpenMP threads there are
 	mutable uint64_t range_next_id = 0;   // reads handed out by batch_from_fastq_range so far (ranges are taken in file order, from offset 0)
 	~Job();
 };

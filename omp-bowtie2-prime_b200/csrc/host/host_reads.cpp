@@ -269,7 +269,7 @@ static int fastq_fast(const Job& job, Batch& b, const std::string& path, uint64_
 		const int fd = fileno(f);
 		int nr = 1;
 #ifdef _OPENMP
-		nr = std::max(1, std::min(omp_get_max_threads(), (int)((size_t)sz >> 22) + 1));
+		nr = std::max(1, std::min(job.reader_threads > 0 ? job.reader_threads : omp_get_max_threads(), (int)((size_t)sz >> 22) + 1));
 #endif
 		bool ok = true;
 		#pragma omp parallel for num_threads(nr) schedule(static, 1) reduction(&&: ok)
@@ -289,7 +289,7 @@ static int fastq_fast(const Job& job, Batch& b, const std::string& path, uint64_
 	// ---- line starts: every thread lists the '\n' of its slice (and looks for a CR, which sends the file to the serial parser)
 	int nt = 1;
 #ifdef _OPENMP
-	nt = std::max(1, std::min(omp_get_max_threads(), (int)(N >> 20) + 1));
+	nt = std::max(1, std::min(job.reader_threads > 0 ? job.reader_threads : omp_get_max_threads(), (int)(N >> 20) + 1));
 #endif
 	std::vector<std::vector<size_t>>& nl = job.scan_nl;   // kept by the job: no allocation from the second range on
 	if(nl.size() < (size_t)nt) nl.resize((size_t)nt);

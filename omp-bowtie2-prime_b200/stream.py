@@ -3,8 +3,9 @@
 records (bt2host_sam_write).  The stages of neighbouring batches overlap: the reference's own driver has the same three
 stages (`PatternSourceReadAhead`, the batch loop, `OutputQueue`; bt2_search.cpp:2414-2862, pat.h, outq.cpp).
 
-Two contexts on the same device take the batches alternately, because a context's results stay valid only until its next
-call and the sink is still reading batch i while batch i+1 is aligned."""
+One context does it: a context keeps two sets of result arrays and successive bt2gpu_align_batch calls take them in turn
+(include/bt2gpu.h), so the sink can still be reading batch i while batch i+1 is aligned; batch i+2 waits for the sink."""
+import os
 import queue
 import threading
 import time
@@ -12,18 +13,36 @@ import time
 from .binding import GpuAligner
 
 
-def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, aligners=None, start=0, end=None, header=True, stats=None):
-    """Returns (reads, bytes written).  `aligners`: two GpuAligner of `job` to reuse (else created and closed here).
+def _cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, aligners=None, start=0, end=None, header=True, stats=None,
+                 threads=None):
+    """Returns (reads, bytes written).  `aligners`: a list with the GpuAligner of `job` to reuse (else one is created and closed here;
+    two objects are taken alternately, for aligners whose results last only until their next call).
     stats: a dict that receives the seconds each stage was busy ("parse", "align", "sam": they overlap) and the number of ranges.
+    threads: (reader, sink) OpenMP threads; default: the cores split 3 : 5 (formatting and writing SAM is the heavier stage), two left
+    to the aligner's own host threads when there are at least eight.
     start / end: byte range of the file to take (both at record starts): a shard of a multi-GPU job (reads shard by batch,
     every device holds a replica of the index, the per-shard SAM files are concatenated in shard order); header=False for shards > 0."""
+    if threads is None and os.environ.get("BT2HOST_STREAM_THREADS"):      # "reader,sink"
+        threads = tuple(int(x) for x in os.environ["BT2HOST_STREAM_THREADS"].split(","))
+    if threads is None:
+        nc = _cores()
+        avail = max(2, nc - 2 if nc >= 8 else nc)
+        threads = (max(1, avail * 3 // 8), max(1, avail - avail * 3 // 8))
+    job.set_threads(*threads)
     own = aligners is None
     if own:
-        aligners = [GpuAligner(job, device), GpuAligner(job, device)]
+        aligners = [GpuAligner(job, device)]
     parsed, done = queue.Queue(maxsize=2), queue.Queue(maxsize=2)
-    free = [threading.Semaphore(1), threading.Semaphore(1)]   # context k may align again once the sink has written its last results
+    free = [threading.Semaphore(1), threading.Semaphore(1)]   # result set k may be written again once the sink is through with what it held
     errors = []
-    busy = {"parse": 0.0, "align": 0.0, "sam": 0.0, "ranges": 0}
+    busy = {"parse": 0.0, "align": 0.0, "sam": 0.0, "ranges": 0, "threads": list(threads)}
 
     def reader():
         try:
@@ -45,7 +64,7 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, a
 
     def sink():
         try:
-            with open(out_path, "wb") as f:
+            with open(out_path, "w+b") as f:      # read + write: the sink copies its blocks into the file through a shared mapping
                 if header:
                     f.write(job.sam_header().encode("latin-1"))
                 while True:
@@ -84,7 +103,7 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, a
             k = i & 1
             free[k].acquire()                  # (the other context's results may still be being written)
             t0 = time.perf_counter()
-            res = aligners[k].align(b)
+            res = aligners[k % len(aligners)].align(b)
             busy["align"] += time.perf_counter() - t0
             busy["ranges"] += 1
             done.put((b, res, k))
@@ -98,6 +117,7 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, a
     if own:
         for g in aligners:
             g.close()
+    job.set_threads(0, 0)
     if errors:
         raise errors[0]
     if stats is not None:

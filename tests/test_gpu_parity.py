@@ -201,3 +201,28 @@ def test_gpu_i16_score_range_limit():
     with pytest.raises(RuntimeError, match="16-bit"):
         gpu.align(batch)
     gpu.close()
+
+
+def test_submit_wait_and_result_lifetime():
+    """bt2gpu_submit / bt2gpu_wait == bt2gpu_align_batch, and what a call returned is still there after the next call on the same
+    context (two sets of result arrays taken in turn): one context is enough for a reader / aligner / sink pipeline"""
+    job = pkg.Job(common.index_base("syn"), "-k 3")
+    a = job.fastq(common.reads_path("syn100"), 0, 700)
+    b = job.fastq(common.reads_path("syn150"), 0, 900)
+    gpu = _gpu(job)
+    ra = gpu.align(a)
+    sam_a = job.sam_bytes(a, ra, 1)
+    gpu.submit(b)
+    with pytest.raises(RuntimeError, match="in flight"):
+        gpu.align(a)                       # one batch in flight per context
+    assert job.sam_bytes(a, ra, 1) == sam_a  # read while b is being aligned
+    rb = gpu.wait()
+    sam_b = job.sam_bytes(b, rb, 1)
+    assert job.sam_bytes(a, ra, 1) == sam_a  # ... and after
+    g2 = _gpu(job)
+    assert job.sam_bytes(b, g2.align(b), 1) == sam_b
+    with pytest.raises(RuntimeError, match="nothing was submitted"):
+        gpu.wait()
+    gpu.submit(a); rc = gpu.wait()          # takes the set ra lived in
+    assert job.sam_bytes(a, rc, 1) == sam_a and job.sam_bytes(b, rb, 1) == sam_b
+    gpu.close(); g2.close()

@@ -68,6 +68,15 @@ def test_sink_to_file_equals_sink_to_buffer(tmp_path):
     assert n == len(want)
     assert (tmp_path / "o.sam").read_bytes() == b"@HD\n" + want
     assert m1[0] - m0[0] == batch.n
+    # a file opened for reading and writing: the blocks go through a shared mapping of the file (twice: growing it, then into a hole)
+    with open(tmp_path / "m.sam", "w+b") as f:
+        f.write(b"@HD\n")
+        assert job.sam_write(batch, res, f, 1) == len(want)
+        f.write(b"mid\n")
+        assert job.sam_write(batch, res, f, 1) == len(want)
+        f.write(b"end\n")
+    assert len(want) > (1 << 16)
+    assert (tmp_path / "m.sam").read_bytes() == b"@HD\n" + want + b"mid\n" + want + b"end\n"
     # a descriptor that cannot seek (pipe): sequential writes, same bytes
     import os, threading
     r, w = os.pipe()
