@@ -42,8 +42,12 @@ extern "C" {
 
 /* Limits inherited from the reference's fixed DP buffers
  * (aligner_result.h:42-43 ALN_MAX_ROWS/ALN_MAX_COLS, aligner_sw_driver.h:95 ALN_MAX_ITER). */
-#define BT2GPU_MAX_ROWS 160
+#ifndef BT2GPU_MAX_ROWS      /* a build-time constant, as in the reference: libbt2gpu_long.so is the same source compiled with   */
+#define BT2GPU_MAX_ROWS 160  /* -DBT2GPU_MAX_ROWS=1000 -DBT2GPU_MAX_COLS=1072 (reads up to 1 kbp; SURVEY 8f rank 3, beyond the     */
+#endif                       /* reference's own limits).  bt2gpu_max_rows() / bt2gpu_max_cols() tell which build was loaded.        */
+#ifndef BT2GPU_MAX_COLS
 #define BT2GPU_MAX_COLS 200
+#endif
 #define BT2GPU_MAX_ITER 800
 
 /* Return codes of SwDriver::extendSeeds (aligner_sw_driver.h:274-291) plus the
@@ -305,6 +309,8 @@ int bt2gpu_reset_counters(bt2gpu_ctx *ctx);
 const char *bt2gpu_last_error(const bt2gpu_ctx *ctx);
 void bt2gpu_destroy(bt2gpu_ctx *ctx);
 int bt2gpu_abi_version(void);
+int bt2gpu_max_rows(void);   /* BT2GPU_MAX_ROWS / BT2GPU_MAX_COLS this library was built with */
+int bt2gpu_max_cols(void);
 
 /* Stage-level test hook (not part of the reference boundary): runs the DP-fill kernel
  * on nprob independent problems.  Problem i uses rows[i] read bases at seq/qual +
@@ -344,7 +350,11 @@ int bt2gpu_test_fill(bt2gpu_ctx *ctx, uint32_t nprob, const uint32_t *seq_off, c
  * range (rows 1..160, cols 1..199) gets ncand = 0, lrmax = -1 and no flags.
  * flags: rows[i] x cols[i] bytes, row-major, at flags + flags_off[i] (0x80 for a cell outside the band of
  * diagonals the kernel computes for the problem's minsc); cand: 256 entries per problem. */
+#if BT2GPU_MAX_ROWS > 160
+#define BT2GPU_NOALLOC_MAX_PROBLEMS 16    /* the long-read build: a problem's cell flags take 32 times the room */
+#else
 #define BT2GPU_NOALLOC_MAX_PROBLEMS 128
+#endif
 int bt2gpu_fill_noalloc(bt2gpu_ctx *ctx, void *stream, uint32_t nprob,
                         const uint32_t *d_seq_off, const uint8_t *d_seq, const uint8_t *d_qual,
                         const uint16_t *d_rows, const uint16_t *d_cols,

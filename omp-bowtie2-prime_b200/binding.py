@@ -84,6 +84,7 @@ assert READ_DT.itemsize == C.sizeof(bt2gpu_read_result) and ALN_DT.itemsize == C
 
 _host = None
 _gpu = None
+_gpu_long = None
 
 
 def load_host():
@@ -121,13 +122,16 @@ def load_host():
     return _host
 
 
-def load_gpu():
-    """Load libbt2gpu.so; fails loudly if it has not been built (there is no CPU path)."""
-    global _gpu
-    if _gpu is None:
+def load_gpu(long_reads=False):
+    """Load libbt2gpu.so -- or libbt2gpu_long.so, the same sources built with the reference's ALN_MAX_ROWS / ALN_MAX_COLS raised to
+    1000 / 1072 (reads up to 1 kbp) -- ; fails loudly if it has not been built (there is no CPU path)."""
+    global _gpu, _gpu_long
+    if (_gpu_long if long_reads else _gpu) is None:
         p = lib_paths()["gpu"]
+        if long_reads:
+            p = p.replace("libbt2gpu.so", "libbt2gpu_long.so")
         if not os.path.exists(p):
-            raise RuntimeError("libbt2gpu.so is missing (run `make` or __graft_entry__.build()); bt2gpu has no CPU fallback")
+            raise RuntimeError("%s is missing (run `make` or __graft_entry__.build()); bt2gpu has no CPU fallback" % os.path.basename(p))
         g = C.CDLL(p)
         g.bt2gpu_create.restype = C.c_void_p
         g.bt2gpu_create.argtypes = [C.POINTER(bt2gpu_index), C.POINTER(bt2gpu_ref), C.POINTER(bt2gpu_params), C.c_int, C.c_char_p, C.c_size_t]
@@ -144,8 +148,13 @@ def load_gpu():
         g.bt2gpu_last_error.argtypes = [C.c_void_p]
         g.bt2gpu_destroy.argtypes = [C.c_void_p]
         g.bt2gpu_abi_version.restype = C.c_int
-        _gpu = g
-    return _gpu
+        if (g.bt2gpu_max_rows() > 160) != bool(long_reads):
+            raise RuntimeError("%s was built for reads of up to %d bases" % (os.path.basename(p), g.bt2gpu_max_rows()))
+        if long_reads:
+            _gpu_long = g
+        else:
+            _gpu = g
+    return _gpu_long if long_reads else _gpu
 
 
 class Job:
@@ -280,8 +289,8 @@ class Counters(dict):
 class GpuAligner:
     """bt2gpu context bound to one CUDA device (index and reference resident in HBM)."""
 
-    def __init__(self, job, device=0):
-        g = load_gpu()
+    def __init__(self, job, device=0, long_reads=False):
+        g = load_gpu(long_reads)
         self._g = g
         err = C.create_string_buffer(512)
         self.ptr = g.bt2gpu_create(job.index, job.ref, job.params, device, err, 512)

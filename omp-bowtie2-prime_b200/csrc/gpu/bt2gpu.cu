@@ -218,9 +218,18 @@ void ensure_batch(bt2gpu_ctx* c, uint32_t n, uint64_t nbases, uint32_t maxOffs) 
 // dumps H, E and F
 void launch_fill(uint32_t K, bool dbg, const DevParams* dP, const FillArgs& fa, cudaStream_t st) {
 	const dim3 grid(nblk(fa.nprob, BT2_FILL_WARPS * 4)), block(BT2_FILL_WARPS * 32);
+#if BT2_FILL_DYNSMEM
+	// (the long-read build: the tables of a 1000-row problem do not fit the 48 KB a kernel gets without asking)
+	#define BT2_LF1(KK, DD) { static bool once = false; const size_t smem = BT2_FILL_WARPS * sizeof(FillShared<KK>); \
+		if(!once) { CK(cudaFuncSetAttribute(k_fill<KK, DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); once = true; } \
+		k_fill<KK, DD><<<grid, block, smem, st>>>(dP, fa); }
+	#define BT2_LF(KK) { if(dbg) BT2_LF1(KK, true) else BT2_LF1(KK, false) }
+#else
 	#define BT2_LF(KK) { if(dbg) k_fill<KK, true><<<grid, block, 0, st>>>(dP, fa); else k_fill<KK, false><<<grid, block, 0, st>>>(dP, fa); }
+#endif
 	switch(K) { case 2: BT2_LF(2) break; case 4: BT2_LF(4) break; case 8: BT2_LF(8) break; default: BT2_LF(16) break; }
 	#undef BT2_LF
+	#undef BT2_LF1
 }
 
 struct Staged { uint32_t n = 0, maxOffs = 1, base = 0; uint64_t nb = 0; int set = 0; uint32_t fillK = 2, maxRows = 1; };
@@ -918,6 +927,8 @@ int bt2gpu_get_create_info(const bt2gpu_ctx* ctx, double ms[4], uint64_t bytes[4
 }
 int bt2gpu_get_counters(bt2gpu_ctx* ctx, bt2gpu_counters* c) { if(!ctx || !c) return -1; *c = ctx->ctr; return 0; }
 int bt2gpu_reset_counters(bt2gpu_ctx* ctx) { if(!ctx) return -1; memset(&ctx->ctr, 0, sizeof(ctx->ctr)); return 0; }
+int bt2gpu_max_rows(void) { return BT2GPU_MAX_ROWS; }
+int bt2gpu_max_cols(void) { return BT2GPU_MAX_COLS; }
 const char* bt2gpu_last_error(const bt2gpu_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 
 int bt2gpu_fill_noalloc(bt2gpu_ctx* ctx, void* stream, uint32_t nprob, const uint32_t* d_seq_off, const uint8_t* d_seq, const uint8_t* d_qual,

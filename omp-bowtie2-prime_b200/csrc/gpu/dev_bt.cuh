@@ -148,7 +148,7 @@ struct BtMachine {
 	int d0; uint32_t lgK, yy;         // fill layout (dev_common.cuh)
 	bool pi16;                        // the problem runs on the reference's 16-bit path (prob_i16)
 	uint32_t ncand;
-	Rng rnd; uint32_t hw, nsteps;     // nsteps: backtrace steps in the low 24 bits, attempts in the high 8 (<= 208 candidates)
+	Rng rnd; uint32_t hw, nsteps;     // nsteps: backtrace steps in the low 22 bits, attempts in the high 10 (one per candidate at most)
 	// ---- nextAlignment state
 	int phase, result;
 	uint32_t cural, reseed;
@@ -174,7 +174,7 @@ struct BtMachine {
 	// the next candidate's start cell (last row), or the end of the candidate loop
 	BT2_HD void seek_cand() {
 		if(cural >= ncand) { phase = BP_DONE; return; }
-		row = rows - 1; col = (int)(cand_at(cural) & 255u);
+		row = rows - 1; col = (int)(cand_at(cural) & ((1u << BT2_CAND_SHIFT) - 1u));
 		cidx = cell_at(row, col);
 		ct = CT_H;   // (the chunk prediction of the start cell reads it)
 		phase = BP_CAND;
@@ -258,7 +258,7 @@ struct BtMachine {
 	}
 	BT2_HD void finish(const BtCtx& cx) {
 		ReadState& r = rs(cx);
-		r.btSteps += nsteps & 0xffffffu; r.btAttempts += nsteps >> 24;
+		r.btSteps += nsteps & 0x3fffffu; r.btAttempts += nsteps >> 22;
 		r.rnd = rnd; r.scr_hw = (uint16_t)hw;
 	}
 	// entering group g = cural / 4: group g + 1 is copied into the buffer group g - 1 leaves (waited for by the next cell's chunk_wait)
@@ -302,7 +302,7 @@ struct BtMachine {
 			if(!pi16) rnd.init(reseed);   // u8: reseed before and reseed+1 after the backtrace; i16: reseed after only (aligner_sw.cpp:324-348)
 			ct = CT_H;
 			score = 0; nbranch = 0; ned = 0; coreHit = false;
-			nsteps += 1u << 24;
+			nsteps += 1u << 22;
 			phase = BP_STEP;
 		}
 		nsteps++;
@@ -374,7 +374,7 @@ struct BtMachine {
 		a.score = score; a.ns = ns; a.gaps = gaps; a.edits = (int32_t)ne;
 		a.basesAligned = (int32_t)p.rows - (int32_t)ne;   // trimEnd is 0: candidates come from the last row only
 		int refns = 0;
-		const int origCol = (int)(cand_at(cural) & 255u);   // the walk's start column
+		const int origCol = (int)(cand_at(cural) & ((1u << BT2_CAND_SHIFT) - 1u));   // the walk's start column
 		for(int i = col; i <= origCol; i++) if(pc_ref_code(pc, pcs, (uint32_t)i) > 3u) refns++;
 		a.refns = refns; a.n_edits = (uint16_t)ne;
 		if(!p.fw) { // AlnRes::invertEdits: scratch becomes 5'-based

@@ -254,7 +254,8 @@ BT2_HD uint32_t edit_chr(uint32_t e)  { return (e >> 10) & 255u; }
 BT2_HD uint32_t edit_qchr(uint32_t e) { return (e >> 18) & 255u; }
 BT2_HD uint32_t edit_type(uint32_t e) { return (e >> 26) & 3u; }
 BT2_HD uint32_t edit_with_pos(uint32_t e, uint32_t pos) { return (e & ~1023u) | (pos & 1023u); }
-#define BT2_SCRATCH_EDITS 256   // >= DList<Edit,160> capacity actually reachable
+#define BT2_SCRATCH_EDITS (((BT2GPU_MAX_ROWS + 96 + 63) / 64) * 64)   // >= DList<Edit,ALN_MAX_ROWS> capacity actually reachable (256 for 160 rows)
+static_assert(BT2GPU_MAX_ROWS <= 1008 && BT2GPU_MAX_COLS <= 4080, "a packed edit holds 10 bits of read position, a candidate 12 bits of column");
 
 enum { RS_IDLE = 0, RS_EXTEND = 1, RS_ROUND_DONE = 2, RS_FINISHED = 3 };
 
@@ -358,8 +359,8 @@ enum { CF_D = 1, CF_HE = 2, CF_HF = 4, CF_EO = 8, CF_EX = 16, CF_FO = 32, CF_FX 
 //   byte index = ((i / per) * 32 + v) * 16 + (i % per) * K + j
 // The fill writes whole 512-byte rows (every lane of the warp stores its chunk of the same iterations at the same time); a
 // backtrace that follows a diagonal stays with one lane and crosses into a new chunk every 16 / K rows.
-#define BT2_PK_WORDS 12   // 2-bit packed read: 16 bases per word (+ words a 32-base window may touch)
-#define BT2_NM_WORDS 6    // its N mask: 32 bases per word
+#define BT2_PK_WORDS ((BT2GPU_MAX_ROWS + 15) / 16 + 2)   // 2-bit packed read: 16 bases per word (+ words a 32-base window may touch); 12 for 160 rows
+#define BT2_NM_WORDS ((BT2GPU_MAX_ROWS + 31) / 32 + 1)   // its N mask: 32 bases per word; 6 for 160 rows
 #define BT2_LANES 32
 #define BT2_SKEW  (BT2_LANES / 2)           // iterations the last lane lags behind the first
 #define BT2_KMAX  16
@@ -399,7 +400,8 @@ BT2_HD uint32_t fill_K_for(int width) { return width <= 64 ? 2u : (width <= 128 
 //   words [BT2_PC_RD, BT2_PC_WORDS) reference characters of the window's columns (0..3, 4 = N)
 #define BT2_PC_RD    ((BT2GPU_MAX_ROWS + 7) / 8)
 #define BT2_PC_RF    ((BT2GPU_MAX_COLS + 8 + 7) / 8)
-#define BT2_PC_WORDS 48
+#define BT2_PC_WORDS (((BT2_PC_RD + BT2_PC_RF + 3) / 4) * 4)   // (copied in 16-byte groups; 48 for 160 x 200)
+#define BT2_CAND_SHIFT (BT2GPU_MAX_COLS > 255 ? 12 : 8)       // a candidate key: raw H << BT2_CAND_SHIFT | column
 BT2_HD uint32_t pc_read_code(const uint32_t* pc, uint32_t stride, uint32_t row) { return (pc[(row >> 3) * stride] >> ((row & 7u) * 4u)) & 15u; }
 BT2_HD uint32_t pc_ref_code(const uint32_t* pc, uint32_t stride, uint32_t col) { return (pc[(BT2_PC_RD + (col >> 3)) * stride] >> ((col & 7u) * 4u)) & 15u; }
 

@@ -28,7 +28,7 @@
 // 512-byte row per problem.
 // Rows before row 0 ("virtual rows": a lane starts (v + y) / 2 iterations early so that the loop has no per-lane start) are
 // copies of row -1: H = 0xff, no penalties, no gaps, so they hand the right boundary values to row 0 by themselves.
-// Columns left of the window are kept at H = E = 0 by a masked variant of the step that only the first iterations run.
+// Columns left of the window need nothing: their diagonals start with H = 0 and stay there (see fill_step).
 #pragma once
 #include "dev_common.cuh"
 #include "simd16.cuh"
@@ -50,7 +50,13 @@ struct FillArgs {
 	int32_t          exact;     // fill the whole rectangle (bt2gpu_params.exactBestLtMinsc)
 };
 
+#if BT2GPU_MAX_ROWS > 160
+#define BT2_FILL_WARPS 1               // the long-read build: a warp's tables take ~70 KB of (dynamic) shared memory
+#define BT2_FILL_DYNSMEM 1
+#else
 #define BT2_FILL_WARPS 2
+#define BT2_FILL_DYNSMEM 0
+#endif
 #ifndef BT2_FILL_UNROLL
 #define BT2_FILL_UNROLL 1              // iterations of the sweep per loop trip (a divisor of 16 / K)
 #endif
@@ -92,7 +98,10 @@ template<int K> struct FillSet {
 // One step of one lane: the K cells of row i - delta on the lane's diagonals.
 // recvE/recvCE: E of the first cell and the accumulator with E's comparisons, from the lane on the left (previous step);
 // recvF/recvCF: F of the last cell, from the lane on the right.  Leaves what the neighbours need next in send*.
-template<int K, bool MASK, bool REFN, bool DBG>
+// (Cells of real rows left of the window -- col < 0, on the diagonals below 0 -- need no special case: their diagonal starts with H = 0
+// (fill_set_init), scores are <= 0, E enters lane 0 as 0 and F comes down from cells of the same kind, so they compute to H = E = F = 0,
+// which is what the reference's first column sees to its left.)
+template<int K, bool REFN, bool DBG>
 BT2_SIMD void fill_step(FillSet<K>& S, const int i, const uint32_t lane, const uint32_t neg_rdge,
                         const uint32_t recvE, const uint32_t recvCE, const uint32_t recvF, const uint32_t recvCF,
                         uint32_t& sendE, uint32_t& sendCE, uint32_t& sendF, uint32_t& sendCF) {
@@ -112,19 +121,12 @@ BT2_SIMD void fill_step(FillSet<K>& S, const int i, const uint32_t lane, const u
 		const uint32_t u = v_add2(S.Hd[j], s);                        // unsaturated H(r-1,c-1) + score
 		const uint32_t f = j + 1 < K ? S.Fdn[(j + 1) % K] : recvF;
 		const uint32_t cf = j + 1 < K ? S.Fc[(j + 1) % K] : recvCF;
-		uint32_t h = v_max3r(u, e, f);
+		const uint32_t h = v_max3r(u, e, f);
 		// the comparisons of the backtrace at this cell (bit 7 stays 0: not visited)
 		uint32_t fl = ce | cf;
 		fl = v_flag_ne<0>(h, u, fl);
 		fl = v_flag_ne<1>(h, e, fl);
 		fl = v_flag_ne<2>(h, f, fl);
-		uint32_t am = 0xffffffffu;
-		if(MASK) {   // a real row (r >= 0) left of the window: H = E = 0
-			const int r = i - S.delta;
-			const uint32_t ma = (uint32_t)(((i + S.tA + j) & ~r) >> 31), mb = (uint32_t)(((i + S.tB + j) & ~r) >> 31);
-			am = ~((ma & 0xffffu) | (mb & 0xffff0000u));
-			h &= am;
-		}
 		if(DBG) {
 			const int r = i - S.delta, cA = i + S.tA + j, cB = i + S.tB + j;
 			const uint32_t he = v_prmt(h, e, 0x6240);   // H_A E_A H_B E_B
@@ -133,9 +135,8 @@ BT2_SIMD void fill_step(FillSet<K>& S, const int i, const uint32_t lane, const u
 		}
 		// E of the next column in this row and its two comparisons
 		const uint32_t be = v_add2(h, rw.neg_rdgo), ae = v_add2(e, neg_rdge);
-		uint32_t en = v_maxr(ae, be);
+		const uint32_t en = v_maxr(ae, be);
 		ce = v_flag_ne<3>(en, be, v_flag_ne<4>(en, ae, BT2_FL_BASE));
-		if(MASK) en &= am;
 		e = en;
 		// F of the next row in this column and its two comparisons
 		const uint32_t bf = v_add2(h, rw.neg_rfgo_nx), af = v_add2(f, rw2.neg_rfge_nx);
@@ -202,7 +203,8 @@ template<int K> BT2_SIMD void fill_set_init(FillSet<K>& S, FillShared<K>& sh, co
 // against a mismatching / an N reference character, and the (negated) gap penalties; inside the gap barrier
 // (aligner_swsse_ee_u8.cpp:101-115: first/last gapbar rows), in the virtual rows and (reference gaps) into row 0 the gap
 // penalties are large enough to keep E and F at 0
-template<int K> BT2_SIMD void fill_build_rows(const DevParams& P, FillShared<K>& sh, const int set, const FillProb& A, const FillProb& B,
+// pentab: Scoring::mmpens then Scoring::npens, 256 bytes each (DevParams holds them back to back; the kernel reads its shared-memory copy)
+template<int K> BT2_SIMD void fill_build_rows(const DevParams& P, const uint8_t* pentab, FillShared<K>& sh, const int set, const FillProb& A, const FillProb& B,
                                               const uint8_t* seqA, const uint8_t* qualA, bool fwA, const uint8_t* seqB, const uint8_t* qualB, bool fwB,
                                               const uint32_t lane, const int nrow) {
 	for(int idx = (int)lane; idx < nrow; idx += BT2_LANES) {
@@ -219,8 +221,8 @@ template<int K> BT2_SIMD void fill_build_rows(const DevParams& P, FillShared<K>&
 				q -= 33; if(q < 0) q = 0; if(q > 255) q = 255;
 			}
 			rdc[x] = c > 3 ? 7 : c;
-			pen[x] = real ? (c > 3 ? P.npens[q] : P.mmpens[q]) : 0;
-			penN[x] = real ? P.npens[q] : 0;
+			pen[x] = real ? (c > 3 ? pentab[256 + q] : pentab[q]) : 0;
+			penN[x] = real ? pentab[256 + q] : 0;
 			const bool gaps_ok = real && !(r < P.gapbar || X.rows - 1 - r < P.gapbar);
 			const int r1 = r + 1;
 			const bool into_ok = X.on && r1 > 0 && r1 < X.rows && !(r1 < P.gapbar || X.rows - 1 - r1 < P.gapbar);
@@ -262,7 +264,7 @@ template<int K> BT2_SIMD bool fill_build_ref(FillShared<K>& sh, const int set, c
 #if defined(__CUDACC__)
 
 // the sweep: iterations [i0, i1), 16 / K per chunk
-template<int K, bool MASK, bool REFN, bool DBG>
+template<int K, bool REFN, bool DBG>
 __device__ __forceinline__ void fill_sweep(int i0, const int i1, FillSet<K>& S0, FillSet<K>& S1, const uint32_t lane, const uint32_t neg_rdge,
                                            uint32_t& sendE, uint32_t& sendCE, uint32_t& sendF, uint32_t& sendCF,
                                            uint4* __restrict__ o0a, uint4* __restrict__ o0b, uint4* __restrict__ o1a, uint4* __restrict__ o1b) {
@@ -281,8 +283,8 @@ __device__ __forceinline__ void fill_sweep(int i0, const int i1, FillSet<K>& S0,
 				uint32_t rF = __shfl_down_sync(0xffffffffu, sendF, 1), rCF = __shfl_down_sync(0xffffffffu, sendCF, 1);
 				if(lane == 0) { rE = 0u; rCE = E_EDGE; }                   // nothing left of the band
 				if(lane == BT2_LANES - 1) { rF = 0u; rCF = F_EDGE; }       // nothing right of it
-				if(slot == 0) fill_step<K, MASK, REFN, DBG>(S0, i, lane, neg_rdge, rE, rCE, rF, rCF, sendE, sendCE, sendF, sendCF);
-				else fill_step<K, MASK, REFN, DBG>(S1, i, lane, neg_rdge, rE, rCE, rF, rCF, sendE, sendCE, sendF, sendCF);
+				if(slot == 0) fill_step<K, REFN, DBG>(S0, i, lane, neg_rdge, rE, rCE, rF, rCF, sendE, sendCE, sendF, sendCF);
+				else fill_step<K, REFN, DBG>(S1, i, lane, neg_rdge, rE, rCE, rF, rCF, sendE, sendCE, sendF, sendCF);
 			}
 		}
 		const int g = (i0 / PER) * BT2_LANES;
@@ -295,7 +297,12 @@ __device__ __forceinline__ void fill_sweep(int i0, const int i1, FillSet<K>& S0,
 
 template<int K, bool DBG>
 __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(const DevParams* __restrict__ Pp, const FillArgs a) {
+#if BT2_FILL_DYNSMEM
+	extern __shared__ __align__(16) unsigned char fill_smem[];
+	FillShared<K>* const shs = reinterpret_cast<FillShared<K>*>(fill_smem);
+#else
 	__shared__ FillShared<K> shs[BT2_FILL_WARPS];
+#endif
 	const DevParams& P = *Pp;
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const uint32_t slot0 = (blockIdx.x * BT2_FILL_WARPS + warp) * 4u;
@@ -317,7 +324,11 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 	}
 	uint8_t* const raw_rf = reinterpret_cast<uint8_t*>(&sh.hl[0][0]);        // [4][BT2GPU_MAX_COLS + 8] masks as the extension step left them
 	uint8_t* const raw_sq = reinterpret_cast<uint8_t*>(&sh.refw[0][0]);      // [4][2][BT2GPU_MAX_ROWS] bases, qualities (forward read)
-	static_assert(sizeof(sh.hl) >= 4 * (BT2GPU_MAX_COLS + 8) && sizeof(sh.refw) >= 8 * BT2GPU_MAX_ROWS, "staging fits the arrays it borrows");
+	uint8_t* const pentab = raw_rf + 4 * (BT2GPU_MAX_COLS + 8);             // [512] mismatch and N penalties by quality (a lane copies 16 bytes)
+	static_assert(sizeof(sh.hl) >= 4 * (BT2GPU_MAX_COLS + 8) + 512 && sizeof(sh.refw) >= 8 * BT2GPU_MAX_ROWS, "staging fits the arrays it borrows");
+	static_assert(offsetof(DevParams, mmpens) % 16 == 0 && offsetof(DevParams, npens) == offsetof(DevParams, mmpens) + 256 && offsetof(FillShared<K>, hl) % 16 == 0
+	              && (4 * (BT2GPU_MAX_COLS + 8)) % 16 == 0 && sizeof(FillShared<K>) % 16 == 0, "the penalty tables are copied as one uint4 per lane");
+	const uint4 pent = *reinterpret_cast<const uint4*>(P.mmpens + 16u * lane);
 	#pragma unroll
 	for(int q = 0; q < 4; q++) {
 		FillProb& X = pr[q];
@@ -325,6 +336,7 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 		X.rows = X.on ? (int)(hd[q].y & 0xffffu) : 0; X.cols = X.on ? (int)(hd[q].y >> 16) : 0; X.d0 = 0;
 		X.fw = (hd[q].z & 0xffu) != 0; X.start = (X.on && (hd[q].z & 0x4000u)) ? BT2_I16_START : 0xff; X.minsc = (int)hd[q].w;
 	}
+#if BT2GPU_MAX_ROWS <= 160 && BT2GPU_MAX_COLS + 8 <= 256
 	{ // loads first, all of them; the stores into the staging area (which wait for their loads) after
 		constexpr int NIT = (BT2GPU_MAX_ROWS + BT2_LANES - 1) / BT2_LANES;
 		uint2 mk[4]; uint8_t sb[4][NIT], qb[4][NIT];
@@ -351,7 +363,18 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 			}
 		}
 	}
-	int rowsW = 0, mask_to = 0, widthW = 1; bool any = false;
+#else
+	#pragma unroll
+	for(int q = 0; q < 4; q++) {   // (the long-read build: plain loops, a warp's prologue is a small part of a 1000-row sweep)
+		const FillProb& X = pr[q];
+		if(!X.on) continue;
+		for(uint32_t c = lane * 8u; c < (uint32_t)X.cols + 1u; c += BT2_LANES * 8u)
+			*reinterpret_cast<uint2*>(raw_rf + q * (BT2GPU_MAX_COLS + 8) + c) = *reinterpret_cast<const uint2*>(a.probs[slot0 + q].rf + c);
+		for(int r = (int)lane; r < X.rows; r += BT2_LANES) { raw_sq[(2 * q) * BT2GPU_MAX_ROWS + r] = a.seq[so[q] + r]; raw_sq[(2 * q + 1) * BT2GPU_MAX_ROWS + r] = a.qual[so[q] + r]; }
+	}
+#endif
+	*reinterpret_cast<uint4*>(pentab + 16u * lane) = pent;
+	int rowsW = 0, widthW = 1; bool any = false;
 	#pragma unroll
 	for(int q = 0; q < 4; q++) {
 		FillProb& X = pr[q];
@@ -361,7 +384,6 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 		if(dhi - dlo + 1 > BT2_LANES * K) { if(lane == 0) atomicOr(a.error, 64u); dhi = dlo + BT2_LANES * K - 1; }
 		X.d0 = dlo;
 		if(X.rows > rowsW) rowsW = X.rows;
-		if(-dlo > mask_to) mask_to = -dlo;
 		if(dhi - dlo + 1 > widthW) widthW = dhi - dlo + 1;
 		if(lane == 0) { a.probs[slot0 + q].lay = (uint8_t)(((hd[q].z >> 8) & 0x40u) | K | ((q >> 1) << 7)); a.probs[slot0 + q].d0 = (int16_t)dlo; }
 	}
@@ -375,7 +397,7 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 	// ---- phase B: the sweep's tables out of the staged bytes: row tables first (they read the bases the window table will overwrite)
 	#pragma unroll
 	for(int set = 0; set < 2; set++)
-		fill_build_rows<K>(P, sh, set, pr[2 * set], pr[2 * set + 1],
+		fill_build_rows<K>(P, pentab, sh, set, pr[2 * set], pr[2 * set + 1],
 		                   raw_sq + (4 * set) * BT2GPU_MAX_ROWS, raw_sq + (4 * set + 1) * BT2GPU_MAX_ROWS, pr[2 * set].fw,
 		                   raw_sq + (4 * set + 2) * BT2GPU_MAX_ROWS, raw_sq + (4 * set + 3) * BT2GPU_MAX_ROWS, pr[2 * set + 1].fw, lane, BT2_FILL_ROWPAD + iters + 1);
 	__syncwarp();
@@ -391,18 +413,22 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 			if(!pr[q].on) continue;
 			const int set = q >> 1, x = q & 1;
 			uint32_t* pcw = a.pcache + (size_t)(slot0 + q) * BT2_PC_WORDS;
-			uint32_t wr = 0, wf = 0;
 			#pragma unroll
-			for(int k = 0; k < 8; k++) {
-				const int r = (int)lane * 8 + k, c = (int)lane * 8 + k;
-				const uint32_t rc = r < pr[q].rows ? ((sh.row[set][BT2_FILL_ROWPAD + r].rdc2 >> (16 * x)) & 0xffu) : 0u;
-				wr |= (rc > 3u ? 4u : rc) << (4 * k);
-				uint32_t fc = 0;
-				if(c < pr[q].cols) { const uint32_t m = raw_rf[q * (BT2GPU_MAX_COLS + 8) + c]; fc = m > 15 ? 4u : (m >= 8 ? 3u : (m >= 4 ? 2u : (m >= 2 ? 1u : 0u))); }
-				wf |= fc << (4 * k);
+			for(int base = 0; base < (BT2_PC_RF > BT2_PC_RD ? BT2_PC_RF : BT2_PC_RD); base += BT2_LANES) {
+				const int w = base + (int)lane;
+				uint32_t wr = 0, wf = 0;
+				#pragma unroll
+				for(int k = 0; k < 8; k++) {
+					const int r = w * 8 + k, c = w * 8 + k;
+					const uint32_t rc = r < pr[q].rows ? ((sh.row[set][BT2_FILL_ROWPAD + r].rdc2 >> (16 * x)) & 0xffu) : 0u;
+					wr |= (rc > 3u ? 4u : rc) << (4 * k);
+					uint32_t fc = 0;
+					if(c < pr[q].cols) { const uint32_t m = raw_rf[q * (BT2GPU_MAX_COLS + 8) + c]; fc = m > 15 ? 4u : (m >= 8 ? 3u : (m >= 4 ? 2u : (m >= 2 ? 1u : 0u))); }
+					wf |= fc << (4 * k);
+				}
+				if(w < BT2_PC_RD) pcw[w] = wr;
+				if(w < BT2_PC_RF) pcw[BT2_PC_RD + w] = wf;
 			}
-			if(lane < BT2_PC_RD) pcw[lane] = wr;
-			if(lane < BT2_PC_RF) pcw[BT2_PC_RD + lane] = wf;
 		}
 	}
 	__syncwarp();
@@ -422,16 +448,9 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 	uint4* const o0a = outp(2 * set0); uint4* const o0b = outp(2 * set0 + 1); uint4* const o1a = outp(2 * set1); uint4* const o1b = outp(2 * set1 + 1);
 	const uint32_t neg_rdge = v_pack2(-P.rdGapExt, -P.rdGapExt);
 	uint32_t sendE = 0u, sendCE = BT2_FL_BASE | ((uint32_t)(CF_EO | CF_EX) * 0x00010001u), sendF = 0u, sendCF = BT2_FL_BASE | ((uint32_t)(CF_FO | CF_FX) * 0x00010001u);
-	// columns left of the window exist only while i < -d0 (lane 0 reaches column 0 of row r = i at iteration i = -d0)
-	int i_mask = DBG ? iters : ((mask_to + PER - 1) / PER) * PER; if(i_mask > iters) i_mask = iters;
 	#define BT2_SWEEP_ARGS S0, S1, lane, neg_rdge, sendE, sendCE, sendF, sendCF, o0a, o0b, o1a, o1b
-	if(refHasN) {
-		fill_sweep<K, true, true, DBG>(0, i_mask, BT2_SWEEP_ARGS);
-		if(!DBG) fill_sweep<K, false, true, false>(i_mask, iters, BT2_SWEEP_ARGS);
-	} else {
-		fill_sweep<K, true, false, DBG>(0, i_mask, BT2_SWEEP_ARGS);
-		if(!DBG) fill_sweep<K, false, false, false>(i_mask, iters, BT2_SWEEP_ARGS);
-	}
+	if(refHasN) fill_sweep<K, true, DBG>(0, iters, BT2_SWEEP_ARGS);
+	else fill_sweep<K, false, DBG>(0, iters, BT2_SWEEP_ARGS);
 	#undef BT2_SWEEP_ARGS
 	fill_last_row<K>(S0); fill_last_row<K>(S1);
 	__syncwarp();
@@ -450,7 +469,7 @@ __global__ void __launch_bounds__(BT2_FILL_WARPS * 32, K <= 4 ? 8 : 4) k_fill(co
 			lrmax = max(lrmax, hv8);
 			const bool isc = c < cols && (hv8 - pr[q].start) >= minsc;
 			const uint32_t bal = __ballot_sync(0xffffffffu, isc);
-			if(isc) ckey[ncand + __popc(bal & ((1u << lane) - 1))] = ((uint32_t)hv8 << 8) | (uint32_t)c;
+			if(isc) ckey[ncand + __popc(bal & ((1u << lane) - 1))] = ((uint32_t)hv8 << BT2_CAND_SHIFT) | (uint32_t)c;
 			ncand += __popc(bal);
 		}
 		#pragma unroll

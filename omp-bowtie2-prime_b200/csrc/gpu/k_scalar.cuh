@@ -178,6 +178,14 @@ __global__ void __launch_bounds__(128, BT2_STEP_BLOCKS_PER_SM) k_step(const DevP
 #ifndef BT2_BT_DONE_MIN
 #define BT2_BT_DONE_MIN 8
 #endif
+#if BT2GPU_MAX_ROWS > 160      // the long-read build: a lane's copy of its problem's characters is ~1 KB of shared memory
+#ifndef BT2_BT_THREADS
+#define BT2_BT_THREADS 32
+#endif
+#ifndef BT2_BT_BLOCKS_PER_SM
+#define BT2_BT_BLOCKS_PER_SM 5
+#endif
+#endif
 #ifndef BT2_BT_THREADS
 #define BT2_BT_THREADS 128
 #endif

@@ -6,6 +6,7 @@
 #include <string>
 #include <vector>
 #include <memory>
+#include <mutex>
 #include <utility>
 #include <new>
 #include <cmath>
@@ -48,6 +49,7 @@ struct Options {
 	std::string cmdline;
 };
 
+struct BatchPool;
 struct Job {
 	// index arrays (owned)
 	std::vector<uint64_t> plen, rstarts, fchr, ftab, eftab, offs;
@@ -66,6 +68,7 @@ struct Job {
 	char* filemem = nullptr; size_t filecap = 0;
 	mutable std::vector<std::vector<size_t>> scan_nl;   // the reader's per-thread newline positions
 	mutable std::vector<size_t> scan_ls; mutable std::vector<uint32_t> scan_len;
+	std::shared_ptr<BatchPool> pool;      // set by bt2host_job_create
 	int reader_threads = 0, sink_threads = 0;   // bt2host_job_set_threads: 0 = all the OpenMP threads there are
 	mutable uint64_t range_next_id = 0;   // reads handed out by batch_from_fastq_range so far (ranges are taken in file order, from offset 0)
 	~Job();
@@ -79,7 +82,9 @@ template<typename T> struct NoInitAlloc : std::allocator<T> {
 };
 typedef std::vector<uint8_t, NoInitAlloc<uint8_t>> ByteVec;
 
+struct BatchPool;
 struct Batch {
+	std::shared_ptr<BatchPool> pool;   // where the batch's arrays go when it is destroyed (a streaming reader's batches: no fresh pages per range)
 	std::vector<uint32_t> off;
 	ByteVec seq, qual;
 	std::vector<uint32_t> seed;
@@ -99,6 +104,13 @@ struct Batch {
 	void finalize();
 };
 
+} // namespace bt2host
+struct bt2host_batch { bt2host::Batch b; };
+namespace bt2host {
+// batches given back by bt2host_batch_destroy, for the next bt2host_batch_from_fastq_range of the same job (their vectors keep
+// their capacity, so a steady stream of ranges allocates nothing); shared by the job and its batches, whichever goes last
+struct BatchPool { std::mutex mu; std::vector<bt2host_batch*> idle; ~BatchPool() { for(bt2host_batch* b : idle) delete b; } };
+
 bool load_index(Job& job, const std::string& base, std::string& err);
 bool parse_options(Options& o, const std::string& args, std::string& err);
 uint32_t gen_rand_seed(const uint8_t* seq, const uint8_t* qual, size_t len,
@@ -112,4 +124,3 @@ bool batch_from_arrays(const Job& job, Batch& b, uint32_t n, const uint32_t* off
 } // namespace bt2host
 
 struct bt2host_job   { bt2host::Job j; };
-struct bt2host_batch { bt2host::Batch b; };

@@ -297,11 +297,12 @@ static int fastq_fast(const Job& job, Batch& b, const std::string& path, uint64_
 	#pragma omp parallel for num_threads(nt) schedule(static, 1) reduction(||: has_cr)
 	for(int t = 0; t < nt; t++) {
 		const size_t lo = N * (size_t)t / (size_t)nt, hi = N * (size_t)(t + 1) / (size_t)nt;
-		std::vector<size_t>& v = nl[(size_t)t];
+		std::vector<size_t> v = std::move(nl[(size_t)t]);   // (on this thread's stack while it grows: neighbouring vector headers share cache lines)
 		v.clear();
 		const char* p = buf.data() + lo; const char* e = buf.data() + hi;
-		if(memchr(p, '\r', (size_t)(e - p))) { has_cr = true; continue; }
-		while(p < e) { const char* q = (const char*)memchr(p, '\n', (size_t)(e - p)); if(!q) break; v.push_back((size_t)(q - buf.data()) + 1); p = q + 1; }
+		if(memchr(p, '\r', (size_t)(e - p))) has_cr = true;
+		else while(p < e) { const char* q = (const char*)memchr(p, '\n', (size_t)(e - p)); if(!q) break; v.push_back((size_t)(q - buf.data()) + 1); p = q + 1; }
+		nl[(size_t)t] = std::move(v);
 	}
 	if(has_cr) return 0;
 	std::vector<size_t>& ls = job.scan_ls;               // ls[i] = start of line i; ls[nlines] = one past the last line's '\n'

@@ -59,7 +59,23 @@ build_gpu() {
   rm -rf "$T"
 }
 
+# Oracle D: the -DENABLE_I16 reference with its two size constants raised in a scratch copy (aligner_result.h:42-43
+# ALN_MAX_ROWS 160 -> 1000, ALN_MAX_COLS 200 -> 1072) -- NOT the reference as shipped: it pins what "the same algorithm without the
+# 160-row limit" prints, for reads the shipped binary leaves unaligned.  Run it with -p 1: its DP buffers are sized per read slot.
+build_long() {
+  if [ "$OUT/bowtie2-align-l-long" -nt "$REF/bt2_search.cpp" ] && [ -z "$FORCE" ]; then return; fi
+  echo "[build_ref] bowtie2-align-l-long (constants raised: not the reference as shipped)" >&2
+  local T; T=$(mktemp -d /tmp/bt2ref_long.XXXXXX)
+  cp -r "$REF"/. "$T"/ && chmod -R u+w "$T"
+  sed -i 's/^#define ALN_MAX_ROWS 160/#define ALN_MAX_ROWS 1000/; s/^#define ALN_MAX_COLS 200/#define ALN_MAX_COLS 1072/' "$T/aligner_result.h"
+  grep -q "ALN_MAX_ROWS 1000" "$T/aligner_result.h" && grep -q "ALN_MAX_COLS 1072" "$T/aligner_result.h" || { echo "[build_ref] constants not found" >&2; rm -rf "$T"; return 1; }
+  local C2="${COMMON//$REF/$T}"
+  g++ -O3 -msse2 $C2 -DENABLE_I16 -o "$OUT/bowtie2-align-l-long" "$T/bowtie2-align.cpp" -lpthread -lz || { rm -rf "$T"; return 1; }
+  rm -rf "$T"
+}
+
 build_align bowtie2-align-l &
+build_long &
 build_build &
 build_gpu &
 # the opt-in 16-bit build (SURVEY 8c oracle mode B): pins the i16 protocol (tests/golden/*_i16.sam)

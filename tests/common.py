@@ -33,6 +33,14 @@ CASES = {
 }
 
 
+# Reads longer than the reference's 160-row limit: the golden SAM comes from oracle/_ref/bowtie2-align-l-long, the
+# -DENABLE_I16 reference with ALN_MAX_ROWS / ALN_MAX_COLS raised in a scratch copy (oracle/build_ref.sh) -- not the reference as shipped.
+CASES_LONG = {
+    "synL_mix_i16": ("syn", "synLmix", "--i16", "synL_mix_i16.sam"),
+    "synL_mix_k3_sens": ("syn", "synLmix", "--i16 --sensitive -k 3", "synL_mix_k3_sens.sam"),
+}
+
+
 def _run(cmd):
     subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
 
@@ -78,6 +86,16 @@ def reads_path(name):
     p = os.path.join(WORK, name + ".fq")
     if os.path.exists(p):
         return p
+    if name == "synLmix":                          # 250, 600 and 1000 bp reads, names made unique per length
+        index_base("syn")
+        with open(p + ".tmp", "w") as out:
+            for L, nr, seed, subst in ((250, 150, 21, 0.01), (600, 120, 22, 0.02), (1000, 120, 23, 0.02)):
+                part = os.path.join(WORK, "synL%d.fq" % L)
+                gen(["reads", os.path.join(WORK, "syn.fa"), part, nr, L, "--seed", seed, "--subst", subst])
+                for i, line in enumerate(open(part)):
+                    out.write("@L%d_%s" % (L, line[1:]) if i % 4 == 0 else line)
+        os.replace(p + ".tmp", p)
+        return p
     if name == "synN120":
         index_base("synN")
         gen(["reads", os.path.join(WORK, "synN.fa"), p, 1500, 120, "--seed", 9, "--randqual"])
@@ -108,10 +126,11 @@ def golden_records(fname):
 
 
 class Oracle:
-    """ctypes view of oracle/liboracle.so (oracle_capi.cpp)."""
+    """ctypes view of oracle/liboracle.so (oracle_capi.cpp); long_reads: liboracle_long.so, the restatement built with the reference's
+    ALN_MAX_ROWS / ALN_MAX_COLS raised to 1000 / 1072 (oracle D: beyond the reference's limits)."""
 
-    def __init__(self, job):
-        p = os.path.join(ROOT, "oracle", "liboracle.so")
+    def __init__(self, job, long_reads=False):
+        p = os.path.join(ROOT, "oracle", "liboracle_long.so" if long_reads else "liboracle.so")
         self.lib = C.CDLL(p)
         self.lib.oracle_create.restype = C.c_void_p
         self.lib.oracle_create.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]

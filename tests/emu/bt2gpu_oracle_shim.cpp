@@ -22,6 +22,8 @@ struct bt2gpu_ctx {
 
 extern "C" {
 int bt2gpu_abi_version(void) { return BT2GPU_ABI_VERSION; }
+int bt2gpu_max_rows(void) { return BT2GPU_MAX_ROWS; }
+int bt2gpu_max_cols(void) { return BT2GPU_MAX_COLS; }
 bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* ix, const bt2gpu_ref* rf, const bt2gpu_params* p, int, char* err, size_t errlen) {
 	if(p->abi_version != BT2GPU_ABI_VERSION) { if(err) snprintf(err, errlen, "shim: ABI mismatch"); return nullptr; }
 	bt2gpu_ctx* c = new bt2gpu_ctx();      // deep copies: like the real library, nothing of the caller's is kept

@@ -44,13 +44,13 @@ static int g_fail = 0; static long g_warps = 0, g_cells = 0, g_skipped = 0;
 template<int K, bool DBG> static void run_warp(const DevParams& P, const TProb* tp[4], bool exact) {
 	constexpr int PER = 16 / K;
 	static FillShared<K> sh; memset(&sh, 0xcd, sizeof(sh));
-	FillProb pr[4]; int rowsW = 0, mask_to = 0, widthW = 1;
+	FillProb pr[4]; int rowsW = 0, widthW = 1;
 	for(int q = 0; q < 4; q++) {
 		FillProb& X = pr[q]; X.on = tp[q] != nullptr; X.rows = X.on ? tp[q]->rows : 0; X.cols = X.on ? tp[q]->cols : 0; X.d0 = 0; X.start = (X.on && tp[q]->i16) ? BT2_I16_START : 0xff;
 		if(!X.on) continue;
 		int dlo, dhi; fill_band(P, X.rows, X.cols, tp[q]->minsc, exact, dlo, dhi);
 		if(dhi - dlo + 1 > BT2_LANES * K) { g_skipped++; return; }   // this K cannot hold the problem (the host picks K so that it can)
-		X.d0 = dlo; if(X.rows > rowsW) rowsW = X.rows; if(-dlo > mask_to) mask_to = -dlo; if(dhi - dlo + 1 > widthW) widthW = dhi - dlo + 1;
+		X.d0 = dlo; if(X.rows > rowsW) rowsW = X.rows; if(dhi - dlo + 1 > widthW) widthW = dhi - dlo + 1;
 	}
 	for(int q = 0; q < 4; q++) if(tp[q]) { int dlo, dhi; fill_band(P, tp[q]->rows, tp[q]->cols, tp[q]->minsc, exact, dlo, dhi); if(dhi - dlo + 1 > BT2_LANES * K) return; }
 	// as the kernel: the sweep ends when the last lane that holds band cells has done its last row
@@ -62,7 +62,7 @@ template<int K, bool DBG> static void run_warp(const DevParams& P, const TProb* 
 	for(int set = 0; set < 2; set++) {
 		const TProb* A = tp[2 * set]; const TProb* B = tp[2 * set + 1];
 		for(uint32_t lane = 0; lane < 32; lane++) {
-			fill_build_rows<K>(P, sh, set, pr[2 * set], pr[2 * set + 1], A ? A->rd.data() : dummy, A ? A->qual.data() : dummy, true,
+			fill_build_rows<K>(P, P.mmpens, sh, set, pr[2 * set], pr[2 * set + 1], A ? A->rd.data() : dummy, A ? A->qual.data() : dummy, true,
 			                   B ? B->rd.data() : dummy, B ? B->qual.data() : dummy, true, lane, BT2_FILL_ROWPAD + iters + 1);
 			hasN = fill_build_ref<K>(sh, set, pr[2 * set], pr[2 * set + 1], A ? A->rf.data() : nullptr, B ? B->rf.data() : nullptr, lane, BT2_FILL_ROWPAD + iters + BT2_LANES * K + 1) || hasN;
 		}
@@ -81,10 +81,8 @@ template<int K, bool DBG> static void run_warp(const DevParams& P, const TProb* 
 	const uint32_t E_EDGE = BT2_FL_BASE | ((uint32_t)(CF_EO | CF_EX) * 0x00010001u), F_EDGE = BT2_FL_BASE | ((uint32_t)(CF_FO | CF_FX) * 0x00010001u);
 	uint32_t sE[32], sCE[32], sF[32], sCF[32];
 	for(int l = 0; l < 32; l++) { sE[l] = 0; sCE[l] = E_EDGE; sF[l] = 0; sCF[l] = F_EDGE; }
-	int i_mask = DBG ? iters : ((mask_to + PER - 1) / PER) * PER; if(i_mask > iters) i_mask = iters;
 	std::vector<std::vector<uint8_t>> cells(4, std::vector<uint8_t>(fill_cell_bytes(BT2GPU_MAX_ROWS, K), 0xee));
 	for(int i0 = 0; i0 < iters; i0 += PER) {
-		const bool MASK = i0 < i_mask;
 		for(int u = 0; u < PER; u++) {
 			const int i = i0 + u;
 			for(int slot = 0; slot < 2; slot++) {
@@ -95,9 +93,8 @@ template<int K, bool DBG> static void run_warp(const DevParams& P, const TProb* 
 				}
 				for(uint32_t l = 0; l < 32; l++) {
 					FillSet<K>& S = slot ? S1[l] : S0[l];
-					#define CALL(M, N) fill_step<K, M, N, DBG>(S, i, l, neg_rdge, rE[l], rCE[l], rF[l], rCF[l], sE[l], sCE[l], sF[l], sCF[l])
-					if(MASK) { if(hasN) CALL(true, true); else CALL(true, false); }
-					else { if(hasN) CALL(false, true); else CALL(false, false); }
+					#define CALL(N) fill_step<K, N, DBG>(S, i, l, neg_rdge, rE[l], rCE[l], rF[l], rCF[l], sE[l], sCE[l], sF[l], sCF[l])
+					if(hasN) CALL(true); else CALL(false);
 					#undef CALL
 				}
 			}
@@ -141,7 +138,7 @@ template<int K, bool DBG> static void run_warp(const DevParams& P, const TProb* 
 		}
 		// last row -> candidates
 		int lrmax = 0; std::vector<uint32_t> cand;
-		for(int c = 0; c < t.cols; c++) { const int h = sh.hl[q][c]; if(h > lrmax) lrmax = h; if(h - pr[q].start >= t.minsc) cand.push_back(((uint32_t)h << 8) | (uint32_t)c); }
+		for(int c = 0; c < t.cols; c++) { const int h = sh.hl[q][c]; if(h > lrmax) lrmax = h; if(h - pr[q].start >= t.minsc) cand.push_back(((uint32_t)h << BT2_CAND_SHIFT) | (uint32_t)c); }
 		std::sort(cand.begin(), cand.end(), [](uint32_t a, uint32_t b) { return a > b; });
 		CHECK(lrmax == pb.lrmax, "K=%d exact=%d problem %dx%d minsc %d: lrmax %d vs %d", K, exact, t.rows, t.cols, t.minsc, lrmax, pb.lrmax);
 		CHECK(cand.size() == pb.ncand, "K=%d problem %dx%d: ncand %zu vs %u", K, t.rows, t.cols, cand.size(), pb.ncand);

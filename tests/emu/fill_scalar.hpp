@@ -61,7 +61,7 @@ static void fill_emu(const DevParams& P, Problem& pb, const ReadView& rv, uint8_
 		}
 		const int lr = Hcur[rows - 1];
 		if(lr > lrmax) lrmax = lr;
-		if(lr - S0 >= pb.minsc) cand.push_back(((uint32_t)lr << 8) | (uint32_t)j);
+		if(lr - S0 >= pb.minsc) cand.push_back(((uint32_t)lr << BT2_CAND_SHIFT) | (uint32_t)j);
 		Hprev.swap(Hcur); Eprev.swap(Ecur); Fprev.swap(Fcur); Eleft = Ehere;
 	}
 	// character cache (what K_fill leaves for the backtrace's edits)

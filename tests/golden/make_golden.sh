@@ -45,5 +45,16 @@ python "$ROOT/tools/gen_data.py" ref "$T/synR.fa" 200000 --seed 77 --repeats 0.4
 python "$ROOT/tools/gen_data.py" reads "$T/synR.fa" "$T/synR100.fq" 1500 100 --seed 11 --subst 0.02
 run synR100_default         "$T/synR" "$T/synR100.fq" ""
 run synR100_k3_vs           "$T/synR" "$T/synR100.fq" "-k 3 --very-sensitive"
+# reads beyond the reference's 160-row limit: 250 / 600 / 1000 bp, through oracle/_ref/bowtie2-align-l-long = the
+# -DENABLE_I16 reference with ALN_MAX_ROWS / ALN_MAX_COLS raised to 1000 / 1072 in a scratch copy (NOT the reference as shipped;
+# oracle/build_ref.sh).  -p 1: that build's DP buffers are sized per read slot.  Same reads as tests/common.py reads_path("synLmix").
+: > "$T/synLmix.fq"
+for spec in "250 150 21 0.01" "600 120 22 0.02" "1000 120 23 0.02"; do set -- $spec
+  python "$ROOT/tools/gen_data.py" reads "$T/syn.fa" "$T/synL$1.fq" $2 $1 --seed $3 --subst $4
+  awk -v L=$1 'NR%4==1{sub(/^@/,"@L" L "_")}1' "$T/synL$1.fq" >> "$T/synLmix.fq"
+done
+runL() { OMP_NUM_THREADS=4 "$B/bowtie2-align-l-long" -x "$2" -U "$3" -S "$T/o.sam" -p 1 $4 2>/dev/null; grep -v '^@' "$T/o.sam" | LC_ALL=C sort > "$HERE/$1.sam"; }
+runL synL_mix_i16     "$T/syn" "$T/synLmix.fq" ""
+runL synL_mix_k3_sens "$T/syn" "$T/synLmix.fq" "--sensitive -k 3"
 rm -rf "$T"
 ls -la "$HERE"

@@ -49,6 +49,22 @@ def main():
                 t6 = time.time(); nb = job.sam_write(b, res, f, 1); t7 = time.time()
             print("threads %2d: parse %.1f ms (%.2f M/s)  sam format+copy %.1f ms (%.2f M/s)  format+write new file %.1f ms (%.2f M/s)  rewrite %.1f ms  new file, mapped %.1f ms (%.2f M/s)" % (
                 nt, (t1 - t0) * 1e3, b.n / (t1 - t0) / 1e6, (t3 - t2) * 1e3, b.n / (t3 - t2) / 1e6, (t5 - t4) * 1e3, b.n / (t5 - t4) / 1e6, (t7 - t6) * 1e3, (t9 - t8) * 1e3, b.n / (t9 - t8) / 1e6))
+        # the same results copied out of the pinned arrays into ordinary memory: does the sink read pinned memory slower?
+        import numpy as np
+        raw = res.raw
+        keep = []
+        r2 = pkg.bt2gpu_results(); r2.n = raw.n; r2.n_alns = raw.n_alns; r2.n_edits = raw.n_edits
+        for name, cnt, typ in (("reads", raw.n, pkg.bt2gpu_read_result), ("alns", raw.n_alns, pkg.bt2gpu_aln), ("edits", raw.n_edits, pkg.bt2gpu_edit)):
+            nbytes = max(1, int(cnt)) * ctypes.sizeof(typ)
+            a = np.empty(nbytes, dtype=np.uint8); ctypes.memmove(a.ctypes.data, ctypes.cast(getattr(raw, name), ctypes.c_void_p), int(cnt) * ctypes.sizeof(typ))
+            keep.append(a); setattr(r2, name, ctypes.cast(a.ctypes.data, ctypes.POINTER(typ)))
+        res2 = pkg.Results(r2)
+        for nt in (1, 4, 16):
+            omp.omp_set_num_threads(nt)
+            for which, rr in (("pinned", res), ("pageable", res2)):
+                with open("/dev/null", "wb") as f:
+                    t0 = time.time(); job.sam_write(b, rr, f, 1); t1 = time.time()
+                print("threads %2d, results in %s memory -> /dev/null: %.1f ms (%.2f M/s)" % (nt, which, (t1 - t0) * 1e3, b.n / (t1 - t0) / 1e6), flush=True)
         orc.close(); b.close(); job.close()
         return
     orc = common.Oracle(job)
