@@ -15,7 +15,7 @@
 #endif
 
 namespace bt2host {
-void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_results& res, uint32_t ri, int mode, std::string& o);
+void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_results& res, uint32_t ri, int mode, std::string& o, SinkScratch& scratch);
 std::string sam_header(const Job& job);
 }
 
@@ -112,8 +112,11 @@ static std::vector<std::string>& sam_blocks(const bt2host_job* job, const bt2hos
 		std::string o = std::move(parts[(size_t)t]);
 		uint64_t met[4] = { 0, 0, 0, 0 };
 		o.clear();
-		o.reserve((size_t)(hi - lo) * 480);
-		for(uint32_t i = lo; i < hi; i++) bt2host::sam_for_read(j, met, b->b, *res, i, mode, o);
+		// (only ever grown: before C++20 std::string::reserve(n) with n below the capacity reallocates to n -- 6 MB of fresh pages per
+		// block and call, which was most of the sink's time when the ranges' read counts differed by a few reads)
+		if(o.capacity() < (size_t)(hi - lo) * 480) o.reserve((size_t)(hi - lo) * 512);
+		bt2host::SinkScratch scratch;
+		for(uint32_t i = lo; i < hi; i++) bt2host::sam_for_read(j, met, b->b, *res, i, mode, o, scratch);
 		parts[(size_t)t] = std::move(o);
 		for(int k = 0; k < 4; k++) mets[(size_t)t * 4 + k] = met[k];
 	}

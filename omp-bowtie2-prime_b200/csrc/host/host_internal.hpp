@@ -111,6 +111,7 @@ namespace bt2host {
 // their capacity, so a steady stream of ranges allocates nothing); shared by the job and its batches, whichever goes last
 struct BatchPool { std::mutex mu; std::vector<bt2host_batch*> idle; ~BatchPool() { for(bt2host_batch* b : idle) delete b; } };
 
+struct SinkScratch { struct Impl; Impl* impl; SinkScratch(); ~SinkScratch(); SinkScratch(const SinkScratch&) = delete; SinkScratch& operator=(const SinkScratch&) = delete; };
 bool load_index(Job& job, const std::string& base, std::string& err);
 bool parse_options(Options& o, const std::string& args, std::string& err);
 uint32_t gen_rand_seed(const uint8_t* seq, const uint8_t* qual, size_t len,

@@ -192,8 +192,33 @@ int mapq_v2(bool hasSecbest, int64_t best, int64_t secbestIn, int64_t scMin, int
 
 } // namespace
 
+// the sink's per-thread scratch (no allocation per read; the caller keeps one per thread)
+struct SinkScratch::Impl {
+	std::vector<std::pair<int64_t, size_t> > buf;
+	std::vector<Ed> ed; Stacked st; std::vector<uint8_t> rcbuf; std::string md, cig;
+};
+SinkScratch::SinkScratch() : impl(new Impl) {}
+SinkScratch::~SinkScratch() { delete impl; }
+
+namespace {
+struct Wr { // writes through a pointer into room the caller reserved
+	char* p;
+	void c(char x) { *p++ = x; }
+	void s(const char* x, size_t n) { memcpy(p, x, n); p += n; }
+	template<size_t N> void lit(const char (&x)[N]) { memcpy(p, x, N - 1); p += N - 1; }
+	void i(long long v) {
+		char t[24]; int n = 0;
+		unsigned long long u = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
+		do { t[n++] = (char)('0' + u % 10); u /= 10; } while(u);
+		if(v < 0) *p++ = '-';
+		while(n) *p++ = t[--n];
+	}
+};
+}
+
 // One read -> SAM text appended to `o`.
-void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_results& res, uint32_t ri, int mode, std::string& o) {
+void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_results& res, uint32_t ri, int mode, std::string& o, SinkScratch& scratch) {
+	SinkScratch::Impl& sc = *scratch.impl;
 	const Options& opt = job.opt;
 	const bt2gpu_read_result& rr = res.reads[ri];
 	const uint8_t* seq = b.seq.data() + b.off[ri];
@@ -235,11 +260,10 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 	}
 	// selectByScore
 	const bt2gpu_aln* al = res.alns + rr.aln_off;
-	static thread_local std::vector<std::pair<int64_t, size_t> > buf;   // per-thread scratch: no allocation per read
+	std::vector<std::pair<int64_t, size_t> >& buf = sc.buf;
 	buf.resize(n);
 	for(size_t i = 0; i < n; i++) { buf[i].first = al[i].score; buf[i].second = i; }
-	std::sort(buf.begin(), buf.end());
-	std::reverse(buf.begin(), buf.end());
+	if(n > 1) { std::sort(buf.begin(), buf.end()); std::reverse(buf.begin(), buf.end()); }
 	Rng rnd; rnd.last = rr.rng_last; rnd.lastOff = rr.rng_lastOff;
 	auto shuffle = [&](size_t begin, size_t num) {
 		if(num < 2) return;
@@ -262,11 +286,9 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 	const int64_t scMin = opt.scoreMin.f<int64_t>((double)(float)rdlen);
 	const int64_t scPer = (int64_t)rdlen * opt.p.matchBonus;
 	// the aliased edit scratch
-	static thread_local std::vector<Ed> ed;
-	static thread_local Stacked st;
-	static thread_local std::vector<uint8_t> rcbuf;
-	rcbuf.resize(rdlen);
-	for(size_t i = 0; i < rdlen; i++) { uint8_t c = seq[rdlen - 1 - i]; rcbuf[i] = c > 3 ? 4 : (uint8_t)(3 - c); }
+	std::vector<Ed>& ed = sc.ed; Stacked& st = sc.st; std::vector<uint8_t>& rcbuf = sc.rcbuf; std::string& md = sc.md; std::string& cig = sc.cig;
+	bool have_rc = false;
+	// the reference sequence's name up to the first whitespace (SamConfig::printRefNameFromIndex)
 	for(uint64_t k = 0; k < nrep; k++) {
 		const bt2gpu_aln& a = al[buf[k].second];
 		const bool primary = (k == 0);
@@ -281,27 +303,39 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 		}
 		// AlnRes::initStacked: positions w.r.t. the left end of the aligned strand
 		if(!a.fw) invert_poss(ed.data(), ne, rdlen);
-		st.init(a.fw ? seq : rcbuf.data(), rdlen, ed.data(), ne);
+		// No gap among the edits (nine alignments in ten; an entry of the aliased buffer that is no edit at all -- type 0 -- only moves
+		// the read offset): the stacked alignment is a row of '=' and 'X' columns, left-alignment has nothing to move, the CIGAR is one
+		// M run, and MD:Z follows from the edits alone.  StackedAln::init and buildMdz walked over the edit list without the strings:
+		bool plain = true;
+		for(size_t i = 0; i < ne && plain; i++) plain = ed[i].type != BT2GPU_EDIT_READ_GAP && ed[i].type != BT2GPU_EDIT_REF_GAP;
+		md.clear(); cig.clear();
+		if(plain) {
+			size_t rdoff = 0, run = 0, cols = 0; bool mm_last = false, first_print = true;
+			for(size_t i = 0; i < ne; i++) {
+				const size_t pos = ed[i].pos;
+				if(rdoff < pos) { const size_t upto = std::min(pos, rdlen + 1024); run += upto - rdoff; rdoff = upto; }
+				if(ed[i].type == BT2GPU_EDIT_MM) {
+					if(run > 0) { put_int(md, (long long)run); cols += run; run = 0; first_print = false; mm_last = false; }
+					if(mm_last || first_print) md.push_back('0');
+					md.push_back((char)ed[i].chr);
+					first_print = false; mm_last = true; rdoff++; cols++;
+				}
+			}
+			if(rdoff < rdlen) run += rdlen - rdoff;
+			if(run > 0) { put_int(md, (long long)run); cols += run; mm_last = false; }
+			if(mm_last) md.push_back('0');
+			if(cols > 0) { put_int(cig, (long long)cols); cig.push_back('M'); }
+		} else {
+			if(!a.fw && !have_rc) {
+				rcbuf.resize(rdlen);
+				for(size_t i = 0; i < rdlen; i++) { uint8_t c = seq[rdlen - 1 - i]; rcbuf[i] = c > 3 ? 4 : (uint8_t)(3 - c); }
+				have_rc = true;
+			}
+			st.init(a.fw ? seq : rcbuf.data(), rdlen, ed.data(), ne);
+			st.leftAlign();
+			st.cigar(cig); st.mdz(md);
+		}
 		if(!a.fw) invert_poss(ed.data(), ne, rdlen);
-		st.leftAlign();
-		qname();
-		int fl = 0;
-		if(!primary) fl |= 256;
-		if(!a.fw) fl |= 16;
-		o.push_back('\t'); put_int(o, fl); o.push_back('\t');
-		if(a.tidx < job.refnames.size()) { // SamConfig::printRefNameFromIndex: up to the first whitespace
-			const std::string& nm = job.refnames[a.tidx];
-			for(size_t k = 0; k < nm.size(); k++) { if(isspace((unsigned char)nm[k])) break; o.push_back(nm[k]); }
-		} else o.push_back('*');
-		o.push_back('\t'); put_int(o, (long long)a.refoff + 1); o.push_back('\t');
-		put_int(o, mapq_v2(hasSec, best, secbest, scMin, scPer, primary, mhitsSet, false));
-		o.push_back('\t');
-		st.cigar(o);
-		o += "\t*\t0\t0\t";
-		seqqual(a.fw != 0);
-		o += "\tAS:i:"; put_int(o, a.score);
-		if(hasSec) { o += "\tXS:i:"; put_int(o, (long long)secbest); }
-		o += "\tXN:i:"; put_int(o, a.refns);
 		size_t num_mm = 0, num_go = 0, num_gx = 0;
 		for(size_t i = 0; i < ne; i++) {
 			if(ed[i].type == BT2GPU_EDIT_MM) num_mm++;
@@ -313,14 +347,38 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 				while(i < ne - 1 && ed[i + 1].pos == ed[i].pos + 1 && ed[i + 1].type == BT2GPU_EDIT_REF_GAP) { i++; num_gx++; }
 			}
 		}
-		o += "\tXM:i:"; put_int(o, (long long)num_mm);
-		o += "\tXO:i:"; put_int(o, (long long)num_go);
-		o += "\tXG:i:"; put_int(o, (long long)num_gx);
-		o += "\tNM:i:"; put_int(o, (long long)ne);
-		o += "\tMD:Z:"; st.mdz(o);
-		o += "\tYT:Z:UU";
-		if(opt.yfQuirk) o += "\tYF:Z:LN";
-		o.push_back('\n');
+		// the record, written through a pointer into room reserved for its longest possible form
+		const std::string* rn = a.tidx < job.refnames.size() ? &job.refnames[a.tidx] : nullptr;
+		const size_t at = o.size();
+		o.resize(at + 512 + std::min<size_t>(name_n, 255) + (rn ? rn->size() : 1) + 2 * rdlen + cig.size() + md.size());
+		Wr w{&o[at]};
+		for(size_t i = 0; i < name_n && i < 255; i++) { if(isspace((unsigned char)name[i])) break; w.c(name[i]); }
+		w.c('\t'); w.i((primary ? 0 : 256) | (a.fw ? 0 : 16)); w.c('\t');
+		if(rn) { for(size_t i = 0; i < rn->size(); i++) { if(isspace((unsigned char)(*rn)[i])) break; w.c((*rn)[i]); } } else w.c('*');
+		w.c('\t'); w.i((long long)a.refoff + 1); w.c('\t');
+		w.i(mapq_v2(hasSec, best, secbest, scMin, scPer, primary, mhitsSet, false));
+		w.c('\t'); w.s(cig.data(), cig.size()); w.lit("\t*\t0\t0\t");
+		if(rdlen == 0) w.lit("*\t*");
+		else {
+			if(a.fw) { for(size_t i = 0; i < rdlen; i++) w.p[i] = "ACGTN"[seq[i]]; }
+			else     { for(size_t i = 0; i < rdlen; i++) w.p[i] = "TGCAN"[seq[rdlen - 1 - i]]; }
+			w.p[rdlen] = '\t'; w.p += rdlen + 1;
+			if(a.fw) memcpy(w.p, qual, rdlen);
+			else     { for(size_t i = 0; i < rdlen; i++) w.p[i] = (char)qual[rdlen - 1 - i]; }
+			w.p += rdlen;
+		}
+		w.lit("\tAS:i:"); w.i(a.score);
+		if(hasSec) { w.lit("\tXS:i:"); w.i((long long)secbest); }
+		w.lit("\tXN:i:"); w.i(a.refns);
+		w.lit("\tXM:i:"); w.i((long long)num_mm);
+		w.lit("\tXO:i:"); w.i((long long)num_go);
+		w.lit("\tXG:i:"); w.i((long long)num_gx);
+		w.lit("\tNM:i:"); w.i((long long)ne);
+		w.lit("\tMD:Z:"); w.s(md.data(), md.size());
+		w.lit("\tYT:Z:UU");
+		if(opt.yfQuirk) w.lit("\tYF:Z:LN");
+		w.c('\n');
+		o.resize((size_t)(w.p - o.data()));
 	}
 }
 

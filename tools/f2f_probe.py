@@ -39,7 +39,20 @@ def main():
                     tp += t1 - t0; ta += t2 - t1; ts += t3 - t2
             print("serial, threads %s: %d reads  parse %.3f s (%.1f M/s)  align %.3f s (%.1f M/s)  sam %.3f s (%.1f M/s)" % (
                 threads, nr, tp, nr / tp / 1e6, ta, nr / ta / 1e6, ts, nr / ts / 1e6), flush=True)
+    # one range, looked at closely: the sink right after the aligner returned, then again on the same results
     job.set_threads(0, 0)
+    b, _ = job.fastq_range(fq, 0, chunk)
+    for rep in range(3):
+        res = gpu.align(b)
+        with open("/dev/null", "wb") as f:
+            ts = []
+            for k in range(3):
+                t0 = time.perf_counter(); job.sam_write(b, res, f, 1); ts.append((time.perf_counter() - t0) * 1e3)
+        time.sleep(0.2)
+        with open("/dev/null", "wb") as f:
+            t0 = time.perf_counter(); job.sam_write(b, res, f, 1); t_idle = (time.perf_counter() - t0) * 1e3
+        print("one range (%d reads): sink right after align %.1f ms, again %.1f ms, again %.1f ms, after 0.2 s idle %.1f ms" % (b.n, ts[0], ts[1], ts[2], t_idle), flush=True)
+    b.close()
     for out in (sam, "/dev/null"):
         for rep in range(2):
             st = {}

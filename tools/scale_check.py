@@ -55,6 +55,9 @@ def main():
     ap.add_argument("--seed", type=int, default=12346)
     ap.add_argument("--keep", action="store_true", help="keep the index and the FASTQ files")
     ap.add_argument("--no-reference", action="store_true", help="skip the reference binary (no parity sample): for runs under ncu")
+    ap.add_argument("--long", default=None, help="read lengths, comma separated (e.g. 250,500,750,1000: BASELINE configs[4]): equal shares of each, aligned by "
+                    "the long-read build (libbt2gpu_long.so) and, for the parity sample, by oracle/_ref/bowtie2-align-l-long (the -DENABLE_I16 reference "
+                    "with ALN_MAX_ROWS / ALN_MAX_COLS raised: not the reference as shipped)")
     args = ap.parse_args()
     global OPTS
     if args.opts:
@@ -98,24 +101,41 @@ def main():
 
     # ---- reads
     bench.REF_LEN = n_ref
-    reads = bench.simulate_reads(codes, args.reads, seed=3)
     fq_all = os.path.join(args.work, "scale_all.fq"); fq_s = os.path.join(args.work, "scale_sample.fq")
-    bench.write_fastq(fq_all, reads)
-    bench.write_fastq(fq_s, reads[: args.sample])
+    long_lens = [int(x) for x in args.long.split(",")] if args.long else None
+    ref_binary, job_opts, pmult = "bowtie2-align-l", OPTS, 100
+    if long_lens:
+        out["read_lengths"] = long_lens
+        ref_binary, job_opts, pmult = "bowtie2-align-l-long", OPTS + " --i16", 1   # (-p 1: that build's DP buffers are sized per read slot)
+        per, per_s, first = args.reads // len(long_lens), args.sample // len(long_lens), 0
+        for k, L in enumerate(long_lens):
+            bench.READ_LEN = L
+            part = bench.simulate_reads(codes, per, seed=3 + L)
+            bench.write_fastq(fq_all, part, first=first, mode="ab" if k else "wb")
+            bench.write_fastq(fq_s, part[:per_s], first=first, mode="ab" if k else "wb")
+            first += per
+        args.reads, args.sample = per * len(long_lens), per_s * len(long_lens)
+        out["reads"], out["sample"] = args.reads, args.sample
+        out["bases_per_read_mean"] = sum(long_lens) / len(long_lens)
+    else:
+        reads = bench.simulate_reads(codes, args.reads, seed=3)
+        bench.write_fastq(fq_all, reads)
+        bench.write_fastq(fq_s, reads[: args.sample])
 
     # ---- the reference binary on the sample
     sam_ref = os.path.join(args.work, "scale_ref.sam")
     want = None
     if not args.no_reference:
-        dt = run_ref("bowtie2-align-l", base, fq_s, sam_ref, threads, [])
+        dt = run_ref(ref_binary, base, fq_s, sam_ref, threads, [], pmult)
+        out["reference_binary"] = ref_binary
         out["reference_reads_per_s"] = round(args.sample / dt)
         want = sorted_records(open(sam_ref, "rb").read())
 
     # ---- this library on the sample
     t0 = time.time()
-    job = pkg.Job(base, OPTS)
+    job = pkg.Job(base, job_opts)
     out["host_index_load_s"] = round(time.time() - t0, 2)   # .bt2l files -> host arrays (libbt2host; the reference: Ebwt::loadIntoMemory)
-    gpu = pkg.GpuAligner(job, 0)
+    gpu = pkg.GpuAligner(job, 0, long_reads=bool(long_lens))
     out["create_s"] = round(time.time() - t0, 2)      # index load + upload + suffix-array expansion on the device
     out["create_info"] = gpu.create_info()
     batch = job.fastq(fq_s)
