@@ -767,7 +767,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		const size_t slotCells = fill_cell_bytes(BT2GPU_MAX_ROWS, 4);   // K = 4 holds every band of the default scoring scheme; a batch that needs more gets fewer slots
 		const size_t perSlot = sizeof(Problem) + slotCells + (size_t)BT2_PC_WORDS * 4;
 		uint32_t slots = es ? (uint32_t)atoi(es) : 262144u;
-		const size_t budget = (freeB / 20) * 9;
+		const size_t budget = std::min<size_t>((freeB / 20) * 9, (size_t)12 << 30);   // (the long-read build's slots are 137 KB each: 12 GB of them is 90 000 problems in flight)
 		if((size_t)slots * perSlot > budget) slots = (uint32_t)(budget / perSlot);
 		if(slots < 64) throw std::string("bt2gpu_create: not enough device memory for the DP problem slots");
 		c->nslots = slots; c->sampSlots = 2048;

@@ -29,6 +29,8 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, a
     to the aligner's own host threads when there are at least eight.
     start / end: byte range of the file to take (both at record starts): a shard of a multi-GPU job (reads shard by batch,
     every device holds a replica of the index, the per-shard SAM files are concatenated in shard order); header=False for shards > 0."""
+    if os.environ.get("BT2HOST_STREAM_CHUNK_MB"):
+        chunk_bytes = int(os.environ["BT2HOST_STREAM_CHUNK_MB"]) << 20
     if threads is None and os.environ.get("BT2HOST_STREAM_THREADS"):      # "reader,sink"
         threads = tuple(int(x) for x in os.environ["BT2HOST_STREAM_THREADS"].split(","))
     if threads is None:

@@ -35,10 +35,18 @@ CASES = {
 
 # Reads longer than the reference's 160-row limit: the golden SAM comes from oracle/_ref/bowtie2-align-l-long, the
 # -DENABLE_I16 reference with ALN_MAX_ROWS / ALN_MAX_COLS raised in a scratch copy (oracle/build_ref.sh) -- not the reference as shipped.
+# 161..255 bp is where that binary is a coherent oracle: its seed layer keeps the read length and the seed offsets in 8-bit fields
+# (aligner_seed.h:679-683, 1226-1230), so beyond 255 bp it cuts seeds from (offset mod 256) and frames them on the wrong diagonal.  The
+# restatement and the CUDA path use the offsets as they are; on the 250/600/1000 bp set below the SAM still comes out the same (the
+# wrapped seeds only add failed extensions), at scale ~1 % of such reads differ.
 CASES_LONG = {
+    "synL255_i16": ("syn", "synL255", "--i16", "synL255_i16.sam"),
+    "synL255_k3_sens": ("syn", "synL255", "--i16 --sensitive -k 3", "synL255_k3_sens.sam"),
     "synL_mix_i16": ("syn", "synLmix", "--i16", "synL_mix_i16.sam"),
     "synL_mix_k3_sens": ("syn", "synLmix", "--i16 --sensitive -k 3", "synL_mix_k3_sens.sam"),
 }
+LONG_SETS = {"synLmix": ((250, 150, 21, 0.01), (600, 120, 22, 0.02), (1000, 120, 23, 0.02)),
+             "synL255": ((170, 400, 31, 0.02), (200, 400, 32, 0.02), (230, 400, 33, 0.03), (255, 400, 34, 0.02))}
 
 
 def _run(cmd):
@@ -86,10 +94,10 @@ def reads_path(name):
     p = os.path.join(WORK, name + ".fq")
     if os.path.exists(p):
         return p
-    if name == "synLmix":                          # 250, 600 and 1000 bp reads, names made unique per length
+    if name in LONG_SETS:                          # reads of several lengths, names made unique per length
         index_base("syn")
         with open(p + ".tmp", "w") as out:
-            for L, nr, seed, subst in ((250, 150, 21, 0.01), (600, 120, 22, 0.02), (1000, 120, 23, 0.02)):
+            for L, nr, seed, subst in LONG_SETS[name]:
                 part = os.path.join(WORK, "synL%d.fq" % L)
                 gen(["reads", os.path.join(WORK, "syn.fa"), part, nr, L, "--seed", seed, "--subst", subst])
                 for i, line in enumerate(open(part)):

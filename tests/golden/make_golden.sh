@@ -56,5 +56,13 @@ done
 runL() { OMP_NUM_THREADS=4 "$B/bowtie2-align-l-long" -x "$2" -U "$3" -S "$T/o.sam" -p 1 $4 2>/dev/null; grep -v '^@' "$T/o.sam" | LC_ALL=C sort > "$HERE/$1.sam"; }
 runL synL_mix_i16     "$T/syn" "$T/synLmix.fq" ""
 runL synL_mix_k3_sens "$T/syn" "$T/synLmix.fq" "--sensitive -k 3"
+# 170..255 bp: the lengths at which that binary is a coherent oracle (its seed layer keeps read length and seed offsets in 8 bits)
+: > "$T/synL255.fq"
+for spec in "170 400 31 0.02" "200 400 32 0.02" "230 400 33 0.03" "255 400 34 0.02"; do set -- $spec
+  python "$ROOT/tools/gen_data.py" reads "$T/syn.fa" "$T/synL$1.fq" $2 $1 --seed $3 --subst $4
+  awk -v L=$1 'NR%4==1{sub(/^@/,"@L" L "_")}1' "$T/synL$1.fq" >> "$T/synL255.fq"
+done
+runL synL255_i16     "$T/syn" "$T/synL255.fq" ""
+runL synL255_k3_sens "$T/syn" "$T/synL255.fq" "--sensitive -k 3"
 rm -rf "$T"
 ls -la "$HERE"

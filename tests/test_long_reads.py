@@ -1,7 +1,11 @@
 """Reads beyond the reference's 160-row limit (BASELINE configs[4]): the long-read build -- the same sources with
 ALN_MAX_ROWS / ALN_MAX_COLS (BT2GPU_MAX_ROWS / BT2GPU_MAX_COLS) raised to 1000 / 1072 -- against oracle D: the golden SAM of
 oracle/_ref/bowtie2-align-l-long (the reference with those two constants raised in a scratch copy; NOT the reference as shipped, whose
-own answer for these reads is "unaligned") and the restatement compiled with the same constants (oracle/liboracle_long.so)."""
+own answer for these reads is "unaligned") and the restatement compiled with the same constants (oracle/liboracle_long.so).
+That binary is a coherent oracle up to 255 bp (cases synL255_*: 170 / 200 / 230 / 255 bp): its seed layer keeps the read length and the
+seed offsets in 8-bit fields (aligner_seed.h:679-683, 1226-1230), so a seed at read offset >= 256 is cut from offset mod 256 and framed
+on the wrong diagonal.  The restatement and the CUDA path take the offsets as they are; the 250 / 600 / 1000 bp cases (synL_mix_*) still
+print the same SAM (the wrapped seeds only add extensions that fail), at scale about 1 % of the reads beyond 255 bp differ."""
 import os
 import subprocess
 import pytest
@@ -20,7 +24,7 @@ def test_long_oracle_matches_constants_raised_reference(name):
     got = common.sorted_records(job.sam(batch, orc.align(batch), mode=1))
     assert got == common.golden_records(gold)
     lens = {len(l.split("\t")[9]) for l in got if not int(l.split("\t")[1]) & 4}
-    assert {250, 600, 1000} <= lens                    # reads of every length aligned
+    assert lens >= ({250, 600, 1000} if "mix" in name else {170, 200, 230, 255})   # reads of every length aligned
     orc.close()
     # the build with the reference's own limits leaves every one of them unaligned (SwAligner::initRead fails; F13)
     short = common.Oracle(job)
