@@ -420,6 +420,8 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = importlib.import_module("omp-bowtie2-prime_b200")
+    if os.environ.get("BT2_BENCH_PINNED", "1") != "0":
+        pkg.use_pinned_batches()      # the host library's batch arrays are page-locked: the file-to-file pipeline's aligner call copies them straight up
 
     if rank == 0:
         base, codes = make_reference()

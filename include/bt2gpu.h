@@ -308,6 +308,10 @@ int bt2gpu_get_counters(bt2gpu_ctx *ctx, bt2gpu_counters *c);
 int bt2gpu_reset_counters(bt2gpu_ctx *ctx);
 const char *bt2gpu_last_error(const bt2gpu_ctx *ctx);
 void bt2gpu_destroy(bt2gpu_ctx *ctx);
+/* Page-locked host memory (cudaMallocHost / cudaFreeHost) for a caller's input arrays: bt2gpu_align_batch copies from it without a
+ * staging pass.  NULL when it cannot be had.  (bt2host_set_array_allocator takes this pair.) */
+void *bt2gpu_host_alloc(size_t bytes);
+void bt2gpu_host_free(void *p);
 int bt2gpu_abi_version(void);
 int bt2gpu_max_rows(void);   /* BT2GPU_MAX_ROWS / BT2GPU_MAX_COLS this library was built with */
 int bt2gpu_max_cols(void);

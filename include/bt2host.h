@@ -96,6 +96,10 @@ void bt2host_job_metrics(const bt2host_job *job, uint64_t out[4]);
 /* OpenMP threads the FASTQ reader and the SAM sink of this job take (0: all there are, the default).  A pipeline that runs the
  * two at the same time on neighbouring batches (stream.py) splits the cores between them instead of letting both ask for all. */
 void bt2host_job_set_threads(bt2host_job *job, int reader_threads, int sink_threads);
+/* Where the batches' large arrays (bases, qualities) are allocated from now on: e.g. libbt2gpu's bt2gpu_host_alloc / bt2gpu_host_free
+ * (page-locked memory: bt2gpu_align_batch then copies to the device without a staging pass).  Process-wide; to be called once, before
+ * the first batch is made (a second call, or a call after batches exist, is refused with -1 / undefined respectively). */
+int bt2host_set_array_allocator(void *(*alloc)(size_t), void (*release)(void *));
 
 #ifdef __cplusplus
 }

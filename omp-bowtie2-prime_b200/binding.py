@@ -7,7 +7,17 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 
 
 def lib_paths():
-    return {"gpu": os.path.join(_HERE, "libbt2gpu.so"), "host": os.path.join(_HERE, "libbt2host.so")}
+    """BT2GPU_LIB: another build of libbt2gpu.so to load instead (kernel experiments)."""
+    return {"gpu": os.environ.get("BT2GPU_LIB") or os.path.join(_HERE, "libbt2gpu.so"), "host": os.path.join(_HERE, "libbt2host.so")}
+
+
+def use_pinned_batches():
+    """From now on the host library allocates the batches' base / quality arrays with libbt2gpu's bt2gpu_host_alloc (page-locked memory):
+    bt2gpu_align_batch copies them to the device without a staging pass.  Needs a CUDA device; process-wide, once, before the first batch."""
+    h, g = load_host(), load_gpu()
+    g.bt2gpu_host_alloc.restype = C.c_void_p
+    h.bt2host_set_array_allocator.argtypes = [C.c_void_p, C.c_void_p]
+    return h.bt2host_set_array_allocator(C.cast(g.bt2gpu_host_alloc, C.c_void_p), C.cast(g.bt2gpu_host_free, C.c_void_p)) == 0
 
 
 class bt2gpu_index(C.Structure):

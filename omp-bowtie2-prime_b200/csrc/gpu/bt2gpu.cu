@@ -767,7 +767,7 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		const size_t slotCells = fill_cell_bytes(BT2GPU_MAX_ROWS, 4);   // K = 4 holds every band of the default scoring scheme; a batch that needs more gets fewer slots
 		const size_t perSlot = sizeof(Problem) + slotCells + (size_t)BT2_PC_WORDS * 4;
 		uint32_t slots = es ? (uint32_t)atoi(es) : 262144u;
-		const size_t budget = std::min<size_t>((freeB / 20) * 9, (size_t)12 << 30);   // (the long-read build's slots are 137 KB each: 12 GB of them is 90 000 problems in flight)
+		const size_t budget = std::min<size_t>((freeB / 20) * 9, (size_t)32 << 30);   // (the long-read build's slots are 137 KB each: 32 GB of them is 245 000 problems in flight)
 		if((size_t)slots * perSlot > budget) slots = (uint32_t)(budget / perSlot);
 		if(slots < 64) throw std::string("bt2gpu_create: not enough device memory for the DP problem slots");
 		c->nslots = slots; c->sampSlots = 2048;
@@ -927,6 +927,8 @@ int bt2gpu_get_create_info(const bt2gpu_ctx* ctx, double ms[4], uint64_t bytes[4
 }
 int bt2gpu_get_counters(bt2gpu_ctx* ctx, bt2gpu_counters* c) { if(!ctx || !c) return -1; *c = ctx->ctr; return 0; }
 int bt2gpu_reset_counters(bt2gpu_ctx* ctx) { if(!ctx) return -1; memset(&ctx->ctr, 0, sizeof(ctx->ctr)); return 0; }
+void* bt2gpu_host_alloc(size_t bytes) { void* p = nullptr; if(cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; } return p; }
+void bt2gpu_host_free(void* p) { if(p && cudaFreeHost(p) != cudaSuccess) cudaGetLastError(); }
 int bt2gpu_max_rows(void) { return BT2GPU_MAX_ROWS; }
 int bt2gpu_max_cols(void) { return BT2GPU_MAX_COLS; }
 const char* bt2gpu_last_error(const bt2gpu_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }

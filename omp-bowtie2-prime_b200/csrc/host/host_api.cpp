@@ -19,6 +19,8 @@ void sam_for_read(const Job& job, uint64_t met[4], const Batch& b, const bt2gpu_
 std::string sam_header(const Job& job);
 }
 
+namespace bt2host { ArrayAllocator g_array_allocator = { nullptr, nullptr }; }
+
 static void set_err(char* err, size_t errlen, const std::string& msg) {
 	if(err && errlen) { snprintf(err, errlen, "%s", msg.c_str()); }
 }
@@ -207,6 +209,12 @@ int bt2host_sam_write(const bt2host_job* job, const bt2host_batch* b, const bt2g
 	return ok ? 0 : -1;
 }
 void bt2host_free(void* p) { free(p); }
+int bt2host_set_array_allocator(void* (*alloc)(size_t), void (*release)(void*)) {
+	static bool fixed = false;               // once: arrays remember nothing about who allocated them
+	if(fixed || !alloc || !release) return -1;
+	bt2host::g_array_allocator.release = release; bt2host::g_array_allocator.alloc = alloc; fixed = true;
+	return 0;
+}
 void bt2host_job_set_threads(bt2host_job* job, int reader_threads, int sink_threads) {
 	job->j.reader_threads = reader_threads > 0 ? reader_threads : 0; job->j.sink_threads = sink_threads > 0 ? sink_threads : 0;
 }

@@ -9,6 +9,7 @@
 #include <mutex>
 #include <utility>
 #include <new>
+#include <cstdlib>
 #include <cmath>
 #include <limits>
 #include "bt2host.h"
@@ -75,10 +76,27 @@ struct Job {
 };
 
 // vector storage that is not zero-filled by resize(): the readers overwrite every element (and do so on several threads)
-template<typename T> struct NoInitAlloc : std::allocator<T> {
+// Where the large per-batch arrays (bases, qualities) come from: malloc, or a pair of functions the caller registered once with
+// bt2host_set_array_allocator -- libbt2gpu's bt2gpu_host_alloc / bt2gpu_host_free hand out page-locked memory, from which
+// bt2gpu_align_batch copies to the device without a staging pass.  (Process-wide, set before the first batch; this library itself
+// stays free of CUDA.)
+struct ArrayAllocator { void* (*alloc)(size_t); void (*release)(void*); };
+extern ArrayAllocator g_array_allocator;
+template<typename T> struct NoInitAlloc {
+	typedef T value_type;
+	NoInitAlloc() = default;
+	template<typename U> NoInitAlloc(const NoInitAlloc<U>&) {}
 	template<typename U> struct rebind { typedef NoInitAlloc<U> other; };
+	T* allocate(size_t n) {
+		void* p = g_array_allocator.alloc ? g_array_allocator.alloc(n * sizeof(T)) : malloc(n * sizeof(T));
+		if(!p) throw std::bad_alloc();
+		return (T*)p;
+	}
+	void deallocate(T* p, size_t) { if(g_array_allocator.alloc) g_array_allocator.release(p); else free(p); }
 	template<typename U> void construct(U* p) noexcept { ::new((void*)p) U; }
 	template<typename U, typename... A> void construct(U* p, A&&... a) { ::new((void*)p) U(std::forward<A>(a)...); }
+	template<typename U> bool operator==(const NoInitAlloc<U>&) const { return true; }
+	template<typename U> bool operator!=(const NoInitAlloc<U>&) const { return false; }
 };
 typedef std::vector<uint8_t, NoInitAlloc<uint8_t>> ByteVec;
 

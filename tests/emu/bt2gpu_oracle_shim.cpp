@@ -22,6 +22,8 @@ struct bt2gpu_ctx {
 
 extern "C" {
 int bt2gpu_abi_version(void) { return BT2GPU_ABI_VERSION; }
+void* bt2gpu_host_alloc(size_t bytes) { return malloc(bytes ? bytes : 1); }
+void bt2gpu_host_free(void* p) { free(p); }
 int bt2gpu_max_rows(void) { return BT2GPU_MAX_ROWS; }
 int bt2gpu_max_cols(void) { return BT2GPU_MAX_COLS; }
 bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* ix, const bt2gpu_ref* rf, const bt2gpu_params* p, int, char* err, size_t errlen) {
