@@ -58,7 +58,10 @@ struct FillArgs {
 #define BT2_FILL_DYNSMEM 0
 #endif
 #ifndef BT2_FILL_UNROLL
-#define BT2_FILL_UNROLL 1              // iterations of the sweep per loop trip (a divisor of 16 / K)
+#define BT2_FILL_UNROLL 4              // iterations of the sweep per loop trip (a divisor of 16 / K; at most the 16 / K of a chunk).  Measured for
+                                       // K = 4 (B200, 1 M x 150 bp): 1 -> 15.6 ms, 2 -> 14.35 ms, 4 -> 14.05 ms (the chunk's shift register and the rotating
+                                       // state become register renaming); while the body still held the masked variant and the one-by-one prologue,
+                                       // 4 iterations (1 430 instructions) did not fit the instruction cache and 1 was the fastest
 #endif
 #define BT2_FILL_ROWPAD BT2_SKEW                       // virtual rows before row 0 (and rows past the end the last lanes touch)
 #define BT2_FILL_NROW (BT2_FILL_ROWPAD + BT2GPU_MAX_ROWS + BT2_SKEW + 4)
@@ -272,8 +275,7 @@ __device__ __forceinline__ void fill_sweep(int i0, const int i1, FillSet<K>& S0,
 	constexpr int UNR = BT2_FILL_UNROLL < PER ? BT2_FILL_UNROLL : PER;
 	const uint32_t E_EDGE = BT2_FL_BASE | ((uint32_t)(CF_EO | CF_EX) * 0x00010001u), F_EDGE = BT2_FL_BASE | ((uint32_t)(CF_FO | CF_FX) * 0x00010001u);
 	for(; i0 < i1; i0 += PER) {
-		// (not unrolled by default: the body of one iteration is ~350 instructions; unrolled over the chunk the loop outgrew the
-		// instruction cache -- ncu r2: 2.9 stalled warps per issue waiting for instructions, issue slots 47 % busy)
+		// (BT2_FILL_UNROLL iterations per trip; see there for what the instruction cache made of the alternatives)
 		#pragma unroll UNR
 		for(int u = 0; u < PER; u++) {
 			const int i = i0 + u;

@@ -73,9 +73,9 @@ bt2host_batch* bt2host_batch_from_arrays(const bt2host_job* job, uint32_t n, con
 }
 void bt2host_batch_destroy(bt2host_batch* b) {
 	if(!b) return;
-	if(std::shared_ptr<bt2host::BatchPool> pl = std::move(b->b.pool)) {   // a range reader's batch: keep up to four sets of arrays for the next ranges
+	if(std::shared_ptr<bt2host::BatchPool> pl = std::move(b->b.pool)) {   // a range reader's batch: keep up to eight sets of arrays for the next ranges (a pipeline has six batches in flight)
 		std::lock_guard<std::mutex> g(pl->mu);
-		if(pl->idle.size() < 4) { pl->idle.push_back(b); return; }
+		if(pl->idle.size() < 8) { pl->idle.push_back(b); return; }
 	}
 	delete b;
 }
