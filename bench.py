@@ -368,14 +368,16 @@ def file_to_file_sharded(pkg, job, ascii_reads, device, rank, world, dist, torch
     ends = [int(x) for x in ends.tolist()]
     start, end = (ends[rank - 1] if rank else 0), ends[rank]
     part = os.path.join(tmp, "bt2gpu_bench.sam.%d" % rank)
+    share = max(2, cpu_cores() // world)           # the ranks of one box split its cores
+    thr = (max(1, share * 3 // 8), max(1, share - share * 3 // 8))
     al = [pkg.GpuAligner(job, device)]
     try:
-        stream.fastq_to_sam(job, fq, part, device, aligners=al, start=start, end=end, header=rank == 0)     # warm-up
+        stream.fastq_to_sam(job, fq, part, device, aligners=al, start=start, end=end, header=rank == 0, threads=thr)     # warm-up
         best = None
         for _ in range(2):
             dist.barrier(); torch.cuda.synchronize()
             t0 = time.time()
-            nr, nb = stream.fastq_to_sam(job, fq, part, device, aligners=al, start=start, end=end, header=rank == 0)
+            nr, nb = stream.fastq_to_sam(job, fq, part, device, aligners=al, start=start, end=end, header=rank == 0, threads=thr)
             dist.barrier()
             dt = torch.tensor([time.time() - t0], dtype=torch.float64, device="cuda")
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
@@ -383,7 +385,7 @@ def file_to_file_sharded(pkg, job, ascii_reads, device, rank, world, dist, torch
         tot = torch.tensor([nr, nb], dtype=torch.int64, device="cuda")
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
         return {"value": int(tot[0].item()) / best, "unit": "reads/s", "reads": int(tot[0].item()), "fastq_bytes": ends[-1], "sam_bytes": int(tot[1].item()),
-                "seconds": best, "where": tmp, "shards": world, "host_cores": cpu_cores(),
+                "seconds": best, "where": tmp, "shards": world, "host_cores": cpu_cores(), "reader_sink_threads_per_rank": list(thr),
                 "note": "one FASTQ file, one byte range per rank -> parse -> bt2gpu_align_batch -> SAM formatting -> one SAM part per rank (concatenated in shard "
                         "order); limited by the host cores all ranks share for parsing and formatting"}
     finally:

@@ -766,14 +766,17 @@ bt2gpu_ctx* bt2gpu_create(const bt2gpu_index* hix, const bt2gpu_ref* hrf, const 
 		size_t freeB = 0, totB = 0; CK(cudaMemGetInfo(&freeB, &totB));
 		const size_t slotCells = fill_cell_bytes(BT2GPU_MAX_ROWS, 4);   // K = 4 holds every band of the default scoring scheme; a batch that needs more gets fewer slots
 		const size_t perSlot = sizeof(Problem) + slotCells + (size_t)BT2_PC_WORDS * 4;
-		uint32_t slots = es ? (uint32_t)atoi(es) : 262144u;
+		// 1 Mi slots (24 GB of cell flags at 150 bp): an extension pass over a 1 M-read batch is then ONE launch each of k_step / K_fill / k_bt,
+		// and k_bt's persistent lanes take 9 problems each instead of 2.3 -- its tail, when most lanes have run out of problems, cost 2.4 ms of
+		// 14.1 per 1 M reads with 262 144 slots (measured: 35.8 / 34.3 / 33.4 ms per step with 256 Ki / 512 Ki / 1 Mi slots)
+		uint32_t slots = es ? (uint32_t)atoi(es) : 1048576u;
 		const size_t budget = std::min<size_t>((freeB / 20) * 9, (size_t)32 << 30);   // (the long-read build's slots are 137 KB each: 32 GB of them is 245 000 problems in flight)
 		if((size_t)slots * perSlot > budget) slots = (uint32_t)(budget / perSlot);
 		if(slots < 64) throw std::string("bt2gpu_create: not enough device memory for the DP problem slots");
 		c->nslots = slots; c->sampSlots = 2048;
 		c->maxBatch = eb ? (uint32_t)atoi(eb) : (1u << 20);
 		if(c->maxBatch < 1) c->maxBatch = 1;
-		{ const char* ep = getenv("BT2GPU_PIPE"); c->pipeChunk = ep ? (uint32_t)std::max(1, atoi(ep)) : 262144u; }
+		{ const char* ep = getenv("BT2GPU_PIPE"); c->pipeChunk = ep ? (uint32_t)std::max(1, atoi(ep)) : 524288u; }   // (measured through the C-ABI at 1 M reads: 24.6 M reads/s with 262 144, 25.8 M with 524 288)
 		c->probs.ensure((size_t)slots * sizeof(Problem)); c->cells.ensure((size_t)slots * slotCells);
 		c->pcache.ensure((size_t)slots * BT2_PC_WORDS * 4);
 		c->counters.ensure(C_N * 4); c->stats.ensure(32 * 8); c->pooltops.ensure(16); c->poolerr.ensure(4);
