@@ -181,6 +181,34 @@ BT2_HD void ref_masks(const DevRef& rf, uint8_t* dst, uint64_t tidx, uint64_t to
 	}
 	uint32_t k = 0;
 	const uint64_t end = toff + count;
+#if defined(__CUDA_ARCH__)
+	// The usual window lies inside one record: 16 bases per step -- two words of the packed text funnel-shifted to the window's phase, four
+	// codes -> four mask bytes by one PRMT (byte c of 0x08040201 = 1 << c), one 16-byte store.  (The byte loop below, 200 loads and 200
+	// one-byte stores per problem, was most of k_step.)  Writes up to 15 bytes past `count` inside the caller's array: Problem::rf holds
+	// a multiple of 16 bytes beyond every window; nobody reads past the window.  upload() pads the packed text by 16 bytes.
+	static_assert((BT2GPU_MAX_COLS + 15) / 16 * 16 <= BT2GPU_MAX_COLS + 8, "a window rounded up to 16 masks fits Problem::rf");
+	if(lo < last && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0u) {
+		const uint64_t gapEnd = rf.rec_tstart[lo] + rf.rec_off[lo], recEnd = gapEnd + rf.rec_len[lo];
+		if(toff >= gapEnd && end <= recEnd) {
+			const uint32_t* __restrict__ w = reinterpret_cast<const uint32_t*>(rf.buf);
+			const uint64_t bi = rf.rec_cum[lo] + (toff - gapEnd);
+			const uint32_t sh = (uint32_t)(bi & 15u) * 2u;
+			uint64_t wi = bi >> 4;
+			uint32_t w0 = w[wi];
+			for(; k < count; k += 16, wi++) {
+				const uint32_t w1 = sh ? w[wi + 1] : 0u;
+				const uint32_t codes = __funnelshift_r(w0, w1, sh);
+				uint4 m;
+				#define BT2_M4(q) __byte_perm(0x08040201u, 0u, ((codes >> (8 * (q))) & 3u) | (((codes >> (8 * (q) + 2)) & 3u) << 4) | (((codes >> (8 * (q) + 4)) & 3u) << 8) | (((codes >> (8 * (q) + 6)) & 3u) << 12))
+				m.x = BT2_M4(0); m.y = BT2_M4(1); m.z = BT2_M4(2); m.w = BT2_M4(3);
+				#undef BT2_M4
+				*reinterpret_cast<uint4*>(dst + k) = m;
+				w0 = sh ? w1 : w[wi + 1];
+			}
+			return;
+		}
+	}
+#endif
 	for(uint64_t r = lo; r < last && k < count; r++) {
 		const uint64_t gapEnd = rf.rec_tstart[r] + rf.rec_off[r];
 		const uint64_t recEnd = gapEnd + rf.rec_len[r];
