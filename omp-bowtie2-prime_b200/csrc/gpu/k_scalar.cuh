@@ -173,10 +173,10 @@ __global__ void __launch_bounds__(128, BT2_STEP_BLOCKS_PER_SM) k_step(const DevP
 
 #define BT2_BT_SPIN_LIMIT (1u << 22)
 #ifndef BT2_BT_POST_MIN
-#define BT2_BT_POST_MIN 8   // lanes that must want the rare paths before the warp takes them while others still walk
-#endif
-#ifndef BT2_BT_DONE_MIN
-#define BT2_BT_DONE_MIN 8
+#define BT2_BT_POST_MIN 16  // lanes that must want the rare paths before the warp takes them while others still walk
+#endif                      // (k_bt per 1 M reads with POST_MIN / DONE_MIN = 4 / 4: 13.4 ms, 8 / 8: 11.7, 16 / 16: 11.2, 24 / 24: 11.2, 16 / 4: 13.9 --
+#ifndef BT2_BT_DONE_MIN     //  the fetch of a new problem is a chain of dependent global loads, best paid by many lanes at once)
+#define BT2_BT_DONE_MIN 16
 #endif
 #if BT2GPU_MAX_ROWS > 160      // the long-read build: a lane's copy of its problem's characters is ~1 KB of shared memory
 #ifndef BT2_BT_THREADS
