@@ -87,12 +87,15 @@ template<typename T> struct NoInitAlloc {
 	NoInitAlloc() = default;
 	template<typename U> NoInitAlloc(const NoInitAlloc<U>&) {}
 	template<typename U> struct rebind { typedef NoInitAlloc<U> other; };
+	// (a 64-byte header in front of every array remembers who handed it out: arrays made before the hook was set go back to free())
 	T* allocate(size_t n) {
-		void* p = g_array_allocator.alloc ? g_array_allocator.alloc(n * sizeof(T)) : malloc(n * sizeof(T));
+		const bool hook = g_array_allocator.alloc != nullptr;
+		char* p = (char*)(hook ? g_array_allocator.alloc(n * sizeof(T) + 64) : malloc(n * sizeof(T) + 64));
 		if(!p) throw std::bad_alloc();
-		return (T*)p;
+		*(uint64_t*)p = hook ? 1u : 0u;
+		return (T*)(p + 64);
 	}
-	void deallocate(T* p, size_t) { if(g_array_allocator.alloc) g_array_allocator.release(p); else free(p); }
+	void deallocate(T* q, size_t) { char* p = (char*)q - 64; if(*(uint64_t*)p) g_array_allocator.release(p); else free(p); }
 	template<typename U> void construct(U* p) noexcept { ::new((void*)p) U; }
 	template<typename U, typename... A> void construct(U* p, A&&... a) { ::new((void*)p) U(std::forward<A>(a)...); }
 	template<typename U> bool operator==(const NoInitAlloc<U>&) const { return true; }

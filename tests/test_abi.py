@@ -175,3 +175,30 @@ def test_fastq_ranges_equal_whole_file():
         assert names == [whole.name(i) for i in range(rw.n)]
     with pytest.raises(RuntimeError, match="longer than the read range"):
         job.fastq_range(src, 0, 20)
+
+
+def test_array_allocator_hook_and_thread_split():
+    """bt2host_set_array_allocator: the batches' base / quality arrays come from the caller's pair of functions (libbt2gpu's page-locked
+    allocator in production; libc's malloc / free here), once per process; bt2host_job_set_threads is accepted and changes no result"""
+    import common
+    from common import pkg
+    if not common.have_builder():
+        import pytest
+        pytest.skip("no builder")
+    h = pkg.load_host()
+    libc = ctypes.CDLL(None)
+    h.bt2host_set_array_allocator.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    job = pkg.Job(common.index_base("lambda"), "")
+    before = job.fastq(common.reads_path("lambda_reads_1k"))
+    rc = h.bt2host_set_array_allocator(ctypes.cast(libc.malloc, ctypes.c_void_p), ctypes.cast(libc.free, ctypes.c_void_p))
+    assert rc in (0, -1)                                   # (-1: another test of this process registered one already)
+    assert h.bt2host_set_array_allocator(ctypes.cast(libc.malloc, ctypes.c_void_p), ctypes.cast(libc.free, ctypes.c_void_p)) == -1
+    assert h.bt2host_set_array_allocator(None, None) == -1
+    job.set_threads(2, 3)
+    after = job.fastq(common.reads_path("lambda_reads_1k"))
+    n = before.nbases()
+    a = ctypes.string_at(before.reads.contents.seq, n); b = ctypes.string_at(after.reads.contents.seq, n)
+    assert a == b and after.n == before.n == 1000
+    job.set_threads(0, 0)
+    after.close(); job.close()     # (`before` was allocated by malloc before the hook changed hands and is freed by free: same functions)
+    before.close()
