@@ -178,13 +178,10 @@ __global__ void __launch_bounds__(128, BT2_STEP_BLOCKS_PER_SM) k_step(const DevP
 #ifndef BT2_BT_DONE_MIN     //  the fetch of a new problem is a chain of dependent global loads, best paid by many lanes at once)
 #define BT2_BT_DONE_MIN 16
 #endif
-#if BT2GPU_MAX_ROWS > 160      // the long-read build: a lane's copy of its problem's characters is ~1 KB of shared memory
-#ifndef BT2_BT_THREADS
-#define BT2_BT_THREADS 32
-#endif
-#ifndef BT2_BT_BLOCKS_PER_SM
-#define BT2_BT_BLOCKS_PER_SM 5
-#endif
+#if BT2GPU_MAX_ROWS > 160      // the long-read build: a lane's copy of its problem's characters would be ~1 KB of shared memory;
+#define BT2_BT_PC_GLOBAL 1     // it reads them where K_fill left them instead (two L1-cached loads per backtrace cell)
+#else
+#define BT2_BT_PC_GLOBAL 0
 #endif
 #ifndef BT2_BT_THREADS
 #define BT2_BT_THREADS 128
@@ -203,10 +200,16 @@ __global__ void __launch_bounds__(128, BT2_STEP_BLOCKS_PER_SM) k_step(const DevP
 // [j * BT2_BT_THREADS + t]: conflict-free whatever j the lanes ask for) and its two cell chunks.
 __global__ void __launch_bounds__(BT2_BT_THREADS, BT2_BT_BLOCKS_PER_SM) k_bt(const __grid_constant__ BtCtx cx, uint32_t count,
                      uint32_t* task, uint32_t* next_list, uint32_t* next_cnt, uint32_t* roundend_list, uint32_t* roundend_cnt) {
+#if !BT2_BT_PC_GLOBAL
 	__shared__ uint32_t pcs[BT2_PC_WORDS * BT2_BT_THREADS];
+#endif
 	__shared__ __align__(16) uint8_t chunks[4 * 16 * BT2_BT_THREADS];   // two cell chunks and two candidate groups per lane
 	BtMachine m;
+#if BT2_BT_PC_GLOBAL
+	m.pc = cx.pcache; m.pcs = 1;
+#else
 	m.pc = pcs + threadIdx.x; m.pcs = BT2_BT_THREADS;
+#endif
 	m.cbuf = chunks + 16 * threadIdx.x; m.cstride = 16 * BT2_BT_THREADS; m.cbuf_sa = (uint32_t)__cvta_generic_to_shared(m.cbuf);
 	m.phase = BP_DONE; m.result = BT_CONTINUE; m.ct = CT_H;
 	bool have = false, drained = false;
@@ -239,6 +242,9 @@ __global__ void __launch_bounds__(BT2_BT_THREADS, BT2_BT_BLOCKS_PER_SM) k_bt(con
 					const uint32_t rd = cx.probs[j].read;
 					if(rd == BT2_NIL) continue;
 					m.slot = j; m.read = rd;
+#if BT2_BT_PC_GLOBAL
+					m.pc = cx.pcache + (size_t)j * BT2_PC_WORDS;
+#else
 					const uint4* src = reinterpret_cast<const uint4*>(cx.pcache + (size_t)j * BT2_PC_WORDS);
 					#pragma unroll
 					for(int q = 0; q < BT2_PC_WORDS / 4; q++) {
@@ -246,6 +252,7 @@ __global__ void __launch_bounds__(BT2_BT_THREADS, BT2_BT_BLOCKS_PER_SM) k_bt(con
 						pcs[(4 * q + 0) * BT2_BT_THREADS + threadIdx.x] = w.x; pcs[(4 * q + 1) * BT2_BT_THREADS + threadIdx.x] = w.y;
 						pcs[(4 * q + 2) * BT2_BT_THREADS + threadIdx.x] = w.z; pcs[(4 * q + 3) * BT2_BT_THREADS + threadIdx.x] = w.w;
 					}
+#endif
 					m.begin(cx);
 					have = true; spins = 0;
 				}

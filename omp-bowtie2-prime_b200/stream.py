@@ -7,6 +7,7 @@ One context does it: a context keeps two sets of result arrays and successive bt
 (include/bt2gpu.h), so the sink can still be reading batch i while batch i+1 is aligned; batch i+2 waits for the sink."""
 import os
 import queue
+import stat
 import threading
 import time
 
@@ -21,12 +22,15 @@ def _cores():
 
 
 def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, aligners=None, start=0, end=None, header=True, stats=None,
-                 threads=None):
+                 threads=None, preallocate=None):
     """Returns (reads, bytes written).  `aligners`: a list with the GpuAligner of `job` to reuse (else one is created and closed here;
     two objects are taken alternately, for aligners whose results last only until their next call).
     stats: a dict that receives the seconds each stage was busy ("parse", "align", "sam": they overlap) and the number of ranges.
     threads: (reader, sink) OpenMP threads; default: the cores split 3 : 5 (formatting and writing SAM is the heavier stage), two left
     to the aligner's own host threads when there are at least eight.
+    preallocate: reserve the output file's blocks ahead of the sink (posix_fallocate of 1.5x the FASTQ bytes on a helper thread, cut back
+    to what was written at the end): on tmpfs the sink otherwise spends most of its time waiting for the kernel to allocate and zero the
+    pages it copies into.  Default: on for regular files, BT2HOST_STREAM_PREALLOC=0 turns it off.
     start / end: byte range of the file to take (both at record starts): a shard of a multi-GPU job (reads shard by batch,
     every device holds a replica of the index, the per-shard SAM files are concatenated in shard order); header=False for shards > 0."""
     if os.environ.get("BT2HOST_STREAM_CHUNK_MB"):
@@ -38,6 +42,7 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, a
         avail = max(2, nc - 2 if nc >= 8 else nc)
         threads = (max(1, avail * 3 // 8), max(1, avail - avail * 3 // 8))
     job.set_threads(*threads)
+    want_prealloc = preallocate if preallocate is not None else os.environ.get("BT2HOST_STREAM_PREALLOC", "1") != "0"
     own = aligners is None
     if own:
         aligners = [GpuAligner(job, device)]
@@ -67,6 +72,17 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, a
     def sink():
         try:
             with open(out_path, "w+b") as f:      # read + write: the sink copies its blocks into the file through a shared mapping
+                pre = None
+                if want_prealloc and stat.S_ISREG(os.fstat(f.fileno()).st_mode):
+                    span = (end if end is not None else os.path.getsize(fastq)) - start
+                    est = span + span // 2 + (1 << 20)
+
+                    def reserve(fd=f.fileno(), est=est):
+                        try:
+                            os.posix_fallocate(fd, 0, est)     # (releases the GIL; pages the sink touches first are simply skipped)
+                        except OSError:
+                            pass
+                    pre = threading.Thread(target=reserve); pre.start()
                 if header:
                     f.write(job.sam_header().encode("latin-1"))
                 while True:
@@ -83,6 +99,10 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, a
                     finally:
                         b.close()
                         free[k].release()
+                if pre is not None:
+                    pre.join()
+                    f.flush()
+                    f.truncate(f.tell())          # (the reservation was an estimate)
         except Exception as e:
             errors.append(e)
             while True:                     # keep the producer from blocking
