@@ -401,8 +401,8 @@ void do_run(bt2gpu_ctx* c, uint32_t aln_glob = 0, uint32_t edit_glob = 0) {
 				{ Phase ph(c, PH_FILL, cs);
 				  FillArgs fa; fa.probs = sprobs; fa.nprob = k; fa.states = states; fa.seq = ba.seq; fa.qual = ba.qual; fa.cells = scells; fa.cell_stride = c->cellStride;
 				  fa.pcache = spc; fa.hef_dbg = nullptr; fa.stats = stats + 8; fa.error = c->poolerr.as<uint32_t>(); fa.exact = c->hp.exactBestLtMinsc;
-				  // (one launch over 1 Mi problems measured 3 % slower than four over 256 Ki: BT2GPU_FILL_SPLIT problems per launch)
-				  static const uint32_t fsplit = getenv("BT2GPU_FILL_SPLIT") ? (uint32_t)std::max(4, atoi(getenv("BT2GPU_FILL_SPLIT"))) & ~3u : 0u;
+				  // (one launch over 1 Mi problems measured 3 % slower than four over 256 Ki -- 14.5 vs 14.0 ms: BT2GPU_FILL_SPLIT problems per launch, 0 = one launch)
+				  static const uint32_t fsplit = getenv("BT2GPU_FILL_SPLIT") ? (atoi(getenv("BT2GPU_FILL_SPLIT")) > 0 ? (uint32_t)std::max(4, atoi(getenv("BT2GPU_FILL_SPLIT"))) & ~3u : 0u) : 262144u;
 				  if(fsplit && k > fsplit) {
 					for(uint32_t p0 = 0; p0 < k; p0 += fsplit) {
 						FillArgs fb = fa; fb.probs = sprobs + p0; fb.nprob = std::min(fsplit, k - p0);

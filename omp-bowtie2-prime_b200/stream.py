@@ -30,7 +30,8 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, a
     to the aligner's own host threads when there are at least eight.
     preallocate: reserve the output file's blocks ahead of the sink (posix_fallocate of 1.5x the FASTQ bytes on a helper thread, cut back
     to what was written at the end): on tmpfs the sink otherwise spends most of its time waiting for the kernel to allocate and zero the
-    pages it copies into.  Default: on for regular files, BT2HOST_STREAM_PREALLOC=0 turns it off.
+    pages it copies into.  Default: off (BT2HOST_STREAM_PREALLOC=1 turns it on) -- measured on tmpfs it cost more than it saved: the
+    reservation holds the file's lock and a core while the pipeline wants both (8.1 vs 8.8 M reads/s).
     start / end: byte range of the file to take (both at record starts): a shard of a multi-GPU job (reads shard by batch,
     every device holds a replica of the index, the per-shard SAM files are concatenated in shard order); header=False for shards > 0."""
     if os.environ.get("BT2HOST_STREAM_CHUNK_MB"):
@@ -42,7 +43,7 @@ def fastq_to_sam(job, fastq, out_path, device=0, chunk_bytes=64 << 20, mode=1, a
         avail = max(2, nc - 2 if nc >= 8 else nc)
         threads = (max(1, avail * 3 // 8), max(1, avail - avail * 3 // 8))
     job.set_threads(*threads)
-    want_prealloc = preallocate if preallocate is not None else os.environ.get("BT2HOST_STREAM_PREALLOC", "1") != "0"
+    want_prealloc = preallocate if preallocate is not None else os.environ.get("BT2HOST_STREAM_PREALLOC", "0") != "0"
     own = aligners is None
     if own:
         aligners = [GpuAligner(job, device)]

@@ -106,4 +106,9 @@ def test_streamed_fastq_to_sam_equals_whole_file(tmp_path):
     got = (tmp_path / "s.sam").read_bytes()
     assert n == 1000 and got == want and nbytes == len(want) - len(job.sam_header().encode("latin-1"))
     assert job.metrics()[0] - m0[0] == 1000
+    # with the output file reserved ahead of the sink (and cut back to what was written), explicit reader / sink thread counts
+    st = {}
+    n, _ = stream.fastq_to_sam(job, src, str(tmp_path / "p.sam"), chunk_bytes=60000, aligners=[o1, o2], preallocate=True, threads=(2, 2), stats=st)
+    assert n == 1000 and (tmp_path / "p.sam").read_bytes() == want
+    assert st["ranges"] >= 3 and st["threads"] == [2, 2] and st["parse"] > 0 and st["sam"] > 0
     o1.close(); o2.close(); batch.close(); job.close()
