@@ -337,13 +337,13 @@ def file_to_file(pkg, job, ascii_reads, device, repeat=4):
                 null_best, null_stages = dt, st
         for g in al:
             g.close()
-        busy = {k: round(stages[k], 4) for k in ("parse", "align", "sam")}
-        null_busy = {k: round(null_stages[k], 4) for k in ("parse", "align", "sam")}
+        busy = {k: round(stages[k], 4) for k in ("parse", "align", "sam", "write")}
+        null_busy = {k: round(null_stages[k], 4) for k in ("parse", "align", "sam", "write")}
         return {"value": nr / best, "unit": "reads/s", "reads": nr, "fastq_bytes": os.path.getsize(fq), "sam_bytes": nb, "seconds": best,
                 "where": tmp, "host_cores": cpu_cores(), "ranges": stages["ranges"], "reader_sink_threads": stages["threads"], "stage_busy_s": busy, "limiting_stage": max(busy, key=busy.get),
                 "sam_to_dev_null": {"value": nr / null_best, "unit": "reads/s", "seconds": null_best, "stage_busy_s": null_busy, "limiting_stage": max(null_busy, key=null_busy.get)},
                 "note": "FASTQ file -> parse -> bt2gpu_align_batch -> SAM formatting -> SAM file, pipelined over byte ranges of the file; stage_busy_s = "
-                        "seconds each of the three overlapping stages was at work (parse and sam share the host cores)"}
+                        "seconds each of the four overlapping stages was at work (parse, sam = formatting and write share the host cores)"}
     finally:
         for f in (fq, sam):
             if os.path.exists(f):
@@ -369,7 +369,7 @@ def file_to_file_sharded(pkg, job, ascii_reads, device, rank, world, dist, torch
     start, end = (ends[rank - 1] if rank else 0), ends[rank]
     part = os.path.join(tmp, "bt2gpu_bench.sam.%d" % rank)
     share = max(2, cpu_cores() // world)           # the ranks of one box split its cores
-    thr = (max(1, share * 3 // 8), max(1, share - share * 3 // 8))
+    thr = (max(1, share * 3 // 8), max(1, share * 3 // 8))
     al = [pkg.GpuAligner(job, device)]
     try:
         stream.fastq_to_sam(job, fq, part, device, aligners=al, start=start, end=end, header=rank == 0, threads=thr)     # warm-up

@@ -88,6 +88,12 @@ char *bt2host_sam_records(const bt2host_job *job, const bt2host_batch *b,
  * (errno is write's); *len receives the number of bytes written. */
 int bt2host_sam_write(const bt2host_job *job, const bt2host_batch *b,
                       const bt2gpu_results *res, int mode, int fd, size_t *len);
+/* bt2host_sam_write in two halves, for a sink that formats batch i+1 while batch i is being written (the reference's AlnSinkSam::append
+ * and OutputQueue::flush are two stages as well): bt2host_sam_format fills the job's block set `set` (0 or 1) and needs the batch and
+ * its results only until it returns (*len: bytes formatted); bt2host_sam_flush writes that set to the descriptor like
+ * bt2host_sam_write does.  One thread at a time per set. */
+int bt2host_sam_format(const bt2host_job *job, const bt2host_batch *b, const bt2gpu_results *res, int mode, int set, size_t *len);
+int bt2host_sam_flush(const bt2host_job *job, int set, int fd, size_t *len);
 void bt2host_free(void *p);
 
 /* Summary counters of the last bt2host_sam_records call sequence on this job

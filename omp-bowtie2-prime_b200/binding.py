@@ -125,6 +125,8 @@ def load_host():
         h.bt2host_sam_records.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(bt2gpu_results), C.c_int, C.POINTER(C.c_size_t)]
         h.bt2host_sam_write.restype = C.c_int
         h.bt2host_sam_write.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(bt2gpu_results), C.c_int, C.c_int, C.POINTER(C.c_size_t)]
+        h.bt2host_sam_format.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(bt2gpu_results), C.c_int, C.c_int, C.POINTER(C.c_size_t)]
+        h.bt2host_sam_flush.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_size_t)]
         h.bt2host_free.argtypes = [C.c_void_p]
         h.bt2host_job_metrics.argtypes = [C.c_void_p, C.POINTER(C.c_uint64 * 4)]
         h.bt2host_job_set_threads.argtypes = [C.c_void_p, C.c_int, C.c_int]
@@ -240,6 +242,21 @@ class Job:
         n = C.c_size_t(0)
         if self._h.bt2host_sam_write(self.ptr, batch.ptr, C.byref(results.raw), mode, fileobj.fileno(), C.byref(n)) != 0:
             raise OSError("bt2host_sam_write failed")
+        return n.value
+
+    def sam_format(self, batch, results, block_set, mode=1):
+        """First half of sam_write: the records formatted into the job's block set 0 or 1 (the batch and its results are free afterwards)."""
+        n = C.c_size_t(0)
+        if self._h.bt2host_sam_format(self.ptr, batch.ptr, C.byref(results.raw), mode, block_set, C.byref(n)) != 0:
+            raise OSError("bt2host_sam_format failed")
+        return n.value
+
+    def sam_flush(self, block_set, fileobj):
+        """Second half: block set 0 or 1 written to an open binary file; returns the number of bytes."""
+        fileobj.flush()
+        n = C.c_size_t(0)
+        if self._h.bt2host_sam_flush(self.ptr, block_set, fileobj.fileno(), C.byref(n)) != 0:
+            raise OSError("bt2host_sam_flush failed")
         return n.value
 
     def set_threads(self, reader=0, sink=0):

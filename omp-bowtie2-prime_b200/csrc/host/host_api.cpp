@@ -94,14 +94,14 @@ static char* dup_out(const std::string& s, size_t* len) {
 char* bt2host_sam_header(const bt2host_job* job) { return dup_out(bt2host::sam_header(job->j), nullptr); }
 // AlnSinkWrap::finishRead -> AlnSinkSam::append per read (aln_sink.cpp:643,1477): reads are independent (their RNG state
 // comes back with the results), so contiguous blocks of reads are formatted by OpenMP threads; the blocks are in read order
-static std::vector<std::string>& sam_blocks(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode) {
+static std::vector<std::string>& sam_blocks(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, int set = 0) {
 	const uint32_t n = res->n;
 	bt2host::Job& j = const_cast<bt2host_job*>(job)->j;
 	int nt = 1;
 #ifdef _OPENMP
 	nt = std::max(1, std::min(j.sink_threads > 0 ? j.sink_threads : omp_get_max_threads(), (int)(n / 2048) + 1));
 #endif
-	std::vector<std::string>& parts = j.sinkparts;   // the blocks' strings keep their capacity (and pages) from call to call
+	std::vector<std::string>& parts = j.sinkparts[set & 1];   // the blocks' strings keep their capacity (and pages) from call to call
 	if(parts.size() < (size_t)nt) parts.resize((size_t)nt);
 	for(std::string& o : parts) o.clear();
 	std::vector<uint64_t> mets((size_t)nt * 4, 0);
@@ -140,12 +140,31 @@ char* bt2host_sam_records(const bt2host_job* job, const bt2host_batch* b, const 
 	return out;
 }
 static double now_ms() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; }
-int bt2host_sam_write(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, int fd, size_t* len) {
+// The sink in two halves, for a caller that formats batch i+1 while batch i is being written: bt2host_sam_format fills block set `set`
+// (0 or 1) and needs the batch and its results only until it returns; bt2host_sam_flush writes that set to the descriptor.
+int bt2host_sam_format(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, int set, size_t* len) {
 	static const bool trace = getenv("BT2HOST_TRACE") != nullptr;
 	const double t0 = now_ms();
-	std::vector<std::string>& parts = sam_blocks(job, b, res, mode);
+	std::vector<std::string>& parts = sam_blocks(job, b, res, mode, set);
+	size_t tot = 0; for(const std::string& o : parts) tot += o.size();
+	if(len) *len = tot;
+	if(trace) fprintf(stderr, "[bt2host] sam: %u reads formatted in %.1f ms (%zu blocks, set %d)\n", res->n, now_ms() - t0, parts.size(), set & 1);
+	return 0;
+}
+int bt2host_sam_write(const bt2host_job* job, const bt2host_batch* b, const bt2gpu_results* res, int mode, int fd, size_t* len) {
+	if(bt2host_sam_format(job, b, res, mode, 0, nullptr) != 0) return -1;
+	return bt2host_sam_flush(job, 0, fd, len);
+}
+int bt2host_sam_flush(const bt2host_job* job, int set, int fd, size_t* len) {
+	static const bool trace = getenv("BT2HOST_TRACE") != nullptr;
 	const double t1 = now_ms();
-	struct Tr { bool on; double t0, t1; uint32_t n; size_t np; ~Tr() { if(on) fprintf(stderr, "[bt2host] sam: %u reads, format %.1f ms, write %.1f ms (%zu blocks)\n", n, t1 - t0, now_ms() - t1, np); } } tr{trace, t0, t1, res->n, parts.size()};
+	bt2host::Job& j = const_cast<bt2host_job*>(job)->j;
+	std::vector<std::string>& parts = j.sinkparts[set & 1];
+	struct Tr { bool on; double t1; size_t np; ~Tr() { if(on) fprintf(stderr, "[bt2host] sam: written in %.1f ms (%zu blocks)\n", now_ms() - t1, np); } } tr{trace, t1, parts.size()};
+	int ncopy = 1;   // threads that copy / write (the blocks may be more: they are what the formatting call's threads made)
+#ifdef _OPENMP
+	ncopy = std::max(1, j.sink_threads > 0 ? j.sink_threads : omp_get_max_threads());
+#endif
 	const int nt = (int)parts.size();
 	std::vector<size_t> offs((size_t)nt + 1, 0);
 	for(int t = 0; t < nt; t++) offs[(size_t)t + 1] = offs[(size_t)t] + parts[(size_t)t].size();
@@ -179,7 +198,7 @@ int bt2host_sam_write(const bt2host_job* job, const bt2host_batch* b, const bt2g
 				static const bool populate = getenv("BT2HOST_SAM_POPULATE") && atoi(getenv("BT2HOST_SAM_POPULATE")) != 0;   // (off: measured no faster than faulting the pages in from the copy)
 				std::vector<std::pair<int, size_t>> work;
 				for(int t = 0; t < nt; t++) for(size_t o = 0; o < parts[(size_t)t].size(); o += piece) work.push_back(std::make_pair(t, o));
-				#pragma omp parallel for num_threads(nt) schedule(dynamic, 1)
+				#pragma omp parallel for num_threads(ncopy) schedule(dynamic, 1)
 				for(size_t w = 0; w < work.size(); w++) {
 					const std::string& src = parts[(size_t)work[w].first]; const size_t o = work[w].second;
 					char* to = dst + offs[(size_t)work[w].first] + o; const size_t nb = std::min(piece, src.size() - o);
@@ -199,7 +218,7 @@ int bt2host_sam_write(const bt2host_job* job, const bt2host_batch* b, const bt2g
 		}
 	}
 	if(base >= 0 && nt > 1 && !append) {   // a seekable file: the blocks are written side by side at their final offsets
-		#pragma omp parallel for num_threads(nt) schedule(static, 1) reduction(&&: ok)
+		#pragma omp parallel for num_threads(ncopy) schedule(static, 1) reduction(&&: ok)
 		for(int t = 0; t < nt; t++) ok = ok && put(fd, parts[(size_t)t].data(), parts[(size_t)t].size(), base + (off_t)offs[(size_t)t]);
 		if(ok && lseek(fd, base + (off_t)tot, SEEK_SET) < 0) ok = false;
 	} else {

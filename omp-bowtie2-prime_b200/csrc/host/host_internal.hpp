@@ -64,7 +64,7 @@ struct Job {
 	Options opt;
 	uint64_t met[4] = {0, 0, 0, 0};
 	// buffers that keep their pages between calls (a job is used by one caller thread at a time)
-	std::vector<std::string> sinkparts;   // SAM text of the sink's blocks
+	std::vector<std::string> sinkparts[2];   // SAM text of the sink's blocks, two sets: one can be written while the other is formatted
 	char* file_buffer(size_t n);          // >= n bytes, not initialised, owned by the job
 	char* filemem = nullptr; size_t filecap = 0;
 	mutable std::vector<std::vector<size_t>> scan_nl;   // the reader's per-thread newline positions
