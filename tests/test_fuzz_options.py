@@ -8,7 +8,7 @@ import pytest
 import common
 from common import pkg
 
-N_SETS = 64
+N_SETS = 96
 
 
 def option_sets():
@@ -86,7 +86,7 @@ def test_oracle_equals_reference_binary_on_random_options(idx, reads, opts, tmp_
     if not os.access(exe, os.X_OK):
         pytest.skip("oracle/_ref/%s not built" % os.path.basename(exe))
     base = common.index_base(REF_OF[reads])
-    fq = _take(common.reads_path(reads), 400, tmp_path)
+    fq = _take(common.reads_path(reads), 1000, tmp_path)
     r = subprocess.run([exe, "-x", base, "-U", fq, "-p", "30", "--no-hd"] + [x for x in opts.split() if x != "--i16"], capture_output=True,
                        env=dict(os.environ, OMP_NUM_THREADS="2"))
     if r.returncode != 0:
@@ -96,7 +96,7 @@ def test_oracle_equals_reference_binary_on_random_options(idx, reads, opts, tmp_
     batch = job.fastq(fq)
     orc = common.Oracle(job)
     got = common.sorted_records(job.sam(batch, orc.align(batch), mode=1))
-    assert len(got) == len(want) >= 400 or "--no-unal" in opts
+    assert len(got) == len(want) >= 1000
     diff = [(a, b) for a, b in zip(got, want) if a != b]
     assert not diff, "%s\n%d records differ, first:\n%s\n%s" % (opts, len(diff), diff[0][0][:300], diff[0][1][:300])
     orc.close(); batch.close(); job.close()
@@ -106,7 +106,7 @@ def test_oracle_equals_reference_binary_on_random_options(idx, reads, opts, tmp_
 @pytest.mark.parametrize("idx,reads,opts", SETS, ids=["set%02d" % s[0] for s in SETS])
 def test_gpu_equals_oracle_on_random_options(idx, reads, opts, tmp_path):
     base = common.index_base(REF_OF[reads])
-    fq = _take(common.reads_path(reads), 400, tmp_path)
+    fq = _take(common.reads_path(reads), 1000, tmp_path)
     job = pkg.Job(base, opts)
     batch = job.fastq(fq)
     orc = common.Oracle(job)
