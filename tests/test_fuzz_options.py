@@ -117,3 +117,44 @@ def test_gpu_equals_oracle_on_random_options(idx, reads, opts, tmp_path):
     assert not diffs, opts + "\n" + "\n".join(diffs[:10])
     assert job.sam_bytes(batch, got, 1) == job.sam_bytes(batch, want, 1)
     gpu.close(); orc.close(); batch.close(); job.close()
+
+
+# ---- the long-read build on reads of 170..255 bp, where the constants-raised reference is a coherent oracle (tests/test_long_reads.py)
+LONG_SETS = [(i, o + (" --i16" if "--i16" not in o else "")) for i, _, o in SETS[:32] if "--trim" not in o]
+
+
+@pytest.mark.parametrize("idx,opts", LONG_SETS, ids=["long%02d" % s[0] for s in LONG_SETS])
+def test_long_oracle_equals_constants_raised_reference_on_random_options(idx, opts, tmp_path):
+    exe = os.path.join(common.REFBIN, "bowtie2-align-l-long")
+    if not os.access(exe, os.X_OK):
+        pytest.skip("oracle/_ref/bowtie2-align-l-long not built")
+    base = common.index_base("syn")
+    fq = _take(common.reads_path("synL255"), 1600, tmp_path)
+    r = subprocess.run([exe, "-x", base, "-U", fq, "-p", "2", "--no-hd"] + [x for x in opts.split() if x != "--i16"], capture_output=True,
+                       env=dict(os.environ, OMP_NUM_THREADS="2"))
+    assert r.returncode == 0, r.stderr.decode("latin-1")[-300:]
+    want = common.sorted_records(r.stdout.decode("latin-1"))
+    job = pkg.Job(base, opts)
+    batch = job.fastq(fq)
+    orc = common.Oracle(job, long_reads=True)
+    got = common.sorted_records(job.sam(batch, orc.align(batch), mode=1))
+    diff = [(a, b) for a, b in zip(got, want) if a != b]
+    assert len(got) == len(want) and not diff, "%s\n%d records differ, first:\n%s\n%s" % (opts, len(diff), diff[0][0][:300] if diff else "", diff[0][1][:300] if diff else "")
+    orc.close(); batch.close(); job.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("idx,opts", LONG_SETS, ids=["long%02d" % s[0] for s in LONG_SETS])
+def test_long_gpu_equals_oracle_on_random_options(idx, opts, tmp_path):
+    base = common.index_base("syn")
+    fq = _take(common.reads_path("synLmix") if idx % 2 else common.reads_path("synL255"), 1600, tmp_path)
+    job = pkg.Job(base, opts)
+    batch = job.fastq(fq)
+    orc = common.Oracle(job, long_reads=True)
+    want = orc.align(batch)
+    gpu = pkg.GpuAligner(job, 0, long_reads=True)
+    got = gpu.align(batch)
+    diffs = common.compare_results(want, got, i16path=True)
+    assert not diffs, opts + "\n" + "\n".join(diffs[:10])
+    assert job.sam_bytes(batch, got, 1) == job.sam_bytes(batch, want, 1)
+    gpu.close(); orc.close(); batch.close(); job.close()
