@@ -129,7 +129,8 @@ def test_full_size_properties(monkeypatch):
 
 @pytest.mark.gpu
 def test_streamed_fastq_to_sam_equals_one_batch(tmp_path):
-    """the reader / aligner / sink pipeline over byte ranges of the 1 M read file (two contexts on the device) writes the SAM of one batch"""
+    """the reader / aligner / formatter / writer pipeline over byte ranges of the 1 M read file (ONE context: two result sets, two block
+    sets) writes the SAM of one batch; then once more with the reader's arrays page-locked (bt2gpu_host_alloc) and the output reserved"""
     import importlib
     stream = importlib.import_module("omp-bowtie2-prime_b200.stream")
     job, batch, reads, codes = _workload(N_READS)
@@ -140,4 +141,9 @@ def test_streamed_fastq_to_sam_equals_one_batch(tmp_path):
     n, nbytes = stream.fastq_to_sam(job, os.path.join(bench.WORK, "fullsize_%d.fq" % N_READS), str(tmp_path / "s.sam"), chunk_bytes=64 << 20)
     assert n == N_READS
     assert (tmp_path / "s.sam").read_bytes() == want
+    pkg.use_pinned_batches()      # (process-wide and once: False if an earlier test did it; arrays made before keep going back to free())
+    st = {}
+    n, nbytes = stream.fastq_to_sam(job, os.path.join(bench.WORK, "fullsize_%d.fq" % N_READS), str(tmp_path / "p.sam"), chunk_bytes=48 << 20, preallocate=True, stats=st)
+    assert n == N_READS and st["ranges"] >= 6
+    assert (tmp_path / "p.sam").read_bytes() == want
     batch.close(); job.close()
