@@ -40,12 +40,10 @@ def main():
         batch.close()
     # the same three stages as a pipeline over byte ranges of the file (omp-bowtie2-prime_b200/stream.py)
     stream = importlib.import_module("omp-bowtie2-prime_b200.stream")
-    pair = [gpu, pkg.GpuAligner(job, 0)]
-    for rep in range(3):
+    for rep in range(3):            # (one context: two result sets, two block sets)
         t0 = time.time()
-        stream.fastq_to_sam(job, fq, os.path.join(bench.WORK, "host_bench.sam"), aligners=pair)
+        stream.fastq_to_sam(job, fq, os.path.join(bench.WORK, "host_bench.sam"), aligners=[gpu])
         best["pipelined"] = min(best.get("pipelined", 1e9), time.time() - t0)
-    pair[1].close()
     for k, v in best.items():
         out[k + "_s"] = round(v, 4); out[k + "_reads_per_s"] = round(n / v)
     print(json.dumps(out))
