@@ -220,8 +220,9 @@ void launch_fill(uint32_t K, bool dbg, const DevParams* dP, const FillArgs& fa, 
 	const dim3 grid(nblk(fa.nprob, BT2_FILL_WARPS * 4)), block(BT2_FILL_WARPS * 32);
 #if BT2_FILL_DYNSMEM
 	// (the long-read build: the tables of a 1000-row problem do not fit the 48 KB a kernel gets without asking)
-	#define BT2_LF1(KK, DD) { static bool once = false; const size_t smem = BT2_FILL_WARPS * sizeof(FillShared<KK>); \
-		if(!once) { CK(cudaFuncSetAttribute(k_fill<KK, DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); once = true; } \
+	#define BT2_LF1(KK, DD) { static bool once[64] = { false }; const size_t smem = BT2_FILL_WARPS * sizeof(FillShared<KK>); \
+		int dev_ = 0; CK(cudaGetDevice(&dev_)); dev_ &= 63;   /* (the attribute is per device) */ \
+		if(!once[dev_]) { CK(cudaFuncSetAttribute(k_fill<KK, DD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); once[dev_] = true; } \
 		k_fill<KK, DD><<<grid, block, smem, st>>>(dP, fa); }
 	#define BT2_LF(KK) { if(dbg) BT2_LF1(KK, true) else BT2_LF1(KK, false) }
 #else
