@@ -54,7 +54,9 @@ struct FillArgs {
 #define BT2_FILL_WARPS 1               // the long-read build: a warp's tables take ~70 KB of (dynamic) shared memory
 #define BT2_FILL_DYNSMEM 1
 #else
+#ifndef BT2_FILL_WARPS
 #define BT2_FILL_WARPS 2
+#endif
 #define BT2_FILL_DYNSMEM 0
 #endif
 #ifndef BT2_FILL_UNROLL
