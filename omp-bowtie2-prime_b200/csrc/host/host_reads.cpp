@@ -80,7 +80,8 @@ bool parse_options(Options& o, const std::string& args, std::string& err) {
 		else if(t == "--end-to-end") { }
 		else if(t == "--exact-xs") { p.exactBestLtMinsc = 1; }   // (not a reference option) bt2gpu_params.exactBestLtMinsc: fill whole DP rectangles
 		else if(t == "-D") { if(!(a = need(i))) return false; maxDpStreak = atoi(a->c_str()); }
-		else if(t == "-R") { if(!(a = need(i))) return false; p.nSeedRounds = atoi(a->c_str()); }
+		else if(t == "-R") { if(!(a = need(i))) return false; p.nSeedRounds = atoi(a->c_str());
+			if(p.nSeedRounds < 1) { err = "-R must be at least 1 (the reference divides by it: bowtie2-align dies of SIGFPE with -R 0)"; return false; } }
 		else if(t == "-L") { if(!(a = need(i))) return false; p.seedLen = atoi(a->c_str());
 			if(p.seedLen < 1 || p.seedLen > 32) { err = "-L must be within [1,32]"; return false; } }
 		else if(t == "-N") { if(!(a = need(i))) return false; p.seedMms = atoi(a->c_str()); }
