@@ -100,6 +100,10 @@ __device__ __forceinline__ void prio_work(const PrioArrays& pa, uint32_t ai, uin
 #ifndef BT2_PRIO_BLOCKS_PER_SM
 #define BT2_PRIO_BLOCKS_PER_SM 6
 #endif
+#ifndef BT2_PRIO_CACHE
+#define BT2_PRIO_CACHE 48   // seed hits (both strands) a thread copies: 2 x 9 for 150 bp --sensitive, 2 x 19 for --very-sensitive
+#endif
+static_assert(sizeof(SeedHit) == 32, "SeedHit is copied as two uint4");
 __global__ void __launch_bounds__(128, BT2_PRIO_BLOCKS_PER_SM) k_prio1(const DevParams* __restrict__ Pp, const Pools pools, ReadState* states, const uint32_t* active, uint32_t nactive,
                         const SeedHit* hits, uint32_t W, uint32_t maxOffs, const PrioArrays pa,
                         uint32_t* ext_list, uint32_t* ext_cnt, uint32_t* samp_list, uint32_t* samp_cnt) {
@@ -111,7 +115,17 @@ __global__ void __launch_bounds__(128, BT2_PRIO_BLOCKS_PER_SM) k_prio1(const Dev
 	uint32_t offset = 0; round_wanted(P, rs, rs.round, offset);
 	const SeedGeom g = seed_geom(P, rs.rdlen, offset, (uint32_t)rs.interval, maxOffs);
 	PrioWork w; prio_work(pa, ai, W, w);
-	const bool sample = prio_stage1(P, pools, rs, hits + (size_t)ai * W, g, w);
+	// The read's seed hits are scanned O(n^2) times (duplicate keys, rankSeedHits, the sort): a thread-local copy turns those scans from
+	// 32-byte records 32 W bytes apart across the warp into local-memory accesses, which the hardware interleaves across the lanes.
+	const SeedHit* hp = hits + (size_t)ai * W;
+	SeedHit lh[BT2_PRIO_CACHE];
+	if(W <= BT2_PRIO_CACHE) {
+		const uint4* src = reinterpret_cast<const uint4*>(hp); uint4* dst = reinterpret_cast<uint4*>(lh);
+		for(uint32_t k = 0; k < 2u * W; k++) dst[k] = src[k];
+		hp = lh;
+	}
+	// (the same for the stage's index arrays measured no further gain: they stay in global memory, where the row sampler reads them)
+	const bool sample = prio_stage1(P, pools, rs, hp, g, w);
 	if(rs.numRanges == 0 || rs.nonzTot == 0) {
 		rs.flags |= BT2GPU_RF_NO_SEED_HITS; rs.phase = RS_FINISHED;
 	} else {
